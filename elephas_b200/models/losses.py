@@ -1,0 +1,112 @@
+"""Keras-named losses on torch (``sum_over_batch_size`` reduction, epsilon 1e-7 as in Keras).
+
+The reference passes ``model.loss`` strings straight to ``keras.Model.compile``
+(``elephas/worker.py:32``, ``elephas/spark_model.py:193``); the names exercised by its tests are
+``categorical_crossentropy``, ``binary_crossentropy``, ``mse``, ``mae``
+(``tests/integration/test_end_to_end.py:40,92``, ``test_custom_models.py:24``,
+``tests/test_ml_model.py:150``). Each loss returns the per-sample loss vector; callers average.
+"""
+import torch
+
+EPS = 1e-7
+
+
+def _match(y_true, y_pred):
+    y_true = y_true.to(y_pred.dtype)
+    if y_true.dim() == y_pred.dim() - 1:
+        y_true = y_true.unsqueeze(-1)
+    return y_true
+
+
+def mean_squared_error(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    return ((y_pred - y_true) ** 2).flatten(1).mean(dim=1) if y_pred.dim() > 1 else (y_pred - y_true) ** 2
+
+
+def mean_absolute_error(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    return (y_pred - y_true).abs().flatten(1).mean(dim=1) if y_pred.dim() > 1 else (y_pred - y_true).abs()
+
+
+def mean_absolute_percentage_error(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    diff = ((y_true - y_pred) / torch.clamp(y_true.abs(), min=EPS)).abs()
+    return 100.0 * (diff.flatten(1).mean(dim=1) if diff.dim() > 1 else diff)
+
+
+def mean_squared_logarithmic_error(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    a = torch.log(torch.clamp(y_pred, min=EPS) + 1.0)
+    b = torch.log(torch.clamp(y_true, min=EPS) + 1.0)
+    d = (a - b) ** 2
+    return d.flatten(1).mean(dim=1) if d.dim() > 1 else d
+
+
+def categorical_crossentropy(y_true, y_pred):
+    """``y_pred`` are probabilities; Keras renormalises, clips to [eps, 1-eps] and takes -sum(y log p)."""
+    y_true = y_true.to(y_pred.dtype)
+    p = y_pred / y_pred.sum(dim=-1, keepdim=True)
+    p = torch.clamp(p, EPS, 1.0 - EPS)
+    return -(y_true * torch.log(p)).sum(dim=-1)
+
+
+def sparse_categorical_crossentropy(y_true, y_pred):
+    idx = y_true.reshape(y_pred.shape[0], -1)[:, 0].long()
+    p = torch.clamp(y_pred, EPS, 1.0 - EPS)
+    return -torch.log(p.gather(1, idx.unsqueeze(1))).squeeze(1)
+
+
+def binary_crossentropy(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    p = torch.clamp(y_pred, EPS, 1.0 - EPS)
+    bce = -(y_true * torch.log(p) + (1.0 - y_true) * torch.log(1.0 - p))
+    return bce.flatten(1).mean(dim=1) if bce.dim() > 1 else bce
+
+
+def logcosh(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    d = y_pred - y_true
+    v = d + torch.nn.functional.softplus(-2.0 * d) - 0.6931471805599453
+    return v.flatten(1).mean(dim=1) if v.dim() > 1 else v
+
+
+def cosine_proximity(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    a = torch.nn.functional.normalize(y_true, dim=-1)
+    b = torch.nn.functional.normalize(y_pred, dim=-1)
+    return -(a * b).sum(dim=-1)
+
+
+_BUILTIN = {
+    'mean_squared_error': mean_squared_error, 'mse': mean_squared_error, 'MSE': mean_squared_error,
+    'mean_absolute_error': mean_absolute_error, 'mae': mean_absolute_error, 'MAE': mean_absolute_error,
+    'mean_absolute_percentage_error': mean_absolute_percentage_error, 'mape': mean_absolute_percentage_error,
+    'mean_squared_logarithmic_error': mean_squared_logarithmic_error, 'msle': mean_squared_logarithmic_error,
+    'categorical_crossentropy': categorical_crossentropy,
+    'sparse_categorical_crossentropy': sparse_categorical_crossentropy,
+    'binary_crossentropy': binary_crossentropy,
+    'logcosh': logcosh, 'log_cosh': logcosh,
+    'cosine_proximity': cosine_proximity, 'cosine_similarity': cosine_proximity,
+}
+
+CANONICAL = {
+    'mse': 'mean_squared_error', 'MSE': 'mean_squared_error', 'mae': 'mean_absolute_error',
+    'MAE': 'mean_absolute_error', 'mape': 'mean_absolute_percentage_error',
+    'msle': 'mean_squared_logarithmic_error', 'log_cosh': 'logcosh', 'cosine_similarity': 'cosine_proximity',
+}
+
+
+def canonical_name(identifier):
+    if callable(identifier):
+        return getattr(identifier, '__name__', 'custom_loss')
+    return CANONICAL.get(identifier, identifier)
+
+
+def get(identifier, custom_objects=None):
+    if callable(identifier):
+        return identifier
+    if custom_objects and identifier in custom_objects:
+        return custom_objects[identifier]
+    if identifier in _BUILTIN:
+        return _BUILTIN[identifier]
+    raise ValueError("Unknown loss function: %r" % (identifier,))

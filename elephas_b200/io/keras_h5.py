@@ -1,0 +1,159 @@
+"""Keras-HDF5-compatible model files.
+
+Reference: ``SparkModel.save`` = ``keras.Model.save(file)`` + one extra root attribute
+``distributed_config`` (``elephas/spark_model.py:115-125``); ``load_spark_model`` =
+``keras.models.load_model`` + reading that attribute back (``:376-381``). The layout reproduced here
+is the Keras 2.10 HDF5 format:
+
+* root attributes ``keras_version``, ``backend``, ``model_config`` (the ``to_json()`` payload),
+  ``training_config`` (JSON with ``loss``, ``metrics``, ``optimizer_config``);
+* group ``model_weights`` with attributes ``layer_names``, ``backend``, ``keras_version`` and one
+  sub-group per layer carrying ``weight_names`` and datasets such as ``dense/kernel:0`` (shape
+  ``(in, out)``) and ``dense/bias:0``;
+* optional group ``optimizer_weights`` (iteration counter and slot variables).
+"""
+import json
+import os
+
+import numpy as np
+
+from . import hdf5
+from ..models import model as _model_mod
+from ..models import optimizers as _optimizers
+
+
+def _training_config(model):
+    loss = model.loss if isinstance(model.loss, str) else getattr(model.loss, '__name__', None)
+    metrics = [m if isinstance(m, str) else getattr(m, '__name__', str(m))
+               for m in (model.compiled_metrics._metrics or [])]
+    return {'loss': loss, 'metrics': metrics, 'weighted_metrics': None, 'loss_weights': None,
+            'optimizer_config': _optimizers.serialize(model.optimizer)}
+
+
+def _optimizer_weight_entries(model):
+    opt = model.optimizer
+    names = ['%s/iter:0' % opt._class_name]
+    values = [np.asarray(opt.iterations, dtype=np.int64)]
+    params = model.trainable_weights
+    layer_of = {}
+    for layer in model.layers:
+        for n, w, _ in layer._weights:
+            layer_of[id(w)] = '%s/%s' % (layer.name, n)
+    for (idx, slot), tensor in sorted(opt._slots.items(), key=lambda kv: (kv[0][0], kv[0][1])):
+        if idx < len(params):
+            base = layer_of.get(id(params[idx]), 'param_%d' % idx)
+            names.append('%s/%s/%s:0' % (opt._class_name, base, slot))
+            values.append(tensor.detach().cpu().numpy())
+    return names, values
+
+
+def build_tree(model, include_optimizer=True, extra_root_attrs=None):
+    root = hdf5.Group()
+    root.attrs['keras_version'] = _model_mod.KERAS_VERSION.encode('utf8')
+    root.attrs['backend'] = _model_mod.BACKEND.encode('utf8')
+    root.attrs['model_config'] = json.dumps(
+        {'class_name': model._json_class_name, 'config': model.get_config()}).encode('utf8')
+    compiled = getattr(model, '_compiled', False)
+    if compiled:
+        root.attrs['training_config'] = json.dumps(_training_config(model)).encode('utf8')
+    mw = root.create_group('model_weights')
+    layers = [l for l in model.layers]
+    mw.attrs['layer_names'] = np.array([l.name.encode('utf8') for l in layers]) if layers else np.zeros((0,))
+    mw.attrs['backend'] = _model_mod.BACKEND.encode('utf8')
+    mw.attrs['keras_version'] = _model_mod.KERAS_VERSION.encode('utf8')
+    model._sync_from_engine()
+    for layer in layers:
+        g = mw.create_group(layer.name)
+        names = layer.weight_names()
+        g.attrs['weight_names'] = np.array([n.encode('utf8') for n in names]) if names else np.zeros((0,))
+        for idx, (name, (_, w, _t)) in enumerate(zip(names, layer._weights)):
+            value = layer.to_keras_layout(idx, w.detach()).cpu().numpy()
+            g.create_dataset(name, np.ascontiguousarray(value, dtype=np.float32))
+    if include_optimizer and compiled and model.optimizer is not None:
+        ow = root.create_group('optimizer_weights')
+        names, values = _optimizer_weight_entries(model)
+        ow.attrs['weight_names'] = np.array([n.encode('utf8') for n in names])
+        for n, v in zip(names, values):
+            ow.create_dataset(n, v)
+    for k, v in (extra_root_attrs or {}).items():
+        root.attrs[k] = v
+    return root
+
+
+def save_model(model, filepath, overwrite=True, include_optimizer=True, extra_root_attrs=None):
+    filepath = str(filepath)
+    if os.path.exists(filepath) and not overwrite:
+        raise IOError("%s already exists" % filepath)
+    hdf5.save_tree(filepath, build_tree(model, include_optimizer, extra_root_attrs))
+
+
+def _text(value):
+    if isinstance(value, bytes):
+        return value.decode('utf8')
+    if isinstance(value, np.ndarray) and value.shape == ():
+        return _text(value[()])
+    return value
+
+
+def _names(value):
+    if value is None:
+        return []
+    arr = np.asarray(value)
+    if arr.size == 0:
+        return []
+    return [_text(v) for v in arr.ravel().tolist()]
+
+
+def read_root_attrs(filepath):
+    return hdf5.load_tree(str(filepath)).attrs
+
+
+def load_model(filepath, custom_objects=None, compile=True):
+    root = hdf5.load_tree(str(filepath))
+    config = json.loads(_text(root.attrs['model_config']))
+    model = _model_mod.model_from_config(config, custom_objects)
+    mw = root['model_weights']
+    by_layer = {}
+    for lname in _names(mw.attrs.get('layer_names')):
+        g = mw[lname]
+        by_layer[lname] = [np.asarray(g[wn].data) for wn in _names(g.attrs.get('weight_names'))]
+    weights = []
+    for layer in model.layers:
+        vals = by_layer.get(layer.name, [])
+        if len(vals) != len(layer._weights):
+            raise ValueError("layer %r expects %d weights, file has %d" % (layer.name, len(layer._weights), len(vals)))
+        weights.extend(vals)
+    model.set_weights(weights)
+    if compile and 'training_config' in root.attrs:
+        tc = json.loads(_text(root.attrs['training_config']))
+        loss = tc.get('loss')
+        if isinstance(loss, dict):
+            loss = loss.get('config', {}).get('name', loss.get('class_name'))
+        model.compile(optimizer=_optimizers.deserialize(tc['optimizer_config'], custom_objects), loss=loss,
+                      metrics=tc.get('metrics') or None)
+        if 'optimizer_weights' in root:
+            _restore_optimizer(model, root['optimizer_weights'])
+    return model
+
+
+def _restore_optimizer(model, group):
+    import torch
+    opt = model.optimizer
+    params = model.trainable_weights
+    index_of = {}
+    for layer in model.layers:
+        for n, w, _ in layer._weights:
+            for i, p in enumerate(params):
+                if p is w:
+                    index_of['%s/%s' % (layer.name, n)] = i
+    for name in _names(group.attrs.get('weight_names')):
+        value = np.asarray(group[name].data)
+        parts = name.rsplit(':', 1)[0].split('/')
+        if parts[-1] == 'iter':
+            opt.iterations = int(np.asarray(value).reshape(-1)[0])
+            continue
+        slot = parts[-1]
+        key = '/'.join(parts[1:-1])
+        if key in index_of:
+            i = index_of[key]
+            opt._slots[(i, slot)] = torch.from_numpy(np.array(value, dtype=np.float32)).to(params[i].device)

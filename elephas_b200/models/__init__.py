@@ -1,0 +1,13 @@
+"""Keras-compatible model layer on torch plus the built-in workload zoo.
+
+``from elephas_b200.models import Sequential, Dense, ...`` plays the role that
+``tensorflow.keras`` plays for the reference (which has no model code of its own).
+"""
+from . import activations, losses, metrics, optimizers  # noqa: F401
+from .layers import (Activation, Add, AveragePooling2D, BatchNormalization, Concatenate, Conv2D, Dense,  # noqa: F401
+                     Dropout, Flatten, GlobalAveragePooling2D, Input, InputLayer, Layer, MaxPooling2D, ReLU,
+                     Reshape, Softmax, ZeroPadding2D)
+from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
+                    to_categorical)
+from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, Nadam, RMSprop  # noqa: F401
+from . import zoo  # noqa: F401

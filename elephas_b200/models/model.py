@@ -1,0 +1,543 @@
+"""Keras-compatible ``Model`` / ``Sequential`` on torch.
+
+Everything the reference asks of a Keras model is here with the same names and semantics:
+``to_json`` / ``model_from_json`` (``elephas/worker.py:30,87``, ``elephas/spark_model.py:205,239``),
+``compile`` with ``loss`` / ``optimizer`` / ``compiled_metrics._metrics``
+(``elephas/spark_model.py:49-54``), ``get_weights`` / ``set_weights`` (Keras order and layouts),
+``fit`` / ``train_on_batch`` / ``predict`` / ``evaluate`` (``elephas/worker.py:42,108,123``,
+``elephas/spark_model.py:248,291``), ``History.history``, ``save`` / ``load_model`` (Keras HDF5
+layout, see ``elephas_b200/io``).
+
+Execution: on a CUDA device an MLP-shaped model (Dense / Activation / Dropout chains, the shape of
+every workload the reference ships) trains and predicts through the native sm_100a engine
+(``elephas_b200/ops/engine.py``: tcgen05 GEMMs with fused epilogues, fused loss, fused optimizer);
+every other model, and every model on the CPU, runs through torch autograd.
+"""
+import json
+import math
+
+import numpy as np
+import torch
+
+from . import layers as L
+from . import losses as _losses
+from . import metrics as _metrics
+from . import optimizers as _optimizers
+
+_PREDICT_BLOCK = 256
+KERAS_VERSION = '2.10.0'
+BACKEND = 'tensorflow'
+
+
+class History:
+    """``History.history`` maps metric name -> list of per-epoch values (Keras semantics)."""
+
+    def __init__(self):
+        self.history = {}
+        self.epoch = []
+
+    def _append(self, epoch, logs):
+        self.epoch.append(epoch)
+        for k, v in logs.items():
+            self.history.setdefault(k, []).append(v)
+
+
+class _CompiledMetrics:
+    """Shim for ``model.compiled_metrics._metrics`` read by ``SparkModel.__init__`` (spark_model.py:52)."""
+
+    def __init__(self, metrics):
+        self._metrics = metrics
+
+
+def _as_tensor(a, device, dtype=torch.float32):
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype if a.is_floating_point() else None)
+    arr = np.asarray(a)
+    if arr.dtype == object:
+        arr = np.stack([np.asarray(r, dtype=np.float32) for r in arr])
+    t = torch.from_numpy(np.ascontiguousarray(arr))
+    if t.is_floating_point() or t.dtype in (torch.int32, torch.int64, torch.uint8, torch.bool, torch.int16, torch.int8):
+        t = t.to(dtype)
+    return t.to(device)
+
+
+class Model:
+    """Functional-API model: a DAG of layers between ``inputs`` and ``outputs`` (KerasTensors)."""
+
+    _json_class_name = 'Functional'
+
+    def __init__(self, inputs=None, outputs=None, name=None):
+        self.name = name or L.unique_name('model')
+        self.layers = []
+        self._device = torch.device('cpu')
+        self._compiled = False
+        self.optimizer = None
+        self.stop_training = False
+        self._engine = None
+        self._engine_key = None
+        self.custom_objects = {}
+        if inputs is not None:
+            self._init_graph(inputs, outputs)
+
+    # ---------------------------------------------------------------- graph
+    def _init_graph(self, inputs, outputs):
+        self._inputs = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
+        self._outputs = list(outputs) if isinstance(outputs, (list, tuple)) else [outputs]
+        order, seen = [], set()
+
+        def visit(t):
+            key = (id(t.layer), t.node_index)
+            if key in seen:
+                return
+            seen.add(key)
+            for src in t.layer.inbound[t.node_index]:
+                visit(src)
+            order.append(t)
+
+        for o in self._outputs:
+            visit(o)
+        self._node_order = order
+        self.layers = []
+        for t in order:
+            if t.layer not in self.layers:
+                self.layers.append(t.layer)
+
+    def _forward(self, xs, training):
+        values = {}
+        for t, x in zip(self._inputs, xs):
+            values[(id(t.layer), t.node_index)] = x
+        for t in self._node_order:
+            key = (id(t.layer), t.node_index)
+            if key in values:
+                continue
+            ins = [values[(id(s.layer), s.node_index)] for s in t.layer.inbound[t.node_index]]
+            values[key] = t.layer.call(ins[0] if len(ins) == 1 else ins, training=training)
+        outs = [values[(id(o.layer), o.node_index)] for o in self._outputs]
+        return outs[0] if len(outs) == 1 else outs
+
+    def __call__(self, x, training=False):
+        xs = list(x) if isinstance(x, (list, tuple)) else [x]
+        return self._forward(xs, training)
+
+    @property
+    def built(self):
+        return all(l.built for l in self.layers)
+
+    def build(self, input_shape=None):
+        return None
+
+    @property
+    def input_shape(self):
+        shapes = [t.shape for t in self._inputs]
+        return shapes[0] if len(shapes) == 1 else shapes
+
+    @property
+    def output_shape(self):
+        shapes = [t.shape for t in self._outputs]
+        return shapes[0] if len(shapes) == 1 else shapes
+
+    # -------------------------------------------------------------- weights
+    def _weight_entries(self):
+        for layer in self.layers:
+            for idx, (_, w, _) in enumerate(layer._weights):
+                yield layer, idx, w
+
+    @property
+    def weights(self):
+        return [w for _, _, w in self._weight_entries()]
+
+    @property
+    def trainable_weights(self):
+        return [w for l in self.layers for w in l.trainable_weights]
+
+    def count_params(self):
+        return int(sum(w.numel() for w in self.weights))
+
+    def get_weights(self):
+        """List of NumPy arrays in Keras order and Keras layouts (Dense kernels are ``(in, out)``)."""
+        self._sync_from_engine()
+        return [layer.to_keras_layout(idx, w.detach()).cpu().numpy().copy() for layer, idx, w in self._weight_entries()]
+
+    def set_weights(self, weights):
+        entries = list(self._weight_entries())
+        if len(entries) != len(weights):
+            raise ValueError("set_weights got %d arrays for a model with %d weights" % (len(weights), len(entries)))
+        with torch.no_grad():
+            for (layer, idx, w), value in zip(entries, weights):
+                if isinstance(value, torch.Tensor):
+                    src = layer.from_keras_layout(idx, value.detach().cpu().numpy())
+                else:
+                    src = layer.from_keras_layout(idx, np.asarray(value))
+                src = torch.from_numpy(np.ascontiguousarray(src, dtype=np.float32))
+                if tuple(src.shape) != tuple(w.shape):
+                    raise ValueError("weight %s expects shape %s, got %s" % (layer.name, tuple(w.shape), tuple(src.shape)))
+                w.copy_(src)
+        self._push_to_engine()
+
+    def to(self, device):
+        """Move the model (weights and optimizer slots) to ``device``; returns self."""
+        device = torch.device(device)
+        if device == self._device:
+            return self
+        self._sync_from_engine()
+        for layer in self.layers:
+            moved = []
+            for n, w, t in layer._weights:
+                nw = w.detach().to(device).requires_grad_(w.requires_grad)
+                moved.append((n, nw, t))
+                for attr in ('kernel', 'bias', 'gamma', 'beta', 'moving_mean', 'moving_variance'):
+                    if getattr(layer, attr, None) is w:
+                        setattr(layer, attr, nw)
+            layer._weights = moved
+        if self.optimizer is not None:
+            self.optimizer._slots = {k: v.to(device) for k, v in self.optimizer._slots.items()}
+        self._device = device
+        self._engine = None
+        return self
+
+    @property
+    def device(self):
+        return self._device
+
+    # ---------------------------------------------------------- native engine
+    def _native_engine(self, batch_size=None):
+        """The sm_100a engine for this model, or None when the model/device does not qualify."""
+        if self._device.type != 'cuda' or not self._compiled:
+            return None
+        from ..ops import engine as _engine_mod
+        key = (self._device, id(self.optimizer))
+        if self._engine is None or self._engine_key != key:
+            self._engine = _engine_mod.maybe_create(self)
+            self._engine_key = key
+        return self._engine
+
+    def _sync_from_engine(self):
+        if self._engine is not None:
+            self._engine.export_weights()
+
+    def _push_to_engine(self):
+        if self._engine is not None:
+            self._engine.import_weights()
+
+    # ---------------------------------------------------------------- config
+    def get_config(self):
+        names = {}
+        layer_cfgs = []
+        for layer in self.layers:
+            inbound = []
+            for node in layer.inbound:
+                if node:
+                    inbound.append([[s.layer.name, s.node_index, s.tensor_index, {}] for s in node])
+            layer_cfgs.append({'class_name': type(layer).__name__, 'config': layer.get_config(), 'name': layer.name,
+                               'inbound_nodes': inbound})
+            names[layer.name] = layer
+        return {'name': self.name, 'layers': layer_cfgs,
+                'input_layers': [[t.layer.name, t.node_index, t.tensor_index] for t in self._inputs],
+                'output_layers': [[t.layer.name, t.node_index, t.tensor_index] for t in self._outputs]}
+
+    def to_json(self, **kwargs):
+        return json.dumps({'class_name': self._json_class_name, 'config': self.get_config(),
+                           'keras_version': KERAS_VERSION, 'backend': BACKEND}, **kwargs)
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        created = {}
+        tensors = {}
+        pending = list(config['layers'])
+        for spec in pending:
+            created[spec['name']] = L.deserialize_layer(spec, custom_objects)
+        progress = True
+        done = set()
+        while len(done) < len(pending) and progress:
+            progress = False
+            for spec in pending:
+                name = spec['name']
+                if name in done:
+                    continue
+                layer = created[name]
+                if isinstance(layer, L.InputLayer):
+                    t = L.KerasTensor(layer.batch_input_shape, layer)
+                    layer.inbound.append([])
+                    layer.outputs.append(t)
+                    tensors[(name, 0)] = t
+                    done.add(name)
+                    progress = True
+                    continue
+                ready = all((src[0], src[1]) in tensors for node in spec['inbound_nodes'] for src in node)
+                if not ready:
+                    continue
+                for node_idx, node in enumerate(spec['inbound_nodes']):
+                    ins = [tensors[(src[0], src[1])] for src in node]
+                    tensors[(name, node_idx)] = layer(ins if len(ins) > 1 else ins[0])
+                done.add(name)
+                progress = True
+        if len(done) < len(pending):
+            raise ValueError("model config has unresolved inbound nodes")
+        inputs = [tensors[(n, i)] for n, i, _ in config['input_layers']]
+        outputs = [tensors[(n, i)] for n, i, _ in config['output_layers']]
+        model = cls(inputs=inputs if len(inputs) > 1 else inputs[0],
+                    outputs=outputs if len(outputs) > 1 else outputs[0], name=config.get('name'))
+        model.custom_objects = dict(custom_objects or {})
+        return model
+
+    # --------------------------------------------------------------- compile
+    def compile(self, optimizer='rmsprop', loss=None, metrics=None, **kwargs):
+        self.optimizer = _optimizers.get(optimizer)
+        self.loss = loss
+        self._loss_name = _losses.canonical_name(loss)
+        self._loss_fn = _losses.get(loss, self.custom_objects)
+        metrics = list(metrics) if metrics else []
+        self.compiled_metrics = _CompiledMetrics(list(metrics) if metrics else None)
+        out_shape = self.output_shape
+        out_dim = out_shape[-1] if out_shape and not isinstance(out_shape[0], (tuple, list)) else None
+        self._metric_fns = [_metrics.resolve(m, self._loss_name, out_dim, self.custom_objects) for m in metrics]
+        self.metrics_names = ['loss'] + [n for n, _ in self._metric_fns]
+        self._compiled = True
+        self._engine = None
+
+    def _require_compiled(self):
+        if not self._compiled:
+            raise RuntimeError("You must compile your model before training/testing. Use `model.compile(optimizer, loss)`.")
+
+    # ------------------------------------------------------------ train step
+    def _fused_softmax_ce(self):
+        """True when the model ends in softmax and the loss is categorical CE: the gradient is then
+        taken through the fused log-softmax form (the same simplification Keras applies)."""
+        last = self.layers[-1] if self.layers else None
+        ends_softmax = (isinstance(last, (L.Dense, L.Activation)) and last.activation_name == 'softmax') or \
+            isinstance(last, L.Softmax)
+        return ends_softmax and self._loss_name == 'categorical_crossentropy'
+
+    def _torch_train_step(self, xb, yb):
+        params = self.trainable_weights
+        for p in params:
+            p.grad = None
+        out = self(xb, training=True)
+        per_sample = self._loss_fn(yb, out)
+        loss = per_sample.mean()
+        loss.backward()
+        grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in params]
+        self.optimizer.apply_gradients(params, grads)
+        with torch.no_grad():
+            stats = [float(loss.detach())]
+            for _, fn in self._metric_fns:
+                stats.append(float(fn(yb, out.detach()).mean()))
+        return stats
+
+    def train_on_batch(self, x, y, **kwargs):
+        self._require_compiled()
+        eng = self._native_engine()
+        if eng is not None:
+            stats = eng.train_on_batch(x, y)
+        else:
+            xb = _as_tensor(x, self._device)
+            yb = _as_tensor(y, self._device)
+            if xb.dim() == 1:
+                xb = xb.unsqueeze(-1)
+            stats = self._torch_train_step(xb, yb)
+        return stats if len(stats) > 1 else stats[0]
+
+    def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=0, callbacks=None, validation_split=0.0,
+            validation_data=None, shuffle=True, initial_epoch=0, **kwargs):
+        self._require_compiled()
+        if 'nb_epoch' in kwargs:
+            epochs = kwargs.pop('nb_epoch')
+        batch_size = int(batch_size or 32)
+        x = np.asarray(x) if not isinstance(x, torch.Tensor) else x
+        y = np.asarray(y) if not isinstance(y, torch.Tensor) else y
+        n_total = len(x)
+        x_val = y_val = None
+        if validation_data is not None:
+            x_val, y_val = validation_data[0], validation_data[1]
+        elif validation_split and 0.0 < validation_split < 1.0:
+            split_at = int(n_total * (1.0 - validation_split))
+            x, x_val = x[:split_at], x[split_at:]
+            y, y_val = y[:split_at], y[split_at:]
+        history = History()
+        eng = self._native_engine()
+        if eng is not None:
+            eng.fit(x, y, batch_size, epochs, shuffle, history, x_val, y_val, verbose, initial_epoch)
+            return history
+        xt = _as_tensor(x, self._device)
+        yt = _as_tensor(y, self._device)
+        if xt.dim() == 1:
+            xt = xt.unsqueeze(-1)
+        n = xt.shape[0]
+        names = self.metrics_names
+        for epoch in range(initial_epoch, epochs):
+            order = torch.randperm(n, device=self._device) if shuffle else torch.arange(n, device=self._device)
+            sums = [0.0] * len(names)
+            for start in range(0, n, batch_size):
+                idx = order[start:start + batch_size]
+                stats = self._torch_train_step(xt[idx], yt[idx])
+                for i, s in enumerate(stats):
+                    sums[i] += s * len(idx)
+            logs = {k: (s / n if n else 0.0) for k, s in zip(names, sums)}
+            if x_val is not None and len(x_val):
+                val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
+                val = val if isinstance(val, list) else [val]
+                logs.update({'val_' + k: v for k, v in zip(names, val)})
+            history._append(epoch, logs)
+            if verbose:
+                print("Epoch %d/%d - " % (epoch + 1, epochs) + " - ".join("%s: %.4f" % kv for kv in logs.items()))
+            for cb in callbacks or []:
+                if hasattr(cb, 'on_epoch_end'):
+                    cb.on_epoch_end(epoch, logs)
+            if self.stop_training:
+                break
+        return history
+
+    # ------------------------------------------------------------- inference
+    @torch.no_grad()
+    def predict(self, x, batch_size=None, verbose=0, **kwargs):
+        batch_size = int(batch_size or 32)
+        eng = self._native_engine() if self._compiled else None
+        if eng is None and self._device.type == 'cuda':
+            from ..ops import engine as _engine_mod
+            eng = _engine_mod.maybe_create_inference(self)
+        if eng is not None:
+            return eng.predict(x)
+        xt = _as_tensor(x, self._device)
+        if xt.dim() == 1:
+            xt = xt.unsqueeze(-1)
+        outs = []
+        # Fixed-size row blocks (the last one zero-padded): every GEMM the library sees has the same
+        # shape, so a row's result does not depend on how the caller batched the rows - the
+        # "batched == unbatched, bit for bit" contract of tests/test_ml_model.py:354.
+        block = _PREDICT_BLOCK
+        n = xt.shape[0]
+        for start in range(0, n, block):
+            xb = xt[start:start + block]
+            if xb.shape[0] < block:
+                pad = torch.zeros((block - xb.shape[0],) + tuple(xb.shape[1:]), dtype=xb.dtype, device=xb.device)
+                outs.append(self(torch.cat([xb, pad], dim=0), training=False)[:xb.shape[0]])
+            else:
+                outs.append(self(xb, training=False))
+        if not outs:
+            return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
+        return torch.cat(outs, dim=0).cpu().numpy()
+
+    @torch.no_grad()
+    def evaluate(self, x=None, y=None, batch_size=None, verbose=0, **kwargs):
+        self._require_compiled()
+        batch_size = int(batch_size or 32)
+        eng = self._native_engine()
+        if eng is not None:
+            stats = eng.evaluate(x, y)
+            return stats if len(stats) > 1 else stats[0]
+        xt = _as_tensor(x, self._device)
+        yt = _as_tensor(y, self._device)
+        if xt.dim() == 1:
+            xt = xt.unsqueeze(-1)
+        n = xt.shape[0]
+        sums = [0.0] * len(self.metrics_names)
+        step = max(batch_size, 8192)
+        for start in range(0, n, step):
+            xb, yb = xt[start:start + step], yt[start:start + step]
+            out = self(xb, training=False)
+            vals = [self._loss_fn(yb, out)] + [fn(yb, out) for _, fn in self._metric_fns]
+            for i, v in enumerate(vals):
+                sums[i] += float(v.double().sum())
+        stats = [s / n if n else 0.0 for s in sums]
+        return stats if len(stats) > 1 else stats[0]
+
+    # ----------------------------------------------------------------- io
+    def save(self, filepath, overwrite=True, include_optimizer=True):
+        from ..io.keras_h5 import save_model
+        save_model(self, filepath, overwrite=overwrite, include_optimizer=include_optimizer)
+
+    def save_weights(self, filepath):
+        from ..io.keras_h5 import save_model
+        save_model(self, filepath, overwrite=True, include_optimizer=False)
+
+    def summary(self, print_fn=print):
+        print_fn('Model: "%s"' % self.name)
+        for layer in self.layers:
+            print_fn("  %-28s %-20s params=%d" % (layer.name, type(layer).__name__,
+                                                  sum(w.numel() for w in layer.weights)))
+        print_fn("Total params: %d" % self.count_params())
+
+
+class Sequential(Model):
+    """Linear stack of layers (``tests/conftest.py:8-28`` builds the reference's fixtures this way)."""
+
+    _json_class_name = 'Sequential'
+
+    def __init__(self, layers=None, name=None):
+        super().__init__(name=name or L.unique_name('sequential'))
+        self._stack = []
+        self._tail = None
+        self._inputs = []
+        self._outputs = []
+        self._node_order = []
+        for layer in layers or []:
+            self.add(layer)
+
+    def add(self, layer):
+        if not self._stack:
+            if isinstance(layer, L.InputLayer):
+                t = L.KerasTensor(layer.batch_input_shape, layer)
+                layer.inbound.append([])
+                layer.outputs.append(t)
+                self._stack.append(layer)
+                self._tail = t
+                self._init_graph([t], [t])
+                return
+            if layer.batch_input_shape is None:
+                raise ValueError("The first layer of a Sequential model needs input_shape / input_dim")
+            inp = L.InputLayer(batch_input_shape=layer.batch_input_shape, name=layer.name + '_input', dtype=layer.dtype)
+            t = L.KerasTensor(inp.batch_input_shape, inp)
+            inp.inbound.append([])
+            inp.outputs.append(t)
+            self._stack.append(inp)
+            self._tail = t
+        self._tail = layer(self._tail)
+        self._stack.append(layer)
+        self._init_graph([self._stack[0].outputs[0]], [self._tail])
+
+    @property
+    def layers_without_input(self):
+        return [l for l in self._stack if not isinstance(l, L.InputLayer)]
+
+    def get_config(self):
+        return {'name': self.name,
+                'layers': [{'class_name': type(l).__name__, 'config': l.get_config()} for l in self._stack]}
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        model = cls(name=config.get('name'))
+        model.custom_objects = dict(custom_objects or {})
+        specs = config['layers'] if isinstance(config, dict) else config
+        for spec in specs:
+            model.add(L.deserialize_layer(spec, custom_objects))
+        return model
+
+
+def model_from_json(json_string, custom_objects=None):
+    """``keras.models.model_from_json``: rebuild an (uncompiled, freshly initialised) model."""
+    spec = json.loads(json_string) if isinstance(json_string, (str, bytes)) else json_string
+    return model_from_config(spec, custom_objects)
+
+
+def model_from_config(spec, custom_objects=None):
+    cls_name = spec.get('class_name')
+    if cls_name == 'Sequential':
+        return Sequential.from_config(spec['config'], custom_objects)
+    if cls_name in ('Functional', 'Model'):
+        return Model.from_config(spec['config'], custom_objects)
+    raise ValueError("Unknown model class %r" % (cls_name,))
+
+
+def load_model(filepath, custom_objects=None, compile=True):
+    from ..io.keras_h5 import load_model as _load
+    return _load(filepath, custom_objects=custom_objects, compile=compile)
+
+
+def to_categorical(y, num_classes=None, dtype='float32'):
+    """``keras.utils.to_categorical``."""
+    y = np.asarray(y, dtype='int64').ravel()
+    if num_classes is None:
+        num_classes = int(y.max()) + 1 if y.size else 0
+    out = np.zeros((y.shape[0], num_classes), dtype=dtype)
+    out[np.arange(y.shape[0]), y] = 1
+    return out

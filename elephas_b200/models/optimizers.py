@@ -276,4 +276,3 @@ def get(identifier) -> Optimizer:
             raise ValueError("Unknown optimizer: %r" % (identifier,))
         return cls()
     raise ValueError("Could not interpret optimizer identifier: %r" % (identifier,))
-EOF

@@ -1,0 +1,105 @@
+"""Device-resident parameter server (``parameter_server_mode='nvlink'``).
+
+The reference's parameter server is a Flask process or a socket thread that receives pickled NumPy
+lists (``elephas/parameter/server.py:42-233``). Here the master weights are one flat fp32 buffer in
+the memory of the owning B200; a *pull* is a vectorised copy kernel out of that buffer (a peer load
+over NVLink when the caller is another GPU) and a *push* applies ``master -= delta`` with
+``red.global.add.f32`` straight into it - fused with the worker-side delta computation - so no
+weight ever crosses the host. ``mode='asynchronous'`` keeps the reference's reader/writer exclusion
+(``utils/rwlock.py``) with a device-side sequence lock: writers take a ticket and bump the sequence
+word before and after the burst, readers retry while it is odd or changed; ``mode='hogwild'`` skips
+both, exactly like ``server.py:109,120``.
+
+A store is addressed by the server's ``port`` number (it plays the role of the URL). Ranks other
+than the owner map the buffer through a CUDA IPC handle (``open_remote``). On machines without a
+GPU the same class runs on CPU tensors with a host ``RWLock``, which is what the CPU test-suite
+exercises.
+"""
+import threading
+
+import numpy as np
+import torch
+
+from ..utils.rwlock import RWLock
+
+_stores = {}
+_stores_guard = threading.Lock()
+
+
+class DeviceStore:
+    def __init__(self, port, layout_model, arrays, mode, device):
+        from .flat import FlatLayout
+        self.port, self.mode, self.device = port, mode, torch.device(device)
+        self.layout = FlatLayout(layout_model)
+        self.flat = self.layout.pack_arrays(arrays, device=self.device)
+        # ctrl[0]: sequence word (odd while a writer is inside), ctrl[1]: next ticket, ctrl[2]: now serving
+        self.ctrl = torch.zeros(8, dtype=torch.int32, device=self.device)
+        self._host_lock = RWLock()
+        self.pushes = 0
+
+    @property
+    def locked(self):
+        return self.mode == 'asynchronous'
+
+    # ---------------------------------------------------------- flat, on device
+    def pull_into(self, dst_flat, dst_bf16=None, stream=None):
+        """``dst_flat <- master`` (and optionally the bf16 compute copy in the same pass)."""
+        if self.flat.is_cuda:
+            from ..ops import native
+            native.ps_pull(self.flat, self.ctrl, dst_flat, dst_bf16, locked=self.locked)
+            return
+        if self.locked:
+            with self._host_lock.reading():
+                dst_flat.copy_(self.flat)
+        else:
+            dst_flat.copy_(self.flat)
+        if dst_bf16 is not None:
+            dst_bf16.copy_(dst_flat)
+
+    def push_delta(self, delta_flat=None, before=None, after=None):
+        """``master -= delta`` where ``delta`` is given directly or as ``before - after`` (fused)."""
+        self.pushes += 1
+        if self.flat.is_cuda:
+            from ..ops import native
+            native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked)
+            return
+        delta = delta_flat if delta_flat is not None else (before - after)
+        if self.locked:
+            with self._host_lock.writing():
+                self.flat.sub_(delta)
+        else:
+            self.flat.sub_(delta)
+
+    # ------------------------------------------------- list-of-arrays contract
+    def pull_arrays(self):
+        tmp = torch.empty_like(self.flat)
+        self.pull_into(tmp)
+        if tmp.is_cuda:
+            torch.cuda.current_stream(tmp.device).synchronize()
+        return self.layout.unpack_arrays(tmp)
+
+    def push_arrays(self, delta):
+        self.push_delta(self.layout.pack_arrays(delta, device=self.device))
+
+
+def create_store(port, arrays, mode, model=None, device=None):
+    from .runtime import default_device
+    if model is None:
+        raise ValueError("create_store needs the model whose weights it holds")
+    store = DeviceStore(port, model, arrays, mode, device or default_device())
+    with _stores_guard:
+        _stores[port] = store
+    return store
+
+
+def get_store(port):
+    with _stores_guard:
+        store = _stores.get(port)
+    if store is None:
+        raise RuntimeError("no device parameter server is running on port %s in this process" % (port,))
+    return store
+
+
+def destroy_store(port):
+    with _stores_guard:
+        _stores.pop(port, None)

@@ -1,0 +1,126 @@
+"""Rank runtime: who am I, which device do I own, how do ranks talk.
+
+The reference distributes work with Spark executors - one Python worker process per RDD partition
+(``elephas/spark_model.py:214,220``) - and moves weights through the driver. Here a *rank* is one
+process that owns one B200 (or, on a machine without GPUs, one CPU process / thread):
+
+* launched by ``torchrun`` (``RANK`` / ``WORLD_SIZE`` / ``LOCAL_RANK`` in the environment): SPMD,
+  every rank executes the user's script, ``SparkModel`` hands partition *i* to rank ``i % world``;
+  ``torch.distributed`` (NCCL on GPUs, gloo on CPUs) is used for rendezvous, object exchange and as
+  the collective fallback, the hot collectives are the P2P kernels of ``parallel/collectives.py``;
+* plain ``python script.py``: one rank, partitions run as worker threads on the one device.
+"""
+import datetime
+import os
+import threading
+
+import torch
+
+_lock = threading.Lock()
+_runtime = None
+
+
+def default_device():
+    """``ELEPHAS_B200_DEVICE`` wins; otherwise ``cuda:LOCAL_RANK`` when CUDA is present, else the CPU."""
+    forced = os.environ.get('ELEPHAS_B200_DEVICE')
+    if forced:
+        return torch.device(forced)
+    if torch.cuda.is_available():
+        return torch.device('cuda', int(os.environ.get('LOCAL_RANK', 0)) % torch.cuda.device_count())
+    return torch.device('cpu')
+
+
+class Runtime:
+    def __init__(self):
+        self.device = default_device()
+        self.world_size = int(os.environ.get('WORLD_SIZE', 1))
+        self.rank = int(os.environ.get('RANK', 0))
+        self.local_rank = int(os.environ.get('LOCAL_RANK', 0))
+        self._group = None
+        if self.device.type == 'cuda':
+            torch.cuda.set_device(self.device)
+        if self.world_size > 1:
+            self._init_process_group()
+
+    def _init_process_group(self):
+        import torch.distributed as dist
+        if not dist.is_initialized():
+            backend = 'nccl' if self.device.type == 'cuda' else 'gloo'
+            os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+            os.environ.setdefault('MASTER_PORT', '29500')
+            kwargs = {}
+            if backend == 'nccl':
+                kwargs['device_id'] = self.device
+            dist.init_process_group(backend=backend, rank=self.rank, world_size=self.world_size,
+                                    timeout=datetime.timedelta(seconds=600), **kwargs)
+        self._dist = dist
+
+    @property
+    def distributed(self):
+        return self.world_size > 1
+
+    @property
+    def is_driver(self):
+        return self.rank == 0
+
+    # ------------------------------------------------------------ plumbing
+    def barrier(self):
+        if self.distributed:
+            if self.device.type == 'cuda':
+                self._dist.barrier(device_ids=[self.device.index])
+            else:
+                self._dist.barrier()
+
+    def all_gather_object(self, obj):
+        if not self.distributed:
+            return [obj]
+        out = [None] * self.world_size
+        self._dist.all_gather_object(out, obj)
+        return out
+
+    def broadcast_object(self, obj, src=0):
+        if not self.distributed:
+            return obj
+        box = [obj]
+        self._dist.broadcast_object_list(box, src=src)
+        return box[0]
+
+    def all_reduce_sum_(self, tensor):
+        """In-place sum over ranks (library fallback; the fused kernels live in ``collectives.py``)."""
+        if self.distributed:
+            self._dist.all_reduce(tensor, op=self._dist.ReduceOp.SUM)
+        return tensor
+
+    def all_reduce_max_(self, tensor):
+        if self.distributed:
+            self._dist.all_reduce(tensor, op=self._dist.ReduceOp.MAX)
+        return tensor
+
+    def broadcast_(self, tensor, src=0):
+        if self.distributed:
+            self._dist.broadcast(tensor, src=src)
+        return tensor
+
+    def shutdown(self):
+        if self.distributed and self._dist.is_initialized():
+            self._dist.destroy_process_group()
+
+
+def get_runtime() -> Runtime:
+    global _runtime
+    with _lock:
+        if _runtime is None:
+            _runtime = Runtime()
+        return _runtime
+
+
+def reset_runtime():
+    """Drop the cached runtime (tests that change WORLD_SIZE / device between cases)."""
+    global _runtime
+    with _lock:
+        if _runtime is not None:
+            try:
+                _runtime.shutdown()
+            except Exception:
+                pass
+        _runtime = None

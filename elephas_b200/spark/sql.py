@@ -1,0 +1,417 @@
+"""Minimal ``pyspark.sql`` stand-in: ``Row``, ``StructType`` & friends, ``DataFrame``, ``SparkSession``.
+
+Only the surface Elephas' Spark ML stages and adapters use (``elephas/ml/adapter.py:11-47``,
+``elephas/ml_model.py:191-256``): ``createDataFrame`` from an RDD of rows / LabeledPoints,
+``df.rdd``, ``df.schema``, ``select`` / ``withColumnRenamed`` / ``withColumn``, temp views with the
+one ``SELECT a AS x, b AS y FROM view`` statement shape Elephas issues, ``show`` / ``take`` /
+``collect`` / ``count`` / ``first``.
+"""
+import copy
+import re
+
+import numpy as np
+
+from .context import RDD, SparkContext
+from .linalg import Vector
+from .regression import LabeledPoint
+
+
+# --------------------------------------------------------------------- types
+class DataType:
+    def __eq__(self, other):
+        return type(self) is type(other) and self.__dict__ == other.__dict__
+
+    def __hash__(self):
+        return hash(type(self).__name__)
+
+    def __repr__(self):
+        return type(self).__name__ + "()"
+
+    def simpleString(self):
+        return type(self).__name__.replace('Type', '').lower()
+
+
+class DoubleType(DataType):
+    pass
+
+
+class FloatType(DataType):
+    pass
+
+
+class IntegerType(DataType):
+    pass
+
+
+class LongType(DataType):
+    pass
+
+
+class StringType(DataType):
+    pass
+
+
+class BooleanType(DataType):
+    pass
+
+
+class VectorUDT(DataType):
+    pass
+
+
+class ArrayType(DataType):
+    def __init__(self, elementType, containsNull=True):
+        self.elementType = elementType
+        self.containsNull = containsNull
+
+    def __repr__(self):
+        return "ArrayType(%r)" % (self.elementType,)
+
+
+class StructField:
+    def __init__(self, name, dataType, nullable=True, metadata=None):
+        self.name, self.dataType, self.nullable, self.metadata = name, dataType, nullable, metadata or {}
+
+    def __repr__(self):
+        return "StructField(%r, %r, %r)" % (self.name, self.dataType, self.nullable)
+
+
+class StructType(DataType):
+    def __init__(self, fields=None):
+        self.fields = list(fields or [])
+
+    def add(self, field, data_type=None, nullable=True):
+        if not isinstance(field, StructField):
+            field = StructField(field, data_type, nullable)
+        self.fields.append(field)
+        return self
+
+    @property
+    def names(self):
+        return [f.name for f in self.fields]
+
+    def fieldNames(self):
+        return self.names
+
+    def __iter__(self):
+        return iter(self.fields)
+
+    def __len__(self):
+        return len(self.fields)
+
+    def __getitem__(self, key):
+        if isinstance(key, str):
+            return next(f for f in self.fields if f.name == key)
+        return self.fields[key]
+
+    def __repr__(self):
+        return "StructType(%r)" % (self.fields,)
+
+
+def _infer_type(value):
+    if isinstance(value, bool):
+        return BooleanType()
+    if isinstance(value, (int, np.integer)):
+        return LongType()
+    if isinstance(value, (float, np.floating)):
+        return DoubleType()
+    if isinstance(value, str):
+        return StringType()
+    if isinstance(value, Vector):
+        return VectorUDT()
+    if isinstance(value, (list, tuple, np.ndarray)):
+        return ArrayType(DoubleType())
+    return StringType()
+
+
+# ----------------------------------------------------------------------- Row
+class Row(tuple):
+    """Tuple with named fields: ``row.label``, ``row['label']``, ``row[0]``; ``row + tuple`` is a tuple."""
+
+    def __new__(cls, *args, **kwargs):
+        if args and kwargs:
+            raise ValueError("Can not use both args and kwargs to create Row")
+        if kwargs:
+            row = tuple.__new__(cls, list(kwargs.values()))
+            row.__fields__ = list(kwargs.keys())
+            return row
+        return tuple.__new__(cls, args)
+
+    @classmethod
+    def _make(cls, fields, values):
+        row = tuple.__new__(cls, values)
+        row.__fields__ = list(fields)
+        return row
+
+    def asDict(self):
+        return dict(zip(self.__fields__, self))
+
+    def __getitem__(self, item):
+        if isinstance(item, str):
+            try:
+                return tuple.__getitem__(self, self.__fields__.index(item))
+            except ValueError:
+                raise KeyError(item)
+        return tuple.__getitem__(self, item)
+
+    def __getattr__(self, item):
+        if item.startswith('__'):
+            raise AttributeError(item)
+        try:
+            return tuple.__getitem__(self, self.__fields__.index(item))
+        except (ValueError, AttributeError):
+            raise AttributeError(item)
+
+    def __repr__(self):
+        if hasattr(self, '__fields__'):
+            return "Row(%s)" % ", ".join("%s=%r" % kv for kv in zip(self.__fields__, self))
+        return "<Row(%s)>" % ", ".join(repr(v) for v in self)
+
+
+class Column:
+    """A column reference with an optional alias, cast and row-wise function."""
+
+    def __init__(self, name, fn=None, alias=None):
+        self.name, self.fn, self._alias = name, fn, alias
+
+    def alias(self, name):
+        return Column(self.name, self.fn, name)
+
+    def astype(self, data_type):
+        caster = float if isinstance(data_type, (DoubleType, FloatType)) else (
+            int if isinstance(data_type, (IntegerType, LongType)) else (lambda v: v))
+        prev = self.fn
+        return Column(self.name, (lambda v: caster(prev(v))) if prev else caster, self._alias)
+
+    cast = astype
+
+    @property
+    def out_name(self):
+        return self._alias or self.name
+
+
+class functions:
+    """Tiny ``pyspark.sql.functions``: ``col`` and ``array_argmax`` (the reference's tests spell the
+    latter ``expr('array_position(c, array_max(c)) - 1')``, ``tests/test_ml_model.py:20-26``)."""
+
+    @staticmethod
+    def col(name):
+        return Column(name)
+
+    @staticmethod
+    def array_argmax(name):
+        return Column(name, fn=lambda v: int(np.argmax(np.asarray(v))))
+
+
+# ----------------------------------------------------------------- DataFrame
+class DataFrame:
+    def __init__(self, rdd, schema, session):
+        self._rdd = rdd
+        self.schema = schema
+        self.sparkSession = session
+        self.sql_ctx = session
+
+    @property
+    def rdd(self):
+        return self._rdd
+
+    @property
+    def columns(self):
+        return self.schema.names
+
+    def count(self):
+        return self._rdd.count()
+
+    def collect(self):
+        return self._rdd.collect()
+
+    def take(self, n):
+        return self._rdd.take(n)
+
+    def first(self):
+        return self._rdd.first()
+
+    def head(self, n=None):
+        return self.first() if n is None else self.take(n)
+
+    def _col_index(self, name):
+        try:
+            return self.columns.index(name)
+        except ValueError:
+            raise ValueError("cannot resolve column %r among %s" % (name, self.columns))
+
+    def select(self, *cols):
+        if len(cols) == 1 and isinstance(cols[0], (list, tuple)):
+            cols = tuple(cols[0])
+        cols = [Column(c) if isinstance(c, str) else c for c in cols]
+        idx = [self._col_index(c.name) for c in cols]
+        names = [c.out_name for c in cols]
+        fns = [c.fn for c in cols]
+        fields = []
+        first = self._rdd.take(1)
+        for c, i, fn in zip(cols, idx, fns):
+            base = self.schema.fields[i]
+            dtype = base.dataType if fn is None else _infer_type(fn(first[0][i])) if first else base.dataType
+            fields.append(StructField(c.out_name, dtype, base.nullable))
+
+        def project(row):
+            return Row._make(names, [row[i] if fn is None else fn(row[i]) for i, fn in zip(idx, fns)])
+
+        return DataFrame(self._rdd.map(project), StructType(fields), self.sparkSession)
+
+    def withColumnRenamed(self, existing, new):
+        names = [new if n == existing else n for n in self.columns]
+        fields = [StructField(n, f.dataType, f.nullable) for n, f in zip(names, self.schema.fields)]
+        return DataFrame(self._rdd.map(lambda r: Row._make(names, list(r))), StructType(fields), self.sparkSession)
+
+    def withColumn(self, name, col):
+        if not isinstance(col, Column):
+            raise TypeError("withColumn expects a Column")
+        src = self._col_index(col.name)
+        fn = col.fn or (lambda v: v)
+        names = list(self.columns)
+        replace = names.index(name) if name in names else None
+        if replace is None:
+            names.append(name)
+        first = self._rdd.take(1)
+        dtype = _infer_type(fn(first[0][src])) if first else DoubleType()
+        fields = list(self.schema.fields)
+        if replace is None:
+            fields.append(StructField(name, dtype))
+        else:
+            fields[replace] = StructField(name, dtype)
+
+        def extend(row):
+            vals = list(row)
+            if replace is None:
+                vals.append(fn(row[src]))
+            else:
+                vals[replace] = fn(row[src])
+            return Row._make(names, vals)
+
+        return DataFrame(self._rdd.map(extend), StructType(fields), self.sparkSession)
+
+    def drop(self, *cols):
+        keep = [c for c in self.columns if c not in cols]
+        return self.select(*keep)
+
+    def distinct(self):
+        seen, rows = set(), []
+        for r in self.collect():
+            key = tuple(repr(v) for v in r)
+            if key not in seen:
+                seen.add(key)
+                rows.append(r)
+        return DataFrame(RDD([rows], self._rdd.context), self.schema, self.sparkSession)
+
+    def repartition(self, n):
+        return DataFrame(self._rdd.repartition(n), self.schema, self.sparkSession)
+
+    def cache(self):
+        return self
+
+    def createOrReplaceTempView(self, name):
+        self.sparkSession._views[name] = self
+
+    registerTempTable = createOrReplaceTempView
+
+    def show(self, n=20, truncate=True):
+        rows = self.take(n)
+        print(" | ".join(self.columns))
+        for r in rows:
+            cells = []
+            for v in r:
+                s = repr(v.toArray().tolist()) if isinstance(v, Vector) else repr(v)
+                cells.append(s[:40] + '...' if truncate and len(s) > 43 else s)
+            print(" | ".join(cells))
+        if self.count() > n:
+            print("only showing top %d rows" % n)
+
+    def toPandas(self):
+        import pandas as pd
+        return pd.DataFrame([list(r) for r in self.collect()], columns=self.columns)
+
+    def __repr__(self):
+        return "DataFrame[%s]" % ", ".join("%s: %s" % (f.name, f.dataType.simpleString()) for f in self.schema.fields)
+
+
+# -------------------------------------------------------------- SparkSession
+_SELECT_RE = re.compile(r'^\s*select\s+(.*?)\s+from\s+(\w+)\s*$', re.IGNORECASE | re.DOTALL)
+
+
+class SparkSession:
+    _active = None
+
+    class Builder:
+        def __init__(self):
+            self._master = None
+            self._app = None
+
+        def appName(self, name):
+            self._app = name
+            return self
+
+        def master(self, master):
+            self._master = master
+            return self
+
+        def config(self, *args, **kwargs):
+            return self
+
+        def getOrCreate(self):
+            if SparkSession._active is None:
+                if SparkContext._active is None:
+                    SparkContext(master=self._master, appName=self._app)
+                SparkSession._active = SparkSession(SparkContext._active)
+            return SparkSession._active
+
+    class _BuilderDescriptor:
+        def __get__(self, obj, owner):
+            return SparkSession.Builder()
+
+    builder = _BuilderDescriptor()
+
+    def __init__(self, sparkContext=None):
+        self.sparkContext = sparkContext or SparkContext.getOrCreate()
+        self._views = {}
+        SparkSession._active = self
+
+    def createDataFrame(self, data, schema=None):
+        rdd = data if isinstance(data, RDD) else self.sparkContext.parallelize(list(data))
+        first = rdd.take(1)
+        if first and isinstance(first[0], LabeledPoint):
+            names = ['features', 'label']
+            rdd = rdd.map(lambda lp: Row._make(names, [lp.features, lp.label]))
+            schema = StructType([StructField('features', VectorUDT()), StructField('label', DoubleType())])
+            return DataFrame(rdd, schema, self)
+        if isinstance(schema, StructType):
+            names = schema.names
+            struct = copy.deepcopy(schema)
+        else:
+            if schema is None:
+                if first and hasattr(first[0], '__fields__'):
+                    names = list(first[0].__fields__)
+                else:
+                    names = ['_%d' % (i + 1) for i in range(len(first[0]))] if first else []
+            else:
+                names = list(schema)
+            struct = StructType([StructField(n, _infer_type(first[0][i]) if first else StringType())
+                                 for i, n in enumerate(names)])
+        rdd = rdd.map(lambda r: Row._make(names, list(r)))
+        return DataFrame(rdd, struct, self)
+
+    def sql(self, query):
+        m = _SELECT_RE.match(query)
+        if not m:
+            raise NotImplementedError("the local SparkSession only understands 'SELECT cols FROM view'")
+        df = self._views[m.group(2)]
+        cols = []
+        for part in m.group(1).split(','):
+            tokens = re.split(r'\s+as\s+', part.strip(), flags=re.IGNORECASE)
+            col = Column(tokens[0].strip())
+            cols.append(col.alias(tokens[1].strip()) if len(tokens) > 1 else col)
+        return df.select(*cols)
+
+    def stop(self):
+        SparkSession._active = None
+        self.sparkContext.stop()

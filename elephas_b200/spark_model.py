@@ -1,0 +1,425 @@
+"""``SparkModel`` / ``SparkMLlibModel`` / ``load_spark_model``: the driver-side API.
+
+Reference: ``elephas/spark_model.py:28-389``. Same constructor, same methods
+(``fit`` / ``predict`` / ``evaluate`` / ``save`` / ``get_config`` / ``start_server`` /
+``stop_server`` / ``training_histories`` / ``master_network``), same three modes and two
+frequencies. What is different is *where things run*:
+
+===================  ==========================================  =====================================
+reference mechanism   reference site                              here
+===================  ==========================================  =====================================
+Spark executors       ``rdd.mapPartitions(worker.train)``          one rank per B200 (``torchrun``: partition
+                      (``spark_model.py:214,220``)                 *i* -> rank ``i % world``), worker threads
+                                                                   inside a rank; CPU ranks without GPUs
+broadcast weights     ``sc.broadcast`` (``:207,241,280``)          every rank already holds the model; weights
+                                                                   are device buffers
+collect + average     driver loop, NumPy (``:221-227``)            flat device buffers, one fused P2P all-reduce
+                                                                   + update kernel (``parallel/collectives.py``)
+parameter server      Flask / socket (``parameter/``)              same two (wire compatible) plus ``'nvlink'``:
+                                                                   master weights in peer HBM
+evaluate reduce       ``map`` + ``reduce`` (``:300-304``)           all-reduce of a tiny ``(k+1)`` vector
+===================  ==========================================  =====================================
+
+Synchronous mode honours ``frequency`` (the reference ignores it there and averages once per
+``fit``): ``'epoch'`` averages the replicas after every epoch, ``'batch'`` after every step
+(DDP-like; the configuration BASELINE.json names for the wide MLP). ``sync_rounds='fit'``
+restores average-once exactly; for ``epochs=1`` both are identical.
+"""
+import json
+import subprocess
+import threading
+from copy import deepcopy
+from pathlib import Path
+from typing import List, Optional, Union
+from uuid import uuid4
+
+import numpy as np
+import torch
+
+from .mllib.adapter import from_matrix, from_vector, to_matrix, to_vector
+from .models import optimizers as _optimizers
+from .parallel.runtime import get_runtime
+from .parameter.factory import ClientServerFactory
+from .spark import Matrix, Vector, get_spark_context, materialize_partitions
+from .utils.functional_utils import add_params, divide_by, get_neutral, subtract_params
+from .utils.rdd_utils import lp_to_simple_rdd, to_simple_rdd
+from .utils.serialization import model_to_dict
+from .worker import AsynchronousSparkWorker, SparkWorker, partition_to_arrays
+
+MODES = ('asynchronous', 'synchronous', 'hogwild')
+
+
+def _is_rdd(obj):
+    return hasattr(obj, 'mapPartitions') and hasattr(obj, 'collect')
+
+
+def _rows_to_array(partition):
+    if hasattr(partition, 'x') and not hasattr(partition, 'y'):
+        return np.asarray(partition.x)
+    rows = list(partition)
+    return np.asarray([np.asarray(r) for r in rows]) if rows else np.zeros((0,), dtype=np.float32)
+
+
+class SparkModel:
+    def __init__(self, model, mode='asynchronous', frequency='epoch', parameter_server_mode='http', num_workers=None,
+                 custom_objects=None, batch_size=32, port=4000, *args, **kwargs):
+        """
+        :param model: compiled model (``elephas_b200.models``)
+        :param mode: ``'asynchronous'``, ``'synchronous'`` or ``'hogwild'``
+        :param frequency: ``'epoch'`` or ``'batch'``
+        :param parameter_server_mode: ``'http'``, ``'socket'`` or ``'nvlink'`` (device-resident)
+        :param num_workers: number of data partitions / workers (None: keep the RDD's partitioning,
+            or one partition per rank under ``torchrun``)
+        :param custom_objects: custom activations / layers / losses by name
+        :param batch_size: default batch size when ``fit`` is not given one
+        :param port: parameter server port
+        Extra keyword arguments are stored and round-trip through ``get_config`` / ``save``
+        (``tests/test_model_serialization.py:16-34``); ``sync_rounds`` ('frequency' | 'fit') is one of them.
+        """
+        self._training_histories = []
+        self._master_network = model
+        if not hasattr(model, "loss"):
+            raise Exception("Compile your Keras model before initializing an Elephas model with it")
+        metrics = model.compiled_metrics._metrics
+        self.mode = mode
+        self.frequency = frequency
+        self.num_workers = num_workers
+        self.weights = self._master_network.get_weights()
+        self.pickled_weights = None
+        self.master_optimizer = _optimizers.serialize(model.optimizer)
+        self.master_loss = model.loss
+        self.master_metrics = metrics if metrics is not None else []
+        self.custom_objects = custom_objects if custom_objects is not None else {}
+        self.parameter_server_mode = parameter_server_mode
+        self.batch_size = batch_size
+        self.port = port
+        self.kwargs = kwargs
+        self.serialized_model = model_to_dict(model)
+        self.parameter_server = None
+        self.client = None
+        if self.mode != 'synchronous':
+            factory = ClientServerFactory.get_factory(self.parameter_server_mode)
+            self.parameter_server = factory.create_server(self.serialized_model, self.port, self.mode,
+                                                          custom_objects=self.custom_objects)
+            self.client = factory.create_client(self.port)
+
+    # ------------------------------------------------------------------ config
+    def get_config(self):
+        config = {'parameter_server_mode': self.parameter_server_mode, 'mode': self.mode,
+                  'frequency': self.frequency, 'num_workers': self.num_workers, 'batch_size': self.batch_size}
+        config.update(self.kwargs)
+        return config
+
+    def save(self, file_name: str, overwrite: bool = False, to_hadoop: bool = False):
+        """Save as Keras-style ``.h5`` / ``.keras`` plus the ``distributed_config`` root attribute
+        (``spark_model.py:92-134``). ``to_hadoop`` shells out to ``hadoop fs -moveFromLocal``."""
+        from .io.keras_h5 import save_model
+        assert file_name[-3:] == ".h5" or file_name[-6:] == ".keras", \
+            "File name must end with either '.h5' or '.keras'"
+        if overwrite and not to_hadoop and Path(file_name).exists():
+            Path(file_name).unlink()
+        cluster_file_path = None
+        if to_hadoop:
+            cluster_file_path = deepcopy(file_name)
+            file_name = str(uuid4()) + "-temp-model-file." + file_name.split(".")[-1]
+        elif Path(file_name).exists():
+            raise IOError("%s exists; pass overwrite=True to replace it" % file_name)
+        distributed_config = json.dumps({'class_name': self.__class__.__name__, 'config': self.get_config()})
+        save_model(self._master_network, file_name, overwrite=True,
+                   extra_root_attrs={'distributed_config': distributed_config.encode('utf8')})
+        if to_hadoop:
+            cli = ["hadoop", "fs", "-moveFromLocal"]
+            if overwrite:
+                cli.append("-f")
+            cli += [file_name, cluster_file_path]
+            subprocess.run(cli)
+
+    @property
+    def training_histories(self):
+        return self._training_histories
+
+    @property
+    def master_network(self):
+        return self._master_network
+
+    @master_network.setter
+    def master_network(self, network):
+        self._master_network = network
+
+    def start_server(self):
+        self.parameter_server.start()
+
+    def stop_server(self):
+        self.parameter_server.stop()
+
+    # ----------------------------------------------------------------- predict
+    def predict(self, data) -> List[np.ndarray]:
+        """Distributed inference; results are in the order of the input samples."""
+        if isinstance(data, np.ndarray):
+            data = get_spark_context().parallelize(data)
+        return self._predict(data)
+
+    def evaluate(self, x_test: np.ndarray, y_test: np.ndarray, **kwargs) -> Union[List[float], float]:
+        """Distributed evaluation: sample-weighted mean of loss and metrics over all partitions."""
+        test_rdd = to_simple_rdd(get_spark_context(), x_test, y_test)
+        return self._evaluate(test_rdd, **kwargs)
+
+    # --------------------------------------------------------------------- fit
+    def fit(self, rdd, **kwargs):
+        """Train on an RDD of ``(features, label)`` pairs.
+
+        :param epochs: number of epochs
+        :param batch_size: batch size (defaults to the constructor's ``batch_size``)
+        :param verbose: 0, 1 or 2
+        :param validation_split: fraction of each partition held out for validation
+        """
+        rt = get_runtime()
+        if rt.is_driver:
+            print('>>> Fit model')
+        if self.num_workers:
+            rdd = rdd.repartition(self.num_workers)
+        elif rt.distributed:
+            rdd = rdd.repartition(rt.world_size)
+        if self.mode not in MODES:
+            raise ValueError("Choose from one of the modes: asynchronous, synchronous or hogwild")
+        self._fit(rdd, **kwargs)
+
+    def _worker_args(self, train_config):
+        model_json = self._master_network.to_json()
+        init = self._master_network.get_weights()
+        return model_json, init, dict(train_config), deepcopy(self.master_optimizer), self.master_loss, \
+            self.master_metrics, self.custom_objects
+
+    def _fit(self, rdd, **kwargs):
+        rt = get_runtime()
+        self._master_network.compile(optimizer=_optimizers.get(deepcopy(self.master_optimizer)),
+                                     loss=self.master_loss, metrics=self.master_metrics)
+        train_config = dict(kwargs)
+        train_config.setdefault('batch_size', self.batch_size)  # D8: fall back to the constructor value
+        train_config.setdefault('epochs', 1)
+        partitions = materialize_partitions(rdd)
+        mine = [(i, p) for i, p in enumerate(partitions) if i % rt.world_size == rt.rank]
+
+        if self.mode in ('asynchronous', 'hogwild'):
+            new_parameters = self._fit_parameter_server(rt, partitions, mine, train_config)
+        elif self.mode == 'synchronous':
+            new_parameters = self._fit_synchronous(rt, partitions, mine, train_config)
+        else:
+            raise ValueError("Unsupported mode {}".format(self.mode))
+        self._master_network.set_weights(new_parameters)
+        self.weights = new_parameters
+
+    # -- asynchronous / hogwild -------------------------------------------------
+    def _fit_parameter_server(self, rt, partitions, mine, train_config):
+        if rt.is_driver:
+            self.parameter_server.set_weights(self._master_network.get_weights())
+            self.start_server()
+        rt.barrier()
+        model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
+        if rt.is_driver:
+            print('>>> Initialize workers')
+        workers = [AsynchronousSparkWorker(model_json, init, self.client, cfg, self.frequency, optimizer, loss,
+                                           metrics, custom, device=rt.device) for _ in mine]
+        if rt.is_driver:
+            print('>>> Distribute load')
+        errors = []
+
+        def run(worker, part):
+            try:
+                for _ in worker.train(part):
+                    pass
+            except BaseException as exc:  # surfaced after join; a dead worker must not hang the rest
+                errors.append(exc)
+
+        threads = [threading.Thread(target=run, args=(w, p), name='elephas-worker-%d' % i)
+                   for w, (i, p) in zip(workers, mine)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join()
+        rt.barrier()
+        new_parameters = None
+        if rt.is_driver:
+            new_parameters = self.parameter_server.get_weights()
+            self.stop_server()
+            print('>>> Async training complete.')
+        new_parameters = rt.broadcast_object(new_parameters, src=0)
+        if errors:
+            raise errors[0]
+        # D10 (extension): per-worker histories are kept for frequency='epoch'
+        local = [(i, w.history or None) for w, (i, _) in zip(workers, mine)]
+        gathered = [h for chunk in rt.all_gather_object(local) for h in chunk]
+        self._training_histories.extend(h for _, h in sorted(gathered, key=lambda t: t[0]) if h)
+        return new_parameters
+
+    # -- synchronous ---------------------------------------------------------------
+    def _reduce_deltas(self, rt, local_sum, n_total):
+        """``mean over all workers`` of the deltas: local partial sums are packed into one flat buffer,
+        summed over ranks (fused P2P all-reduce on GPUs), divided by the number of sub-models."""
+        if not rt.distributed:
+            return divide_by(local_sum, n_total)
+        from .parallel.collectives import all_reduce_arrays_sum
+        return divide_by(all_reduce_arrays_sum(rt, local_sum), n_total)
+
+    def _fit_synchronous(self, rt, partitions, mine, train_config):
+        from .parallel import sync_engine
+        n_sub = len(partitions)
+        sync_rounds = self.kwargs.get('sync_rounds', 'frequency')
+        if sync_rounds not in ('frequency', 'fit'):
+            raise ValueError("sync_rounds must be 'frequency' or 'fit', got %r" % (sync_rounds,))
+        if self.frequency not in ('epoch', 'batch'):
+            raise ValueError('frequency parameter can be `epoch` or `batch, got {}'.format(self.frequency))
+        epochs = int(train_config.get('epochs', 1))
+
+        # Fast path: native engines + fused delta all-reduce/update, one worker per rank.
+        fast = sync_engine.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
+        if fast is not None:
+            new_parameters, histories = fast
+            self._training_histories.extend(histories)
+            if rt.is_driver:
+                print('>>> Synchronous training complete.')
+            return new_parameters
+
+        model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
+        workers = [SparkWorker(model_json, init, cfg, optimizer, loss, metrics, custom, device=rt.device).begin(p)
+                   for _, p in mine]
+        current = init
+        zero = get_neutral(init)
+
+        def averaged_round(deltas):
+            local = zero
+            for d in deltas:
+                local = add_params(local, d)
+            return subtract_params(current, self._reduce_deltas(rt, local, n_sub))
+
+        if sync_rounds == 'fit' or (self.frequency == 'epoch' and epochs <= 1):
+            current = averaged_round([w.train_round(current, epochs=epochs)[0] for w in workers])
+        elif self.frequency == 'epoch':
+            for epoch in range(epochs):
+                current = averaged_round([w.train_round(current, epochs=1, initial_epoch=epoch)[0] for w in workers])
+        else:  # 'batch': every worker takes one step from the same weights, then the replicas are averaged
+            steps = max([w.num_batches() for w in workers] + [0])
+            steps = int(rt.all_reduce_max_(torch.tensor([steps], device=rt.device if rt.device.type == 'cuda'
+                                                        else 'cpu'))[0])
+            for _ in range(epochs):
+                for b in range(steps):
+                    current = averaged_round([w.train_batch(current, b) for w in workers])
+        local_hist = [(i, (w.history if w.trainable else None)) for w, (i, _) in zip(workers, mine)]
+        gathered = [h for chunk in rt.all_gather_object(local_hist) for h in chunk]
+        self._training_histories.extend(h for _, h in sorted(gathered, key=lambda t: t[0]))
+        if rt.is_driver:
+            print('>>> Synchronous training complete.')
+        return current
+
+    # ---------------------------------------------------------------- inference
+    def _device_model(self):
+        """The master network placed on this rank's device (weights moved once, reused afterwards)."""
+        rt = get_runtime()
+        model = self._master_network
+        if model.device != rt.device:
+            model.to(rt.device)
+        return model
+
+    def _predict(self, rdd) -> List[np.ndarray]:
+        rt = get_runtime()
+        if self.num_workers and self.num_workers > 1:
+            rdd = rdd.repartition(self.num_workers)
+        elif rt.distributed:
+            rdd = rdd.repartition(rt.world_size)
+        partitions = materialize_partitions(rdd)
+        model = self._device_model()
+        local = []
+        for i, part in enumerate(partitions):
+            if i % rt.world_size != rt.rank:
+                continue
+            x = _rows_to_array(part)
+            if x.shape[0] == 0:
+                local.append((i, None))
+                continue
+            local.append((i, model.predict(x)))
+        gathered = [item for chunk in rt.all_gather_object(local) for item in chunk]
+        predictions = []
+        for _, pred in sorted(gathered, key=lambda t: t[0]):
+            if pred is not None:
+                predictions.extend(list(pred))
+        return predictions
+
+    def _evaluate(self, rdd, **kwargs) -> Union[List[float], float]:
+        rt = get_runtime()
+        if self.num_workers:
+            rdd = rdd.repartition(self.num_workers)
+        elif rt.distributed:
+            rdd = rdd.repartition(rt.world_size)
+        partitions = materialize_partitions(rdd)
+        model = self._device_model()
+        if not getattr(model, '_compiled', False):
+            model.compile(optimizer=_optimizers.get(deepcopy(self.master_optimizer)), loss=self.master_loss,
+                          metrics=self.master_metrics)
+        width = len(model.metrics_names) + 1
+        totals = np.zeros(width, dtype=np.float64)
+        for i, part in enumerate(partitions):
+            if i % rt.world_size != rt.rank:
+                continue
+            x, y = partition_to_arrays(part)
+            if x.shape[0] == 0:
+                continue
+            res = model.evaluate(x, y, **kwargs)
+            res = res if isinstance(res, list) else [res]
+            totals[:-1] += np.asarray(res, dtype=np.float64) * x.shape[0]
+            totals[-1] += x.shape[0]
+        if rt.distributed:
+            t = torch.from_numpy(totals).to(rt.device if rt.device.type == 'cuda' else 'cpu')
+            totals = rt.all_reduce_sum_(t).cpu().numpy()
+        n = totals[-1]
+        avg = [float(v / n) for v in totals[:-1]]
+        return avg if len(avg) > 1 else avg[0]
+
+
+class SparkMLlibModel(SparkModel):
+    """Trains on an RDD of MLlib ``LabeledPoint`` (``spark_model.py:311-352``)."""
+
+    def __init__(self, model, mode='asynchronous', frequency='epoch', parameter_server_mode='http',
+                 num_workers=4, elephas_optimizer=None, custom_objects=None, batch_size=32, port=4000, *args,
+                 **kwargs):
+        SparkModel.__init__(self, model=model, mode=mode, frequency=frequency,
+                            parameter_server_mode=parameter_server_mode, num_workers=num_workers,
+                            custom_objects=custom_objects, batch_size=batch_size, port=port, *args, **kwargs)
+
+    def fit(self, labeled_points, epochs: int = 10, batch_size: int = 32, verbose: int = 0,
+            validation_split: float = 0.1, categorical: bool = False, nb_classes: Optional[int] = None):
+        rdd = lp_to_simple_rdd(labeled_points, categorical, nb_classes)
+        rdd = rdd.repartition(self.num_workers)
+        self._fit(rdd=rdd, epochs=epochs, batch_size=batch_size, verbose=verbose, validation_split=validation_split)
+
+    train = fit  # the reference README spells it ``train`` (README.md:155); the code spells it ``fit``
+
+    def predict(self, mllib_data):
+        """Predict on an MLlib ``Matrix`` or ``Vector`` locally on the driver (``spark_model.py:343-352``)."""
+        if isinstance(mllib_data, Matrix):
+            return to_matrix(self._master_network.predict(from_matrix(mllib_data)))
+        if isinstance(mllib_data, Vector):
+            return to_vector(self._master_network.predict(from_vector(mllib_data)[None, :])[0])
+        raise ValueError('Provide either an MLLib matrix or vector, got {}'.format(type(mllib_data).__name__))
+
+
+def load_spark_model(file_name: str, from_hadoop: bool = False) -> Union[SparkModel, SparkMLlibModel]:
+    """Load a model written by :meth:`SparkModel.save` (``spark_model.py:355-389``)."""
+    from .io.keras_h5 import load_model, read_root_attrs
+    assert file_name[-3:] == ".h5" or file_name[-6:] == ".keras", \
+        "File name must end with either '.h5' or '.keras'"
+    if from_hadoop:
+        temp_file = str(uuid4()) + "-temp-model-file." + file_name.split(".")[-1]
+        subprocess.run(["hadoop", "fs", "-copyToLocal", file_name, temp_file])
+        file_name = temp_file
+    model = load_model(file_name)
+    raw = read_root_attrs(file_name).get('distributed_config')
+    elephas_conf = json.loads(raw.decode('utf8') if isinstance(raw, bytes) else raw)
+    class_name = elephas_conf.get('class_name')
+    config = elephas_conf.get('config')
+    if from_hadoop:
+        Path(file_name).unlink()
+    if class_name == SparkModel.__name__:
+        return SparkModel(model=model, **config)
+    if class_name == SparkMLlibModel.__name__:
+        return SparkMLlibModel(model=model, **config)
+    raise ValueError("unknown distributed_config class_name %r" % (class_name,))

@@ -1,0 +1,57 @@
+"""NumPy <-> RDD <-> LabeledPoint conversions.
+
+Reference: ``elephas/utils/rdd_utils.py:10-85`` (``to_simple_rdd``, ``to_labeled_point``,
+``from_labeled_point``, ``encode_label``, ``lp_to_simple_rdd``). Same signatures and results; with
+the local Spark stand-in ``to_simple_rdd`` keeps each partition as two dense arrays
+(:class:`elephas_b200.spark.context.PairBlock`) so that the GPU workers can stage a partition into
+pinned memory without touching Python rows (generic RDD callers still see ``(x, y)`` pairs).
+"""
+from typing import Optional, Tuple
+
+import numpy as np
+
+from ..mllib.adapter import from_vector, to_vector
+from ..spark import HAVE_PYSPARK, LabeledPoint, PairBlock
+
+
+def to_simple_rdd(sc, features: np.ndarray, labels: np.ndarray):
+    """Features and labels -> RDD of ``(feature_row, label_row)`` pairs."""
+    if not HAVE_PYSPARK:
+        return sc.parallelize(PairBlock(np.asarray(features), np.asarray(labels)))
+    return sc.parallelize([(x, y) for x, y in zip(features, labels)])
+
+
+def to_labeled_point(sc, features: np.ndarray, labels: np.ndarray, categorical: bool = False):
+    """Features and labels -> RDD of ``LabeledPoint``; one-hot labels are argmax-decoded when ``categorical``."""
+    points = [LabeledPoint(np.argmax(y) if categorical else y, to_vector(np.asarray(x).ravel()))
+              for x, y in zip(features, labels)]
+    return sc.parallelize(points)
+
+
+def from_labeled_point(rdd, categorical: bool = False, nb_classes: Optional[int] = None) -> Tuple[np.ndarray, np.ndarray]:
+    """LabeledPoint RDD -> ``(features, labels)`` arrays; labels one-hot encoded when ``categorical``."""
+    pairs = rdd.map(lambda lp: (from_vector(lp.features), int(lp.label))).collect()
+    features = np.array([p[0] for p in pairs])
+    labels = np.array([p[1] for p in pairs])
+    if categorical:
+        if not nb_classes:
+            nb_classes = int(np.max(labels)) + 1
+        labels = np.stack([encode_label(l, nb_classes) for l in labels])
+    return features, labels
+
+
+def encode_label(label, nb_classes: int) -> np.ndarray:
+    """One-hot vector for a single (integral) label."""
+    encoded = np.zeros(nb_classes)
+    encoded[int(label)] = 1.
+    return encoded
+
+
+def lp_to_simple_rdd(lp_rdd, categorical: bool = False, nb_classes: int = None):
+    """LabeledPoint RDD -> RDD of ``(features, label)`` pairs (label one-hot when ``categorical``;
+    ``nb_classes`` inferred as ``max + 1`` when not given, ``rdd_utils.py:80``)."""
+    if categorical:
+        if not nb_classes:
+            nb_classes = int(lp_rdd.map(lambda lp: lp.label).map(int).max()) + 1
+        return lp_rdd.map(lambda lp: (from_vector(lp.features), encode_label(lp.label, nb_classes)))
+    return lp_rdd.map(lambda lp: (from_vector(lp.features), lp.label))

@@ -1,0 +1,199 @@
+"""Workers: the code that trains one data partition.
+
+Reference: ``elephas/worker.py:11-131`` (``SparkWorker`` for synchronous mode,
+``AsynchronousSparkWorker`` for asynchronous / hogwild). Constructor signatures and the
+``train(data_iterator)`` generator protocol are unchanged - ``train`` yields ``[deltas, history]``
+(sync) or ``[]`` (async) - so they still work as ``rdd.mapPartitions(worker.train)``.
+
+What changed underneath: a worker is bound to a *device* (one B200 per rank, or the CPU), the
+partition can arrive as dense arrays (:class:`~elephas_b200.spark.context.PairBlock`) instead of an
+iterator of Python rows, and the synchronous worker additionally exposes a round-based API
+(``begin`` / ``train_round`` / ``train_batch``) so ``SparkModel`` can average every epoch or every
+batch while the worker keeps its model and optimizer state between rounds.
+
+Reference quirks kept on purpose: partitions with ``rows <= batch_size`` train nothing and yield a
+zero delta (``worker.py:41,107,116``, D2); batch-frequency async training never shuffles and
+ignores ``validation_split`` (``worker.py:96,114-127``, D4).
+"""
+import copy
+
+import numpy as np
+
+from .models import model_from_json
+from .models import optimizers as _optimizers
+from .parameter.client import BaseParameterClient
+from .utils.functional_utils import subtract_params
+
+
+def partition_to_arrays(data_iterator):
+    """Materialise a partition as ``(x, y)`` arrays. Accepts a PairBlock, any object with ``x``/``y``
+    arrays, or an iterator / list of ``(features, label)`` rows (``worker.py:36-38``)."""
+    if hasattr(data_iterator, 'x') and hasattr(data_iterator, 'y'):
+        return np.asarray(data_iterator.x), np.asarray(data_iterator.y)
+    rows = list(data_iterator)
+    if not rows:
+        return np.zeros((0,), dtype=np.float32), np.zeros((0,), dtype=np.float32)
+    x = np.asarray([np.asarray(r[0]) for r in rows])
+    y = np.asarray([np.asarray(r[1]) for r in rows])
+    return x, y
+
+
+def fresh_optimizer(master_optimizer):
+    """Every worker gets its own optimizer instance with empty slots (``worker.py:29,88``)."""
+    if isinstance(master_optimizer, _optimizers.Optimizer):
+        return _optimizers.deserialize(_optimizers.serialize(master_optimizer))
+    return _optimizers.get(copy.deepcopy(master_optimizer))
+
+
+def _weights_of(parameters):
+    return parameters.value if hasattr(parameters, 'value') else parameters
+
+
+class _WorkerBase:
+    def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
+                 custom_objects, device=None):
+        self.json = json
+        self.parameters = parameters
+        self.train_config = dict(train_config)
+        self.master_optimizer = master_optimizer
+        self.master_loss = master_loss
+        self.master_metrics = master_metrics
+        self.custom_objects = custom_objects
+        self.device = device
+        self.model = None
+
+    def _build_model(self):
+        from .parallel.runtime import default_device
+        model = model_from_json(self.json, self.custom_objects)
+        model.custom_objects = dict(self.custom_objects or {})
+        model.compile(optimizer=fresh_optimizer(self.master_optimizer), loss=self.master_loss,
+                      metrics=self.master_metrics)
+        model.set_weights(_weights_of(self.parameters))
+        model.to(self.device if self.device is not None else default_device())
+        self.model = model
+        return model
+
+
+class SparkWorker(_WorkerBase):
+    """Synchronous worker: trains a replica on its partition and reports ``before - after``."""
+
+    def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
+                 custom_objects, device=None):
+        super().__init__(json, parameters, train_config, master_optimizer, master_loss, master_metrics,
+                         custom_objects, device)
+        self.x_train = self.y_train = None
+        self.history = {}
+
+    # ---------------------------------------------------- reference protocol
+    def train(self, data_iterator):
+        """Train all epochs on the partition, then yield ``[deltas, history_dict_or_None]``."""
+        self.begin(data_iterator)
+        deltas, history = self.train_round(None, epochs=self.train_config.get('epochs', 1))
+        yield [deltas, history]
+
+    # ------------------------------------------------------ round-based API
+    def begin(self, data_iterator):
+        self._build_model()
+        self.x_train, self.y_train = partition_to_arrays(data_iterator)
+        self.history = {}
+        return self
+
+    @property
+    def trainable(self):
+        """Reference guard: a partition not larger than one batch is skipped (``worker.py:41``)."""
+        return self.x_train is not None and self.x_train.shape[0] > int(self.train_config.get('batch_size') or 32)
+
+    def num_batches(self):
+        if not self.trainable:
+            return 0
+        n = self.x_train.shape[0]
+        split = float(self.train_config.get('validation_split') or 0.0)
+        n_train = int(n * (1.0 - split)) if 0.0 < split < 1.0 else n
+        bs = int(self.train_config.get('batch_size') or 32)
+        return -(-n_train // bs)
+
+    def train_round(self, weights, epochs=1, initial_epoch=0):
+        """Load ``weights`` (None: keep current), train ``epochs`` epochs, return ``(deltas, history)``."""
+        if weights is not None:
+            self.model.set_weights(weights)
+        before = self.model.get_weights()
+        history = None
+        if self.trainable:
+            cfg = dict(self.train_config)
+            cfg['epochs'] = initial_epoch + epochs
+            cfg['initial_epoch'] = initial_epoch
+            h = self.model.fit(self.x_train, self.y_train, **cfg)
+            for k, v in h.history.items():
+                self.history.setdefault(k, []).extend(v)
+            history = self.history
+        after = self.model.get_weights()
+        return subtract_params(before, after), history
+
+    def train_batch(self, weights, batch_index):
+        """One ``train_on_batch`` on the ``batch_index``-th contiguous batch (no shuffling); returns the
+        delta, or a zero delta when this worker has no such batch."""
+        if weights is not None:
+            self.model.set_weights(weights)
+        before = self.model.get_weights()
+        bs = int(self.train_config.get('batch_size') or 32)
+        start = batch_index * bs
+        if self.trainable and start < self.x_train.shape[0]:
+            stats = self.model.train_on_batch(self.x_train[start:start + bs], self.y_train[start:start + bs])
+            stats = stats if isinstance(stats, list) else [stats]
+            for k, v in zip(self.model.metrics_names, stats):
+                self.history.setdefault('batch_' + k, []).append(v)
+        after = self.model.get_weights()
+        return subtract_params(before, after)
+
+
+class AsynchronousSparkWorker(_WorkerBase):
+    """Asynchronous / hogwild worker: pull -> train -> push against a parameter server, once per
+    epoch or once per batch."""
+
+    def __init__(self, json, parameters, client, train_config, frequency, master_optimizer, master_loss,
+                 master_metrics, custom_objects, device=None):
+        super().__init__(json, parameters, train_config, master_optimizer, master_loss, master_metrics,
+                         custom_objects, device)
+        if isinstance(client, BaseParameterClient):
+            self.client = client
+        else:  # a client type name ('http' | 'socket' | 'nvlink'), as the reference allows
+            self.client = BaseParameterClient.get_client(client)
+        self.frequency = frequency
+        self.history = {}
+
+    def train(self, data_iterator):
+        x_train, y_train = partition_to_arrays(data_iterator)
+        if x_train.size == 0:
+            return
+        if self.frequency not in ('epoch', 'batch'):
+            raise ValueError('frequency parameter can be `epoch` or `batch, got {}'.format(self.frequency))
+        model = self._build_model()
+        epochs = int(self.train_config['epochs'])
+        batch_size = int(self.train_config.get('batch_size') or 32)
+        n = x_train.shape[0]
+        trainable = n > batch_size
+
+        if self.frequency == 'epoch':
+            cfg = dict(self.train_config)
+            for epoch in range(epochs):
+                before = self.client.get_parameters()
+                model.set_weights(before)
+                if trainable:
+                    cfg['epochs'] = epoch + 1
+                    cfg['initial_epoch'] = epoch
+                    h = model.fit(x_train, y_train, **cfg)
+                    for k, v in h.history.items():
+                        self.history.setdefault(k, []).extend(v)
+                self.client.update_parameters(subtract_params(before, model.get_weights()))
+        else:
+            nb_batch = -(-n // batch_size)
+            for epoch in range(epochs):
+                if not trainable:
+                    continue
+                for b in range(nb_batch):
+                    before = self.client.get_parameters()
+                    model.set_weights(before)
+                    lo, hi = b * batch_size, min(n, (b + 1) * batch_size)
+                    model.train_on_batch(x_train[lo:hi], y_train[lo:hi])
+                    self.client.update_parameters(subtract_params(before, model.get_weights()))
+        yield []

@@ -1,0 +1,84 @@
+import struct
+
+import numpy as np
+import pytest
+
+from elephas_b200.io import hdf5
+from elephas_b200.models import SGD, load_model, to_categorical, zoo
+
+
+def test_lookup3_vectors():
+    # self-test vectors from Bob Jenkins' lookup3.c
+    assert hdf5.lookup3(b'') == 0xdeadbeef
+    assert hdf5.lookup3(b'Four score and seven years ago') == 0x17770551
+    assert hdf5.lookup3(b'Four score and seven years ago', 1) == 0xcd628161
+
+
+def test_tree_round_trip(tmp_path):
+    root = hdf5.Group({'text': b'hello', 'number': np.int64(7), 'vec': np.arange(4, dtype=np.float64),
+                       'names': np.array([b'dense/kernel:0', b'dense/bias:0'])})
+    g = root.create_group('a/b')
+    g.attrs['empty'] = np.zeros((0,))
+    g.create_dataset('w:0', np.arange(12, dtype=np.float32).reshape(3, 4), attrs={'unit': b'none'})
+    root.create_dataset('i64', np.arange(5, dtype=np.int64))
+    path = str(tmp_path / 't.h5')
+    hdf5.write_file(path, root)
+    back = hdf5.read_file(path)
+    assert back.attrs['text'] == b'hello' and int(back.attrs['number']) == 7
+    assert np.array_equal(back.attrs['vec'], np.arange(4.0))
+    assert [bytes(n) for n in back.attrs['names']] == [b'dense/kernel:0', b'dense/bias:0']
+    assert np.array_equal(back['a/b/w:0'].data, np.arange(12, dtype=np.float32).reshape(3, 4))
+    assert back['a/b/w:0'].attrs['unit'] == b'none' and back['a/b'].attrs['empty'].shape == (0,)
+    assert np.array_equal(back['i64'].data, np.arange(5))
+
+
+def test_file_structure_is_spec_conformant(tmp_path):
+    path = str(tmp_path / 's.h5')
+    hdf5.write_file(path, hdf5.Group({'k': b'v'}))
+    raw = open(path, 'rb').read()
+    assert raw[:8] == b'\x89HDF\r\n\x1a\n' and raw[8] == 2 and raw[9] == 8 and raw[10] == 8
+    eof, root_addr = struct.unpack('<QQ', raw[28:44])
+    assert eof == len(raw) and raw[root_addr:root_addr + 4] == b'OHDR'
+    assert struct.unpack('<I', raw[44:48])[0] == hdf5.lookup3(raw[:44])
+    size = struct.unpack('<I', raw[root_addr + 6:root_addr + 10])[0]
+    end = root_addr + 10 + size
+    assert struct.unpack('<I', raw[end:end + 4])[0] == hdf5.lookup3(raw[root_addr:end])
+
+
+def test_large_attribute_is_split_and_rejoined(tmp_path):
+    blob = bytes(range(1, 251)) * 700  # 175 kB
+    path = str(tmp_path / 'big.h5')
+    hdf5.write_file(path, hdf5.Group({'model_config': blob}))
+    assert hdf5.read_file(path).attrs['model_config'] == blob
+
+
+def test_keras_layout_and_model_round_trip(tmp_path, mnist_data):
+    x, y, _, _ = mnist_data
+    m = zoo.mnist_mlp(dropout=0.0)
+    m.compile(SGD(lr=0.1, momentum=0.9), 'categorical_crossentropy', ['acc'])
+    m.fit(x[:200], y[:200], batch_size=50, epochs=1)
+    path = str(tmp_path / 'm.h5')
+    m.save(path)
+    tree = hdf5.read_file(path)
+    assert set(tree.attrs) >= {'keras_version', 'backend', 'model_config', 'training_config'}
+    mw = tree['model_weights']
+    names = [bytes(n).decode() for n in mw.attrs['layer_names']]
+    assert names == [l.name for l in m.layers]
+    dense = m.layers[1].name
+    assert mw[dense + '/' + dense + '/kernel:0'].data.shape == (784, 128)  # Keras (in, out) layout
+    assert 'optimizer_weights' in tree
+    m2 = load_model(path)
+    assert m2.to_json() == m.to_json()
+    assert np.array_equal(m2.predict(x[:20]), m.predict(x[:20]))
+    assert m2.optimizer.get_config() == m.optimizer.get_config() and m2.optimizer.iterations == 4
+    assert m2.loss == 'categorical_crossentropy' and m2.metrics_names == ['loss', 'acc']
+    # resume: momentum slots survived
+    s1 = m.train_on_batch(x[:50], y[:50]); s2 = m2.train_on_batch(x[:50], y[:50])
+    assert np.allclose(m.get_weights()[-2], m2.get_weights()[-2], atol=1e-6)
+
+
+def test_not_hdf5(tmp_path):
+    p = tmp_path / 'x.h5'
+    p.write_bytes(b'nope' * 100)
+    with pytest.raises(ValueError):
+        hdf5.read_file(str(p))

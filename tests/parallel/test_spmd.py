@@ -1,0 +1,41 @@
+"""Multi-process path on the CPU: two ranks over gloo (the host-side logic of the one-rank-per-GPU design)."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(('127.0.0.1', 0))
+        return s.getsockname()[1]
+
+
+def _launch(tmp_path, mode, ps, freq):
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(HERE, 'spmd_script.py'), mode, ps, freq, str(_free_port()), str(tmp_path)]
+    env = dict(os.environ, SPARK_LOCAL_IP='127.0.0.1', OMP_NUM_THREADS='2')
+    res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
+    return [json.load(open(os.path.join(str(tmp_path), 'rank%d.json' % r))) for r in range(2)]
+
+
+@pytest.mark.parametrize('mode,ps,freq', [('synchronous', 'none', 'epoch'), ('synchronous', 'none', 'batch'),
+                                          ('asynchronous', 'socket', 'epoch'), ('hogwild', 'http', 'epoch')])
+def test_two_ranks(tmp_path, mode, ps, freq):
+    r0, r1 = _launch(tmp_path, mode, ps, freq)
+    # every rank ends with the same master weights, predictions and evaluation
+    assert abs(r0['digest'] - r1['digest']) < 1e-3 * max(1.0, abs(r0['digest']))
+    assert r0['argmax'] == r1['argmax'] and r0['n_pred'] == 200
+    assert abs(r0['eval'][0] - r1['eval'][0]) < 1e-6
+    # distributed evaluate == local evaluate, and training made progress
+    assert abs(r0['eval'][0] - r0['local'][0]) < 0.01 and abs(r0['eval'][1] - r0['local'][1]) < 0.01
+    assert r0['eval'][0] < r0['before'][0]
+    if mode == 'synchronous':
+        assert r0['hist'] == 2

@@ -1,0 +1,86 @@
+"""The reference leaves this file as a TODO (tests/parameter/test_server.py:1). Servers and clients are
+tested directly here: protocol round trips, the w <- w - delta arithmetic against a NumPy oracle, and
+exactness of concurrent pushes in the locked ('asynchronous') mode."""
+import threading
+from itertools import count
+
+import numpy as np
+import pytest
+
+from elephas.parameter.factory import ClientServerFactory
+from elephas.utils.serialization import model_to_dict
+from elephas_b200.models import Dense, Sequential
+
+_ports = count(5200)
+
+
+def _tiny_model():
+    m = Sequential()
+    m.add(Dense(8, input_dim=4, activation='relu'))
+    m.add(Dense(2))
+    return m
+
+
+@pytest.mark.parametrize('ps', ['http', 'socket', 'nvlink'])
+@pytest.mark.parametrize('mode', ['asynchronous', 'hogwild'])
+def test_pull_push_round_trip(ps, mode):
+    port = next(_ports)
+    model = _tiny_model()
+    factory = ClientServerFactory.get_factory(ps)
+    server = factory.create_server(model_to_dict(model), port, mode)
+    client = factory.create_client(port)
+    server.start()
+    try:
+        w0 = model.get_weights()
+        pulled = client.get_parameters()
+        assert all(np.allclose(a, b) for a, b in zip(pulled, w0))
+        delta = [np.full_like(w, 0.25) for w in w0]
+        client.update_parameters(delta)
+        client.update_parameters(delta)
+        after = client.get_parameters()
+        assert all(np.allclose(a, b - 0.5) for a, b in zip(after, w0))
+        assert all(np.allclose(a, b - 0.5) for a, b in zip(server.get_weights(), w0))
+    finally:
+        server.stop()
+
+
+@pytest.mark.parametrize('ps', ['http', 'socket', 'nvlink'])
+def test_locked_mode_loses_no_update(ps):
+    port = next(_ports)
+    model = _tiny_model()
+    factory = ClientServerFactory.get_factory(ps)
+    server = factory.create_server(model_to_dict(model), port, 'asynchronous')
+    server.start()
+    try:
+        w0 = model.get_weights()
+        n_threads, n_push = 4, 10
+
+        def pusher():
+            client = factory.create_client(port)
+            for _ in range(n_push):
+                client.update_parameters([np.ones_like(w) for w in w0])
+
+        threads = [threading.Thread(target=pusher) for _ in range(n_threads)]
+        [t.start() for t in threads]
+        [t.join() for t in threads]
+        final = factory.create_client(port).get_parameters()
+        for a, b in zip(final, w0):
+            assert np.allclose(a, b - n_threads * n_push, atol=1e-4)
+    finally:
+        server.stop()
+
+
+def test_unknown_factory():
+    with pytest.raises(ValueError):
+        ClientServerFactory.get_factory('smoke-signals')
+
+
+def test_http_home_route():
+    import urllib.request
+    port = next(_ports)
+    server = ClientServerFactory.get_factory('http').create_server(model_to_dict(_tiny_model()), port, 'hogwild')
+    server.start()
+    try:
+        assert urllib.request.urlopen('http://%s/' % server.master_url).read() == b'Elephas'
+    finally:
+        server.stop()

@@ -1,0 +1,433 @@
+// K6 / K7: collectives and the parameter server as kernels over NVLink peer memory.
+//
+// Every rank maps every other rank's communication buffers (CUDA IPC, see eb_ipc_*), so a kernel on
+// GPU r can load from and store / reduce into the HBM of GPU p directly; NVSwitch gives each pair
+// full bandwidth, so the kernels use flat all-to-all access patterns rather than rings.
+//
+//  * allreduce_update (K6): the synchronous-mode round of the reference - collect every worker's
+//    delta, average, subtract from the master weights (elephas/spark_model.py:220-231) - as ONE
+//    kernel: cross-GPU flag barrier, P2P reduction of the peers' deltas, 1/N scaling, fp32 master
+//    update and bf16 weight refresh. One-shot variant (every rank reduces everything; latency bound
+//    payloads) and two-shot variant (reduce-scatter of a 1/N slice + P2P all-gather of the averaged
+//    slice + local apply; bandwidth bound payloads, 2(N-1)/N bytes per element over NVLink).
+//  * allreduce_sum: plain one-shot sum (evaluate statistics, generic delta lists).
+//  * ps_push / ps_pull / ps_lock / ps_unlock (K7): the parameter server of elephas/parameter/server.py
+//    with the master weights resident in (peer) HBM: push is red.global.add.f32 of -delta straight
+//    into the owner's memory (fused with delta = before - after), pull is a vectorised (peer) copy
+//    fused with the bf16 cast; 'asynchronous' mode brackets them with a system-scope ticket lock
+//    (the device-side counterpart of utils/rwlock.py), 'hogwild' does not (server.py:109,120).
+//
+// Barrier protocol: each rank owns a signal pad of 32-bit epoch flags (one per peer). A rank
+// announces "my delta for epoch e is visible" by storing e into slot [rank] of every peer's pad
+// (st.release.sys after a system fence) and waits until all of its own slots are >= e
+// (ld.acquire.sys). Delta buffers are double buffered by the caller, which makes the start barrier
+// of epoch e+1 double as the "everyone finished reading epoch e" barrier.
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+#include <string.h>
+
+#include "../include/elephas_b200.h"
+#include "host.h"
+#include "ptx.cuh"
+
+namespace eb {
+
+constexpr int kMaxRanks = 8;
+
+__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void red_add_v4_f32_sys(float* p, float a, float b, float c, float d) {
+  asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+__device__ __forceinline__ void red_add_f32_sys(float* p, float a) {
+  asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
+}
+
+struct CommDev {
+  const void* delta[kMaxRanks];  // every rank's delta buffer for this epoch (peer mapped)
+  void* avg[kMaxRanks];          // two-shot: every rank's averaged-delta buffer (peer mapped)
+  uint32_t* pad[kMaxRanks];      // every rank's signal pad: [0..8) start flags, [8..16) phase flags
+  uint32_t* local;               // local scratch: [0] epoch counter, [1] finished-block counter, [2] phase counter
+  float* w32;
+  __nv_bfloat16* w16;
+  float* out32;                  // allreduce_sum output
+  long n;
+  int rank, world;
+  float scale;
+};
+
+// All blocks wait until every peer has published epoch `e` in this rank's pad (slot base `slot0`).
+__device__ __forceinline__ void wait_flags(const CommDev& p, int slot0, uint32_t e) {
+  if (threadIdx.x < p.world) {
+    const uint32_t* f = p.pad[p.rank] + slot0 + threadIdx.x;
+    while (ld_acquire_sys(f) < e) {
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ void publish_flags(const CommDev& p, int slot0, uint32_t e) {
+  __threadfence_system();
+  if (threadIdx.x < p.world) st_release_sys(p.pad[threadIdx.x] + slot0 + p.rank, e);
+}
+
+template <typename T>
+__device__ __forceinline__ void accumulate8(const void* base, long i, float (&s)[8]);
+
+template <>
+__device__ __forceinline__ void accumulate8<__nv_bfloat16>(const void* base, long i, float (&s)[8]) {
+  const uint4 v = ld_peer_v4(static_cast<const __nv_bfloat16*>(base) + i);
+  s[0] += bf16_lo(v.x); s[1] += bf16_hi(v.x); s[2] += bf16_lo(v.y); s[3] += bf16_hi(v.y);
+  s[4] += bf16_lo(v.z); s[5] += bf16_hi(v.z); s[6] += bf16_lo(v.w); s[7] += bf16_hi(v.w);
+}
+
+template <>
+__device__ __forceinline__ void accumulate8<float>(const void* base, long i, float (&s)[8]) {
+  const uint4 a = ld_peer_v4(static_cast<const float*>(base) + i);
+  const uint4 b = ld_peer_v4(static_cast<const float*>(base) + i + 4);
+  s[0] += __uint_as_float(a.x); s[1] += __uint_as_float(a.y); s[2] += __uint_as_float(a.z); s[3] += __uint_as_float(a.w);
+  s[4] += __uint_as_float(b.x); s[5] += __uint_as_float(b.y); s[6] += __uint_as_float(b.z); s[7] += __uint_as_float(b.w);
+}
+
+__device__ __forceinline__ void apply8(const CommDev& p, long i, const float (&d)[8]) {
+  float4 w0 = *reinterpret_cast<float4*>(p.w32 + i), w1 = *reinterpret_cast<float4*>(p.w32 + i + 4);
+  w0.x -= d[0]; w0.y -= d[1]; w0.z -= d[2]; w0.w -= d[3];
+  w1.x -= d[4]; w1.y -= d[5]; w1.z -= d[6]; w1.w -= d[7];
+  *reinterpret_cast<float4*>(p.w32 + i) = w0;
+  *reinterpret_cast<float4*>(p.w32 + i + 4) = w1;
+  if (p.w16) {
+    uint4 o;
+    o.x = pack_bf16x2(w0.x, w0.y); o.y = pack_bf16x2(w0.z, w0.w);
+    o.z = pack_bf16x2(w1.x, w1.y); o.w = pack_bf16x2(w1.z, w1.w);
+    *reinterpret_cast<uint4*>(p.w16 + i) = o;
+  }
+}
+
+// mode 0: one-shot all-reduce + update; mode 1: one-shot sum into out32 (no update).
+template <typename T, int MODE>
+__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommDev p) {
+  const uint32_t e = p.local[0] + 1;
+  if (blockIdx.x == 0) publish_flags(p, 0, e);
+  wait_flags(p, 0, e);
+  const long n8 = p.n / 8;
+  for (long g = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < n8;
+       g += static_cast<long>(gridDim.x) * blockDim.x) {
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+    for (int k = 0; k < p.world; ++k) {
+      int peer = p.rank + k;
+      if (peer >= p.world) peer -= p.world;
+      accumulate8<T>(p.delta[peer], g * 8, s);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] *= p.scale;
+    if (MODE == 0) {
+      apply8(p, g * 8, s);
+    } else {
+      *reinterpret_cast<float4*>(p.out32 + g * 8) = make_float4(s[0], s[1], s[2], s[3]);
+      *reinterpret_cast<float4*>(p.out32 + g * 8 + 4) = make_float4(s[4], s[5], s[6], s[7]);
+    }
+  }
+  // the last block to finish advances the local epoch counter
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.local + 1, 1u) == gridDim.x - 1) {
+      p.local[1] = 0;
+      p.local[0] = e;
+    }
+  }
+}
+
+// Two-shot: reduce-scatter my slice from all peers, write the averaged slice into every peer's avg
+// buffer, cross-GPU barrier, apply the full averaged delta locally. The grid must be co-resident.
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev p) {
+  const uint32_t e = p.local[0] + 1;
+  if (blockIdx.x == 0) publish_flags(p, 0, e);
+  wait_flags(p, 0, e);
+  const long n8 = p.n / 8;
+  const long per = (n8 + p.world - 1) / p.world;
+  const long lo = per * p.rank, hi = min(n8, lo + per);
+  for (long g = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < hi;
+       g += static_cast<long>(gridDim.x) * blockDim.x) {
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+    for (int k = 0; k < p.world; ++k) {
+      int peer = p.rank + k;
+      if (peer >= p.world) peer -= p.world;
+      accumulate8<T>(p.delta[peer], g * 8, s);
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] *= p.scale;
+    if (sizeof(T) == 2) {
+      uint4 o;
+      o.x = pack_bf16x2(s[0], s[1]); o.y = pack_bf16x2(s[2], s[3]);
+      o.z = pack_bf16x2(s[4], s[5]); o.w = pack_bf16x2(s[6], s[7]);
+#pragma unroll 1
+      for (int k = 0; k < p.world; ++k) {
+        int peer = p.rank + k;
+        if (peer >= p.world) peer -= p.world;
+        st_v4(static_cast<__nv_bfloat16*>(p.avg[peer]) + g * 8, o);
+      }
+    } else {
+      uint4 o0 = make_uint4(__float_as_uint(s[0]), __float_as_uint(s[1]), __float_as_uint(s[2]), __float_as_uint(s[3]));
+      uint4 o1 = make_uint4(__float_as_uint(s[4]), __float_as_uint(s[5]), __float_as_uint(s[6]), __float_as_uint(s[7]));
+#pragma unroll 1
+      for (int k = 0; k < p.world; ++k) {
+        int peer = p.rank + k;
+        if (peer >= p.world) peer -= p.world;
+        st_v4(static_cast<float*>(p.avg[peer]) + g * 8, o0);
+        st_v4(static_cast<float*>(p.avg[peer]) + g * 8 + 4, o1);
+      }
+    }
+  }
+  // phase barrier: when every block of this rank has stored its part, tell all peers
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(p.local + 2, 1u) == gridDim.x - 1) {
+      p.local[2] = 0;
+      __threadfence_system();
+      for (int k = 0; k < p.world; ++k) st_release_sys(p.pad[k] + 8 + p.rank, e);
+    }
+  }
+  wait_flags(p, 8, e);
+  // apply the averaged delta (now complete in my avg buffer) to the local weights
+  const void* avg = p.avg[p.rank];
+  for (long g = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < n8;
+       g += static_cast<long>(gridDim.x) * blockDim.x) {
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    accumulate8<T>(avg, g * 8, s);
+    apply8(p, g * 8, s);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.local + 1, 1u) == gridDim.x - 1) {
+      p.local[1] = 0;
+      p.local[0] = e;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ parameter server
+__global__ void ps_lock_kernel(uint32_t* ctrl) {
+  // ctrl[1]: next ticket, ctrl[2]: now serving, ctrl[0]: sequence word (odd while a writer is inside)
+  const uint32_t ticket = atomicAdd_system(ctrl + 1, 1u);
+  while (ld_acquire_sys(ctrl + 2) != ticket) {
+  }
+  atomicAdd_system(ctrl + 0, 1u);
+  __threadfence_system();
+}
+
+__global__ void ps_unlock_kernel(uint32_t* ctrl) {
+  __threadfence_system();
+  atomicAdd_system(ctrl + 0, 1u);
+  __threadfence_system();
+  atomicAdd_system(ctrl + 2, 1u);
+}
+
+// master -= delta, where delta is given directly (fp32) or as before - after. red.add into (peer) HBM.
+__global__ void __launch_bounds__(256) ps_push_kernel(float* __restrict__ master, const float* __restrict__ delta,
+                                                      const float* __restrict__ before,
+                                                      const float* __restrict__ after, long n) {
+  const long n4 = n / 4;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    float4 d;
+    if (delta) {
+      d = reinterpret_cast<const float4*>(delta)[i];
+    } else {
+      const float4 b = reinterpret_cast<const float4*>(before)[i], a = reinterpret_cast<const float4*>(after)[i];
+      d = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, b.w - a.w);
+    }
+    if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) red_add_v4_f32_sys(master + 4 * i, -d.x, -d.y, -d.z, -d.w);
+  }
+  for (long i = n4 * 4 + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float d = delta ? delta[i] : before[i] - after[i];
+    if (d != 0.f) red_add_f32_sys(master + i, -d);
+  }
+}
+
+// dst32 <- master (peer loads), optionally dst16 <- bf16(master) in the same pass.
+__global__ void __launch_bounds__(256) ps_pull_kernel(const float* __restrict__ master, float* __restrict__ dst32,
+                                                      __nv_bfloat16* __restrict__ dst16, long n) {
+  const long n4 = n / 4;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const uint4 v = ld_peer_v4(master + 4 * i);
+    if (dst32) reinterpret_cast<uint4*>(dst32)[i] = v;
+    if (dst16) {
+      uint2 o;
+      o.x = pack_bf16x2(__uint_as_float(v.x), __uint_as_float(v.y));
+      o.y = pack_bf16x2(__uint_as_float(v.z), __uint_as_float(v.w));
+      reinterpret_cast<uint2*>(dst16)[i] = o;
+    }
+  }
+  for (long i = n4 * 4 + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float v = master[i];
+    if (dst32) dst32[i] = v;
+    if (dst16) dst16[i] = __float2bfloat16_rn(v);
+  }
+}
+
+static int fill_comm(const EbCommArgs* a, CommDev& p) {
+  if (a->world < 1 || a->world > kMaxRanks) return fail("comm: world size %d outside [1, %d]", a->world, kMaxRanks);
+  if (a->rank < 0 || a->rank >= a->world) return fail("comm: bad rank %d", a->rank);
+  if (a->n % 8) return fail("comm: element count must be a multiple of 8 (got %lld)", (long long)a->n);
+  for (int i = 0; i < kMaxRanks; ++i) {
+    p.delta[i] = i < a->world ? a->delta[i] : nullptr;
+    p.avg[i] = i < a->world ? a->avg[i] : nullptr;
+    p.pad[i] = i < a->world ? static_cast<uint32_t*>(a->pad[i]) : nullptr;
+    if (i < a->world && (p.delta[i] == nullptr || p.pad[i] == nullptr)) return fail("comm: missing peer pointer %d", i);
+  }
+  p.local = static_cast<uint32_t*>(a->local);
+  if (p.local == nullptr) return fail("comm: local scratch missing");
+  p.w32 = a->w32; p.w16 = static_cast<__nv_bfloat16*>(a->w16); p.out32 = a->out32;
+  p.n = a->n; p.rank = a->rank; p.world = a->world; p.scale = a->scale;
+  return 0;
+}
+
+}  // namespace eb
+
+using namespace eb;
+
+extern "C" int eb_allreduce_update(const EbCommArgs* a, void* stream) {
+  if (a == nullptr) return fail("eb_allreduce_update: null args");
+  if (a->n <= 0) return 0;
+  CommDev p;
+  if (fill_comm(a, p)) return 1;
+  if (p.w32 == nullptr) return fail("eb_allreduce_update: fp32 weights missing");
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int blocks = a->blocks > 0 ? a->blocks : num_sms();
+  const long work = a->n / 8;
+  const bool twoshot = a->algo == 2 || (a->algo == 0 && a->world > 2 && a->n * (a->dtype_bf16 ? 2 : 4) > (4l << 20));
+  if (twoshot) {
+    for (int i = 0; i < a->world; ++i)
+      if (p.avg[i] == nullptr) return fail("eb_allreduce_update: two-shot needs the avg buffers");
+    if (blocks > num_sms()) blocks = num_sms();  // co-resident grid: the kernel contains a grid-wide barrier
+    if (a->dtype_bf16) allreduce_twoshot_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(p);
+    else allreduce_twoshot_kernel<float><<<blocks, 512, 0, s>>>(p);
+    EB_LAUNCH_OK("allreduce_twoshot_kernel");
+  } else {
+    if (blocks > (work + 511) / 512) blocks = static_cast<int>((work + 511) / 512);
+    if (blocks < 1) blocks = 1;
+    if (a->dtype_bf16) allreduce_oneshot_kernel<__nv_bfloat16, 0><<<blocks, 512, 0, s>>>(p);
+    else allreduce_oneshot_kernel<float, 0><<<blocks, 512, 0, s>>>(p);
+    EB_LAUNCH_OK("allreduce_oneshot_kernel");
+  }
+  return 0;
+}
+
+extern "C" int eb_allreduce_sum(const EbCommArgs* a, void* stream) {
+  if (a == nullptr) return fail("eb_allreduce_sum: null args");
+  if (a->n <= 0) return 0;
+  CommDev p;
+  if (fill_comm(a, p)) return 1;
+  if (p.out32 == nullptr) return fail("eb_allreduce_sum: output missing");
+  int blocks = a->blocks > 0 ? a->blocks : num_sms();
+  const long work = a->n / 8;
+  if (blocks > (work + 511) / 512) blocks = static_cast<int>((work + 511) / 512);
+  if (blocks < 1) blocks = 1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (a->dtype_bf16) allreduce_oneshot_kernel<__nv_bfloat16, 1><<<blocks, 512, 0, s>>>(p);
+  else allreduce_oneshot_kernel<float, 1><<<blocks, 512, 0, s>>>(p);
+  EB_LAUNCH_OK("allreduce_oneshot_kernel(sum)");
+  return 0;
+}
+
+extern "C" int eb_ps_lock(void* ctrl, void* stream) {
+  ps_lock_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<uint32_t*>(ctrl));
+  EB_LAUNCH_OK("ps_lock_kernel");
+  return 0;
+}
+
+extern "C" int eb_ps_unlock(void* ctrl, void* stream) {
+  ps_unlock_kernel<<<1, 1, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<uint32_t*>(ctrl));
+  EB_LAUNCH_OK("ps_unlock_kernel");
+  return 0;
+}
+
+extern "C" int eb_ps_push(float* master, const float* delta, const float* before, const float* after, int64_t n,
+                          void* stream) {
+  if (n <= 0) return 0;
+  if (delta == nullptr && (before == nullptr || after == nullptr)) return fail("eb_ps_push: need delta or before/after");
+  long blocks = (n / 4 + 255) / 256;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  if (blocks < 1) blocks = 1;
+  ps_push_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(master, delta, before, after, n);
+  EB_LAUNCH_OK("ps_push_kernel");
+  return 0;
+}
+
+extern "C" int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  long blocks = (n / 4 + 255) / 256;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  if (blocks < 1) blocks = 1;
+  ps_pull_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      master, dst_f32, static_cast<__nv_bfloat16*>(dst_bf16), n);
+  EB_LAUNCH_OK("ps_pull_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------ memory / IPC plumbing
+extern "C" int eb_device_malloc(void** ptr, int64_t bytes) {
+  EB_CUDA_OK(cudaMalloc(ptr, static_cast<size_t>(bytes)));
+  EB_CUDA_OK(cudaMemset(*ptr, 0, static_cast<size_t>(bytes)));
+  return 0;
+}
+
+extern "C" int eb_device_free(void* ptr) {
+  EB_CUDA_OK(cudaFree(ptr));
+  return 0;
+}
+
+extern "C" int eb_ipc_export(void* ptr, void* handle64) {
+  cudaIpcMemHandle_t h;
+  EB_CUDA_OK(cudaIpcGetMemHandle(&h, ptr));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64, &h, 64);
+  return 0;
+}
+
+extern "C" int eb_ipc_import(const void* handle64, void** ptr) {
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  EB_CUDA_OK(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+extern "C" int eb_ipc_close(void* ptr) {
+  EB_CUDA_OK(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+extern "C" int eb_enable_peer_access(int32_t peer_device) {
+  cudaError_t e = cudaDeviceEnablePeerAccess(peer_device, 0);
+  if (e == cudaErrorPeerAccessAlreadyEnabled) {
+    cudaGetLastError();
+    return 0;
+  }
+  EB_CUDA_OK(e);
+  return 0;
+}

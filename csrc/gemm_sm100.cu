@@ -46,6 +46,7 @@ struct GemmDev {
   uint32_t drop_thresh;
   float drop_scale;
   uint64_t seed, drop_stream;
+  const long long* step_ptr;
   __nv_bfloat16* out_bf16;
   int ldo;
   float* out_f32;
@@ -214,6 +215,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     int acc = 0;
     uint32_t acc_phase = 0;
     const bool has_drop = p.drop_p > 0.f;
+    // the Philox stream is offset by the device-side step counter so that a CUDA-graph replay draws fresh masks
+    const uint64_t drop_stream = p.drop_stream + (p.step_ptr ? static_cast<uint64_t>(*p.step_ptr) * 1024ull : 0ull);
     for (int t = first_tile; t < num_tiles; t += tile_step) {
       int tm, tn;
       tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
@@ -256,7 +259,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 4) {
               bool keep[4];
-              dropout_keep4(p.seed, p.drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
+              dropout_keep4(p.seed, drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
 #pragma unroll
               for (int e = 0; e < 4; ++e) x[j + e] = keep[e] ? x[j + e] * p.drop_scale : 0.f;
             }
@@ -282,7 +285,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 4) {
               bool keep[4];
-              dropout_keep4(p.seed, p.drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
+              dropout_keep4(p.seed, drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
 #pragma unroll
               for (int e = 0; e < 4; ++e)
                 x[j + e] = keep[e] ? x[j + e] * p.drop_scale * act_grad_from_out(p.act, y[j + e] * inv_scale) : 0.f;
@@ -471,6 +474,7 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
   p.drop_p = a.drop_p; p.drop_thresh = dropout_threshold(a.drop_p);
   p.drop_scale = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;
   p.seed = a.seed; p.drop_stream = a.drop_stream;
+  p.step_ptr = static_cast<const long long*>(a.step_ptr);
   p.out_bf16 = static_cast<__nv_bfloat16*>(a.out_bf16); p.ldo = a.ldo;
   p.out_f32 = a.out_f32; p.ldo32 = a.ldo32; p.beta = a.beta;
   p.tiles_m = p.tiles_n = 0;

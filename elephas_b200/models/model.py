@@ -193,6 +193,7 @@ class Model:
             self.optimizer._slots = {k: v.to(device) for k, v in self.optimizer._slots.items()}
         self._device = device
         self._engine = None
+        self._infer_engine = None
         return self
 
     @property
@@ -216,8 +217,9 @@ class Model:
             self._engine.export_weights()
 
     def _push_to_engine(self):
-        if self._engine is not None:
-            self._engine.import_weights()
+        for eng in (self._engine, getattr(self, '_infer_engine', None)):
+            if eng is not None:
+                eng.import_weights()
 
     # ---------------------------------------------------------------- config
     def get_config(self):
@@ -282,18 +284,30 @@ class Model:
 
     # --------------------------------------------------------------- compile
     def compile(self, optimizer='rmsprop', loss=None, metrics=None, **kwargs):
-        self.optimizer = _optimizers.get(optimizer)
+        new_opt = _optimizers.get(optimizer)
+        metrics = list(metrics) if metrics else []
+        signature = (json.dumps(_optimizers.serialize(new_opt), sort_keys=True, default=str),
+                     _losses.canonical_name(loss), tuple(str(m) for m in metrics), str(self._device))
+        same = self._compiled and getattr(self, '_compile_signature', None) == signature and self._engine is not None
+        self.optimizer = new_opt
         self.loss = loss
         self._loss_name = _losses.canonical_name(loss)
         self._loss_fn = _losses.get(loss, self.custom_objects)
-        metrics = list(metrics) if metrics else []
         self.compiled_metrics = _CompiledMetrics(list(metrics) if metrics else None)
         out_shape = self.output_shape
         out_dim = out_shape[-1] if out_shape and not isinstance(out_shape[0], (tuple, list)) else None
         self._metric_fns = [_metrics.resolve(m, self._loss_name, out_dim, self.custom_objects) for m in metrics]
         self.metrics_names = ['loss'] + [n for n, _ in self._metric_fns]
         self._compiled = True
+        self._compile_signature = signature
+        if same:
+            # identical configuration: keep the native engine (buffers, CUDA graphs), start from fresh slots
+            self._engine.reset_optimizer(new_opt)
+            self._engine_key = (self._device, id(self.optimizer))
+            return
+        self._sync_from_engine()
         self._engine = None
+        self._infer_engine = None
 
     def _require_compiled(self):
         if not self._compiled:

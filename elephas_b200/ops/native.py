@@ -1,0 +1,348 @@
+"""ctypes bindings of ``libelephas_b200.so`` (C ABI declared in ``include/elephas_b200.h``).
+
+Every wrapper takes torch CUDA tensors, passes raw device pointers and the *current* torch CUDA
+stream, and raises ``NativeError`` with the library's message on failure - there is no silent
+fallback: on a machine with a GPU a missing library is an error (``require()``), so a test that
+passes has run the sm_100a kernels.
+"""
+import ctypes
+import os
+import threading
+
+import torch
+
+from . import build as _build
+
+c_void_p, c_int32, c_int64, c_float, c_uint64 = (ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64, ctypes.c_float,
+                                                   ctypes.c_uint64)
+
+ACT_IDS = {'linear': 0, 'relu': 1, 'sigmoid': 2, 'tanh': 3, 'softplus': 4, 'softsign': 5, 'elu': 6, 'selu': 7,
+           'exponential': 8, 'hard_sigmoid': 9, 'softmax': 100}
+EPI_FWD, EPI_ACTGRAD = 0, 1
+LOSS_IDS = {'mean_squared_error': 0, 'mean_absolute_error': 1, 'mean_absolute_percentage_error': 2,
+            'mean_squared_logarithmic_error': 3, 'categorical_crossentropy': 4, 'binary_crossentropy': 5,
+            'logcosh': 6}
+METRIC_IDS = {'none': 0, 'categorical_accuracy': 1, 'binary_accuracy': 2, 'mean_absolute_error': 3,
+              'mean_squared_error': 4, 'mean_absolute_percentage_error': 5}
+OPT_IDS = {'SGD': 1, 'RMSprop': 2, 'Adam': 3, 'Adagrad': 4, 'Adadelta': 5, 'Adamax': 6}
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+class GemmArgs(ctypes.Structure):
+    _fields_ = [('M', c_int32), ('N', c_int32), ('K', c_int32),
+                ('A', c_void_p), ('lda', c_int32), ('a_mn', c_int32),
+                ('B', c_void_p), ('ldb', c_int32), ('b_mn', c_int32),
+                ('alpha', c_float), ('epi', c_int32), ('act', c_int32),
+                ('bias', c_void_p), ('aux', c_void_p), ('ldaux', c_int32),
+                ('drop_p', c_float), ('seed', c_uint64), ('drop_stream', c_uint64), ('step_ptr', c_void_p),
+                ('out_bf16', c_void_p), ('ldo', c_int32),
+                ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float),
+                ('block_n', c_int32), ('cta_group', c_int32)]
+
+
+class LossArgs(ctypes.Structure):
+    _fields_ = [('z', c_void_p), ('ldz', c_int64), ('y', c_void_p), ('ldy', c_int64),
+                ('out', c_void_p), ('ldo', c_int64), ('dz', c_void_p), ('lddz', c_int64),
+                ('stats', c_void_p), ('rows', c_int32), ('cols', c_int32), ('loss', c_int32), ('act', c_int32),
+                ('metrics', c_int32 * 4), ('grad_scale', c_float)]
+
+
+class OptimArgs(ctypes.Structure):
+    _fields_ = [('kind', c_int32), ('n', c_int64), ('w32', c_void_p), ('g32', c_void_p),
+                ('slot0', c_void_p), ('slot1', c_void_p), ('slot2', c_void_p), ('w16', c_void_p),
+                ('delta_bf16', c_void_p), ('delta_f32', c_void_p), ('apply', c_int32), ('advance', c_int32),
+                ('lr', c_float), ('decay', c_float), ('momentum', c_float), ('rho', c_float), ('eps', c_float),
+                ('beta1', c_float), ('beta2', c_float), ('nesterov', c_int32), ('centered', c_int32),
+                ('amsgrad', c_int32), ('step', c_void_p)]
+
+
+class CommArgs(ctypes.Structure):
+    _fields_ = [('delta', c_void_p * 8), ('avg', c_void_p * 8), ('pad', c_void_p * 8), ('local', c_void_p),
+                ('w32', c_void_p), ('w16', c_void_p), ('out32', c_void_p), ('n', c_int64),
+                ('rank', c_int32), ('world', c_int32), ('scale', c_float), ('dtype_bf16', c_int32),
+                ('algo', c_int32), ('blocks', c_int32)]
+
+
+_lib = None
+_lib_lock = threading.Lock()
+
+
+def lib_path():
+    return _build.LIB_PATH
+
+
+def available() -> bool:
+    return os.path.exists(_build.LIB_PATH)
+
+
+def load():
+    """Load (building first if the sources are newer and nvcc is present) and return the library."""
+    global _lib
+    with _lib_lock:
+        if _lib is not None:
+            return _lib
+        if not os.path.exists(_build.LIB_PATH):
+            _build.build()
+        lib = ctypes.CDLL(_build.LIB_PATH, mode=ctypes.RTLD_GLOBAL)
+        lib.eb_last_error.restype = ctypes.c_char_p
+        lib.eb_launch_count.restype = c_uint64
+        lib.eb_version.restype = c_int32
+        for name in ('eb_gemm_bf16', 'eb_loss_fwd_bwd', 'eb_optimizer_step', 'eb_allreduce_update',
+                     'eb_allreduce_sum'):
+            getattr(lib, name).argtypes = [c_void_p, c_void_p]
+        lib.eb_stage_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
+        lib.eb_cast_f32_to_bf16.argtypes = [c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_colsum_bf16.argtypes = [c_void_p, c_int64, c_int32, c_int32, c_void_p, c_int32, c_void_p]
+        lib.eb_act_dropout_fwd.argtypes = [c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_float, c_uint64,
+                                           c_uint64, c_void_p, c_void_p]
+        lib.eb_act_dropout_bwd.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_float,
+                                           c_uint64, c_uint64, c_void_p, c_void_p]
+        lib.eb_delta.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_ps_lock.argtypes = [c_void_p, c_void_p]
+        lib.eb_ps_unlock.argtypes = [c_void_p, c_void_p]
+        lib.eb_ps_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_ps_pull.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
+        lib.eb_device_free.argtypes = [c_void_p]
+        lib.eb_ipc_export.argtypes = [c_void_p, c_void_p]
+        lib.eb_ipc_import.argtypes = [c_void_p, ctypes.POINTER(c_void_p)]
+        lib.eb_ipc_close.argtypes = [c_void_p]
+        lib.eb_enable_peer_access.argtypes = [c_int32]
+        _lib = lib
+        return lib
+
+
+def require():
+    """The library, or a loud failure: used on every GPU code path."""
+    try:
+        return load()
+    except Exception as exc:
+        raise NativeError("libelephas_b200.so is required on a CUDA device but could not be loaded/built: %s" % exc)
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise NativeError("%s failed: %s" % (what, load().eb_last_error().decode('utf8', 'replace')))
+
+
+def _ptr(t):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream(device=None):
+    return c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def launch_count() -> int:
+    return int(load().eb_launch_count()) if _lib is not None or available() else 0
+
+
+# ----------------------------------------------------------------------- GEMM
+def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=None, ldo=None, out_f32=None,
+         ldo32=None, beta=0.0, alpha=1.0, epi=EPI_FWD, act=0, bias=None, aux=None, ldaux=None, drop_p=0.0, seed=0,
+         drop_stream=0, step_ptr=None, block_n=0, cta_group=0):
+    """``C[M,N] = epilogue(A x B^T)`` on the tcgen05 GEMM (see ``EbGemmArgs`` for the operand layouts)."""
+    g = GemmArgs()
+    g.M, g.N, g.K = int(M), int(N), int(K)
+    g.A, g.lda, g.a_mn = A.data_ptr(), int(lda if lda is not None else A.stride(0)), int(bool(a_mn))
+    g.B, g.ldb, g.b_mn = B.data_ptr(), int(ldb if ldb is not None else B.stride(0)), int(bool(b_mn))
+    g.alpha, g.epi, g.act = float(alpha), int(epi), int(act)
+    g.bias = bias.data_ptr() if bias is not None else None
+    g.aux = aux.data_ptr() if aux is not None else None
+    g.ldaux = int(ldaux if ldaux is not None else (aux.stride(0) if aux is not None else 0))
+    g.drop_p, g.seed, g.drop_stream = float(drop_p), int(seed) & (2 ** 64 - 1), int(drop_stream) & (2 ** 64 - 1)
+    g.step_ptr = step_ptr.data_ptr() if step_ptr is not None else None
+    g.out_bf16 = out_bf16.data_ptr() if out_bf16 is not None else None
+    g.ldo = int(ldo if ldo is not None else (out_bf16.stride(0) if out_bf16 is not None else 0))
+    g.out_f32 = out_f32.data_ptr() if out_f32 is not None else None
+    g.ldo32 = int(ldo32 if ldo32 is not None else (out_f32.stride(0) if out_f32 is not None else 0))
+    g.beta = float(beta)
+    g.block_n, g.cta_group = int(block_n), int(cta_group)
+    _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
+
+
+# ---------------------------------------------------------------- elementwise
+def stage_f32_to_bf16(src, dst, rows, cols):
+    _check(require().eb_stage_f32_to_bf16(_ptr(src), src.stride(0), _ptr(dst), dst.stride(0), int(rows), int(cols),
+                                          _stream(src.device)), 'eb_stage_f32_to_bf16')
+
+
+def cast_f32_to_bf16(src, dst, n=None):
+    _check(require().eb_cast_f32_to_bf16(_ptr(src), _ptr(dst), int(n if n is not None else src.numel()),
+                                         _stream(src.device)), 'eb_cast_f32_to_bf16')
+
+
+def colsum_bf16(x, rows, cols, out, accumulate=False, ld=None):
+    _check(require().eb_colsum_bf16(_ptr(x), int(ld if ld is not None else x.stride(0)), int(rows), int(cols),
+                                    _ptr(out), int(bool(accumulate)), _stream(x.device)), 'eb_colsum_bf16')
+
+
+def act_dropout_fwd(x, y, rows, cols, act=0, drop_p=0.0, seed=0, drop_stream=0, ld=None, step_ptr=None):
+    _check(require().eb_act_dropout_fwd(_ptr(x), _ptr(y), int(ld if ld is not None else x.stride(0)), int(rows),
+                                        int(cols), int(act), float(drop_p), int(seed), int(drop_stream),
+                                        _ptr(step_ptr), _stream(x.device)), 'eb_act_dropout_fwd')
+
+
+def act_dropout_bwd(dy, y, dx, rows, cols, act=0, drop_p=0.0, seed=0, drop_stream=0, ld=None, step_ptr=None):
+    _check(require().eb_act_dropout_bwd(_ptr(dy), _ptr(y), _ptr(dx), int(ld if ld is not None else y.stride(0)),
+                                        int(rows), int(cols), int(act), float(drop_p), int(seed), int(drop_stream),
+                                        _ptr(step_ptr), _stream(y.device)), 'eb_act_dropout_bwd')
+
+
+def delta(before, after, out_f32=None, out_bf16=None, n=None):
+    _check(require().eb_delta(_ptr(before), _ptr(after), _ptr(out_f32), _ptr(out_bf16),
+                              int(n if n is not None else before.numel()), _stream(before.device)), 'eb_delta')
+
+
+# ----------------------------------------------------------------------- loss
+def loss_fwd_bwd(z, y, rows, cols, loss, act, out=None, dz=None, stats=None, metrics=(0, 0, 0, 0), grad_scale=1.0,
+                 ldz=None, ldy=None, ldo=None, lddz=None):
+    a = LossArgs()
+    a.z, a.ldz = z.data_ptr(), int(ldz if ldz is not None else z.stride(0))
+    a.y = y.data_ptr()
+    a.ldy = int(ldy if ldy is not None else (y.stride(0) if y.dim() > 1 else 0))
+    a.out = out.data_ptr() if out is not None else None
+    a.ldo = int(ldo if ldo is not None else (out.stride(0) if out is not None else 0))
+    a.dz = dz.data_ptr() if dz is not None else None
+    a.lddz = int(lddz if lddz is not None else (dz.stride(0) if dz is not None else 0))
+    a.stats = stats.data_ptr() if stats is not None else None
+    a.rows, a.cols, a.loss, a.act = int(rows), int(cols), int(loss), int(act)
+    m = list(metrics) + [0] * (4 - len(metrics))
+    a.metrics = (c_int32 * 4)(*m[:4])
+    a.grad_scale = float(grad_scale)
+    _check(require().eb_loss_fwd_bwd(ctypes.byref(a), _stream(z.device)), 'eb_loss_fwd_bwd')
+
+
+# ------------------------------------------------------------------ optimizer
+def optimizer_step(kind, n, g32, step, w32=None, w16=None, slots=(None, None, None), delta_bf16=None, delta_f32=None,
+                   apply=True, advance=True, lr=0.01, decay=0.0, momentum=0.0, rho=0.9, eps=1e-7, beta1=0.9,
+                   beta2=0.999, nesterov=False, centered=False, amsgrad=False):
+    a = OptimArgs()
+    a.kind, a.n = int(kind), int(n)
+    a.w32, a.g32 = (w32.data_ptr() if w32 is not None else None), g32.data_ptr()
+    s = list(slots) + [None] * (3 - len(slots))
+    a.slot0, a.slot1, a.slot2 = [(t.data_ptr() if t is not None else None) for t in s[:3]]
+    a.w16 = w16.data_ptr() if w16 is not None else None
+    a.delta_bf16 = delta_bf16.data_ptr() if delta_bf16 is not None else None
+    a.delta_f32 = delta_f32.data_ptr() if delta_f32 is not None else None
+    a.apply, a.advance = int(bool(apply)), int(bool(advance))
+    a.lr, a.decay, a.momentum, a.rho, a.eps = float(lr), float(decay), float(momentum), float(rho), float(eps)
+    a.beta1, a.beta2 = float(beta1), float(beta2)
+    a.nesterov, a.centered, a.amsgrad = int(bool(nesterov)), int(bool(centered)), int(bool(amsgrad))
+    a.step = step.data_ptr()
+    _check(require().eb_optimizer_step(ctypes.byref(a), _stream(g32.device)), 'eb_optimizer_step')
+
+
+# ------------------------------------------------------------------ collectives
+def _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, avg_ptrs=None, w32=None, w16=None,
+               out32=None, algo=0, blocks=0):
+    a = CommArgs()
+    for i in range(8):
+        a.delta[i] = delta_ptrs[i] if i < world else None
+        a.pad[i] = pad_ptrs[i] if i < world else None
+        a.avg[i] = avg_ptrs[i] if (avg_ptrs is not None and i < world) else None
+    a.local = local.data_ptr() if hasattr(local, 'data_ptr') else local
+    a.w32 = w32.data_ptr() if w32 is not None else None
+    a.w16 = w16.data_ptr() if w16 is not None else None
+    a.out32 = out32.data_ptr() if out32 is not None else None
+    a.n, a.rank, a.world, a.scale = int(n), int(rank), int(world), float(scale)
+    a.dtype_bf16, a.algo, a.blocks = int(bool(dtype_bf16)), int(algo), int(blocks)
+    return a
+
+
+def allreduce_update(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, w32, w16=None, avg_ptrs=None,
+                     algo=0, blocks=0, device=None):
+    a = _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, avg_ptrs, w32, w16, None, algo,
+                   blocks)
+    _check(require().eb_allreduce_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_update')
+
+
+def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32, scale=1.0, blocks=0, device=None):
+    a = _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, None, None, None, out32, 1, blocks)
+    _check(require().eb_allreduce_sum(ctypes.byref(a), _stream(device)), 'eb_allreduce_sum')
+
+
+# ------------------------------------------------------------ parameter server
+def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None):
+    lib = require()
+    s = _stream(dst_f32.device if dst_f32 is not None else dst_bf16.device)
+    n = int(n if n is not None else (dst_f32.numel() if dst_f32 is not None else dst_bf16.numel()))
+    mptr = master.data_ptr() if hasattr(master, 'data_ptr') else master
+    cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
+    if locked:
+        _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
+    _check(lib.eb_ps_pull(mptr, _ptr(dst_f32), _ptr(dst_bf16), n, s), 'eb_ps_pull')
+    if locked:
+        _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+
+
+def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=None):
+    lib = require()
+    ref = delta if delta is not None else before
+    s = _stream(ref.device)
+    n = int(n if n is not None else ref.numel())
+    mptr = master.data_ptr() if hasattr(master, 'data_ptr') else master
+    cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
+    if locked:
+        _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
+    _check(lib.eb_ps_push(mptr, _ptr(delta), _ptr(before), _ptr(after), n, s), 'eb_ps_push')
+    if locked:
+        _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+
+
+# --------------------------------------------------------------- memory / IPC
+def device_malloc(nbytes) -> int:
+    p = c_void_p()
+    _check(require().eb_device_malloc(ctypes.byref(p), int(nbytes)), 'eb_device_malloc')
+    return p.value
+
+
+def device_free(ptr):
+    _check(require().eb_device_free(c_void_p(ptr)), 'eb_device_free')
+
+
+def ipc_export(ptr) -> bytes:
+    buf = ctypes.create_string_buffer(64)
+    _check(require().eb_ipc_export(c_void_p(ptr), buf), 'eb_ipc_export')
+    return buf.raw
+
+
+def ipc_import(handle: bytes) -> int:
+    p = c_void_p()
+    buf = ctypes.create_string_buffer(handle, 64)
+    _check(require().eb_ipc_import(buf, ctypes.byref(p)), 'eb_ipc_import')
+    return p.value
+
+
+def ipc_close(ptr):
+    _check(require().eb_ipc_close(c_void_p(ptr)), 'eb_ipc_close')
+
+
+class RawBuffer:
+    """A device allocation made by the library (cudaMalloc, IPC-exportable) viewed as torch tensors."""
+
+    def __init__(self, nbytes, device):
+        self.nbytes = int(nbytes)
+        self.device = torch.device(device)
+        with torch.cuda.device(self.device):
+            self.ptr = device_malloc(self.nbytes)
+        self._owned = True
+
+    def tensor(self, dtype, numel=None, offset_bytes=0):
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        numel = int(numel if numel is not None else (self.nbytes - offset_bytes) // itemsize)
+        typestr = {torch.float32: '<f4', torch.bfloat16: '<u2', torch.int32: '<i4', torch.uint8: '|u1',
+                   torch.int64: '<i8', torch.float64: '<f8'}[dtype]
+        iface = {'shape': (numel,), 'typestr': typestr, 'data': (self.ptr + offset_bytes, False), 'version': 3}
+        holder = type('_CudaArray', (), {'__cuda_array_interface__': iface})()
+        t = torch.as_tensor(holder, device=self.device)
+        return t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
+
+    def free(self):
+        if self._owned and self.ptr:
+            with torch.cuda.device(self.device):
+                device_free(self.ptr)
+            self.ptr = 0

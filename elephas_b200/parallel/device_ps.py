@@ -27,15 +27,53 @@ _stores_guard = threading.Lock()
 
 
 class DeviceStore:
-    def __init__(self, port, layout_model, arrays, mode, device):
+    def __init__(self, port, layout_model, arrays, mode, device, remote_handle=None):
         from .flat import FlatLayout
         self.port, self.mode, self.device = port, mode, torch.device(device)
         self.layout = FlatLayout(layout_model)
-        self.flat = self.layout.pack_arrays(arrays, device=self.device)
-        # ctrl[0]: sequence word (odd while a writer is inside), ctrl[1]: next ticket, ctrl[2]: now serving
-        self.ctrl = torch.zeros(8, dtype=torch.int32, device=self.device)
+        self._raw = None
+        self._remote_base = None
+        n = self.layout.numel
+        if self.device.type == 'cuda':
+            from ..ops import native
+            ctrl_off = n * 4
+            if remote_handle is None:
+                # owner: one IPC-exportable allocation holding the master weights and the control words
+                self._raw = native.RawBuffer(ctrl_off + 256, self.device)
+                base = self._raw.ptr
+                self.flat = self._raw.tensor(torch.float32, n)
+                self.ctrl = self._raw.tensor(torch.int32, 8, offset_bytes=ctrl_off)
+                self.layout.pack_arrays(arrays, out=self.flat)
+            else:
+                # another rank: map the owner's allocation; pulls/pushes go over NVLink
+                with torch.cuda.device(self.device):
+                    base = native.ipc_import(remote_handle)
+                self._remote_base = base
+                self.flat = _PeerPointer(base, n, self.device)
+                self.ctrl = _PeerPointer(base + ctrl_off, 8, self.device)
+        else:
+            self.flat = self.layout.pack_arrays(arrays, device=self.device)
+            # ctrl[0]: sequence word (odd while a writer is inside), ctrl[1]: next ticket, ctrl[2]: now serving
+            self.ctrl = torch.zeros(8, dtype=torch.int32, device=self.device)
         self._host_lock = RWLock()
         self.pushes = 0
+
+    def export_handle(self):
+        from ..ops import native
+        return native.ipc_export(self._raw.ptr) if self._raw is not None else None
+
+    def close(self):
+        from ..ops import native
+        if self._remote_base is not None:
+            try:
+                native.ipc_close(self._remote_base)
+            except native.NativeError:
+                pass
+            self._remote_base = None
+        if self._raw is not None:
+            torch.cuda.synchronize(self.device)
+            self._raw.free()
+            self._raw = None
 
     @property
     def locked(self):
@@ -72,7 +110,7 @@ class DeviceStore:
 
     # ------------------------------------------------- list-of-arrays contract
     def pull_arrays(self):
-        tmp = torch.empty_like(self.flat)
+        tmp = torch.empty(self.layout.numel, dtype=torch.float32, device=self.device)
         self.pull_into(tmp)
         if tmp.is_cuda:
             torch.cuda.current_stream(tmp.device).synchronize()
@@ -82,11 +120,33 @@ class DeviceStore:
         self.push_delta(self.layout.pack_arrays(delta, device=self.device))
 
 
+class _PeerPointer:
+    """A raw (peer-mapped) device address that quacks enough like a tensor for the native wrappers."""
+
+    def __init__(self, ptr, numel, device):
+        self._ptr, self._numel, self.device, self.is_cuda = ptr, numel, device, True
+
+    def data_ptr(self):
+        return self._ptr
+
+    def numel(self):
+        return self._numel
+
+
 def create_store(port, arrays, mode, model=None, device=None):
     from .runtime import default_device
     if model is None:
         raise ValueError("create_store needs the model whose weights it holds")
     store = DeviceStore(port, model, arrays, mode, device or default_device())
+    with _stores_guard:
+        _stores[port] = store
+    return store
+
+
+def attach_remote_store(port, handle, mode, model, device=None):
+    """Register a proxy for a store owned by another rank (``handle``: its CUDA IPC handle)."""
+    from .runtime import default_device
+    store = DeviceStore(port, model, None, mode, device or default_device(), remote_handle=handle)
     with _stores_guard:
         _stores[port] = store
     return store
@@ -102,4 +162,6 @@ def get_store(port):
 
 def destroy_store(port):
     with _stores_guard:
-        _stores.pop(port, None)
+        store = _stores.pop(port, None)
+    if store is not None:
+        store.close()

@@ -1,0 +1,330 @@
+"""Synchronous mode on the native engine: local steps + ONE fused all-reduce/update kernel per round.
+
+Reference semantics (``elephas/spark_model.py:217-231`` + ``elephas/worker.py:26-49``): every worker
+trains a replica from the same weights, reports ``delta = before - after``, the driver subtracts the
+mean delta from the master weights. Here one rank = one worker = one B200, and the replica *is* the
+rank's copy of the master network (moved to the device once and trained in place - no broadcast, no
+collect, no host copy of the weights):
+
+* ``frequency='batch'``: the optimizer kernel runs in *delta mode* - it updates its slots and writes
+  the step as a bf16 delta into peer-mapped memory instead of touching the weights - and the
+  ``allreduce_update`` kernel (K6) reads all peers' deltas over NVLink, averages them, applies the
+  result to the fp32 master weights and refreshes the bf16 compute copy, all in one launch;
+* ``frequency='epoch'`` (or ``sync_rounds='fit'``): the replica trains an epoch (or all epochs)
+  locally, ``eb_delta`` (K5) forms ``before - after`` in fp32 straight into peer-mapped memory, the
+  weights are reset to ``before`` and the same K6 kernel applies the mean delta.
+
+Input pipeline: the partition lives in pinned host memory; ``input_mode='device'`` (default when the
+partition fits comfortably) uploads it once and gathers batches on the device, ``input_mode='stream'``
+copies every batch host->device on a side stream, double buffered, overlapping the previous step.
+``log_batch_loss=True`` additionally reads the running loss back every step (one 64-byte
+device->host copy, one step delayed so it never stalls the GPU). ``keep_context=True`` keeps engine,
+CUDA graphs and peer-mapped buffers alive on the ``SparkModel`` for the next ``fit`` call.
+"""
+import numpy as np
+import torch
+
+from ..models import History
+from ..ops import engine as _engine
+from ..ops import native
+from ..worker import partition_to_arrays
+from .symm import SymmetricMemory
+
+IN_PLACE = object()  # returned instead of a weight list: the master network already holds the result
+
+
+def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
+    if rt.device.type != 'cuda' or not _engine.native_enabled():
+        return None
+    if len(partitions) != rt.world_size or len(mine) != 1:
+        return None
+    master = spark_model.master_network
+    if master.device != rt.device:
+        master.to(rt.device)
+    eng = master._native_engine()
+    if not all(rt.all_gather_object(eng is not None)):
+        return None
+    ctx = getattr(spark_model, '_sync_context', None)
+    if ctx is None or ctx.eng is not eng:
+        if ctx is not None:
+            ctx.close()
+        ctx = SyncContext(spark_model, rt, master, eng)
+        spark_model._sync_context = ctx
+    histories = ctx.run(mine[0][1], train_config, sync_rounds)
+    if not train_config.get('keep_context'):
+        ctx.close()
+        spark_model._sync_context = None
+    return IN_PLACE, histories
+
+
+class _InputFeeder:
+    """Delivers batches into the engine's static input buffers."""
+
+    def __init__(self, eng, x, y, batch_size, mode, shuffle):
+        self.eng, self.bs, self.shuffle = eng, batch_size, shuffle
+        dev = eng.device
+        n = len(x)
+        self.n = n
+        self.x_host = self._pinned(x, n)
+        self.y_host = self._pinned(y, n)
+        nbytes = self.x_host.numel() * 4 + self.y_host.numel() * 4
+        if mode is None:
+            mode = 'device' if nbytes < (8 << 30) else 'stream'
+        if mode not in ('device', 'stream'):
+            raise ValueError("input_mode must be 'device' or 'stream', got %r" % (mode,))
+        self.mode = mode
+        self.h2d_bytes_per_step = 0
+        if mode == 'device':
+            self.xd = self.x_host.to(dev, non_blocking=True)
+            self.yd = self.y_host.to(dev, non_blocking=True)
+        else:
+            self.copy_stream = torch.cuda.Stream(dev)
+            self.stage = [(torch.empty(batch_size, self.x_host.shape[1], dtype=torch.float32, device=dev),
+                           torch.empty(batch_size, self.y_host.shape[1], dtype=torch.float32, device=dev),
+                           torch.cuda.Event()) for _ in range(2)]
+            self.h2d_bytes_per_step = batch_size * (self.x_host.shape[1] + self.y_host.shape[1]) * 4
+            self.consumed = [None, None]
+        self.order = None
+
+    @staticmethod
+    def _pinned(a, n):
+        """Host tensor view of ``a`` in page-locked memory; arrays that already live in pinned memory
+        (e.g. NumPy views of ``torch.empty(..., pin_memory=True)``) are used in place."""
+        t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32).reshape(n, -1))
+        return t if t.is_pinned() else t.pin_memory()
+
+    def start_epoch(self):
+        dev = self.eng.device
+        if self.shuffle:
+            self.order = torch.randperm(self.n, device=dev if self.mode == 'device' else 'cpu')
+        else:
+            self.order = None
+        if self.mode == 'stream':
+            self._prefetch(0, 0)
+
+    def _host_batch(self, start, rows):
+        if self.order is None:
+            return self.x_host[start:start + rows], self.y_host[start:start + rows]
+        idx = self.order[start:start + rows]
+        return self.x_host.index_select(0, idx).pin_memory(), self.y_host.index_select(0, idx).pin_memory()
+
+    def _prefetch(self, step, start):
+        rows = min(self.bs, self.n - start)
+        if rows <= 0:
+            return
+        slot = step % 2
+        xs, ys, ev = self.stage[slot]
+        xh, yh = self._host_batch(start, rows)
+        if self.consumed[slot] is not None:
+            # the slot may only be overwritten once the compute stream has drained its previous contents
+            self.copy_stream.wait_event(self.consumed[slot])
+        with torch.cuda.stream(self.copy_stream):
+            xs[:rows].copy_(xh, non_blocking=True)
+            ys[:rows].copy_(yh, non_blocking=True)
+            ev.record(self.copy_stream)
+
+    def load(self, step, start, buf):
+        """Fill ``buf.x32`` / ``buf.y32`` with batch ``step``; returns the number of rows."""
+        rows = min(self.bs, self.n - start)
+        if self.mode == 'device':
+            if self.order is not None:
+                idx = self.order[start:start + rows]
+                torch.index_select(self.xd, 0, idx, out=buf.x32)
+                torch.index_select(self.yd, 0, idx, out=buf.y32)
+            else:
+                buf.x32.copy_(self.xd[start:start + rows])
+                buf.y32.copy_(self.yd[start:start + rows])
+            return rows
+        slot = step % 2
+        xs, ys, ev = self.stage[slot]
+        cur = torch.cuda.current_stream(self.eng.device)
+        cur.wait_event(ev)
+        buf.x32.copy_(xs[:rows])
+        buf.y32.copy_(ys[:rows])
+        done = torch.cuda.Event()
+        done.record(cur)
+        self.consumed[slot] = done
+        # the next batch goes into the other slot: its H2D copy overlaps this step's compute
+        self._prefetch(step + 1, start + rows)
+        return rows
+
+
+class SyncContext:
+    """Everything a rank keeps between synchronous rounds: engine, peer-mapped buffers, flags."""
+
+    def __init__(self, spark_model, rt, model, eng):
+        self.sm, self.rt, self.model, self.eng = spark_model, rt, model, eng
+        self.mem = None
+        self.dtype_bf16 = None
+        self.bs = None
+        self.n_sub = rt.world_size
+
+    # ---------------------------------------------------------------- comm setup
+    def _setup_comm(self, dtype_bf16):
+        if self.mem is not None and self.dtype_bf16 == dtype_bf16:
+            return
+        if self.mem is not None:
+            self.mem.close()
+        n = self.eng.layout.numel
+        item = 2 if dtype_bf16 else 4
+        self.mem = SymmetricMemory(self.rt, {'delta0': n * item, 'delta1': n * item, 'avg': n * item, 'pad': 256})
+        self.comm_local = torch.zeros(16, dtype=torch.int32, device=self.rt.device)
+        self.dtype_bf16 = dtype_bf16
+        tdt = torch.bfloat16 if dtype_bf16 else torch.float32
+        self.delta = [self.mem.local('delta0', tdt, n), self.mem.local('delta1', tdt, n)]
+        self.flip = 0
+
+    def _allreduce_update(self):
+        name = 'delta%d' % self.flip
+        self.flip ^= 1
+        eng = self.eng
+        native.allreduce_update(self.mem.ptrs(name), self.mem.ptrs('pad'), self.comm_local, eng.layout.numel,
+                                self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32,
+                                w16=eng.w16, avg_ptrs=self.mem.ptrs('avg'), device=self.rt.device)
+        eng._weights_dirty_in_model = True
+
+    def close(self):
+        self.eng.delta_target = None
+        if self.mem is not None:
+            self.mem.close()
+            self.mem = None
+
+    # -------------------------------------------------------------- one sync step
+    def _step(self, buf, per_batch, have_batch):
+        eng = self.eng
+        if per_batch:
+            if have_batch:
+                eng.delta_target = self.delta[self.flip]
+                eng.train_step_device(buf)
+            else:
+                self.delta[self.flip].zero_()
+            self._allreduce_update()
+        elif have_batch:
+            eng.delta_target = None
+            eng.train_step_device(buf)
+
+    def _sync_start(self):
+        """All replicas start a fit from rank 0's weights (the reference broadcasts the driver's)."""
+        eng, rt = self.eng, self.rt
+        eng.reset_optimizer()
+        if rt.distributed:
+            rt.broadcast_(eng.w32, src=0)
+            eng.refresh_bf16()
+            eng._weights_dirty_in_model = True
+
+    # ----------------------------------------------------------------------- fit
+    def run(self, partition, train_config, sync_rounds):
+        rt, eng = self.rt, self.eng
+        cfg = dict(train_config)
+        x, y = partition_to_arrays(partition)
+        bs = self.bs = int(cfg.get('batch_size') or 32)
+        epochs = int(cfg.get('epochs', 1))
+        split = float(cfg.get('validation_split') or 0.0)
+        x_val = y_val = None
+        n_all = len(x)
+        if 0.0 < split < 1.0:
+            at = int(len(x) * (1.0 - split))
+            x, x_val, y, y_val = x[:at], x[at:], y[:at], y[at:]
+        trainable = n_all > bs and len(x) > 0  # reference guard (worker.py:41)
+        log_batch_loss = bool(cfg.get('log_batch_loss', False))
+        batch_losses = []
+        history = History()
+        frequency = self.sm.frequency
+        with torch.cuda.device(rt.device):
+            distributed = rt.distributed
+            per_batch = distributed and frequency == 'batch' and sync_rounds != 'fit'
+            self._sync_start()
+            if distributed:
+                self._setup_comm(dtype_bf16=per_batch)
+            steps_local = -(-len(x) // bs) if trainable else 0
+            steps = steps_local
+            if distributed:
+                steps = int(rt.all_reduce_max_(torch.tensor([steps_local], device=rt.device))[0])
+            feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True))) \
+                if trainable else None
+            names = self.model.metrics_names
+            pinned = [torch.zeros(8, dtype=torch.float64).pin_memory() for _ in range(2)]
+            events = [torch.cuda.Event() for _ in range(2)]
+            before = torch.empty_like(eng.w32) if (distributed and not per_batch) else None
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
+            for epoch in range(epochs):
+                if before is not None and (epoch == 0 or sync_rounds != 'fit'):
+                    before.copy_(eng.w32)
+                eng.stats.zero_()
+                if feeder:
+                    feeder.start_epoch()
+                start = 0
+                for s in range(steps):
+                    have = s < steps_local
+                    buf = None
+                    if have:
+                        rows = min(bs, len(x) - start)
+                        buf = eng._buf(rows)
+                        feeder.load(s, start, buf)
+                        start += rows
+                    self._step(buf, per_batch, have)
+                    if log_batch_loss:
+                        slot = s % 2
+                        pinned[slot].copy_(eng.stats, non_blocking=True)
+                        events[slot].record()
+                        if s > 0:
+                            events[1 - slot].synchronize()
+                            p = pinned[1 - slot]
+                            batch_losses.append(float(p[0] / max(float(p[7]), 1.0)))
+                if log_batch_loss and steps > 0:
+                    slot = (steps - 1) % 2
+                    events[slot].synchronize()
+                    batch_losses.append(float(pinned[slot][0] / max(float(pinned[slot][7]), 1.0)))
+                vals, count = eng.read_stats()
+                logs = dict(zip(names, vals)) if count else {}
+                if before is not None and (sync_rounds != 'fit' or epoch == epochs - 1):
+                    # delta = before - after (fp32, straight into peer-mapped memory), reset, fused reduce+update
+                    native.delta(before, eng.w32, out_f32=self.delta[self.flip])
+                    eng.w32.copy_(before)
+                    self._allreduce_update()
+                if x_val is not None and len(x_val) and logs:
+                    val = eng.evaluate(x_val, y_val)
+                    logs.update({'val_' + k: v for k, v in zip(names, val)})
+                if logs:
+                    history._append(epoch, logs)
+            t1.record()
+            torch.cuda.synchronize(rt.device)
+            eng.delta_target = None
+            eng._weights_dirty_in_model = True
+            self.model.optimizer.iterations = int(eng.step.item())
+        hist = dict(history.history) if trainable else None
+        if hist is not None and log_batch_loss:
+            hist['batch_loss'] = batch_losses
+        self.sm._last_sync_run = {'h2d_bytes_per_step': feeder.h2d_bytes_per_step if feeder else 0,
+                                  'steps_per_epoch': steps, 'device_ms': t0.elapsed_time(t1)}
+        gathered = rt.all_gather_object((rt.rank, hist))
+        return [h for _, h in sorted(gathered, key=lambda t: t[0])]
+
+    # ------------------------------------------------------------- kernel timing
+    def timed_steps(self, x, y, steps, input_mode='device'):
+        """Device time (ms, CUDA events) of exactly ``steps`` synchronous ``frequency='batch'`` steps on data
+        that is already resident on the device: the kernel-path number of bench.py."""
+        rt, eng, bs = self.rt, self.eng, self.bs
+        with torch.cuda.device(rt.device):
+            per_batch = rt.distributed
+            if per_batch:
+                self._setup_comm(dtype_bf16=True)
+            feeder = _InputFeeder(eng, x, y, bs, input_mode, False)
+            feeder.start_epoch()
+            torch.cuda.synchronize(rt.device)
+            rt.barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            start = 0
+            for s in range(steps):
+                rows = min(bs, len(x) - start)
+                buf = eng._buf(rows)
+                feeder.load(s, start, buf)
+                start += rows
+                self._step(buf, per_batch, True)
+            e1.record()
+            torch.cuda.synchronize(rt.device)
+            rt.barrier()
+            eng.delta_target = None
+            return e0.elapsed_time(e1)

@@ -259,3 +259,12 @@ class DeviceServer(BaseParameterServer):
         if self._store is not None:
             return self._store.pull_arrays()
         return super().get_weights()
+
+    def set_weights(self, weights):
+        super().set_weights(weights)
+        if self._store is not None:
+            self._store.layout.pack_arrays(self.weights, out=self._store.flat)
+
+    def export_handle(self):
+        """CUDA IPC handle of the master buffer (None on CPU): lets other ranks attach to the store."""
+        return self._store.export_handle() if self._store is not None else None

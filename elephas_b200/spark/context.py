@@ -111,6 +111,8 @@ class RDD:
 
     def repartition(self, numPartitions):
         numPartitions = max(1, int(numPartitions))
+        if numPartitions == len(self._partitions) and getattr(self, '_pinned_partitioning', False):
+            return self  # rank-sharded RDDs keep their one-partition-per-rank layout
         merged = _concat_blocks(self._partitions)
         return RDD([merged[a:b] for a, b in _split_bounds(len(merged), numPartitions)], self.context)
 

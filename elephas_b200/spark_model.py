@@ -84,7 +84,6 @@ class SparkModel:
         self.mode = mode
         self.frequency = frequency
         self.num_workers = num_workers
-        self.weights = self._master_network.get_weights()
         self.pickled_weights = None
         self.master_optimizer = _optimizers.serialize(model.optimizer)
         self.master_loss = model.loss
@@ -137,6 +136,19 @@ class SparkModel:
     @property
     def training_histories(self):
         return self._training_histories
+
+    @property
+    def weights(self):
+        """Current master weights (Keras order / layouts); read lazily so device-resident training
+        never pays a host copy it does not need."""
+        return self._master_network.get_weights()
+
+    def release_context(self):
+        """Free engine-side state kept by ``fit(..., keep_context=True)`` (peer-mapped buffers)."""
+        ctx = getattr(self, '_sync_context', None)
+        if ctx is not None:
+            ctx.close()
+            self._sync_context = None
 
     @property
     def master_network(self):
@@ -206,8 +218,8 @@ class SparkModel:
             new_parameters = self._fit_synchronous(rt, partitions, mine, train_config)
         else:
             raise ValueError("Unsupported mode {}".format(self.mode))
-        self._master_network.set_weights(new_parameters)
-        self.weights = new_parameters
+        if new_parameters is not None:  # None: trained in place on the device-resident master network
+            self._master_network.set_weights(new_parameters)
 
     # -- asynchronous / hogwild -------------------------------------------------
     def _fit_parameter_server(self, rt, partitions, mine, train_config):
@@ -215,7 +227,15 @@ class SparkModel:
             self.parameter_server.set_weights(self._master_network.get_weights())
             self.start_server()
         rt.barrier()
+        if self.parameter_server_mode == 'nvlink' and rt.distributed:
+            # ranks other than the owner map the master buffer through CUDA IPC (NVLink peer access)
+            handle = rt.broadcast_object(self.parameter_server.export_handle() if rt.is_driver else None, src=0)
+            if not rt.is_driver:
+                from .parallel.device_ps import attach_remote_store
+                attach_remote_store(self.port, handle, self.mode, self._master_network, rt.device)
         model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
+        for key in ('input_mode', 'log_batch_loss', 'keep_context'):
+            cfg.pop(key, None)
         if rt.is_driver:
             print('>>> Initialize workers')
         workers = [AsynchronousSparkWorker(model_json, init, self.client, cfg, self.frequency, optimizer, loss,
@@ -226,8 +246,15 @@ class SparkModel:
 
         def run(worker, part):
             try:
-                for _ in worker.train(part):
-                    pass
+                if rt.device.type == 'cuda':
+                    # every worker thread drives the GPU through its own stream
+                    with torch.cuda.device(rt.device), torch.cuda.stream(torch.cuda.Stream(rt.device)):
+                        for _ in worker.train(part):
+                            pass
+                        torch.cuda.current_stream(rt.device).synchronize()
+                else:
+                    for _ in worker.train(part):
+                        pass
             except BaseException as exc:  # surfaced after join; a dead worker must not hang the rest
                 errors.append(exc)
 
@@ -239,6 +266,10 @@ class SparkModel:
             t.join()
         rt.barrier()
         new_parameters = None
+        if self.parameter_server_mode == 'nvlink' and rt.distributed and not rt.is_driver:
+            from .parallel.device_ps import destroy_store
+            destroy_store(self.port)
+        rt.barrier()
         if rt.is_driver:
             new_parameters = self.parameter_server.get_weights()
             self.stop_server()
@@ -274,13 +305,16 @@ class SparkModel:
         # Fast path: native engines + fused delta all-reduce/update, one worker per rank.
         fast = sync_engine.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
         if fast is not None:
-            new_parameters, histories = fast
+            _, histories = fast
             self._training_histories.extend(histories)
             if rt.is_driver:
                 print('>>> Synchronous training complete.')
-            return new_parameters
+            return None
 
         model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
+        init = rt.broadcast_object(init, src=0)  # every replica starts from the driver's weights
+        for key in ('input_mode', 'log_batch_loss', 'keep_context'):
+            cfg.pop(key, None)  # options of the native fast path only
         workers = [SparkWorker(model_json, init, cfg, optimizer, loss, metrics, custom, device=rt.device).begin(p)
                    for _, p in mine]
         current = init

@@ -5,7 +5,7 @@ from .functional_utils import *  # noqa: F401,F403
 from .functional_utils import add_params, divide_by, get_neutral, subtract_params  # noqa: F401
 from .rdd_utils import *  # noqa: F401,F403
 from .rdd_utils import (encode_label, from_labeled_point, lp_to_simple_rdd, to_labeled_point,  # noqa: F401
-                        to_simple_rdd)
+                        to_sharded_rdd, to_simple_rdd)
 from .rwlock import *  # noqa: F401,F403
 from .rwlock import RWLock  # noqa: F401
 from .serialization import *  # noqa: F401,F403

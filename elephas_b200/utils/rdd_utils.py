@@ -55,3 +55,21 @@ def lp_to_simple_rdd(lp_rdd, categorical: bool = False, nb_classes: int = None):
             nb_classes = int(lp_rdd.map(lambda lp: lp.label).map(int).max()) + 1
         return lp_rdd.map(lambda lp: (from_vector(lp.features), encode_label(lp.label, nb_classes)))
     return lp_rdd.map(lambda lp: (from_vector(lp.features), lp.label))
+
+
+def to_sharded_rdd(sc, features: np.ndarray, labels: np.ndarray, rank: int = None, world_size: int = None):
+    """Rank-sharded variant of :func:`to_simple_rdd` for SPMD (``torchrun``) programs (no counterpart in
+    the reference, where Spark owns data placement): every rank passes only ITS OWN shard of the data and
+    gets an RDD with one partition per rank in which partition ``rank`` holds that shard and the others
+    are empty on this rank. ``SparkModel`` trains / predicts partition *i* on rank *i*, so the global
+    dataset is never replicated in every process - the way to feed datasets sized for 180 GB GPUs."""
+    from ..parallel.runtime import get_runtime
+    from ..spark.context import RDD
+    rt = get_runtime()
+    rank = rt.rank if rank is None else rank
+    world_size = rt.world_size if world_size is None else world_size
+    features, labels = np.asarray(features), np.asarray(labels)
+    empty = PairBlock(features[:0], labels[:0])
+    rdd = RDD([PairBlock(features, labels) if r == rank else empty for r in range(world_size)], sc)
+    rdd._pinned_partitioning = True
+    return rdd

@@ -173,6 +173,13 @@ class AsynchronousSparkWorker(_WorkerBase):
         n = x_train.shape[0]
         trainable = n > batch_size
 
+        from .parameter.client import DeviceClient
+        eng = model._native_engine() if model.device.type == 'cuda' else None
+        if eng is not None and isinstance(self.client, DeviceClient):
+            self._train_against_device_ps(model, eng, x_train, y_train, epochs, batch_size, trainable)
+            yield []
+            return
+
         if self.frequency == 'epoch':
             cfg = dict(self.train_config)
             for epoch in range(epochs):
@@ -197,3 +204,47 @@ class AsynchronousSparkWorker(_WorkerBase):
                     model.train_on_batch(x_train[lo:hi], y_train[lo:hi])
                     self.client.update_parameters(subtract_params(before, model.get_weights()))
         yield []
+
+    def _train_against_device_ps(self, model, eng, x_train, y_train, epochs, batch_size, trainable):
+        """B200 path of the pull -> train -> push loop: the replica's weights never leave the device.
+        Pull is a (peer) copy kernel straight into the engine's flat fp32/bf16 buffers, push is
+        ``red.add(master, -(before - after))`` fused with the delta computation (K7)."""
+        import torch
+        from .models import History
+        store = self.client._store()
+        before = torch.empty_like(eng.w32)
+        history = History()
+        cfg = self.train_config
+        if self.frequency == 'epoch':
+            split = float(cfg.get('validation_split') or 0.0)
+            x, y, x_val, y_val = x_train, y_train, None, None
+            if 0.0 < split < 1.0:
+                at = int(len(x_train) * (1.0 - split))
+                x, x_val, y, y_val = x_train[:at], x_train[at:], y_train[:at], y_train[at:]
+            for epoch in range(epochs):
+                store.pull_into(eng.w32, eng.w16)
+                before.copy_(eng.w32)
+                eng._weights_dirty_in_model = True
+                if trainable:
+                    eng.fit(x, y, batch_size, epoch + 1, bool(cfg.get('shuffle', True)), history, x_val, y_val,
+                            int(cfg.get('verbose', 0) or 0), initial_epoch=epoch)
+                store.push_delta(before=before, after=eng.w32)
+            self.history = history.history
+        else:
+            n = x_train.shape[0]
+            dev = eng.device
+            xd = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1).to(dev)
+            yd = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1).to(dev)
+            for epoch in range(epochs):
+                if not trainable:
+                    continue
+                for lo in range(0, n, batch_size):
+                    rows = min(batch_size, n - lo)
+                    buf = eng._buf(rows)
+                    store.pull_into(eng.w32, eng.w16)
+                    before.copy_(eng.w32)
+                    buf.x32.copy_(xd[lo:lo + rows])
+                    buf.y32.copy_(yd[lo:lo + rows])
+                    eng.train_step_device(buf)
+                    store.push_delta(before=before, after=eng.w32)
+        torch.cuda.current_stream(eng.device).synchronize()

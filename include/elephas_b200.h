@@ -72,6 +72,7 @@ typedef struct EbGemmArgs {
   float drop_p;           /* dropout rate, 0 disables                            */
   uint64_t seed;          /* Philox key                                          */
   uint64_t drop_stream;   /* Philox stream id (layer / step)                     */
+  const void* step_ptr;   /* optional device int64: stream id += 1024 * (*step_ptr) */
   void* out_bf16;         /* bf16 [M][ldo] or NULL                               */
   int32_t ldo;
   float* out_f32;         /* fp32 [M][ldo32] or NULL; out = beta*out + value      */
@@ -82,6 +83,110 @@ typedef struct EbGemmArgs {
 } EbGemmArgs;
 
 int eb_gemm_bf16(const EbGemmArgs* args, void* stream);
+
+/* ------------------------------------------------------------ elementwise helpers
+ * eb_stage_f32_to_bf16: dst[r][0..cols) = bf16(src[r][0..cols)), padding columns zeroed (input staging).
+ * eb_cast_f32_to_bf16:  flat cast (refresh of the bf16 compute copy of the weights).
+ * eb_colsum_bf16:       out[n] (+)= sum_m x[m][n]  - the bias gradient.
+ * eb_act_dropout_fwd/bwd: standalone Activation / Dropout layers (Keras layers of tests/conftest.py:12-18).
+ * eb_delta (K5):        out = before - after (reference: subtract_params, elephas/worker.py:44-45). */
+int eb_stage_f32_to_bf16(const float* src, int64_t ld_src, void* dst, int64_t ld_dst, int64_t rows, int32_t cols,
+                         void* stream);
+int eb_cast_f32_to_bf16(const float* src, void* dst, int64_t n, void* stream);
+int eb_colsum_bf16(const void* x, int64_t ld, int32_t rows, int32_t cols, float* out, int32_t accumulate,
+                   void* stream);
+int eb_act_dropout_fwd(const void* x, void* y, int64_t ld, int32_t rows, int32_t cols, int32_t act, float drop_p,
+                       uint64_t seed, uint64_t drop_stream, const void* step_ptr, void* stream);
+int eb_act_dropout_bwd(const void* dy, const void* y, void* dx, int64_t ld, int32_t rows, int32_t cols, int32_t act,
+                       float drop_p, uint64_t seed, uint64_t drop_stream, const void* step_ptr, void* stream);
+int eb_delta(const float* before, const float* after, float* out_f32, void* out_bf16, int64_t n, void* stream);
+
+/* ------------------------------------------------------------------ K4: fused loss
+ * Output activation + Keras loss + metrics + dL/dz in one pass over the last layer's pre-activations.
+ * Absorbs Keras loss / metric evaluation and their backward pass (elephas/worker.py:42,108,123;
+ * elephas/spark_model.py:291). */
+enum { EB_ACT_SOFTMAX = 100 };
+enum { EB_LOSS_MSE = 0, EB_LOSS_MAE = 1, EB_LOSS_MAPE = 2, EB_LOSS_MSLE = 3, EB_LOSS_CCE = 4, EB_LOSS_BCE = 5,
+       EB_LOSS_LOGCOSH = 6 };
+enum { EB_METRIC_NONE = 0, EB_METRIC_CATEGORICAL_ACC = 1, EB_METRIC_BINARY_ACC = 2, EB_METRIC_MAE = 3,
+       EB_METRIC_MSE = 4, EB_METRIC_MAPE = 5 };
+
+typedef struct EbLossArgs {
+  const float* z; int64_t ldz;   /* pre-activations fp32 [rows][ldz]                              */
+  const float* y; int64_t ldy;   /* targets fp32 [rows][ldy]; ldy == 0: one scalar target per row  */
+  float* out; int64_t ldo;       /* optional: activated output fp32                                */
+  void* dz; int64_t lddz;        /* optional: gradient wrt z, bf16, scaled by grad_scale           */
+  double* stats;                 /* optional: [0] += sum loss, [1..4] += sum metric_k, [7] += rows */
+  int32_t rows, cols;
+  int32_t loss, act;
+  int32_t metrics[4];
+  float grad_scale;
+} EbLossArgs;
+
+int eb_loss_fwd_bwd(const EbLossArgs* args, void* stream);
+
+/* -------------------------------------------------------------- K10: fused optimizers
+ * Keras 2.10 update rules over the flat parameter buffer; `apply` = 0 writes the step as a delta
+ * instead of applying it (input of K6 / K7). `step` is a device int64 iteration counter, advanced
+ * on the device when `advance` is set (CUDA-graph friendly). Reference: Keras optimizers reached
+ * through elephas/worker.py:29-33,88-89. */
+enum { EB_OPT_SGD = 1, EB_OPT_RMSPROP = 2, EB_OPT_ADAM = 3, EB_OPT_ADAGRAD = 4, EB_OPT_ADADELTA = 5,
+       EB_OPT_ADAMAX = 6 };
+
+typedef struct EbOptimArgs {
+  int32_t kind;
+  int64_t n;
+  float* w32; const float* g32;
+  float *slot0, *slot1, *slot2;
+  void* w16;                /* optional bf16 copy refreshed when apply != 0 */
+  void* delta_bf16; float* delta_f32;
+  int32_t apply, advance;
+  float lr, decay, momentum, rho, eps, beta1, beta2;
+  int32_t nesterov, centered, amsgrad;
+  void* step;               /* device int64 */
+} EbOptimArgs;
+
+int eb_optimizer_step(const EbOptimArgs* args, void* stream);
+
+/* ------------------------------------------- K6: fused all-reduce + update over NVLink peer memory
+ * The synchronous round of the reference (collect deltas, average, subtract:
+ * elephas/spark_model.py:220-231) as one kernel per rank. `delta[r]`, `avg[r]`, `pad[r]` are the
+ * peer-mapped buffers of rank r (r < world); `local` is 64 bytes of zero-initialised device memory
+ * private to the rank. algo: 0 auto, 1 one-shot, 2 two-shot. Must be launched by all ranks; delta
+ * buffers must be double buffered across consecutive calls. */
+typedef struct EbCommArgs {
+  const void* delta[8];
+  void* avg[8];
+  void* pad[8];
+  void* local;
+  float* w32; void* w16;
+  float* out32;             /* eb_allreduce_sum only */
+  int64_t n;
+  int32_t rank, world;
+  float scale;              /* 1/number_of_sub_models for the update, 1 for a plain sum */
+  int32_t dtype_bf16;       /* element type of delta / avg: 1 = bf16, 0 = fp32 */
+  int32_t algo, blocks;
+} EbCommArgs;
+
+int eb_allreduce_update(const EbCommArgs* args, void* stream);
+int eb_allreduce_sum(const EbCommArgs* args, void* stream);
+
+/* ------------------------------------------------ K7: device-resident parameter server
+ * master -= delta via red.global.add.f32 into (peer) HBM, pulls as vectorised (peer) loads fused
+ * with the bf16 cast, ticket lock for mode='asynchronous' (elephas/parameter/server.py:107-132,
+ * 201-218; elephas/utils/rwlock.py). ctrl: 32 bytes of zero-initialised memory next to the master. */
+int eb_ps_lock(void* ctrl, void* stream);
+int eb_ps_unlock(void* ctrl, void* stream);
+int eb_ps_push(float* master, const float* delta, const float* before, const float* after, int64_t n, void* stream);
+int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, void* stream);
+
+/* ------------------------------------------------------------ memory / IPC plumbing */
+int eb_device_malloc(void** ptr, int64_t bytes);   /* cudaMalloc + zero fill (IPC-exportable) */
+int eb_device_free(void* ptr);
+int eb_ipc_export(void* ptr, void* handle64);
+int eb_ipc_import(const void* handle64, void** ptr);
+int eb_ipc_close(void* ptr);
+int eb_enable_peer_access(int32_t peer_device);
 
 #ifdef __cplusplus
 }

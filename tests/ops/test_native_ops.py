@@ -1,0 +1,295 @@
+"""Numerics of every hand-written sm_100a kernel against a plain PyTorch fp32 reference of the same op."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from elephas_b200.models import optimizers  # noqa: E402
+
+
+@pytest.fixture(scope='module')
+def native():
+    from elephas_b200.ops import native as n
+    n.require()
+    return n
+
+
+def _bf(t):
+    return t.to(torch.bfloat16)
+
+
+def _pad(t, ld):
+    out = torch.zeros(t.shape[0], ld, dtype=t.dtype, device=t.device)
+    out[:, :t.shape[1]] = t
+    return out
+
+
+ACT = {0: lambda x: x, 1: torch.relu, 2: torch.sigmoid, 3: torch.tanh, 4: torch.nn.functional.softplus,
+       5: torch.nn.functional.softsign, 6: torch.nn.functional.elu, 7: torch.nn.functional.selu, 8: torch.exp,
+       9: lambda x: torch.clamp(0.2 * x + 0.5, 0, 1)}
+
+
+@pytest.mark.parametrize('M,N,K', [(64, 128, 784), (64, 10, 128), (128, 512, 93), (300, 200, 520), (4096, 1024, 512)])
+def test_dense_forward(native, M, N, K):
+    torch.manual_seed(0)
+    dev = 'cuda'
+    x, w, b = torch.randn(M, K, device=dev), torch.randn(N, K, device=dev) / math.sqrt(K), torch.randn(N, device=dev)
+    ldk, ldn = (K + 7) // 8 * 8, (N + 7) // 8 * 8
+    x16, w16 = _pad(_bf(x), ldk), _pad(_bf(w), ldk)
+    out = torch.zeros(M, ldn, dtype=torch.bfloat16, device=dev)
+    native.gemm(x16, w16, M, N, K, out_bf16=out, bias=b, act=1)
+    ref = torch.relu(x16[:, :K].float() @ w16[:, :K].float().t() + b)
+    assert torch.allclose(out[:, :N].float(), ref, atol=2e-2, rtol=2e-2)
+    assert torch.all(out[:, N:] == 0)
+
+
+@pytest.mark.parametrize('act', sorted(ACT))
+def test_activations_in_epilogue(native, act):
+    torch.manual_seed(act)
+    M, N, K = 128, 64, 64
+    x, w = torch.randn(M, K, device='cuda') * 0.5, torch.randn(N, K, device='cuda') * 0.2
+    x16, w16 = _bf(x), _bf(w)
+    z32 = torch.zeros(M, N, device='cuda')
+    native.gemm(x16, w16, M, N, K, out_f32=z32, act=act)
+    ref = ACT[act](x16.float() @ w16.float().t())
+    assert torch.allclose(z32, ref, atol=1e-4, rtol=1e-4)
+
+
+def test_dgrad_and_wgrad_match_autograd(native):
+    torch.manual_seed(1)
+    B, IN, OUT = 256, 200, 136
+    ld_in, ld_out = 200, 136
+    a_prev = torch.rand(B, IN, device='cuda')          # stored activation (relu output, > 0 mostly)
+    a_prev[a_prev < 0.3] = 0.0
+    w = torch.randn(OUT, IN, device='cuda') / math.sqrt(IN)
+    dz = torch.randn(B, OUT, device='cuda') * 0.1
+    a16, w16, dz16 = _bf(a_prev), _bf(w), _bf(dz)
+    # wgrad: dW = dZ^T A_prev (fp32 out)
+    dw = torch.zeros(OUT, ld_in, device='cuda')
+    native.gemm(dz16, a16, OUT, IN, B, a_mn=True, b_mn=True, out_f32=dw)
+    assert torch.allclose(dw, dz16.float().t() @ a16.float(), atol=1e-3, rtol=1e-3)
+    # dgrad with relu derivative taken from the stored output
+    dprev = torch.zeros(B, ld_in, dtype=torch.bfloat16, device='cuda')
+    native.gemm(dz16, w16, B, IN, OUT, b_mn=True, out_bf16=dprev, epi=native.EPI_ACTGRAD, act=1, aux=a16)
+    ref = (dz16.float() @ w16.float()) * (a16.float() > 0)
+    assert torch.allclose(dprev.float(), ref, atol=2e-2, rtol=2e-2)
+    # bias gradient
+    db = torch.zeros(OUT, device='cuda')
+    native.colsum_bf16(dz16, B, OUT, db)
+    assert torch.allclose(db, dz16.float().sum(0), atol=1e-3, rtol=1e-3)
+
+
+def test_dropout_epilogue_statistics_and_backward_mask(native):
+    torch.manual_seed(2)
+    M, N, K, p = 512, 256, 64, 0.2
+    x, w = torch.rand(M, K, device='cuda') + 0.1, torch.rand(N, K, device='cuda') + 0.1
+    out = torch.zeros(M, N, dtype=torch.bfloat16, device='cuda')
+    nodrop = torch.zeros_like(out)
+    native.gemm(_bf(x), _bf(w), M, N, K, out_bf16=nodrop, act=1)
+    native.gemm(_bf(x), _bf(w), M, N, K, out_bf16=out, act=1, drop_p=p, seed=123, drop_stream=5)
+    kept = out != 0
+    assert abs(kept.float().mean().item() - (1 - p)) < 0.01
+    assert torch.allclose(out[kept].float(), nodrop[kept].float() / (1 - p), rtol=2e-2)
+    # same seed/stream reproduces the mask, another stream does not
+    again = torch.zeros_like(out)
+    native.gemm(_bf(x), _bf(w), M, N, K, out_bf16=again, act=1, drop_p=p, seed=123, drop_stream=5)
+    assert torch.equal(again, out)
+    other = torch.zeros_like(out)
+    native.gemm(_bf(x), _bf(w), M, N, K, out_bf16=other, act=1, drop_p=p, seed=123, drop_stream=6)
+    assert not torch.equal(other != 0, kept)
+    # backward regenerates the same mask: gradient is zero exactly where the forward output was dropped
+    dz = torch.ones(M, 64, dtype=torch.bfloat16, device='cuda')
+    w2 = _bf(torch.ones(64, N, device='cuda'))
+    dprev = torch.zeros(M, N, dtype=torch.bfloat16, device='cuda')
+    native.gemm(dz, w2, M, N, 64, b_mn=True, out_bf16=dprev, epi=native.EPI_ACTGRAD, act=1, aux=out, drop_p=p,
+                seed=123, drop_stream=5)
+    assert torch.equal(dprev != 0, kept)
+    assert torch.allclose(dprev[kept].float(), torch.full_like(dprev[kept].float(), 64 / (1 - p)), rtol=1e-2)
+
+
+def test_stage_cast_delta_actdrop(native):
+    torch.manual_seed(3)
+    x = torch.randn(37, 93, device='cuda')
+    dst = torch.full((37, 96), 7.0, dtype=torch.bfloat16, device='cuda')
+    native.stage_f32_to_bf16(x, dst, 37, 93)
+    assert torch.equal(dst[:, :93], _bf(x)) and torch.all(dst[:, 93:] == 0)
+    flat = torch.randn(100003 // 8 * 8 + 8, device='cuda')
+    out = torch.zeros_like(flat, dtype=torch.bfloat16)
+    native.cast_f32_to_bf16(flat, out)
+    assert torch.equal(out, _bf(flat))
+    a, b = torch.randn(4099, device='cuda'), torch.randn(4099, device='cuda')
+    d32, d16 = torch.zeros(4099, device='cuda'), torch.zeros(4099, dtype=torch.bfloat16, device='cuda')
+    native.delta(a, b, out_f32=d32, out_bf16=d16)
+    assert torch.equal(d32, a - b) and torch.equal(d16, _bf(a - b))
+    h = _bf(torch.randn(64, 40, device='cuda'))
+    y = torch.zeros_like(h)
+    native.act_dropout_fwd(h, y, 64, 40, act=3, drop_p=0.5, seed=9, drop_stream=1)
+    keep = y != 0
+    assert 0.4 < keep.float().mean().item() < 0.6
+    assert torch.allclose(y[keep].float(), 2 * torch.tanh(h.float())[keep], atol=2e-2, rtol=2e-2)
+    dy, dx = _bf(torch.ones(64, 40, device='cuda')), torch.zeros_like(h)
+    native.act_dropout_bwd(dy, y, dx, 64, 40, act=3, drop_p=0.5, seed=9, drop_stream=1)
+    ref = torch.where(keep, 2 * (1 - (y.float() * 0.5) ** 2), torch.zeros_like(y.float()))
+    assert torch.allclose(dx.float(), ref, atol=2e-2, rtol=2e-2)
+
+
+LOSS_CASES = [('categorical_crossentropy', 'softmax', 10), ('binary_crossentropy', 'sigmoid', 1),
+              ('mean_squared_error', 'linear', 1), ('mean_absolute_error', 'linear', 3),
+              ('mean_squared_error', 'relu', 7), ('mean_absolute_percentage_error', 'linear', 1),
+              ('logcosh', 'tanh', 5), ('mean_squared_logarithmic_error', 'softplus', 4)]
+
+
+@pytest.mark.parametrize('loss_name,act_name,n_out', LOSS_CASES)
+def test_fused_loss_matches_autograd(native, loss_name, act_name, n_out):
+    from elephas_b200.models import activations, losses
+    torch.manual_seed(4)
+    B = 333
+    z = (torch.randn(B, n_out, device='cuda') * 1.5).requires_grad_(True)
+    if loss_name == 'categorical_crossentropy':
+        y = torch.eye(n_out, device='cuda')[torch.randint(0, n_out, (B,), device='cuda')]
+    elif loss_name == 'binary_crossentropy':
+        y = torch.randint(0, 2, (B, n_out), device='cuda').float()
+    else:
+        y = torch.rand(B, n_out, device='cuda') * 2 + 0.5
+    act_fn = activations.get(act_name)[1]
+    a = act_fn(z)
+    per_sample = losses.get(loss_name)(y, a)
+    per_sample.mean().backward()
+    ldz = (n_out + 3) // 4 * 4
+    zbuf = torch.zeros(B, ldz, device='cuda')
+    zbuf[:, :n_out] = z.detach()
+    out = torch.zeros(B, n_out, device='cuda')
+    ldd = (n_out + 7) // 8 * 8
+    dz = torch.zeros(B, ldd, dtype=torch.bfloat16, device='cuda')
+    stats = torch.zeros(8, dtype=torch.float64, device='cuda')
+    mets = [native.METRIC_IDS['categorical_accuracy' if act_name == 'softmax' else 'binary_accuracy'],
+            native.METRIC_IDS['mean_absolute_error'], native.METRIC_IDS['mean_squared_error'],
+            native.METRIC_IDS['mean_absolute_percentage_error']]
+    native.loss_fwd_bwd(zbuf, y, B, n_out, native.LOSS_IDS[loss_name], native.ACT_IDS[act_name], out=out, dz=dz,
+                        stats=stats, metrics=mets, grad_scale=1.0 / B)
+    s = stats.cpu().numpy()
+    assert s[7] == B
+    assert torch.allclose(out, a.detach(), atol=1e-5, rtol=1e-5)
+    assert abs(s[0] / B - per_sample.mean().item()) < 1e-4 * max(1.0, abs(per_sample.mean().item()))
+    assert torch.allclose(dz[:, :n_out].float(), z.grad, atol=2e-4, rtol=2e-2)
+    if act_name == 'softmax':
+        assert abs(s[1] / B - (a.argmax(1) == y.argmax(1)).float().mean().item()) < 1e-6
+    else:
+        assert abs(s[1] / B - ((a > 0.5).float() == y).float().mean().item()) < 1e-6
+    assert abs(s[2] / B - (a - y).abs().mean().item()) < 1e-4
+    assert abs(s[3] / B - ((a - y) ** 2).mean().item()) < 1e-3
+
+
+OPT_CASES = [('SGD', {}), ('SGD', {'momentum': 0.9}), ('SGD', {'momentum': 0.9, 'nesterov': True, 'decay': 1e-2}),
+             ('RMSprop', {}), ('RMSprop', {'momentum': 0.5, 'centered': True}), ('Adam', {}),
+             ('Adam', {'amsgrad': True, 'decay': 1e-3}), ('Adagrad', {'learning_rate': 0.1}),
+             ('Adadelta', {'learning_rate': 1.0}), ('Adamax', {})]
+
+
+@pytest.mark.parametrize('name,cfg', OPT_CASES)
+def test_fused_optimizers_match_python(native, name, cfg):
+    torch.manual_seed(5)
+    n = 4096 + 24
+    opt = optimizers.deserialize({'class_name': name, 'config': dict(cfg)})
+    w_ref = torch.randn(n, dtype=torch.float64)
+    w32 = w_ref.float().cuda()
+    w16 = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    c = opt._config
+    init0 = c.get('initial_accumulator_value', 0.0) if name == 'Adagrad' else 0.0
+    slots = [torch.full((n,), init0 if i == 0 else 0.0, device='cuda') for i in range(3)]
+    step = torch.zeros(1, dtype=torch.int64, device='cuda')
+    for it in range(5):
+        g = torch.randn(n, dtype=torch.float64)
+        opt.apply_gradients([w_ref], [g])
+        native.optimizer_step(native.OPT_IDS[name], n, g.float().cuda(), step, w32=w32, w16=w16, slots=slots,
+                              lr=c['learning_rate'], decay=c.get('decay', 0.0), momentum=c.get('momentum', 0.0),
+                              rho=c.get('rho', 0.9), eps=c.get('epsilon', 1e-7), beta1=c.get('beta_1', 0.9),
+                              beta2=c.get('beta_2', 0.999), nesterov=c.get('nesterov', False),
+                              centered=c.get('centered', False), amsgrad=c.get('amsgrad', False))
+    assert int(step.item()) == 5
+    assert torch.allclose(w32.cpu().double(), w_ref, atol=2e-5, rtol=2e-4)
+    assert torch.equal(w16, w32.to(torch.bfloat16))
+
+
+def test_optimizer_delta_mode_leaves_weights(native):
+    n = 1024
+    w32 = torch.randn(n, device='cuda')
+    w0 = w32.clone()
+    g = torch.randn(n, device='cuda')
+    d16 = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    step = torch.zeros(1, dtype=torch.int64, device='cuda')
+    native.optimizer_step(native.OPT_IDS['SGD'], n, g, step, w32=w32, delta_bf16=d16, apply=False, lr=0.5)
+    assert torch.equal(w32, w0) and torch.equal(d16, (0.5 * g).to(torch.bfloat16))
+
+
+def test_allreduce_update_single_rank(native):
+    """world=1 exercises the kernel's barrier (trivially), reduction, scaling, update and bf16 refresh."""
+    torch.manual_seed(6)
+    n = 1 << 16
+    w32 = torch.randn(n, device='cuda')
+    w0 = w32.clone()
+    w16 = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    pad = torch.zeros(64, dtype=torch.int32, device='cuda')
+    local = torch.zeros(16, dtype=torch.int32, device='cuda')
+    for it, dtype in enumerate((torch.bfloat16, torch.float32, torch.bfloat16)):
+        d = torch.randn(n, device='cuda').to(dtype)
+        avg = torch.zeros(n, dtype=dtype, device='cuda')
+        native.allreduce_update([d.data_ptr()], [pad.data_ptr()], local, n, 0, 1, 1.0, dtype == torch.bfloat16, w32,
+                                w16=w16, avg_ptrs=[avg.data_ptr()], algo=1 if it < 2 else 2)
+        w0 = w0 - d.float()
+        torch.cuda.synchronize()
+        assert torch.allclose(w32, w0, atol=1e-6)
+        assert torch.equal(w16, w32.to(torch.bfloat16))
+    assert int(local[0].item()) == 3
+
+
+def test_emulated_four_rank_reduction(native):
+    """The reduction/scale/update arithmetic for N=4 'ranks' whose buffers live on one GPU: one launch per
+    emulated rank, each seeing all four delta buffers (flags pre-published so that no launch waits on another)."""
+    torch.manual_seed(7)
+    n, world = 1 << 14, 4
+    deltas = [torch.randn(n, device='cuda').to(torch.bfloat16) for _ in range(world)]
+    pads = [torch.full((64,), 1 << 30, dtype=torch.int32, device='cuda') for _ in range(world)]
+    mean = sum(d.float() for d in deltas) / world
+    for r in range(world):
+        w32 = torch.ones(n, device='cuda')
+        local = torch.zeros(16, dtype=torch.int32, device='cuda')
+        native.allreduce_update([d.data_ptr() for d in deltas], [p.data_ptr() for p in pads], local, n, r, world,
+                                1.0 / world, True, w32, algo=1)
+        torch.cuda.synchronize()
+        assert torch.allclose(w32, 1.0 - mean, atol=1e-6)
+
+
+@pytest.mark.parametrize('locked', [True, False])
+def test_parameter_server_kernels(native, locked):
+    torch.manual_seed(8)
+    n = 50000
+    master = torch.randn(n, device='cuda')
+    m0 = master.clone()
+    ctrl = torch.zeros(8, dtype=torch.int32, device='cuda')
+    streams = [torch.cuda.Stream() for _ in range(4)]
+    deltas = [torch.randn(n, device='cuda') for _ in range(4)]
+    torch.cuda.synchronize()
+    for s, d in zip(streams, deltas):
+        with torch.cuda.stream(s):
+            for _ in range(5):
+                before = torch.zeros(n, device='cuda')
+                native.ps_push(master, ctrl, before=before, after=-d, locked=locked)  # delta = before - after = d
+    torch.cuda.synchronize()
+    expect = m0 - 5 * sum(deltas)
+    assert torch.allclose(master, expect, atol=1e-4)   # red.add is atomic per element: exact in both modes
+    dst32, dst16 = torch.zeros(n, device='cuda'), torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    native.ps_pull(master, ctrl, dst32, dst16, locked=locked)
+    torch.cuda.synchronize()
+    assert torch.equal(dst32, master) and torch.equal(dst16, master.to(torch.bfloat16))
+    if locked:
+        assert int(ctrl[1].item()) == 21 and int(ctrl[2].item()) == 21 and int(ctrl[0].item()) % 2 == 0
+
+
+def test_launch_counter_moves(native):
+    before = native.launch_count()
+    native.cast_f32_to_bf16(torch.zeros(64, device='cuda'), torch.zeros(64, dtype=torch.bfloat16, device='cuda'))
+    assert native.launch_count() == before + 1

@@ -138,7 +138,6 @@ def run_ours(args, rt):
     from elephas_b200.models import model_from_json
     from elephas_b200.ops import engine as _engine
     from elephas_b200.ops import native
-    from elephas_b200.parallel.sync_fast import _InputFeeder, _SyncRun  # noqa: F401
     from elephas_b200.spark import SparkContext
     from elephas_b200.spark_model import SparkModel
     from elephas_b200.utils.rdd_utils import to_sharded_rdd

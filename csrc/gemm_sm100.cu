@@ -52,6 +52,7 @@ struct GemmDev {
   float* out_f32;
   int ldo32;
   float beta;
+  int bf16_from_f32;
   int tiles_m, tiles_n;
 };
 
@@ -100,7 +101,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   uint64_t* tempty_bar = tfull_bar + kAccStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + kAccStages);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: provably warp-uniform, so role dispatch compiles to uniform branches
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
   const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
   const bool leader = cta_rank == 0;
@@ -125,7 +127,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   tc_fence_before();
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
   const int num_tiles = p.tiles_m * p.tiles_n;
   const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
@@ -134,7 +136,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
+    if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       for (int t = first_tile; t < num_tiles; t += tile_step) {
@@ -178,7 +180,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       // K-major:  8-row groups are 1024 B apart (SBO); LBO is unused with swizzling (canonical value 16 B).
       // MN-major: 8 k-rows of one 64-wide block are 1024 B apart (SBO); 64-wide blocks are 8192 B apart (LBO).
       const uint32_t a_lbo = p.a_mn ? 64 * BLOCK_K * 2 : 16, b_lbo = p.b_mn ? 64 * BLOCK_K * 2 : 16;
-      const uint32_t a_kstep = p.a_mn ? UMMA_K * 128 : UMMA_K * 2, b_kstep = p.b_mn ? UMMA_K * 128 : UMMA_K * 2;
+      const uint32_t a_kstep = (p.a_mn ? UMMA_K * 128 : UMMA_K * 2) >> 4, b_kstep = (p.b_mn ? UMMA_K * 128 : UMMA_K * 2) >> 4;
+      // Descriptors differ between stages / k-steps only in the 14-bit start-address field (smem < 256 KB, so
+      // adding to the low word never carries out of it): build them once, then add 16-byte-unit offsets.
+      const uint64_t desc_a0 = make_smem_desc_sw128(smem_u32(smem_a), a_lbo, 1024);
+      const uint64_t desc_b0 = make_smem_desc_sw128(smem_u32(smem_b), b_lbo, 1024);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -190,15 +196,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
-          if (lane == 0) {
-            const uint32_t a_addr = smem_u32(smem_a + stage * Cfg::A_STAGE);
-            const uint32_t b_addr = smem_u32(smem_b + stage * Cfg::B_STAGE);
+          if (elect_one()) {
+            const uint64_t da0 = desc_a0 + static_cast<uint32_t>(stage * (Cfg::A_STAGE >> 4));
+            const uint64_t db0 = desc_b0 + static_cast<uint32_t>(stage * (Cfg::B_STAGE >> 4));
 #pragma unroll
-            for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
-              const uint64_t da = make_smem_desc_sw128(a_addr + k * a_kstep, a_lbo, 1024);
-              const uint64_t db = make_smem_desc_sw128(b_addr + k * b_kstep, b_lbo, 1024);
-              umma_bf16<CG>(tmem_d, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
-            }
+            for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
+              umma_bf16<CG>(tmem_d, da0 + k * a_kstep, db0 + k * b_kstep, idesc, (kb | k) != 0 ? 1u : 0u);
             umma_commit<CG>(&empty_bar[stage]);                      // smem slot reusable once these MMAs retire
             if (kb == num_kb - 1) umma_commit<CG>(&tfull_bar[acc]);  // accumulator complete
           }
@@ -306,11 +309,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
               }
               *reinterpret_cast<float4*>(orow + j) = o;
+              if (p.bf16_from_f32) { x[j] = o.x; x[j + 1] = o.y; x[j + 2] = o.z; x[j + 3] = o.w; }
             }
           } else {
 #pragma unroll
             for (int j = 0; j < CHUNK; ++j)
-              if (n0 + j < p.N) orow[j] = (p.beta != 0.f ? p.beta * orow[j] : 0.f) + x[j];
+              if (n0 + j < p.N) {
+                const float o = (p.beta != 0.f ? p.beta * orow[j] : 0.f) + x[j];
+                orow[j] = o;
+                if (p.bf16_from_f32) x[j] = o;
+              }
           }
         }
         if (p.out_bf16 != nullptr) {
@@ -477,6 +485,7 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
   p.step_ptr = static_cast<const long long*>(a.step_ptr);
   p.out_bf16 = static_cast<__nv_bfloat16*>(a.out_bf16); p.ldo = a.ldo;
   p.out_f32 = a.out_f32; p.ldo32 = a.ldo32; p.beta = a.beta;
+  p.bf16_from_f32 = a.bf16_from_f32;
   p.tiles_m = p.tiles_n = 0;
 
   int bn, cg;

@@ -108,7 +108,36 @@ __global__ void __launch_bounds__(256) optimizer_kernel(const OptimDev p) {
   }
   __syncthreads();
   const float lr_t = sh_lr[0], lr_adam = sh_lr[1];
-  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < p.n;
+  // four consecutive elements per thread per iteration: 16-byte accesses on every stream
+  const long n4 = p.n / 4;
+  for (long q = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; q < n4;
+       q += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float4 g = reinterpret_cast<const float4*>(p.g32)[q];
+    float st[4];
+    st[0] = step_value(p, 4 * q + 0, g.x, lr_t, lr_adam);
+    st[1] = step_value(p, 4 * q + 1, g.y, lr_t, lr_adam);
+    st[2] = step_value(p, 4 * q + 2, g.z, lr_t, lr_adam);
+    st[3] = step_value(p, 4 * q + 3, g.w, lr_t, lr_adam);
+    if (p.apply) {
+      float4 w = reinterpret_cast<float4*>(p.w32)[q];
+      w.x -= st[0]; w.y -= st[1]; w.z -= st[2]; w.w -= st[3];
+      reinterpret_cast<float4*>(p.w32)[q] = w;
+      if (p.w16) {
+        uint2 o;
+        o.x = pack_bf16x2(w.x, w.y);
+        o.y = pack_bf16x2(w.z, w.w);
+        reinterpret_cast<uint2*>(p.w16)[q] = o;
+      }
+    }
+    if (p.delta16) {
+      uint2 o;
+      o.x = pack_bf16x2(st[0], st[1]);
+      o.y = pack_bf16x2(st[2], st[3]);
+      reinterpret_cast<uint2*>(p.delta16)[q] = o;
+    }
+    if (p.delta32) reinterpret_cast<float4*>(p.delta32)[q] = make_float4(st[0], st[1], st[2], st[3]);
+  }
+  for (long i = n4 * 4 + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < p.n;
        i += static_cast<long>(gridDim.x) * blockDim.x) {
     const float st = step_value(p, i, p.g32[i], lr_t, lr_adam);
     if (p.apply) {
@@ -150,7 +179,11 @@ extern "C" int eb_optimizer_step(const EbOptimArgs* a, void* stream) {
   p.beta1 = a->beta1; p.beta2 = a->beta2;
   p.nesterov = a->nesterov; p.centered = a->centered; p.amsgrad = a->amsgrad;
   p.step = reinterpret_cast<const long long*>(a->step);
-  long blocks = (a->n + 256 * 4 - 1) / (256 * 4);
+  if ((reinterpret_cast<uintptr_t>(a->g32) & 15) || (a->w32 && (reinterpret_cast<uintptr_t>(a->w32) & 15)) ||
+      (a->w16 && (reinterpret_cast<uintptr_t>(a->w16) & 7)) || (a->delta_bf16 && (reinterpret_cast<uintptr_t>(a->delta_bf16) & 7)) ||
+      (a->delta_f32 && (reinterpret_cast<uintptr_t>(a->delta_f32) & 15)))
+    return fail("eb_optimizer_step: buffers must be 16-byte aligned (bf16 buffers 8-byte)");
+  long blocks = (a->n / 4 + 255) / 256 + 1;
   const long cap = static_cast<long>(num_sms()) * 8;
   if (blocks > cap) blocks = cap;
   cudaStream_t s = static_cast<cudaStream_t>(stream);

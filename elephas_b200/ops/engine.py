@@ -25,6 +25,7 @@ Weights live in one flat fp32 master buffer plus an index-identical bf16 compute
 """
 import math
 import os
+import threading
 
 import numpy as np
 import torch
@@ -34,6 +35,7 @@ from ..parallel.flat import FlatLayout
 from . import native
 
 _round8 = lambda v: (v + 7) // 8 * 8  # noqa: E731
+_CAPTURE_LOCK = threading.Lock()  # one CUDA-graph capture at a time per process
 
 _METRIC_FOR_FN = {'categorical_accuracy': 'categorical_accuracy', 'binary_accuracy': 'binary_accuracy',
                   'mean_absolute_error': 'mean_absolute_error', 'mean_squared_error': 'mean_squared_error',
@@ -222,6 +224,7 @@ class MLPEngine:
         self.y_cols = ops[-1].out_dim
         self.use_graphs = os.environ.get('ELEPHAS_B200_GRAPHS', '1') != '0'
         self._buffers = {}
+        self._graph_launches = {}
         self._weights_dirty_in_model = False  # True: engine holds newer weights than the Model tensors
         self.seed = int(torch.randint(0, 2 ** 62, (1,)).item())
         self.stats = torch.zeros(8, dtype=torch.float64, device=dev)
@@ -353,30 +356,54 @@ class MLPEngine:
                             metrics=self.metric_ids, grad_scale=1.0 / float(grad_rows or rows),
                             ldy=buf.y32.stride(0))
 
+    def _fused_sgd(self):
+        """Plain SGD (no momentum, no decay): the weight update rides in the wgrad GEMM epilogue."""
+        if not self.trainable or self.opt_kind != native.OPT_IDS['SGD']:
+            return False
+        cfg = self.model.optimizer._config
+        return not cfg.get('momentum') and not cfg.get('decay')
+
     def _backward(self, buf):
         B = buf.B
+        fused = self._fused_sgd()
+        lr = float(self.model.optimizer._config['learning_rate']) if fused else 0.0
         for op in reversed(self.ops):
             dz = buf.dz[op.index]
             a_prev = buf.x16 if op.index == 0 else buf.acts[op.index - 1]
-            gw = self.g32[op.w_seg.offset:]
-            # dW[out, in] = dZ^T[out, B] x A_prev[B, in]: both operands MN-major, fp32 out into the flat grads
-            native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out, ldb=op.ld_in,
-                        out_f32=gw, ldo32=op.ld_in)
-            native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
             if op.index > 0:
                 prev = self.ops[op.index - 1]
                 # dZ_prev[B, in] = (dZ[B, out] x W[out, in]) * act'(A_prev) * dropout mask
+                # (before the wgrad of this layer: the fused-SGD epilogue overwrites W)
                 native.gemm(dz, self._w16(op), B, op.in_dim, op.out_dim, b_mn=True, lda=op.ld_out, ldb=op.ld_in,
                             out_bf16=buf.dz[prev.index], ldo=prev.ld_out, epi=native.EPI_ACTGRAD,
                             act=native.ACT_IDS[prev.act], aux=a_prev, ldaux=prev.ld_out, drop_p=prev.drop_p,
                             seed=self.seed, drop_stream=prev.index, step_ptr=self.step)
+            off = op.w_seg.offset
+            # dW[out, in] = dZ^T[out, B] x A_prev[B, in]: both operands MN-major
+            if not fused:
+                native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
+                            ldb=op.ld_in, out_f32=self.g32[off:], ldo32=op.ld_in)
+            elif self.delta_target is None:
+                # W32 <- W32 - lr * dW and W16 <- bf16(W32) in the epilogue: no gradient buffer, no extra pass
+                native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
+                            ldb=op.ld_in, out_f32=self.w32[off:], ldo32=op.ld_in, beta=1.0, alpha=-lr,
+                            out_bf16=self.w16[off:], ldo=op.ld_in, bf16_from_f32=True)
+            else:
+                # synchronous data parallel: the step lr * dW goes straight into the peer-mapped delta buffer
+                native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
+                            ldb=op.ld_in, alpha=lr, out_bf16=self.delta_target[off:], ldo=op.ld_in)
+            native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
 
     def _optimizer(self):
         cfg = self.model.optimizer._config
         delta = self.delta_target
-        native.optimizer_step(self.opt_kind, self.layout.numel, self.g32, self.step, w32=self.w32,
-                              w16=self.w16, slots=self.slots, delta_bf16=delta, apply=delta is None, advance=True,
-                              lr=cfg['learning_rate'], decay=cfg.get('decay', 0.0) or 0.0,
+        # with the fused-SGD epilogue only the vector range (biases) is left for the optimizer kernel
+        lo = self.layout.matrix_end if self._fused_sgd() else 0
+        n = self.layout.numel - lo
+        native.optimizer_step(self.opt_kind, n, self.g32[lo:], self.step, w32=self.w32[lo:],
+                              w16=self.w16[lo:], slots=[s[lo:] if s is not None else None for s in self.slots],
+                              delta_bf16=delta[lo:] if delta is not None else None, apply=delta is None,
+                              advance=True, lr=cfg['learning_rate'], decay=cfg.get('decay', 0.0) or 0.0,
                               momentum=cfg.get('momentum', 0.0) or 0.0, rho=cfg.get('rho', 0.9),
                               eps=cfg.get('epsilon', 1e-7), beta1=cfg.get('beta_1', 0.9),
                               beta2=cfg.get('beta_2', 0.999), nesterov=cfg.get('nesterov', False),
@@ -399,30 +426,40 @@ class MLPEngine:
         key = (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0)
         graph = buf.graphs.get(key)
         if graph is None:
-            # warm-up outside capture (module loading, function attributes), then record
-            stream = torch.cuda.Stream(self.device)
-            stream.wait_stream(torch.cuda.current_stream(self.device))
-            saved = self._snapshot_state() if is_train else None
-            with torch.cuda.stream(stream):
-                body()
-            torch.cuda.current_stream(self.device).wait_stream(stream)
-            if saved is not None:
-                self._restore_state(saved)
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph, stream=stream, capture_error_mode='thread_local'):
-                body()
-            buf.graphs[key] = graph
-            if saved is not None:
-                self._restore_state(saved)
+            with _CAPTURE_LOCK:
+                graph = self._record(buf, key, body, is_train)
         graph.replay()
+        native.count_replay(self._graph_launches.get(id(graph), 0))
+
+    def _record(self, buf, key, body, is_train):
+        # warm-up outside capture (module loading, function attributes), then record
+        stream = torch.cuda.Stream(self.device)
+        stream.wait_stream(torch.cuda.current_stream(self.device))
+        saved = self._snapshot_state() if is_train else None
+        with torch.cuda.stream(stream):
+            body()
+        torch.cuda.current_stream(self.device).wait_stream(stream)
+        if saved is not None:
+            self._restore_state(saved)
+        graph = torch.cuda.CUDAGraph()
+        launched = native.launch_count()
+        with torch.cuda.graph(graph, stream=stream, capture_error_mode='thread_local'):
+            body()
+        # kernels recorded into the graph: every replay launches this many native kernels
+        self._graph_launches[id(graph)] = native.launch_count() - launched
+        buf.graphs[key] = graph
+        if saved is not None:
+            self._restore_state(saved)
+        return graph
 
     def _snapshot_state(self):
-        torch.cuda.synchronize(self.device)
+        # stream-level syncs only: another worker thread may be capturing a graph on its own stream
+        torch.cuda.current_stream(self.device).synchronize()
         return (self.w32.clone(), self.w16.clone(), [s.clone() if s is not None else None for s in self.slots],
                 self.step.clone(), self.stats.clone())
 
     def _restore_state(self, saved):
-        torch.cuda.synchronize(self.device)
+        torch.cuda.current_stream(self.device).synchronize()
         w32, w16, slots, step, stats = saved
         self.w32.copy_(w32)
         self.w16.copy_(w16)
@@ -479,7 +516,8 @@ class MLPEngine:
             yd = torch.as_tensor(np.ascontiguousarray(y, dtype=np.float32)).reshape(n, -1).to(dev, non_blocking=True)
             names = self.model.metrics_names
             for epoch in range(initial_epoch, epochs):
-                order = torch.randperm(n, device=dev) if shuffle else None
+                # CPU generator: the CUDA generator may be in graph-capture mode in another worker thread
+                order = torch.randperm(n).to(dev, non_blocking=True) if shuffle else None
                 self.stats.zero_()
                 for start in range(0, n, batch_size):
                     rows = min(batch_size, n - start)

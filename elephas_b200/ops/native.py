@@ -39,7 +39,7 @@ class GemmArgs(ctypes.Structure):
                 ('bias', c_void_p), ('aux', c_void_p), ('ldaux', c_int32),
                 ('drop_p', c_float), ('seed', c_uint64), ('drop_stream', c_uint64), ('step_ptr', c_void_p),
                 ('out_bf16', c_void_p), ('ldo', c_int32),
-                ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float),
+                ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float), ('bf16_from_f32', c_int32),
                 ('block_n', c_int32), ('cta_group', c_int32)]
 
 
@@ -136,14 +136,24 @@ def _stream(device=None):
     return c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
+_replayed = [0]
+
+
+def count_replay(n: int):
+    """Kernels launched by a CUDA-graph replay do not pass through the library's launch wrappers;
+    the engine reports them here so that ``launch_count`` stays the number of native kernels run."""
+    _replayed[0] += int(n)
+
+
 def launch_count() -> int:
-    return int(load().eb_launch_count()) if _lib is not None or available() else 0
+    base = int(load().eb_launch_count()) if _lib is not None or available() else 0
+    return base + _replayed[0]
 
 
 # ----------------------------------------------------------------------- GEMM
 def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=None, ldo=None, out_f32=None,
          ldo32=None, beta=0.0, alpha=1.0, epi=EPI_FWD, act=0, bias=None, aux=None, ldaux=None, drop_p=0.0, seed=0,
-         drop_stream=0, step_ptr=None, block_n=0, cta_group=0):
+         drop_stream=0, step_ptr=None, block_n=0, cta_group=0, bf16_from_f32=False):
     """``C[M,N] = epilogue(A x B^T)`` on the tcgen05 GEMM (see ``EbGemmArgs`` for the operand layouts)."""
     g = GemmArgs()
     g.M, g.N, g.K = int(M), int(N), int(K)
@@ -160,6 +170,7 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
     g.out_f32 = out_f32.data_ptr() if out_f32 is not None else None
     g.ldo32 = int(ldo32 if ldo32 is not None else (out_f32.stride(0) if out_f32 is not None else 0))
     g.beta = float(beta)
+    g.bf16_from_f32 = int(bool(bf16_from_f32))
     g.block_n, g.cta_group = int(block_n), int(cta_group)
     _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
 

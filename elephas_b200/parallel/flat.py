@@ -7,7 +7,8 @@ pointer instead of a Python loop over a list of arrays.
 
 Segment rules: weights appear in Keras order; a Dense kernel is stored ``[out, ld]`` with
 ``ld = round_up(in, 8)`` (zero padding, so rows satisfy the 16-byte TMA stride rule in bf16); every
-segment starts on a 64-element boundary.
+segment starts on a 64-element boundary; Dense kernels
+are stored first, all other weights after them (``matrix_end`` marks the boundary).
 """
 import numpy as np
 import torch
@@ -20,7 +21,7 @@ def _round_up(x, m):
 
 
 class Segment:
-    __slots__ = ('offset', 'rows', 'cols', 'ld', 'layer', 'index', 'shape')
+    __slots__ = ('offset', 'rows', 'cols', 'ld', 'layer', 'index', 'shape', '_is_matrix')
 
     def __init__(self, offset, rows, cols, ld, layer, index, shape):
         self.offset, self.rows, self.cols, self.ld = offset, rows, cols, ld
@@ -34,18 +35,28 @@ class Segment:
 class FlatLayout:
     def __init__(self, model):
         from ..models.layers import Dense
-        self.segments = []
-        offset = 0
+        entries = []
         for layer, idx, w in model._weight_entries():
             shape = tuple(w.shape)
             if isinstance(layer, Dense) and idx == 0:
                 rows, cols = shape
                 ld = _round_up(cols, 8)
+                is_matrix = True
             else:
                 rows, cols = 1, int(np.prod(shape)) if shape else 1
                 ld = cols
-            self.segments.append(Segment(offset, rows, cols, ld, layer, idx, shape))
-            offset = _round_up(offset + rows * ld, ALIGN)
+                is_matrix = False
+            entries.append(Segment(0, rows, cols, ld, layer, idx, shape))
+            entries[-1]._is_matrix = is_matrix
+        # storage order: all Dense kernels first, then everything else (biases, BN statistics ...), so that
+        # "the matrices" and "the vectors" are two contiguous ranges (the fused SGD path updates the matrices
+        # inside the wgrad GEMM epilogue and runs the optimizer kernel over the vector range only).
+        offset = 0
+        for seg in [e for e in entries if e._is_matrix] + [e for e in entries if not e._is_matrix]:
+            seg.offset = offset
+            offset = _round_up(offset + seg.rows * seg.ld, ALIGN)
+        self.segments = entries  # Keras order
+        self.matrix_end = max([_round_up(e.offset + e.span, ALIGN) for e in entries if e._is_matrix] + [0])
         self.numel = max(offset, ALIGN)
 
     def view(self, flat, seg):

@@ -96,7 +96,8 @@ class _InputFeeder:
     def start_epoch(self):
         dev = self.eng.device
         if self.shuffle:
-            self.order = torch.randperm(self.n, device=dev if self.mode == 'device' else 'cpu')
+            order = torch.randperm(self.n)  # CPU generator (safe while another thread captures a CUDA graph)
+            self.order = order.to(dev, non_blocking=True) if self.mode == 'device' else order
         else:
             self.order = None
         if self.mode == 'stream':

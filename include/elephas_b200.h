@@ -78,6 +78,7 @@ typedef struct EbGemmArgs {
   float* out_f32;         /* fp32 [M][ldo32] or NULL; out = beta*out + value      */
   int32_t ldo32;
   float beta;
+  int32_t bf16_from_f32;  /* out_bf16 = bf16(final fp32 value) instead of bf16(alpha*acc): fused SGD weight update */
   int32_t block_n;        /* 0 = auto, else 16/32/64/128/256                     */
   int32_t cta_group;      /* 0 = auto, else 1 or 2 (CTA pair, UMMA M=256)        */
 } EbGemmArgs;

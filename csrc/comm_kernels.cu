@@ -26,6 +26,8 @@
 #include <cuda_runtime.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "../include/elephas_b200.h"
 #include "host.h"
 #include "ptx.cuh"
@@ -387,6 +389,71 @@ extern "C" int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, i
   ps_pull_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
       master, dst_f32, static_cast<__nv_bfloat16*>(dst_bf16), n);
   EB_LAUNCH_OK("ps_pull_kernel");
+  return 0;
+}
+
+// ------------------------------------------------------------------ allocation-free entry point
+// Scratch of eb_allreduce_update_noalloc: one copy per GPU that loads this library, resident until the
+// process exits. Layout: [0,256) signal pad, [256,512) kernel counters, [512, ...) averaged-delta buffer.
+constexpr long kNoAllocMaxElems = 1l << 20;  // largest n accepted (fp32 elements fill the buffer exactly)
+constexpr long kNoAllocAvgOffset = 512;
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocAvgOffset + kNoAllocMaxElems * 4];
+
+namespace eb {
+static void* g_noalloc_ptr[64] = {nullptr};  // device address of the array above, per CUDA device ordinal
+static std::mutex g_noalloc_mutex;
+
+// In host code `g_noalloc_scratch` is only a handle for the runtime, not an address a kernel can use:
+// ask the runtime for the device address once per device (with that device current) and cache it.
+static int noalloc_scratch_address(unsigned char** out) {
+  int dev = 0;
+  EB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail("eb_allreduce_update_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> guard(g_noalloc_mutex);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    EB_CUDA_OK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = static_cast<unsigned char*>(g_noalloc_ptr[dev]);
+  return 0;
+}
+}  // namespace eb
+
+extern "C" int eb_allreduce_update_noalloc(const void* delta, int64_t n, int32_t dtype_bf16, float scale, float* w32,
+                                           void* w16, void* stream) {
+  if (delta == nullptr || w32 == nullptr) return fail("eb_allreduce_update_noalloc: delta and w32 are required");
+  if (n <= 0) return 0;
+  if (n > kNoAllocMaxElems)
+    return fail("eb_allreduce_update_noalloc: n = %lld exceeds the built-in scratch capacity of %ld elements; "
+                "use eb_allreduce_update with caller-provided buffers for larger payloads",
+                (long long)n, kNoAllocMaxElems);
+  if (n % 8) return fail("eb_allreduce_update_noalloc: n must be a multiple of 8 (got %lld)", (long long)n);
+  if ((reinterpret_cast<uintptr_t>(delta) & 15) || (reinterpret_cast<uintptr_t>(w32) & 15) ||
+      (w16 && (reinterpret_cast<uintptr_t>(w16) & 15)))
+    return fail("eb_allreduce_update_noalloc: delta, w32 and w16 must be 16-byte aligned");
+  unsigned char* scratch = nullptr;
+  if (noalloc_scratch_address(&scratch)) return 1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  uint32_t* local = reinterpret_cast<uint32_t*>(scratch + 256);
+  // The array keeps whatever the previous call left. The epoch word (local[0]) and the pad flags are
+  // monotonic on purpose; the two block counters must be zero when the kernel starts.
+  EB_CUDA_OK(cudaMemsetAsync(local + 1, 0, 2 * sizeof(uint32_t), s));
+  CommDev p;
+  for (int i = 0; i < kMaxRanks; ++i) { p.delta[i] = nullptr; p.avg[i] = nullptr; p.pad[i] = nullptr; }
+  p.delta[0] = delta;
+  p.avg[0] = scratch + kNoAllocAvgOffset;
+  p.pad[0] = reinterpret_cast<uint32_t*>(scratch);
+  p.local = local;
+  p.w32 = w32; p.w16 = static_cast<__nv_bfloat16*>(w16); p.out32 = nullptr;
+  p.n = n; p.rank = 0; p.world = 1; p.scale = scale;
+  int blocks = num_sms();
+  const long work = (n / 8 + 511) / 512;
+  if (blocks > work) blocks = static_cast<int>(work);
+  if (blocks < 1) blocks = 1;
+  if (dtype_bf16) allreduce_twoshot_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(p);
+  else allreduce_twoshot_kernel<float><<<blocks, 512, 0, s>>>(p);
+  EB_LAUNCH_OK("allreduce_twoshot_kernel(noalloc)");
   return 0;
 }
 

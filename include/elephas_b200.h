@@ -172,6 +172,31 @@ typedef struct EbCommArgs {
 int eb_allreduce_update(const EbCommArgs* args, void* stream);
 int eb_allreduce_sum(const EbCommArgs* args, void* stream);
 
+/* Allocation-free form of eb_allreduce_update for ONE rank (world = 1). This entry point has no
+ * counterpart in the reference; it exists for hosts that are not allowed to allocate device memory at the
+ * time they need the update: a serving or training process that has already handed all of the GPU's
+ * memory to its own pool (a cudaMalloc there fails or fragments the pool), or a loop with a latency
+ * budget that cannot absorb the device-wide synchronisation a cudaMalloc / cudaFree implies. The regular
+ * entry point needs three caller-allocated buffers besides its operands (signal pad, counters, averaged
+ * delta); here they live in one array compiled into the library (EB_NOALLOC_MAX_ELEMS elements of
+ * averaged-delta space, about 4 MiB, held by every GPU that loads the library until the process ends).
+ * The function itself calls no cudaMalloc / cudaFree and no allocating library routine.
+ *
+ *   w32[i] -= scale * delta[i]  and, when w16 is given,  w16[i] = bf16(w32[i])      for i < n
+ *
+ * delta: n elements, bf16 if dtype_bf16 else fp32. n must be a multiple of 8 and at most
+ * EB_NOALLOC_MAX_ELEMS; larger n is rejected with an error (use eb_allreduce_update). Results are those of
+ * eb_allreduce_update with world = 1, algo = 2.
+ *
+ * The first call on each device looks up the array's device address (cudaGetSymbolAddress, that device
+ * must be current); make that first call outside of any stream capture. All calls on a device share the
+ * one array: it keeps the previous call's contents (the function re-zeroes the counters that must start
+ * at zero), and two calls that overlap on the GPU - different streams, or several host threads - race on
+ * it. Issue them on one stream, or order them with events. */
+#define EB_NOALLOC_MAX_ELEMS (1 << 20)
+int eb_allreduce_update_noalloc(const void* delta, int64_t n, int32_t dtype_bf16, float scale, float* w32, void* w16,
+                                void* stream);
+
 /* ------------------------------------------------ K7: device-resident parameter server
  * master -= delta via red.global.add.f32 into (peer) HBM, pulls as vectorised (peer) loads fused
  * with the bf16 cast, ticket lock for mode='asynchronous' (elephas/parameter/server.py:107-132,

@@ -20,6 +20,10 @@ def pytest_configure(config):
 
 def pytest_collection_modifyitems(config, items):
     import torch
+    # test_zz_no_alloc.py runs after everything else (directories such as tests/utils sort behind it otherwise)
+    last = [it for it in items if it.fspath.basename == 'test_zz_no_alloc.py']
+    if last:
+        items[:] = [it for it in items if it.fspath.basename != 'test_zz_no_alloc.py'] + last
     if torch.cuda.is_available():
         return
     skip = pytest.mark.skip(reason="no CUDA device")

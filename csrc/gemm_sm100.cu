@@ -30,7 +30,8 @@ namespace eb {
 constexpr int BLOCK_M = 128;
 constexpr int BLOCK_K = 64;  // 64 bf16 = one 128-byte swizzle atom
 constexpr int UMMA_K = 16;
-constexpr int kGemmThreads = 192;
+constexpr int kEpiWarps = 8;                       // two warps per TMEM lane quarter, each takes half the columns
+constexpr int kGemmThreads = 64 + 32 * kEpiWarps;  // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
 constexpr int kAccStages = 2;
 constexpr int kGroupM = 8;  // tile rasterisation: 8 m-tiles share each B tile through L2
 
@@ -40,6 +41,7 @@ struct GemmDev {
   float alpha;
   int epi, act;
   const float* bias;
+  int bias_vec;  // bias pointer is 16-byte aligned: float4 loads
   const __nv_bfloat16* aux;
   int ldaux;
   float drop_p;
@@ -116,7 +118,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
     for (int i = 0; i < kAccStages; ++i) {
       mbar_init(&tfull_bar[i], 1);        // one tcgen05.commit
-      mbar_init(&tempty_bar[i], CG * 4);  // one arrival per epilogue warp of every CTA in the group
+      mbar_init(&tempty_bar[i], CG * kEpiWarps);  // one arrival per epilogue warp of every CTA in the group
     }
     fence_barrier_init();
   }
@@ -213,7 +215,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     }
   } else {
     // ---------------------------------------------------------------- epilogue
-    const int quarter = warp & 3;  // TMEM lane quarter this warp may access
+    const int quarter = warp & 3;          // TMEM lane quarter this warp may access (hardware: warp id % 4)
+    const int half = (warp - 2) >> 2;      // which half of the tile's column chunks this warp handles
     const int row = quarter * 32 + lane;
     int acc = 0;
     uint32_t acc_phase = 0;
@@ -229,12 +232,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       constexpr int CHUNK = BN >= 32 ? 32 : 16;
+      constexpr int NCHUNK = BN / CHUNK;
+      // chunks [c_lo, c_hi) belong to this warp; with a single chunk the second warp of the quarter only
+      // takes part in the barrier protocol
+      constexpr int PER = (NCHUNK + 1) / 2;
+      const int c_lo = half * PER, c_hi = min(NCHUNK, c_lo + PER);
+      if (c_lo >= c_hi) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CG == 1) mbar_arrive(&tempty_bar[acc]); else mbar_arrive_leader(&tempty_bar[acc]);
+        }
+      }
 #pragma unroll 1
-      for (int c = 0; c < BN / CHUNK; ++c) {
+      for (int c = c_lo; c < c_hi; ++c) {
         uint32_t v[32];
         if constexpr (CHUNK == 32) tmem_ld_32x32(taddr + c * 32, v); else tmem_ld_32x16(taddr + c * 16, v);
         tmem_ld_wait();
-        if (c == BN / CHUNK - 1) {
+        if (c == c_hi - 1) {
           // all of this warp's accumulator reads are complete: hand the TMEM stage back to the MMA warp
           tc_fence_before();
           __syncwarp();
@@ -250,9 +265,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         const bool full = (n0 + CHUNK <= p.N);
         if (p.epi == EB_EPI_FWD) {
           if (p.bias != nullptr) {
+            if (full && p.bias_vec) {
+              const float4* b4 = reinterpret_cast<const float4*>(p.bias + n0);
 #pragma unroll
-            for (int j = 0; j < CHUNK; ++j)
-              if (full || n0 + j < p.N) x[j] += __ldg(p.bias + n0 + j);
+              for (int j = 0; j < CHUNK; j += 4) {
+                const float4 b = __ldg(b4 + (j >> 2));
+                x[j] += b.x; x[j + 1] += b.y; x[j + 2] += b.z; x[j + 3] += b.w;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j)
+                if (full || n0 + j < p.N) x[j] += __ldg(p.bias + n0 + j);
+            }
           }
           if (p.act != ACT_LINEAR) {
 #pragma unroll
@@ -478,6 +502,7 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
   p.a_mn = a.a_mn ? 1 : 0; p.b_mn = a.b_mn ? 1 : 0;
   p.alpha = a.alpha; p.epi = a.epi; p.act = a.act;
   p.bias = a.bias;
+  p.bias_vec = (reinterpret_cast<uintptr_t>(a.bias) & 15) == 0 ? 1 : 0;
   p.aux = static_cast<const __nv_bfloat16*>(a.aux); p.ldaux = a.ldaux;
   p.drop_p = a.drop_p; p.drop_thresh = dropout_threshold(a.drop_p);
   p.drop_scale = a.drop_p > 0.f ? 1.f / (1.f - a.drop_p) : 1.f;

@@ -1,0 +1,136 @@
+"""Multi-GPU checks, run under torch.distributed.run with one rank per GPU (see test_gpu_spmd.py):
+fused P2P all-reduce + update (one-shot and two-shot), the synchronous fast path at both frequencies, the
+device-resident parameter server across processes (CUDA IPC), the socket PS across processes, and the generic
+(torch autograd) path with the P2P sum all-reduce."""
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
+os.environ.setdefault('SPARK_LOCAL_IP', '127.0.0.1')
+
+from elephas.spark_model import SparkModel  # noqa: E402
+from elephas.utils.rdd_utils import to_simple_rdd  # noqa: E402
+from elephas_b200.models import SGD, Adam, Dense, Sequential, zoo  # noqa: E402
+from elephas_b200.ops import native  # noqa: E402
+from elephas_b200.parallel import get_runtime  # noqa: E402
+from elephas_b200.parallel.symm import SymmetricMemory, all_reduce_sum  # noqa: E402
+from elephas_b200.spark import SparkContext  # noqa: E402
+from tests.conftest import make_mnist_like  # noqa: E402
+
+rt = get_runtime()
+W, R = rt.world_size, rt.rank
+sc = SparkContext(master='local[%d]' % W)
+port = int(sys.argv[1]) if len(sys.argv) > 1 else 7300
+
+
+def log(msg):
+    if R == 0:
+        print(msg, flush=True)
+
+
+def same_on_all_ranks(arrays, tol=0.0):
+    digest = float(sum(np.abs(a).astype(np.float64).sum() for a in arrays))
+    all_d = rt.all_gather_object(digest)
+    assert max(all_d) - min(all_d) <= tol * max(1.0, abs(all_d[0])), all_d
+    return digest
+
+
+# ---- 1. raw fused all-reduce + update kernels over peer memory -------------------------------------
+for algo, n, dtype in ((1, 1 << 16, torch.bfloat16), (2, 1 << 22, torch.bfloat16), (2, 1 << 20, torch.float32),
+                       (1, 1 << 12, torch.float32)):
+    item = 2 if dtype == torch.bfloat16 else 4
+    mem = SymmetricMemory(rt, {'delta0': n * item, 'delta1': n * item, 'avg': n * item, 'pad': 256})
+    local = torch.zeros(16, dtype=torch.int32, device=rt.device)
+    w32 = torch.ones(n, device=rt.device)
+    w16 = torch.zeros(n, dtype=torch.bfloat16, device=rt.device)
+    expect = torch.ones(n, device=rt.device)
+    for it in range(4):
+        name = 'delta%d' % (it % 2)
+        g = torch.Generator(device='cpu').manual_seed(100 * it + R)
+        d = torch.randn(n, generator=g).to(dtype)
+        mem.local(name, dtype, n).copy_(d.to(rt.device))
+        parts = [torch.randn(n, generator=torch.Generator().manual_seed(100 * it + r)).to(dtype).float() for r in range(W)]
+        mean = sum(parts) / W
+        if algo == 2 and dtype == torch.bfloat16:
+            mean = mean.to(torch.bfloat16).float()  # the averaged slice travels as bf16 in the two-shot variant
+        expect -= mean.to(rt.device)
+        native.allreduce_update(mem.ptrs(name), mem.ptrs('pad'), local, n, R, W, 1.0 / W, dtype == torch.bfloat16, w32,
+                                w16=w16, avg_ptrs=mem.ptrs('avg'), algo=algo, device=rt.device)
+    torch.cuda.synchronize()
+    err = (w32 - expect).abs().max().item()
+    assert err < 1e-5, (algo, n, dtype, err)
+    assert torch.equal(w16, w32.to(torch.bfloat16))
+    rt.barrier()
+    mem.close()
+    log("allreduce_update algo=%d n=%d %s ok (max err %.2e)" % (algo, n, dtype, err))
+
+# ---- 2. P2P sum all-reduce used by the generic path --------------------------------------------------
+flat = torch.full((1000,), float(R + 1), device=rt.device)
+out = all_reduce_sum(rt, flat)
+assert torch.allclose(out, torch.full_like(out, W * (W + 1) / 2.0)), out[:4]
+log("all_reduce_sum ok")
+
+# ---- 3. SparkModel matrix on GPUs ---------------------------------------------------------------------
+x, y, xt, yt = make_mnist_like(256 * W * 2, 300)
+CASES = [('synchronous', None, 'batch'), ('synchronous', None, 'epoch'), ('asynchronous', 'nvlink', 'epoch'),
+         ('asynchronous', 'nvlink', 'batch'), ('hogwild', 'nvlink', 'epoch'), ('asynchronous', 'socket', 'epoch')]
+for i, (mode, ps, freq) in enumerate(CASES):
+    torch.manual_seed(R)  # different init per rank on purpose: fit must start every replica from rank 0's weights
+    model = zoo.mnist_mlp()
+    model.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode=mode, frequency=freq, parameter_server_mode=ps, num_workers=W, port=port + i)
+    t0 = time.time()
+    sm.fit(to_simple_rdd(sc, x, y), epochs=3, batch_size=64, verbose=0, validation_split=0.1)
+    dt = time.time() - t0
+    weights = sm.master_network.get_weights()
+    same_on_all_ranks(weights, tol=1e-6)
+    ev = sm.evaluate(xt, yt)
+    local_ev = sm.master_network.evaluate(xt, yt)
+    preds = sm.predict(xt)
+    assert len(preds) == len(xt)
+    assert abs(ev[0] - local_ev[0]) < 0.01 and abs(ev[1] - local_ev[1]) < 0.01, (ev, local_ev)
+    assert ev[1] > 0.6, (mode, ps, freq, ev)
+    if mode == 'synchronous':
+        assert len(sm.training_histories) == W and all('loss' in h for h in sm.training_histories)
+    log("SparkModel %-12s %-7s %-5s ok: loss %.4f acc %.3f  (%.2fs)" % (mode, ps, freq, ev[0], ev[1], dt))
+
+# ---- 4. synchronous batch == single-process large-batch SGD (exact data-parallel equivalence) ---------
+torch.manual_seed(123)
+ref = Sequential([Dense(32, input_dim=784, activation='relu'), Dense(10, activation='softmax')])
+ref.compile(SGD(lr=0.1), 'categorical_crossentropy')
+w0 = ref.get_weights()
+dist = Sequential([Dense(32, input_dim=784, activation='relu'), Dense(10, activation='softmax')])
+dist.compile(SGD(lr=0.1), 'categorical_crossentropy')
+dist.set_weights(w0)
+n_per = 128
+xs, ys = x[:n_per * W], y[:n_per * W]
+sm = SparkModel(dist, mode='synchronous', frequency='batch', num_workers=W)
+sm.fit(to_simple_rdd(sc, xs, ys), epochs=1, batch_size=64, shuffle=False)
+# oracle: every step averages the W ranks' batch gradients == one SGD step on the concatenated batch
+ref.to(rt.device)
+for s in range(n_per // 64):
+    idx = np.concatenate([np.arange(r * n_per + s * 64, r * n_per + (s + 1) * 64) for r in range(W)])
+    ref.train_on_batch(xs[idx], ys[idx])
+for a, b in zip(sm.master_network.get_weights(), ref.get_weights()):
+    assert np.allclose(a, b, atol=3e-3), np.abs(a - b).max()
+log("synchronous/batch matches large-batch SGD oracle")
+
+# ---- 5. generic (torch autograd) path on GPUs: custom activation -------------------------------------
+def custom_activation(t):
+    return torch.sigmoid(t) + 1
+
+
+m = Sequential([Dense(16, input_dim=784, activation=custom_activation), Dense(10, activation='softmax')])
+m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
+sm = SparkModel(m, mode='synchronous', frequency='epoch', num_workers=W, custom_objects={'custom_activation': custom_activation})
+sm.fit(to_simple_rdd(sc, x, y), epochs=2, batch_size=64)
+same_on_all_ranks(sm.master_network.get_weights(), tol=1e-6)
+log("generic torch path with custom activation ok: acc %.3f" % sm.evaluate(xt, yt)[1])
+
+rt.barrier()
+log("ALL OK (world=%d)" % W)
+rt.shutdown()

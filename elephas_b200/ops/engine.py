@@ -231,6 +231,9 @@ class MLPEngine:
         self._pinned_stats = torch.zeros(8, dtype=torch.float64).pin_memory()
         self.step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.delta_target = None  # (bf16 tensor) when the optimizer must emit deltas instead of applying
+        self.comm_hook = None     # callable(lo, n): a delta range is ready (synchronous data parallel)
+        self.comm_join = None     # callable(): make the compute stream wait for all communication of the step
+        self._in_warmup = False
         if self.trainable:
             self.loss_id, self.metric_ids = spec
             self.opt_kind = opt_kind
@@ -363,13 +366,49 @@ class MLPEngine:
         cfg = self.model.optimizer._config
         return not cfg.get('momentum') and not cfg.get('decay')
 
+    def _opt_kwargs(self):
+        cfg = self.model.optimizer._config
+        return dict(lr=cfg['learning_rate'], decay=cfg.get('decay', 0.0) or 0.0,
+                    momentum=cfg.get('momentum', 0.0) or 0.0, rho=cfg.get('rho', 0.9), eps=cfg.get('epsilon', 1e-7),
+                    beta1=cfg.get('beta_1', 0.9), beta2=cfg.get('beta_2', 0.999), nesterov=cfg.get('nesterov', False),
+                    centered=cfg.get('centered', False), amsgrad=cfg.get('amsgrad', False))
+
+    def _optimizer_range(self, lo, n, advance):
+        """Optimizer kernel over flat elements [lo, lo+n): applies the step, or - in delta mode - writes it as
+        a bf16 delta into the communication buffer."""
+        delta = self.delta_target
+        native.optimizer_step(self.opt_kind, n, self.g32[lo:], self.step, w32=self.w32[lo:], w16=self.w16[lo:],
+                              slots=[sl[lo:] if sl is not None else None for sl in self.slots],
+                              delta_bf16=delta[lo:] if delta is not None else None, apply=delta is None,
+                              advance=advance, **self._opt_kwargs())
+
+    def _emit(self, lo, n):
+        """Delta range [lo, lo+n) is complete: hand it to the communication hook (per-bucket fused all-reduce)."""
+        # (skipped during the pre-capture warm-up run: collectives must execute exactly once per step on
+        # every rank, and a rank without a batch at this step does not run a warm-up)
+        if self.comm_hook is not None and self.delta_target is not None and not self._in_warmup:
+            self.comm_hook(lo, n)
+
+    def bucket_ranges(self):
+        """The order in which delta ranges are emitted during a step: one bucket per Dense kernel, last layer
+        first, then one bucket with all vectors (ranks without a batch replay exactly this sequence)."""
+        out = []
+        for op in reversed(self.ops):
+            off = op.w_seg.offset
+            out.append((off, (op.w_seg.span + 63) // 64 * 64))
+        out.append((self.layout.matrix_end, self.layout.numel - self.layout.matrix_end))
+        return out
+
     def _backward(self, buf):
         B = buf.B
         fused = self._fused_sgd()
+        delta_mode = self.delta_target is not None
         lr = float(self.model.optimizer._config['learning_rate']) if fused else 0.0
         for op in reversed(self.ops):
             dz = buf.dz[op.index]
             a_prev = buf.x16 if op.index == 0 else buf.acts[op.index - 1]
+            off = op.w_seg.offset
+            span = (op.w_seg.span + 63) // 64 * 64
             if op.index > 0:
                 prev = self.ops[op.index - 1]
                 # dZ_prev[B, in] = (dZ[B, out] x W[out, in]) * act'(A_prev) * dropout mask
@@ -378,12 +417,13 @@ class MLPEngine:
                             out_bf16=buf.dz[prev.index], ldo=prev.ld_out, epi=native.EPI_ACTGRAD,
                             act=native.ACT_IDS[prev.act], aux=a_prev, ldaux=prev.ld_out, drop_p=prev.drop_p,
                             seed=self.seed, drop_stream=prev.index, step_ptr=self.step)
-            off = op.w_seg.offset
             # dW[out, in] = dZ^T[out, B] x A_prev[B, in]: both operands MN-major
             if not fused:
                 native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
                             ldb=op.ld_in, out_f32=self.g32[off:], ldo32=op.ld_in)
-            elif self.delta_target is None:
+                if delta_mode:
+                    self._optimizer_range(off, span, advance=False)
+            elif not delta_mode:
                 # W32 <- W32 - lr * dW and W16 <- bf16(W32) in the epilogue: no gradient buffer, no extra pass
                 native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
                             ldb=op.ld_in, out_f32=self.w32[off:], ldo32=op.ld_in, beta=1.0, alpha=-lr,
@@ -392,22 +432,22 @@ class MLPEngine:
                 # synchronous data parallel: the step lr * dW goes straight into the peer-mapped delta buffer
                 native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
                             ldb=op.ld_in, alpha=lr, out_bf16=self.delta_target[off:], ldo=op.ld_in)
+            if delta_mode:
+                self._emit(off, span)  # this layer's delta can travel while the earlier layers are computed
             native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
 
     def _optimizer(self):
-        cfg = self.model.optimizer._config
-        delta = self.delta_target
-        # with the fused-SGD epilogue only the vector range (biases) is left for the optimizer kernel
-        lo = self.layout.matrix_end if self._fused_sgd() else 0
+        if self.delta_target is not None or self._fused_sgd():
+            # matrices were handled layer by layer (fused epilogue or per-layer delta): only vectors are left
+            lo = self.layout.matrix_end
+        else:
+            lo = 0
         n = self.layout.numel - lo
-        native.optimizer_step(self.opt_kind, n, self.g32[lo:], self.step, w32=self.w32[lo:],
-                              w16=self.w16[lo:], slots=[s[lo:] if s is not None else None for s in self.slots],
-                              delta_bf16=delta[lo:] if delta is not None else None, apply=delta is None,
-                              advance=True, lr=cfg['learning_rate'], decay=cfg.get('decay', 0.0) or 0.0,
-                              momentum=cfg.get('momentum', 0.0) or 0.0, rho=cfg.get('rho', 0.9),
-                              eps=cfg.get('epsilon', 1e-7), beta1=cfg.get('beta_1', 0.9),
-                              beta2=cfg.get('beta_2', 0.999), nesterov=cfg.get('nesterov', False),
-                              centered=cfg.get('centered', False), amsgrad=cfg.get('amsgrad', False))
+        self._optimizer_range(lo, n, advance=True)
+        if self.delta_target is not None:
+            self._emit(lo, n)
+        if self.comm_join is not None and self.delta_target is not None and not self._in_warmup:
+            self.comm_join()
 
     def _train_body(self, buf):
         self._forward(buf, training=True)
@@ -436,8 +476,12 @@ class MLPEngine:
         stream = torch.cuda.Stream(self.device)
         stream.wait_stream(torch.cuda.current_stream(self.device))
         saved = self._snapshot_state() if is_train else None
-        with torch.cuda.stream(stream):
-            body()
+        self._in_warmup = True
+        try:
+            with torch.cuda.stream(stream):
+                body()
+        finally:
+            self._in_warmup = False
         torch.cuda.current_stream(self.device).wait_stream(stream)
         if saved is not None:
             self._restore_state(saved)

@@ -21,6 +21,8 @@ copies every batch host->device on a side stream, double buffered, overlapping t
 device->host copy, one step delayed so it never stalls the GPU). ``keep_context=True`` keeps engine,
 CUDA graphs and peer-mapped buffers alive on the ``SparkModel`` for the next ``fit`` call.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -165,6 +167,7 @@ class SyncContext:
         if self.mem is not None and self.dtype_bf16 == dtype_bf16:
             return
         if self.mem is not None:
+            self.eng.invalidate_graphs()  # recorded graphs hold pointers into the old buffers
             self.mem.close()
         n = self.eng.layout.numel
         item = 2 if dtype_bf16 else 4
@@ -174,18 +177,54 @@ class SyncContext:
         tdt = torch.bfloat16 if dtype_bf16 else torch.float32
         self.delta = [self.mem.local('delta0', tdt, n), self.mem.local('delta1', tdt, n)]
         self.flip = 0
+        # first launch of both collective kernels outside of any graph capture (zero delta: weights unchanged)
+        for algo in (1, 2):
+            native.allreduce_update(self.mem.ptrs('delta0'), self.mem.ptrs('pad'), self.comm_local, 1024,
+                                    self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, dtype_bf16, self.eng.w32,
+                                    w16=self.eng.w16, avg_ptrs=self.mem.ptrs('avg'), algo=algo, blocks=2,
+                                    device=self.rt.device)
+        torch.cuda.synchronize(self.rt.device)
 
-    def _allreduce_update(self):
-        name = 'delta%d' % self.flip
-        self.flip ^= 1
+    def _allreduce_update(self, lo=0, n=None, stream=None, blocks=0):
+        """Fused all-reduce + update of flat elements [lo, lo+n) of the current delta buffer."""
         eng = self.eng
-        native.allreduce_update(self.mem.ptrs(name), self.mem.ptrs('pad'), self.comm_local, eng.layout.numel,
-                                self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32,
-                                w16=eng.w16, avg_ptrs=self.mem.ptrs('avg'), device=self.rt.device)
+        n = eng.layout.numel - lo if n is None else n
+        name = 'delta%d' % self.flip
+        item = 2 if self.dtype_bf16 else 4
+        native.allreduce_update(self.mem.ptrs(name, lo * item), self.mem.ptrs('pad'), self.comm_local, n,
+                                self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32[lo:],
+                                w16=eng.w16[lo:], avg_ptrs=self.mem.ptrs('avg', lo * item), blocks=blocks,
+                                device=self.rt.device)
         eng._weights_dirty_in_model = True
+
+    # -- per-bucket communication overlapped with the rest of the backward pass -------------------------
+    def _install_hooks(self):
+        eng, dev = self.eng, self.rt.device
+        self.comm_stream = torch.cuda.Stream(dev)
+        blocks = int(os.environ.get('ELEPHAS_B200_COMM_BLOCKS', '74'))
+
+        def hook(lo, n):
+            cur = torch.cuda.current_stream(dev)
+            ready = torch.cuda.Event()
+            ready.record(cur)
+            self.comm_stream.wait_event(ready)
+            with torch.cuda.stream(self.comm_stream):
+                self._allreduce_update(lo, n, blocks=blocks)
+
+        def join():
+            done = torch.cuda.Event()
+            done.record(self.comm_stream)
+            torch.cuda.current_stream(dev).wait_event(done)
+
+        eng.comm_hook, eng.comm_join = hook, join
+
+    def _remove_hooks(self):
+        self.eng.comm_hook = self.eng.comm_join = None
 
     def close(self):
         self.eng.delta_target = None
+        self._remove_hooks()
+        self.eng.invalidate_graphs()
         if self.mem is not None:
             self.mem.close()
             self.mem = None
@@ -194,12 +233,17 @@ class SyncContext:
     def _step(self, buf, per_batch, have_batch):
         eng = self.eng
         if per_batch:
+            eng.delta_target = self.delta[self.flip]
             if have_batch:
-                eng.delta_target = self.delta[self.flip]
-                eng.train_step_device(buf)
+                eng.train_step_device(buf)  # the per-bucket all-reduces are part of the (graph-captured) step
             else:
+                # no batch left on this rank: contribute zero deltas through the same sequence of collectives
                 self.delta[self.flip].zero_()
-            self._allreduce_update()
+                for lo, n in eng.bucket_ranges():
+                    eng.comm_hook(lo, n)
+                eng.comm_join()
+            self.flip ^= 1
+            eng._weights_dirty_in_model = True
         elif have_batch:
             eng.delta_target = None
             eng.train_step_device(buf)
@@ -237,6 +281,10 @@ class SyncContext:
             self._sync_start()
             if distributed:
                 self._setup_comm(dtype_bf16=per_batch)
+            if per_batch:
+                self._install_hooks()
+            else:
+                self._remove_hooks()
             steps_local = -(-len(x) // bs) if trainable else 0
             steps = steps_local
             if distributed:
@@ -284,6 +332,7 @@ class SyncContext:
                     native.delta(before, eng.w32, out_f32=self.delta[self.flip])
                     eng.w32.copy_(before)
                     self._allreduce_update()
+                    self.flip ^= 1
                 if x_val is not None and len(x_val) and logs:
                     val = eng.evaluate(x_val, y_val)
                     logs.update({'val_' + k: v for k, v in zip(names, val)})
@@ -311,6 +360,7 @@ class SyncContext:
             per_batch = rt.distributed
             if per_batch:
                 self._setup_comm(dtype_bf16=True)
+                self._install_hooks()
             feeder = _InputFeeder(eng, x, y, bs, input_mode, False)
             feeder.start_epoch()
             torch.cuda.synchronize(rt.device)

@@ -130,12 +130,9 @@ __global__ void __launch_bounds__(512) allreduce_oneshot_kernel(const CommDev p)
   for (long g = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < n8;
        g += static_cast<long>(gridDim.x) * blockDim.x) {
     float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    // fixed summation order 0..world-1 on every rank: all replicas compute bit-identical results
 #pragma unroll 1
-    for (int k = 0; k < p.world; ++k) {
-      int peer = p.rank + k;
-      if (peer >= p.world) peer -= p.world;
-      accumulate8<T>(p.delta[peer], g * 8, s);
-    }
+    for (int peer = 0; peer < p.world; ++peer) accumulate8<T>(p.delta[peer], g * 8, s);
 #pragma unroll
     for (int j = 0; j < 8; ++j) s[j] *= p.scale;
     if (MODE == 0) {

@@ -23,6 +23,7 @@ Weights live in one flat fp32 master buffer plus an index-identical bf16 compute
 (``parallel/flat.py``); ``export_weights`` / ``import_weights`` sync them with the Keras-facing
 ``Model`` tensors lazily.
 """
+import gc
 import math
 import os
 import threading
@@ -487,8 +488,17 @@ class MLPEngine:
             self._restore_state(saved)
         graph = torch.cuda.CUDAGraph()
         launched = native.launch_count()
-        with torch.cuda.graph(graph, stream=stream, capture_error_mode='thread_local'):
-            body()
+        # No garbage collection while capturing: a collected CUDAGraph / stream / event of an earlier fit would be
+        # destroyed from inside the capture, which CUDA forbids and which invalidates the capture.
+        gc.collect()
+        gc_was_enabled = gc.isenabled()
+        gc.disable()
+        try:
+            with torch.cuda.graph(graph, stream=stream, capture_error_mode='thread_local'):
+                body()
+        finally:
+            if gc_was_enabled:
+                gc.enable()
         # kernels recorded into the graph: every replay launches this many native kernels
         self._graph_launches[id(graph)] = native.launch_count() - launched
         buf.graphs[key] = graph

@@ -62,7 +62,11 @@ for algo, n, dtype in ((1, 1 << 16, torch.bfloat16), (2, 1 << 22, torch.bfloat16
                                 w16=w16, avg_ptrs=mem.ptrs('avg'), algo=algo, device=rt.device)
     torch.cuda.synchronize()
     err = (w32 - expect).abs().max().item()
-    assert err < 1e-5, (algo, n, dtype, err)
+    # two-shot bf16: the slice owner rounds its fp32 sum (accumulated starting at its own rank) to bf16 once;
+    # the oracle sums in rank order, so a value may land on the neighbouring bf16 (1 ulp of an O(1) number)
+    tol = 4e-3 if (algo == 2 and dtype == torch.bfloat16 and W > 2) else 1e-5
+    assert err < tol, (algo, n, dtype, err)
+    same_on_all_ranks([w32.cpu().numpy()])  # replicas must stay bit-identical
     assert torch.equal(w16, w32.to(torch.bfloat16))
     rt.barrier()
     mem.close()

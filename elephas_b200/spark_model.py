@@ -338,6 +338,8 @@ class SparkModel:
             for _ in range(epochs):
                 for b in range(steps):
                     current = averaged_round([w.train_batch(current, b) for w in workers])
+                for w in workers:
+                    w.end_batch_epoch()
         local_hist = [(i, (w.history if w.trainable else None)) for w, (i, _) in zip(workers, mine)]
         gathered = [h for chunk in rt.all_gather_object(local_hist) for h in chunk]
         self._training_histories.extend(h for _, h in sorted(gathered, key=lambda t: t[0]))

@@ -83,6 +83,7 @@ class SparkWorker(_WorkerBase):
                          custom_objects, device)
         self.x_train = self.y_train = None
         self.history = {}
+        self._epoch_acc = {}
 
     # ---------------------------------------------------- reference protocol
     def train(self, data_iterator):
@@ -140,10 +141,21 @@ class SparkWorker(_WorkerBase):
         if self.trainable and start < self.x_train.shape[0]:
             stats = self.model.train_on_batch(self.x_train[start:start + bs], self.y_train[start:start + bs])
             stats = stats if isinstance(stats, list) else [stats]
+            n = min(bs, self.x_train.shape[0] - start)
             for k, v in zip(self.model.metrics_names, stats):
                 self.history.setdefault('batch_' + k, []).append(v)
+                acc = self._epoch_acc.setdefault(k, [0.0, 0])
+                acc[0] += v * n
+                acc[1] += n
         after = self.model.get_weights()
         return subtract_params(before, after)
+
+    def end_batch_epoch(self):
+        """Close an epoch of ``train_batch`` calls: sample-weighted epoch means go to ``history['loss']`` ..."""
+        for k, (total, n) in self._epoch_acc.items():
+            if n:
+                self.history.setdefault(k, []).append(total / n)
+        self._epoch_acc = {}
 
 
 class AsynchronousSparkWorker(_WorkerBase):

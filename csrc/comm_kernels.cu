@@ -60,6 +60,18 @@ __device__ __forceinline__ void red_add_f32_sys(float* p, float a) {
   asm volatile("red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(p), "f"(a) : "memory");
 }
 
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Watchdog: every cross-GPU wait gives up after this long, records the fact in a status word the host reads
+// back, and lets the kernel finish (with meaningless results) instead of hanging the GPU - a peer that died or
+// never launched must not take the whole node down (the reference has no failure detection at all).
+constexpr unsigned long long kBarrierTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;
+constexpr unsigned long long kLockTimeoutNs = 10ull * 1000ull * 1000ull * 1000ull;
+
 struct CommDev {
   const void* delta[kMaxRanks];  // every rank's delta buffer for this epoch (peer mapped)
   void* avg[kMaxRanks];          // two-shot: every rank's averaged-delta buffer (peer mapped)
@@ -77,7 +89,17 @@ struct CommDev {
 __device__ __forceinline__ void wait_flags(const CommDev& p, int slot0, uint32_t e) {
   if (threadIdx.x < p.world) {
     const uint32_t* f = p.pad[p.rank] + slot0 + threadIdx.x;
+    unsigned long long t0 = 0;
+    uint32_t spins = 0;
     while (ld_acquire_sys(f) < e) {
+      if ((++spins & 0x3FFu) == 0) {
+        const unsigned long long now = global_timer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > kBarrierTimeoutNs) {
+          atomicExch(p.local + 8, 1u + threadIdx.x);  // status word: 1 + rank of the peer that never arrived
+          break;
+        }
+      }
     }
   }
   __syncthreads();
@@ -228,9 +250,20 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev p)
 
 // ------------------------------------------------------------------ parameter server
 __global__ void ps_lock_kernel(uint32_t* ctrl) {
-  // ctrl[1]: next ticket, ctrl[2]: now serving, ctrl[0]: sequence word (odd while a writer is inside)
+  // ctrl[1]: next ticket, ctrl[2]: now serving, ctrl[0]: sequence word (odd while a writer is inside),
+  // ctrl[4]: watchdog status (non-zero: a waiter gave up after kLockTimeoutNs and went ahead unlocked)
   const uint32_t ticket = atomicAdd_system(ctrl + 1, 1u);
+  unsigned long long t0 = 0;
+  uint32_t spins = 0;
   while (ld_acquire_sys(ctrl + 2) != ticket) {
+    if ((++spins & 0x3FFu) == 0) {
+      const unsigned long long now = global_timer_ns();
+      if (t0 == 0) t0 = now;
+      else if (now - t0 > kLockTimeoutNs) {
+        atomicExch_system(ctrl + 4, 1u);
+        break;
+      }
+    }
   }
   atomicAdd_system(ctrl + 0, 1u);
   __threadfence_system();

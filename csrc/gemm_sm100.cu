@@ -18,6 +18,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "../include/elephas_b200.h"
@@ -56,6 +58,7 @@ struct GemmDev {
   float beta;
   int bf16_from_f32;
   int tiles_m, tiles_n;
+  int full_work, num_work;  // work items: [0, full_work) whole tiles, then the tail tiles as two half-N items each
 };
 
 template <int BN, int CG>
@@ -64,7 +67,7 @@ struct GemmCfg {
   static constexpr int A_STAGE = BLOCK_M * BLOCK_K * 2;
   static constexpr int B_STAGE = B_ROWS * BLOCK_K * 2;
   static constexpr int STAGE = A_STAGE + B_STAGE;
-  static constexpr int STAGES_RAW = (196 * 1024) / STAGE;
+  static constexpr int STAGES_RAW = (225 * 1024) / STAGE;  // 227 KB per CTA minus barriers and alignment slack
   static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int TMEM_COLS = (kAccStages * BN <= 32)    ? 32
                                    : (kAccStages * BN <= 64)  ? 64
@@ -87,7 +90,30 @@ __device__ __forceinline__ void tile_coords(int t, int tiles_m, int tiles_n, int
   tn = r / gsize;
 }
 
-template <int BN, int CG>
+// Work item -> tile coordinates. The last, partially filled wave of a persistent grid leaves most SMs idle;
+// when at most half of the CTA groups would get a tile there, each tail tile is issued as two half-width
+// (BN/2) work items instead, so the tail wave is shorter and busier.
+struct WorkItem {
+  int tm, tn, n_off, width;
+};
+
+template <int BN>
+__device__ __forceinline__ WorkItem decode_work(int w, const GemmDev& p) {
+  WorkItem it;
+  int tile = w;
+  it.n_off = 0;
+  it.width = BN;
+  if (w >= p.full_work) {
+    const int s = w - p.full_work;
+    tile = p.full_work + (s >> 1);
+    it.n_off = (s & 1) * (BN / 2);
+    it.width = BN / 2;
+  }
+  tile_coords(tile, p.tiles_m, p.tiles_n, it.tm, it.tn);
+  return it;
+}
+
+template <int BN, int CG, int MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                  const GemmDev p) {
@@ -106,7 +132,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   // warp index through a shuffle: provably warp-uniform, so role dispatch compiles to uniform branches
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
   const int lane = threadIdx.x & 31;
-  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  // cluster = MC CTA groups stacked along M that share (multicast) the B tile; cta_rank is the rank inside the group
+  const uint32_t cluster_rank = (CG * MC > 1) ? cluster_ctarank() : 0u;
+  const uint32_t cta_rank = cluster_rank & (CG - 1);
+  const uint32_t group = cluster_rank / CG;
   const bool leader = cta_rank == 0;
 
   if (warp == 0 && lane == 0) {
@@ -114,7 +143,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     tma_prefetch_desc(&map_b);
     for (int i = 0; i < Cfg::STAGES; ++i) {
       mbar_init(&full_bar[i], CG);  // leader: arrive.expect_tx; peer CTA: remote arrive
-      mbar_init(&empty_bar[i], 1);  // one tcgen05.commit
+      mbar_init(&empty_bar[i], MC);  // one tcgen05.commit per CTA group that reads this CTA's B rows
     }
     for (int i = 0; i < kAccStages; ++i) {
       mbar_init(&tfull_bar[i], 1);        // one tcgen05.commit
@@ -127,14 +156,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     tmem_relinquish<CG>();
   }
   tc_fence_before();
-  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (CG * MC > 1) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
 
-  const int num_tiles = p.tiles_m * p.tiles_n;
+  const int num_tiles = p.num_work;  // work items (whole tiles and half-width tail items)
   const int num_kb = (p.K + BLOCK_K - 1) / BLOCK_K;
-  const int first_tile = blockIdx.x / CG;
-  const int tile_step = gridDim.x / CG;
+  const int first_tile = blockIdx.x / (CG * MC);
+  const int tile_step = gridDim.x / (CG * MC);
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
@@ -142,10 +171,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
       int stage = 0;
       uint32_t phase = 0;
       for (int t = first_tile; t < num_tiles; t += tile_step) {
-        int tm, tn;
-        tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-        const int m0 = (tm * CG + cta_rank) * BLOCK_M;
-        const int n0 = tn * BN + cta_rank * Cfg::B_ROWS;
+        const WorkItem it = decode_work<BN>(t, p);
+        const int m0 = ((it.tm * MC + group) * CG + cta_rank) * BLOCK_M;
+        // a half-width item still loads full-height B boxes (constant transaction size); only width/CG rows are used
+        const int n0 = it.tn * BN + it.n_off + cta_rank * (it.width / CG);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           const int k0 = kb * BLOCK_K;
@@ -162,14 +191,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             for (int j = 0; j < BLOCK_M / 64; ++j)
               tma_load_2d<CG>(&map_a, &full_bar[stage], sa + j * (64 * BLOCK_K * 2), m0 + 64 * j, k0);
           }
-          if (!p.b_mn) {
-            tma_load_2d<CG>(&map_b, &full_bar[stage], sb, k0, n0);
-          } else {
-            if constexpr (Cfg::B_ROWS % 64 == 0) {
+          if constexpr (MC == 1) {
+            if (!p.b_mn) {
+              tma_load_2d<CG>(&map_b, &full_bar[stage], sb, k0, n0);
+            } else {
+              if constexpr (Cfg::B_ROWS % 64 == 0) {
 #pragma unroll
-              for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
-                tma_load_2d<CG>(&map_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), n0 + 64 * j, k0);
+                for (int j = 0; j < Cfg::B_ROWS / 64; ++j)
+                  tma_load_2d<CG>(&map_b, &full_bar[stage], sb + j * (64 * BLOCK_K * 2), n0 + 64 * j, k0);
+              }
             }
+          } else {
+            // Both CTA groups of the cluster need the same B rows: each loads half of them (64 rows) and
+            // multicasts the box to its counterpart (same in-group rank) in the other group.
+            const uint16_t mask = static_cast<uint16_t>((1u << cta_rank) | (1u << (cta_rank + CG)));
+            uint8_t* dst = sb + group * (64 * BLOCK_K * 2);
+            if (!p.b_mn) tma_load_2d_mcast_pair(&map_b, &full_bar[stage], dst, k0, n0 + 64 * group, mask);
+            else tma_load_2d_mcast_pair(&map_b, &full_bar[stage], dst, n0 + 64 * group, k0, mask);
           }
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -178,7 +216,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
   } else if (warp == 1) {
     // -------------------------------------------------------------- MMA issuer
     if (leader) {
-      const uint32_t idesc = make_idesc_bf16(BLOCK_M * CG, BN, p.a_mn, p.b_mn);
+      const uint32_t idesc_full = make_idesc_bf16(BLOCK_M * CG, BN, p.a_mn, p.b_mn);
+      const uint32_t idesc_half = make_idesc_bf16(BLOCK_M * CG, BN / 2, p.a_mn, p.b_mn);
       // K-major:  8-row groups are 1024 B apart (SBO); LBO is unused with swizzling (canonical value 16 B).
       // MN-major: 8 k-rows of one 64-wide block are 1024 B apart (SBO); 64-wide blocks are 8192 B apart (LBO).
       const uint32_t a_lbo = p.a_mn ? 64 * BLOCK_K * 2 : 16, b_lbo = p.b_mn ? 64 * BLOCK_K * 2 : 16;
@@ -195,6 +234,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
         mbar_wait(&tempty_bar[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + acc * BN;
+        const uint32_t idesc = t >= p.full_work ? idesc_half : idesc_full;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
@@ -204,8 +244,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
             for (int k = 0; k < BLOCK_K / UMMA_K; ++k)
               umma_bf16<CG>(tmem_d, da0 + k * a_kstep, db0 + k * b_kstep, idesc, (kb | k) != 0 ? 1u : 0u);
-            umma_commit<CG>(&empty_bar[stage]);                      // smem slot reusable once these MMAs retire
-            if (kb == num_kb - 1) umma_commit<CG>(&tfull_bar[acc]);  // accumulator complete
+            // smem slot reusable once these MMAs retire: tell every CTA that writes into it
+            umma_commit<CG>(&empty_bar[stage], static_cast<uint16_t>((1u << (CG * MC)) - 1));
+            // accumulator complete: tell the epilogue warps of this CTA group
+            if (kb == num_kb - 1) umma_commit<CG>(&tfull_bar[acc], static_cast<uint16_t>(0x3u << (CG * group)));
           }
           __syncwarp();
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
@@ -224,19 +266,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     // the Philox stream is offset by the device-side step counter so that a CUDA-graph replay draws fresh masks
     const uint64_t drop_stream = p.drop_stream + (p.step_ptr ? static_cast<uint64_t>(*p.step_ptr) * 1024ull : 0ull);
     for (int t = first_tile; t < num_tiles; t += tile_step) {
-      int tm, tn;
-      tile_coords(t, p.tiles_m, p.tiles_n, tm, tn);
-      const int m = (tm * CG + cta_rank) * BLOCK_M + row;
-      const int n_tile = tn * BN;
+      const WorkItem it = decode_work<BN>(t, p);
+      const int m = ((it.tm * MC + group) * CG + cta_rank) * BLOCK_M + row;
+      const int n_tile = it.tn * BN + it.n_off;
       mbar_wait(&tfull_bar[acc], acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16) + acc * BN;
       constexpr int CHUNK = BN >= 32 ? 32 : 16;
-      constexpr int NCHUNK = BN / CHUNK;
+      const int nchunk = it.width / CHUNK > 0 ? it.width / CHUNK : 1;
       // chunks [c_lo, c_hi) belong to this warp; with a single chunk the second warp of the quarter only
       // takes part in the barrier protocol
-      constexpr int PER = (NCHUNK + 1) / 2;
-      const int c_lo = half * PER, c_hi = min(NCHUNK, c_lo + PER);
+      const int per = (nchunk + 1) / 2;
+      const int c_lo = half * per, c_hi = min(nchunk, c_lo + per);
       if (c_lo >= c_hi) {
         tc_fence_before();
         __syncwarp();
@@ -278,10 +319,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
                 if (full || n0 + j < p.N) x[j] += __ldg(p.bias + n0 + j);
             }
           }
-          if (p.act != ACT_LINEAR) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j) x[j] = act_apply(p.act, x[j]);
-          }
+          if (p.act != ACT_LINEAR) act_apply_chunk<CHUNK>(p.act, x);
           if (has_drop) {
 #pragma unroll
             for (int j = 0; j < CHUNK; j += 4) {
@@ -307,19 +345,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 #pragma unroll
             for (int j = 0; j < CHUNK; ++j) y[j] = (n0 + j < p.N) ? __bfloat162float(arow[j]) : 0.f;
           }
-          if (has_drop) {
-            const float inv_scale = 1.f - p.drop_p;
+          if (has_drop || p.act != ACT_LINEAR) {
+            float g[CHUNK];
+            act_grad_chunk<CHUNK>(p.act, y, has_drop ? 1.f - p.drop_p : 1.f, g);
+            if (has_drop) {
 #pragma unroll
-            for (int j = 0; j < CHUNK; j += 4) {
-              bool keep[4];
-              dropout_keep4(p.seed, drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
+              for (int j = 0; j < CHUNK; j += 4) {
+                bool keep[4];
+                dropout_keep4(p.seed, drop_stream, static_cast<uint64_t>(m) * p.N + n0 + j, p.drop_thresh, keep);
 #pragma unroll
-              for (int e = 0; e < 4; ++e)
-                x[j + e] = keep[e] ? x[j + e] * p.drop_scale * act_grad_from_out(p.act, y[j + e] * inv_scale) : 0.f;
+                for (int e = 0; e < 4; ++e) x[j + e] = keep[e] ? x[j + e] * p.drop_scale * g[j + e] : 0.f;
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < CHUNK; ++j) x[j] *= g[j];
             }
-          } else if (p.act != ACT_LINEAR) {
-#pragma unroll
-            for (int j = 0; j < CHUNK; ++j) x[j] *= act_grad_from_out(p.act, y[j]);
           }
         }
         if (p.out_f32 != nullptr) {
@@ -370,7 +410,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
 
   // ------------------------------------------------------------------ teardown
   tc_fence_before();
-  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if constexpr (CG * MC > 1) cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc<CG>(tmem_base, Cfg::TMEM_COLS);
@@ -414,47 +454,70 @@ static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t 
   return 0;
 }
 
-template <int BN, int CG>
+template <int BN, int CG, int MC>
 static int launch_gemm(const EbGemmArgs& a, GemmDev p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CG>;
+  static_assert(MC == 1 || (CG == 2 && Cfg::B_ROWS == 128), "B multicast is built for 256-wide CTA-pair tiles");
   CUtensorMap map_a, map_b;
   if (!a.a_mn) { if (make_map(&map_a, a.A, a.M, a.K, a.lda, BLOCK_M, BLOCK_K)) return 1; }
   else         { if (make_map(&map_a, a.A, a.K, a.M, a.lda, BLOCK_K, 64)) return 1; }
-  if (!a.b_mn) { if (make_map(&map_b, a.B, a.N, a.K, a.ldb, Cfg::B_ROWS, BLOCK_K)) return 1; }
+  if (!a.b_mn) { if (make_map(&map_b, a.B, a.N, a.K, a.ldb, Cfg::B_ROWS / MC, BLOCK_K)) return 1; }
   else         { if (make_map(&map_b, a.B, a.K, a.N, a.ldb, BLOCK_K, 64)) return 1; }
-  p.tiles_m = (a.M + BLOCK_M * CG - 1) / (BLOCK_M * CG);
+  constexpr int CLUSTER = CG * MC;
+  p.tiles_m = (a.M + BLOCK_M * CLUSTER - 1) / (BLOCK_M * CLUSTER);
   p.tiles_n = (a.N + BN - 1) / BN;
   const int tiles = p.tiles_m * p.tiles_n;
-  int clusters = num_sms() / CG;
-  if (clusters > tiles) clusters = tiles;
-  auto kern = gemm_bf16_kernel<BN, CG>;
+  auto kern = gemm_bf16_kernel<BN, CG, MC>;
   static bool attr_set[64] = {false};  // per instantiation, per device
+  static int max_clusters[64] = {0};
   int dev = 0;
   EB_CUDA_OK(cudaGetDevice(&dev));
-  if (!attr_set[dev & 63]) {
-    EB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
-    attr_set[dev & 63] = true;
-  }
   cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3(clusters * CG);
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
   cfg.stream = stream;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.x = CLUSTER;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
+  {
+    // first use of this instantiation on this device (several worker threads may race here)
+    static std::mutex init_mutex;
+    std::lock_guard<std::mutex> guard(init_mutex);
+    if (!attr_set[dev & 63]) {
+      EB_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+      int n = num_sms() / CLUSTER;
+      if (CLUSTER > 2) {
+        // clusters of 4 do not tile every GPC evenly: ask how many can actually be co-resident
+        cfg.gridDim = dim3((num_sms() / CLUSTER) * CLUSTER);
+        int q = 0;
+        if (cudaOccupancyMaxActiveClusters(&q, kern, &cfg) == cudaSuccess && q > 0 && q < n) n = q;
+        cudaGetLastError();
+      }
+      max_clusters[dev & 63] = n > 0 ? n : 1;
+      attr_set[dev & 63] = true;
+    }
+  }
+  int clusters = max_clusters[dev & 63];
+  // tail handling: split the tiles of a sparsely filled last wave into two half-width work items
+  const int rem = tiles % clusters;
+  const bool split = BN == 256 && tiles > clusters && rem > 0 && 2 * rem <= clusters && !a.no_tail_split;
+  p.full_work = split ? tiles - rem : tiles;
+  p.num_work = split ? tiles + rem : tiles;
+  if (clusters > p.num_work) clusters = p.num_work;
+  cfg.gridDim = dim3(clusters * CLUSTER);
   EB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, map_a, map_b, p));
   count_launch();
   return 0;
 }
 
-static void pick_config(const EbGemmArgs& a, int& bn, int& cg) {
+static void pick_config(const EbGemmArgs& a, int& bn, int& cg, int& mc) {
   bn = a.block_n;
   cg = a.cta_group;
+  mc = a.multicast;
   if (bn == 0) {
     const int min_bn = a.b_mn ? 64 : 16;
     const int sms = num_sms();
@@ -475,6 +538,13 @@ static void pick_config(const EbGemmArgs& a, int& bn, int& cg) {
     const long tiles2 = static_cast<long>((a.M + 2 * BLOCK_M - 1) / (2 * BLOCK_M)) * ((a.N + bn - 1) / bn);
     cg = (bn >= 128 && tiles2 >= num_sms() / 2 && a.K >= 512) ? 2 : 1;
   }
+  if (mc == 0) {
+    // B multicast across two CTA pairs pays once the kernel is limited by L2 -> SM traffic: big, deep GEMMs
+    const long tiles4 = static_cast<long>((a.M + 4 * BLOCK_M - 1) / (4 * BLOCK_M)) * ((a.N + bn - 1) / bn);
+    static const int env = getenv("EB_GEMM_MC") ? atoi(getenv("EB_GEMM_MC")) : 0;
+    mc = env ? env : ((cg == 2 && bn == 256 && tiles4 >= num_sms() / 8 && a.K >= 512 && (a.M % 512 == 0 || a.M >= 2048)) ? 2 : 1);
+  }
+  if (cg != 2 || bn != 256) mc = 1;
 }
 
 }  // namespace eb
@@ -513,18 +583,19 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
   p.bf16_from_f32 = a.bf16_from_f32;
   p.tiles_m = p.tiles_n = 0;
 
-  int bn, cg;
-  pick_config(a, bn, cg);
+  int bn, cg, mc;
+  pick_config(a, bn, cg, mc);
   if (a.b_mn && bn < 64) return fail("eb_gemm_bf16: MN-major B needs block_n >= 64 (got %d)", bn);
   if (cg == 2 && bn < 128) return fail("eb_gemm_bf16: cta_group 2 needs block_n >= 128 (got %d)", bn);
+  if (mc == 2) return launch_gemm<256, 2, 2>(a, p, stream);
   switch (cg * 1000 + bn) {
-    case 1016: return launch_gemm<16, 1>(a, p, stream);
-    case 1032: return launch_gemm<32, 1>(a, p, stream);
-    case 1064: return launch_gemm<64, 1>(a, p, stream);
-    case 1128: return launch_gemm<128, 1>(a, p, stream);
-    case 1256: return launch_gemm<256, 1>(a, p, stream);
-    case 2128: return launch_gemm<128, 2>(a, p, stream);
-    case 2256: return launch_gemm<256, 2>(a, p, stream);
+    case 1016: return launch_gemm<16, 1, 1>(a, p, stream);
+    case 1032: return launch_gemm<32, 1, 1>(a, p, stream);
+    case 1064: return launch_gemm<64, 1, 1>(a, p, stream);
+    case 1128: return launch_gemm<128, 1, 1>(a, p, stream);
+    case 1256: return launch_gemm<256, 1, 1>(a, p, stream);
+    case 2128: return launch_gemm<128, 2, 1>(a, p, stream);
+    case 2256: return launch_gemm<256, 2, 1>(a, p, stream);
     default: return fail("eb_gemm_bf16: unsupported config block_n=%d cta_group=%d", bn, cg);
   }
 }

@@ -65,6 +65,42 @@ __host__ __device__ __forceinline__ float act_grad_from_out(int act, float y) {
   }
 }
 
+
+// Whole-chunk forms with the activation switch OUTSIDE the element loop (one uniform branch per chunk instead
+// of a divergence-managed switch per element).
+template <int N>
+__device__ __forceinline__ void act_apply_chunk(int act, float (&x)[N]) {
+#define EB_ACT_CASE(ID)                                   \
+  case ID:                                                \
+    _Pragma("unroll") for (int j = 0; j < N; ++j) x[j] = act_apply(ID, x[j]); \
+    break;
+  switch (act) {
+    EB_ACT_CASE(ACT_RELU) EB_ACT_CASE(ACT_SIGMOID) EB_ACT_CASE(ACT_TANH) EB_ACT_CASE(ACT_SOFTPLUS)
+    EB_ACT_CASE(ACT_SOFTSIGN) EB_ACT_CASE(ACT_ELU) EB_ACT_CASE(ACT_SELU) EB_ACT_CASE(ACT_EXPONENTIAL)
+    EB_ACT_CASE(ACT_HARD_SIGMOID)
+    default: break;
+  }
+#undef EB_ACT_CASE
+}
+
+// g[j] = act'(y[j] * y_scale) for a whole chunk.
+template <int N>
+__device__ __forceinline__ void act_grad_chunk(int act, const float (&y)[N], float y_scale, float (&g)[N]) {
+#define EB_ACT_CASE(ID)                                   \
+  case ID:                                                \
+    _Pragma("unroll") for (int j = 0; j < N; ++j) g[j] = act_grad_from_out(ID, y[j] * y_scale); \
+    break;
+  switch (act) {
+    EB_ACT_CASE(ACT_RELU) EB_ACT_CASE(ACT_SIGMOID) EB_ACT_CASE(ACT_TANH) EB_ACT_CASE(ACT_SOFTPLUS)
+    EB_ACT_CASE(ACT_SOFTSIGN) EB_ACT_CASE(ACT_ELU) EB_ACT_CASE(ACT_SELU) EB_ACT_CASE(ACT_EXPONENTIAL)
+    EB_ACT_CASE(ACT_HARD_SIGMOID)
+    default:
+      _Pragma("unroll") for (int j = 0; j < N; ++j) g[j] = 1.f;
+      break;
+  }
+#undef EB_ACT_CASE
+}
+
 // ------------------------------------------------------------------ Philox
 struct Philox4 {
   uint32_t x, y, z, w;

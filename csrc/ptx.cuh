@@ -115,6 +115,19 @@ __device__ __forceinline__ void tma_load_2d(const CUtensorMap* map, uint64_t* ba
   }
 }
 
+// Multicast form for CTA pairs inside a larger cluster: the box lands at the same CTA-relative smem offset in
+// every CTA of `cta_mask`, and every destination's transaction count is credited on the barrier at the same
+// offset in that destination's pair leader (peer bit cleared).
+__device__ __forceinline__ void tma_load_2d_mcast_pair(const CUtensorMap* map, uint64_t* bar, void* smem, int c0,
+                                                       int c1, uint16_t cta_mask) {
+  uint32_t mbar = smem_u32(bar) & 0xFEFFFFFFu;
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+      " [%0], [%1, {%4, %5}], [%2], %3;" ::"r"(smem_u32(smem)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(mbar), "h"(cta_mask), "r"(c0), "r"(c1)
+      : "memory");
+}
+
 // ------------------------------------------------------------------ tcgen05
 template <int kCtaGroup>
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
@@ -174,16 +187,16 @@ __device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint
 // tcgen05.commit: the mbarrier gets one arrival once all previously issued MMAs retire.
 // For a CTA pair the arrival is multicast to the same barrier in both CTAs.
 template <int kCtaGroup>
-__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+__device__ __forceinline__ void umma_commit(uint64_t* bar, uint16_t cta_mask = 0x3) {
   if constexpr (kCtaGroup == 1) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                  : "memory");
   } else {
-    uint16_t mask = 0x3;
+    // the arrival is delivered to the barrier at this offset in every CTA of cta_mask
     asm volatile(
         "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
             smem_u32(bar)),
-        "h"(mask)
+        "h"(cta_mask)
         : "memory");
   }
 }

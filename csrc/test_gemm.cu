@@ -97,6 +97,8 @@ int main(int argc, char** argv) {
   g.alpha = 1.f;
   g.out_bf16 = dO; g.ldo = ldo;
   g.block_n = bn; g.cta_group = cg;
+  g.no_tail_split = getenv("EB_NO_TAIL_SPLIT") ? 1 : 0;
+  g.multicast = getenv("EB_MC") ? atoi(getenv("EB_MC")) : 0;
 
   if (!strcmp(mode, "bench")) {
     int iters = argc > 9 ? atoi(argv[9]) : 10;

@@ -40,7 +40,7 @@ class GemmArgs(ctypes.Structure):
                 ('drop_p', c_float), ('seed', c_uint64), ('drop_stream', c_uint64), ('step_ptr', c_void_p),
                 ('out_bf16', c_void_p), ('ldo', c_int32),
                 ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float), ('bf16_from_f32', c_int32),
-                ('block_n', c_int32), ('cta_group', c_int32)]
+                ('block_n', c_int32), ('cta_group', c_int32), ('multicast', c_int32), ('no_tail_split', c_int32)]
 
 
 class LossArgs(ctypes.Structure):
@@ -285,9 +285,11 @@ def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None):
     cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
     if locked:
         _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
-    _check(lib.eb_ps_pull(mptr, _ptr(dst_f32), _ptr(dst_bf16), n, s), 'eb_ps_pull')
-    if locked:
-        _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+    try:
+        _check(lib.eb_ps_pull(mptr, _ptr(dst_f32), _ptr(dst_bf16), n, s), 'eb_ps_pull')
+    finally:
+        if locked:  # a lock that was enqueued is always followed by its unlock, whatever happens in between
+            _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
 
 
 def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=None):
@@ -299,9 +301,11 @@ def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=N
     cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
     if locked:
         _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
-    _check(lib.eb_ps_push(mptr, _ptr(delta), _ptr(before), _ptr(after), n, s), 'eb_ps_push')
-    if locked:
-        _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+    try:
+        _check(lib.eb_ps_push(mptr, _ptr(delta), _ptr(before), _ptr(after), n, s), 'eb_ps_push')
+    finally:
+        if locked:
+            _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
 
 
 # --------------------------------------------------------------- memory / IPC

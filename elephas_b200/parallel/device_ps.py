@@ -114,6 +114,9 @@ class DeviceStore:
         self.pull_into(tmp)
         if tmp.is_cuda:
             torch.cuda.current_stream(tmp.device).synchronize()
+            if isinstance(self.ctrl, torch.Tensor) and int(self.ctrl[4].item()):
+                raise RuntimeError("device parameter server: a lock holder never released the ticket lock "
+                                   "(watchdog fired after 10 s); master weights may have been updated unlocked")
         return self.layout.unpack_arrays(tmp)
 
     def push_arrays(self, delta):

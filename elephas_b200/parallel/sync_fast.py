@@ -221,6 +221,14 @@ class SyncContext:
     def _remove_hooks(self):
         self.eng.comm_hook = self.eng.comm_join = None
 
+    def _check_watchdog(self):
+        """The collective kernels give up on a peer after 20 s and leave a status word instead of hanging."""
+        if self.mem is not None:
+            status = int(self.comm_local[8].item())
+            if status:
+                raise RuntimeError("rank %d: peer rank %d never reached a fused all-reduce (watchdog fired); "
+                                   "the replicas are no longer consistent" % (self.rt.rank, status - 1))
+
     def close(self):
         self.eng.delta_target = None
         self._remove_hooks()
@@ -340,6 +348,7 @@ class SyncContext:
                     history._append(epoch, logs)
             t1.record()
             torch.cuda.synchronize(rt.device)
+            self._check_watchdog()
             eng.delta_target = None
             eng._weights_dirty_in_model = True
             self.model.optimizer.iterations = int(eng.step.item())

@@ -81,6 +81,8 @@ typedef struct EbGemmArgs {
   int32_t bf16_from_f32;  /* out_bf16 = bf16(final fp32 value) instead of bf16(alpha*acc): fused SGD weight update */
   int32_t block_n;        /* 0 = auto, else 16/32/64/128/256                     */
   int32_t cta_group;      /* 0 = auto, else 1 or 2 (CTA pair, UMMA M=256)        */
+  int32_t multicast;      /* 0 = auto, 1 = off, 2 = B tile multicast across two CTA pairs (cluster of 4) */
+  int32_t no_tail_split;  /* 1 disables the half-width scheduling of a sparse last wave */
 } EbGemmArgs;
 
 int eb_gemm_bf16(const EbGemmArgs* args, void* stream);

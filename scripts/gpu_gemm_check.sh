@@ -47,6 +47,14 @@ run check 4096 4096 1024 0 0 0 0
 run check 4096 4096 1024 0 1 0 0 1 1 0
 run check 4096 4096 1024 1 1 0 0 0 0 0 2
 run check 2048 3000 520 0 0 0 0 0 1 0.2
+# --- split tail wave (tiles % CTA-groups small): 256 tiles on 74 pairs, 160 tiles on 148 CTAs
+run check 4096 4096 512 0 0 256 2
+run check 4096 4096 512 0 1 256 2 1 1 0.2
+run check 4096 4096 512 1 1 256 2 0 0 0 2
+run check 4096 4000 520 0 0 256 2 0 1 0.2
+run check 1280 4096 256 0 0 256 1 0 2 0
+run check 1280 4096 256 1 1 256 1 0 0 0 1
+run check 1280 4090 256 0 1 256 1 1 3 0
 # --- speed (L2 flushed between iterations, operands > L2)
 for cfg in "256 1" "256 2" "128 1" "128 2"; do
   run bench 8192 8192 8192 0 0 $cfg 10

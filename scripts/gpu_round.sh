@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 export SPARK_LOCAL_IP=127.0.0.1
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/round.log 2>&1
 echo "=== pytest -m gpu" >> gpurun_out/round.log
-timeout 900 python -m pytest tests -m gpu -q --timeout 300 ${PYTEST_ARGS} > gpurun_out/pytest_gpu.log 2>&1
+timeout 420 python -m pytest tests -m gpu -q --timeout 90 --timeout-method=thread ${PYTEST_ARGS} > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest rc=$?" >> gpurun_out/round.log
 tail -40 gpurun_out/pytest_gpu.log >> gpurun_out/round.log
 echo "=== smoke" >> gpurun_out/round.log

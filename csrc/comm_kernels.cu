@@ -248,6 +248,65 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev p)
   }
 }
 
+// Sharded-master variant (ZeRO-1 style): rank r owns slice r of the fp32 master weights. It reduces the peers'
+// deltas for its slice over NVLink, updates its fp32 slice, and stores the refreshed bf16 weights of the slice
+// straight into EVERY rank's (peer-mapped) compute copy; a second flag barrier tells each rank that all slices
+// of its bf16 copy have arrived. Per rank and element this moves (N-1)/N delta reads + (N-1)/N bf16 stores over
+// NVLink (the two-shot optimum) but touches only 1/N of the fp32 master in local HBM - instead of every rank
+// re-reading and re-writing all of it - which matters because the GEMMs running next to it are L2-bound.
+template <typename T>
+__global__ void __launch_bounds__(512) allreduce_shard_update_kernel(const CommDev p) {
+  const uint32_t e = p.local[0] + 1;
+  if (blockIdx.x == 0) publish_flags(p, 0, e);
+  wait_flags(p, 0, e);
+  const long n8 = p.n / 8;
+  const long per = (n8 + p.world - 1) / p.world;
+  const long lo = per * p.rank, hi = min(n8, lo + per);
+  for (long g = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < hi;
+       g += static_cast<long>(gridDim.x) * blockDim.x) {
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll 1
+    for (int k = 0; k < p.world; ++k) {
+      int peer = p.rank + k;
+      if (peer >= p.world) peer -= p.world;
+      accumulate8<T>(p.delta[peer], g * 8, s);
+    }
+    float4 w0 = *reinterpret_cast<float4*>(p.w32 + g * 8), w1 = *reinterpret_cast<float4*>(p.w32 + g * 8 + 4);
+    w0.x -= s[0] * p.scale; w0.y -= s[1] * p.scale; w0.z -= s[2] * p.scale; w0.w -= s[3] * p.scale;
+    w1.x -= s[4] * p.scale; w1.y -= s[5] * p.scale; w1.z -= s[6] * p.scale; w1.w -= s[7] * p.scale;
+    *reinterpret_cast<float4*>(p.w32 + g * 8) = w0;
+    *reinterpret_cast<float4*>(p.w32 + g * 8 + 4) = w1;
+    uint4 o;
+    o.x = pack_bf16x2(w0.x, w0.y); o.y = pack_bf16x2(w0.z, w0.w);
+    o.z = pack_bf16x2(w1.x, w1.y); o.w = pack_bf16x2(w1.z, w1.w);
+#pragma unroll 1
+    for (int k = 0; k < p.world; ++k) {
+      int peer = p.rank + k;
+      if (peer >= p.world) peer -= p.world;
+      st_v4(static_cast<__nv_bfloat16*>(p.avg[peer]) + g * 8, o);  // avg[] carries the peers' bf16 weight buffers here
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(p.local + 2, 1u) == gridDim.x - 1) {
+      p.local[2] = 0;
+      __threadfence_system();
+      for (int k = 0; k < p.world; ++k) st_release_sys(p.pad[k] + 8 + p.rank, e);
+    }
+  }
+  wait_flags(p, 8, e);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.local + 1, 1u) == gridDim.x - 1) {
+      p.local[1] = 0;
+      p.local[0] = e;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ parameter server
 __global__ void ps_lock_kernel(uint32_t* ctrl) {
   // ctrl[1]: next ticket, ctrl[2]: now serving, ctrl[0]: sequence word (odd while a writer is inside),
@@ -367,6 +426,26 @@ extern "C" int eb_allreduce_update(const EbCommArgs* a, void* stream) {
     else allreduce_oneshot_kernel<float, 0><<<blocks, 512, 0, s>>>(p);
     EB_LAUNCH_OK("allreduce_oneshot_kernel");
   }
+  return 0;
+}
+
+extern "C" int eb_allreduce_shard_update(const EbCommArgs* a, void* stream) {
+  if (a == nullptr) return fail("eb_allreduce_shard_update: null args");
+  if (a->n <= 0) return 0;
+  CommDev p;
+  if (fill_comm(a, p)) return 1;
+  if (p.w32 == nullptr) return fail("eb_allreduce_shard_update: fp32 weights missing");
+  for (int i = 0; i < a->world; ++i)
+    if (p.avg[i] == nullptr) return fail("eb_allreduce_shard_update: every rank's bf16 weight buffer is required (avg[])");
+  int blocks = a->blocks > 0 ? a->blocks : num_sms() / 2;
+  if (blocks > num_sms()) blocks = num_sms();  // co-resident grid: the kernel contains a grid-wide barrier
+  const long work = (a->n / 8 / a->world + 511) / 512;
+  if (blocks > work) blocks = static_cast<int>(work);
+  if (blocks < 1) blocks = 1;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (a->dtype_bf16) allreduce_shard_update_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(p);
+  else allreduce_shard_update_kernel<float><<<blocks, 512, 0, s>>>(p);
+  EB_LAUNCH_OK("allreduce_shard_update_kernel");
   return 0;
 }
 

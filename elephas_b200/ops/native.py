@@ -91,7 +91,7 @@ def load():
         lib.eb_launch_count.restype = c_uint64
         lib.eb_version.restype = c_int32
         for name in ('eb_gemm_bf16', 'eb_loss_fwd_bwd', 'eb_optimizer_step', 'eb_allreduce_update',
-                     'eb_allreduce_sum'):
+                     'eb_allreduce_sum', 'eb_allreduce_shard_update'):
             getattr(lib, name).argtypes = [c_void_p, c_void_p]
         lib.eb_stage_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
         lib.eb_cast_f32_to_bf16.argtypes = [c_void_p, c_void_p, c_int64, c_void_p]
@@ -269,6 +269,14 @@ def allreduce_update(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_b
     a = _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, avg_ptrs, w32, w16, None, algo,
                    blocks)
     _check(require().eb_allreduce_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_update')
+
+
+def allreduce_shard_update(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, w32, w16_ptrs, blocks=0,
+                           device=None):
+    """Sharded-master fused all-reduce + update: ``w16_ptrs`` are every rank's peer-mapped bf16 weight buffers."""
+    a = _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, w16_ptrs, w32, None, None, 0,
+                   blocks)
+    _check(require().eb_allreduce_shard_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_shard_update')
 
 
 def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32, scale=1.0, blocks=0, device=None):

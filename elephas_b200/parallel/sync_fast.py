@@ -161,29 +161,89 @@ class SyncContext:
         self.dtype_bf16 = None
         self.bs = None
         self.n_sub = rt.world_size
+        self.sharded = False
+        self.w32_partial = False
+        self._private_w16 = None
 
     # ---------------------------------------------------------------- comm setup
     def _setup_comm(self, dtype_bf16):
         if self.mem is not None and self.dtype_bf16 == dtype_bf16:
             return
+        eng = self.eng
         if self.mem is not None:
-            self.eng.invalidate_graphs()  # recorded graphs hold pointers into the old buffers
-            self.mem.close()
-        n = self.eng.layout.numel
+            self._release_mem()
+        n = eng.layout.numel
         item = 2 if dtype_bf16 else 4
-        self.mem = SymmetricMemory(self.rt, {'delta0': n * item, 'delta1': n * item, 'avg': n * item, 'pad': 256})
+        spec = {'delta0': n * item, 'delta1': n * item, 'pad': 256}
+        # per-batch mode shards the fp32 master across ranks (each rank updates 1/N of it and stores the refreshed
+        # bf16 weights into every peer's compute copy, which therefore lives in peer-mapped memory); the epoch/fit
+        # modes keep whole replicas and need the averaged-delta staging buffer of the two-shot kernel instead
+        self.sharded = bool(dtype_bf16) and os.environ.get('ELEPHAS_B200_SHARDED_MASTER', '1') != '0'
+        spec['w16' if self.sharded else 'avg'] = n * item
+        self.mem = SymmetricMemory(self.rt, spec)
         self.comm_local = torch.zeros(16, dtype=torch.int32, device=self.rt.device)
         self.dtype_bf16 = dtype_bf16
         tdt = torch.bfloat16 if dtype_bf16 else torch.float32
         self.delta = [self.mem.local('delta0', tdt, n), self.mem.local('delta1', tdt, n)]
         self.flip = 0
-        # first launch of both collective kernels outside of any graph capture (zero delta: weights unchanged)
-        for algo in (1, 2):
-            native.allreduce_update(self.mem.ptrs('delta0'), self.mem.ptrs('pad'), self.comm_local, 1024,
-                                    self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, dtype_bf16, self.eng.w32,
-                                    w16=self.eng.w16, avg_ptrs=self.mem.ptrs('avg'), algo=algo, blocks=2,
-                                    device=self.rt.device)
+        self.w32_partial = False
+        if self.sharded:
+            self._private_w16 = eng.w16
+            shared = self.mem.local('w16', torch.bfloat16, n)
+            shared.copy_(eng.w16)
+            eng.w16 = shared
+            eng.invalidate_graphs()  # recorded graphs point at the private copy
+        # first launch of the collective kernels outside of any graph capture (zero delta: weights unchanged)
+        self.delta[0][:1024].zero_()
         torch.cuda.synchronize(self.rt.device)
+        self.rt.barrier()
+        common = (self.mem.ptrs('delta0'), self.mem.ptrs('pad'), self.comm_local, 1024, self.rt.rank,
+                  self.rt.world_size, 1.0 / self.n_sub, dtype_bf16, eng.w32)
+        if self.sharded:
+            native.allreduce_shard_update(*common, self.mem.ptrs('w16'), blocks=2, device=self.rt.device)
+        else:
+            for algo in (1, 2):
+                native.allreduce_update(*common, w16=eng.w16, avg_ptrs=self.mem.ptrs('avg'), algo=algo, blocks=2,
+                                        device=self.rt.device)
+        torch.cuda.synchronize(self.rt.device)
+
+    def _release_mem(self):
+        eng = self.eng
+        self._gather_master()
+        if self.sharded and eng.w16 is not self._private_w16:
+            self._private_w16.copy_(eng.w16)
+            eng.w16 = self._private_w16
+        eng.invalidate_graphs()  # recorded graphs hold pointers into the buffers that go away now
+        torch.cuda.synchronize(self.rt.device)
+        self.mem.close()
+        self.mem = None
+
+    def _owned_ranges(self):
+        """Flat element ranges of the fp32 master this rank owns in sharded mode (slice ``rank`` of every bucket,
+        the same split as ``allreduce_shard_update_kernel``)."""
+        rank, world = self.rt.rank, self.rt.world_size
+        out = []
+        for lo, n in self.eng.bucket_ranges():
+            n8 = n // 8
+            per = -(-n8 // world)
+            a, b = per * rank, min(n8, per * (rank + 1))
+            if b > a:
+                out.append((lo + a * 8, lo + b * 8))
+        return out
+
+    def _gather_master(self):
+        """Sharded mode leaves every rank with an up-to-date fp32 master only for the slices it owns: rebuild
+        the full replica (once per fit, not per step) so that ``get_weights`` / ``save`` see exact values."""
+        if not self.w32_partial:
+            return
+        eng = self.eng
+        full = torch.zeros_like(eng.w32)
+        for a, b in self._owned_ranges():
+            full[a:b].copy_(eng.w32[a:b])
+        self.rt.all_reduce_sum_(full)
+        eng.w32.copy_(full)
+        self.w32_partial = False
+        eng._weights_dirty_in_model = True
 
     def _allreduce_update(self, lo=0, n=None, stream=None, blocks=0):
         """Fused all-reduce + update of flat elements [lo, lo+n) of the current delta buffer."""
@@ -191,10 +251,14 @@ class SyncContext:
         n = eng.layout.numel - lo if n is None else n
         name = 'delta%d' % self.flip
         item = 2 if self.dtype_bf16 else 4
-        native.allreduce_update(self.mem.ptrs(name, lo * item), self.mem.ptrs('pad'), self.comm_local, n,
-                                self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32[lo:],
-                                w16=eng.w16[lo:], avg_ptrs=self.mem.ptrs('avg', lo * item), blocks=blocks,
-                                device=self.rt.device)
+        common = (self.mem.ptrs(name, lo * item), self.mem.ptrs('pad'), self.comm_local, n, self.rt.rank,
+                  self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32[lo:])
+        if self.sharded:
+            native.allreduce_shard_update(*common, self.mem.ptrs('w16', lo * 2), blocks=blocks,
+                                          device=self.rt.device)
+        else:
+            native.allreduce_update(*common, w16=eng.w16[lo:], avg_ptrs=self.mem.ptrs('avg', lo * item),
+                                    blocks=blocks, device=self.rt.device)
         eng._weights_dirty_in_model = True
 
     # -- per-bucket communication overlapped with the rest of the backward pass -------------------------
@@ -232,16 +296,17 @@ class SyncContext:
     def close(self):
         self.eng.delta_target = None
         self._remove_hooks()
-        self.eng.invalidate_graphs()
         if self.mem is not None:
-            self.mem.close()
-            self.mem = None
+            self._release_mem()
+        else:
+            self.eng.invalidate_graphs()
 
     # -------------------------------------------------------------- one sync step
     def _step(self, buf, per_batch, have_batch):
         eng = self.eng
         if per_batch:
             eng.delta_target = self.delta[self.flip]
+            self.w32_partial = self.sharded  # (set here, not in the hook: the hook only runs while capturing)
             if have_batch:
                 eng.train_step_device(buf)  # the per-bucket all-reduces are part of the (graph-captured) step
             else:
@@ -346,6 +411,7 @@ class SyncContext:
                     logs.update({'val_' + k: v for k, v in zip(names, val)})
                 if logs:
                     history._append(epoch, logs)
+            self._gather_master()
             t1.record()
             torch.cuda.synchronize(rt.device)
             self._check_watchdog()
@@ -387,4 +453,5 @@ class SyncContext:
             torch.cuda.synchronize(rt.device)
             rt.barrier()
             eng.delta_target = None
+            self._gather_master()
             return e0.elapsed_time(e1)

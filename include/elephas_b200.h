@@ -173,6 +173,10 @@ typedef struct EbCommArgs {
 
 int eb_allreduce_update(const EbCommArgs* args, void* stream);
 int eb_allreduce_sum(const EbCommArgs* args, void* stream);
+/* Sharded-master form of eb_allreduce_update: rank r reduces and updates only slice r of w32 and stores the
+ * refreshed bf16 weights of that slice into every rank's compute copy, whose peer-mapped addresses are passed
+ * in avg[]. The fp32 master of the other slices is NOT maintained on this rank (gather the slices afterwards). */
+int eb_allreduce_shard_update(const EbCommArgs* args, void* stream);
 
 /* Allocation-free form of eb_allreduce_update for ONE rank (world = 1). This entry point has no
  * counterpart in the reference; it exists for hosts that are not allowed to allocate device memory at the

@@ -72,6 +72,42 @@ for algo, n, dtype in ((1, 1 << 16, torch.bfloat16), (2, 1 << 22, torch.bfloat16
     mem.close()
     log("allreduce_update algo=%d n=%d %s ok (max err %.2e)" % (algo, n, dtype, err))
 
+# ---- 1b. sharded-master variant: rank r updates slice r, stores bf16 weights into every peer's copy ----
+for n in (1 << 12, (1 << 22) + 64):
+    mem = SymmetricMemory(rt, {'delta0': n * 2, 'delta1': n * 2, 'w16': n * 2, 'pad': 256})
+    local = torch.zeros(16, dtype=torch.int32, device=rt.device)
+    w32 = torch.ones(n, device=rt.device)
+    w16 = mem.local('w16', torch.bfloat16, n)
+    w16.fill_(1.0)
+    expect = torch.ones(n, device=rt.device)
+    torch.cuda.synchronize()
+    rt.barrier()
+    for it in range(4):
+        name = 'delta%d' % (it % 2)
+        d = torch.randn(n, generator=torch.Generator().manual_seed(100 * it + R)).to(torch.bfloat16)
+        mem.local(name, torch.bfloat16, n).copy_(d.to(rt.device))
+        parts = [torch.randn(n, generator=torch.Generator().manual_seed(100 * it + r)).to(torch.bfloat16).float()
+                 for r in range(W)]
+        expect -= (sum(parts) / W).to(rt.device)
+        native.allreduce_shard_update(mem.ptrs(name), mem.ptrs('pad'), local, n, R, W, 1.0 / W, True, w32,
+                                      mem.ptrs('w16'), device=rt.device)
+    torch.cuda.synchronize()
+    n8 = n // 8
+    per = -(-n8 // W)
+    a, b = per * R * 8, min(n8, per * (R + 1)) * 8
+    err = (w32[a:b] - expect[a:b]).abs().max().item() if b > a else 0.0
+    assert err < 1e-5, (n, err)
+    # the bf16 compute copy is complete and identical on every rank, and agrees with the owners' fp32 slices
+    assert bool(((w16.float() - expect).abs() <= expect.abs() * 2.0 ** -8 + 1e-3).all())  # bf16 rounding of the fp32 value
+    assert torch.equal(w16[a:b], w32[a:b].to(torch.bfloat16))
+    same_on_all_ranks([w16.float().cpu().numpy()])
+    untouched = torch.ones_like(w32)
+    untouched[a:b] = w32[a:b]
+    assert torch.equal(untouched, w32)  # nothing outside the owned slice was written
+    rt.barrier()
+    mem.close()
+    log("allreduce_shard_update n=%d ok (max err %.2e)" % (n, err))
+
 # ---- 2. P2P sum all-reduce used by the generic path --------------------------------------------------
 flat = torch.full((1000,), float(R + 1), device=rt.device)
 out = all_reduce_sum(rt, flat)

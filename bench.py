@@ -140,6 +140,7 @@ def run_ours(args, rt):
     from elephas_b200.ops import native
     from elephas_b200.spark import SparkContext
     from elephas_b200.spark_model import SparkModel
+    from elephas_b200.utils import tracing
     from elephas_b200.utils.rdd_utils import to_sharded_rdd
 
     model, in_dim, out_dim, default_batch = build_model(args)
@@ -170,6 +171,7 @@ def run_ours(args, rt):
                         log_batch_loss=True, keep_context=True)  # warm-up of the streaming path
         rt.barrier()
         torch.cuda.synchronize()
+        tracing.reset()
         t0 = time.perf_counter()
         spark_model.fit(to_sharded_rdd(sc, xk, yk), epochs=1, batch_size=B, shuffle=False, input_mode='stream',
                         log_batch_loss=True, keep_context=True)
@@ -180,6 +182,8 @@ def run_ours(args, rt):
         t = torch.tensor([max(wall_ms, dev_ms)], device=rt.device, dtype=torch.float64)
         rt.all_reduce_max_(t)
         e2e_ms = float(t[0])
+        if tracing.enabled() and rt.is_driver:
+            print(tracing.report(), file=sys.stderr)
         hist = spark_model.training_histories[-1]
         assert len(hist['batch_loss']) == K, "one loss read-back per step expected"
         e2e = {'value': round(N * B * K / (e2e_ms / 1e3), 2), 'unit': 'samples/sec',

@@ -255,35 +255,77 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(const CommDev p)
 // NVLink (the two-shot optimum) but touches only 1/N of the fp32 master in local HBM - instead of every rank
 // re-reading and re-writing all of it - which matters because the GEMMs running next to it are L2-bound.
 template <typename T>
+__device__ __forceinline__ void add8(const uint4 (&v)[sizeof(T) / 2], float (&s)[8]);
+
+template <>
+__device__ __forceinline__ void add8<__nv_bfloat16>(const uint4 (&v)[1], float (&s)[8]) {
+  s[0] += bf16_lo(v[0].x); s[1] += bf16_hi(v[0].x); s[2] += bf16_lo(v[0].y); s[3] += bf16_hi(v[0].y);
+  s[4] += bf16_lo(v[0].z); s[5] += bf16_hi(v[0].z); s[6] += bf16_lo(v[0].w); s[7] += bf16_hi(v[0].w);
+}
+
+template <>
+__device__ __forceinline__ void add8<float>(const uint4 (&v)[2], float (&s)[8]) {
+  s[0] += __uint_as_float(v[0].x); s[1] += __uint_as_float(v[0].y); s[2] += __uint_as_float(v[0].z);
+  s[3] += __uint_as_float(v[0].w); s[4] += __uint_as_float(v[1].x); s[5] += __uint_as_float(v[1].y);
+  s[6] += __uint_as_float(v[1].z); s[7] += __uint_as_float(v[1].w);
+}
+
+// MAXW: compile-time bound on the number of ranks; U: groups of 8 elements per thread and iteration. All U x world
+// peer loads of an iteration are issued before the first one is consumed: with a ~2 us NVLink round trip the
+// bytes in flight (not the block count) decide the bandwidth, and a small grid leaves the SMs to the GEMMs.
+template <typename T, int MAXW, int U>
 __global__ void __launch_bounds__(512) allreduce_shard_update_kernel(const CommDev p) {
+  constexpr int V = sizeof(T) / 2;  // 16-byte vectors per group of 8 elements
   const uint32_t e = p.local[0] + 1;
   if (blockIdx.x == 0) publish_flags(p, 0, e);
   wait_flags(p, 0, e);
   const long n8 = p.n / 8;
   const long per = (n8 + p.world - 1) / p.world;
   const long lo = per * p.rank, hi = min(n8, lo + per);
-  for (long g = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g < hi;
-       g += static_cast<long>(gridDim.x) * blockDim.x) {
-    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-#pragma unroll 1
-    for (int k = 0; k < p.world; ++k) {
-      int peer = p.rank + k;
-      if (peer >= p.world) peer -= p.world;
-      accumulate8<T>(p.delta[peer], g * 8, s);
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  for (long g0 = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g0 < hi; g0 += stride * U) {
+    uint4 raw[U][MAXW][V];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long g = g0 + u * stride;
+      if (g < hi) {
+#pragma unroll
+        for (int k = 0; k < MAXW; ++k) {
+          if (k < p.world) {
+            int peer = p.rank + k;
+            if (peer >= p.world) peer -= p.world;
+            const T* src = static_cast<const T*>(p.delta[peer]) + g * 8;
+#pragma unroll
+            for (int v = 0; v < V; ++v) raw[u][k][v] = ld_peer_v4(src + v * (8 / V));
+          }
+        }
+      }
     }
-    float4 w0 = *reinterpret_cast<float4*>(p.w32 + g * 8), w1 = *reinterpret_cast<float4*>(p.w32 + g * 8 + 4);
-    w0.x -= s[0] * p.scale; w0.y -= s[1] * p.scale; w0.z -= s[2] * p.scale; w0.w -= s[3] * p.scale;
-    w1.x -= s[4] * p.scale; w1.y -= s[5] * p.scale; w1.z -= s[6] * p.scale; w1.w -= s[7] * p.scale;
-    *reinterpret_cast<float4*>(p.w32 + g * 8) = w0;
-    *reinterpret_cast<float4*>(p.w32 + g * 8 + 4) = w1;
-    uint4 o;
-    o.x = pack_bf16x2(w0.x, w0.y); o.y = pack_bf16x2(w0.z, w0.w);
-    o.z = pack_bf16x2(w1.x, w1.y); o.w = pack_bf16x2(w1.z, w1.w);
-#pragma unroll 1
-    for (int k = 0; k < p.world; ++k) {
-      int peer = p.rank + k;
-      if (peer >= p.world) peer -= p.world;
-      st_v4(static_cast<__nv_bfloat16*>(p.avg[peer]) + g * 8, o);  // avg[] carries the peers' bf16 weight buffers here
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long g = g0 + u * stride;
+      if (g < hi) {
+        float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int k = 0; k < MAXW; ++k)
+          if (k < p.world) add8<T>(raw[u][k], s);
+        float4 w0 = *reinterpret_cast<float4*>(p.w32 + g * 8), w1 = *reinterpret_cast<float4*>(p.w32 + g * 8 + 4);
+        w0.x -= s[0] * p.scale; w0.y -= s[1] * p.scale; w0.z -= s[2] * p.scale; w0.w -= s[3] * p.scale;
+        w1.x -= s[4] * p.scale; w1.y -= s[5] * p.scale; w1.z -= s[6] * p.scale; w1.w -= s[7] * p.scale;
+        *reinterpret_cast<float4*>(p.w32 + g * 8) = w0;
+        *reinterpret_cast<float4*>(p.w32 + g * 8 + 4) = w1;
+        uint4 o;
+        o.x = pack_bf16x2(w0.x, w0.y); o.y = pack_bf16x2(w0.z, w0.w);
+        o.z = pack_bf16x2(w1.x, w1.y); o.w = pack_bf16x2(w1.z, w1.w);
+#pragma unroll
+        for (int k = 0; k < MAXW; ++k) {
+          if (k < p.world) {
+            int peer = p.rank + k;
+            if (peer >= p.world) peer -= p.world;
+            st_v4(static_cast<__nv_bfloat16*>(p.avg[peer]) + g * 8, o);  // avg[]: the peers' bf16 weight buffers
+          }
+        }
+      }
     }
   }
   __threadfence_system();
@@ -439,12 +481,19 @@ extern "C" int eb_allreduce_shard_update(const EbCommArgs* a, void* stream) {
     if (p.avg[i] == nullptr) return fail("eb_allreduce_shard_update: every rank's bf16 weight buffer is required (avg[])");
   int blocks = a->blocks > 0 ? a->blocks : num_sms() / 2;
   if (blocks > num_sms()) blocks = num_sms();  // co-resident grid: the kernel contains a grid-wide barrier
-  const long work = (a->n / 8 / a->world + 511) / 512;
+  const bool small_world = a->world <= 4;
+  const int per_thread = a->dtype_bf16 ? (small_world ? 4 : 2) : (small_world ? 2 : 1);
+  const long work = (a->n / 8 / a->world + 512L * per_thread - 1) / (512L * per_thread);
   if (blocks > work) blocks = static_cast<int>(work);
   if (blocks < 1) blocks = 1;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  if (a->dtype_bf16) allreduce_shard_update_kernel<__nv_bfloat16><<<blocks, 512, 0, s>>>(p);
-  else allreduce_shard_update_kernel<float><<<blocks, 512, 0, s>>>(p);
+  if (a->dtype_bf16) {
+    if (small_world) allreduce_shard_update_kernel<__nv_bfloat16, 4, 4><<<blocks, 512, 0, s>>>(p);
+    else allreduce_shard_update_kernel<__nv_bfloat16, 8, 2><<<blocks, 512, 0, s>>>(p);
+  } else {
+    if (small_world) allreduce_shard_update_kernel<float, 4, 2><<<blocks, 512, 0, s>>>(p);
+    else allreduce_shard_update_kernel<float, 8, 1><<<blocks, 512, 0, s>>>(p);
+  }
   EB_LAUNCH_OK("allreduce_shard_update_kernel");
   return 0;
 }

@@ -22,6 +22,7 @@ device->host copy, one step delayed so it never stalls the GPU). ``keep_context=
 CUDA graphs and peer-mapped buffers alive on the ``SparkModel`` for the next ``fit`` call.
 """
 import os
+import time
 
 import numpy as np
 import torch
@@ -29,6 +30,7 @@ import torch
 from ..models import History
 from ..ops import engine as _engine
 from ..ops import native
+from ..utils import tracing
 from ..worker import partition_to_arrays
 from .symm import SymmetricMemory
 
@@ -43,9 +45,11 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
     master = spark_model.master_network
     if master.device != rt.device:
         master.to(rt.device)
-    eng = master._native_engine()
-    if not all(rt.all_gather_object(eng is not None)):
-        return None
+    with tracing.span('sync/engine'):
+        eng = master._native_engine()
+    with tracing.span('sync/agree'):
+        if not all(rt.all_gather_object(eng is not None)):
+            return None
     ctx = getattr(spark_model, '_sync_context', None)
     if ctx is None or ctx.eng is not eng:
         if ctx is not None:
@@ -265,9 +269,16 @@ class SyncContext:
     def _install_hooks(self):
         eng, dev = self.eng, self.rt.device
         self.comm_stream = torch.cuda.Stream(dev)
-        blocks = int(os.environ.get('ELEPHAS_B200_COMM_BLOCKS', '74'))
+        # the sharded kernel keeps 2-4 x world 16-byte peer loads in flight per thread: a small grid already
+        # saturates NVLink and leaves the SMs to the GEMMs it overlaps with (8 GPUs: 16 blocks 2.68 ms/step,
+        # 74 blocks 3.12); the replicated kernel streams the whole fp32 master and wants half the machine
+        blocks = int(os.environ.get('ELEPHAS_B200_COMM_BLOCKS', '16' if self.sharded else '74'))
+
+        skip = os.environ.get('ELEPHAS_B200_DEBUG_SKIP_COMM') == '1'  # timing experiments only: wrong results
 
         def hook(lo, n):
+            if skip:
+                return
             cur = torch.cuda.current_stream(dev)
             ready = torch.cuda.Event()
             ready.record(cur)
@@ -276,6 +287,8 @@ class SyncContext:
                 self._allreduce_update(lo, n, blocks=blocks)
 
         def join():
+            if skip:
+                return
             done = torch.cuda.Event()
             done.record(self.comm_stream)
             torch.cuda.current_stream(dev).wait_event(done)
@@ -334,7 +347,8 @@ class SyncContext:
     def run(self, partition, train_config, sync_rounds):
         rt, eng = self.rt, self.eng
         cfg = dict(train_config)
-        x, y = partition_to_arrays(partition)
+        with tracing.span('sync/partition_to_arrays'):
+            x, y = partition_to_arrays(partition)
         bs = self.bs = int(cfg.get('batch_size') or 32)
         epochs = int(cfg.get('epochs', 1))
         split = float(cfg.get('validation_split') or 0.0)
@@ -351,9 +365,11 @@ class SyncContext:
         with torch.cuda.device(rt.device):
             distributed = rt.distributed
             per_batch = distributed and frequency == 'batch' and sync_rounds != 'fit'
-            self._sync_start()
+            with tracing.span('sync/broadcast_start'):
+                self._sync_start()
             if distributed:
-                self._setup_comm(dtype_bf16=per_batch)
+                with tracing.span('sync/setup_comm'):
+                    self._setup_comm(dtype_bf16=per_batch)
             if per_batch:
                 self._install_hooks()
             else:
@@ -362,8 +378,9 @@ class SyncContext:
             steps = steps_local
             if distributed:
                 steps = int(rt.all_reduce_max_(torch.tensor([steps_local], device=rt.device))[0])
-            feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True))) \
-                if trainable else None
+            with tracing.span('sync/input_feeder'):
+                feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True))) \
+                    if trainable else None
             names = self.model.metrics_names
             pinned = [torch.zeros(8, dtype=torch.float64).pin_memory() for _ in range(2)]
             events = [torch.cuda.Event() for _ in range(2)]
@@ -377,6 +394,7 @@ class SyncContext:
                 if feeder:
                     feeder.start_epoch()
                 start = 0
+                t_loop = time.perf_counter()
                 for s in range(steps):
                     have = s < steps_local
                     buf = None
@@ -398,7 +416,9 @@ class SyncContext:
                     slot = (steps - 1) % 2
                     events[slot].synchronize()
                     batch_losses.append(float(pinned[slot][0] / max(float(pinned[slot][7]), 1.0)))
-                vals, count = eng.read_stats()
+                tracing.add_host('sync/step_loop', time.perf_counter() - t_loop)
+                with tracing.span('sync/read_stats'):
+                    vals, count = eng.read_stats()
                 logs = dict(zip(names, vals)) if count else {}
                 if before is not None and (sync_rounds != 'fit' or epoch == epochs - 1):
                     # delta = before - after (fp32, straight into peer-mapped memory), reset, fused reduce+update
@@ -411,9 +431,11 @@ class SyncContext:
                     logs.update({'val_' + k: v for k, v in zip(names, val)})
                 if logs:
                     history._append(epoch, logs)
-            self._gather_master()
+            with tracing.device_span('sync/gather_master'):
+                self._gather_master()
             t1.record()
-            torch.cuda.synchronize(rt.device)
+            with tracing.span('sync/drain'):
+                torch.cuda.synchronize(rt.device)
             self._check_watchdog()
             eng.delta_target = None
             eng._weights_dirty_in_model = True
@@ -423,7 +445,8 @@ class SyncContext:
             hist['batch_loss'] = batch_losses
         self.sm._last_sync_run = {'h2d_bytes_per_step': feeder.h2d_bytes_per_step if feeder else 0,
                                   'steps_per_epoch': steps, 'device_ms': t0.elapsed_time(t1)}
-        gathered = rt.all_gather_object((rt.rank, hist))
+        with tracing.span('sync/gather_histories'):
+            gathered = rt.all_gather_object((rt.rank, hist))
         return [h for _, h in sorted(gathered, key=lambda t: t[0])]
 
     # ------------------------------------------------------------- kernel timing

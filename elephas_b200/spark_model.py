@@ -41,6 +41,7 @@ from .models import optimizers as _optimizers
 from .parallel.runtime import get_runtime
 from .parameter.factory import ClientServerFactory
 from .spark import Matrix, Vector, get_spark_context, materialize_partitions
+from .utils import tracing
 from .utils.functional_utils import add_params, divide_by, get_neutral, subtract_params
 from .utils.rdd_utils import lp_to_simple_rdd, to_simple_rdd
 from .utils.serialization import model_to_dict
@@ -194,7 +195,8 @@ class SparkModel:
             rdd = rdd.repartition(rt.world_size)
         if self.mode not in MODES:
             raise ValueError("Choose from one of the modes: asynchronous, synchronous or hogwild")
-        self._fit(rdd, **kwargs)
+        with tracing.span('fit'):
+            self._fit(rdd, **kwargs)
 
     def _worker_args(self, train_config):
         model_json = self._master_network.to_json()
@@ -204,12 +206,14 @@ class SparkModel:
 
     def _fit(self, rdd, **kwargs):
         rt = get_runtime()
-        self._master_network.compile(optimizer=_optimizers.get(deepcopy(self.master_optimizer)),
-                                     loss=self.master_loss, metrics=self.master_metrics)
+        with tracing.span('fit/compile'):
+            self._master_network.compile(optimizer=_optimizers.get(deepcopy(self.master_optimizer)),
+                                         loss=self.master_loss, metrics=self.master_metrics)
         train_config = dict(kwargs)
         train_config.setdefault('batch_size', self.batch_size)  # D8: fall back to the constructor value
         train_config.setdefault('epochs', 1)
-        partitions = materialize_partitions(rdd)
+        with tracing.span('fit/materialize_partitions'):
+            partitions = materialize_partitions(rdd)
         mine = [(i, p) for i, p in enumerate(partitions) if i % rt.world_size == rt.rank]
 
         if self.mode in ('asynchronous', 'hogwild'):

@@ -322,11 +322,25 @@ class Model:
             isinstance(last, L.Softmax)
         return ends_softmax and self._loss_name == 'categorical_crossentropy'
 
+    def set_compute_dtype(self, dtype):
+        """Compute precision of the generic (torch autograd / cuDNN) path on CUDA devices: ``'bfloat16'`` runs the
+        forward/backward under bf16 autocast with fp32 master weights and an fp32 loss (what the native Dense
+        engine always does); ``'float32'`` (default) switches it off. No counterpart in the reference."""
+        if dtype not in ('float32', 'bfloat16'):
+            raise ValueError("compute dtype must be 'float32' or 'bfloat16', got %r" % (dtype,))
+        self._compute_dtype = dtype
+
+    def _autocast(self, xb):
+        on = getattr(self, '_compute_dtype', 'float32') == 'bfloat16' and xb.is_cuda
+        return torch.autocast('cuda', dtype=torch.bfloat16, enabled=on)
+
     def _torch_train_step(self, xb, yb):
         params = self.trainable_weights
         for p in params:
             p.grad = None
-        out = self(xb, training=True)
+        with self._autocast(xb):
+            out = self(xb, training=True)
+        out = out.float()
         per_sample = self._loss_fn(yb, out)
         loss = per_sample.mean()
         loss.backward()
@@ -424,9 +438,13 @@ class Model:
             xb = xt[start:start + block]
             if xb.shape[0] < block:
                 pad = torch.zeros((block - xb.shape[0],) + tuple(xb.shape[1:]), dtype=xb.dtype, device=xb.device)
-                outs.append(self(torch.cat([xb, pad], dim=0), training=False)[:xb.shape[0]])
+                with self._autocast(xb):
+                    o = self(torch.cat([xb, pad], dim=0), training=False)
+                outs.append(o.float()[:xb.shape[0]])
             else:
-                outs.append(self(xb, training=False))
+                with self._autocast(xb):
+                    o = self(xb, training=False)
+                outs.append(o.float())
         if not outs:
             return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
         return torch.cat(outs, dim=0).cpu().numpy()
@@ -448,7 +466,9 @@ class Model:
         step = max(batch_size, 8192)
         for start in range(0, n, step):
             xb, yb = xt[start:start + step], yt[start:start + step]
-            out = self(xb, training=False)
+            with self._autocast(xb):
+                out = self(xb, training=False)
+            out = out.float()
             vals = [self._loss_fn(yb, out)] + [fn(yb, out) for _, fn in self._metric_fns]
             for i, v in enumerate(vals):
                 sums[i] += float(v.double().sum())

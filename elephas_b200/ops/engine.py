@@ -37,6 +37,7 @@ from . import native
 
 _round8 = lambda v: (v + 7) // 8 * 8  # noqa: E731
 _CAPTURE_LOCK = threading.Lock()  # one CUDA-graph capture at a time per process
+_SIDE_STREAM = os.environ.get('ELEPHAS_B200_SIDE_STREAM', '1') != '0'  # bias-gradient sums next to the GEMMs
 
 _METRIC_FOR_FN = {'categorical_accuracy': 'categorical_accuracy', 'binary_accuracy': 'binary_accuracy',
                   'mean_absolute_error': 'mean_absolute_error', 'mean_squared_error': 'mean_squared_error',
@@ -233,6 +234,7 @@ class MLPEngine:
         self.step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.delta_target = None  # (bf16 tensor) when the optimizer must emit deltas instead of applying
         self.comm_hook = None     # callable(lo, n): a delta range is ready (synchronous data parallel)
+        self._aux_stream = None
         self.comm_join = None     # callable(): make the compute stream wait for all communication of the step
         self._in_warmup = False
         if self.trainable:
@@ -405,8 +407,18 @@ class MLPEngine:
         fused = self._fused_sgd()
         delta_mode = self.delta_target is not None
         lr = float(self.model.optimizer._config['learning_rate']) if fused else 0.0
+        # bias gradients (column sums of dZ, bandwidth-bound) run on a side stream next to the GEMMs: the
+        # clustered GEMM grid leaves 16 of the 148 SMs idle, and nothing needs the sums before the optimizer
+        side = self._side_stream()
+        cur = torch.cuda.current_stream(self.device)
         for op in reversed(self.ops):
             dz = buf.dz[op.index]
+            if side is not None:
+                ready = torch.cuda.Event()
+                ready.record(cur)
+                side.wait_event(ready)
+                with torch.cuda.stream(side):
+                    native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
             a_prev = buf.x16 if op.index == 0 else buf.acts[op.index - 1]
             off = op.w_seg.offset
             span = (op.w_seg.span + 63) // 64 * 64
@@ -435,7 +447,19 @@ class MLPEngine:
                             ldb=op.ld_in, alpha=lr, out_bf16=self.delta_target[off:], ldo=op.ld_in)
             if delta_mode:
                 self._emit(off, span)  # this layer's delta can travel while the earlier layers are computed
-            native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
+            if side is None:
+                native.colsum_bf16(dz, B, op.out_dim, self.g32[op.b_seg.offset:], ld=op.ld_out)
+        if side is not None:
+            done = torch.cuda.Event()
+            done.record(side)
+            cur.wait_event(done)
+
+    def _side_stream(self):
+        if not _SIDE_STREAM:
+            return None
+        if self._aux_stream is None:
+            self._aux_stream = torch.cuda.Stream(self.device)
+        return self._aux_stream
 
     def _optimizer(self):
         if self.delta_target is not None or self._fused_sgd():

@@ -307,6 +307,27 @@ class DataFrame:
     def repartition(self, n):
         return DataFrame(self._rdd.repartition(n), self.schema, self.sparkSession)
 
+    def limit(self, n):
+        return DataFrame(RDD([self.take(int(n))], self._rdd.context), self.schema, self.sparkSession)
+
+    def randomSplit(self, weights, seed=None):
+        """Random split by normalised ``weights`` (every row lands in exactly one part)."""
+        import random
+        total = float(sum(weights))
+        bounds, acc = [], 0.0
+        for w in weights:
+            acc += w / total
+            bounds.append(acc)
+        rng = random.Random(seed)
+        parts = [[] for _ in weights]
+        for row in self.collect():
+            u = rng.random()
+            for i, b in enumerate(bounds):
+                if u < b or i == len(bounds) - 1:
+                    parts[i].append(row)
+                    break
+        return [DataFrame(RDD([rows], self._rdd.context), self.schema, self.sparkSession) for rows in parts]
+
     def cache(self):
         return self
 

@@ -210,6 +210,9 @@ class SparkModel:
             self._master_network.compile(optimizer=_optimizers.get(deepcopy(self.master_optimizer)),
                                          loss=self.master_loss, metrics=self.master_metrics)
         train_config = dict(kwargs)
+        dtype = getattr(self._master_network, '_compute_dtype', None)
+        if dtype and dtype != 'float32':
+            train_config.setdefault('compute_dtype', dtype)  # replicas built from JSON inherit the master's setting
         train_config.setdefault('batch_size', self.batch_size)  # D8: fall back to the constructor value
         train_config.setdefault('epochs', 1)
         with tracing.span('fit/materialize_partitions'):

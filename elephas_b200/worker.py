@@ -70,6 +70,9 @@ class _WorkerBase:
                       metrics=self.master_metrics)
         model.set_weights(_weights_of(self.parameters))
         model.to(self.device if self.device is not None else default_device())
+        dtype = self.train_config.pop('compute_dtype', None)  # extension: bf16 autocast on the generic path
+        if dtype:
+            model.set_compute_dtype(dtype)
         self.model = model
         return model
 

@@ -22,6 +22,15 @@ static inline int grid_for(long n_items, int threads, int per_thread) {
   return static_cast<int>(blocks);
 }
 
+// Grid of the row-strided vector kernels: gx blocks across the columns, enough row lanes for ~8 blocks per SM.
+static inline dim3 rows_grid(int gx, long rows) {
+  long gy = (static_cast<long>(num_sms()) * 8 + gx - 1) / gx;
+  if (gy > rows) gy = rows;
+  if (gy > 65535) gy = 65535;
+  if (gy < 1) gy = 1;
+  return dim3(gx, static_cast<unsigned>(gy));
+}
+
 // dst[r][0..cols) = bf16(src[r][0..cols)), dst[r][cols..ld_dst) = 0. Stages fp32 inputs into the padded
 // bf16 layout the GEMM's TMA descriptors need.
 __global__ void stage_f32_to_bf16_kernel(const float* __restrict__ src, long ld_src, __nv_bfloat16* __restrict__ dst,
@@ -32,6 +41,28 @@ __global__ void stage_f32_to_bf16_kernel(const float* __restrict__ src, long ld_
     const long r = i / ld_dst;
     const int c = static_cast<int>(i - r * ld_dst);
     dst[i] = __float2bfloat16_rn(c < cols ? src[r * ld_src + c] : 0.f);
+  }
+}
+
+// Vector path of the above (cols, ld_dst multiples of 8, ld_src of 4, 16-byte aligned bases): a thread converts 8
+// consecutive elements (two 16-byte loads, one 16-byte store); x indexes column groups, y strides over rows, so
+// there is no integer division and four rows are in flight per thread.
+__global__ void __launch_bounds__(128) stage_f32_to_bf16_vec_kernel(const float* __restrict__ src, long ld_src,
+                                                                    __nv_bfloat16* __restrict__ dst, long ld_dst,
+                                                                    int rows, int cols) {
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= ld_dst) return;
+  const bool live = c < cols;
+#pragma unroll 4
+  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+    if (live) {
+      const float4 a = ld_nc_f4(src + r * ld_src + c);
+      const float4 b = ld_nc_f4(src + r * ld_src + c + 4);
+      o.x = pack_bf16x2(a.x, a.y); o.y = pack_bf16x2(a.z, a.w);
+      o.z = pack_bf16x2(b.x, b.y); o.w = pack_bf16x2(b.z, b.w);
+    }
+    *reinterpret_cast<uint4*>(dst + r * ld_dst + c) = o;
   }
 }
 
@@ -78,6 +109,108 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, long ld,
     for (int j = 1; j < 8; ++j) { s.x += red[j][threadIdx.x].x; s.y += red[j][threadIdx.x].y; }
     atomicAdd(out + c, s.x);
     if (c + 1 < cols) atomicAdd(out + c + 1, s.y);
+  }
+}
+
+// Vector path (cols, ld multiples of 8, 16-byte aligned): block = 32 x 8 threads owns 256 columns (16-byte loads,
+// 8 columns per thread) and a slab of rows, four rows in flight per thread; the eight row-partials per column meet
+// in shared memory and every thread publishes one column with a single atomicAdd.
+__global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, long ld, int rows,
+                                                              int cols, float* __restrict__ out) {
+  __shared__ float red[8][256];
+  const int c = blockIdx.x * 256 + threadIdx.x * 8;
+  const int rows_per_block = (rows + gridDim.y - 1) / gridDim.y;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (c < cols) {
+#pragma unroll 4
+    for (int r = r0 + threadIdx.y; r < r1; r += 8) {
+      const uint4 v = ld_nc_u4(x + static_cast<long>(r) * ld + c);
+      acc[0] += bf16_lo(v.x); acc[1] += bf16_hi(v.x); acc[2] += bf16_lo(v.y); acc[3] += bf16_hi(v.y);
+      acc[4] += bf16_lo(v.z); acc[5] += bf16_hi(v.z); acc[6] += bf16_lo(v.w); acc[7] += bf16_hi(v.w);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) red[threadIdx.y][threadIdx.x * 8 + j] = acc[j];
+  __syncthreads();
+  const int t = threadIdx.y * 32 + threadIdx.x;
+  const int col = blockIdx.x * 256 + t;
+  if (col < cols) {
+    float s = red[0][t];
+#pragma unroll
+    for (int j = 1; j < 8; ++j) s += red[j][t];
+    atomicAdd(out + col, s);
+  }
+}
+
+// Vector paths of the two kernels below (cols, ld multiples of 8): 8 elements per thread, 16-byte accesses, the
+// activation switch hoisted out of the element loop, the same Philox counters (two groups of four per thread).
+__global__ void __launch_bounds__(128) act_dropout_fwd_vec_kernel(const __nv_bfloat16* __restrict__ x,
+                                                                  __nv_bfloat16* __restrict__ y, long ld, int rows,
+                                                                  int cols, int act, float p, uint32_t thresh, float scale,
+                                                                  uint64_t seed, uint64_t stream,
+                                                                  const long long* step_ptr) {
+  if (step_ptr) stream += static_cast<uint64_t>(*step_ptr) * 1024ull;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= cols) return;
+#pragma unroll 4
+  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+    const uint4 v = ld_nc_u4(x + static_cast<long>(r) * ld + c);
+    float f[8] = {bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y),
+                  bf16_lo(v.z), bf16_hi(v.z), bf16_lo(v.w), bf16_hi(v.w)};
+    act_apply_chunk<8>(act, f);
+    if (p > 0.f) {
+      bool k0[4], k1[4];
+      dropout_keep4(seed, stream, static_cast<uint64_t>(r) * cols + c, thresh, k0);
+      dropout_keep4(seed, stream, static_cast<uint64_t>(r) * cols + c + 4, thresh, k1);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        f[e] = k0[e] ? f[e] * scale : 0.f;
+        f[e + 4] = k1[e] ? f[e + 4] * scale : 0.f;
+      }
+    }
+    uint4 o;
+    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+    *reinterpret_cast<uint4*>(y + static_cast<long>(r) * ld + c) = o;
+  }
+}
+
+__global__ void __launch_bounds__(128) act_dropout_bwd_vec_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                                  const __nv_bfloat16* __restrict__ y,
+                                                                  __nv_bfloat16* __restrict__ dx, long ld, int rows,
+                                                                  int cols, int act, float p, uint32_t thresh, float scale,
+                                                                  uint64_t seed, uint64_t stream,
+                                                                  const long long* step_ptr) {
+  if (step_ptr) stream += static_cast<uint64_t>(*step_ptr) * 1024ull;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+  if (c >= cols) return;
+  const float unscale = p > 0.f ? 1.f - p : 1.f;
+#pragma unroll 4
+  for (int r = blockIdx.y; r < rows; r += gridDim.y) {
+    const long i = static_cast<long>(r) * ld + c;
+    const uint4 vy = ld_nc_u4(y + i), vg = ld_nc_u4(dy + i);
+    float yy[8] = {bf16_lo(vy.x), bf16_hi(vy.x), bf16_lo(vy.y), bf16_hi(vy.y),
+                   bf16_lo(vy.z), bf16_hi(vy.z), bf16_lo(vy.w), bf16_hi(vy.w)};
+    float g[8] = {bf16_lo(vg.x), bf16_hi(vg.x), bf16_lo(vg.y), bf16_hi(vg.y),
+                  bf16_lo(vg.z), bf16_hi(vg.z), bf16_lo(vg.w), bf16_hi(vg.w)};
+    float d[8];
+    act_grad_chunk<8>(act, yy, unscale, d);  // act'(forward output before the dropout scaling)
+    bool k0[4] = {true, true, true, true}, k1[4] = {true, true, true, true};
+    if (p > 0.f) {
+      dropout_keep4(seed, stream, static_cast<uint64_t>(r) * cols + c, thresh, k0);
+      dropout_keep4(seed, stream, static_cast<uint64_t>(r) * cols + c + 4, thresh, k1);
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      g[e] = k0[e] ? g[e] * scale * d[e] : 0.f;
+      g[e + 4] = k1[e] ? g[e + 4] * scale * d[e + 4] : 0.f;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(g[0], g[1]); o.y = pack_bf16x2(g[2], g[3]);
+    o.z = pack_bf16x2(g[4], g[5]); o.w = pack_bf16x2(g[6], g[7]);
+    *reinterpret_cast<uint4*>(dx + i) = o;
   }
 }
 
@@ -163,7 +296,17 @@ extern "C" int eb_stage_f32_to_bf16(const float* src, int64_t ld_src, void* dst,
                                     int32_t cols, void* stream) {
   if (rows <= 0) return 0;
   if (ld_dst < cols || ld_src < cols) return fail("eb_stage_f32_to_bf16: leading dimensions smaller than cols");
-  stage_f32_to_bf16_kernel<<<grid_for(rows * ld_dst, 256, 4), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const bool vec = cols % 8 == 0 && ld_dst % 8 == 0 && ld_src % 4 == 0 && rows < (1L << 31) &&
+                   !(reinterpret_cast<uintptr_t>(src) & 15) && !(reinterpret_cast<uintptr_t>(dst) & 15);
+  if (vec) {
+    const int gx = static_cast<int>((ld_dst / 8 + 127) / 128);
+    stage_f32_to_bf16_vec_kernel<<<rows_grid(gx, rows), 128, 0, s>>>(src, ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst,
+                                                                   static_cast<int>(rows), cols);
+    EB_LAUNCH_OK("stage_f32_to_bf16_vec_kernel");
+    return 0;
+  }
+  stage_f32_to_bf16_kernel<<<grid_for(rows * ld_dst, 256, 4), 256, 0, s>>>(
       src, ld_src, static_cast<__nv_bfloat16*>(dst), ld_dst, rows, cols);
   EB_LAUNCH_OK("stage_f32_to_bf16_kernel");
   return 0;
@@ -186,6 +329,15 @@ extern "C" int eb_colsum_bf16(const void* x, int64_t ld, int32_t rows, int32_t c
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   if (!accumulate) EB_CUDA_OK(cudaMemsetAsync(out, 0, sizeof(float) * cols, s));
   dim3 block(32, 8);
+  if (cols % 8 == 0 && ld % 8 == 0 && !(reinterpret_cast<uintptr_t>(x) & 15)) {
+    const int cb = (cols + 255) / 256;
+    int rb = (num_sms() * 4 + cb - 1) / cb;
+    if (rb > (rows + 31) / 32) rb = (rows + 31) / 32;
+    if (rb < 1) rb = 1;
+    colsum_bf16_vec_kernel<<<dim3(cb, rb), block, 0, s>>>(static_cast<const __nv_bfloat16*>(x), ld, rows, cols, out);
+    EB_LAUNCH_OK("colsum_bf16_vec_kernel");
+    return 0;
+  }
   int col_blocks = (cols + 63) / 64;
   int row_blocks = (num_sms() * 4 + col_blocks - 1) / col_blocks;
   if (row_blocks > (rows + 63) / 64) row_blocks = (rows + 63) / 64;
@@ -200,6 +352,14 @@ extern "C" int eb_act_dropout_fwd(const void* x, void* y, int64_t ld, int32_t ro
                                   float drop_p, uint64_t seed, uint64_t drop_stream, const void* step_ptr, void* stream) {
   if (rows <= 0 || cols <= 0) return 0;
   const float scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  if (cols % 8 == 0 && ld % 8 == 0 && !(reinterpret_cast<uintptr_t>(x) & 15) && !(reinterpret_cast<uintptr_t>(y) & 15)) {
+    const int gx = (cols / 8 + 127) / 128;
+    act_dropout_fwd_vec_kernel<<<rows_grid(gx, rows), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), ld, rows, cols, act, drop_p,
+        dropout_threshold(drop_p), scale, seed, drop_stream, static_cast<const long long*>(step_ptr));
+    EB_LAUNCH_OK("act_dropout_fwd_vec_kernel");
+    return 0;
+  }
   act_dropout_fwd_kernel<<<grid_for(static_cast<long>(rows) * ((cols + 3) / 4), 256, 2), 256, 0,
                            static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), ld, rows, cols, act, drop_p,
@@ -213,6 +373,16 @@ extern "C" int eb_act_dropout_bwd(const void* dy, const void* y, void* dx, int64
                                   void* stream) {
   if (rows <= 0 || cols <= 0) return 0;
   const float scale = drop_p > 0.f ? 1.f / (1.f - drop_p) : 1.f;
+  if (cols % 8 == 0 && ld % 8 == 0 && !(reinterpret_cast<uintptr_t>(dy) & 15) && !(reinterpret_cast<uintptr_t>(y) & 15) &&
+      !(reinterpret_cast<uintptr_t>(dx) & 15)) {
+    const int gx = (cols / 8 + 127) / 128;
+    act_dropout_bwd_vec_kernel<<<rows_grid(gx, rows), 128, 0, static_cast<cudaStream_t>(stream)>>>(
+        static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<__nv_bfloat16*>(dx), ld,
+        rows, cols, act, drop_p, dropout_threshold(drop_p), scale, seed, drop_stream,
+        static_cast<const long long*>(step_ptr));
+    EB_LAUNCH_OK("act_dropout_bwd_vec_kernel");
+    return 0;
+  }
   act_dropout_bwd_kernel<<<grid_for(static_cast<long>(rows) * ((cols + 3) / 4), 256, 2), 256, 0,
                            static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<__nv_bfloat16*>(dx), ld,

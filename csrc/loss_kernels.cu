@@ -33,15 +33,18 @@ struct LossParams {
   float grad_scale;               // 1 / (rows of the whole batch)
 };
 
-__device__ __forceinline__ float warp_sum(float v) {
+// Reductions over the LANES (power of two) consecutive lanes that share a row.
+template <int LANES>
+__device__ __forceinline__ float group_sum(float v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  for (int o = LANES / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
   return v;
 }
 
-__device__ __forceinline__ float warp_max(float v) {
+template <int LANES>
+__device__ __forceinline__ float group_max(float v) {
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  for (int o = LANES / 2; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
   return v;
 }
 
@@ -83,31 +86,39 @@ __device__ __forceinline__ void loss_elem(int loss, float a, float y, float inv_
   }
 }
 
+// LANES lanes of a warp share one row (32 / LANES rows per warp): narrow heads (10 classes, one regression output)
+// keep every lane busy instead of leaving 22 - 31 of them idle, and the reductions shrink to log2(LANES) shuffles.
+template <int LANES>
 __global__ void __launch_bounds__(256) loss_kernel(const LossParams p) {
   __shared__ double block_stats[8][5];
+  constexpr int RPW = 32 / LANES;  // rows per warp
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int sub = lane % LANES;
   double acc[5] = {0, 0, 0, 0, 0};
   const float inv_n = 1.f / static_cast<float>(p.cols);
-  for (int row = blockIdx.x * 8 + warp; row < p.rows; row += gridDim.x * 8) {
-    const float* z = p.z + static_cast<long>(row) * p.ldz;
-    const float* y = p.ldy ? p.y + static_cast<long>(row) * p.ldy : nullptr;
-    const float y_scalar = p.ldy ? 0.f : p.y[row];
-    float* out = p.out ? p.out + static_cast<long>(row) * p.ldo : nullptr;
-    __nv_bfloat16* dz = p.dz ? p.dz + static_cast<long>(row) * p.lddz : nullptr;
+  for (int base = (blockIdx.x * 8 + warp) * RPW; base < p.rows; base += gridDim.x * 8 * RPW) {
+    const int row = base + lane / LANES;
+    const int cols = row < p.rows ? p.cols : 0;  // lanes of a missing row run the shuffles with empty loops
+    const int srow = row < p.rows ? row : base;
+    const float* z = p.z + static_cast<long>(srow) * p.ldz;
+    const float* y = p.ldy ? p.y + static_cast<long>(srow) * p.ldy : nullptr;
+    const float y_scalar = p.ldy ? 0.f : p.y[srow];
+    float* out = p.out ? p.out + static_cast<long>(srow) * p.ldo : nullptr;
+    __nv_bfloat16* dz = p.dz ? p.dz + static_cast<long>(srow) * p.lddz : nullptr;
     float loss_part = 0.f, m_abs = 0.f, m_sq = 0.f, m_ape = 0.f, m_bin = 0.f;
     float best_a = -INFINITY, best_y = -INFINITY;
     int arg_a = 0, arg_y = 0;
 
     if (p.act == EB_ACT_SOFTMAX) {
       float mx = -INFINITY;
-      for (int j = lane; j < p.cols; j += 32) mx = fmaxf(mx, z[j]);
-      mx = warp_max(mx);
+      for (int j = sub; j < cols; j += LANES) mx = fmaxf(mx, z[j]);
+      mx = group_max<LANES>(mx);
       float se = 0.f, sy = 0.f;
-      for (int j = lane; j < p.cols; j += 32) { se += expf(z[j] - mx); sy += y[j]; }
-      se = warp_sum(se);
-      sy = warp_sum(sy);
+      for (int j = sub; j < cols; j += LANES) { se += expf(z[j] - mx); sy += y[j]; }
+      se = group_sum<LANES>(se);
+      sy = group_sum<LANES>(sy);
       const float inv_se = 1.f / se;
-      for (int j = lane; j < p.cols; j += 32) {
+      for (int j = sub; j < cols; j += LANES) {
         const float a = expf(z[j] - mx) * inv_se, yy = y[j];
         if (out) out[j] = a;
         if (p.loss == EB_LOSS_CCE) {
@@ -120,7 +131,7 @@ __global__ void __launch_bounds__(256) loss_kernel(const LossParams p) {
         if (yy > best_y) { best_y = yy; arg_y = j; }
       }
     } else {
-      for (int j = lane; j < p.cols; j += 32) {
+      for (int j = sub; j < cols; j += LANES) {
         const float a = act_apply(p.act, z[j]);
         const float yy = y ? y[j] : y_scalar;
         if (out) out[j] = a;
@@ -135,17 +146,17 @@ __global__ void __launch_bounds__(256) loss_kernel(const LossParams p) {
         if (yy > best_y) { best_y = yy; arg_y = j; }
       }
     }
-    loss_part = warp_sum(loss_part);
-    m_abs = warp_sum(m_abs); m_sq = warp_sum(m_sq); m_ape = warp_sum(m_ape); m_bin = warp_sum(m_bin);
+    loss_part = group_sum<LANES>(loss_part);
+    m_abs = group_sum<LANES>(m_abs); m_sq = group_sum<LANES>(m_sq); m_ape = group_sum<LANES>(m_ape); m_bin = group_sum<LANES>(m_bin);
     // argmax across lanes; ties resolve to the lowest index, like np.argmax
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
+    for (int o = LANES / 2; o > 0; o >>= 1) {
       float oa = __shfl_xor_sync(0xffffffffu, best_a, o); int ia = __shfl_xor_sync(0xffffffffu, arg_a, o);
       if (oa > best_a || (oa == best_a && ia < arg_a)) { best_a = oa; arg_a = ia; }
       float oy = __shfl_xor_sync(0xffffffffu, best_y, o); int iy = __shfl_xor_sync(0xffffffffu, arg_y, o);
       if (oy > best_y || (oy == best_y && iy < arg_y)) { best_y = oy; arg_y = iy; }
     }
-    if (lane == 0) {
+    if (sub == 0 && row < p.rows) {
       acc[0] += loss_part;
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
@@ -161,6 +172,12 @@ __global__ void __launch_bounds__(256) loss_kernel(const LossParams p) {
         acc[1 + k] += v;
       }
     }
+  }
+  // fold the rows of a warp (lanes 0, LANES, 2*LANES, ...) into lane 0
+#pragma unroll
+  for (int k = 0; k < 5; ++k) {
+#pragma unroll
+    for (int o = 16; o >= LANES; o >>= 1) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
   }
   if (lane == 0)
     for (int k = 0; k < 5; ++k) block_stats[warp][k] = acc[k];
@@ -190,10 +207,21 @@ extern "C" int eb_loss_fwd_bwd(const EbLossArgs* a, void* stream) {
   p.rows = a->rows; p.cols = a->cols; p.loss = a->loss; p.act = a->act;
   for (int k = 0; k < 4; ++k) p.metrics[k] = a->metrics[k];
   p.grad_scale = a->grad_scale;
-  int blocks = (a->rows + 7) / 8;
+  // lanes per row: at most ~4 columns per lane
+  const int lanes = a->cols > 64 ? 32 : a->cols > 32 ? 16 : a->cols > 16 ? 8 : a->cols > 4 ? 4 : a->cols > 1 ? 2 : 1;
+  const int rows_per_block = 8 * (32 / lanes);
+  int blocks = (a->rows + rows_per_block - 1) / rows_per_block;
   const int cap = num_sms() * 8;
   if (blocks > cap) blocks = cap;
-  loss_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  switch (lanes) {
+    case 32: loss_kernel<32><<<blocks, 256, 0, s>>>(p); break;
+    case 16: loss_kernel<16><<<blocks, 256, 0, s>>>(p); break;
+    case 8: loss_kernel<8><<<blocks, 256, 0, s>>>(p); break;
+    case 4: loss_kernel<4><<<blocks, 256, 0, s>>>(p); break;
+    case 2: loss_kernel<2><<<blocks, 256, 0, s>>>(p); break;
+    default: loss_kernel<1><<<blocks, 256, 0, s>>>(p); break;
+  }
   EB_LAUNCH_OK("loss_kernel");
   return 0;
 }

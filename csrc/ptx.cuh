@@ -260,6 +260,19 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {
   return r;
 }
 
+// Read-only streaming loads the compiler may hoist and batch (not volatile: the data is never written by the kernel).
+__device__ __forceinline__ float4 ld_nc_f4(const float* p) {
+  float4 r;
+  asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ uint4 ld_nc_u4(const void* p) {
+  uint4 r;
+  asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
 __device__ __forceinline__ void st_v4(void* p, const uint4& v) {
   asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }

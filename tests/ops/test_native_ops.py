@@ -136,7 +136,41 @@ def test_stage_cast_delta_actdrop(native):
     assert torch.allclose(dx.float(), ref, atol=2e-2, rtol=2e-2)
 
 
+def test_vector_and_scalar_paths_of_elementwise_kernels(native):
+    """Every elementwise kernel has a 16-byte vector path (cols, ld multiples of 8) and a scalar one."""
+    torch.manual_seed(11)
+    for rows, cols, ld in ((64, 256, 264), (5, 4096, 4096), (300, 784, 784), (33, 93, 96), (7, 12, 16)):
+        x = torch.randn(rows, cols, device='cuda')
+        dst = torch.full((rows, ld), 7.0, dtype=torch.bfloat16, device='cuda')
+        native.stage_f32_to_bf16(x, dst, rows, cols)
+        assert torch.equal(dst[:, :cols], _bf(x)) and torch.all(dst[:, cols:] == 0), (rows, cols, ld)
+        h = _bf(torch.randn(rows, ld, device='cuda'))
+        out = torch.full((cols,), 3.0, device='cuda')
+        native.colsum_bf16(h, rows, cols, out, ld=ld)
+        assert torch.allclose(out, h[:, :cols].float().sum(0), atol=1e-3, rtol=1e-4), (rows, cols, ld)
+        native.colsum_bf16(h, rows, cols, out, accumulate=True, ld=ld)
+        assert torch.allclose(out, 2 * h[:, :cols].float().sum(0), atol=2e-3, rtol=1e-4)
+        # activation + dropout: forward statistics, backward mask identical to the forward one
+        y = torch.zeros_like(h)
+        native.act_dropout_fwd(h, y, rows, cols, act=2, drop_p=0.25, seed=5, drop_stream=3, ld=ld)
+        keep = y[:, :cols] != 0
+        if rows * cols > 2000:
+            assert 0.70 < keep.float().mean().item() < 0.80
+        ref = torch.sigmoid(h[:, :cols].float()) / 0.75
+        assert torch.allclose(y[:, :cols][keep].float(), ref[keep], atol=2e-2, rtol=2e-2)
+        dy, dx = _bf(torch.randn(rows, ld, device='cuda')), torch.zeros_like(h)
+        native.act_dropout_bwd(dy, y, dx, rows, cols, act=2, drop_p=0.25, seed=5, drop_stream=3, ld=ld)
+        a = y[:, :cols].float() * 0.75
+        ref = torch.where(keep, dy[:, :cols].float() / 0.75 * a * (1 - a), torch.zeros_like(a))
+        assert torch.allclose(dx[:, :cols].float(), ref, atol=2e-2, rtol=3e-2), (rows, cols, ld)
+        # no dropout: plain activation
+        native.act_dropout_fwd(h, y, rows, cols, act=1, ld=ld)
+        assert torch.equal(y[:, :cols], _bf(torch.relu(h[:, :cols].float())))
+
+
 LOSS_CASES = [('categorical_crossentropy', 'softmax', 10), ('binary_crossentropy', 'sigmoid', 1),
+              ('categorical_crossentropy', 'softmax', 24), ('categorical_crossentropy', 'softmax', 1000),
+              ('mean_squared_error', 'linear', 40), ('mean_squared_error', 'sigmoid', 2),
               ('mean_squared_error', 'linear', 1), ('mean_absolute_error', 'linear', 3),
               ('mean_squared_error', 'relu', 7), ('mean_absolute_percentage_error', 'linear', 1),
               ('logcosh', 'tanh', 5), ('mean_squared_logarithmic_error', 'softplus', 4)]

@@ -44,6 +44,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+__device__ __forceinline__ float ld_relaxed_sys_f32(const float* p) {
+  float v;
+  asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
 __device__ __forceinline__ uint4 ld_peer_v4(const void* p) {
   uint4 r;
   asm volatile("ld.global.relaxed.sys.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -400,6 +405,47 @@ __global__ void __launch_bounds__(256) ps_push_kernel(float* __restrict__ master
   }
 }
 
+// Push for stores that publish a bf16 mirror of the master (the operand the pull-fused GEMM, K2, reads through TMA):
+// master -= delta with red.add as above, then the updated values are read back (same thread, same address: the load
+// observes at least this thread's own reduction) and the mirror entries are refreshed. delta: fp32, bf16 or
+// before - after. Elements whose delta is zero are skipped - their mirror entry is already current.
+__global__ void __launch_bounds__(256) ps_push_mirror_kernel(float* __restrict__ master, __nv_bfloat16* __restrict__ mirror,
+                                                             const float* __restrict__ delta32,
+                                                             const __nv_bfloat16* __restrict__ delta16,
+                                                             const float* __restrict__ before,
+                                                             const float* __restrict__ after, long n) {
+  const long n4 = n / 4;
+  for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    float4 d;
+    if (delta32) {
+      d = reinterpret_cast<const float4*>(delta32)[i];
+    } else if (delta16) {
+      const uint2 v = reinterpret_cast<const uint2*>(delta16)[i];
+      d = make_float4(bf16_lo(v.x), bf16_hi(v.x), bf16_lo(v.y), bf16_hi(v.y));
+    } else {
+      const float4 b = reinterpret_cast<const float4*>(before)[i], a = reinterpret_cast<const float4*>(after)[i];
+      d = make_float4(b.x - a.x, b.y - a.y, b.z - a.z, b.w - a.w);
+    }
+    if (d.x != 0.f || d.y != 0.f || d.z != 0.f || d.w != 0.f) {
+      red_add_v4_f32_sys(master + 4 * i, -d.x, -d.y, -d.z, -d.w);
+      const uint4 w = ld_peer_v4(master + 4 * i);
+      uint2 o;
+      o.x = pack_bf16x2(__uint_as_float(w.x), __uint_as_float(w.y));
+      o.y = pack_bf16x2(__uint_as_float(w.z), __uint_as_float(w.w));
+      reinterpret_cast<uint2*>(mirror)[i] = o;
+    }
+  }
+  for (long i = n4 * 4 + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long>(gridDim.x) * blockDim.x) {
+    const float d = delta32 ? delta32[i] : delta16 ? __bfloat162float(delta16[i]) : before[i] - after[i];
+    if (d != 0.f) {
+      red_add_f32_sys(master + i, -d);
+      mirror[i] = __float2bfloat16_rn(ld_relaxed_sys_f32(master + i));
+    }
+  }
+}
+
 // dst32 <- master (peer loads), optionally dst16 <- bf16(master) in the same pass.
 __global__ void __launch_bounds__(256) ps_pull_kernel(const float* __restrict__ master, float* __restrict__ dst32,
                                                       __nv_bfloat16* __restrict__ dst16, long n) {
@@ -536,6 +582,22 @@ extern "C" int eb_ps_push(float* master, const float* delta, const float* before
   if (blocks < 1) blocks = 1;
   ps_push_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(master, delta, before, after, n);
   EB_LAUNCH_OK("ps_push_kernel");
+  return 0;
+}
+
+extern "C" int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
+                                 const float* before, const float* after, int64_t n, void* stream) {
+  if (n <= 0) return 0;
+  if (master == nullptr || mirror_bf16 == nullptr) return fail("eb_ps_push_mirror: master and mirror are required");
+  if (delta_f32 == nullptr && delta_bf16 == nullptr && (before == nullptr || after == nullptr))
+    return fail("eb_ps_push_mirror: need a delta (fp32 or bf16) or before/after");
+  long blocks = (n / 4 + 255) / 256;
+  if (blocks > num_sms() * 4) blocks = num_sms() * 4;
+  if (blocks < 1) blocks = 1;
+  ps_push_mirror_kernel<<<static_cast<int>(blocks), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      master, static_cast<__nv_bfloat16*>(mirror_bf16), delta_f32, static_cast<const __nv_bfloat16*>(delta_bf16), before,
+      after, n);
+  EB_LAUNCH_OK("ps_push_mirror_kernel");
   return 0;
 }
 

@@ -58,6 +58,7 @@ struct GemmDev {
   float beta;
   int bf16_from_f32;
   int tiles_m, tiles_n;
+  int b_copy_on;  // side-write every landed B tile through map_c (K2: the GEMM is the weight pull)
   int full_work, num_work;  // work items: [0, full_work) whole tiles, then the tail tiles as two half-N items each
 };
 
@@ -116,7 +117,7 @@ __device__ __forceinline__ WorkItem decode_work(int w, const GemmDev& p) {
 template <int BN, int CG, int MC>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                 const GemmDev p) {
+                 const __grid_constant__ CUtensorMap map_c, const GemmDev p) {
   using Cfg = GemmCfg<BN, CG>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B needs 1024-byte aligned tiles; the dynamic smem base is only 16-byte aligned by contract.
@@ -170,13 +171,21 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
+      // K2: B tiles of the first m-tile row are written back to the local copy one pipeline step after their
+      // load was issued (by then they have usually landed, so the producer rarely stalls)
+      int pend_stage = -1, pend_k0 = 0, pend_n0 = 0;
+      uint32_t pend_phase = 0;
       for (int t = first_tile; t < num_tiles; t += tile_step) {
         const WorkItem it = decode_work<BN>(t, p);
+        const bool copy_tile = (CG * MC == 1) && p.b_copy_on && it.tm == 0;
         const int m0 = ((it.tm * MC + group) * CG + cta_rank) * BLOCK_M;
         // a half-width item still loads full-height B boxes (constant transaction size); only width/CG rows are used
         const int n0 = it.tn * BN + it.n_off + cta_rank * (it.width / CG);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
+          if constexpr (CG * MC == 1) {
+            if (p.b_copy_on) tma_store_wait_read();  // an earlier side-write may still be reading this slot
+          }
           const int k0 = kb * BLOCK_K;
           uint8_t* sa = smem_a + stage * Cfg::A_STAGE;
           uint8_t* sb = smem_b + stage * Cfg::B_STAGE;
@@ -209,8 +218,25 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constan
             if (!p.b_mn) tma_load_2d_mcast_pair(&map_b, &full_bar[stage], dst, k0, n0 + 64 * group, mask);
             else tma_load_2d_mcast_pair(&map_b, &full_bar[stage], dst, n0 + 64 * group, k0, mask);
           }
+          if constexpr (CG * MC == 1) {
+            if (pend_stage >= 0) {
+              mbar_wait(&full_bar[pend_stage], pend_phase);
+              tma_store_2d(&map_c, smem_b + pend_stage * Cfg::B_STAGE, pend_k0, pend_n0);
+              tma_store_commit();
+              pend_stage = -1;
+            }
+            if (copy_tile) { pend_stage = stage; pend_phase = phase; pend_k0 = k0; pend_n0 = n0; }
+          }
           if (++stage == Cfg::STAGES) { stage = 0; phase ^= 1; }
         }
+      }
+      if constexpr (CG * MC == 1) {
+        if (pend_stage >= 0) {
+          mbar_wait(&full_bar[pend_stage], pend_phase);
+          tma_store_2d(&map_c, smem_b + pend_stage * Cfg::B_STAGE, pend_k0, pend_n0);
+          tma_store_commit();
+        }
+        if (p.b_copy_on) tma_store_wait();
       }
     }
   } else if (warp == 1) {
@@ -458,11 +484,15 @@ template <int BN, int CG, int MC>
 static int launch_gemm(const EbGemmArgs& a, GemmDev p, cudaStream_t stream) {
   using Cfg = GemmCfg<BN, CG>;
   static_assert(MC == 1 || (CG == 2 && Cfg::B_ROWS == 128), "B multicast is built for 256-wide CTA-pair tiles");
-  CUtensorMap map_a, map_b;
+  CUtensorMap map_a, map_b, map_c;
   if (!a.a_mn) { if (make_map(&map_a, a.A, a.M, a.K, a.lda, BLOCK_M, BLOCK_K)) return 1; }
   else         { if (make_map(&map_a, a.A, a.K, a.M, a.lda, BLOCK_K, 64)) return 1; }
   if (!a.b_mn) { if (make_map(&map_b, a.B, a.N, a.K, a.ldb, Cfg::B_ROWS / MC, BLOCK_K)) return 1; }
   else         { if (make_map(&map_b, a.B, a.K, a.N, a.ldb, BLOCK_K, 64)) return 1; }
+  // K2: destination of the side-written B tiles (same geometry as B); otherwise an unused copy of map_b
+  if (a.b_copy) { if (make_map(&map_c, a.b_copy, a.N, a.K, a.ldb, Cfg::B_ROWS / MC, BLOCK_K)) return 1; }
+  else map_c = map_b;
+  p.b_copy_on = a.b_copy != nullptr ? 1 : 0;
   constexpr int CLUSTER = CG * MC;
   p.tiles_m = (a.M + BLOCK_M * CLUSTER - 1) / (BLOCK_M * CLUSTER);
   p.tiles_n = (a.N + BN - 1) / BN;
@@ -504,12 +534,12 @@ static int launch_gemm(const EbGemmArgs& a, GemmDev p, cudaStream_t stream) {
   int clusters = max_clusters[dev & 63];
   // tail handling: split the tiles of a sparsely filled last wave into two half-width work items
   const int rem = tiles % clusters;
-  const bool split = BN == 256 && tiles > clusters && rem > 0 && 2 * rem <= clusters && !a.no_tail_split;
+  const bool split = BN == 256 && tiles > clusters && rem > 0 && 2 * rem <= clusters && !a.no_tail_split && !a.b_copy;
   p.full_work = split ? tiles - rem : tiles;
   p.num_work = split ? tiles + rem : tiles;
   if (clusters > p.num_work) clusters = p.num_work;
   cfg.gridDim = dim3(clusters * CLUSTER);
-  EB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, map_a, map_b, p));
+  EB_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, map_a, map_b, map_c, p));
   count_launch();
   return 0;
 }
@@ -585,6 +615,13 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
 
   int bn, cg, mc;
   pick_config(a, bn, cg, mc);
+  if (a.b_copy) {
+    // the pull GEMM runs on single CTAs: every B tile lands whole in one CTA's shared memory and is stored from there
+    if (a.b_mn) return fail("eb_gemm_bf16: b_copy (fused weight pull) needs a K-major B operand");
+    if (reinterpret_cast<uintptr_t>(a.b_copy) & 15) return fail("eb_gemm_bf16: b_copy must be 16-byte aligned");
+    cg = 1;
+    mc = 1;
+  }
   if (a.b_mn && bn < 64) return fail("eb_gemm_bf16: MN-major B needs block_n >= 64 (got %d)", bn);
   if (cg == 2 && bn < 128) return fail("eb_gemm_bf16: cta_group 2 needs block_n >= 128 (got %d)", bn);
   if (mc == 2) return launch_gemm<256, 2, 2>(a, p, stream);

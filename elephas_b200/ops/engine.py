@@ -235,6 +235,9 @@ class MLPEngine:
         self.delta_target = None  # (bf16 tensor) when the optimizer must emit deltas instead of applying
         self.comm_hook = None     # callable(lo, n): a delta range is ready (synchronous data parallel)
         self._aux_stream = None
+        self.pull_source = None   # device address of a bf16 weight mirror the training forward GEMMs pull from (K2)
+        self.pre_step = None      # callables run (and captured) at the start / end of every training step
+        self.post_step = None
         self.comm_join = None     # callable(): make the compute stream wait for all communication of the step
         self._in_warmup = False
         if self.trainable:
@@ -343,16 +346,27 @@ class MLPEngine:
         B = buf.B
         native.stage_f32_to_bf16(buf.x32, buf.x16, B, self.ops[0].in_dim)
         a = buf.x16
+        pull = self.pull_source if training else None
+
+        def weights(op):
+            # K2: with a pull source (address of a parameter server's bf16 mirror, usually peer memory) the GEMM reads
+            # the weight tiles from there through TMA and side-writes them into the local copy the backward pass uses
+            if pull is None:
+                return self._w16(op), None
+            return pull + 2 * op.w_seg.offset, self._w16(op)
+
         for op in self.ops[:-1]:
             out = buf.acts[op.index]
-            native.gemm(a, self._w16(op), B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
+            w, w_copy = weights(op)
+            native.gemm(a, w, B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
                         out_bf16=out, ldo=op.ld_out, bias=self.w32[op.b_seg.offset:],
                         act=native.ACT_IDS[op.act], drop_p=op.drop_p if training else 0.0, seed=self.seed,
-                        drop_stream=op.index, step_ptr=self.step if training else None)
+                        drop_stream=op.index, step_ptr=self.step if training else None, b_copy=w_copy)
             a = out
         op = self.ops[-1]
-        native.gemm(a, self._w16(op), B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
-                    out_f32=buf.z, ldo32=buf.z.stride(0), bias=self.w32[op.b_seg.offset:], act=0)
+        w, w_copy = weights(op)
+        native.gemm(a, w, B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
+                    out_f32=buf.z, ldo32=buf.z.stride(0), bias=self.w32[op.b_seg.offset:], act=0, b_copy=w_copy)
 
     def _loss(self, buf, with_grad, rows=None, grad_rows=None):
         op = self.ops[-1]
@@ -475,10 +489,14 @@ class MLPEngine:
             self.comm_join()
 
     def _train_body(self, buf):
+        if self.pre_step is not None:
+            self.pre_step()   # e.g. pull of the bias tail from a parameter server (captured with the step)
         self._forward(buf, training=True)
         self._loss(buf, with_grad=True)
         self._backward(buf)
         self._optimizer()
+        if self.post_step is not None and not self._in_warmup:
+            self.post_step()  # e.g. push of the step's delta into a parameter server
 
     # -------------------------------------------------------------- graph capture
     def _run(self, buf, which, body):
@@ -488,7 +506,8 @@ class MLPEngine:
             body()
             return
         is_train = which == 'train'
-        key = (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0)
+        key = (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0,
+               (self.pull_source or 0) if is_train else 0, id(self.post_step) if is_train else 0)
         graph = buf.graphs.get(key)
         if graph is None:
             with _CAPTURE_LOCK:
@@ -548,8 +567,9 @@ class MLPEngine:
         self.stats.copy_(stats)
 
     def invalidate_graphs(self):
-        for buf in self._buffers.values():
-            buf.graphs = {}
+        with _CAPTURE_LOCK:  # never destroy graph objects while another worker thread is capturing
+            for buf in self._buffers.values():
+                buf.graphs = {}
 
     # ------------------------------------------------------------------ public
     def _to_device_xy(self, x, y, buf, rows):

@@ -40,7 +40,8 @@ class GemmArgs(ctypes.Structure):
                 ('drop_p', c_float), ('seed', c_uint64), ('drop_stream', c_uint64), ('step_ptr', c_void_p),
                 ('out_bf16', c_void_p), ('ldo', c_int32),
                 ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float), ('bf16_from_f32', c_int32),
-                ('block_n', c_int32), ('cta_group', c_int32), ('multicast', c_int32), ('no_tail_split', c_int32)]
+                ('block_n', c_int32), ('cta_group', c_int32), ('multicast', c_int32), ('no_tail_split', c_int32),
+                ('b_copy', c_void_p)]
 
 
 class LossArgs(ctypes.Structure):
@@ -105,6 +106,7 @@ def load():
         lib.eb_ps_unlock.argtypes = [c_void_p, c_void_p]
         lib.eb_ps_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_ps_pull.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_ps_push_mirror.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
         lib.eb_ipc_export.argtypes = [c_void_p, c_void_p]
@@ -153,12 +155,19 @@ def launch_count() -> int:
 # ----------------------------------------------------------------------- GEMM
 def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=None, ldo=None, out_f32=None,
          ldo32=None, beta=0.0, alpha=1.0, epi=EPI_FWD, act=0, bias=None, aux=None, ldaux=None, drop_p=0.0, seed=0,
-         drop_stream=0, step_ptr=None, block_n=0, cta_group=0, bf16_from_f32=False):
-    """``C[M,N] = epilogue(A x B^T)`` on the tcgen05 GEMM (see ``EbGemmArgs`` for the operand layouts)."""
+         drop_stream=0, step_ptr=None, block_n=0, cta_group=0, bf16_from_f32=False, b_copy=None):
+    """``C[M,N] = epilogue(A x B^T)`` on the tcgen05 GEMM (see ``EbGemmArgs`` for the operand layouts).
+
+    ``B`` may be a raw device address (``int``, e.g. a peer-mapped parameter-server buffer; ``ldb`` is then
+    required); with ``b_copy`` (a local bf16 tensor of B's layout) the GEMM doubles as the weight pull (K2)."""
     g = GemmArgs()
     g.M, g.N, g.K = int(M), int(N), int(K)
     g.A, g.lda, g.a_mn = A.data_ptr(), int(lda if lda is not None else A.stride(0)), int(bool(a_mn))
-    g.B, g.ldb, g.b_mn = B.data_ptr(), int(ldb if ldb is not None else B.stride(0)), int(bool(b_mn))
+    if isinstance(B, int):
+        g.B, g.ldb, g.b_mn = B, int(ldb), int(bool(b_mn))
+    else:
+        g.B, g.ldb, g.b_mn = B.data_ptr(), int(ldb if ldb is not None else B.stride(0)), int(bool(b_mn))
+    g.b_copy = b_copy.data_ptr() if b_copy is not None else None
     g.alpha, g.epi, g.act = float(alpha), int(epi), int(act)
     g.bias = bias.data_ptr() if bias is not None else None
     g.aux = aux.data_ptr() if aux is not None else None
@@ -285,11 +294,11 @@ def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32
 
 
 # ------------------------------------------------------------ parameter server
-def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None):
+def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None, offset=0):
     lib = require()
     s = _stream(dst_f32.device if dst_f32 is not None else dst_bf16.device)
     n = int(n if n is not None else (dst_f32.numel() if dst_f32 is not None else dst_bf16.numel()))
-    mptr = master.data_ptr() if hasattr(master, 'data_ptr') else master
+    mptr = (master.data_ptr() if hasattr(master, 'data_ptr') else master) + 4 * int(offset)
     cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
     if locked:
         _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
@@ -300,17 +309,27 @@ def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None):
             _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
 
 
-def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=None):
+def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=None, mirror=None, delta_bf16=None,
+            offset=0):
+    """``master -= delta``. ``mirror`` (address of the store's bf16 mirror) switches to the kernel that also refreshes
+    the mirror; ``delta_bf16`` is accepted only there. ``offset``: first element of master / mirror this push covers."""
     lib = require()
-    ref = delta if delta is not None else before
+    ref = delta if delta is not None else (delta_bf16 if delta_bf16 is not None else before)
     s = _stream(ref.device)
     n = int(n if n is not None else ref.numel())
-    mptr = master.data_ptr() if hasattr(master, 'data_ptr') else master
+    mptr = (master.data_ptr() if hasattr(master, 'data_ptr') else master) + 4 * int(offset)
     cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
+    if delta_bf16 is not None and mirror is None:
+        raise NativeError("a bf16 delta can only be pushed into a store with a bf16 mirror")
     if locked:
         _check(lib.eb_ps_lock(cptr, s), 'eb_ps_lock')
     try:
-        _check(lib.eb_ps_push(mptr, _ptr(delta), _ptr(before), _ptr(after), n, s), 'eb_ps_push')
+        if mirror is not None:
+            mir = (mirror.data_ptr() if hasattr(mirror, 'data_ptr') else mirror) + 2 * int(offset)
+            _check(lib.eb_ps_push_mirror(mptr, mir, _ptr(delta), _ptr(delta_bf16), _ptr(before), _ptr(after), n, s),
+                   'eb_ps_push_mirror')
+        else:
+            _check(lib.eb_ps_push(mptr, _ptr(delta), _ptr(before), _ptr(after), n, s), 'eb_ps_push')
     finally:
         if locked:
             _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')

@@ -27,23 +27,29 @@ _stores_guard = threading.Lock()
 
 
 class DeviceStore:
-    def __init__(self, port, layout_model, arrays, mode, device, remote_handle=None):
+    def __init__(self, port, layout_model, arrays, mode, device, remote_handle=None, mirror=False):
         from .flat import FlatLayout
         self.port, self.mode, self.device = port, mode, torch.device(device)
         self.layout = FlatLayout(layout_model)
         self._raw = None
         self._remote_base = None
+        self.mirror = None  # bf16 copy of the master, kept current by every push: the operand of the pull-fused GEMM
         n = self.layout.numel
         if self.device.type == 'cuda':
             from ..ops import native
             ctrl_off = n * 4
+            mirror_off = ctrl_off + 256
             if remote_handle is None:
-                # owner: one IPC-exportable allocation holding the master weights and the control words
-                self._raw = native.RawBuffer(ctrl_off + 256, self.device)
+                # owner: one IPC-exportable allocation holding the master weights, the control words and (for
+                # stores that serve pull-fused GEMMs) the bf16 mirror
+                self._raw = native.RawBuffer(mirror_off + (n * 2 if mirror else 0), self.device)
                 base = self._raw.ptr
                 self.flat = self._raw.tensor(torch.float32, n)
                 self.ctrl = self._raw.tensor(torch.int32, 8, offset_bytes=ctrl_off)
                 self.layout.pack_arrays(arrays, out=self.flat)
+                if mirror:
+                    self.mirror = self._raw.tensor(torch.bfloat16, n, offset_bytes=mirror_off)
+                    native.cast_f32_to_bf16(self.flat, self.mirror)
             else:
                 # another rank: map the owner's allocation; pulls/pushes go over NVLink
                 with torch.cuda.device(self.device):
@@ -51,6 +57,8 @@ class DeviceStore:
                 self._remote_base = base
                 self.flat = _PeerPointer(base, n, self.device)
                 self.ctrl = _PeerPointer(base + ctrl_off, 8, self.device)
+                if mirror:
+                    self.mirror = _PeerPointer(base + mirror_off, n, self.device)
         else:
             self.flat = self.layout.pack_arrays(arrays, device=self.device)
             # ctrl[0]: sequence word (odd while a writer is inside), ctrl[1]: next ticket, ctrl[2]: now serving
@@ -79,6 +87,12 @@ class DeviceStore:
     def locked(self):
         return self.mode == 'asynchronous'
 
+    def refresh_mirror(self):
+        """Rebuild the bf16 mirror from the master (after the owner overwrote the master wholesale)."""
+        if self.mirror is not None and self._raw is not None:
+            from ..ops import native
+            native.cast_f32_to_bf16(self.flat, self.mirror)
+
     # ---------------------------------------------------------- flat, on device
     def pull_into(self, dst_flat, dst_bf16=None, stream=None):
         """``dst_flat <- master`` (and optionally the bf16 compute copy in the same pass)."""
@@ -94,13 +108,22 @@ class DeviceStore:
         if dst_bf16 is not None:
             dst_bf16.copy_(dst_flat)
 
-    def push_delta(self, delta_flat=None, before=None, after=None):
-        """``master -= delta`` where ``delta`` is given directly or as ``before - after`` (fused)."""
+    def pull_range_into(self, dst_flat, lo, n):
+        """``dst_flat[lo:lo+n] <- master[lo:lo+n]`` (device stores; used for the bias tail next to pull-fused GEMMs)."""
+        from ..ops import native
+        native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=self.locked, n=n, offset=lo)
+
+    def push_delta(self, delta_flat=None, before=None, after=None, delta_bf16=None):
+        """``master -= delta`` where ``delta`` is given directly (fp32, or bf16 for mirrored stores) or as
+        ``before - after`` (fused). A mirrored store refreshes its bf16 mirror in the same kernel."""
         self.pushes += 1
         if self.flat.is_cuda:
             from ..ops import native
-            native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked)
+            native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked, mirror=self.mirror,
+                           delta_bf16=delta_bf16)
             return
+        if delta_bf16 is not None:
+            delta_flat = delta_bf16.float()
         delta = delta_flat if delta_flat is not None else (before - after)
         if self.locked:
             with self._host_lock.writing():
@@ -136,20 +159,20 @@ class _PeerPointer:
         return self._numel
 
 
-def create_store(port, arrays, mode, model=None, device=None):
+def create_store(port, arrays, mode, model=None, device=None, mirror=False):
     from .runtime import default_device
     if model is None:
         raise ValueError("create_store needs the model whose weights it holds")
-    store = DeviceStore(port, model, arrays, mode, device or default_device())
+    store = DeviceStore(port, model, arrays, mode, device or default_device(), mirror=mirror)
     with _stores_guard:
         _stores[port] = store
     return store
 
 
-def attach_remote_store(port, handle, mode, model, device=None):
+def attach_remote_store(port, handle, mode, model, device=None, mirror=False):
     """Register a proxy for a store owned by another rank (``handle``: its CUDA IPC handle)."""
     from .runtime import default_device
-    store = DeviceStore(port, model, None, mode, device or default_device(), remote_handle=handle)
+    store = DeviceStore(port, model, None, mode, device or default_device(), remote_handle=handle, mirror=mirror)
     with _stores_guard:
         _stores[port] = store
     return store

@@ -243,10 +243,15 @@ class DeviceServer(BaseParameterServer):
     def __init__(self, model, port: int, mode: str, **kwargs):
         super().__init__(model, port, mode, **kwargs)
         self._store = None
+        # publish a bf16 mirror of the master next to it: workers then read the weights tile by tile from inside
+        # their forward GEMMs (pull fused into the GEMM) instead of copying them first; set by SparkModel for
+        # mode='hogwild', frequency='batch'
+        self.fused_pull = bool(kwargs.get('fused_pull', False))
 
     def start(self):
         from ..parallel.device_ps import create_store
-        self._store = create_store(self.port, self.weights, self.mode, model=self.master_network)
+        self._store = create_store(self.port, self.weights, self.mode, model=self.master_network,
+                                   mirror=self.fused_pull)
 
     def stop(self):
         from ..parallel.device_ps import destroy_store
@@ -264,6 +269,7 @@ class DeviceServer(BaseParameterServer):
         super().set_weights(weights)
         if self._store is not None:
             self._store.layout.pack_arrays(self.weights, out=self._store.flat)
+            self._store.refresh_mirror()
 
     def export_handle(self):
         """CUDA IPC handle of the master buffer (None on CPU): lets other ranks attach to the store."""

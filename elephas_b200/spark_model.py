@@ -26,6 +26,7 @@ Synchronous mode honours ``frequency`` (the reference ignores it there and avera
 restores average-once exactly; for ``epochs=1`` both are identical.
 """
 import json
+import os
 import subprocess
 import threading
 from copy import deepcopy
@@ -230,6 +231,12 @@ class SparkModel:
 
     # -- asynchronous / hogwild -------------------------------------------------
     def _fit_parameter_server(self, rt, partitions, mine, train_config):
+        # hogwild + per-batch pulls on GPUs: the store publishes a bf16 mirror and the workers' forward GEMMs read the
+        # weights straight from it (pull fused into the GEMM, K2); the locked mode keeps the copy-under-lock pull
+        fused_pull = (self.parameter_server_mode == 'nvlink' and self.mode == 'hogwild' and self.frequency == 'batch'
+                      and rt.device.type == 'cuda' and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
+        if hasattr(self.parameter_server, 'fused_pull'):
+            self.parameter_server.fused_pull = fused_pull
         if rt.is_driver:
             self.parameter_server.set_weights(self._master_network.get_weights())
             self.start_server()
@@ -239,7 +246,7 @@ class SparkModel:
             handle = rt.broadcast_object(self.parameter_server.export_handle() if rt.is_driver else None, src=0)
             if not rt.is_driver:
                 from .parallel.device_ps import attach_remote_store
-                attach_remote_store(self.port, handle, self.mode, self._master_network, rt.device)
+                attach_remote_store(self.port, handle, self.mode, self._master_network, rt.device, mirror=fused_pull)
         model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
         for key in ('input_mode', 'log_batch_loss', 'keep_context'):
             cfg.pop(key, None)

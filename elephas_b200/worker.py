@@ -49,6 +49,9 @@ def _weights_of(parameters):
     return parameters.value if hasattr(parameters, 'value') else parameters
 
 
+# counters for tests / diagnostics: which device paths actually ran in this process
+STATS = {'fused_pull_steps': 0}
+
 class _WorkerBase:
     def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
                  custom_objects, device=None):
@@ -250,6 +253,10 @@ class AsynchronousSparkWorker(_WorkerBase):
             dev = eng.device
             xd = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1).to(dev)
             yd = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1).to(dev)
+            if store.mirror is not None and not store.locked and trainable:
+                self._train_fused_pull(eng, store, xd, yd, epochs, batch_size)
+                torch.cuda.current_stream(eng.device).synchronize()
+                return
             for epoch in range(epochs):
                 if not trainable:
                     continue
@@ -263,3 +270,41 @@ class AsynchronousSparkWorker(_WorkerBase):
                     eng.train_step_device(buf)
                     store.push_delta(before=before, after=eng.w32)
         torch.cuda.current_stream(eng.device).synchronize()
+
+    @staticmethod
+    def _train_fused_pull(eng, store, xd, yd, epochs, batch_size):
+        """Hogwild, ``frequency='batch'``, device parameter server with a bf16 mirror: ONE graph replay per batch.
+
+        pull   = the forward GEMMs read their weight tiles from the store's mirror (peer memory over NVLink) through
+                 TMA and side-write them into the local copy the backward pass uses (K2); only the bias tail is copied
+        train  = forward / loss / backward on the native engine, the optimizer runs in delta mode
+        push   = ``master -= delta`` with ``red.add`` straight into the store + refresh of the mirror, same graph
+
+        Reference loop: ``get_parameters`` / ``set_weights`` / ``train_on_batch`` / ``update_parameters`` per batch
+        (``elephas/worker.py:116-127``)."""
+        import torch
+        lay = eng.layout
+        tail_lo, tail_n = lay.matrix_end, lay.numel - lay.matrix_end
+        delta16 = torch.zeros(lay.numel, dtype=torch.bfloat16, device=eng.device)
+        n = xd.shape[0]
+        saved = (eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step)
+        eng.pull_source = store.mirror.data_ptr()
+        eng.delta_target = delta16
+        eng.pre_step = (lambda: store.pull_range_into(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
+        eng.post_step = lambda: store.push_delta(delta_bf16=delta16)
+        try:
+            store.push_delta(delta_bf16=delta16)  # all-zero delta: loads the push kernel outside of graph capture
+            for _ in range(epochs):
+                for lo in range(0, n, batch_size):
+                    rows = min(batch_size, n - lo)
+                    buf = eng._buf(rows)
+                    buf.x32.copy_(xd[lo:lo + rows])
+                    buf.y32.copy_(yd[lo:lo + rows])
+                    eng.train_step_device(buf)
+                    STATS['fused_pull_steps'] += 1
+            torch.cuda.current_stream(eng.device).synchronize()
+        finally:
+            eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step = saved
+            eng.invalidate_graphs()  # the recorded steps hold the store's addresses
+        store.pull_into(eng.w32, eng.w16)  # leave the replica with a complete, current copy
+        eng._weights_dirty_in_model = True

@@ -83,6 +83,11 @@ typedef struct EbGemmArgs {
   int32_t cta_group;      /* 0 = auto, else 1 or 2 (CTA pair, UMMA M=256)        */
   int32_t multicast;      /* 0 = auto, 1 = off, 2 = B tile multicast across two CTA pairs (cluster of 4) */
   int32_t no_tail_split;  /* 1 disables the half-width scheduling of a sparse last wave */
+  void* b_copy;           /* K2 (pull fused into the GEMM): when set, B may live in peer memory (a parameter server or
+                             another rank's weights, read tile by tile through TMA over NVLink) and every B tile that
+                             lands in shared memory is also written to this local bf16 buffer (same [N][ldb] layout,
+                             K-major B only). The GEMM is the pull. No counterpart in the reference
+                             (client.get_parameters + set_weights + first layer forward, elephas/worker.py:104-119). */
 } EbGemmArgs;
 
 int eb_gemm_bf16(const EbGemmArgs* args, void* stream);
@@ -211,6 +216,11 @@ int eb_ps_lock(void* ctrl, void* stream);
 int eb_ps_unlock(void* ctrl, void* stream);
 int eb_ps_push(float* master, const float* delta, const float* before, const float* after, int64_t n, void* stream);
 int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, void* stream);
+/* Push into a store that publishes a bf16 mirror of its master (the B operand of the pull-fused GEMM, K2):
+ * master -= delta (red.add), then mirror = bf16(master) for the touched elements. Exactly one of delta_f32,
+ * delta_bf16 or before/after describes the delta. No counterpart in the reference. */
+int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
+                      const float* before, const float* after, int64_t n, void* stream);
 
 /* ------------------------------------------------------------ memory / IPC plumbing */
 int eb_device_malloc(void** ptr, int64_t bytes);   /* cudaMalloc + zero fill (IPC-exportable) */

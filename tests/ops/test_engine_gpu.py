@@ -136,6 +136,30 @@ def test_spark_model_matrix_on_gpu(spark_context, mode, ps, freq, workers):
     assert evals[0] < before
 
 
+def test_hogwild_batch_uses_the_pull_fused_gemm(spark_context):
+    """K2: hogwild + frequency='batch' on the device parameter server pulls through the forward GEMMs."""
+    from elephas_b200 import worker as _worker
+    x, y, xt, yt = make_mnist_like(1024, 300)
+    model = zoo.mnist_mlp()
+    model.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode='hogwild', frequency='batch', parameter_server_mode='nvlink', num_workers=2,
+                    port=next(_ports))
+    before_steps = _worker.STATS['fused_pull_steps']
+    before = sm.evaluate(xt, yt)
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=2, batch_size=64, verbose=0)
+    assert _worker.STATS['fused_pull_steps'] - before_steps == 2 * 2 * 8  # 2 workers x 2 epochs x 512/64 batches
+    after = sm.evaluate(xt, yt)
+    assert after[0] < before[0] and after[1] > 0.8
+    # the locked mode keeps the copy-under-lock pull
+    model2 = zoo.mnist_mlp()
+    model2.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    sm2 = SparkModel(model2, mode='asynchronous', frequency='batch', parameter_server_mode='nvlink', num_workers=2,
+                     port=next(_ports))
+    steps = _worker.STATS['fused_pull_steps']
+    sm2.fit(to_simple_rdd(spark_context, x, y), epochs=1, batch_size=64, verbose=0)
+    assert _worker.STATS['fused_pull_steps'] == steps
+
+
 def test_wide_mlp_shape_small_on_gpu(spark_context):
     """BASELINE config 4 at reduced width: regression MLP, synchronous, frequency='batch'."""
     rng = np.random.default_rng(0)

@@ -323,6 +323,63 @@ def test_parameter_server_kernels(native, locked):
         assert int(ctrl[1].item()) == 21 and int(ctrl[2].item()) == 21 and int(ctrl[0].item()) % 2 == 0
 
 
+@pytest.mark.parametrize('M,N,K', [(64, 128, 784), (64, 10, 128), (300, 200, 520), (4096, 1024, 512), (512, 4096, 4096)])
+def test_gemm_fused_pull_side_writes_the_weights(native, M, N, K):
+    """K2: the B operand is read from a 'remote' buffer and every tile is also stored into the local copy."""
+    torch.manual_seed(21)
+    ld = (K + 7) // 8 * 8
+    x = _bf(torch.randn(M, ld, device='cuda'))
+    x[:, K:] = 0
+    remote = _bf(torch.randn(N, ld, device='cuda') * 0.1)
+    local = torch.full((N, ld), 7.0, dtype=torch.bfloat16, device='cuda')
+    bias = torch.randn(N, device='cuda')
+    ldo = (N + 7) // 8 * 8
+    out = torch.zeros(M, ldo, dtype=torch.bfloat16, device='cuda')
+    ref_out = torch.zeros_like(out)
+    native.gemm(x, remote, M, N, K, out_bf16=ref_out, bias=bias, act=1)            # plain GEMM on the remote weights
+    native.gemm(x, remote.data_ptr(), M, N, K, ldb=ld, out_bf16=out, bias=bias, act=1, b_copy=local)  # raw address + copy
+    assert torch.equal(out, ref_out)
+    assert torch.equal(local[:, :K], remote[:, :K])
+    assert torch.all(local[:, K:] == 7.0)  # padding columns are outside the tensor map: untouched
+    ref = torch.relu(x[:, :K].float() @ remote[:, :K].float().t() + bias)
+    assert torch.allclose(out[:, :N].float(), ref, atol=3e-2, rtol=3e-2)
+
+
+@pytest.mark.parametrize('kind', ['f32', 'bf16', 'before_after'])
+def test_parameter_server_push_refreshes_the_bf16_mirror(native, kind):
+    torch.manual_seed(22)
+    n = 4096 * 3 + 5
+    master = torch.randn(n, device='cuda')
+    mirror = master.to(torch.bfloat16)
+    ctrl = torch.zeros(16, dtype=torch.int32, device='cuda')
+    expect = master.clone()
+    for it in range(3):
+        d = torch.randn(n, device='cuda') * 0.1
+        d[::7] = 0.0  # untouched elements keep their (already current) mirror entry
+        if kind == 'f32':
+            native.ps_push(master, ctrl, delta=d, mirror=mirror)
+            expect -= d
+        elif kind == 'bf16':
+            d16 = d.to(torch.bfloat16)
+            native.ps_push(master, ctrl, delta_bf16=d16, mirror=mirror, locked=True)
+            expect -= d16.float()
+        else:
+            after = expect - d
+            native.ps_push(master, ctrl, before=expect.clone(), after=after, mirror=mirror)
+            expect = expect - (expect - after)
+    torch.cuda.synchronize()
+    assert torch.allclose(master, expect, atol=1e-5)
+    assert torch.equal(mirror, master.to(torch.bfloat16))
+    # ranges: push into a slice of the store
+    native.ps_push(master, ctrl, delta=torch.ones(64, device='cuda'), mirror=mirror, offset=128, n=64)
+    torch.cuda.synchronize()
+    expect[128:192] -= 1.0
+    assert torch.allclose(master, expect, atol=1e-5) and torch.equal(mirror, master.to(torch.bfloat16))
+    tail = torch.zeros(n, device='cuda')
+    native.ps_pull(master, ctrl, tail[100:164], n=64, offset=100)
+    assert torch.equal(tail[100:164], master[100:164]) and float(tail[:100].abs().sum()) == 0.0
+
+
 def test_launch_counter_moves(native):
     before = native.launch_count()
     native.cast_f32_to_bf16(torch.zeros(64, device='cuda'), torch.zeros(64, dtype=torch.bfloat16, device='cuda'))

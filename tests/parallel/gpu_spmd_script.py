@@ -117,7 +117,8 @@ log("all_reduce_sum ok")
 # ---- 3. SparkModel matrix on GPUs ---------------------------------------------------------------------
 x, y, xt, yt = make_mnist_like(256 * W * 2, 300)
 CASES = [('synchronous', None, 'batch'), ('synchronous', None, 'epoch'), ('asynchronous', 'nvlink', 'epoch'),
-         ('asynchronous', 'nvlink', 'batch'), ('hogwild', 'nvlink', 'epoch'), ('asynchronous', 'socket', 'epoch')]
+         ('asynchronous', 'nvlink', 'batch'), ('hogwild', 'nvlink', 'epoch'), ('hogwild', 'nvlink', 'batch'),
+         ('asynchronous', 'socket', 'epoch')]
 for i, (mode, ps, freq) in enumerate(CASES):
     torch.manual_seed(R)  # different init per rank on purpose: fit must start every replica from rank 0's weights
     model = zoo.mnist_mlp()

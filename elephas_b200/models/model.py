@@ -194,6 +194,8 @@ class Model:
         self._device = device
         self._engine = None
         self._infer_engine = None
+        self._torch_step = None
+        self._torch_engine_failed = False
         return self
 
     @property
@@ -212,9 +214,48 @@ class Model:
             self._engine_key = key
         return self._engine
 
+    def _torch_engine(self):
+        """Graph-captured torch step (flat weights + native optimizer kernel) for models without a native engine."""
+        if self._device.type != 'cuda' or not self._compiled or getattr(self, '_torch_engine_failed', False):
+            return None
+        te = getattr(self, '_torch_step', None)
+        key = (self._device, id(self.optimizer))
+        if te is not None and (getattr(self, '_torch_step_key', None) != key or not te.still_valid()):
+            te = self._torch_step = None
+        if te is None:
+            from ..ops import torch_step as _ts
+            te = _ts.maybe_create(self)
+            if te is None:
+                self._torch_engine_failed = True
+                return None
+            self._torch_step, self._torch_step_key = te, key
+        return te
+
+    def _graphed_step(self, xb, yb):
+        """Run one training step through the captured graph; False when the model cannot be captured (the eager
+        path then takes over for good)."""
+        te = self._torch_engine()
+        if te is None:
+            return False
+        try:
+            te.train_step(xb, yb)
+            return True
+        except Exception as exc:  # a layer that synchronises or allocates in a way capture forbids
+            import warnings
+            warnings.warn("CUDA-graph capture of the training step failed (%s: %s); continuing eagerly"
+                          % (type(exc).__name__, exc))
+            self._torch_engine_failed = True
+            self._torch_step = None
+            for p in self.trainable_weights:
+                p.grad = None
+            return False
+
     def _sync_from_engine(self):
         if self._engine is not None:
             self._engine.export_weights()
+        te = getattr(self, '_torch_step', None)
+        if te is not None:
+            te.export_optimizer_state()
 
     def _push_to_engine(self):
         for eng in (self._engine, getattr(self, '_infer_engine', None)):
@@ -288,7 +329,18 @@ class Model:
         metrics = list(metrics) if metrics else []
         signature = (json.dumps(_optimizers.serialize(new_opt), sort_keys=True, default=str),
                      _losses.canonical_name(loss), tuple(str(m) for m in metrics), str(self._device))
-        same = self._compiled and getattr(self, '_compile_signature', None) == signature and self._engine is not None
+        unchanged = self._compiled and getattr(self, '_compile_signature', None) == signature
+        same = unchanged and self._engine is not None
+        te = getattr(self, '_torch_step', None)
+        if te is not None:
+            if unchanged and te.still_valid():
+                # identical configuration: keep the captured step (flat buffers, CUDA graphs), start from fresh slots
+                te.reset_optimizer()
+                self._torch_step_key = (self._device, id(new_opt))
+            else:
+                te.export_optimizer_state()  # the captured step's slots belong to the outgoing optimizer
+                self._torch_step = None
+        self._torch_engine_failed = False
         self.optimizer = new_opt
         self.loss = loss
         self._loss_name = _losses.canonical_name(loss)
@@ -362,7 +414,14 @@ class Model:
             yb = _as_tensor(y, self._device)
             if xb.dim() == 1:
                 xb = xb.unsqueeze(-1)
-            stats = self._torch_train_step(xb, yb)
+            te = self._torch_engine()
+            if te is not None:
+                te.stats.zero_()
+            if te is not None and self._graphed_step(xb, yb):
+                stats, _ = te.read_stats()
+                self.optimizer.iterations = int(te.step.item())
+            else:
+                stats = self._torch_train_step(xb, yb)
         return stats if len(stats) > 1 else stats[0]
 
     def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=0, callbacks=None, validation_split=0.0,
@@ -395,11 +454,25 @@ class Model:
         for epoch in range(initial_epoch, epochs):
             order = torch.randperm(n, device=self._device) if shuffle else torch.arange(n, device=self._device)
             sums = [0.0] * len(names)
+            te = self._torch_engine()
+            if te is not None:
+                te.stats.zero_()
+            graphed_rows = 0
             for start in range(0, n, batch_size):
                 idx = order[start:start + batch_size]
+                if te is not None and self._graphed_step(xt[idx], yt[idx]):
+                    graphed_rows += len(idx)  # loss / metric sums stay on the device until the epoch ends
+                    continue
+                te = None
                 stats = self._torch_train_step(xt[idx], yt[idx])
                 for i, s in enumerate(stats):
                     sums[i] += s * len(idx)
+            if graphed_rows:
+                te = self._torch_step
+                vals, rows = te.read_stats()
+                for i, v in enumerate(vals):
+                    sums[i] += v * rows
+                self.optimizer.iterations = int(te.step.item())
             logs = {k: (s / n if n else 0.0) for k, s in zip(names, sums)}
             if x_val is not None and len(x_val):
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)

@@ -1,0 +1,150 @@
+"""Synchronous mode for models the native Dense engine does not cover (CNNs, custom activations), one rank per GPU.
+
+Same semantics as ``sync_fast`` (and as the reference: every worker trains a replica from the same weights, the driver
+applies the mean of ``before - after``, ``elephas/spark_model.py:217-231``), same structure: the rank's copy of the
+master network *is* the replica. Its trainable weights live in the flat fp32 buffer of the graph-captured torch step
+(``ops/torch_step.py``), so a round is
+
+    before <- w32 ; [epoch of CUDA-graph replays] ; delta = before - w32 (K5, straight into peer-mapped memory) ;
+    w32 <- before ; fused P2P all-reduce + update (K6)
+
+without a model rebuild from JSON, without host copies of the weights and without re-capturing the step. Non-trainable
+state (BatchNormalization moving statistics) is averaged over ranks with one packed all-reduce per round.
+Per-batch synchronisation of generic models stays on the worker path (``SparkWorker``).
+"""
+import numpy as np
+import torch
+
+from ..models import History
+from ..ops import engine as _engine
+from ..ops import native
+from ..utils import tracing
+from ..worker import partition_to_arrays
+from .symm import SymmetricMemory
+
+IN_PLACE = object()
+
+
+def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
+    if rt.device.type != 'cuda' or not _engine.native_enabled():
+        return None
+    if len(partitions) != rt.world_size or len(mine) != 1:
+        return None
+    if rt.distributed and spark_model.frequency != 'epoch' and sync_rounds != 'fit':
+        return None
+    master = spark_model.master_network
+    if master.device != rt.device:
+        master.to(rt.device)
+    te = master._torch_engine()
+    if not all(rt.all_gather_object(te is not None)):
+        return None
+    ctx = getattr(spark_model, '_sync_torch_context', None)
+    if ctx is None or ctx.te is not te:
+        if ctx is not None:
+            ctx.close()
+        ctx = TorchSyncContext(spark_model, rt, master, te)
+        spark_model._sync_torch_context = ctx
+    histories = ctx.run(mine[0][1], train_config, sync_rounds)
+    if not train_config.get('keep_context'):
+        ctx.close()
+        spark_model._sync_torch_context = None
+    return IN_PLACE, histories
+
+
+class TorchSyncContext:
+    def __init__(self, spark_model, rt, model, te):
+        self.sm, self.rt, self.model, self.te = spark_model, rt, model, te
+        self.mem = None
+
+    def _setup_comm(self):
+        if self.mem is not None:
+            return
+        n = self.te.numel
+        self.mem = SymmetricMemory(self.rt, {'delta': n * 4, 'avg': n * 4, 'pad': 256})
+        self.comm_local = torch.zeros(16, dtype=torch.int32, device=self.rt.device)
+        self.delta = self.mem.local('delta', torch.float32, n)
+
+    def close(self):
+        if self.mem is not None:
+            torch.cuda.synchronize(self.rt.device)
+            self.mem.close()
+            self.mem = None
+
+    def _buffers(self):
+        return [w for w in self.model.weights if not w.requires_grad]
+
+    def _reduce_round(self, before):
+        """Apply the mean delta of all ranks to ``before`` (fused kernel) and average the non-trainable state."""
+        te, rt = self.te, self.rt
+        native.delta(before, te.w32, out_f32=self.delta)
+        te.w32.copy_(before)
+        native.allreduce_update(self.mem.ptrs('delta'), self.mem.ptrs('pad'), self.comm_local, te.numel, rt.rank,
+                                rt.world_size, 1.0 / rt.world_size, False, te.w32, w16=None,
+                                avg_ptrs=self.mem.ptrs('avg'), device=rt.device)
+        bufs = self._buffers()
+        if bufs:
+            packed = self._pack(bufs)
+            rt.all_reduce_sum_(packed)
+            packed /= rt.world_size
+            self._unpack(packed, bufs)
+
+    @staticmethod
+    def _pack(bufs):
+        return torch.cat([b.reshape(-1).float() for b in bufs])
+
+    @staticmethod
+    def _unpack(packed, bufs):
+        off = 0
+        with torch.no_grad():
+            for b in bufs:
+                b.copy_(packed[off:off + b.numel()].view(b.shape))
+                off += b.numel()
+
+    def run(self, partition, train_config, sync_rounds):
+        rt, te, model = self.rt, self.te, self.model
+        cfg = dict(train_config)
+        with tracing.span('sync_torch/partition_to_arrays'):
+            x, y = partition_to_arrays(partition)
+        bs = int(cfg.get('batch_size') or 32)
+        epochs = int(cfg.get('epochs', 1))
+        split = float(cfg.get('validation_split') or 0.0)
+        trainable = len(x) > bs  # reference guard (worker.py:41)
+        history = History()
+        with torch.cuda.device(rt.device):
+            distributed = rt.distributed
+            # every replica starts from rank 0's weights with a fresh optimizer, like the reference's workers
+            te.reset_optimizer()
+            model.optimizer.reset_state()
+            if distributed:
+                with tracing.span('sync_torch/broadcast_start'):
+                    rt.broadcast_(te.w32, src=0)
+                    bufs = self._buffers()
+                    if bufs:
+                        packed = self._pack(bufs)
+                        rt.broadcast_(packed, src=0)
+                        self._unpack(packed, bufs)
+                self._setup_comm()
+            xt = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(rt.device) if trainable else None
+            yt = torch.as_tensor(np.ascontiguousarray(y, dtype=np.float32)).to(rt.device) if trainable else None
+            before = torch.empty_like(te.w32) if distributed else None
+            for epoch in range(epochs):
+                if before is not None and (epoch == 0 or sync_rounds != 'fit'):
+                    before.copy_(te.w32)
+                if trainable:
+                    with tracing.span('sync_torch/epoch'):
+                        h = model.fit(xt, yt, batch_size=bs, epochs=epoch + 1, initial_epoch=epoch, verbose=0,
+                                      validation_split=split, shuffle=bool(cfg.get('shuffle', True)))
+                    for k, v in h.history.items():
+                        history.history.setdefault(k, []).extend(v)
+                if before is not None and (sync_rounds != 'fit' or epoch == epochs - 1):
+                    with tracing.span('sync_torch/reduce'):
+                        self._reduce_round(before)
+            torch.cuda.synchronize(rt.device)
+            if self.mem is not None:
+                status = int(self.comm_local[8].item())
+                if status:
+                    raise RuntimeError("rank %d: peer rank %d never reached a fused all-reduce (watchdog fired)"
+                                       % (rt.rank, status - 1))
+        hist = dict(history.history) if trainable else None
+        gathered = rt.all_gather_object((rt.rank, hist))
+        return [h for _, h in sorted(gathered, key=lambda t: t[0])]

@@ -147,10 +147,11 @@ class SparkModel:
 
     def release_context(self):
         """Free engine-side state kept by ``fit(..., keep_context=True)`` (peer-mapped buffers)."""
-        ctx = getattr(self, '_sync_context', None)
-        if ctx is not None:
-            ctx.close()
-            self._sync_context = None
+        for attr in ('_sync_context', '_sync_torch_context'):
+            ctx = getattr(self, attr, None)
+            if ctx is not None:
+                ctx.close()
+                setattr(self, attr, None)
 
     @property
     def master_network(self):
@@ -318,6 +319,10 @@ class SparkModel:
 
         # Fast path: native engines + fused delta all-reduce/update, one worker per rank.
         fast = sync_engine.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
+        if fast is None and rt.device.type == 'cuda':
+            # models without a native Dense engine: graph-captured torch step on flat weights, same in-place scheme
+            from .parallel import sync_torch
+            fast = sync_torch.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
         if fast is not None:
             _, histories = fast
             self._training_histories.extend(histories)

@@ -182,3 +182,106 @@ def test_fallback_for_custom_activation_stays_on_torch():
     m.to('cuda')
     assert m._native_engine() is None
     assert np.isfinite(m.train_on_batch(np.random.rand(16, 4).astype('f4'), np.random.rand(16, 1).astype('f4')))
+
+
+# ---------------------------------------------------------------- graph-captured torch step (non-Dense models)
+def _small_cnn():
+    from elephas_b200.models.layers import BatchNormalization, Conv2D, Flatten, MaxPooling2D
+    return Sequential([Conv2D(8, 3, padding='same', activation='relu', input_shape=(8, 8, 3)), BatchNormalization(),
+                       MaxPooling2D(2), Conv2D(16, 3, padding='same', activation='relu'), Flatten(),
+                       Dense(10, activation='softmax')])
+
+
+@pytest.mark.parametrize('opt_name', ['sgd_momentum', 'adam', 'rmsprop'])
+def test_graphed_torch_step_matches_eager(monkeypatch, opt_name):
+    """Flat weights + native optimizer kernel + CUDA-graph replay == the eager torch path, step for step."""
+    def make_opt():
+        return {'sgd_momentum': lambda: SGD(learning_rate=0.05, momentum=0.9, decay=1e-3),
+                'adam': lambda: Adam(learning_rate=0.01), 'rmsprop': lambda: RMSprop(learning_rate=0.005)}[opt_name]()
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(96, 8, 8, 3)).astype(np.float32)
+    y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, 96)]
+    torch.manual_seed(1)
+    a = _small_cnn()
+    a.compile(make_opt(), 'categorical_crossentropy', ['acc'])
+    w0 = a.get_weights()
+    b = _small_cnn()
+    b.compile(make_opt(), 'categorical_crossentropy', ['acc'])
+    b.set_weights(w0)
+    a.to('cuda')
+    b.to('cuda')
+    ha = a.fit(x, y, batch_size=32, epochs=3, shuffle=False)          # captured
+    assert a._torch_engine() is not None and a._torch_step.graphs, "the graphed step did not run"
+    monkeypatch.setenv('ELEPHAS_B200_TORCH_GRAPHS', '0')
+    hb = b.fit(x, y, batch_size=32, epochs=3, shuffle=False)          # eager
+    assert b._torch_engine() is None
+    for wa, wb in zip(a.get_weights(), b.get_weights()):
+        assert np.allclose(wa, wb, atol=2e-4, rtol=2e-3), np.abs(wa - wb).max()
+    assert np.allclose(ha.history['loss'], hb.history['loss'], rtol=1e-3, atol=1e-4)
+    assert np.allclose(ha.history['acc'], hb.history['acc'], atol=0.03)
+    assert a.optimizer.iterations == b.optimizer.iterations == 9
+    # train_on_batch goes through the same graph and reports the step's own statistics
+    sa = a.train_on_batch(x[:32], y[:32])
+    sb = b.train_on_batch(x[:32], y[:32])
+    assert abs(sa[0] - sb[0]) < 2e-3 and abs(sa[1] - sb[1]) < 0.04
+
+
+def test_graphed_torch_step_survives_recompile_save_and_device_moves(tmp_path):
+    rng = np.random.default_rng(4)
+    x = rng.normal(size=(64, 8, 8, 3)).astype(np.float32)
+    y = np.eye(10, dtype=np.float32)[rng.integers(0, 10, 64)]
+    m = _small_cnn()
+    m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
+    m.to('cuda')
+    m.fit(x, y, batch_size=32, epochs=2)
+    first = m.evaluate(x, y)[0]
+    path = str(tmp_path / 'cnn.h5')
+    m.save(path)                                   # exports the flat optimizer slots
+    m2 = load_model(path)
+    assert m2.optimizer.iterations == 4
+    m2.to('cuda')
+    m2.fit(x, y, batch_size=32, epochs=2)          # resumes: imports the slots into a new flat buffer
+    assert m2.evaluate(x, y)[0] < first
+    m.compile(SGD(learning_rate=0.01), 'categorical_crossentropy', ['acc'])   # new optimizer: new engine
+    m.fit(x, y, batch_size=32, epochs=1)
+    m.to('cpu')                                    # weights leave the flat buffer; the eager CPU path takes over
+    m.fit(x, y, batch_size=32, epochs=1)
+    assert np.isfinite(m.evaluate(x, y)[0])
+
+
+def test_graphed_torch_step_bf16_autocast_trains():
+    rng = np.random.default_rng(5)
+    x = rng.normal(size=(128, 8, 8, 3)).astype(np.float32)
+    labels = (x.mean(axis=(1, 2, 3)) > 0).astype(int)
+    y = np.eye(10, dtype=np.float32)[labels]
+    m = _small_cnn()
+    m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
+    m.set_compute_dtype('bfloat16')
+    m.to('cuda')
+    h = m.fit(x, y, batch_size=32, epochs=8)
+    assert h.history['loss'][-1] < h.history['loss'][0] and m._torch_step.graphs
+
+
+def test_sync_torch_path_trains_in_place_and_reuses_the_graph(spark_context):
+    """SparkModel synchronous on a model without a native Dense engine: the master network is the replica, the
+    captured step survives the per-fit recompile (same configuration)."""
+    rng = np.random.default_rng(6)
+    x = rng.normal(size=(256, 8, 8, 3)).astype(np.float32)
+    labels = (x.mean(axis=(1, 2, 3)) > 0).astype(int)
+    y = np.eye(10, dtype=np.float32)[labels]
+    m = _small_cnn()
+    m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(m, mode='synchronous', frequency='epoch', num_workers=1)
+    before = sm.evaluate(x, y)[0]
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=3, batch_size=32, verbose=0, validation_split=0.125)
+    te = sm.master_network._torch_step
+    assert te is not None and len(te.graphs) >= 1
+    n_graphs = len(te.graphs)
+    hist = sm.training_histories[-1]
+    assert len(hist['loss']) == 3 and 'val_loss' in hist and hist['loss'][-1] < hist['loss'][0]
+    mid = sm.evaluate(x, y)[0]
+    assert mid < before
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=2, batch_size=32, verbose=0, validation_split=0.125)
+    assert sm.master_network._torch_step is te and len(te.graphs) == n_graphs   # nothing was re-captured
+    assert sm.evaluate(x, y)[0] < mid
+    assert len(sm.predict(x[:10])) == 10

@@ -35,6 +35,8 @@ def parse():
 
 
 def timed(rt, fn):
+    from elephas_b200.utils import tracing
+    tracing.reset()
     """Wall-clock seconds of ``fn()`` bracketed by synchronize + barrier, max over ranks."""
     import torch
     cuda = rt.device.type == 'cuda'
@@ -49,6 +51,8 @@ def timed(rt, fn):
     dt = time.perf_counter() - t0
     t = torch.tensor([dt], dtype=torch.float64, device=rt.device)
     rt.all_reduce_max_(t)
+    if tracing.enabled() and rt.is_driver:
+        print(tracing.report(), file=sys.stderr)
     return float(t[0]), out
 
 
@@ -139,7 +143,7 @@ def config_resnet(args, rt):
     from elephas_b200.spark import SparkContext
     bs = args.batch_size or 64
     steps = 10
-    epochs = args.epochs or 2
+    epochs = args.epochs or 4
     side, classes = 224, 1000
     n_rank = bs * steps
     rng = np.random.default_rng(7 + rt.rank)

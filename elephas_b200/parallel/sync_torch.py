@@ -124,8 +124,9 @@ class TorchSyncContext:
                         rt.broadcast_(packed, src=0)
                         self._unpack(packed, bufs)
                 self._setup_comm()
-            xt = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(rt.device) if trainable else None
-            yt = torch.as_tensor(np.ascontiguousarray(y, dtype=np.float32)).to(rt.device) if trainable else None
+            with tracing.span('sync_torch/h2d'):
+                xt = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(rt.device) if trainable else None
+                yt = torch.as_tensor(np.ascontiguousarray(y, dtype=np.float32)).to(rt.device) if trainable else None
             before = torch.empty_like(te.w32) if distributed else None
             for epoch in range(epochs):
                 if before is not None and (epoch == 0 or sync_rounds != 'fit'):
@@ -146,5 +147,6 @@ class TorchSyncContext:
                     raise RuntimeError("rank %d: peer rank %d never reached a fused all-reduce (watchdog fired)"
                                        % (rt.rank, status - 1))
         hist = dict(history.history) if trainable else None
-        gathered = rt.all_gather_object((rt.rank, hist))
+        with tracing.span('sync_torch/gather_histories'):
+            gathered = rt.all_gather_object((rt.rank, hist))
         return [h for _, h in sorted(gathered, key=lambda t: t[0])]

@@ -69,6 +69,8 @@ def _split_bounds(n, parts):
 def _concat_blocks(partitions):
     """Merge partitions into one; keeps the array fast path when every partition is a block."""
     partitions = [p for p in partitions if len(p)]
+    if len(partitions) == 1 and isinstance(partitions[0], (PairBlock, ArrayBlock)):
+        return partitions[0]  # nothing to merge: the new partitions are views of the one block (no copy)
     if partitions and all(isinstance(p, PairBlock) for p in partitions):
         return PairBlock(np.concatenate([np.asarray(p.x) for p in partitions]),
                          np.concatenate([np.asarray(p.y) for p in partitions]))

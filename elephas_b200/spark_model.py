@@ -191,10 +191,11 @@ class SparkModel:
         rt = get_runtime()
         if rt.is_driver:
             print('>>> Fit model')
-        if self.num_workers:
-            rdd = rdd.repartition(self.num_workers)
-        elif rt.distributed:
-            rdd = rdd.repartition(rt.world_size)
+        with tracing.span('fit/repartition'):
+            if self.num_workers:
+                rdd = rdd.repartition(self.num_workers)
+            elif rt.distributed:
+                rdd = rdd.repartition(rt.world_size)
         if self.mode not in MODES:
             raise ValueError("Choose from one of the modes: asynchronous, synchronous or hogwild")
         with tracing.span('fit'):

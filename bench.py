@@ -183,7 +183,10 @@ def run_ours(args, rt):
         rt.all_reduce_max_(t)
         e2e_ms = float(t[0])
         if tracing.enabled() and rt.is_driver:
+            from elephas_b200.parallel import sync_fast
             print(tracing.report(), file=sys.stderr)
+            print('host bf16 staging choices (rows, cols, threads) -> use: %r' % (sync_fast._HOST_BF16_CHOICE,),
+                  file=sys.stderr)
         hist = spark_model.training_histories[-1]
         assert len(hist['batch_loss']) == K, "one loss read-back per step expected"
         e2e = {'value': round(N * B * K / (e2e_ms / 1e3), 2), 'unit': 'samples/sec',

@@ -235,6 +235,7 @@ class MLPEngine:
         self.delta_target = None  # (bf16 tensor) when the optimizer must emit deltas instead of applying
         self.comm_hook = None     # callable(lo, n): a delta range is ready (synchronous data parallel)
         self._aux_stream = None
+        self.input_bf16 = False   # training batches are delivered straight into buf.x16 (already bf16)
         self.pull_source = None   # device address of a bf16 weight mirror the training forward GEMMs pull from (K2)
         self.pre_step = None      # callables run (and captured) at the start / end of every training step
         self.post_step = None
@@ -344,7 +345,8 @@ class MLPEngine:
 
     def _forward(self, buf, training):
         B = buf.B
-        native.stage_f32_to_bf16(buf.x32, buf.x16, B, self.ops[0].in_dim)
+        if not (self.input_bf16 and training):  # (streamed training inputs arrive already cast to bf16 by the host: half the PCIe bytes)
+            native.stage_f32_to_bf16(buf.x32, buf.x16, B, self.ops[0].in_dim)
         a = buf.x16
         pull = self.pull_source if training else None
 
@@ -507,7 +509,8 @@ class MLPEngine:
             return
         is_train = which == 'train'
         key = (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0,
-               (self.pull_source or 0) if is_train else 0, id(self.post_step) if is_train else 0)
+               (self.pull_source or 0) if is_train else 0, id(self.post_step) if is_train else 0,
+               bool(self.input_bf16) if is_train else False)
         graph = buf.graphs.get(key)
         if graph is None:
             with _CAPTURE_LOCK:

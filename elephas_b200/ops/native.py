@@ -107,6 +107,7 @@ def load():
         lib.eb_ps_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_ps_pull.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_ps_push_mirror.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
         lib.eb_ipc_export.argtypes = [c_void_p, c_void_p]
@@ -333,6 +334,18 @@ def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=N
     finally:
         if locked:
             _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+
+
+# ------------------------------------------------------------------ host staging
+def host_f32_to_bf16(src, dst, rows=None, cols=None, threads=4):
+    """``dst[:rows, :cols] = bf16(src[:rows, :cols])`` on CPU threads (host tensors; ``dst`` usually pinned, bf16 or
+    int16 storage), padding columns of ``dst`` zeroed. The GIL is released for the duration of the call."""
+    rows = int(src.shape[0] if rows is None else rows)
+    cols = int(src.shape[1] if cols is None else cols)
+    if src.is_cuda or dst.is_cuda or src.dtype != torch.float32 or dst.element_size() != 2:
+        raise NativeError("host_f32_to_bf16 needs a host fp32 source and a host 16-bit destination")
+    _check(load().eb_host_f32_to_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), rows, cols,
+                                      int(threads)), 'eb_host_f32_to_bf16')
 
 
 # --------------------------------------------------------------- memory / IPC

@@ -65,6 +65,12 @@ class DeviceStore:
             self.ctrl = torch.zeros(8, dtype=torch.int32, device=self.device)
         self._host_lock = RWLock()
         self.pushes = 0
+        # Locked operations of all worker threads of this process go through ONE stream, enqueued under a host mutex:
+        # a ticket-lock kernel that spins on the GPU must never sit in front of the unlock kernel it waits for, and two
+        # streams of one GPU can share a hardware queue. On a single in-order stream the previous holder's unlock always
+        # precedes the next lock, so a lock kernel only ever waits for holders on OTHER GPUs (other ranks).
+        self._ps_stream = None
+        self._enqueue_lock = threading.Lock()
 
     def export_handle(self):
         from ..ops import native
@@ -94,11 +100,30 @@ class DeviceStore:
             native.cast_f32_to_bf16(self.flat, self.mirror)
 
     # ---------------------------------------------------------- flat, on device
+    def _device_op(self, fn):
+        """Run ``fn`` (which enqueues lock / kernel / unlock) - on the caller's stream when the store is unlocked, on
+        the store's own stream, ordered against the caller's stream with events, when it is locked."""
+        if not self.locked:
+            fn()
+            return
+        cur = torch.cuda.current_stream(self.device)
+        with self._enqueue_lock:
+            if self._ps_stream is None:
+                self._ps_stream = torch.cuda.Stream(self.device)
+            ready = torch.cuda.Event()
+            ready.record(cur)
+            self._ps_stream.wait_event(ready)
+            with torch.cuda.stream(self._ps_stream):
+                fn()
+            done = torch.cuda.Event()
+            done.record(self._ps_stream)
+        cur.wait_event(done)
+
     def pull_into(self, dst_flat, dst_bf16=None, stream=None):
         """``dst_flat <- master`` (and optionally the bf16 compute copy in the same pass)."""
         if self.flat.is_cuda:
             from ..ops import native
-            native.ps_pull(self.flat, self.ctrl, dst_flat, dst_bf16, locked=self.locked)
+            self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat, dst_bf16, locked=self.locked))
             return
         if self.locked:
             with self._host_lock.reading():
@@ -111,7 +136,8 @@ class DeviceStore:
     def pull_range_into(self, dst_flat, lo, n):
         """``dst_flat[lo:lo+n] <- master[lo:lo+n]`` (device stores; used for the bias tail next to pull-fused GEMMs)."""
         from ..ops import native
-        native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=self.locked, n=n, offset=lo)
+        self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=self.locked,
+                                               n=n, offset=lo))
 
     def push_delta(self, delta_flat=None, before=None, after=None, delta_bf16=None):
         """``master -= delta`` where ``delta`` is given directly (fp32, or bf16 for mirrored stores) or as
@@ -119,8 +145,8 @@ class DeviceStore:
         self.pushes += 1
         if self.flat.is_cuda:
             from ..ops import native
-            native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked, mirror=self.mirror,
-                           delta_bf16=delta_bf16)
+            self._device_op(lambda: native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked,
+                                                   mirror=self.mirror, delta_bf16=delta_bf16))
             return
         if delta_bf16 is not None:
             delta_flat = delta_bf16.float()

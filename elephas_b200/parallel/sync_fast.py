@@ -63,8 +63,18 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
     return IN_PLACE, histories
 
 
+_HOST_BF16_CHOICE = {}  # (rows, cols, threads) -> bool: measured once per process
+
+
 class _InputFeeder:
-    """Delivers batches into the engine's static input buffers."""
+    """Delivers batches into the engine's static input buffers.
+
+    ``device``: the partition is uploaded once, batches are gathered on the device.
+    ``stream``: every batch crosses PCIe while the previous step computes. The features are cast to bf16 on the host
+    first (``eb_host_f32_to_bf16``, CPU thread pool, bit-identical to the device cast the engine would do) - half the
+    bytes per step - by a helper thread that runs two batches ahead: convert into a pinned slot, enqueue the H2D copy
+    on the copy stream, record an event the compute stream waits on.
+    """
 
     def __init__(self, eng, x, y, batch_size, mode, shuffle):
         self.eng, self.bs, self.shuffle = eng, batch_size, shuffle
@@ -80,17 +90,66 @@ class _InputFeeder:
             raise ValueError("input_mode must be 'device' or 'stream', got %r" % (mode,))
         self.mode = mode
         self.h2d_bytes_per_step = 0
+        self.host_bf16 = False
+        self.pool = None
         if mode == 'device':
             self.xd = self.x_host.to(dev, non_blocking=True)
             self.yd = self.y_host.to(dev, non_blocking=True)
         else:
             self.copy_stream = torch.cuda.Stream(dev)
-            self.stage = [(torch.empty(batch_size, self.x_host.shape[1], dtype=torch.float32, device=dev),
-                           torch.empty(batch_size, self.y_host.shape[1], dtype=torch.float32, device=dev),
-                           torch.cuda.Event()) for _ in range(2)]
-            self.h2d_bytes_per_step = batch_size * (self.x_host.shape[1] + self.y_host.shape[1]) * 4
+            cols, ycols = self.x_host.shape[1], self.y_host.shape[1]
+            self.threads = int(os.environ.get('ELEPHAS_B200_HOST_THREADS', '6'))
+            self.host_bf16 = self._choose_host_bf16(eng, batch_size)
+            if self.host_bf16:
+                ld = eng.ops[0].ld_in
+                self.pinned = [torch.empty(batch_size, ld, dtype=torch.bfloat16).pin_memory() for _ in range(3)]
+                self.pinned_free = [None, None, None]  # event: the slot's last H2D copy has finished
+                self.stage = [(torch.empty(batch_size, ld, dtype=torch.bfloat16, device=dev),
+                               torch.empty(batch_size, ycols, dtype=torch.float32, device=dev),
+                               torch.cuda.Event()) for _ in range(2)]
+                self.h2d_bytes_per_step = batch_size * (ld * 2 + ycols * 4)
+                from concurrent.futures import ThreadPoolExecutor
+                self.pool = ThreadPoolExecutor(max_workers=1, thread_name_prefix='elephas-feeder')
+                self.jobs = {}
+            else:
+                self.stage = [(torch.empty(batch_size, cols, dtype=torch.float32, device=dev),
+                               torch.empty(batch_size, ycols, dtype=torch.float32, device=dev),
+                               torch.cuda.Event()) for _ in range(2)]
+                self.h2d_bytes_per_step = batch_size * (cols + ycols) * 4
             self.consumed = [None, None]
         self.order = None
+
+    def _choose_host_bf16(self, eng, batch_size):
+        """Cast the features to bf16 on the host (half the PCIe bytes) or stream them as fp32 and cast on the device?
+        ``ELEPHAS_B200_HOST_BF16=1|0`` decides; otherwise one batch is timed both ways, once per process and input
+        width: with pipelining a step pays max(host cast, bf16 copy) against the fp32 copy. Few cores per GPU favour
+        the fp32 copy, many GPUs sharing the host's PCIe switches favour the cast."""
+        forced = os.environ.get('ELEPHAS_B200_HOST_BF16', 'auto')
+        if forced in ('0', '1'):
+            return forced == '1'
+        rows = min(batch_size, self.n)
+        cols = self.x_host.shape[1]
+        key = (rows, cols, self.threads)
+        if key not in _HOST_BF16_CHOICE:
+            dev = eng.device
+            dst16 = torch.empty(rows, eng.ops[0].ld_in, dtype=torch.bfloat16).pin_memory()
+            d32 = torch.empty(rows, cols, dtype=torch.float32, device=dev)
+            src = self.x_host[:rows]
+            native.host_f32_to_bf16(src, dst16, rows, cols, threads=self.threads)  # starts the pool, touches the pages
+            t0 = time.perf_counter()
+            native.host_f32_to_bf16(src, dst16, rows, cols, threads=self.threads)
+            t_cast = (time.perf_counter() - t0) * 1e3
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with torch.cuda.stream(self.copy_stream):
+                d32.copy_(src, non_blocking=True)
+                e0.record(self.copy_stream)
+                d32.copy_(src, non_blocking=True)
+                e1.record(self.copy_stream)
+            e1.synchronize()
+            t_copy32 = e0.elapsed_time(e1)
+            _HOST_BF16_CHOICE[key] = max(t_cast, 0.5 * t_copy32) < 0.9 * t_copy32
+            tracing.add_host('sync/input_calibration cast %.2f ms copy32 %.2f ms' % (t_cast, t_copy32), 0.0)
+        return _HOST_BF16_CHOICE[key]
 
     @staticmethod
     def _pinned(a, n):
@@ -98,6 +157,11 @@ class _InputFeeder:
         (e.g. NumPy views of ``torch.empty(..., pin_memory=True)``) are used in place."""
         t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.float32).reshape(n, -1))
         return t if t.is_pinned() else t.pin_memory()
+
+    def close(self):
+        if self.pool is not None:
+            self.pool.shutdown(wait=True)
+            self.pool = None
 
     def start_epoch(self):
         dev = self.eng.device
@@ -107,7 +171,14 @@ class _InputFeeder:
         else:
             self.order = None
         if self.mode == 'stream':
-            self._prefetch(0, 0)
+            if self.host_bf16:
+                for fut in self.jobs.values():
+                    fut.result()
+                self.jobs = {}
+                self._submit(0, 0)
+                self._submit(1, self.bs)
+            else:
+                self._prefetch(0, 0)
 
     def _host_batch(self, start, rows):
         if self.order is None:
@@ -115,6 +186,7 @@ class _InputFeeder:
         idx = self.order[start:start + rows]
         return self.x_host.index_select(0, idx).pin_memory(), self.y_host.index_select(0, idx).pin_memory()
 
+    # -- fp32 streaming (ELEPHAS_B200_HOST_BF16=0) ---------------------------------------------------------
     def _prefetch(self, step, start):
         rows = min(self.bs, self.n - start)
         if rows <= 0:
@@ -130,8 +202,41 @@ class _InputFeeder:
             ys[:rows].copy_(yh, non_blocking=True)
             ev.record(self.copy_stream)
 
+    # -- bf16 streaming: helper thread converts and uploads two batches ahead ----------------------------------
+    def _submit(self, step, start):
+        rows = min(self.bs, self.n - start)
+        if rows <= 0:
+            return
+        consumed = self.consumed[step % 2]
+        self.jobs[step] = self.pool.submit(self._job, step, start, rows, consumed)
+
+    def _job(self, step, start, rows, consumed):
+        dev = self.eng.device
+        with torch.cuda.device(dev):
+            pslot, dslot = step % 3, step % 2
+            if self.order is None:
+                xh, yh = self.x_host[start:start + rows], self.y_host[start:start + rows]
+            else:
+                idx = self.order[start:start + rows]
+                xh, yh = self.x_host.index_select(0, idx), self.y_host.index_select(0, idx).pin_memory()
+            free = self.pinned_free[pslot]
+            if free is not None:
+                free.synchronize()  # the copy that last read this pinned slot is done
+            native.host_f32_to_bf16(xh, self.pinned[pslot], rows, xh.shape[1], threads=self.threads)
+            xs, ys, ev = self.stage[dslot]
+            if consumed is not None:
+                self.copy_stream.wait_event(consumed)  # the compute stream has drained this device slot
+            with torch.cuda.stream(self.copy_stream):
+                xs[:rows].copy_(self.pinned[pslot][:rows], non_blocking=True)
+                ys[:rows].copy_(yh, non_blocking=True)
+                done = torch.cuda.Event()
+                done.record(self.copy_stream)
+                ev.record(self.copy_stream)
+            self.pinned_free[pslot] = done
+        return rows
+
     def load(self, step, start, buf):
-        """Fill ``buf.x32`` / ``buf.y32`` with batch ``step``; returns the number of rows."""
+        """Fill the engine's input buffers with batch ``step``; returns the number of rows."""
         rows = min(self.bs, self.n - start)
         if self.mode == 'device':
             if self.order is not None:
@@ -145,14 +250,22 @@ class _InputFeeder:
         slot = step % 2
         xs, ys, ev = self.stage[slot]
         cur = torch.cuda.current_stream(self.eng.device)
-        cur.wait_event(ev)
-        buf.x32.copy_(xs[:rows])
+        if self.host_bf16:
+            self.jobs.pop(step).result()  # converted and enqueued (normally long done: it ran during step - 2)
+            cur.wait_event(ev)
+            buf.x16.copy_(xs[:rows])
+        else:
+            cur.wait_event(ev)
+            buf.x32.copy_(xs[:rows])
         buf.y32.copy_(ys[:rows])
         done = torch.cuda.Event()
         done.record(cur)
         self.consumed[slot] = done
-        # the next batch goes into the other slot: its H2D copy overlaps this step's compute
-        self._prefetch(step + 1, start + rows)
+        if self.host_bf16:
+            self._submit(step + 2, start + rows + self.bs)
+        else:
+            # the next batch goes into the other slot: its H2D copy overlaps this step's compute
+            self._prefetch(step + 1, start + rows)
         return rows
 
 
@@ -381,6 +494,7 @@ class SyncContext:
             with tracing.span('sync/input_feeder'):
                 feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True))) \
                     if trainable else None
+            eng.input_bf16 = bool(feeder is not None and feeder.host_bf16)
             names = self.model.metrics_names
             pinned = [torch.zeros(8, dtype=torch.float64).pin_memory() for _ in range(2)]
             events = [torch.cuda.Event() for _ in range(2)]
@@ -438,6 +552,9 @@ class SyncContext:
                 torch.cuda.synchronize(rt.device)
             self._check_watchdog()
             eng.delta_target = None
+            eng.input_bf16 = False
+            if feeder is not None:
+                feeder.close()
             eng._weights_dirty_in_model = True
             self.model.optimizer.iterations = int(eng.step.item())
         hist = dict(history.history) if trainable else None
@@ -460,6 +577,7 @@ class SyncContext:
                 self._setup_comm(dtype_bf16=True)
                 self._install_hooks()
             feeder = _InputFeeder(eng, x, y, bs, input_mode, False)
+            eng.input_bf16 = feeder.host_bf16
             feeder.start_epoch()
             torch.cuda.synchronize(rt.device)
             rt.barrier()
@@ -476,5 +594,7 @@ class SyncContext:
             torch.cuda.synchronize(rt.device)
             rt.barrier()
             eng.delta_target = None
+            eng.input_bf16 = False
+            feeder.close()
             self._gather_master()
             return e0.elapsed_time(e1)

@@ -222,6 +222,14 @@ int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, v
 int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
                       const float* before, const float* after, int64_t n, void* stream);
 
+/* ------------------------------------------------------------ host side of the input pipeline
+ * dst[r][0..cols) = bf16(src[r][0..cols)) (round to nearest even, bit-identical to the device cast), padding columns
+ * [cols, ld_dst) zeroed; runs on `threads` CPU threads (persistent pool) and returns when the batch is converted.
+ * src/dst are host pointers (dst usually pinned). Halves the bytes a step sends over PCIe. No counterpart in the
+ * reference. */
+int eb_host_f32_to_bf16(const float* src, int64_t ld_src, void* dst, int64_t ld_dst, int64_t rows, int32_t cols,
+                        int32_t threads);
+
 /* ------------------------------------------------------------ memory / IPC plumbing */
 int eb_device_malloc(void** ptr, int64_t bytes);   /* cudaMalloc + zero fill (IPC-exportable) */
 int eb_device_free(void* ptr);

@@ -12,6 +12,7 @@ for K in ${STEPS_LIST:-20 60}; do
   echo "rc=$?" >> $L
   grep '^{' gpurun_out/tr.json >> $L
   grep -A30 "^host " gpurun_out/tr.err >> $L
+  grep "staging choices" gpurun_out/tr.err >> $L
   grep -i "error\|Traceback" gpurun_out/tr.err | head -3 >> $L
 done
 cat $L

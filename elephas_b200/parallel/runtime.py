@@ -30,6 +30,42 @@ def default_device():
     return torch.device('cpu')
 
 
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(','):
+        if not part:
+            continue
+        lo, _, hi = part.partition('-')
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+def bind_to_gpu_numa_node(device):
+    """Pin this rank's process to the CPUs of the NUMA node its GPU hangs off (sysfs: PCI device -> numa_node ->
+    cpulist). Pinned host buffers are then first-touched on that node, so the per-step host->device copies do not
+    cross the socket interconnect - with eight ranks streaming inputs at once that link is the first to saturate.
+    Returns the node, or None when there is nothing to do (one node, no sysfs, ``ELEPHAS_B200_NUMA_BIND=0``)."""
+    if os.environ.get('ELEPHAS_B200_NUMA_BIND', '1') == '0' or not hasattr(os, 'sched_setaffinity'):
+        return None
+    try:
+        props = torch.cuda.get_device_properties(device)
+        bdf = '%04x:%02x:%02x.0' % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        with open('/sys/bus/pci/devices/%s/numa_node' % bdf) as fh:
+            node = int(fh.read().strip())
+        if node < 0:
+            return None
+        with open('/sys/devices/system/node/node%d/cpulist' % node) as fh:
+            cpus = _parse_cpulist(fh.read())
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus or cpus == allowed:
+            return node if cpus else None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError, RuntimeError):
+        return None
+
+
 class Runtime:
     def __init__(self):
         self.device = default_device()
@@ -37,8 +73,11 @@ class Runtime:
         self.rank = int(os.environ.get('RANK', 0))
         self.local_rank = int(os.environ.get('LOCAL_RANK', 0))
         self._group = None
+        self.numa_node = None
         if self.device.type == 'cuda':
             torch.cuda.set_device(self.device)
+            if self.world_size > 1:
+                self.numa_node = bind_to_gpu_numa_node(self.device)
         if self.world_size > 1:
             self._init_process_group()
 

@@ -39,3 +39,11 @@ def test_two_ranks(tmp_path, mode, ps, freq):
     assert r0['eval'][0] < r0['before'][0]
     if mode == 'synchronous':
         assert r0['hist'] == 2
+
+
+def test_cpulist_parser_and_numa_binding_is_harmless_without_a_gpu():
+    from elephas_b200.parallel import runtime
+    assert runtime._parse_cpulist('0-3,8,10-11\n') == {0, 1, 2, 3, 8, 10, 11}
+    assert runtime._parse_cpulist('') == set()
+    import torch
+    assert runtime.bind_to_gpu_numa_node(torch.device('cpu')) is None  # no PCI device behind it: nothing happens

@@ -208,14 +208,21 @@ class ElephasTransformer(Model, HasKerasModelConfig, HasLabelCol, HasOutputCol, 
                 return list(np.vstack(chunks))
             return list(model.predict(feats))
 
-        predictions = rdd.mapPartitions(predict_partition)
-        if getattr(self, 'model_type', None) == ModelType.REGRESSION:
-            predictions = predictions.map(lambda x: tuple([float(np.asarray(x).reshape(-1)[0])]))
-            output_field = StructField(output_col, DoubleType(), True)
-        else:
-            predictions = predictions.map(lambda x: tuple([[float(v) for v in np.asarray(x).reshape(-1)]]))
-            output_field = StructField(output_col, ArrayType(DoubleType()), True)
-        results_rdd = rdd.zip(predictions).map(lambda x: tuple(x[0]) + tuple(x[1]))
+        regression = getattr(self, 'model_type', None) == ModelType.REGRESSION
+
+        def predict_rows(rows):
+            # one predict per partition, then the output column is attached row by row: ndarray.tolist() converts the
+            # whole block to Python floats at C speed (reference: one np.asarray + float() per row, ml_model.py:222-227)
+            rows = list(rows)
+            preds = predict_partition(rows)
+            if not rows:
+                return []
+            block = np.asarray(preds, dtype=np.float64).reshape(len(rows), -1)
+            values = block[:, 0].tolist() if regression else block.tolist()
+            return [tuple(r) + (v,) for r, v in zip(rows, values)]
+
+        results_rdd = rdd.mapPartitions(predict_rows)
+        output_field = StructField(output_col, DoubleType() if regression else ArrayType(DoubleType()), True)
         new_schema.add(output_field)
         return SparkSession.builder.getOrCreate().createDataFrame(results_rdd, new_schema)
 

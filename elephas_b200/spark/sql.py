@@ -125,6 +125,20 @@ def _infer_type(value):
 
 
 # ----------------------------------------------------------------------- Row
+_ROW_CLASSES = {}
+
+
+def _row_class(fields):
+    """One ``Row`` subclass per schema (field names as a class attribute, like a namedtuple): building a row is then a
+    bare ``tuple.__new__`` - no per-row field list, no instance dict. DataFrame transforms create one Row per record."""
+    key = fields if isinstance(fields, tuple) else tuple(fields)
+    cls = _ROW_CLASSES.get(key)
+    if cls is None:
+        cls = type('Row', (Row,), {'__fields__': list(key), '__slots__': ()})
+        _ROW_CLASSES[key] = cls
+    return cls
+
+
 class Row(tuple):
     """Tuple with named fields: ``row.label``, ``row['label']``, ``row[0]``; ``row + tuple`` is a tuple."""
 
@@ -139,9 +153,13 @@ class Row(tuple):
 
     @classmethod
     def _make(cls, fields, values):
-        row = tuple.__new__(cls, values)
-        row.__fields__ = list(fields)
-        return row
+        return tuple.__new__(_row_class(fields), values)
+
+    def __reduce__(self):
+        fields = getattr(self, '__fields__', None)
+        if fields is None:
+            return (Row, tuple(self))
+        return (Row._make, (list(fields), tuple(self)))
 
     def asDict(self):
         return dict(zip(self.__fields__, self))
@@ -281,13 +299,14 @@ class DataFrame:
         else:
             fields[replace] = StructField(name, dtype)
 
+        row_cls, new = _row_class(names), tuple.__new__
+
         def extend(row):
-            vals = list(row)
             if replace is None:
-                vals.append(fn(row[src]))
-            else:
-                vals[replace] = fn(row[src])
-            return Row._make(names, vals)
+                return new(row_cls, tuple(row) + (fn(row[src]),))
+            vals = list(row)
+            vals[replace] = fn(row[src])
+            return new(row_cls, vals)
 
         return DataFrame(self._rdd.map(extend), StructType(fields), self.sparkSession)
 
@@ -402,7 +421,8 @@ class SparkSession:
         first = rdd.take(1)
         if first and isinstance(first[0], LabeledPoint):
             names = ['features', 'label']
-            rdd = rdd.map(lambda lp: Row._make(names, [lp.features, lp.label]))
+            row_cls = _row_class(names)
+            rdd = rdd.map(lambda lp: tuple.__new__(row_cls, (lp.features, lp.label)))
             schema = StructType([StructField('features', VectorUDT()), StructField('label', DoubleType())])
             return DataFrame(rdd, schema, self)
         if isinstance(schema, StructType):
@@ -418,7 +438,8 @@ class SparkSession:
                 names = list(schema)
             struct = StructType([StructField(n, _infer_type(first[0][i]) if first else StringType())
                                  for i, n in enumerate(names)])
-        rdd = rdd.map(lambda r: Row._make(names, list(r)))
+        row_cls, new = _row_class(names), tuple.__new__
+        rdd = rdd.map(lambda r: new(row_cls, r))
         return DataFrame(rdd, struct, self)
 
     def sql(self, query):

@@ -12,6 +12,13 @@ class DenseVector(Vector):
     def __init__(self, values):
         self.values = np.asarray(values, dtype=np.float64).reshape(-1)
 
+    @classmethod
+    def _wrap(cls, values):
+        """A vector around an existing 1-D float64 array (no copy, no checks): bulk producers use this."""
+        v = cls.__new__(cls)
+        v.values = values
+        return v
+
     def toArray(self):
         return self.values
 

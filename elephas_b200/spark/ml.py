@@ -417,7 +417,43 @@ class StandardScalerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadabl
             arr = v.toArray() if isinstance(v, Vector) else np.asarray(v, dtype=np.float64)
             return DenseVector((arr - mean) * scale)
 
+        blocked = self._transform_blocks(dataset, mean, scale)
+        if blocked is not None:
+            return blocked
         return dataset.withColumn(self.getOutputCol(), Column(self.getInputCol(), fn=fn))
+
+    def _transform_blocks(self, dataset, mean, scale):
+        """Local DataFrames: scale a whole partition as one matrix (one NumPy expression per partition instead of three
+        per row); the rows then share views of that matrix. None: not applicable, use the row path."""
+        from .sql import DataFrame, _row_class
+        from .context import RDD
+        rdd = dataset.rdd
+        out_col, in_col = self.getOutputCol(), self.getInputCol()
+        if not (hasattr(rdd, 'partitions') and callable(rdd.partitions)) or out_col in dataset.columns:
+            return None
+        src = dataset.columns.index(in_col)
+        names = list(dataset.columns) + [out_col]
+        row_cls, new, get = _row_class(names), tuple.__new__, tuple.__getitem__
+        parts = []
+        for p in rdd.partitions():
+            rows = p if isinstance(p, list) else list(p)
+            if not rows:
+                parts.append([])
+                continue
+            if not isinstance(rows[0], tuple):
+                return None
+            try:
+                block = np.asarray([get(r, src).toArray() if isinstance(get(r, src), Vector) else
+                                    np.asarray(get(r, src), dtype=np.float64).ravel() for r in rows], dtype=np.float64)
+            except (TypeError, ValueError):
+                return None
+            if block.ndim != 2:
+                return None
+            block = (block - mean) * scale
+            wrap = DenseVector._wrap
+            parts.append([new(row_cls, tuple(r) + (wrap(block[i]),)) for i, r in enumerate(rows)])
+        fields = list(dataset.schema.fields) + [StructField(out_col, VectorUDT())]
+        return DataFrame(RDD(parts, rdd.context), StructType(fields), dataset.sparkSession)
 
 
 class StandardScaler(Estimator, HasInputCol, HasOutputCol, DefaultParamsReadable, DefaultParamsWritable):

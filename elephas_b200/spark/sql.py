@@ -299,13 +299,13 @@ class DataFrame:
         else:
             fields[replace] = StructField(name, dtype)
 
-        row_cls, new = _row_class(names), tuple.__new__
+        row_cls, new, get = _row_class(names), tuple.__new__, tuple.__getitem__
 
         def extend(row):
             if replace is None:
-                return new(row_cls, tuple(row) + (fn(row[src]),))
+                return new(row_cls, tuple(row) + (fn(get(row, src)),))
             vals = list(row)
-            vals[replace] = fn(row[src])
+            vals[replace] = fn(get(row, src))
             return new(row_cls, vals)
 
         return DataFrame(self._rdd.map(extend), StructType(fields), self.sparkSession)

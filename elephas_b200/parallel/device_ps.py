@@ -71,6 +71,8 @@ class DeviceStore:
         # precedes the next lock, so a lock kernel only ever waits for holders on OTHER GPUs (other ranks).
         self._ps_stream = None
         self._enqueue_lock = threading.Lock()
+        # how the exclusion of mode='asynchronous' is realised (see configure()): 'ticket+stream' is always safe
+        self._exclusion = 'ticket+stream'
 
     def export_handle(self):
         from ..ops import native
@@ -99,11 +101,31 @@ class DeviceStore:
             from ..ops import native
             native.cast_f32_to_bf16(self.flat, self.mirror)
 
+    def configure(self, local_workers, distributed):
+        """Tell the store who uses it, so that it can pick the cheapest correct exclusion for ``asynchronous`` mode:
+
+        * one process, several worker threads: all locked operations go through the store's in-order stream - the
+          stream order IS the lock, no ticket-lock kernels are launched ('stream');
+        * several processes, one worker each: ticket-lock kernels on the worker's own stream - every other holder
+          runs on another GPU, so a spinning lock kernel never waits for work queued behind it ('ticket');
+        * several processes with several workers each: both ('ticket+stream', also the default when unknown)."""
+        if not distributed:
+            self._exclusion = 'stream'
+        elif local_workers <= 1:
+            self._exclusion = 'ticket'
+        else:
+            self._exclusion = 'ticket+stream'
+
+    @property
+    def _ticket(self):
+        """Launch ticket-lock kernels around an operation?"""
+        return self.locked and self._exclusion != 'stream'
+
     # ---------------------------------------------------------- flat, on device
     def _device_op(self, fn):
-        """Run ``fn`` (which enqueues lock / kernel / unlock) - on the caller's stream when the store is unlocked, on
-        the store's own stream, ordered against the caller's stream with events, when it is locked."""
-        if not self.locked:
+        """Run ``fn`` (which enqueues [lock,] kernel [, unlock]) - on the caller's stream, or, where the exclusion
+        needs it, on the store's own stream, ordered against the caller's stream with events."""
+        if not self.locked or self._exclusion == 'ticket':
             fn()
             return
         cur = torch.cuda.current_stream(self.device)
@@ -123,7 +145,7 @@ class DeviceStore:
         """``dst_flat <- master`` (and optionally the bf16 compute copy in the same pass)."""
         if self.flat.is_cuda:
             from ..ops import native
-            self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat, dst_bf16, locked=self.locked))
+            self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat, dst_bf16, locked=self._ticket))
             return
         if self.locked:
             with self._host_lock.reading():
@@ -136,7 +158,7 @@ class DeviceStore:
     def pull_range_into(self, dst_flat, lo, n):
         """``dst_flat[lo:lo+n] <- master[lo:lo+n]`` (device stores; used for the bias tail next to pull-fused GEMMs)."""
         from ..ops import native
-        self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=self.locked,
+        self._device_op(lambda: native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=self._ticket,
                                                n=n, offset=lo))
 
     def push_delta(self, delta_flat=None, before=None, after=None, delta_bf16=None):
@@ -145,7 +167,7 @@ class DeviceStore:
         self.pushes += 1
         if self.flat.is_cuda:
             from ..ops import native
-            self._device_op(lambda: native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self.locked,
+            self._device_op(lambda: native.ps_push(self.flat, self.ctrl, delta_flat, before, after, locked=self._ticket,
                                                    mirror=self.mirror, delta_bf16=delta_bf16))
             return
         if delta_bf16 is not None:

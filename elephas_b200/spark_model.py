@@ -249,6 +249,9 @@ class SparkModel:
             if not rt.is_driver:
                 from .parallel.device_ps import attach_remote_store
                 attach_remote_store(self.port, handle, self.mode, self._master_network, rt.device, mirror=fused_pull)
+        if self.parameter_server_mode == 'nvlink':
+            from .parallel.device_ps import get_store
+            get_store(self.port).configure(local_workers=len(mine), distributed=rt.distributed)
         model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
         for key in ('input_mode', 'log_batch_loss', 'keep_context'):
             cfg.pop(key, None)

@@ -38,6 +38,10 @@ from . import native
 _round8 = lambda v: (v + 7) // 8 * 8  # noqa: E731
 _CAPTURE_LOCK = threading.Lock()  # one CUDA-graph capture at a time per process
 _SIDE_STREAM = os.environ.get('ELEPHAS_B200_SIDE_STREAM', '1') != '0'  # bias-gradient sums next to the GEMMs
+# Kernels for layers with <= 8 output units (csrc/narrow_head.cu). Opt-in: on the wide-MLP step they measure the same as
+# the tensor-core path (2.446 vs 2.449 ms/step, A/B on one B200) and their weight gradient uses atomics, which costs
+# run-to-run bit reproducibility.
+_NARROW_HEAD = os.environ.get('ELEPHAS_B200_NARROW_HEAD', '0') != '0'
 
 _METRIC_FOR_FN = {'categorical_accuracy': 'categorical_accuracy', 'binary_accuracy': 'binary_accuracy',
                   'mean_absolute_error': 'mean_absolute_error', 'mean_squared_error': 'mean_squared_error',
@@ -367,8 +371,18 @@ class MLPEngine:
             a = out
         op = self.ops[-1]
         w, w_copy = weights(op)
-        native.gemm(a, w, B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
-                    out_f32=buf.z, ldo32=buf.z.stride(0), bias=self.w32[op.b_seg.offset:], act=0, b_copy=w_copy)
+        if self._narrow(op) and w_copy is None:
+            # a handful of output units: one pass over the activations at HBM speed (csrc/narrow_head.cu)
+            native.head_fwd(a, w, B, op.in_dim, op.out_dim, buf.z, bias=self.w32[op.b_seg.offset:], lda=op.ld_in,
+                            ldw=op.ld_in)
+        else:
+            native.gemm(a, w, B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
+                        out_f32=buf.z, ldo32=buf.z.stride(0), bias=self.w32[op.b_seg.offset:], act=0, b_copy=w_copy)
+
+    def _narrow(self, op):
+        """Last layer with at most 8 output units and an 8-aligned input width: served by the narrow-head kernels."""
+        return (_NARROW_HEAD and op is self.ops[-1] and op.out_dim <= native.HEAD_MAX_OUT and op.in_dim % 8 == 0
+                and op.in_dim * op.out_dim * 2 <= 96 * 1024)
 
     def _loss(self, buf, with_grad, rows=None, grad_rows=None):
         op = self.ops[-1]
@@ -438,16 +452,28 @@ class MLPEngine:
             a_prev = buf.x16 if op.index == 0 else buf.acts[op.index - 1]
             off = op.w_seg.offset
             span = (op.w_seg.span + 63) // 64 * 64
+            narrow = self._narrow(op)
             if op.index > 0:
                 prev = self.ops[op.index - 1]
                 # dZ_prev[B, in] = (dZ[B, out] x W[out, in]) * act'(A_prev) * dropout mask
                 # (before the wgrad of this layer: the fused-SGD epilogue overwrites W)
-                native.gemm(dz, self._w16(op), B, op.in_dim, op.out_dim, b_mn=True, lda=op.ld_out, ldb=op.ld_in,
-                            out_bf16=buf.dz[prev.index], ldo=prev.ld_out, epi=native.EPI_ACTGRAD,
-                            act=native.ACT_IDS[prev.act], aux=a_prev, ldaux=prev.ld_out, drop_p=prev.drop_p,
-                            seed=self.seed, drop_stream=prev.index, step_ptr=self.step)
+                if narrow and prev.drop_p == 0.0:
+                    native.head_dgrad(dz, self._w16(op), a_prev, buf.dz[prev.index], B, op.in_dim, op.out_dim,
+                                      act=native.ACT_IDS[prev.act], lddz=op.ld_out, ldw=op.ld_in, ldaux=prev.ld_out,
+                                      lddzp=prev.ld_out)
+                else:
+                    native.gemm(dz, self._w16(op), B, op.in_dim, op.out_dim, b_mn=True, lda=op.ld_out, ldb=op.ld_in,
+                                out_bf16=buf.dz[prev.index], ldo=prev.ld_out, epi=native.EPI_ACTGRAD,
+                                act=native.ACT_IDS[prev.act], aux=a_prev, ldaux=prev.ld_out, drop_p=prev.drop_p,
+                                seed=self.seed, drop_stream=prev.index, step_ptr=self.step)
             # dW[out, in] = dZ^T[out, B] x A_prev[B, in]: both operands MN-major
-            if not fused:
+            if narrow:
+                # dZ-weighted column sums into the gradient buffer, then the (tiny) optimizer range of this kernel
+                native.head_wgrad(dz, a_prev, B, op.in_dim, op.out_dim, self.g32[off:], lddz=op.ld_out, lda=op.ld_in,
+                                  lddw=op.ld_in)
+                if fused or delta_mode:
+                    self._optimizer_range(off, span, advance=False)
+            elif not fused:
                 native.gemm(dz, a_prev, op.out_dim, op.in_dim, B, a_mn=True, b_mn=True, lda=op.ld_out,
                             ldb=op.ld_in, out_f32=self.g32[off:], ldo32=op.ld_in)
                 if delta_mode:

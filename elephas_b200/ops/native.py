@@ -44,6 +44,14 @@ class GemmArgs(ctypes.Structure):
                 ('b_copy', c_void_p)]
 
 
+class HeadArgs(ctypes.Structure):
+    _fields_ = [('rows', c_int32), ('K', c_int32), ('out', c_int32),
+                ('A', c_void_p), ('lda', c_int64), ('W', c_void_p), ('ldw', c_int64), ('bias', c_void_p),
+                ('z', c_void_p), ('ldz', c_int64), ('dz', c_void_p), ('lddz', c_int64),
+                ('dw', c_void_p), ('lddw', c_int64), ('aux', c_void_p), ('ldaux', c_int64),
+                ('dzp', c_void_p), ('lddzp', c_int64), ('act', c_int32)]
+
+
 class LossArgs(ctypes.Structure):
     _fields_ = [('z', c_void_p), ('ldz', c_int64), ('y', c_void_p), ('ldy', c_int64),
                 ('out', c_void_p), ('ldo', c_int64), ('dz', c_void_p), ('lddz', c_int64),
@@ -92,7 +100,7 @@ def load():
         lib.eb_launch_count.restype = c_uint64
         lib.eb_version.restype = c_int32
         for name in ('eb_gemm_bf16', 'eb_loss_fwd_bwd', 'eb_optimizer_step', 'eb_allreduce_update',
-                     'eb_allreduce_sum', 'eb_allreduce_shard_update'):
+                     'eb_allreduce_sum', 'eb_allreduce_shard_update', 'eb_head_fwd', 'eb_head_wgrad', 'eb_head_dgrad'):
             getattr(lib, name).argtypes = [c_void_p, c_void_p]
         lib.eb_stage_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
         lib.eb_cast_f32_to_bf16.argtypes = [c_void_p, c_void_p, c_int64, c_void_p]
@@ -183,6 +191,48 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
     g.bf16_from_f32 = int(bool(bf16_from_f32))
     g.block_n, g.cta_group = int(block_n), int(cta_group)
     _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
+
+
+# ------------------------------------------------------------- narrow Dense layers
+HEAD_MAX_OUT = 8
+
+
+def _head_args(rows, K, out):
+    a = HeadArgs()
+    a.rows, a.K, a.out = int(rows), int(K), int(out)
+    return a
+
+
+def head_fwd(A, W, rows, K, out, z, bias=None, lda=None, ldw=None):
+    """``z[:rows, :out] = A[:rows, :K] @ W[:out, :K].T + bias`` for ``out <= 8`` (fp32 ``z``)."""
+    a = _head_args(rows, K, out)
+    a.A, a.lda = A.data_ptr(), int(lda if lda is not None else A.stride(0))
+    a.W, a.ldw = W.data_ptr(), int(ldw if ldw is not None else W.stride(0))
+    a.bias = bias.data_ptr() if bias is not None else None
+    a.z, a.ldz = z.data_ptr(), z.stride(0)
+    _check(require().eb_head_fwd(ctypes.byref(a), _stream(A.device)), 'eb_head_fwd')
+
+
+def head_wgrad(dz, A, rows, K, out, dw, lddz=None, lda=None, lddw=None):
+    """``dw[:out, :K] = dz[:rows, :out].T @ A[:rows, :K]`` (fp32 ``dw``, overwritten)."""
+    a = _head_args(rows, K, out)
+    a.A, a.lda = A.data_ptr(), int(lda if lda is not None else A.stride(0))
+    a.W, a.ldw = A.data_ptr(), 8  # unused by this entry point (kept valid for the shared argument check)
+    a.dz, a.lddz = dz.data_ptr(), int(lddz if lddz is not None else dz.stride(0))
+    a.dw, a.lddw = dw.data_ptr(), int(lddw if lddw is not None else K)
+    _check(require().eb_head_wgrad(ctypes.byref(a), _stream(A.device)), 'eb_head_wgrad')
+
+
+def head_dgrad(dz, W, aux, dzp, rows, K, out, act=0, lddz=None, ldw=None, ldaux=None, lddzp=None):
+    """``dzp[:rows, :K] = (dz[:rows, :out] @ W[:out, :K]) * act'(aux)`` (bf16 ``dzp``)."""
+    a = _head_args(rows, K, out)
+    a.A, a.lda = aux.data_ptr(), 8  # unused here
+    a.W, a.ldw = W.data_ptr(), int(ldw if ldw is not None else W.stride(0))
+    a.dz, a.lddz = dz.data_ptr(), int(lddz if lddz is not None else dz.stride(0))
+    a.aux, a.ldaux = aux.data_ptr(), int(ldaux if ldaux is not None else aux.stride(0))
+    a.dzp, a.lddzp = dzp.data_ptr(), int(lddzp if lddzp is not None else dzp.stride(0))
+    a.act = int(act)
+    _check(require().eb_head_dgrad(ctypes.byref(a), _stream(W.device)), 'eb_head_dgrad')
 
 
 # ---------------------------------------------------------------- elementwise

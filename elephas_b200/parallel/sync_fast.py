@@ -389,6 +389,11 @@ class SyncContext:
 
         skip = os.environ.get('ELEPHAS_B200_DEBUG_SKIP_COMM') == '1'  # timing experiments only: wrong results
 
+        # the first layer's bucket and the vector bucket are reduced after the last GEMM of the step: nothing is left to
+        # overlap with, so they take the whole machine instead of the small overlap-friendly grid
+        tail_from = eng.ops[0].w_seg.offset if self.sharded else None
+        tail_blocks = int(os.environ.get('ELEPHAS_B200_COMM_TAIL_BLOCKS', '148'))
+
         def hook(lo, n):
             if skip:
                 return
@@ -396,8 +401,9 @@ class SyncContext:
             ready = torch.cuda.Event()
             ready.record(cur)
             self.comm_stream.wait_event(ready)
+            tail = tail_from is not None and (lo == eng.ops[0].w_seg.offset or lo >= eng.layout.matrix_end)
             with torch.cuda.stream(self.comm_stream):
-                self._allreduce_update(lo, n, blocks=blocks)
+                self._allreduce_update(lo, n, blocks=tail_blocks if tail else blocks)
 
         def join():
             if skip:

@@ -222,6 +222,29 @@ int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, v
 int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
                       const float* before, const float* after, int64_t n, void* stream);
 
+/* ------------------------------------------------------------ narrow Dense layers (at most 8 output units)
+ * Regression heads and tiny classifiers: one pass over the activations at HBM speed instead of a nearly empty
+ * tensor-core tile. Layouts as in EbGemmArgs (bf16, K-major, leading dimensions in elements).
+ *   eb_head_fwd    z[b][o]   = bias[o] + sum_k A[b][k] W[o][k]                       (z fp32)
+ *   eb_head_wgrad  dw[o][k]  = sum_b dz[b][o] A[b][k]                                (dw fp32, overwritten)
+ *   eb_head_dgrad  dzp[b][k] = (sum_o dz[b][o] W[o][k]) * act'(aux[b][k])            (aux = stored layer output)
+ * Reference: the last Dense layer of the regression examples (Keras fit/predict, elephas/worker.py:42,108,123). */
+typedef struct {
+  int32_t rows, K, out;
+  const void* A;  int64_t lda;     /* activations [rows][lda] bf16 (fwd, wgrad) */
+  const void* W;  int64_t ldw;     /* weights [out][ldw] bf16 (fwd, dgrad) */
+  const float* bias;               /* [out] or NULL (fwd) */
+  float* z;       int64_t ldz;     /* fwd output */
+  const void* dz; int64_t lddz;    /* upstream gradient [rows][lddz] bf16 (wgrad, dgrad) */
+  float* dw;      int64_t lddw;    /* wgrad output [out][lddw] */
+  const void* aux; int64_t ldaux;  /* previous layer's stored output (dgrad) */
+  void* dzp;      int64_t lddzp;   /* dgrad output [rows][lddzp] bf16 */
+  int32_t act;                     /* activation of the previous layer (EB_ACT_*) */
+} EbHeadArgs;
+int eb_head_fwd(const EbHeadArgs* args, void* stream);
+int eb_head_wgrad(const EbHeadArgs* args, void* stream);
+int eb_head_dgrad(const EbHeadArgs* args, void* stream);
+
 /* ------------------------------------------------------------ host side of the input pipeline
  * dst[r][0..cols) = bf16(src[r][0..cols)) (round to nearest even, bit-identical to the device cast), padding columns
  * [cols, ld_dst) zeroed; runs on `threads` CPU threads (persistent pool) and returns when the batch is converted.

@@ -380,6 +380,38 @@ def test_parameter_server_push_refreshes_the_bf16_mirror(native, kind):
     assert torch.equal(tail[100:164], master[100:164]) and float(tail[:100].abs().sum()) == 0.0
 
 
+@pytest.mark.parametrize('rows,K,out', [(64, 128, 1), (300, 520, 3), (4096, 4096, 1), (1000, 512, 8), (5, 8, 2)])
+def test_narrow_head_kernels_match_torch(native, rows, K, out):
+    """Dense layers with <= 8 output units: forward, weight gradient and input gradient at HBM speed."""
+    torch.manual_seed(31)
+    ld = K + 8
+    A = _bf(torch.randn(rows, ld, device='cuda'))
+    W = _bf(torch.randn(out, ld, device='cuda') * 0.1)
+    bias = torch.randn(out, device='cuda')
+    z = torch.full((rows, max(4, (out + 3) // 4 * 4)), 9.0, device='cuda')
+    native.head_fwd(A, W, rows, K, out, z, bias=bias)
+    ref = A[:, :K].float() @ W[:, :K].float().t() + bias
+    assert torch.allclose(z[:, :out], ref, atol=2e-3, rtol=2e-3)
+    assert torch.all(z[:, out:] == 9.0)
+    ldz = 8
+    dz = _bf(torch.randn(rows, ldz, device='cuda') * 0.05)
+    dw = torch.full((out, ld), 3.0, device='cuda')
+    native.head_wgrad(dz, A, rows, K, out, dw, lddw=ld)
+    ref_dw = dz[:, :out].float().t() @ A[:, :K].float()
+    assert torch.allclose(dw[:, :K], ref_dw, atol=3e-3, rtol=3e-3), (dw[:, :K] - ref_dw).abs().max()
+    for act_name in ('relu', 'tanh', 'linear'):
+        aux = _bf(torch.randn(rows, ld, device='cuda'))
+        if act_name == 'relu':
+            aux = torch.relu(aux)
+        dzp = torch.full((rows, ld), 7.0, dtype=torch.bfloat16, device='cuda')
+        native.head_dgrad(dz, W, aux, dzp, rows, K, out, act=native.ACT_IDS[act_name])
+        g = dz[:, :out].float() @ W[:, :K].float()
+        a = aux[:, :K].float()
+        grad = {'relu': (a > 0).float(), 'tanh': 1 - a * a, 'linear': torch.ones_like(a)}[act_name]
+        assert torch.allclose(dzp[:, :K].float(), g * grad, atol=2e-2, rtol=2e-2)
+        assert torch.all(dzp[:, K:] == 7.0)
+
+
 def test_launch_counter_moves(native):
     before = native.launch_count()
     native.cast_f32_to_bf16(torch.zeros(64, device='cuda'), torch.zeros(64, dtype=torch.bfloat16, device='cuda'))

@@ -357,3 +357,52 @@ def test_narrow_head_path_matches_gemm_path(monkeypatch, opt):
         else:
             assert np.abs(a - b).mean() < 2e-3
     assert np.allclose(weights[0][1], weights[1][1], rtol=2e-2, atol=1e-3)
+
+
+@pytest.mark.parametrize('mode,exclusion', [('asynchronous', 'stream'), ('asynchronous', 'ticket+stream'),
+                                            ('hogwild', 'stream')])
+def test_device_store_concurrent_pushes_sum_exactly(mode, exclusion):
+    """Race test (the reference's server loses updates: it reads the weights before taking the write lock,
+    elephas/parameter/server.py:204-206): worker threads push integer-valued deltas concurrently, each through its own
+    stream; `red.add` makes every push land exactly once in both modes, and locked pulls never see a torn push."""
+    import threading
+    from elephas_b200.parallel.device_ps import create_store, destroy_store
+    model = Sequential([Dense(64, input_dim=256, activation='relu'), Dense(8)])
+    model.compile(SGD(learning_rate=0.1), 'mse')
+    model.to('cuda')
+    port = next(_ports)
+    store = create_store(port, model.get_weights(), mode, model=model, device=torch.device('cuda', 0), mirror=True)
+    if exclusion == 'stream':
+        store.configure(local_workers=4, distributed=False)
+    n = store.layout.numel
+    store.flat.zero_()  # integer-valued master and deltas: every partial sum is exact in fp32
+    store.refresh_mirror()
+    start = store.flat.clone()
+    threads, pushes, torn = 4, 25, []
+
+    def work(tid):
+        with torch.cuda.device(0), torch.cuda.stream(torch.cuda.Stream(0)):
+            delta = torch.full((n,), float(tid + 1), device='cuda')
+            snap = torch.empty(n, device='cuda')
+            for i in range(pushes):
+                store.push_delta(delta)
+                if mode == 'asynchronous':
+                    store.pull_into(snap)
+                    d = start - snap
+                    # under the lock a snapshot is a whole number of pushes: every element moved by the same amount
+                    if float((d - d[0]).abs().max()) != 0.0:
+                        torn.append((tid, i))
+            torch.cuda.current_stream().synchronize()
+
+    ts = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    torch.cuda.synchronize()
+    expected = start - float(pushes * sum(range(1, threads + 1)))
+    assert torch.equal(store.flat, expected)
+    assert torch.equal(store.mirror, store.flat.to(torch.bfloat16))
+    assert not torn
+    assert int(store.ctrl[4].item()) == 0  # the lock watchdog never fired
+    destroy_store(port)

@@ -172,6 +172,47 @@ sm.fit(to_simple_rdd(sc, x, y), epochs=2, batch_size=64)
 same_on_all_ranks(sm.master_network.get_weights(), tol=1e-6)
 log("generic torch path with custom activation ok: acc %.3f" % sm.evaluate(xt, yt)[1])
 
+# ---- 6. race test across ranks: every rank pushes integer deltas into rank 0's store over NVLink ----------
+from elephas_b200.parallel.device_ps import attach_remote_store, create_store, destroy_store  # noqa: E402
+
+stress_model = Sequential([Dense(64, input_dim=256, activation='relu'), Dense(8)])
+stress_model.compile(SGD(lr=0.1), 'mse')
+stress_model.to(rt.device)
+for mode in ('asynchronous', 'hogwild'):
+    sport = port + 50 + (0 if mode == 'asynchronous' else 1)
+    if R == 0:
+        store = create_store(sport, stress_model.get_weights(), mode, model=stress_model, device=rt.device, mirror=True)
+        handle = store.export_handle()
+        store.flat.zero_()  # integer-valued master and deltas: every partial sum is exact in fp32
+        store.refresh_mirror()
+        torch.cuda.synchronize()
+        start = store.flat.clone()
+    else:
+        handle = None
+    handle = rt.broadcast_object(handle, src=0)
+    if R != 0:
+        store = attach_remote_store(sport, handle, mode, stress_model, rt.device, mirror=True)
+    store.configure(local_workers=1, distributed=True)
+    n = store.layout.numel
+    delta = torch.full((n,), float(R + 1), device=rt.device)
+    snap = torch.empty(n, device=rt.device)
+    rt.barrier()
+    for i in range(40):
+        store.push_delta(delta)
+        if mode == 'asynchronous':
+            store.pull_into(snap)  # locked pulls interleave with the other ranks' locked pushes
+    torch.cuda.synchronize()
+    rt.barrier()
+    if R == 0:
+        expected = start - float(40 * W * (W + 1) // 2)
+        assert torch.equal(store.flat, expected), (store.flat - expected).abs().max()
+        assert torch.equal(store.mirror, store.flat.to(torch.bfloat16))
+        assert int(store.ctrl[4].item()) == 0
+    rt.barrier()
+    destroy_store(sport)
+    rt.barrier()
+    log("parameter-server race test (%s): %d ranks x 40 pushes land exactly once" % (mode, W))
+
 rt.barrier()
 log("ALL OK (world=%d)" % W)
 rt.shutdown()

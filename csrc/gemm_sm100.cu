@@ -463,8 +463,8 @@ static EncodeTiledFn get_encode_fn() {
 
 // 2-D bf16 tensor map over a row-major [rows][ld] array whose logical extent is [rows][cols];
 // box = [box_rows][box_cols], 128-byte swizzle, out-of-bounds elements read as zero.
-static int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
-                    uint32_t box_cols) {
+int make_map(CUtensorMap* map, const void* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+             uint32_t box_cols) {
   EncodeTiledFn enc = get_encode_fn();
   if (enc == nullptr) return fail("cuTensorMapEncodeTiled not available from the driver");
   cuuint64_t gdim[2] = {cols, rows};

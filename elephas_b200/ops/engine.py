@@ -42,6 +42,7 @@ _SIDE_STREAM = os.environ.get('ELEPHAS_B200_SIDE_STREAM', '1') != '0'  # bias-gr
 # the tensor-core path (2.446 vs 2.449 ms/step, A/B on one B200) and their weight gradient uses atomics, which costs
 # run-to-run bit reproducibility.
 _NARROW_HEAD = os.environ.get('ELEPHAS_B200_NARROW_HEAD', '0') != '0'
+_FUSED_MLP = os.environ.get('ELEPHAS_B200_FUSED_MLP', '1') != '0'  # K8: whole-MLP forward kernel for predict / evaluate
 
 _METRIC_FOR_FN = {'categorical_accuracy': 'categorical_accuracy', 'binary_accuracy': 'binary_accuracy',
                   'mean_absolute_error': 'mean_absolute_error', 'mean_squared_error': 'mean_squared_error',
@@ -352,6 +353,12 @@ class MLPEngine:
         if not (self.input_bf16 and training):  # (streamed training inputs arrive already cast to bf16 by the host: half the PCIe bytes)
             native.stage_f32_to_bf16(buf.x32, buf.x16, B, self.ops[0].in_dim)
         a = buf.x16
+        if not training and self._fused_mlp_ok():
+            # K8: the whole chain in one persistent kernel, hidden activations never leave the SM
+            native.mlp_forward(buf.x16, B, self.ops[0].ld_in,
+                               [(self._w16(op), op.out_dim, self.w32[op.b_seg.offset:], native.ACT_IDS[op.act])
+                                for op in self.ops], buf.z, ldx=self.ops[0].ld_in)
+            return
         pull = self.pull_source if training else None
 
         def weights(op):
@@ -378,6 +385,14 @@ class MLPEngine:
         else:
             native.gemm(a, w, B, op.out_dim, op.in_dim, lda=op.ld_in, ldb=op.ld_in,
                         out_f32=buf.z, ldo32=buf.z.stride(0), bias=self.w32[op.b_seg.offset:], act=0, b_copy=w_copy)
+
+    def _fused_mlp_ok(self):
+        """Inference forward through ``eb_mlp_forward`` (K8)? Small Dense chains only (see its limits)."""
+        ok = getattr(self, '_fused_mlp', None)
+        if ok is None:
+            ok = _FUSED_MLP and native.mlp_forward_supported(self.ops[0].ld_in, [op.out_dim for op in self.ops])
+            self._fused_mlp = ok
+        return ok
 
     def _narrow(self, op):
         """Last layer with at most 8 output units and an 8-aligned input width: served by the narrow-head kernels."""

@@ -52,6 +52,16 @@ class HeadArgs(ctypes.Structure):
                 ('dzp', c_void_p), ('lddzp', c_int64), ('act', c_int32)]
 
 
+MLP_MAX_LAYERS = 4
+
+
+class MlpArgs(ctypes.Structure):
+    _fields_ = [('rows', c_int32), ('layers', c_int32), ('dims', c_int32 * (MLP_MAX_LAYERS + 1)),
+                ('x', c_void_p), ('ldx', c_int64), ('w', c_void_p * MLP_MAX_LAYERS), ('ldw', c_int64 * MLP_MAX_LAYERS),
+                ('bias', c_void_p * MLP_MAX_LAYERS), ('act', c_int32 * MLP_MAX_LAYERS), ('z', c_void_p),
+                ('ldz', c_int64)]
+
+
 class LossArgs(ctypes.Structure):
     _fields_ = [('z', c_void_p), ('ldz', c_int64), ('y', c_void_p), ('ldy', c_int64),
                 ('out', c_void_p), ('ldo', c_int64), ('dz', c_void_p), ('lddz', c_int64),
@@ -100,7 +110,8 @@ def load():
         lib.eb_launch_count.restype = c_uint64
         lib.eb_version.restype = c_int32
         for name in ('eb_gemm_bf16', 'eb_loss_fwd_bwd', 'eb_optimizer_step', 'eb_allreduce_update',
-                     'eb_allreduce_sum', 'eb_allreduce_shard_update', 'eb_head_fwd', 'eb_head_wgrad', 'eb_head_dgrad'):
+                     'eb_allreduce_sum', 'eb_allreduce_shard_update', 'eb_head_fwd', 'eb_head_wgrad', 'eb_head_dgrad',
+                     'eb_mlp_forward'):
             getattr(lib, name).argtypes = [c_void_p, c_void_p]
         lib.eb_stage_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
         lib.eb_cast_f32_to_bf16.argtypes = [c_void_p, c_void_p, c_int64, c_void_p]
@@ -191,6 +202,31 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
     g.bf16_from_f32 = int(bool(bf16_from_f32))
     g.block_n, g.cta_group = int(block_n), int(cta_group)
     _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
+
+
+# ------------------------------------------------------------- fused MLP forward (K8)
+def mlp_forward_supported(in_dim, units):
+    """Can ``eb_mlp_forward`` run a Dense chain with these widths? (2-4 layers, hidden widths multiples of 16 up to
+    128, at most 128 output units, 8-aligned input width.)"""
+    units = list(units)
+    return (2 <= len(units) <= MLP_MAX_LAYERS and in_dim % 8 == 0 and all(u % 16 == 0 and 0 < u <= 128 for u in units[:-1])
+            and 0 < units[-1] <= 128)
+
+
+def mlp_forward(x16, rows, in_dim, layers, z, ldx=None):
+    """Whole-MLP forward in one persistent kernel. ``layers``: list of ``(w16 [units, ld], units, bias32, act_id)``;
+    ``z``: fp32 ``[rows, >= units_last]`` receives the last layer's pre-activations."""
+    a = MlpArgs()
+    a.rows, a.layers = int(rows), len(layers)
+    a.dims[0] = int(in_dim)
+    a.x, a.ldx = x16.data_ptr(), int(ldx if ldx is not None else x16.stride(0))
+    for i, (w, units, bias, act) in enumerate(layers):
+        a.dims[i + 1] = int(units)
+        a.w[i], a.ldw[i] = w.data_ptr(), int(w.stride(0))
+        a.bias[i] = bias.data_ptr() if bias is not None else None
+        a.act[i] = int(act)
+    a.z, a.ldz = z.data_ptr(), z.stride(0)
+    _check(require().eb_mlp_forward(ctypes.byref(a), _stream(x16.device)), 'eb_mlp_forward')
 
 
 # ------------------------------------------------------------- narrow Dense layers

@@ -222,6 +222,26 @@ int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, v
 int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
                       const float* before, const float* after, int64_t n, void* stream);
 
+/* ------------------------------------------------------------ K8: whole-MLP forward in one persistent kernel
+ * z = W_{L-1} act(... act(W_0 x + b_0) ...) + b_{L-1} for a chain of 2-4 Dense layers whose hidden widths are multiples
+ * of 16 up to 128 and whose output has at most 128 units: a CTA carries a tile of 128 rows through every layer, layer 0
+ * streams through a TMA ring, later weights are resident in shared memory, activations go TMEM -> registers -> shared
+ * memory (swizzled A operand of the next tcgen05.mma) and never touch HBM. z is the fp32 pre-activation of the last
+ * layer (feed it to eb_loss_fwd_bwd for the output activation / loss / metrics). Reference: model.predict / evaluate
+ * on the workers (elephas/spark_model.py:244-255,284-308). */
+#define EB_MLP_MAX_LAYERS 4
+typedef struct {
+  int32_t rows, layers;
+  int32_t dims[EB_MLP_MAX_LAYERS + 1];   /* dims[0] = input width, dims[l + 1] = units of layer l */
+  const void* x;  int64_t ldx;           /* bf16 input [rows][ldx] */
+  const void* w[EB_MLP_MAX_LAYERS];      /* bf16 kernels [units][ldw], K-major */
+  int64_t ldw[EB_MLP_MAX_LAYERS];
+  const float* bias[EB_MLP_MAX_LAYERS];  /* fp32 [units] or NULL */
+  int32_t act[EB_MLP_MAX_LAYERS];        /* EB_ACT_* of the hidden layers (the last entry is ignored) */
+  float* z;       int64_t ldz;           /* fp32 output [rows][ldz] */
+} EbMlpArgs;
+int eb_mlp_forward(const EbMlpArgs* args, void* stream);
+
 /* ------------------------------------------------------------ narrow Dense layers (at most 8 output units)
  * Regression heads and tiny classifiers: one pass over the activations at HBM speed instead of a nearly empty
  * tensor-core tile. Layouts as in EbGemmArgs (bf16, K-major, leading dimensions in elements).

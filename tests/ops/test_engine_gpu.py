@@ -406,3 +406,34 @@ def test_device_store_concurrent_pushes_sum_exactly(mode, exclusion):
     assert not torn
     assert int(store.ctrl[4].item()) == 0  # the lock watchdog never fired
     destroy_store(port)
+
+
+def test_fused_mlp_predict_and_evaluate_match_the_gemm_chain(monkeypatch):
+    """K8 on the reference's MNIST MLP: predict / evaluate through the one-kernel forward == the per-layer GEMM chain."""
+    from elephas_b200.ops import engine as engine_mod
+    x, y, xt, yt = make_mnist_like(2048, 1500)
+    torch.manual_seed(12)
+    m = zoo.mnist_mlp()
+    m.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    m.to('cuda')
+    m.fit(x, y, batch_size=64, epochs=2)
+    outs = {}
+    for fused in (True, False):
+        monkeypatch.setattr(engine_mod, '_FUSED_MLP', fused)
+        eng = m._native_engine()
+        eng._fused_mlp = None          # re-evaluate the eligibility under the patched switch
+        eng.invalidate_graphs()
+        launches = native_launches()
+        outs[fused] = (m.predict(xt), m.evaluate(xt, yt))
+        outs[fused] += (native_launches() - launches,)
+        assert eng._fused_mlp_ok() is fused
+    pa, ea, la = outs[True]
+    pb, eb, lb = outs[False]
+    assert np.allclose(pa, pb, atol=2e-2) and (pa.argmax(1) == pb.argmax(1)).mean() > 0.995
+    assert abs(ea[0] - eb[0]) < 5e-3 and abs(ea[1] - eb[1]) < 5e-3
+    assert la < lb                     # one forward kernel instead of three GEMMs per block of rows
+
+
+def native_launches():
+    from elephas_b200.ops import native
+    return native.launch_count()

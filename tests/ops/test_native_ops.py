@@ -412,6 +412,43 @@ def test_narrow_head_kernels_match_torch(native, rows, K, out):
         assert torch.all(dzp[:, K:] == 7.0)
 
 
+@pytest.mark.parametrize('rows,dims,acts', [
+    (300, (784, 128, 128, 10), ('relu', 'relu')),        # the reference's MNIST MLP
+    (128, (64, 64, 16), ('tanh',)),
+    (1000, (200, 32, 48, 128, 3), ('relu', 'sigmoid', 'elu')),
+    (20000, (784, 128, 128, 10), ('relu', 'relu')),      # several tiles per CTA
+    (77, (96, 16, 1), ('linear',)),
+])
+def test_fused_mlp_forward_matches_layer_by_layer(native, rows, dims, acts):
+    """K8: one persistent kernel carries a row tile through every layer (activations stay on chip)."""
+    torch.manual_seed(41)
+    in_dim = dims[0]
+    ldx = in_dim + 8
+    x = _bf(torch.randn(rows, ldx, device='cuda'))
+    layers, ref = [], x[:, :in_dim].float()
+    k = in_dim
+    for i, units in enumerate(dims[1:]):
+        ld = (k + 7) // 8 * 8 + 8
+        w = _bf(torch.randn(units, ld, device='cuda') / (k ** 0.5))
+        b = torch.randn(units, device='cuda') * 0.1
+        last = i == len(dims) - 2
+        act = 'linear' if last else acts[i]
+        layers.append((w, units, b, native.ACT_IDS[act]))
+        ref = ref @ w[:, :k].float().t() + b
+        if not last:
+            ref = _bf({'relu': torch.relu, 'tanh': torch.tanh, 'sigmoid': torch.sigmoid, 'linear': lambda t: t,
+                       'elu': torch.nn.functional.elu}[act](ref)).float()   # the kernel keeps hidden activations in bf16
+        k = units
+    assert native.mlp_forward_supported(in_dim, dims[1:])
+    ldz = max(4, (dims[-1] + 3) // 4 * 4)
+    z = torch.full((rows, ldz), 9.0, device='cuda')
+    native.mlp_forward(x, rows, in_dim, layers, z)
+    torch.cuda.synchronize()
+    assert torch.allclose(z[:, :dims[-1]], ref, atol=3e-2, rtol=3e-2), (z[:, :dims[-1]] - ref).abs().max()
+    assert torch.all(z[:, dims[-1]:] == 9.0)
+    assert not native.mlp_forward_supported(in_dim, (512, 10)) and not native.mlp_forward_supported(in_dim, (10,))
+
+
 def test_launch_counter_moves(native):
     before = native.launch_count()
     native.cast_f32_to_bf16(torch.zeros(64, device='cuda'), torch.zeros(64, dtype=torch.bfloat16, device='cuda'))

@@ -29,6 +29,9 @@ PAGES = [
     ('runtime/runtime.md', 'elephas_b200.parallel.runtime', None),
     ('runtime/sync-fast-path.md', 'elephas_b200.parallel.sync_fast', None),
     ('runtime/symmetric-memory.md', 'elephas_b200.parallel.symm', None),
+    ('runtime/sync-torch-path.md', 'elephas_b200.parallel.sync_torch', None),
+    ('runtime/torch-step.md', 'elephas_b200.ops.torch_step', None),
+    ('utils/tracing.md', 'elephas_b200.utils.tracing', None),
     ('runtime/engine.md', 'elephas_b200.ops.engine', None),
     ('runtime/native-bindings.md', 'elephas_b200.ops.native', None),
     ('utils/functional_utils.md', 'elephas_b200.utils.functional_utils', None),

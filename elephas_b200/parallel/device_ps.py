@@ -155,6 +155,28 @@ class DeviceStore:
         if dst_bf16 is not None:
             dst_bf16.copy_(dst_flat)
 
+    # -- raw forms: enqueue on the CURRENT stream without any exclusion (the caller provides it, e.g. by running a whole
+    #    captured pull+step+push graph inside ``exclusive``) ------------------------------------------------------------
+    def raw_pull_range(self, dst_flat, lo, n):
+        from ..ops import native
+        native.ps_pull(self.flat, self.ctrl, dst_flat[lo:lo + n], None, locked=False, n=n, offset=lo)
+
+    def raw_push(self, delta_flat=None, delta_bf16=None):
+        from ..ops import native
+        self.pushes += 1
+        native.ps_push(self.flat, self.ctrl, delta_flat, None, None, locked=False, mirror=self.mirror,
+                       delta_bf16=delta_bf16)
+
+    @property
+    def stream_exclusive(self):
+        """True when locked operations are serialised by the store's own stream (one process, no ticket kernels): a
+        worker may then run a whole pull+step+push graph as ONE exclusive operation."""
+        return self.locked and self._exclusion == 'stream' and self.flat.is_cuda
+
+    def exclusive(self, fn):
+        """Run ``fn`` as one exclusive operation of the store (see ``_device_op``)."""
+        self._device_op(fn)
+
     def pull_range_into(self, dst_flat, lo, n):
         """``dst_flat[lo:lo+n] <- master[lo:lo+n]`` (device stores; used for the bias tail next to pull-fused GEMMs)."""
         from ..ops import native

@@ -233,10 +233,13 @@ class SparkModel:
 
     # -- asynchronous / hogwild -------------------------------------------------
     def _fit_parameter_server(self, rt, partitions, mine, train_config):
-        # hogwild + per-batch pulls on GPUs: the store publishes a bf16 mirror and the workers' forward GEMMs read the
-        # weights straight from it (pull fused into the GEMM, K2); the locked mode keeps the copy-under-lock pull
-        fused_pull = (self.parameter_server_mode == 'nvlink' and self.mode == 'hogwild' and self.frequency == 'batch'
-                      and rt.device.type == 'cuda' and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
+        # per-batch pulls on GPUs: the store publishes a bf16 mirror and the workers' forward GEMMs read the weights
+        # straight from it (pull fused into the GEMM, K2) - hogwild always, the locked mode when all workers live in this
+        # process (the store's stream then serialises whole pull+step+push graphs); across ranks the locked mode keeps
+        # the copy-under-lock pull
+        fused_pull = (self.parameter_server_mode == 'nvlink' and self.frequency == 'batch' and rt.device.type == 'cuda'
+                      and (self.mode == 'hogwild' or not rt.distributed)
+                      and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
         if hasattr(self.parameter_server, 'fused_pull'):
             self.parameter_server.fused_pull = fused_pull
         if rt.is_driver:

@@ -253,7 +253,7 @@ class AsynchronousSparkWorker(_WorkerBase):
             dev = eng.device
             xd = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1).to(dev)
             yd = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1).to(dev)
-            if store.mirror is not None and not store.locked and trainable:
+            if store.mirror is not None and (not store.locked or store.stream_exclusive) and trainable:
                 self._train_fused_pull(eng, store, xd, yd, epochs, batch_size)
                 torch.cuda.current_stream(eng.device).synchronize()
                 return
@@ -290,17 +290,27 @@ class AsynchronousSparkWorker(_WorkerBase):
         saved = (eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step)
         eng.pull_source = store.mirror.data_ptr()
         eng.delta_target = delta16
-        eng.pre_step = (lambda: store.pull_range_into(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
-        eng.post_step = lambda: store.push_delta(delta_bf16=delta16)
+        eng.pre_step = (lambda: store.raw_pull_range(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
+        eng.post_step = lambda: store.raw_push(delta_bf16=delta16)
+        # mode='asynchronous' inside one process: the store's in-order stream is the lock, and the whole batch (pull,
+        # step, push) runs on it as ONE exclusive operation - the strictest form of the reference's locked updates
+        exclusive = store.stream_exclusive
+
+        def one_batch(lo, rows):
+            buf = eng._buf(rows)
+            buf.x32.copy_(xd[lo:lo + rows])
+            buf.y32.copy_(yd[lo:lo + rows])
+            eng.train_step_device(buf)
+
         try:
             store.push_delta(delta_bf16=delta16)  # all-zero delta: loads the push kernel outside of graph capture
             for _ in range(epochs):
                 for lo in range(0, n, batch_size):
                     rows = min(batch_size, n - lo)
-                    buf = eng._buf(rows)
-                    buf.x32.copy_(xd[lo:lo + rows])
-                    buf.y32.copy_(yd[lo:lo + rows])
-                    eng.train_step_device(buf)
+                    if exclusive:
+                        store.exclusive(lambda: one_batch(lo, rows))
+                    else:
+                        one_batch(lo, rows)
                     STATS['fused_pull_steps'] += 1
             torch.cuda.current_stream(eng.device).synchronize()
         finally:

@@ -150,13 +150,22 @@ def test_hogwild_batch_uses_the_pull_fused_gemm(spark_context):
     assert _worker.STATS['fused_pull_steps'] - before_steps == 2 * 2 * 8  # 2 workers x 2 epochs x 512/64 batches
     after = sm.evaluate(xt, yt)
     assert after[0] < before[0] and after[1] > 0.8
-    # the locked mode keeps the copy-under-lock pull
+    # the locked mode inside one process: whole pull+step+push graphs, serialised by the store's stream
     model2 = zoo.mnist_mlp()
     model2.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
     sm2 = SparkModel(model2, mode='asynchronous', frequency='batch', parameter_server_mode='nvlink', num_workers=2,
                      port=next(_ports))
     steps = _worker.STATS['fused_pull_steps']
-    sm2.fit(to_simple_rdd(spark_context, x, y), epochs=1, batch_size=64, verbose=0)
+    before2 = sm2.evaluate(xt, yt)
+    sm2.fit(to_simple_rdd(spark_context, x, y), epochs=2, batch_size=64, verbose=0)
+    assert _worker.STATS['fused_pull_steps'] - steps == 2 * 2 * 8
+    after2 = sm2.evaluate(xt, yt)
+    assert after2[0] < before2[0] and after2[1] > 0.8
+    # frequency='epoch' keeps the copy-under-lock pull
+    sm3 = SparkModel(model2, mode='asynchronous', frequency='epoch', parameter_server_mode='nvlink', num_workers=2,
+                     port=next(_ports))
+    steps = _worker.STATS['fused_pull_steps']
+    sm3.fit(to_simple_rdd(spark_context, x, y), epochs=1, batch_size=64, verbose=0)
     assert _worker.STATS['fused_pull_steps'] == steps
 
 

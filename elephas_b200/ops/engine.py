@@ -244,6 +244,7 @@ class MLPEngine:
         self.pull_source = None   # device address of a bf16 weight mirror the training forward GEMMs pull from (K2)
         self.pre_step = None      # callables run (and captured) at the start / end of every training step
         self.post_step = None
+        self.mid_step = None      # ... and between the forward pass and the loss
         self.comm_join = None     # callable(): make the compute stream wait for all communication of the step
         self._in_warmup = False
         if self.trainable:
@@ -535,6 +536,8 @@ class MLPEngine:
         if self.pre_step is not None:
             self.pre_step()   # e.g. pull of the bias tail from a parameter server (captured with the step)
         self._forward(buf, training=True)
+        if self.mid_step is not None:
+            self.mid_step()   # e.g. release of a parameter-server lock held while the forward GEMMs pulled the weights
         self._loss(buf, with_grad=True)
         self._backward(buf)
         self._optimizer()

@@ -381,6 +381,17 @@ def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32
 
 
 # ------------------------------------------------------------ parameter server
+def ps_lock(ctrl, device=None):
+    """Enqueue the ticket-lock kernel of a device parameter server (pair every call with :func:`ps_unlock`)."""
+    cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
+    _check(require().eb_ps_lock(cptr, _stream(device if device is not None else ctrl.device)), 'eb_ps_lock')
+
+
+def ps_unlock(ctrl, device=None):
+    cptr = ctrl.data_ptr() if hasattr(ctrl, 'data_ptr') else ctrl
+    _check(require().eb_ps_unlock(cptr, _stream(device if device is not None else ctrl.device)), 'eb_ps_unlock')
+
+
 def ps_pull(master, ctrl, dst_f32, dst_bf16=None, locked=False, n=None, offset=0):
     lib = require()
     s = _stream(dst_f32.device if dst_f32 is not None else dst_bf16.device)

@@ -167,6 +167,20 @@ class DeviceStore:
         native.ps_push(self.flat, self.ctrl, delta_flat, None, None, locked=False, mirror=self.mirror,
                        delta_bf16=delta_bf16)
 
+    def raw_lock(self):
+        from ..ops import native
+        native.ps_lock(self.ctrl, self.device)
+
+    def raw_unlock(self):
+        from ..ops import native
+        native.ps_unlock(self.ctrl, self.device)
+
+    @property
+    def ticket_only(self):
+        """Locked store whose exclusion is the ticket lock alone (one worker per rank): lock / unlock kernels may be
+        recorded into the worker's own step graph - every other holder runs on another GPU."""
+        return self.locked and self._exclusion == 'ticket' and self.flat.is_cuda
+
     @property
     def stream_exclusive(self):
         """True when locked operations are serialised by the store's own stream (one process, no ticket kernels): a

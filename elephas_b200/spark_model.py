@@ -235,11 +235,13 @@ class SparkModel:
     def _fit_parameter_server(self, rt, partitions, mine, train_config):
         # per-batch pulls on GPUs: the store publishes a bf16 mirror and the workers' forward GEMMs read the weights
         # straight from it (pull fused into the GEMM, K2) - hogwild always, the locked mode when all workers live in this
-        # process (the store's stream then serialises whole pull+step+push graphs); across ranks the locked mode keeps
-        # the copy-under-lock pull
+        # process (the store's stream then serialises whole pull+step+push graphs) or, with one worker per rank and a
+        # small model, with the ticket lock recorded into the step graph; otherwise it keeps the copy-under-lock pull
         fused_pull = (self.parameter_server_mode == 'nvlink' and self.frequency == 'batch' and rt.device.type == 'cuda'
-                      and (self.mode == 'hogwild' or not rt.distributed)
+                      and (self.mode == 'hogwild' or not rt.distributed or len(mine) <= 1)
                       and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
+        if rt.distributed:
+            fused_pull = bool(rt.broadcast_object(fused_pull, src=0))  # owner and proxies must agree on the mirror
         if hasattr(self.parameter_server, 'fused_pull'):
             self.parameter_server.fused_pull = fused_pull
         if rt.is_driver:

@@ -51,6 +51,9 @@ def _weights_of(parameters):
 
 # counters for tests / diagnostics: which device paths actually ran in this process
 STATS = {'fused_pull_steps': 0}
+# largest model (parameters) whose locked per-batch pull across ranks is fused into the forward pass: the lock is then held
+# for the forward instead of for one copy kernel, which only pays while the step is launch-bound
+FUSED_LOCKED_MAX = 4 << 20
 
 class _WorkerBase:
     def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
@@ -253,7 +256,8 @@ class AsynchronousSparkWorker(_WorkerBase):
             dev = eng.device
             xd = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1).to(dev)
             yd = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1).to(dev)
-            if store.mirror is not None and (not store.locked or store.stream_exclusive) and trainable:
+            if store.mirror is not None and trainable and (not store.locked or store.stream_exclusive or
+                                                           (store.ticket_only and eng.layout.numel <= FUSED_LOCKED_MAX)):
                 self._train_fused_pull(eng, store, xd, yd, epochs, batch_size)
                 torch.cuda.current_stream(eng.device).synchronize()
                 return
@@ -287,11 +291,26 @@ class AsynchronousSparkWorker(_WorkerBase):
         tail_lo, tail_n = lay.matrix_end, lay.numel - lay.matrix_end
         delta16 = torch.zeros(lay.numel, dtype=torch.bfloat16, device=eng.device)
         n = xd.shape[0]
-        saved = (eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step)
+        saved = (eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step, eng.mid_step)
         eng.pull_source = store.mirror.data_ptr()
         eng.delta_target = delta16
-        eng.pre_step = (lambda: store.raw_pull_range(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
-        eng.post_step = lambda: store.raw_push(delta_bf16=delta16)
+        if store.ticket_only:
+            # mode='asynchronous' across ranks, small model: the ticket lock is taken inside the graph, once around the
+            # pulling forward pass and once around the push (a rank's holders are always on other GPUs)
+            def pre():
+                store.raw_lock()
+                if tail_n > 0:
+                    store.raw_pull_range(eng.w32, tail_lo, tail_n)
+
+            def post():
+                store.raw_lock()
+                store.raw_push(delta_bf16=delta16)
+                store.raw_unlock()
+
+            eng.pre_step, eng.mid_step, eng.post_step = pre, store.raw_unlock, post
+        else:
+            eng.pre_step = (lambda: store.raw_pull_range(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
+            eng.post_step = lambda: store.raw_push(delta_bf16=delta16)
         # mode='asynchronous' inside one process: the store's in-order stream is the lock, and the whole batch (pull,
         # step, push) runs on it as ONE exclusive operation - the strictest form of the reference's locked updates
         exclusive = store.stream_exclusive
@@ -314,7 +333,7 @@ class AsynchronousSparkWorker(_WorkerBase):
                     STATS['fused_pull_steps'] += 1
             torch.cuda.current_stream(eng.device).synchronize()
         finally:
-            eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step = saved
+            eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step, eng.mid_step = saved
             eng.invalidate_graphs()  # the recorded steps hold the store's addresses
         store.pull_into(eng.w32, eng.w16)  # leave the replica with a complete, current copy
         eng._weights_dirty_in_model = True

@@ -507,50 +507,58 @@ class SyncContext:
             before = torch.empty_like(eng.w32) if (distributed and not per_batch) else None
             t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             t0.record()
-            for epoch in range(epochs):
-                if before is not None and (epoch == 0 or sync_rounds != 'fit'):
-                    before.copy_(eng.w32)
-                eng.stats.zero_()
-                if feeder:
-                    feeder.start_epoch()
-                start = 0
-                t_loop = time.perf_counter()
-                for s in range(steps):
-                    have = s < steps_local
-                    buf = None
-                    if have:
-                        rows = min(bs, len(x) - start)
-                        buf = eng._buf(rows)
-                        feeder.load(s, start, buf)
-                        start += rows
-                    self._step(buf, per_batch, have)
-                    if log_batch_loss:
-                        slot = s % 2
-                        pinned[slot].copy_(eng.stats, non_blocking=True)
-                        events[slot].record()
-                        if s > 0:
-                            events[1 - slot].synchronize()
-                            p = pinned[1 - slot]
-                            batch_losses.append(float(p[0] / max(float(p[7]), 1.0)))
-                if log_batch_loss and steps > 0:
-                    slot = (steps - 1) % 2
-                    events[slot].synchronize()
-                    batch_losses.append(float(pinned[slot][0] / max(float(pinned[slot][7]), 1.0)))
-                tracing.add_host('sync/step_loop', time.perf_counter() - t_loop)
-                with tracing.span('sync/read_stats'):
-                    vals, count = eng.read_stats()
-                logs = dict(zip(names, vals)) if count else {}
-                if before is not None and (sync_rounds != 'fit' or epoch == epochs - 1):
-                    # delta = before - after (fp32, straight into peer-mapped memory), reset, fused reduce+update
-                    native.delta(before, eng.w32, out_f32=self.delta[self.flip])
-                    eng.w32.copy_(before)
-                    self._allreduce_update()
-                    self.flip ^= 1
-                if x_val is not None and len(x_val) and logs:
-                    val = eng.evaluate(x_val, y_val)
-                    logs.update({'val_' + k: v for k, v in zip(names, val)})
-                if logs:
-                    history._append(epoch, logs)
+            try:
+                for epoch in range(epochs):
+                    if before is not None and (epoch == 0 or sync_rounds != 'fit'):
+                        before.copy_(eng.w32)
+                    eng.stats.zero_()
+                    if feeder:
+                        feeder.start_epoch()
+                    start = 0
+                    t_loop = time.perf_counter()
+                    for s in range(steps):
+                        have = s < steps_local
+                        buf = None
+                        if have:
+                            rows = min(bs, len(x) - start)
+                            buf = eng._buf(rows)
+                            feeder.load(s, start, buf)
+                            start += rows
+                        self._step(buf, per_batch, have)
+                        if log_batch_loss:
+                            slot = s % 2
+                            pinned[slot].copy_(eng.stats, non_blocking=True)
+                            events[slot].record()
+                            if s > 0:
+                                events[1 - slot].synchronize()
+                                p = pinned[1 - slot]
+                                batch_losses.append(float(p[0] / max(float(p[7]), 1.0)))
+                    if log_batch_loss and steps > 0:
+                        slot = (steps - 1) % 2
+                        events[slot].synchronize()
+                        batch_losses.append(float(pinned[slot][0] / max(float(pinned[slot][7]), 1.0)))
+                    tracing.add_host('sync/step_loop', time.perf_counter() - t_loop)
+                    with tracing.span('sync/read_stats'):
+                        vals, count = eng.read_stats()
+                    logs = dict(zip(names, vals)) if count else {}
+                    if before is not None and (sync_rounds != 'fit' or epoch == epochs - 1):
+                        # delta = before - after (fp32, straight into peer-mapped memory), reset, fused reduce+update
+                        native.delta(before, eng.w32, out_f32=self.delta[self.flip])
+                        eng.w32.copy_(before)
+                        self._allreduce_update()
+                        self.flip ^= 1
+                    if x_val is not None and len(x_val) and logs:
+                        val = eng.evaluate(x_val, y_val)
+                        logs.update({'val_' + k: v for k, v in zip(names, val)})
+                    if logs:
+                        history._append(epoch, logs)
+            except BaseException:
+                # leave the engine usable (and the feeder thread stopped) when a step fails
+                eng.delta_target = None
+                eng.input_bf16 = False
+                if feeder is not None:
+                    feeder.close()
+                raise
             with tracing.device_span('sync/gather_master'):
                 self._gather_master()
             t1.record()

@@ -30,6 +30,15 @@ sys.path.insert(0, ROOT)
 METRIC = "samples/sec (device-timed, max over ranks)"
 
 
+_REAL_STDOUT = sys.stdout
+
+
+def print_result(line):
+    """The ONE JSON line of the contract goes to the real stdout; everything the framework prints while it runs (the
+    reference's '>>> Fit model' progress lines among it) is routed to stderr by main()."""
+    print(line, file=_REAL_STDOUT, flush=True)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -45,26 +54,53 @@ def parse():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clocks and throttle reasons while the timed region runs: through NVML (a query takes microseconds, so
+    a 50 ms region yields dozens of samples), falling back to ``nvidia-smi`` (one sample per ~100 ms) without it."""
 
     FIELDS = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
               'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+    NAMES = ('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap')
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], threading.Event()
+        self.nvml = self.handle = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            visible = os.environ.get('CUDA_VISIBLE_DEVICES')
+            physical = int(visible.split(',')[index]) if visible and visible.split(',')[index].isdigit() else index
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(physical)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _nvml_sample(self):
+        n = self.nvml
+        mhz = n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)
+        get = getattr(n, 'nvmlDeviceGetCurrentClocksEventReasons', None) or n.nvmlDeviceGetCurrentClocksThrottleReasons
+        mask = int(get(self.handle))
+        bits = {'hw_slowdown': 0x8, 'hw_thermal_slowdown': 0x40, 'sw_thermal_slowdown': 0x20, 'sw_power_cap': 0x4}
+        flags = ['Active' if mask & bits[k] else 'Not Active' for k in self.NAMES]
+        return [str(mhz), str(self.max_mhz)] + flags
 
     def run(self):
         while not self.stop_flag.is_set():
             try:
+                if self.nvml is not None:
+                    self.samples.append(self._nvml_sample())
+                    self.stop_flag.wait(0.002)
+                    continue
                 out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.FIELDS,
                                       '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
                 parts = [p.strip() for p in out.strip().split(',')]
                 if len(parts) >= 6:
                     self.samples.append(parts)
             except Exception:
-                pass
-            self.stop_flag.wait(0.2)
+                if self.nvml is not None:
+                    self.nvml = None  # NVML refused: fall back to nvidia-smi for the rest of the run
+            self.stop_flag.wait(0.2 if self.nvml is None else 0.002)
 
     def summary(self):
         self.stop_flag.set()
@@ -74,11 +110,12 @@ class ClockSampler(threading.Thread):
         clocks = sorted(int(float(s[0])) for s in self.samples)
         reasons = set()
         for s in self.samples:
-            for name, val in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), s[2:6]):
+            for name, val in zip(self.NAMES, s[2:6]):
                 if val.lower().startswith('active'):
                     reasons.add(name)
         return {'sm_mhz': clocks[len(clocks) // 2], 'sm_max_mhz': int(float(self.samples[0][1])),
-                'reasons': sorted(reasons), 'samples': len(clocks)}
+                'reasons': sorted(reasons), 'samples': len(clocks),
+                'source': 'nvml' if self.nvml is not None else 'nvidia-smi'}
 
 
 def build_model(args):
@@ -129,7 +166,7 @@ def reference_arm():
     except Exception as exc:
         why = ("reference (elephas 4.1.0) not installable in this image: %s; it also needs tensorflow<=2.10, "
                "pyspark<=3.3, flask, h5py and python<3.11, none of which are available offline" % exc)
-    print(json.dumps({'impl': 'reference', 'unavailable': why or 'reference stack import failed'}))
+    print_result(json.dumps({'impl': 'reference', 'unavailable': why or 'reference stack import failed'}))
 
 
 def run_ours(args, rt):
@@ -159,8 +196,8 @@ def run_ours(args, rt):
     ctx = spark_model._sync_context
     launches_before = native.launch_count()
     sampler = ClockSampler(rt.local_rank)
-    sampler.start()
-    ms_kernel = ctx.timed_steps(xk, yk, K, input_mode='device')
+    # the sampler covers exactly the timed steps (not the upload of the data set that precedes them)
+    ms_kernel = ctx.timed_steps(xk, yk, K, input_mode='device', on_start=sampler.start, on_stop=sampler.stop_flag.set)
     launches = native.launch_count() - launches_before
     clocks = sampler.summary()
 
@@ -213,7 +250,7 @@ def run_ours(args, rt):
         'tflops_per_gpu': round(flops_step / (ms_total / K / 1e3) / 1e12, 1),
     }
     if rt.is_driver:
-        print(json.dumps(result))
+        print_result(json.dumps(result))
     spark_model.release_context()
 
 
@@ -271,7 +308,7 @@ def run_ddp(args, rt):
     rt.all_reduce_max_(t)
     ms = float(t[0])
     if rt.is_driver:
-        print(json.dumps({'metric': METRIC, 'value': round(N * B * K / (ms / 1e3), 2), 'unit': 'samples/sec',
+        print_result(json.dumps({'metric': METRIC, 'value': round(N * B * K / (ms / 1e3), 2), 'unit': 'samples/sec',
                           'n_gpus': N, 'steps': K, 'warmup': W, 'ms_per_step': round(ms / K, 4),
                           'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16',
                           'data': 'synthetic', 'impl': 'ddp',
@@ -281,12 +318,13 @@ def run_ddp(args, rt):
 
 def main():
     args = parse()
+    sys.stdout = sys.stderr  # keep stdout clean for the result line
     if args.impl == 'reference':
         reference_arm()
         return
     import torch
     if not torch.cuda.is_available():
-        print(json.dumps({'metric': METRIC, 'value': None, 'unavailable': 'no CUDA device', 'impl': args.impl}))
+        print_result(json.dumps({'metric': METRIC, 'value': None, 'unavailable': 'no CUDA device', 'impl': args.impl}))
         return
     os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
     from elephas_b200.parallel import get_runtime

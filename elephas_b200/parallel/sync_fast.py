@@ -581,7 +581,7 @@ class SyncContext:
         return [h for _, h in sorted(gathered, key=lambda t: t[0])]
 
     # ------------------------------------------------------------- kernel timing
-    def timed_steps(self, x, y, steps, input_mode='device'):
+    def timed_steps(self, x, y, steps, input_mode='device', on_start=None, on_stop=None):
         """Device time (ms, CUDA events) of exactly ``steps`` synchronous ``frequency='batch'`` steps on data
         that is already resident on the device: the kernel-path number of bench.py."""
         rt, eng, bs = self.rt, self.eng, self.bs
@@ -596,6 +596,8 @@ class SyncContext:
             torch.cuda.synchronize(rt.device)
             rt.barrier()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if on_start is not None:
+                on_start()  # (e.g. a clock sampler that must cover exactly the timed region)
             e0.record()
             start = 0
             for s in range(steps):
@@ -606,6 +608,8 @@ class SyncContext:
                 self._step(buf, per_batch, True)
             e1.record()
             torch.cuda.synchronize(rt.device)
+            if on_stop is not None:
+                on_stop()
             rt.barrier()
             eng.delta_target = None
             eng.input_bf16 = False

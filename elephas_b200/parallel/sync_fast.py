@@ -601,6 +601,8 @@ class SyncContext:
             e0.record()
             start = 0
             for s in range(steps):
+                if start >= len(x):
+                    start = 0  # more steps than batches in the data: cycle
                 rows = min(bs, len(x) - start)
                 buf = eng._buf(rows)
                 feeder.load(s, start, buf)

@@ -5,7 +5,6 @@ Reference use: ``['acc']`` (``tests/integration/test_end_to_end.py:40``), ``['ma
 'mean_absolute_percentage_error']`` (``:92``), ``['mae']`` (``tests/test_ml_model.py:151``).
 Each metric returns a per-sample vector; callers average.
 """
-import torch
 
 from . import losses as _losses
 

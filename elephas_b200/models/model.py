@@ -14,7 +14,6 @@ every workload the reference ships) trains and predicts through the native sm_10
 every other model, and every model on the CPU, runs through torch autograd.
 """
 import json
-import math
 
 import numpy as np
 import torch

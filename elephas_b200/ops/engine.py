@@ -24,7 +24,6 @@ Weights live in one flat fp32 master buffer plus an index-identical bf16 compute
 ``Model`` tensors lazily.
 """
 import gc
-import math
 import os
 import threading
 

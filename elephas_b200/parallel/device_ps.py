@@ -17,7 +17,6 @@ exercises.
 """
 import threading
 
-import numpy as np
 import torch
 
 from ..utils.rwlock import RWLock

@@ -66,6 +66,20 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
 _HOST_BF16_CHOICE = {}  # (rows, cols, threads) -> bool: measured once per process
 
 
+def _host_threads():
+    """CPU threads for the host-side input cast: ``ELEPHAS_B200_HOST_THREADS``, else this rank's share of the cores
+    (minus one for the Python threads that drive the GPU), between 1 and 16."""
+    forced = os.environ.get('ELEPHAS_B200_HOST_THREADS')
+    if forced:
+        return max(1, int(forced))
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except (AttributeError, OSError):
+        cores = os.cpu_count() or 1
+    ranks_here = max(1, int(os.environ.get('LOCAL_WORLD_SIZE', '1')))
+    return max(1, min(16, cores // ranks_here - 1))
+
+
 class _InputFeeder:
     """Delivers batches into the engine's static input buffers.
 
@@ -98,7 +112,7 @@ class _InputFeeder:
         else:
             self.copy_stream = torch.cuda.Stream(dev)
             cols, ycols = self.x_host.shape[1], self.y_host.shape[1]
-            self.threads = int(os.environ.get('ELEPHAS_B200_HOST_THREADS', '6'))
+            self.threads = _host_threads()
             self.host_bf16 = self._choose_host_bf16(eng, batch_size)
             if self.host_bf16:
                 ld = eng.ops[0].ld_in
@@ -121,11 +135,13 @@ class _InputFeeder:
 
     def _choose_host_bf16(self, eng, batch_size):
         """Cast the features to bf16 on the host (half the PCIe bytes) or stream them as fp32 and cast on the device?
-        ``ELEPHAS_B200_HOST_BF16=1|0`` decides; otherwise one batch is timed both ways, once per process and input
-        width: with pipelining a step pays max(host cast, bf16 copy) against the fp32 copy. Few cores per GPU favour
+        ``ELEPHAS_B200_HOST_BF16=1|0`` decides (default 0); with ``auto`` one batch is timed both ways, once per process and
+        input width: with pipelining a step pays max(host cast, bf16 copy) against the fp32 copy. Few cores per GPU favour
         the fp32 copy, many GPUs sharing the host's PCIe switches favour the cast."""
-        forced = os.environ.get('ELEPHAS_B200_HOST_BF16', 'auto')
-        if forced in ('0', '1'):
+        # default off: on the hosts measured so far (16 vCPUs for one GPU, 32 for eight) the pipelined cast ends up slower
+        # than the fp32 copy even where the one-batch calibration says otherwise (2.74 vs 2.65 ms/step end to end)
+        forced = os.environ.get('ELEPHAS_B200_HOST_BF16', '0')
+        if forced != 'auto':
             return forced == '1'
         rows = min(batch_size, self.n)
         cols = self.x_host.shape[1]

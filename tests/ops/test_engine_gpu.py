@@ -326,7 +326,7 @@ def test_streamed_inputs_cast_on_the_host_match_device_staging(spark_context, mo
         assert np.allclose(a, b, atol=1e-5, rtol=1e-4), np.abs(a - b).max()
     assert np.allclose(results[0][1], results[1][1], rtol=1e-4) and len(results[0][1]) == 3 * 8
     # without an override the feeder times both ways once and picks one
-    monkeypatch.delenv('ELEPHAS_B200_HOST_BF16')
+    monkeypatch.setenv('ELEPHAS_B200_HOST_BF16', 'auto')
     from elephas_b200.parallel import sync_fast
     sync_fast._HOST_BF16_CHOICE.clear()
     sm.fit(to_simple_rdd(spark_context, x, y), epochs=1, batch_size=128, input_mode='stream')

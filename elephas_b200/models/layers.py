@@ -446,6 +446,12 @@ class Conv2D(Layer):
             pads = _same_pad(x, self.kernel_size, self.strides, self.dilation_rate)
             if any(pads):
                 x = F.pad(x, (0, 0) + tuple(pads))
+        if x.is_cuda and torch.is_autocast_enabled('cuda'):
+            from ..ops import conv1x1 as _c1
+            # bf16 compute on a GPU: 1x1 / stride-1 convolutions can run on the tcgen05 GEMM (opt-in, ops/conv1x1.py)
+            if _c1.enabled() and _c1.eligible(x, self.kernel, self.strides, self.dilation_rate, self.groups,
+                                              self.padding == 'same' and self.kernel_size != (1, 1)):
+                return self.activation(_c1.conv1x1(x, self.kernel, self.bias))
         y = F.conv2d(x.permute(0, 3, 1, 2), self.kernel, self.bias, stride=self.strides,
                      dilation=self.dilation_rate, groups=self.groups)
         return self.activation(y.permute(0, 2, 3, 1))

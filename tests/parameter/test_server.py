@@ -84,3 +84,30 @@ def test_http_home_route():
         assert urllib.request.urlopen('http://%s/' % server.master_url).read() == b'Elephas'
     finally:
         server.stop()
+
+
+def test_device_store_exclusion_policy_on_cpu():
+    """``configure`` picks how mode='asynchronous' excludes writers; on CPU tensors the host RWLock does the work and
+    the GPU-only shortcuts stay off."""
+    import numpy as np
+    from elephas_b200.models import Dense, Sequential
+    from elephas_b200.parallel.device_ps import create_store, destroy_store
+    import torch
+    model = Sequential([Dense(4, input_dim=6), Dense(2)])
+    weights = model.get_weights()
+    store = create_store(45991, weights, 'asynchronous', model=model, device=torch.device('cpu'))
+    try:
+        assert store._exclusion == 'ticket+stream'
+        store.configure(local_workers=3, distributed=False)
+        assert store._exclusion == 'stream' and not store.stream_exclusive and not store.ticket_only  # CPU store
+        store.configure(local_workers=1, distributed=True)
+        assert store._exclusion == 'ticket'
+        store.configure(local_workers=2, distributed=True)
+        assert store._exclusion == 'ticket+stream'
+        delta = [np.ones_like(w) for w in weights]
+        store.push_arrays(delta)
+        for got, w in zip(store.pull_arrays(), weights):
+            assert np.allclose(got, w - 1.0)
+        assert store.mirror is None and store.pushes == 1
+    finally:
+        destroy_store(45991)

@@ -226,7 +226,7 @@ def test_graphed_torch_step_matches_eager(monkeypatch, opt_name):
     assert b._torch_engine() is None
     for wa, wb in zip(a.get_weights(), b.get_weights()):
         if opt_name == 'sgd_momentum':
-            assert np.allclose(wa, wb, atol=2e-4, rtol=2e-3), np.abs(wa - wb).max()
+            assert np.allclose(wa, wb, atol=1e-3, rtol=5e-3), np.abs(wa - wb).max()
         else:
             # adaptive optimizers turn a last-bit difference of a tiny gradient (cuDNN's backward kernels are not
             # run-to-run deterministic) into a full-size step: compare on average

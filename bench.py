@@ -225,7 +225,9 @@ def run_ours(args, rt):
         rt.barrier()
         torch.cuda.synchronize()
         tracing.reset()
-        Ke = min(K, E2E_MAX)  # steps of the end-to-end run (every one streams its own pinned host batch)
+        # steps of the end-to-end run (every one streams its own pinned host batch); at least 2: a partition that is
+        # not larger than one batch is skipped by design (reference guard, elephas/worker.py:41)
+        Ke = max(2, min(K, E2E_MAX))
         xe, ye = tile_pinned(xk, Ke * B), tile_pinned(yk, Ke * B)
         rt.barrier()
         t0 = time.perf_counter()

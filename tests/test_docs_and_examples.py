@@ -25,3 +25,22 @@ def test_example_runs(script):
     res = subprocess.run([sys.executable, script], cwd=os.path.join(ROOT, 'examples'), env=env, capture_output=True,
                          text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+
+
+def test_pipeline_notebook_cells_run(tmp_path):
+    """examples/Spark_ML_Pipeline.ipynb (the reference ships the same notebook): its code cells execute in order."""
+    import json
+    nb = json.load(open(os.path.join(ROOT, 'examples', 'Spark_ML_Pipeline.ipynb')))
+    assert nb['nbformat'] == 4 and nb['cells'][0]['cell_type'] == 'markdown'
+    code = '\n\n'.join(''.join(c['source']) for c in nb['cells'] if c['cell_type'] == 'code')
+    script = os.path.join(ROOT, 'examples', '_nb_cells_check.py')
+    with open(script, 'w') as fh:
+        fh.write(code)
+    try:
+        env = dict(os.environ, ELEPHAS_B200_DEVICE='cpu', SPARK_LOCAL_IP='127.0.0.1')
+        res = subprocess.run([sys.executable, script], cwd=os.path.join(ROOT, 'examples'), env=env, capture_output=True,
+                             text=True, timeout=600)
+    finally:
+        os.remove(script)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert 'train precision' in res.stdout

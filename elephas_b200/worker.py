@@ -277,7 +277,9 @@ class AsynchronousSparkWorker(_WorkerBase):
 
     @staticmethod
     def _train_fused_pull(eng, store, xd, yd, epochs, batch_size):
-        """Hogwild, ``frequency='batch'``, device parameter server with a bf16 mirror: ONE graph replay per batch.
+        """``frequency='batch'`` against a device parameter server with a bf16 mirror: ONE graph replay per batch.
+        (hogwild: always; asynchronous: inside one process - the store's stream serialises whole batches - or, with one
+        worker per rank and a small model, with the ticket lock recorded around the pulling forward and the push.)
 
         pull   = the forward GEMMs read their weight tiles from the store's mirror (peer memory over NVLink) through
                  TMA and side-write them into the local copy the backward pass uses (K2); only the bias tail is copied

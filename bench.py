@@ -30,13 +30,14 @@ sys.path.insert(0, ROOT)
 METRIC = "samples/sec (device-timed, max over ranks)"
 
 
-_REAL_STDOUT = sys.stdout
+_RESULT_FD = os.dup(1)  # the real stdout, kept aside before main() points fd 1 at stderr
 
 
 def print_result(line):
-    """The ONE JSON line of the contract goes to the real stdout; everything the framework prints while it runs (the
-    reference's '>>> Fit model' progress lines among it) is routed to stderr by main()."""
-    print(line, file=_REAL_STDOUT, flush=True)
+    """The ONE JSON line of the contract goes to the real stdout; everything else that would land there while the run
+    is in progress - the reference's '>>> Fit model' progress lines, but also what C libraries write to fd 1 directly
+    (NCCL prints its version banner there when the first communicator comes up) - is routed to stderr by main()."""
+    os.write(_RESULT_FD, (line + '\n').encode())
 
 
 def parse():
@@ -339,12 +340,16 @@ def run_ddp(args, rt):
 
 def main():
     args = parse()
+    sys.stdout.flush()
+    os.dup2(2, 1)            # fd level: C libraries (NCCL) write to fd 1 without going through sys.stdout
     sys.stdout = sys.stderr  # keep stdout clean for the result line
     if args.impl == 'reference':
         reference_arm()
         return
     import torch
     if not torch.cuda.is_available():
+        if os.environ.get('RANK', '0') != '0':
+            return
         print_result(json.dumps({'metric': METRIC, 'value': None, 'unavailable': 'no CUDA device', 'impl': args.impl}))
         return
     os.environ.setdefault('MASTER_ADDR', '127.0.0.1')

@@ -11,6 +11,8 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 
+#include <mutex>
+
 #include "../include/elephas_b200.h"
 #include "host.h"
 #include "math.cuh"
@@ -166,10 +168,17 @@ extern "C" int eb_head_fwd(const EbHeadArgs* a, void* stream) {
   if (a->z == nullptr) return fail("eb_head_fwd: output missing");
   const size_t smem = static_cast<size_t>(a->out) * a->K * 2;
   if (smem > 96 * 1024) return fail("eb_head_fwd: weights (%zu bytes) do not fit in shared memory", smem);
-  static bool attr_done = false;
-  if (!attr_done) {
-    EB_CUDA_OK(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-    attr_done = true;
+  {
+    // once per device; several worker threads may get here at the same time
+    static std::mutex init_mutex;
+    static bool attr_done[64] = {false};
+    int dev = 0;
+    EB_CUDA_OK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> guard(init_mutex);
+    if (!attr_done[dev & 63]) {
+      EB_CUDA_OK(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      attr_done[dev & 63] = true;
+    }
   }
   int blocks = (a->rows + 7) / 8;
   const int cap = num_sms() * 4;

@@ -21,7 +21,7 @@ from elephas_b200.spark import SparkConf, SparkContext
 
 rt = get_runtime()
 rng = np.random.default_rng(0)
-n, side, classes = 2048, 16, 4
+n, side, classes = (2048 if rt.device.type == 'cuda' else 768), 16, 4  # (smaller on a CPU: the eager path is slow)
 labels = rng.integers(0, classes, n)
 x = rng.normal(size=(n, side, side, 3)).astype('float32')
 for c in range(classes):  # class c brightens one quadrant

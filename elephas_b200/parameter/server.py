@@ -151,12 +151,26 @@ class HttpServer(BaseParameterServer):
         self._thread.start()
         self.master_url = determine_master(self.port)
 
+    def start_flask_service(self):
+        """Blocking form of :meth:`start` under the reference's name (``elephas/parameter/server.py:91``, where it is
+        the target of the server process): serves ``/``, ``/parameters`` and ``/update`` in the calling thread until
+        :meth:`stop` is called from another one. The service is the stdlib HTTP server here, not Flask (D11)."""
+        if self._httpd is not None:
+            self.stop()
+        host = determine_master(self.port).split(':')[0]
+        ThreadingHTTPServer.allow_reuse_address = True
+        self._httpd = ThreadingHTTPServer((host, self.port), self._handler_class())
+        self._httpd.daemon_threads = True
+        self.master_url = determine_master(self.port)
+        self._httpd.serve_forever(poll_interval=0.05)
+
     def stop(self):
         if self._httpd is None:
             return
         self._httpd.shutdown()
         self._httpd.server_close()
-        self._thread.join()
+        if self._thread is not None:
+            self._thread.join()
         self._httpd = None
         self._thread = None
 
@@ -195,6 +209,24 @@ class SocketServer(BaseParameterServer):
         if self.socket is not None:
             self.socket.close()
             self.socket = None
+
+    def start_server(self):
+        """Blocking form of :meth:`start` under the reference's name (``elephas/parameter/server.py:173``, the target
+        of its server thread): binds and runs the accept loop in the calling thread until :meth:`stop_server`."""
+        sock = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+        sock.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+        sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+        host = determine_master(port=self.port).split(':')[0]
+        sock.bind((host, self.port))
+        sock.listen(64)
+        sock.settimeout(0.1)
+        self.socket = sock
+        self.runs = True
+        self.run()
+
+    def stop_server(self):
+        """Reference name of :meth:`stop` (``elephas/parameter/server.py:184``)."""
+        self.stop()
 
     def update_parameters(self, conn):
         data = receive(conn)

@@ -111,3 +111,38 @@ def test_device_store_exclusion_policy_on_cpu():
         assert store.mirror is None and store.pushes == 1
     finally:
         destroy_store(45991)
+
+
+def test_reference_method_names_of_the_servers_work_as_blocking_services():
+    """``HttpServer.start_flask_service`` and ``SocketServer.start_server`` / ``stop_server`` (the reference's entry
+    points, run there as process / thread targets) serve in the calling thread until stopped."""
+    import threading
+    import time
+    import numpy as np
+    from elephas_b200.models import Dense, Sequential
+    from elephas_b200.parameter.client import HttpClient, SocketClient
+    from elephas_b200.parameter.server import HttpServer, SocketServer
+    from elephas_b200.utils.serialization import model_to_dict
+    model = Sequential([Dense(3, input_dim=4), Dense(1)])
+    for cls, client_cls, port, entry, stop in ((HttpServer, HttpClient, 45981, 'start_flask_service', 'stop'),
+                                               (SocketServer, SocketClient, 45982, 'start_server', 'stop_server')):
+        server = cls(model_to_dict(model), port, 'asynchronous')
+        t = threading.Thread(target=getattr(server, entry), daemon=True)
+        t.start()
+        client = client_cls(port)
+        for _ in range(100):
+            try:
+                before = client.get_parameters()
+                break
+            except Exception:
+                time.sleep(0.05)
+        else:
+            raise AssertionError('server did not come up')
+        client.update_parameters([np.ones_like(w) for w in before])
+        after = client.get_parameters()
+        assert all(np.allclose(a, b - 1.0) for a, b in zip(after, before))
+        if hasattr(client, 'close'):
+            client.close()
+        getattr(server, stop)()
+        t.join(timeout=10)
+        assert not t.is_alive()

@@ -29,8 +29,9 @@ from ..spark import Param, Params
 _UNSET = object()
 
 
-def _make_mixin(class_name, param_name, doc, accessor=None, default=_UNSET):
+def _make_mixin(class_name, param_name, doc, accessor=None, default=_UNSET, arg_name=None):
     accessor = accessor or param_name
+    arg_name = arg_name or param_name  # keyword the reference's setter takes (set_mode(mode=...), params.py:33)
 
     def __init__(self):
         super(cls, self).__init__()
@@ -40,9 +41,14 @@ def _make_mixin(class_name, param_name, doc, accessor=None, default=_UNSET):
             value = default.copy() if isinstance(default, (list, dict)) else default
             self._setDefault(**{param_name: value})
 
-    def setter(self, value):
+    def _set(self, value):
         self._paramMap[getattr(self, param_name)] = value
         return self
+
+    # the setter's one parameter carries the reference's name, so keyword calls written against Elephas keep working
+    scope = {'_set': _set}
+    exec("def setter(self, %s):\n    return _set(self, %s)\n" % (arg_name, arg_name), scope)
+    setter = scope['setter']
 
     def getter(self):
         return self.getOrDefault(getattr(self, param_name))
@@ -77,7 +83,7 @@ HasCustomObjects = _make_mixin('HasCustomObjects', 'custom_objects',
                                default={})
 HasInferenceBatchSize = _make_mixin('HasInferenceBatchSize', 'inference_batch_size',
                                     "Batch inference could help limit memory consumption in executors",
-                                    default=None)
+                                    default=None, arg_name='batch_size')
 
 __all__ = ['HasKerasModelConfig', 'HasMode', 'HasFrequency', 'HasNumberOfClasses', 'HasCategoricalLabels',
            'HasEpochs', 'HasBatchSize', 'HasVerbosity', 'HasValidationSplit', 'HasNumberOfWorkers',

@@ -23,12 +23,12 @@ def determine_master(port: int = 4000) -> str:
     return "%s:%d" % (host, port)
 
 
-def _receive_all(sock, num_bytes: int) -> bytes:
-    """Read exactly ``num_bytes`` from ``sock``; raises ``ConnectionError`` on EOF."""
+def _receive_all(socket, num_bytes: int) -> bytes:  # noqa: A002 (parameter named as in the reference)
+    """Read exactly ``num_bytes`` from ``socket``; raises ``ConnectionError`` on EOF."""
     chunks = []
     remaining = num_bytes
     while remaining > 0:
-        data = sock.recv(min(remaining, 1 << 20))
+        data = socket.recv(min(remaining, 1 << 20))
         if not data:
             raise ConnectionError("socket closed with %d bytes outstanding" % remaining)
         chunks.append(data)
@@ -36,14 +36,14 @@ def _receive_all(sock, num_bytes: int) -> bytes:
     return b''.join(chunks)
 
 
-def receive(sock, num_bytes: int = HEADER_BYTES):
+def receive(socket, num_bytes: int = HEADER_BYTES):
     """Receive one length-prefixed pickle frame."""
-    length = int(_receive_all(sock, num_bytes).decode())
-    return pickle.loads(_receive_all(sock, length))
+    length = int(_receive_all(socket, num_bytes).decode())
+    return pickle.loads(_receive_all(socket, length))
 
 
-def send(sock, data, num_bytes: int = HEADER_BYTES):
+def send(socket, data, num_bytes: int = HEADER_BYTES):
     """Send ``data`` as one length-prefixed pickle frame."""
     payload = pickle.dumps(data, -1)
-    sock.sendall(str(len(payload)).zfill(num_bytes).encode())
-    sock.sendall(payload)
+    socket.sendall(str(len(payload)).zfill(num_bytes).encode())
+    socket.sendall(payload)

@@ -32,3 +32,22 @@ def test_mutable_defaults_are_not_shared():
     a, b = HasMetrics(), HasMetrics()
     a.get_metrics().append('x')
     assert b.get_metrics() == ['acc']
+
+
+def test_setters_accept_the_reference_keyword_names():
+    """Calls written against Elephas with keywords keep working (``set_mode(mode=...)``, ``elephas/ml/params.py``)."""
+    from elephas_b200.ml import params as P
+
+    class Holder(P.HasMode, P.HasVerbosity, P.HasCategoricalLabels, P.HasInferenceBatchSize, P.HasNumberOfClasses):
+        pass
+
+    h = Holder()
+    assert h.set_mode(mode='hogwild') is h and h.get_mode() == 'hogwild'
+    h.set_verbosity(verbose=2)
+    h.set_categorical_labels(categorical=False)
+    h.set_inference_batch_size(batch_size=64)
+    h.set_nb_classes(nb_classes=3)
+    assert (h.get_verbosity(), h.get_categorical_labels(), h.get_inference_batch_size(), h.get_nb_classes()) == \
+        (2, False, 64, 3)
+    h.set_mode('synchronous')
+    assert h.get_mode() == 'synchronous'

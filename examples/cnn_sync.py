@@ -19,7 +19,10 @@ from elephas_b200.models.layers import (Activation, BatchNormalization, Conv2D, 
 from elephas_b200.parallel import get_runtime
 from elephas_b200.spark import SparkConf, SparkContext
 
+import torch
+
 rt = get_runtime()
+torch.manual_seed(0)  # reproducible initial weights
 rng = np.random.default_rng(0)
 n, side, classes = (2048 if rt.device.type == 'cuda' else 768), 16, 4  # (smaller on a CPU: the eager path is slow)
 labels = rng.integers(0, classes, n)
@@ -38,7 +41,7 @@ if rt.device.type == 'cuda':
 
 sc = SparkContext(conf=SparkConf().setAppName('cnn_sync').setMaster('local[%d]' % max(rt.world_size, 1)))
 spark_model = SparkModel(model, mode='synchronous', frequency='epoch', num_workers=max(rt.world_size, 1))
-spark_model.fit(to_simple_rdd(sc, x, y), epochs=4, batch_size=64, verbose=0, validation_split=0.1)
+spark_model.fit(to_simple_rdd(sc, x, y), epochs=6, batch_size=32, verbose=0, validation_split=0.1)
 loss, acc = spark_model.evaluate(x[:512], y[:512])
 if rt.is_driver:
     print('loss %.4f  acc %.3f  (%s)' % (loss, acc, 'graph-captured bf16 step' if rt.device.type == 'cuda' else 'eager CPU step'))

@@ -117,3 +117,16 @@ def mnist_data():
 @pytest.fixture(scope='session')
 def boston_housing_dataset():
     return make_boston_like()
+
+
+@pytest.fixture(autouse=True)
+def _seeded():
+    """CPU tests start from the same torch / NumPy seeds: weight initialisation and dropout masks are reproducible
+    (tests that want other seeds set them themselves)."""
+    import torch
+    if not torch.cuda.is_available():
+        # CPU runs (the per-round check) are fully reproducible; GPU runs keep fresh seeds, which is what the numerics
+        # tolerances there were exercised with
+        torch.manual_seed(20240607)
+        np.random.seed(20240607)
+    yield

@@ -659,6 +659,9 @@ extern "C" int eb_allreduce_update_noalloc(const void* delta, int64_t n, int32_t
   // The array keeps whatever the previous call left. The epoch word (local[0]) and the pad flags are
   // monotonic on purpose; the two block counters must be zero when the kernel starts.
   EB_CUDA_OK(cudaMemsetAsync(local + 1, 0, 2 * sizeof(uint32_t), s));
+  // ... and so must the watchdog status word (local[8]): with one rank no wait can time out, a non-zero
+  // value could only be left over from whatever ran on this array before
+  EB_CUDA_OK(cudaMemsetAsync(local + 8, 0, sizeof(uint32_t), s));
   CommDev p;
   for (int i = 0; i < kMaxRanks; ++i) { p.delta[i] = nullptr; p.avg[i] = nullptr; p.pad[i] = nullptr; }
   p.delta[0] = delta;

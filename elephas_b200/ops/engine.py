@@ -240,11 +240,16 @@ class MLPEngine:
         self.comm_hook = None     # callable(lo, n): a delta range is ready (synchronous data parallel)
         self._aux_stream = None
         self.input_bf16 = False   # training batches are delivered straight into buf.x16 (already bf16)
-        self.pull_source = None   # device address of a bf16 weight mirror the training forward GEMMs pull from (K2)
+        self.pull_source = None   # per Dense op: device address of the bf16 mirror of its kernel in a parameter server's
+        #                           stripe (usually peer memory) that the training forward GEMM pulls from (K2); None = off
+        self.grad_sink = None     # callable(warmup): consumes the complete flat gradient g32 INSTEAD of the local optimizer
+        #                           (parameter server: optimizer step fused with the push into peer memory)
         self.pre_step = None      # callables run (and captured) at the start / end of every training step
         self.post_step = None
         self.mid_step = None      # ... and between the forward pass and the loss
         self.comm_join = None     # callable(): make the compute stream wait for all communication of the step
+        self.last_graph_kernels = 0  # native kernels in the most recently recorded graph
+        self._hook_generation = 0  # bumped by set_step_hooks(): part of the graph key (never an object address)
         self._in_warmup = False
         if self.trainable:
             self.loss_id, self.metric_ids = spec
@@ -364,9 +369,9 @@ class MLPEngine:
         def weights(op):
             # K2: with a pull source (address of a parameter server's bf16 mirror, usually peer memory) the GEMM reads
             # the weight tiles from there through TMA and side-writes them into the local copy the backward pass uses
-            if pull is None:
+            if pull is None or pull[op.index] is None:
                 return self._w16(op), None
-            return pull + 2 * op.w_seg.offset, self._w16(op)
+            return int(pull[op.index]), self._w16(op)
 
         for op in self.ops[:-1]:
             out = buf.acts[op.index]
@@ -449,8 +454,8 @@ class MLPEngine:
 
     def _backward(self, buf):
         B = buf.B
-        fused = self._fused_sgd()
-        delta_mode = self.delta_target is not None
+        fused = self._fused_sgd() and self.grad_sink is None  # a gradient sink wants the plain gradient in g32
+        delta_mode = self.delta_target is not None and self.grad_sink is None
         lr = float(self.model.optimizer._config['learning_rate']) if fused else 0.0
         # bias gradients (column sums of dZ, bandwidth-bound) run on a side stream next to the GEMMs: the
         # clustered GEMM grid leaves 16 of the 148 SMs idle, and nothing needs the sums before the optimizer
@@ -518,7 +523,13 @@ class MLPEngine:
             self._aux_stream = torch.cuda.Stream(self.device)
         return self._aux_stream
 
+    def _pull_key(self):
+        return tuple(int(a or 0) for a in self.pull_source) if self.pull_source is not None else 0
+
     def _optimizer(self):
+        if self.grad_sink is not None:
+            self.grad_sink(self._in_warmup)
+            return
         if self.delta_target is not None or self._fused_sgd():
             # matrices were handled layer by layer (fused epilogue or per-layer delta): only vectors are left
             lo = self.layout.matrix_end
@@ -543,6 +554,15 @@ class MLPEngine:
         if self.post_step is not None and not self._in_warmup:
             self.post_step()  # e.g. push of the step's delta into a parameter server
 
+    def set_step_hooks(self, pre=None, mid=None, post=None):
+        """Install the callables captured at the start / between forward and loss / at the end of every training step
+        and return the previous triple. Every call starts a new hook generation, which is part of the CUDA-graph key:
+        a graph recorded with one set of hooks is never replayed for another, whatever addresses the callables have."""
+        previous = (self.pre_step, self.mid_step, self.post_step)
+        self.pre_step, self.mid_step, self.post_step = pre, mid, post
+        self._hook_generation += 1
+        return previous
+
     # -------------------------------------------------------------- graph capture
     def _run(self, buf, which, body):
         """Run ``body`` through a CUDA graph recorded on first use. One graph per batch size, kind
@@ -551,15 +571,19 @@ class MLPEngine:
             body()
             return
         is_train = which == 'train'
-        key = (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0,
-               (self.pull_source or 0) if is_train else 0, id(self.post_step) if is_train else 0,
-               bool(self.input_bf16) if is_train else False)
+        key = self._graph_key(which)
         graph = buf.graphs.get(key)
         if graph is None:
             with _CAPTURE_LOCK:
                 graph = self._record(buf, key, body, is_train)
         graph.replay()
         native.count_replay(self._graph_launches.get(id(graph), 0))
+
+    def _graph_key(self, which):
+        is_train = which == 'train'
+        return (which, self.delta_target.data_ptr() if (is_train and self.delta_target is not None) else 0,
+                self._pull_key() if is_train else 0, self._hook_generation if is_train else 0,
+                bool(self.input_bf16) if is_train else False, (self.grad_sink is not None) if is_train else False)
 
     def _record(self, buf, key, body, is_train):
         # warm-up outside capture (module loading, function attributes), then record
@@ -589,7 +613,7 @@ class MLPEngine:
             if gc_was_enabled:
                 gc.enable()
         # kernels recorded into the graph: every replay launches this many native kernels
-        self._graph_launches[id(graph)] = native.launch_count() - launched
+        self._graph_launches[id(graph)] = self.last_graph_kernels = native.launch_count() - launched
         buf.graphs[key] = graph
         if saved is not None:
             self._restore_state(saved)
@@ -645,6 +669,16 @@ class MLPEngine:
             self._run(buf, 'train', lambda: self._train_body(buf))
             self._weights_dirty_in_model = True
             return self.read_stats()[0]
+
+    def prepare_train(self, buf):
+        """Record the training-step graph for ``buf`` now (no step is taken: the recording runs on a snapshot of the
+        engine state that is restored afterwards), so that a timed loop of ``train_step_device`` only replays."""
+        if not self.use_graphs:
+            return
+        key = self._graph_key('train')
+        if key not in buf.graphs:
+            with _CAPTURE_LOCK:
+                self._record(buf, key, lambda: self._train_body(buf), True)
 
     def train_step_device(self, buf):
         """One step on data already staged in ``buf.x32`` / ``buf.y32`` (no host sync)."""
@@ -731,7 +765,3 @@ class MLPEngine:
             self.stats.copy_(saved)
             return vals
 
-
-def try_sync_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
-    from ..parallel import sync_fast
-    return sync_fast.try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds)

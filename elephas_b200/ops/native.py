@@ -85,6 +85,19 @@ class CommArgs(ctypes.Structure):
                 ('algo', c_int32), ('blocks', c_int32)]
 
 
+PS_MAX_RANKS, PS_MAX_SPANS, PS_MAX_CHUNKS, PS_LOCK_WORDS = 8, 48, 64, 8
+
+
+class PsSpan(ctypes.Structure):
+    _fields_ = [('flat_off', c_int64), ('n', c_int64), ('owner_off', c_int64), ('owner', c_int32), ('reserved', c_int32)]
+
+
+class PsStore(ctypes.Structure):
+    _fields_ = [('master', c_void_p * PS_MAX_RANKS), ('mirror', c_void_p * PS_MAX_RANKS), ('ctrl', c_void_p * PS_MAX_RANKS),
+                ('stripe_len', c_int64 * PS_MAX_RANKS), ('chunk_len', c_int64), ('chunks', c_int32),
+                ('world', c_int32), ('rank', c_int32), ('nspans', c_int32), ('spans', PsSpan * PS_MAX_SPANS)]
+
+
 _lib = None
 _lib_lock = threading.Lock()
 
@@ -126,6 +139,9 @@ def load():
         lib.eb_ps_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_ps_pull.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
         lib.eb_ps_push_mirror.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p]
+        lib.eb_ps_striped_pull.argtypes = [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
+        lib.eb_ps_striped_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]
+        lib.eb_ps_striped_optimizer_push.argtypes = [c_void_p, c_void_p, c_int32, c_void_p]
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
@@ -327,6 +343,14 @@ def loss_fwd_bwd(z, y, rows, cols, loss, act, out=None, dz=None, stats=None, met
 def optimizer_step(kind, n, g32, step, w32=None, w16=None, slots=(None, None, None), delta_bf16=None, delta_f32=None,
                    apply=True, advance=True, lr=0.01, decay=0.0, momentum=0.0, rho=0.9, eps=1e-7, beta1=0.9,
                    beta2=0.999, nesterov=False, centered=False, amsgrad=False):
+    a = _optim_args(kind, n, g32, step, w32, w16, slots, delta_bf16, delta_f32, apply, advance, lr, decay, momentum, rho,
+                    eps, beta1, beta2, nesterov, centered, amsgrad)
+    _check(require().eb_optimizer_step(ctypes.byref(a), _stream(g32.device)), 'eb_optimizer_step')
+
+
+def _optim_args(kind, n, g32, step, w32=None, w16=None, slots=(None, None, None), delta_bf16=None, delta_f32=None,
+                apply=True, advance=True, lr=0.01, decay=0.0, momentum=0.0, rho=0.9, eps=1e-7, beta1=0.9,
+                beta2=0.999, nesterov=False, centered=False, amsgrad=False):
     a = OptimArgs()
     a.kind, a.n = int(kind), int(n)
     a.w32, a.g32 = (w32.data_ptr() if w32 is not None else None), g32.data_ptr()
@@ -340,7 +364,7 @@ def optimizer_step(kind, n, g32, step, w32=None, w16=None, slots=(None, None, No
     a.beta1, a.beta2 = float(beta1), float(beta2)
     a.nesterov, a.centered, a.amsgrad = int(bool(nesterov)), int(bool(centered)), int(bool(amsgrad))
     a.step = step.data_ptr()
-    _check(require().eb_optimizer_step(ctypes.byref(a), _stream(g32.device)), 'eb_optimizer_step')
+    return a
 
 
 # ------------------------------------------------------------------ collectives
@@ -431,6 +455,49 @@ def ps_push(master, ctrl, delta=None, before=None, after=None, locked=False, n=N
     finally:
         if locked:
             _check(lib.eb_ps_unlock(cptr, s), 'eb_ps_unlock')
+
+
+# ---------------------------------------------- parameter server, striped over all ranks
+def ps_store_args(master_ptrs, mirror_ptrs, ctrl_ptrs, stripe_len, chunk_len, chunks, rank, spans):
+    """``EbPsStore`` from Python values. ``spans``: iterable of ``(flat_off, n, owner, owner_off)``."""
+    world = len(master_ptrs)
+    spans = list(spans)
+    if world > PS_MAX_RANKS or len(spans) > PS_MAX_SPANS or chunks > PS_MAX_CHUNKS:
+        raise NativeError("striped parameter server: %d ranks / %d spans / %d chunks exceed the kernel limits (%d / %d / %d)"
+                          % (world, len(spans), chunks, PS_MAX_RANKS, PS_MAX_SPANS, PS_MAX_CHUNKS))
+    a = PsStore()
+    for r in range(world):
+        a.master[r], a.mirror[r], a.ctrl[r] = master_ptrs[r], mirror_ptrs[r], ctrl_ptrs[r]
+        a.stripe_len[r] = int(stripe_len[r])
+    a.chunk_len, a.chunks, a.world, a.rank, a.nspans = int(chunk_len), int(chunks), world, int(rank), len(spans)
+    for i, (flat_off, n, owner, owner_off) in enumerate(spans):
+        a.spans[i].flat_off, a.spans[i].n, a.spans[i].owner_off, a.spans[i].owner = int(flat_off), int(n), int(owner_off), int(owner)
+    return a
+
+
+def ps_striped_pull(store, dst_f32=None, f32_range=None, dst_bf16=None, b16_range=None, seqlock=False, device=None):
+    """Flat-indexed pull: ``dst_f32[i] = master[i]`` for ``i`` in ``f32_range``, ``dst_bf16[i] = mirror[i]`` for ``i`` in
+    ``b16_range`` (ranges default to the whole destination)."""
+    ref = dst_f32 if dst_f32 is not None else dst_bf16
+    f_lo, f_hi = f32_range if f32_range is not None else (0, dst_f32.numel() if dst_f32 is not None else 0)
+    b_lo, b_hi = b16_range if b16_range is not None else (0, dst_bf16.numel() if dst_bf16 is not None else 0)
+    _check(require().eb_ps_striped_pull(ctypes.byref(store), _ptr(dst_f32), int(f_lo), int(f_hi), _ptr(dst_bf16), int(b_lo),
+                                        int(b_hi), int(bool(seqlock)), _stream(device if device is not None else ref.device)),
+           'eb_ps_striped_pull')
+
+
+def ps_striped_push(store, delta_f32=None, delta_bf16=None, before=None, after=None, locked=False, device=None):
+    ref = delta_f32 if delta_f32 is not None else (delta_bf16 if delta_bf16 is not None else before)
+    _check(require().eb_ps_striped_push(ctypes.byref(store), _ptr(delta_f32), _ptr(delta_bf16), _ptr(before), _ptr(after),
+                                        int(bool(locked)), _stream(device if device is not None else ref.device)),
+           'eb_ps_striped_push')
+
+
+def ps_striped_optimizer_push(store, kind, n, g32, step, slots=(None, None, None), locked=False, advance=True, **hyper):
+    """Optimizer step fused with the push into the striped store (``master -= step`` as red.add into peer memory)."""
+    a = _optim_args(kind, n, g32, step, slots=slots, apply=False, advance=advance, **hyper)
+    _check(require().eb_ps_striped_optimizer_push(ctypes.byref(store), ctypes.byref(a), int(bool(locked)), _stream(g32.device)),
+           'eb_ps_striped_optimizer_push')
 
 
 # ------------------------------------------------------------------ host staging

@@ -3,7 +3,7 @@
 Reference mechanism replaced: Spark ``collect`` of every worker's delta followed by a sequential
 NumPy average on the driver (``elephas/spark_model.py:220-227``, O(N*P) on one core). Here every
 rank packs its partial sum into one flat buffer and the ranks all-reduce it: on B200s through the
-fused one-shot / two-shot P2P kernels over NVLink peer memory (``csrc/allreduce_kernels.cu``,
+fused one-shot / two-shot P2P kernels over NVLink peer memory (``csrc/comm_kernels.cu``,
 bound in ``elephas_b200/parallel/symm.py``), on CPU ranks through gloo.
 """
 import numpy as np

@@ -270,27 +270,40 @@ class SocketServer(BaseParameterServer):
 
 
 class DeviceServer(BaseParameterServer):
-    """Master weights resident in GPU (peer) memory; ``parameter_server_mode='nvlink'``."""
+    """Master weights resident in GPU (peer) memory, one stripe per rank; ``parameter_server_mode='nvlink'``.
+
+    Under ``torchrun`` this server is *collective*: every rank constructs it, and ``start`` / ``stop`` are called by all
+    ranks together (each contributes the stripe it owns, rank 0's weights become the master). The reference's counterpart
+    lives in the driver process only (``elephas/spark_model.py:75-79,196-197,232-233``)."""
+    collective = True
 
     def __init__(self, model, port: int, mode: str, **kwargs):
         super().__init__(model, port, mode, **kwargs)
         self._store = None
-        # publish a bf16 mirror of the master next to it: workers then read the weights tile by tile from inside
-        # their forward GEMMs (pull fused into the GEMM) instead of copying them first; set by SparkModel for
-        # mode='hogwild', frequency='batch'
-        self.fused_pull = bool(kwargs.get('fused_pull', False))
+        self.fused_pull = bool(kwargs.get('fused_pull', False))  # kept for callers of the first design; unused
 
     def start(self):
         from ..parallel.device_ps import create_store
-        self._store = create_store(self.port, self.weights, self.mode, model=self.master_network,
-                                   mirror=self.fused_pull)
+        from ..parallel.runtime import get_runtime
+        rt = get_runtime()
+        if rt.distributed and rt.device.type != 'cuda':
+            raise RuntimeError("parameter_server_mode='nvlink' keeps the master weights in GPU peer memory; ranks that are "
+                               "separate CPU processes have nothing to map - use 'socket' or 'http' there")
+        self._store = create_store(self.port, self.weights, self.mode, model=self.master_network, rt=rt,
+                                   device=rt.device if rt.distributed else None)
 
     def stop(self):
         from ..parallel.device_ps import destroy_store
         if self._store is not None:
             self.weights = self._store.pull_arrays()
+            status = self._store.watchdog_status()
+            if self._store.rt is not None:
+                self._store.rt.barrier()  # nobody unmaps a stripe another rank may still be reading
             destroy_store(self.port)
             self._store = None
+            if status:
+                raise RuntimeError("device parameter server: a waiter of a chunk lock gave up after 10 s on this rank's "
+                                   "stripe (status %d); the run is not trustworthy" % status)
 
     def get_weights(self):
         if self._store is not None:
@@ -300,9 +313,4 @@ class DeviceServer(BaseParameterServer):
     def set_weights(self, weights):
         super().set_weights(weights)
         if self._store is not None:
-            self._store.layout.pack_arrays(self.weights, out=self._store.flat)
-            self._store.refresh_mirror()
-
-    def export_handle(self):
-        """CUDA IPC handle of the master buffer (None on CPU): lets other ranks attach to the store."""
-        return self._store.export_handle() if self._store is not None else None
+            self._store.load_arrays(self.weights)

@@ -233,33 +233,19 @@ class SparkModel:
 
     # -- asynchronous / hogwild -------------------------------------------------
     def _fit_parameter_server(self, rt, partitions, mine, train_config):
-        # per-batch pulls on GPUs: the store publishes a bf16 mirror and the workers' forward GEMMs read the weights
-        # straight from it (pull fused into the GEMM, K2) - hogwild always, the locked mode when all workers live in this
-        # process (the store's stream then serialises whole pull+step+push graphs) or, with one worker per rank and a
-        # small model, with the ticket lock recorded into the step graph; otherwise it keeps the copy-under-lock pull
-        fused_pull = (self.parameter_server_mode == 'nvlink' and self.frequency == 'batch' and rt.device.type == 'cuda'
-                      and (self.mode == 'hogwild' or not rt.distributed or len(mine) <= 1)
-                      and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
-        if rt.distributed:
-            fused_pull = bool(rt.broadcast_object(fused_pull, src=0))  # owner and proxies must agree on the mirror
-        if hasattr(self.parameter_server, 'fused_pull'):
-            self.parameter_server.fused_pull = fused_pull
-        if rt.is_driver:
+        # The device parameter server ('nvlink') is collective under torchrun: every rank holds one stripe of the master
+        # (parallel/device_ps.py), so every rank starts and stops it; the HTTP / socket servers live on the driver only,
+        # like the reference's (spark_model.py:196-197,232-233).
+        collective = bool(getattr(self.parameter_server, 'collective', False)) and rt.distributed
+        if rt.is_driver or collective:
             self.parameter_server.set_weights(self._master_network.get_weights())
             self.start_server()
         rt.barrier()
-        if self.parameter_server_mode == 'nvlink' and rt.distributed:
-            # ranks other than the owner map the master buffer through CUDA IPC (NVLink peer access)
-            handle = rt.broadcast_object(self.parameter_server.export_handle() if rt.is_driver else None, src=0)
-            if not rt.is_driver:
-                from .parallel.device_ps import attach_remote_store
-                attach_remote_store(self.port, handle, self.mode, self._master_network, rt.device, mirror=fused_pull)
-        if self.parameter_server_mode == 'nvlink':
-            from .parallel.device_ps import get_store
-            get_store(self.port).configure(local_workers=len(mine), distributed=rt.distributed)
         model_json, init, cfg, optimizer, loss, metrics, custom = self._worker_args(train_config)
-        for key in ('input_mode', 'log_batch_loss', 'keep_context'):
-            cfg.pop(key, None)
+        cfg.pop('keep_context', None)
+        if self.parameter_server_mode != 'nvlink':
+            for key in ('input_mode', 'log_batch_loss', 'timed_from'):
+                cfg.pop(key, None)  # options of the device paths only
         if rt.is_driver:
             print('>>> Initialize workers')
         workers = [AsynchronousSparkWorker(model_json, init, self.client, cfg, self.frequency, optimizer, loss,
@@ -290,15 +276,18 @@ class SparkModel:
             t.join()
         rt.barrier()
         new_parameters = None
-        if self.parameter_server_mode == 'nvlink' and rt.distributed and not rt.is_driver:
-            from .parallel.device_ps import destroy_store
-            destroy_store(self.port)
-        rt.barrier()
-        if rt.is_driver:
+        if collective:
+            # every rank reads the final master itself (one-sided pulls from all stripes), then the stripes are released
             new_parameters = self.parameter_server.get_weights()
             self.stop_server()
+        else:
+            if rt.is_driver:
+                new_parameters = self.parameter_server.get_weights()
+                self.stop_server()
+            new_parameters = rt.broadcast_object(new_parameters, src=0)
+        if rt.is_driver:
             print('>>> Async training complete.')
-        new_parameters = rt.broadcast_object(new_parameters, src=0)
+        self._last_async_run = [dict(w.run_info) for w in workers if getattr(w, 'run_info', None)]
         if errors:
             raise errors[0]
         # D10 (extension): per-worker histories are kept for frequency='epoch'
@@ -317,7 +306,7 @@ class SparkModel:
         return divide_by(all_reduce_arrays_sum(rt, local_sum), n_total)
 
     def _fit_synchronous(self, rt, partitions, mine, train_config):
-        from .parallel import sync_engine
+        from .parallel import sync_fast
         n_sub = len(partitions)
         sync_rounds = self.kwargs.get('sync_rounds', 'frequency')
         if sync_rounds not in ('frequency', 'fit'):
@@ -327,7 +316,7 @@ class SparkModel:
         epochs = int(train_config.get('epochs', 1))
 
         # Fast path: native engines + fused delta all-reduce/update, one worker per rank.
-        fast = sync_engine.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
+        fast = sync_fast.try_fit(self, rt, partitions, mine, train_config, sync_rounds)
         if fast is None and rt.device.type == 'cuda':
             # models without a native Dense engine: graph-captured torch step on flat weights, same in-place scheme
             from .parallel import sync_torch

@@ -50,10 +50,7 @@ def _weights_of(parameters):
 
 
 # counters for tests / diagnostics: which device paths actually ran in this process
-STATS = {'fused_pull_steps': 0}
-# largest model (parameters) whose locked per-batch pull across ranks is fused into the forward pass: the lock is then held
-# for the forward instead of for one copy kernel, which only pays while the step is launch-bound
-FUSED_LOCKED_MAX = 4 << 20
+STATS = {'fused_pull_steps': 0, 'device_ps_steps': 0}
 
 class _WorkerBase:
     def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
@@ -181,6 +178,7 @@ class AsynchronousSparkWorker(_WorkerBase):
             self.client = BaseParameterClient.get_client(client)
         self.frequency = frequency
         self.history = {}
+        self.run_info = {}  # device path: device time of the step loop, number of steps, ... (bench.py reads it)
 
     def train(self, data_iterator):
         x_train, y_train = partition_to_arrays(data_iterator)
@@ -188,6 +186,8 @@ class AsynchronousSparkWorker(_WorkerBase):
             return
         if self.frequency not in ('epoch', 'batch'):
             raise ValueError('frequency parameter can be `epoch` or `batch, got {}'.format(self.frequency))
+        # options of the device parameter-server path only; Model.fit must never see them
+        self._device_opts = {k: self.train_config.pop(k, None) for k in ('input_mode', 'log_batch_loss', 'timed_from')}
         model = self._build_model()
         epochs = int(self.train_config['epochs'])
         batch_size = int(self.train_config.get('batch_size') or 32)
@@ -228,15 +228,15 @@ class AsynchronousSparkWorker(_WorkerBase):
 
     def _train_against_device_ps(self, model, eng, x_train, y_train, epochs, batch_size, trainable):
         """B200 path of the pull -> train -> push loop: the replica's weights never leave the device.
-        Pull is a (peer) copy kernel straight into the engine's flat fp32/bf16 buffers, push is
-        ``red.add(master, -(before - after))`` fused with the delta computation (K7)."""
+        Pull is a (peer) copy kernel out of the striped store straight into the engine's flat fp32 / bf16 buffers, push
+        is ``red.add(master, -delta)`` into the owners' stripes over NVLink (K7)."""
         import torch
         from .models import History
         store = self.client._store()
-        before = torch.empty_like(eng.w32)
         history = History()
         cfg = self.train_config
         if self.frequency == 'epoch':
+            before = torch.empty_like(eng.w32)
             split = float(cfg.get('validation_split') or 0.0)
             x, y, x_val, y_val = x_train, y_train, None, None
             if 0.0 < split < 1.0:
@@ -251,91 +251,138 @@ class AsynchronousSparkWorker(_WorkerBase):
                             int(cfg.get('verbose', 0) or 0), initial_epoch=epoch)
                 store.push_delta(before=before, after=eng.w32)
             self.history = history.history
+        elif trainable:
+            self._train_batches_device(eng, store, x_train, y_train, epochs, batch_size)
+        torch.cuda.current_stream(eng.device).synchronize()
+
+    def _train_batches_device(self, eng, store, x_train, y_train, epochs, batch_size):
+        """``frequency='batch'`` against the device parameter server: ONE CUDA-graph replay per batch, no host round trip.
+
+        pull   hogwild: the forward GEMMs read their weight tiles from the owner's bf16 mirror (peer memory over NVLink)
+               through TMA and side-write them into the local copy the backward pass uses (K2); only the vector tail is
+               copied. asynchronous: one seqlock pull kernel (bf16 mirror -> compute copy, fp32 tail) - readers take no
+               lock and retry a chunk that a writer touched meanwhile.
+        train  forward / loss / backward on the native engine; the gradient stays in the flat fp32 buffer
+        push   the optimizer kernel IS the push: the step of every element goes from registers into its owner's master
+               (``red.add``, under the chunk's ticket in asynchronous mode); the delta is never materialised
+
+        Reference loop: ``get_parameters`` / ``set_weights`` / ``train_on_batch`` / ``subtract_params`` /
+        ``update_parameters`` per batch (``elephas/worker.py:116-127``). Options (``train_config``): ``input_mode``
+        'device' (default: the partition is uploaded once) or 'stream' (every batch is copied from pinned host memory),
+        ``log_batch_loss`` (one 64-byte loss read-back per step, one step delayed)."""
+        import os
+        import torch
+        cfg = self.train_config
+        dev = eng.device
+        lay = eng.layout
+        n = x_train.shape[0]
+        stream_inputs = self._device_opts.get('input_mode') == 'stream'
+        log_loss = bool(self._device_opts.get('log_batch_loss'))
+        xh = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1)
+        yh = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1)
+        if stream_inputs:
+            xh = xh if xh.is_pinned() else xh.pin_memory()
+            yh = yh if yh.is_pinned() else yh.pin_memory()
+            copy_stream = torch.cuda.Stream(dev)
+            stage = [(torch.empty(batch_size, xh.shape[1], device=dev), torch.empty(batch_size, yh.shape[1], device=dev),
+                      torch.cuda.Event()) for _ in range(2)]
+            consumed = [None, None]
         else:
-            n = x_train.shape[0]
-            dev = eng.device
-            xd = torch.as_tensor(np.ascontiguousarray(x_train, dtype=np.float32)).reshape(n, -1).to(dev)
-            yd = torch.as_tensor(np.ascontiguousarray(y_train, dtype=np.float32)).reshape(n, -1).to(dev)
-            if store.mirror is not None and trainable and (not store.locked or store.stream_exclusive or
-                                                           (store.ticket_only and eng.layout.numel <= FUSED_LOCKED_MAX)):
-                self._train_fused_pull(eng, store, xd, yd, epochs, batch_size)
-                torch.cuda.current_stream(eng.device).synchronize()
-                return
-            for epoch in range(epochs):
-                if not trainable:
-                    continue
+            xd, yd = xh.to(dev), yh.to(dev)
+        tail = (lay.matrix_end, lay.numel)
+        sources = [store.matrix_source(op.w_seg.offset) for op in eng.ops]
+        fused_pull = (not store.locked and all(a is not None for a in sources)
+                      and os.environ.get('ELEPHAS_B200_FUSED_PULL', '1') != '0')
+        saved_pull, saved_sink, saved_delta = eng.pull_source, eng.grad_sink, eng.delta_target
+        eng.delta_target = None
+        if fused_pull:
+            eng.pull_source = sources
+            pre = (lambda: store.pull_into(eng.w32, None, f32_range=tail)) if tail[1] > tail[0] else None
+        else:
+            eng.pull_source = None
+            pre = lambda: store.pull_into(eng.w32, eng.w16, f32_range=tail, b16_range=(0, lay.matrix_end))  # noqa: E731
+        hyper = eng._opt_kwargs()
+
+        def sink(warmup):
+            if warmup:
+                # the run that loads the kernels before the capture must not move the master: with a zero gradient and
+                # the fresh optimizer slots every worker starts from, the step of every element is zero
+                eng.g32.zero_()
+            store.optimizer_push(eng.opt_kind, eng.g32, eng.step, eng.slots, advance=not warmup, **hyper)
+
+        eng.grad_sink = sink
+        saved_hooks = eng.set_step_hooks(pre=pre)
+        pinned = [torch.zeros(8, dtype=torch.float64).pin_memory() for _ in range(2)]
+        events = [torch.cuda.Event() for _ in range(2)]
+        losses = []
+        cur = torch.cuda.current_stream(dev)
+
+        def prefetch(step, lo):
+            rows = min(batch_size, n - lo)
+            xs, ys, ev = stage[step % 2]
+            if consumed[step % 2] is not None:
+                copy_stream.wait_event(consumed[step % 2])
+            with torch.cuda.stream(copy_stream):
+                xs[:rows].copy_(xh[lo:lo + rows], non_blocking=True)
+                ys[:rows].copy_(yh[lo:lo + rows], non_blocking=True)
+                ev.record(copy_stream)
+
+        t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        steps = 0
+        timed_from = int(self._device_opts.get('timed_from') or 0)  # steps before this one are warm-up (not device-timed)
+        try:
+            eng.stats.zero_()
+            eng.prepare_train(eng._buf(min(batch_size, n)))  # record the step graph now: the loop below only replays
+            if timed_from == 0:
+                t0.record(cur)
+            for _ in range(epochs):
+                if stream_inputs:
+                    prefetch(steps, 0)
                 for lo in range(0, n, batch_size):
                     rows = min(batch_size, n - lo)
                     buf = eng._buf(rows)
-                    store.pull_into(eng.w32, eng.w16)
-                    before.copy_(eng.w32)
-                    buf.x32.copy_(xd[lo:lo + rows])
-                    buf.y32.copy_(yd[lo:lo + rows])
-                    eng.train_step_device(buf)
-                    store.push_delta(before=before, after=eng.w32)
-        torch.cuda.current_stream(eng.device).synchronize()
-
-    @staticmethod
-    def _train_fused_pull(eng, store, xd, yd, epochs, batch_size):
-        """``frequency='batch'`` against a device parameter server with a bf16 mirror: ONE graph replay per batch.
-        (hogwild: always; asynchronous: inside one process - the store's stream serialises whole batches - or, with one
-        worker per rank and a small model, with the ticket lock recorded around the pulling forward and the push.)
-
-        pull   = the forward GEMMs read their weight tiles from the store's mirror (peer memory over NVLink) through
-                 TMA and side-write them into the local copy the backward pass uses (K2); only the bias tail is copied
-        train  = forward / loss / backward on the native engine, the optimizer runs in delta mode
-        push   = ``master -= delta`` with ``red.add`` straight into the store + refresh of the mirror, same graph
-
-        Reference loop: ``get_parameters`` / ``set_weights`` / ``train_on_batch`` / ``update_parameters`` per batch
-        (``elephas/worker.py:116-127``)."""
-        import torch
-        lay = eng.layout
-        tail_lo, tail_n = lay.matrix_end, lay.numel - lay.matrix_end
-        delta16 = torch.zeros(lay.numel, dtype=torch.bfloat16, device=eng.device)
-        n = xd.shape[0]
-        saved = (eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step, eng.mid_step)
-        eng.pull_source = store.mirror.data_ptr()
-        eng.delta_target = delta16
-        if store.ticket_only:
-            # mode='asynchronous' across ranks, small model: the ticket lock is taken inside the graph, once around the
-            # pulling forward pass and once around the push (a rank's holders are always on other GPUs)
-            def pre():
-                store.raw_lock()
-                if tail_n > 0:
-                    store.raw_pull_range(eng.w32, tail_lo, tail_n)
-
-            def post():
-                store.raw_lock()
-                store.raw_push(delta_bf16=delta16)
-                store.raw_unlock()
-
-            eng.pre_step, eng.mid_step, eng.post_step = pre, store.raw_unlock, post
-        else:
-            eng.pre_step = (lambda: store.raw_pull_range(eng.w32, tail_lo, tail_n)) if tail_n > 0 else None
-            eng.post_step = lambda: store.raw_push(delta_bf16=delta16)
-        # mode='asynchronous' inside one process: the store's in-order stream is the lock, and the whole batch (pull,
-        # step, push) runs on it as ONE exclusive operation - the strictest form of the reference's locked updates
-        exclusive = store.stream_exclusive
-
-        def one_batch(lo, rows):
-            buf = eng._buf(rows)
-            buf.x32.copy_(xd[lo:lo + rows])
-            buf.y32.copy_(yd[lo:lo + rows])
-            eng.train_step_device(buf)
-
-        try:
-            store.push_delta(delta_bf16=delta16)  # all-zero delta: loads the push kernel outside of graph capture
-            for _ in range(epochs):
-                for lo in range(0, n, batch_size):
-                    rows = min(batch_size, n - lo)
-                    if exclusive:
-                        store.exclusive(lambda: one_batch(lo, rows))
+                    if stream_inputs:
+                        xs, ys, ev = stage[steps % 2]
+                        cur.wait_event(ev)
+                        buf.x32.copy_(xs[:rows])
+                        buf.y32.copy_(ys[:rows])
+                        done = torch.cuda.Event()
+                        done.record(cur)
+                        consumed[steps % 2] = done
+                        if lo + rows < n:
+                            prefetch(steps + 1, lo + rows)
                     else:
-                        one_batch(lo, rows)
-                    STATS['fused_pull_steps'] += 1
-            torch.cuda.current_stream(eng.device).synchronize()
+                        buf.x32.copy_(xd[lo:lo + rows])
+                        buf.y32.copy_(yd[lo:lo + rows])
+                    eng.train_step_device(buf)
+                    if log_loss:
+                        slot = steps % 2
+                        pinned[slot].copy_(eng.stats, non_blocking=True)
+                        events[slot].record(cur)
+                        if steps > 0:
+                            events[1 - slot].synchronize()
+                            losses.append(float(pinned[1 - slot][0] / max(float(pinned[1 - slot][7]), 1.0)))
+                    steps += 1
+                    if steps == timed_from:
+                        t0.record(cur)
+                    STATS['fused_pull_steps'] += int(fused_pull)
+                    STATS['device_ps_steps'] += 1
+            t1.record(cur)
+            cur.synchronize()
+            if log_loss and steps:
+                slot = (steps - 1) % 2
+                losses.append(float(pinned[slot][0] / max(float(pinned[slot][7]), 1.0)))
         finally:
-            eng.pull_source, eng.delta_target, eng.pre_step, eng.post_step, eng.mid_step = saved
+            eng.pull_source, eng.grad_sink, eng.delta_target = saved_pull, saved_sink, saved_delta
+            eng.set_step_hooks(*saved_hooks)
             eng.invalidate_graphs()  # the recorded steps hold the store's addresses
+        vals, count = eng.read_stats()
+        if count:
+            self.history = dict(zip(eng.model.metrics_names, [[v] for v in vals]))
+            if log_loss:
+                self.history['batch_loss'] = losses
+        self.run_info = {'device_ms': t0.elapsed_time(t1), 'steps': steps, 'timed_steps': steps - timed_from,
+                         'fused_pull': fused_pull, 'graph_kernels': eng.last_graph_kernels,
+                         'h2d_bytes_per_step': batch_size * (xh.shape[1] + yh.shape[1]) * 4 if stream_inputs else 0}
         store.pull_into(eng.w32, eng.w16)  # leave the replica with a complete, current copy
         eng._weights_dirty_in_model = True

@@ -193,11 +193,17 @@ int eb_allreduce_shard_update(const EbCommArgs* args, void* stream);
  * averaged-delta space, about 4 MiB, held by every GPU that loads the library until the process ends).
  * The function itself calls no cudaMalloc / cudaFree and no allocating library routine.
  *
- *   w32[i] -= scale * delta[i]  and, when w16 is given,  w16[i] = bf16(w32[i])      for i < n
+ *   fp32 delta (dtype_bf16 = 0):  w32[i] -= scale * delta[i]
+ *   bf16 delta (dtype_bf16 = 1):  w32[i] -= bf16(scale * delta[i])   (the averaged delta is staged in the
+ *                                 delta's own type, exactly as the multi-rank kernel exchanges it; the rounding
+ *                                 is exact only when scale is a power of two)
+ *   and, when w16 is given,       w16[i] = bf16(w32[i])                                            for i < n
  *
  * delta: n elements, bf16 if dtype_bf16 else fp32. n must be a multiple of 8 and at most
  * EB_NOALLOC_MAX_ELEMS; larger n is rejected with an error (use eb_allreduce_update). Results are those of
- * eb_allreduce_update with world = 1, algo = 2.
+ * eb_allreduce_update with world = 1, algo = 2. With one rank there is no peer to wait for, so the peer
+ * watchdog of the multi-rank kernels cannot fire here; its status word inside the array is cleared by every
+ * call so that nothing stale is ever left in it.
  *
  * The first call on each device looks up the array's device address (cudaGetSymbolAddress, that device
  * must be current); make that first call outside of any stream capture. All calls on a device share the
@@ -221,6 +227,56 @@ int eb_ps_pull(const float* master, float* dst_f32, void* dst_bf16, int64_t n, v
  * delta_bf16 or before/after describes the delta. No counterpart in the reference. */
 int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, const void* delta_bf16,
                       const float* before, const float* after, int64_t n, void* stream);
+
+/* ------------------------------------------------ K7 (striped): the parameter server spread over all GPUs
+ * The master weights (fp32) and their bf16 mirror are cut into STRIPES, one per rank, each resident in its owner's HBM and
+ * peer-mapped by every other rank, so that pushes and pulls of N workers land on N memories, N L2s and N sets of NVLink
+ * ports instead of one. `spans` maps the flat parameter index space onto the stripes: span s covers flat elements
+ * [flat_off, flat_off + n) and lives at elements [owner_off, owner_off + n) of rank `owner`'s stripe (all three multiples
+ * of 64; a Dense kernel is normally one span, so that the pull-fused GEMM, K2, can read it through one tensor map).
+ * Every stripe is divided into `chunks` chunks of `chunk_len` elements, each guarded by its own lock record in the owner's
+ * `ctrl` array (8 words per chunk: [0] sequence word, [1] next ticket, [2] now serving, [3] watchdog status):
+ *   push, locked   (mode='asynchronous'): the block that pushes a chunk takes the chunk's FIFO ticket, makes the sequence
+ *                  word odd, applies master -= delta with red.global.add.f32 into the owner's memory, refreshes the bf16
+ *                  mirror, makes the sequence word even again and passes the ticket on - all inside one kernel, so a
+ *                  lock is only ever held by a running block (elephas/parameter/server.py:117-132,201-210: write lock);
+ *   pull, seqlock  (mode='asynchronous'): readers take NO lock: read the sequence word, copy the chunk, read the word again,
+ *                  retry when it was odd or has changed (after EB_PS_SEQ_RETRIES failed attempts: take the ticket like a
+ *                  writer). Any number of readers proceed at once and never delay a writer - the reference's "several
+ *                  threads can hold this type of lock" for reads (elephas/utils/rwlock.py:24-33, server.py:107-115);
+ *   unlocked       (mode='hogwild'): neither (server.py:109,120): relaxed red.add / plain loads.
+ * The unit of consistency is the chunk: a seqlock pull never observes a half-applied push inside a chunk. */
+#define EB_PS_MAX_RANKS 8
+#define EB_PS_MAX_SPANS 48
+#define EB_PS_MAX_CHUNKS 64
+#define EB_PS_LOCK_WORDS 8
+#define EB_PS_SEQ_RETRIES 8
+typedef struct {
+  int64_t flat_off, n, owner_off;
+  int32_t owner, reserved;
+} EbPsSpan;
+typedef struct {
+  void* master[EB_PS_MAX_RANKS];        /* fp32 stripe of every rank (peer mapped) */
+  void* mirror[EB_PS_MAX_RANKS];        /* bf16 stripe of every rank (peer mapped) */
+  void* ctrl[EB_PS_MAX_RANKS];          /* lock records of every rank's stripe: chunks * EB_PS_LOCK_WORDS uint32, zeroed */
+  int64_t stripe_len[EB_PS_MAX_RANKS];  /* elements owned by each rank */
+  int64_t chunk_len;                    /* elements per chunk (multiple of 64) */
+  int32_t chunks;                       /* chunk locks per stripe (<= EB_PS_MAX_CHUNKS) */
+  int32_t world, rank, nspans;
+  EbPsSpan spans[EB_PS_MAX_SPANS];
+} EbPsStore;
+/* dst_f32[i] = master[i] for flat i in [f32_lo, f32_hi), dst_bf16[i] = mirror[i] for flat i in [b16_lo, b16_hi)
+ * (destinations are indexed by FLAT element; either may be NULL). seqlock != 0: validated reads as described above. */
+int eb_ps_striped_pull(const EbPsStore* store, float* dst_f32, int64_t f32_lo, int64_t f32_hi, void* dst_bf16,
+                       int64_t b16_lo, int64_t b16_hi, int32_t seqlock, void* stream);
+/* master -= delta over the whole flat range; exactly one of delta_f32 / delta_bf16 / (before, after) describes the
+ * delta (flat indexed). The bf16 mirror of every touched element is refreshed. locked != 0: per-chunk ticket + sequence. */
+int eb_ps_striped_push(const EbPsStore* store, const float* delta_f32, const void* delta_bf16, const float* before,
+                       const float* after, int32_t locked, void* stream);
+/* The optimizer step (K10: slots updated from the flat gradient opt->g32, Keras formulas) fused with the push: the step
+ * of every element goes straight from registers into the owner's master as a red.add - the delta is never written to
+ * memory. opt->w32 / w16 / delta_* are ignored; opt->advance advances the iteration counter afterwards. */
+int eb_ps_striped_optimizer_push(const EbPsStore* store, const EbOptimArgs* opt, int32_t locked, void* stream);
 
 /* ------------------------------------------------------------ K8: whole-MLP forward in one persistent kernel
  * z = W_{L-1} act(... act(W_0 x + b_0) ...) + b_{L-1} for a chain of 2-4 Dense layers whose hidden widths are multiples

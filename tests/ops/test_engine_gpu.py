@@ -150,23 +150,43 @@ def test_hogwild_batch_uses_the_pull_fused_gemm(spark_context):
     assert _worker.STATS['fused_pull_steps'] - before_steps == 2 * 2 * 8  # 2 workers x 2 epochs x 512/64 batches
     after = sm.evaluate(xt, yt)
     assert after[0] < before[0] and after[1] > 0.8
-    # the locked mode inside one process: whole pull+step+push graphs, serialised by the store's stream
+    # the locked mode pulls with one seqlock kernel per batch (readers take no lock) instead of through the GEMMs; the
+    # optimizer step is fused with the push in both modes
     model2 = zoo.mnist_mlp()
     model2.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
     sm2 = SparkModel(model2, mode='asynchronous', frequency='batch', parameter_server_mode='nvlink', num_workers=2,
                      port=next(_ports))
-    steps = _worker.STATS['fused_pull_steps']
+    fused, steps = _worker.STATS['fused_pull_steps'], _worker.STATS['device_ps_steps']
     before2 = sm2.evaluate(xt, yt)
     sm2.fit(to_simple_rdd(spark_context, x, y), epochs=2, batch_size=64, verbose=0)
-    assert _worker.STATS['fused_pull_steps'] - steps == 2 * 2 * 8
+    assert _worker.STATS['fused_pull_steps'] == fused and _worker.STATS['device_ps_steps'] - steps == 2 * 2 * 8
     after2 = sm2.evaluate(xt, yt)
     assert after2[0] < before2[0] and after2[1] > 0.8
-    # frequency='epoch' keeps the copy-under-lock pull
+    assert all(info['steps'] == 16 and info['device_ms'] > 0 for info in sm2._last_async_run)
+    # frequency='epoch' pulls whole replicas
     sm3 = SparkModel(model2, mode='asynchronous', frequency='epoch', parameter_server_mode='nvlink', num_workers=2,
                      port=next(_ports))
-    steps = _worker.STATS['fused_pull_steps']
+    steps = _worker.STATS['device_ps_steps']
     sm3.fit(to_simple_rdd(spark_context, x, y), epochs=1, batch_size=64, verbose=0)
-    assert _worker.STATS['fused_pull_steps'] == steps
+    assert _worker.STATS['device_ps_steps'] == steps
+
+
+def test_device_ps_batch_mode_streams_inputs_and_logs_losses(spark_context):
+    """input_mode='stream' (every batch copied from pinned host memory) and log_batch_loss (64-byte read-back per step)
+    on the per-batch parameter-server path - what bench.py's end-to-end number goes through."""
+    x, y, xt, yt = make_mnist_like(1024, 300)
+    model = zoo.mnist_mlp()
+    model.compile(Adam(learning_rate=0.002), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode='asynchronous', frequency='batch', parameter_server_mode='nvlink', num_workers=1,
+                    port=next(_ports))
+    before = sm.evaluate(xt, yt)
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=2, batch_size=64, input_mode='stream', log_batch_loss=True)
+    after = sm.evaluate(xt, yt)
+    assert after[0] < before[0] and after[1] > 0.8
+    info = sm._last_async_run[0]
+    assert info['steps'] == 32 and info['h2d_bytes_per_step'] == 64 * (784 + 10) * 4
+    hist = sm.training_histories[-1]
+    assert len(hist['batch_loss']) == 32 and hist['batch_loss'][-1] < hist['batch_loss'][0]
 
 
 def test_wide_mlp_shape_small_on_gpu(spark_context):
@@ -368,25 +388,124 @@ def test_narrow_head_path_matches_gemm_path(monkeypatch, opt):
     assert np.allclose(weights[0][1], weights[1][1], rtol=2e-2, atol=1e-3)
 
 
-@pytest.mark.parametrize('mode,exclusion', [('asynchronous', 'stream'), ('asynchronous', 'ticket+stream'),
-                                            ('hogwild', 'stream')])
-def test_device_store_concurrent_pushes_sum_exactly(mode, exclusion):
+def _emulated_store(model, world, device='cuda'):
+    """The striped store of ``world`` ranks emulated on ONE GPU: all stripes are local tensors, one EbPsStore per
+    emulated rank (same stripes, different ``rank``). Push / pull kernels never wait for another kernel launch - a lock
+    is taken and released inside one kernel - so launching the ranks' kernels one after another on one GPU is legal."""
+    from elephas_b200.ops import native
+    from elephas_b200.parallel.device_ps import MAX_CHUNKS, StripePlan
+    from elephas_b200.parallel.flat import FlatLayout
+    layout = FlatLayout(model)
+    plan = StripePlan(layout, world)
+    master = [torch.zeros(plan.capacity, device=device) for _ in range(world)]
+    mirror = [torch.zeros(plan.capacity, dtype=torch.bfloat16, device=device) for _ in range(world)]
+    ctrl = [torch.zeros(MAX_CHUNKS * native.PS_LOCK_WORDS, dtype=torch.int32, device=device) for _ in range(world)]
+    args = [native.ps_store_args([t.data_ptr() for t in master], [t.data_ptr() for t in mirror],
+                                 [t.data_ptr() for t in ctrl], plan.stripe_len, plan.chunk_len, plan.chunks, r, plan.spans)
+            for r in range(world)]
+    return layout, plan, master, mirror, ctrl, args
+
+
+@pytest.mark.parametrize('world', [1, 3, 8])
+@pytest.mark.parametrize('locked', [False, True])
+def test_striped_store_push_pull_match_pytorch(world, locked):
+    """Every push source (fp32 delta, bf16 delta, before - after) and the flat-indexed pull against plain PyTorch
+    arithmetic, with the master spread over 1 / 3 / 8 (emulated) stripes."""
+    from elephas_b200.ops import native
+    model = zoo.otto_mlp()
+    layout, plan, master, mirror, ctrl, args = _emulated_store(model, world)
+    n = layout.numel
+    g = torch.Generator(device='cuda').manual_seed(world)
+    flat = torch.randn(n, device='cuda', generator=g)
+    for flat_off, cnt, owner, owner_off in plan.spans:  # scatter the initial master into the stripes
+        master[owner][owner_off:owner_off + cnt] = flat[flat_off:flat_off + cnt]
+        mirror[owner][owner_off:owner_off + cnt] = flat[flat_off:flat_off + cnt].to(torch.bfloat16)
+    oracle = flat.clone()
+    d32 = torch.randn(n, device='cuda', generator=g)
+    native.ps_striped_push(args[0], delta_f32=d32, locked=locked)
+    oracle -= d32
+    d16 = torch.randn(n, device='cuda', generator=g).to(torch.bfloat16)
+    native.ps_striped_push(args[world - 1], delta_bf16=d16, locked=locked)
+    oracle -= d16.float()
+    before, after = torch.randn(n, device='cuda', generator=g), torch.randn(n, device='cuda', generator=g)
+    native.ps_striped_push(args[world // 2], before=before, after=after, locked=locked)
+    oracle -= before - after
+    got32 = torch.full((n,), float('nan'), device='cuda')
+    got16 = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    native.ps_striped_pull(args[0], got32, None, got16, None, seqlock=locked)
+    torch.cuda.synchronize()
+    assert torch.allclose(got32, oracle, atol=1e-5, rtol=0), (got32 - oracle).abs().max()
+    assert torch.equal(got16, got32.to(torch.bfloat16))  # the mirror is bf16 of the master, element for element
+    # range-limited pull: fp32 for the vector tail only, bf16 for the matrices only; everything else untouched
+    lo = layout.matrix_end
+    part32 = torch.full((n,), 7.0, device='cuda')
+    part16 = torch.full((n,), 3.0, dtype=torch.bfloat16, device='cuda')
+    native.ps_striped_pull(args[world - 1], part32, (lo, n), part16, (0, lo), seqlock=locked)
+    torch.cuda.synchronize()
+    assert torch.equal(part32[lo:], got32[lo:]) and bool((part32[:lo] == 7.0).all())
+    assert torch.equal(part16[:lo], got16[:lo]) and bool((part16[lo:] == 3.0).all())
+    assert all(int(c.view(-1, native.PS_LOCK_WORDS)[:, 3].max()) == 0 for c in ctrl)
+    if locked:  # three pushes: every touched chunk's sequence word advanced by 2 per push and is even again
+        for r in range(world):
+            words = ctrl[r].view(-1, native.PS_LOCK_WORDS)
+            used = -(-plan.stripe_len[r] // plan.chunk_len)
+            assert bool((words[:used, 0] == 6).all()) and bool((words[:used, 1] == words[:used, 2]).all())
+
+
+@pytest.mark.parametrize('opt', ['sgd', 'momentum', 'adam', 'rmsprop'])
+def test_optimizer_fused_with_the_push_matches_optimizer_then_push(opt):
+    """eb_ps_striped_optimizer_push == eb_optimizer_step in delta mode followed by a push of that delta - and both equal
+    a PyTorch fp32 evaluation of the Keras update rule."""
+    from elephas_b200.ops import native
+    model = zoo.mnist_mlp()
+    layout, plan, master, mirror, ctrl, args = _emulated_store(model, 4)
+    n = layout.numel
+    g = torch.Generator(device='cuda').manual_seed(3)
+    kind = {'sgd': 'SGD', 'momentum': 'SGD', 'adam': 'Adam', 'rmsprop': 'RMSprop'}[opt]
+    hyper = dict(lr=0.01, momentum=0.9 if opt == 'momentum' else 0.0, rho=0.9, eps=1e-7, beta1=0.9, beta2=0.999)
+    need = {'sgd': 0, 'momentum': 1, 'adam': 2, 'rmsprop': 1}[opt]
+    step = torch.zeros(1, dtype=torch.int64, device='cuda')
+    slots_a = [torch.zeros(n, device='cuda') if i < need else None for i in range(3)]
+    slots_b = [t.clone() if t is not None else None for t in slots_a]
+    w_ref = torch.zeros(n, device='cuda')
+    for it in range(3):
+        grad = torch.randn(n, device='cuda', generator=g)
+        native.ps_striped_optimizer_push(args[it % 4], native.OPT_IDS[kind], n, grad, step, slots=slots_a, locked=True,
+                                         advance=False, **hyper)
+        delta = torch.zeros(n, device='cuda')
+        native.optimizer_step(native.OPT_IDS[kind], n, grad, step, slots=slots_b, delta_f32=delta, apply=False,
+                              advance=True, **hyper)
+        w_ref -= delta
+        if opt == 'sgd' and it == 0:
+            assert torch.allclose(delta, 0.01 * grad, atol=1e-7)  # the PyTorch oracle of the plain rule
+        if opt == 'adam' and it == 0:
+            m, v = 0.1 * grad, 0.001 * grad * grad
+            lr_t = 0.01 * (1 - 0.999) ** 0.5 / (1 - 0.9)
+            assert torch.allclose(delta, lr_t * m / (v.sqrt() + 1e-7), atol=1e-6, rtol=1e-4)
+    got = torch.empty(n, device='cuda')
+    native.ps_striped_pull(args[0], got, None, None, None, seqlock=True)
+    torch.cuda.synchronize()
+    assert torch.allclose(got, w_ref, atol=1e-6, rtol=0), (got - w_ref).abs().max()
+    for a, b in zip(slots_a, slots_b):
+        assert a is None or torch.equal(a, b)
+
+
+@pytest.mark.parametrize('mode', ['asynchronous', 'hogwild'])
+def test_device_store_concurrent_pushes_sum_exactly(mode):
     """Race test (the reference's server loses updates: it reads the weights before taking the write lock,
     elephas/parameter/server.py:204-206): worker threads push integer-valued deltas concurrently, each through its own
-    stream; `red.add` makes every push land exactly once in both modes, and locked pulls never see a torn push."""
+    stream; `red.add` makes every push land exactly once in both modes, and in asynchronous mode a seqlock pull never
+    sees a half-applied push inside a chunk - although readers take no lock at all."""
     import threading
     from elephas_b200.parallel.device_ps import create_store, destroy_store
-    model = Sequential([Dense(64, input_dim=256, activation='relu'), Dense(8)])
+    model = Sequential([Dense(96, input_dim=256, activation='relu'), Dense(8)])
     model.compile(SGD(learning_rate=0.1), 'mse')
-    model.to('cuda')
     port = next(_ports)
-    store = create_store(port, model.get_weights(), mode, model=model, device=torch.device('cuda', 0), mirror=True)
-    if exclusion == 'stream':
-        store.configure(local_workers=4, distributed=False)
+    store = create_store(port, model.get_weights(), mode, model=model, device=torch.device('cuda', 0))
     n = store.layout.numel
-    store.flat.zero_()  # integer-valued master and deltas: every partial sum is exact in fp32
-    store.refresh_mirror()
-    start = store.flat.clone()
+    store.load_flat(torch.zeros(n, device='cuda'))  # integer-valued master and deltas: every partial sum is exact in fp32
+    ranges = store.plan.chunk_ranges_flat()
+    assert len(ranges) >= 3  # several chunks: several independent locks
     threads, pushes, torn = 4, 25, []
 
     def work(tid):
@@ -397,10 +516,11 @@ def test_device_store_concurrent_pushes_sum_exactly(mode, exclusion):
                 store.push_delta(delta)
                 if mode == 'asynchronous':
                     store.pull_into(snap)
-                    d = start - snap
-                    # under the lock a snapshot is a whole number of pushes: every element moved by the same amount
-                    if float((d - d[0]).abs().max()) != 0.0:
-                        torn.append((tid, i))
+                    torch.cuda.current_stream().synchronize()
+                    for lo, hi in ranges:
+                        # a chunk snapshot is a whole number of pushes: all of its elements moved by the same amount
+                        if float((snap[lo:hi] - snap[lo]).abs().max()) != 0.0:
+                            torn.append((tid, i, lo))
             torch.cuda.current_stream().synchronize()
 
     ts = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
@@ -409,11 +529,15 @@ def test_device_store_concurrent_pushes_sum_exactly(mode, exclusion):
     for t in ts:
         t.join()
     torch.cuda.synchronize()
-    expected = start - float(pushes * sum(range(1, threads + 1)))
-    assert torch.equal(store.flat, expected)
-    assert torch.equal(store.mirror, store.flat.to(torch.bfloat16))
+    final = store.pull_flat()
+    assert torch.equal(final, torch.full((n,), -float(pushes * sum(range(1, threads + 1))), device='cuda'))
+    mirror = torch.empty(n, dtype=torch.bfloat16, device='cuda')
+    store.pull_into(None, mirror)
+    torch.cuda.synchronize()
+    if mode == 'asynchronous':  # (hogwild: a racing read-back may leave an older mirror entry, see device_ps.py)
+        assert torch.equal(mirror, final.to(torch.bfloat16))
     assert not torn
-    assert int(store.ctrl[4].item()) == 0  # the lock watchdog never fired
+    assert store.watchdog_status() == 0  # no waiter ever gave up
     destroy_store(port)
 
 

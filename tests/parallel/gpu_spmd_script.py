@@ -172,46 +172,46 @@ sm.fit(to_simple_rdd(sc, x, y), epochs=2, batch_size=64)
 same_on_all_ranks(sm.master_network.get_weights(), tol=1e-6)
 log("generic torch path with custom activation ok: acc %.3f" % sm.evaluate(xt, yt)[1])
 
-# ---- 6. race test across ranks: every rank pushes integer deltas into rank 0's store over NVLink ----------
-from elephas_b200.parallel.device_ps import attach_remote_store, create_store, destroy_store  # noqa: E402
+# ---- 6. race test across ranks: every rank pushes integer deltas into ALL stripes of the striped store over NVLink ---
+from elephas_b200.parallel.device_ps import create_store, destroy_store  # noqa: E402
 
-stress_model = Sequential([Dense(64, input_dim=256, activation='relu'), Dense(8)])
+stress_model = Sequential([Dense(512, input_dim=512, activation='relu'), Dense(512, activation='relu'), Dense(8)])
 stress_model.compile(SGD(lr=0.1), 'mse')
-stress_model.to(rt.device)
 for mode in ('asynchronous', 'hogwild'):
     sport = port + 50 + (0 if mode == 'asynchronous' else 1)
-    if R == 0:
-        store = create_store(sport, stress_model.get_weights(), mode, model=stress_model, device=rt.device, mirror=True)
-        handle = store.export_handle()
-        store.flat.zero_()  # integer-valued master and deltas: every partial sum is exact in fp32
-        store.refresh_mirror()
-        torch.cuda.synchronize()
-        start = store.flat.clone()
-    else:
-        handle = None
-    handle = rt.broadcast_object(handle, src=0)
-    if R != 0:
-        store = attach_remote_store(sport, handle, mode, stress_model, rt.device, mirror=True)
-    store.configure(local_workers=1, distributed=True)
+    store = create_store(sport, stress_model.get_weights(), mode, model=stress_model, device=rt.device, rt=rt)  # collective
     n = store.layout.numel
+    store.load_flat(torch.zeros(n, device=rt.device))  # integer-valued master and deltas: every partial sum is exact
+    owners = {owner for _, _, owner, _ in store.plan.spans}
+    assert len(owners) == min(W, 4), owners  # 3 kernels + tail spread over the ranks
+    ranges = store.plan.chunk_ranges_flat()
     delta = torch.full((n,), float(R + 1), device=rt.device)
     snap = torch.empty(n, device=rt.device)
+    torn = 0
     rt.barrier()
     for i in range(40):
         store.push_delta(delta)
         if mode == 'asynchronous':
-            store.pull_into(snap)  # locked pulls interleave with the other ranks' locked pushes
+            store.pull_into(snap)  # seqlock pulls run while the other ranks' locked pushes land
+            torch.cuda.synchronize()
+            for lo, hi in ranges:
+                torn += int(float((snap[lo:hi] - snap[lo]).abs().max()) != 0.0)
     torch.cuda.synchronize()
     rt.barrier()
-    if R == 0:
-        expected = start - float(40 * W * (W + 1) // 2)
-        assert torch.equal(store.flat, expected), (store.flat - expected).abs().max()
-        assert torch.equal(store.mirror, store.flat.to(torch.bfloat16))
-        assert int(store.ctrl[4].item()) == 0
+    final = store.pull_flat()
+    expected = torch.full((n,), -float(40 * W * (W + 1) // 2), device=rt.device)
+    assert torch.equal(final, expected), (final - expected).abs().max()
+    assert torn == 0, "%d torn chunk snapshots" % torn
+    if mode == 'asynchronous':
+        mirror = torch.empty(n, dtype=torch.bfloat16, device=rt.device)
+        store.pull_into(None, mirror)
+        torch.cuda.synchronize()
+        assert torch.equal(mirror, final.to(torch.bfloat16))
+    assert store.watchdog_status() == 0
     rt.barrier()
     destroy_store(sport)
-    rt.barrier()
-    log("parameter-server race test (%s): %d ranks x 40 pushes land exactly once" % (mode, W))
+    log("parameter-server race test (%s): %d ranks x 40 pushes into %d stripes land exactly once, no torn chunk"
+        % (mode, W, len(owners)))
 
 rt.barrier()
 log("ALL OK (world=%d)" % W)

@@ -86,9 +86,8 @@ def test_http_home_route():
         server.stop()
 
 
-def test_device_store_exclusion_policy_on_cpu():
-    """``configure`` picks how mode='asynchronous' excludes writers; on CPU tensors the host RWLock does the work and
-    the GPU-only shortcuts stay off."""
+def test_device_store_on_cpu_keeps_the_list_of_arrays_contract():
+    """On CPU tensors the host RWLock does the exclusion; push / pull keep the reference's list-of-arrays contract."""
     import numpy as np
     from elephas_b200.models import Dense, Sequential
     from elephas_b200.parallel.device_ps import create_store, destroy_store
@@ -97,20 +96,50 @@ def test_device_store_exclusion_policy_on_cpu():
     weights = model.get_weights()
     store = create_store(45991, weights, 'asynchronous', model=model, device=torch.device('cpu'))
     try:
-        assert store._exclusion == 'ticket+stream'
-        store.configure(local_workers=3, distributed=False)
-        assert store._exclusion == 'stream' and not store.stream_exclusive and not store.ticket_only  # CPU store
-        store.configure(local_workers=1, distributed=True)
-        assert store._exclusion == 'ticket'
-        store.configure(local_workers=2, distributed=True)
-        assert store._exclusion == 'ticket+stream'
+        assert store.locked and not store.on_device
+        store.configure(local_workers=3, distributed=False)  # accepted for callers of the first design: nothing to choose
         delta = [np.ones_like(w) for w in weights]
         store.push_arrays(delta)
         for got, w in zip(store.pull_arrays(), weights):
             assert np.allclose(got, w - 1.0)
-        assert store.mirror is None and store.pushes == 1
+        assert store.pushes == 1 and store.matrix_source(0) is None and store.watchdog_status() == 0
     finally:
         destroy_store(45991)
+
+
+def test_stripe_plan_covers_the_flat_buffer_exactly_once():
+    """Ownership plan of the striped store: whole Dense kernels per owner, the vector tail split evenly, every flat
+    element in exactly one span, stripe-local ranges disjoint, chunk ranges inside one chunk each."""
+    import numpy as np
+    from elephas_b200.models import Dense, Sequential, zoo
+    from elephas_b200.parallel.device_ps import MAX_CHUNKS, MIN_CHUNK, StripePlan
+    from elephas_b200.parallel.flat import FlatLayout
+    for model in (zoo.mnist_mlp(), zoo.otto_mlp(), Sequential([Dense(4, input_dim=6), Dense(2)]),
+                  zoo.wide_mlp(input_dim=512, hidden=512, depth=8, out_dim=1)):
+        layout = FlatLayout(model)
+        for world in (1, 2, 3, 8):
+            plan = StripePlan(layout, world)
+            seen = np.zeros(layout.numel, dtype=np.int32)
+            used = [np.zeros(plan.capacity, dtype=np.int32) for _ in range(world)]
+            for flat_off, n, owner, owner_off in plan.spans:
+                assert n > 0 and n % 64 == 0 and flat_off % 64 == 0 and owner_off % 64 == 0 and 0 <= owner < world
+                seen[flat_off:flat_off + n] += 1
+                used[owner][owner_off:owner_off + n] += 1
+            assert (seen == 1).all()
+            for r in range(world):
+                assert used[r].max() <= 1 and used[r].sum() == plan.stripe_len[r]
+            assert sum(plan.stripe_len) == layout.numel
+            assert plan.chunk_len % 64 == 0 and plan.chunk_len >= MIN_CHUNK and 1 <= plan.chunks <= MAX_CHUNKS
+            assert plan.chunks * plan.chunk_len >= max(plan.stripe_len)
+            # every Dense kernel is one span with a home; with several ranks the big model's layers spread out
+            mats = [s for s in layout.segments if s._is_matrix]
+            assert all(plan.matrix_home(s.offset) is not None for s in mats)
+            if world == 8 and len(mats) >= 8:
+                assert len({plan.matrix_home(s.offset)[0] for s in mats}) == 8
+            covered = np.zeros(layout.numel, dtype=np.int32)
+            for lo, hi in plan.chunk_ranges_flat():
+                covered[lo:hi] += 1
+            assert (covered == 1).all()
 
 
 def test_reference_method_names_of_the_servers_work_as_blocking_services():

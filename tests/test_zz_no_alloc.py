@@ -76,6 +76,35 @@ def test_matches_regular_entry_point_on_two_calls_in_a_row(lib, dtype):
     assert torch.equal(h_new, w_new.to(torch.bfloat16))
 
 
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+def test_matches_plain_pytorch_arithmetic_with_a_scale_that_is_not_a_power_of_two(lib, dtype):
+    """Independent oracle: the documented formula evaluated with PyTorch in fp32, not another entry point of this
+    library (a mistake shared by both entry points would pass the comparison above). scale = 1/3 is not exact in
+    bf16, so this also pins down WHERE the bf16 path rounds: the averaged delta is rounded to bf16 before it is
+    subtracted."""
+    torch.manual_seed(5)
+    n, scale = 200000 // 8 * 8, 1.0 / 3.0
+    w = torch.randn(n, device='cuda')
+    w_oracle = w.clone()
+    h = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    scale32 = torch.tensor(scale, dtype=torch.float32, device='cuda')
+    for call in range(2):
+        delta = torch.randn(n, device='cuda').to(dtype)
+        step = delta.float() * scale32
+        if dtype == torch.bfloat16:
+            step = step.to(torch.bfloat16).float()
+        w_oracle = w_oracle - step
+        rc = lib.eb_allreduce_update_noalloc(delta.data_ptr(), n, int(dtype == torch.bfloat16), scale,
+                                             w.data_ptr(), h.data_ptr(), stream)
+        assert rc == 0, lib.eb_last_error()
+        torch.cuda.synchronize()
+        # (a bf16 delta rounded in the wrong place would be off by up to 2^-9 * |delta|, thousands of times this bound)
+        assert torch.allclose(w, w_oracle, atol=1e-6, rtol=0), \
+            "call %d: max |diff| %g" % (call, (w - w_oracle).abs().max().item())
+        assert torch.equal(h, w.to(torch.bfloat16))
+
+
 def test_rejects_payloads_beyond_the_built_in_scratch(lib):
     n = MAX_ELEMS + 8
     delta = torch.zeros(n, device='cuda')

@@ -237,11 +237,12 @@ def run_sync(args, rt):
     DISTINCT, E2E_MAX = 16, 64
     xk, yk = synthetic(min(K, DISTINCT) * B, in_dim, out_dim, 2000 + rt.rank, classification)
     x_eval, y_eval = synthetic(B, in_dim, out_dim, 3000, classification)  # the same held-out batch on every rank / arm
+    model.to(rt.device)
+    loss_before = float(model.evaluate(x_eval, y_eval)[0])  # before any training step, like the torch arms
     # warm-up fit: builds the engine, symmetric memory, CUDA graphs (W untimed steps)
     spark_model.fit(to_sharded_rdd(sc, xw, yw), epochs=1, batch_size=B, shuffle=False, input_mode='device',
                     keep_context=True)
     ctx = spark_model._sync_context
-    loss_before = float(model.evaluate(x_eval, y_eval)[0])
     launches_before = native.launch_count()
     sampler = ClockSampler(rt.local_rank)
     # the sampler covers exactly the timed steps (not the upload of the data set that precedes them)
@@ -456,7 +457,9 @@ def run_torch(args, rt):
         for p_ in net.parameters():
             dist.broadcast(p_.data, src=0)
     loss_fn = nn.CrossEntropyLoss() if classification else nn.MSELoss()
-    DISTINCT = 16
+    # the same data policy as the ours arm: 16 distinct 67 MB batches for the wide MLP, a fresh batch at every step
+    # for the small models (2000 steps over 16 batches would just memorise them)
+    DISTINCT = 16 if args.config == 'wide_mlp' else K
     xw, yw = synthetic(W * B, in_dim, out_dim, 1000 + rt.rank, classification)
     xk, yk = synthetic(min(K, DISTINCT) * B, in_dim, out_dim, 2000 + rt.rank, classification)
     x_eval, y_eval = synthetic(B if args.config == 'wide_mlp' else 4096, in_dim, out_dim, 3000, classification)

@@ -217,6 +217,10 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
     g.beta = float(beta)
     g.bf16_from_f32 = int(bool(bf16_from_f32))
     g.block_n, g.cta_group = int(block_n), int(cta_group)
+    if isinstance(B, int):
+        # a raw address may be another GPU's memory: single-CTA, non-multicast TMA loads only (the library checks the
+        # pointer as well; TMA multicast loads here read only this GPU's memory)
+        g.cta_group, g.multicast = 1, 1
     _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
 
 

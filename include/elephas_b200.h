@@ -82,6 +82,10 @@ typedef struct EbGemmArgs {
   int32_t block_n;        /* 0 = auto, else 16/32/64/128/256                     */
   int32_t cta_group;      /* 0 = auto, else 1 or 2 (CTA pair, UMMA M=256)        */
   int32_t multicast;      /* 0 = auto, 1 = off, 2 = B tile multicast across two CTA pairs (cluster of 4) */
+                          /* Operands in ANOTHER GPU's memory (peer / IPC mappings, e.g. B of the pull-fused GEMM) are
+                           * always loaded by single CTAs without multicast (cta_group = multicast = 1 is forced): TMA
+                           * multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
+                           * another GPU's memory hung the GPU. Pass cta_group = 1, multicast = 1 for such operands. */
   int32_t no_tail_split;  /* 1 disables the half-width scheduling of a sparse last wave */
   void* b_copy;           /* K2 (pull fused into the GEMM): when set, B may live in peer memory (a parameter server or
                              another rank's weights, read tile by tile through TMA over NVLink) and every B tile that

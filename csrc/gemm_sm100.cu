@@ -544,19 +544,6 @@ static int launch_gemm(const EbGemmArgs& a, GemmDev p, cudaStream_t stream) {
   return 0;
 }
 
-// Is `ptr` ordinary device memory of the CURRENT device? (false for peer-mapped, IPC-imported, managed, host and
-// unregistered pointers, and when the runtime cannot tell.)
-static bool on_this_device(const void* ptr) {
-  int dev = -1;
-  if (cudaGetDevice(&dev) != cudaSuccess) return false;
-  cudaPointerAttributes attr;
-  if (cudaPointerGetAttributes(&attr, ptr) != cudaSuccess) {
-    cudaGetLastError();
-    return false;
-  }
-  return attr.type == cudaMemoryTypeDevice && attr.device == dev;
-}
-
 static void pick_config(const EbGemmArgs& a, int& bn, int& cg, int& mc) {
   bn = a.block_n;
   cg = a.cta_group;
@@ -629,12 +616,15 @@ extern "C" int eb_gemm_bf16(const EbGemmArgs* args, void* stream_) {
   int bn, cg, mc;
   pick_config(a, bn, cg, mc);
   // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
-  // hung the GPU: an operand that lives on (or cannot be shown to live on) this device takes the single-CTA,
-  // non-multicast loads, whatever the caller asked for.
-  if (!on_this_device(a.A) || !on_this_device(a.B)) {
+  // hung the GPU: CTA pairs and the B multicast are only ever used when the caller has declared both operands to be
+  // memory of this GPU; everything else (peer / IPC mappings, undeclared callers, the pull-fused GEMM) gets one plain
+  // TMA load per CTA.
+  if (!a.operands_local || a.b_copy) {
+    if (a.cta_group == 2 || a.multicast == 2)
+      return fail("eb_gemm_bf16: cta_group 2 / multicast 2 need operands_local = 1 (and no b_copy): TMA multicast loads "
+                  "read only this GPU's memory");
     cg = 1;
     mc = 1;
-    if (bn == 256 && a.block_n == 0) bn = 128;
   }
   if (a.b_copy) {
     // the pull GEMM runs on single CTAs: every B tile lands whole in one CTA's shared memory and is stored from there

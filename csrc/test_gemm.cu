@@ -98,6 +98,7 @@ int main(int argc, char** argv) {
   g.out_bf16 = dO; g.ldo = ldo;
   g.block_n = bn; g.cta_group = cg;
   g.no_tail_split = getenv("EB_NO_TAIL_SPLIT") ? 1 : 0;
+  g.operands_local = 1;  // A and B are cudaMalloc'ed on the one device this program uses
   g.multicast = getenv("EB_MC") ? atoi(getenv("EB_MC")) : 0;
 
   if (!strcmp(mode, "bench")) {

@@ -41,7 +41,7 @@ class GemmArgs(ctypes.Structure):
                 ('out_bf16', c_void_p), ('ldo', c_int32),
                 ('out_f32', c_void_p), ('ldo32', c_int32), ('beta', c_float), ('bf16_from_f32', c_int32),
                 ('block_n', c_int32), ('cta_group', c_int32), ('multicast', c_int32), ('no_tail_split', c_int32),
-                ('b_copy', c_void_p)]
+                ('b_copy', c_void_p), ('operands_local', c_int32)]
 
 
 class HeadArgs(ctypes.Structure):
@@ -217,10 +217,10 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
     g.beta = float(beta)
     g.bf16_from_f32 = int(bool(bf16_from_f32))
     g.block_n, g.cta_group = int(block_n), int(cta_group)
-    if isinstance(B, int):
-        # a raw address may be another GPU's memory: single-CTA, non-multicast TMA loads only (the library checks the
-        # pointer as well; TMA multicast loads here read only this GPU's memory)
-        g.cta_group, g.multicast = 1, 1
+    # torch tensors on the launching device are this GPU's memory; a raw address (a parameter server's stripe, usually peer
+    # memory) is not declared local, which keeps the kernel on single-CTA, non-multicast TMA loads (TMA multicast loads
+    # here read only this GPU's memory)
+    g.operands_local = int(not isinstance(B, int) and b_copy is None and A.device == B.device)
     _check(require().eb_gemm_bf16(ctypes.byref(g), _stream(A.device)), 'eb_gemm_bf16')
 
 

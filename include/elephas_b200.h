@@ -82,16 +82,18 @@ typedef struct EbGemmArgs {
   int32_t block_n;        /* 0 = auto, else 16/32/64/128/256                     */
   int32_t cta_group;      /* 0 = auto, else 1 or 2 (CTA pair, UMMA M=256)        */
   int32_t multicast;      /* 0 = auto, 1 = off, 2 = B tile multicast across two CTA pairs (cluster of 4) */
-                          /* Operands in ANOTHER GPU's memory (peer / IPC mappings, e.g. B of the pull-fused GEMM) are
-                           * always loaded by single CTAs without multicast (cta_group = multicast = 1 is forced): TMA
-                           * multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from
-                           * another GPU's memory hung the GPU. Pass cta_group = 1, multicast = 1 for such operands. */
   int32_t no_tail_split;  /* 1 disables the half-width scheduling of a sparse last wave */
   void* b_copy;           /* K2 (pull fused into the GEMM): when set, B may live in peer memory (a parameter server or
                              another rank's weights, read tile by tile through TMA over NVLink) and every B tile that
                              lands in shared memory is also written to this local bf16 buffer (same [N][ldb] layout,
                              K-major B only). The GEMM is the pull. No counterpart in the reference
                              (client.get_parameters + set_weights + first layer forward, elephas/worker.py:104-119). */
+  int32_t operands_local; /* 1: the caller states that A and B are memory of the GPU this kernel runs on; only then may
+                             CTA pairs (cta_group 2) and the B-tile multicast be used, by choice or by the automatic
+                             pick. 0 (the default of a zeroed struct): operands may be peer / IPC / multi-GPU mappings,
+                             so every tile is loaded by a single CTA with a plain TMA load - TMA multicast loads here
+                             read only this GPU's memory, since on B200 a TMA multicast load from another GPU's memory
+                             hung the GPU. Asking for cta_group 2 or multicast 2 without it is an error; b_copy implies 0. */
 } EbGemmArgs;
 
 int eb_gemm_bf16(const EbGemmArgs* args, void* stream);

@@ -37,13 +37,18 @@ def _optimizer_weight_entries(model):
     params = model.trainable_weights
     layer_of = {}
     for layer in model.layers:
-        for n, w, _ in layer._weights:
-            layer_of[id(w)] = '%s/%s' % (layer.name, n)
+        for widx, (n, w, _) in enumerate(layer._weights):
+            layer_of[id(w)] = ('%s/%s' % (layer.name, n), layer, widx)
     for (idx, slot), tensor in sorted(opt._slots.items(), key=lambda kv: (kv[0][0], kv[0][1])):
         if idx < len(params):
-            base = layer_of.get(id(params[idx]), 'param_%d' % idx)
+            base, layer, widx = layer_of.get(id(params[idx]), ('param_%d' % idx, None, 0))
             names.append('%s/%s/%s:0' % (opt._class_name, base, slot))
-            values.append(tensor.detach().cpu().numpy())
+            value = tensor.detach()
+            if layer is not None and tuple(value.shape) == tuple(params[idx].shape):
+                # a slot has the shape of its weight: stored in the Keras layout, exactly like the weight itself
+                # (Dense kernels (in, out), Conv2D kernels HWIO), so the file means the same thing to Keras
+                value = layer.to_keras_layout(widx, value)
+            values.append(np.ascontiguousarray(value.cpu().numpy()))
     return names, values
 
 
@@ -142,10 +147,10 @@ def _restore_optimizer(model, group):
     params = model.trainable_weights
     index_of = {}
     for layer in model.layers:
-        for n, w, _ in layer._weights:
+        for widx, (n, w, _) in enumerate(layer._weights):
             for i, p in enumerate(params):
                 if p is w:
-                    index_of['%s/%s' % (layer.name, n)] = i
+                    index_of['%s/%s' % (layer.name, n)] = (i, layer, widx)
     for name in _names(group.attrs.get('weight_names')):
         value = np.asarray(group[name].data)
         parts = name.rsplit(':', 1)[0].split('/')
@@ -155,5 +160,9 @@ def _restore_optimizer(model, group):
         slot = parts[-1]
         key = '/'.join(parts[1:-1])
         if key in index_of:
-            i = index_of[key]
-            opt._slots[(i, slot)] = torch.from_numpy(np.array(value, dtype=np.float32)).to(params[i].device)
+            i, layer, widx = index_of[key]
+            value = np.array(value, dtype=np.float32)
+            keras_shape = tuple(layer.to_keras_layout(widx, params[i].detach()).shape)
+            if value.shape == keras_shape:
+                value = np.ascontiguousarray(layer.from_keras_layout(widx, value))  # file: Keras layout, like the weights
+            opt._slots[(i, slot)] = torch.from_numpy(value).to(params[i].device)

@@ -3,7 +3,7 @@
 Reference: ``elephas/parameter/client.py:13-91``. ``HttpClient`` (GET ``/parameters``, POST
 ``/update``, pickle bodies, ``Content-Type: application/elephas``) and ``SocketClient`` (opcode
 ``b'g'`` / ``b'u'`` + length-prefixed pickle frames) are wire-compatible with the reference's
-servers. ``DeviceClient`` is the B200 addition (``parameter_server_mode='nvlink'``): pull and push
+servers (``SocketClient(ack=False)``; the default adds an acknowledged update opcode ``b'U'``). ``DeviceClient`` is the B200 addition (``parameter_server_mode='nvlink'``): pull and push
 are kernels that read and update master weights resident in (peer) HBM - no host round trip.
 """
 import abc
@@ -68,8 +68,13 @@ class SocketClient(BaseParameterClient):
     """Opens one TCP connection per request, like the reference (``client.py:78,86``)."""
     client_type = 'socket'
 
-    def __init__(self, port: int = 4000):
+    def __init__(self, port: int = 4000, ack: bool = True):
+        """``ack=True`` (default): updates use opcode ``U`` and wait for this package's server to confirm that the delta
+        has been applied, so a pull that follows a push always sees it. ``ack=False``: the reference's un-acknowledged
+        ``u`` frame - use it against a reference ``SocketServer`` (``elephas/parameter/server.py:220-226``), which
+        never replies."""
         self.port = port
+        self.ack = ack
 
     def _connect(self):
         host = determine_master(port=self.port).split(':')[0]
@@ -85,15 +90,10 @@ class SocketClient(BaseParameterClient):
 
     def update_parameters(self, delta: list):
         with self._connect() as sock:
-            sock.sendall(b'u')
+            sock.sendall(b'U' if self.ack else b'u')
             send(sock, {'delta': _to_numpy_list(delta)})
-            # wait for the server's one-byte acknowledgement so a push is applied before the next pull
-            # (a reference SocketServer sends no acknowledgement: give up after a short wait)
-            sock.settimeout(2.0)
-            try:
-                sock.recv(1)
-            except OSError:
-                pass
+            if self.ack and sock.recv(1) != b'k':
+                raise ConnectionError("socket parameter server closed the connection before acknowledging an update")
 
 
 def _to_numpy_list(arrays):

@@ -228,21 +228,28 @@ class SocketServer(BaseParameterServer):
         """Reference name of :meth:`stop` (``elephas/parameter/server.py:184``)."""
         self.stop()
 
-    def update_parameters(self, conn):
+    def update_parameters(self, conn, ack=False):
         data = receive(conn)
         self.apply_delta(data['delta'])
-        try:
-            conn.sendall(b'k')
-        except OSError:
-            pass
+        if ack:  # opcode b'U' only: the reference's b'u' frame has no reply (elephas/parameter/server.py:201-210)
+            try:
+                conn.sendall(b'k')
+            except OSError:
+                pass
 
     def get_parameters(self, conn):
         send(conn, self.get_weights())
 
+    OPCODE_TIMEOUT, PAYLOAD_TIMEOUT = 5.0, 120.0
+
     def action_listener(self, conn):
+        """One connection: opcode ``g`` (send the weights), ``u`` (apply a delta, no reply: the reference's frame) or
+        ``U`` (apply a delta, then acknowledge with one byte). The short timeout only paces the wait for the next
+        opcode so that ``stop`` is noticed; a payload may take as long as it takes, and a connection that breaks in the
+        middle of one is closed without touching the weights."""
         with conn:
-            conn.settimeout(5.0)
             while self.runs:
+                conn.settimeout(self.OPCODE_TIMEOUT)
                 try:
                     op = conn.recv(1)
                 except socket.timeout:
@@ -251,10 +258,14 @@ class SocketServer(BaseParameterServer):
                     return
                 if not op:
                     return  # peer closed the connection
-                if op == b'u':
-                    self.update_parameters(conn)
-                elif op == b'g':
-                    self.get_parameters(conn)
+                conn.settimeout(self.PAYLOAD_TIMEOUT)
+                try:
+                    if op in (b'u', b'U'):
+                        self.update_parameters(conn, ack=op == b'U')
+                    elif op == b'g':
+                        self.get_parameters(conn)
+                except (OSError, EOFError, ValueError, KeyError, pickle.UnpicklingError):
+                    return  # half a frame: drop the connection, the master weights are untouched
 
     def run(self):
         while self.runs:

@@ -1,4 +1,9 @@
-import random
+"""A user-defined activation has to reach every worker replica (and the parameter server's copy of the model) through
+``custom_objects`` and actually be the function that runs there. The reference only checks that predict / evaluate
+return something (tests/integration/test_custom_models.py:37-38); here the result is compared with a hand computation
+that uses the custom function, and the model must NOT be taken over by the native Dense engine, which only knows the
+built-in activations."""
+from itertools import count
 
 import numpy as np
 import pytest
@@ -8,24 +13,53 @@ from elephas.spark_model import SparkModel
 from elephas.utils import to_simple_rdd
 from elephas_b200.models import SGD, Dense, Sequential
 
+_ports = count(4810)
+CALLS = {'n': 0}
 
-@pytest.mark.parametrize('mode', ['synchronous', 'asynchronous', 'hogwild'])
-def test_training_custom_activation(mode, spark_context):
-    def custom_activation(x):
-        return torch.sigmoid(x) + 1
 
+def shifted_sigmoid(x):
+    CALLS['n'] += 1
+    return torch.sigmoid(x) + 1
+
+
+def _by_hand(weights, x):
+    """The two-layer network evaluated with NumPy and the custom activation written out."""
+    k1, b1, k2, b2 = [np.asarray(w, dtype=np.float64) for w in weights]
+    hidden = 1.0 / (1.0 + np.exp(-(x.reshape(-1, 1) @ k1 + b1))) + 1.0
+    return 1.0 / (1.0 + np.exp(-(hidden @ k2 + b2)))
+
+
+@pytest.mark.parametrize('mode,workers', [('synchronous', 2), ('asynchronous', 2), ('hogwild', 3)])
+def test_custom_activation_trains_and_predicts_on_every_worker(mode, workers, spark_context):
+    rng = np.random.default_rng(3)
     model = Sequential()
-    model.add(Dense(1, input_dim=1, activation=custom_activation))
+    model.add(Dense(4, input_dim=1, activation=shifted_sigmoid))
     model.add(Dense(1, activation='sigmoid'))
     model.compile(SGD(learning_rate=0.1), 'binary_crossentropy', ['acc'])
+    assert model._native_engine() is None  # a custom activation keeps the model on the generic (torch) path
 
-    x_train, y_train = np.random.rand(100), np.zeros(100)
-    x_test, y_test = np.random.rand(10), np.zeros(10)
-    y_train[:50] = 1
-    rdd = to_simple_rdd(spark_context, x_train, y_train)
-    spark_model = SparkModel(model, frequency='epoch', mode=mode,
-                             custom_objects={'custom_activation': custom_activation},
-                             port=4000 + random.randint(0, 800))
-    spark_model.fit(rdd, epochs=1, batch_size=16, verbose=0, validation_split=0.1)
-    assert spark_model.predict(x_test)
-    assert spark_model.evaluate(x_test, y_test)
+    x_train = rng.random(240).astype(np.float32)
+    y_train = (x_train > 0.5).astype(np.float32)
+    x_test = rng.random(31).astype(np.float32)
+    y_test = (x_test > 0.5).astype(np.float32)
+    before = model.get_weights()
+    spark_model = SparkModel(model, frequency='epoch', mode=mode, num_workers=workers,
+                             custom_objects={'shifted_sigmoid': shifted_sigmoid}, port=next(_ports))
+    loss_before = spark_model.evaluate(x_test, y_test)[0]
+    calls = CALLS['n']
+    spark_model.fit(to_simple_rdd(spark_context, x_train, y_train), epochs=3, batch_size=16, verbose=0,
+                    validation_split=0.1)
+    assert CALLS['n'] > calls  # the replicas built from JSON resolved the name to OUR function and ran it
+    after = spark_model.master_network.get_weights()
+    assert any(not np.allclose(a, b) for a, b in zip(before, after))  # training moved the master weights
+
+    preds = np.asarray(spark_model.predict(x_test)).reshape(-1)
+    assert preds.shape == (31,)
+    # the distributed prediction is the network with the +1-shifted sigmoid, not with a plain one
+    assert np.allclose(preds, _by_hand(after, x_test).reshape(-1), atol=1e-5)
+    loss, acc = spark_model.evaluate(x_test, y_test)
+    expect = _by_hand(after, x_test).reshape(-1)
+    by_hand_loss = float(np.mean(-(y_test * np.log(expect) + (1 - y_test) * np.log(1 - expect))))
+    assert abs(loss - by_hand_loss) < 1e-4 and 0.0 <= acc <= 1.0
+    if mode == 'synchronous':  # (a parameter server ADDS the workers' deltas: no monotonicity promise after one fit)
+        assert loss < loss_before

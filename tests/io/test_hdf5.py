@@ -67,7 +67,14 @@ def test_keras_layout_and_model_round_trip(tmp_path, mnist_data):
     dense = m.layers[1].name
     assert mw[dense + '/' + dense + '/kernel:0'].data.shape == (784, 128)  # Keras (in, out) layout
     assert 'optimizer_weights' in tree
+    # optimizer slots are stored in the Keras layout too (momentum of a Dense kernel: (in, out)), element for element
+    ow = tree['optimizer_weights']
+    slot = ow['SGD/' + dense + '/kernel/momentum:0'].data
+    assert slot.shape == (784, 128)
+    assert np.array_equal(slot, m.optimizer._slots[(0, 'momentum')].detach().cpu().numpy().T)
     m2 = load_model(path)
+    assert np.array_equal(m2.optimizer._slots[(0, 'momentum')].cpu().numpy(),
+                          m.optimizer._slots[(0, 'momentum')].cpu().numpy())
     assert m2.to_json() == m.to_json()
     assert np.array_equal(m2.predict(x[:20]), m.predict(x[:20]))
     assert m2.optimizer.get_config() == m.optimizer.get_config() and m2.optimizer.iterations == 4

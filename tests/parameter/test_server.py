@@ -175,3 +175,45 @@ def test_reference_method_names_of_the_servers_work_as_blocking_services():
         getattr(server, stop)()
         t.join(timeout=10)
         assert not t.is_alive()
+
+
+def test_socket_server_speaks_the_reference_frames_and_survives_half_a_frame():
+    """Opcode ``u`` is the reference's un-acknowledged update (elephas/parameter/client.py:85-91): nothing comes back on
+    the wire. Opcode ``U`` is acknowledged. A client that dies in the middle of a payload costs the server one
+    connection, not the weights and not the listener."""
+    import socket as _socket
+    import time
+    from elephas_b200.parameter.client import SocketClient
+    from elephas_b200.utils.sockets import determine_master, send
+    port = next(_ports)
+    model = _tiny_model()
+    factory = ClientServerFactory.get_factory('socket')
+    server = factory.create_server(model_to_dict(model), port, 'asynchronous')
+    server.start()
+    try:
+        w0 = model.get_weights()
+        delta = [np.full_like(w, 0.5) for w in w0]
+        host = determine_master(port=port).split(':')[0]
+        # the reference frame: no reply, the connection stays usable for the next opcode
+        with _socket.create_connection((host, port)) as sock:
+            sock.sendall(b'u')
+            send(sock, {'delta': delta})
+            sock.settimeout(0.3)
+            with pytest.raises(_socket.timeout):
+                sock.recv(1)
+        legacy = SocketClient(port, ack=False)
+        legacy.update_parameters(delta)
+        # half a frame, then the client disappears
+        with _socket.create_connection((host, port)) as sock:
+            sock.sendall(b'U' + b'00000000000000009999' + b'x' * 10)
+        acked = SocketClient(port)  # default: acknowledged updates
+        acked.update_parameters(delta)
+        deadline = time.time() + 5.0
+        while time.time() < deadline:
+            got = acked.get_parameters()
+            if all(np.allclose(a, b - 1.5) for a, b in zip(got, w0)):
+                break
+            time.sleep(0.05)
+        assert all(np.allclose(a, b - 1.5) for a, b in zip(acked.get_parameters(), w0))
+    finally:
+        server.stop()

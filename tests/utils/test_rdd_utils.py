@@ -1,65 +1,58 @@
+"""NumPy <-> RDD <-> LabeledPoint converters (reference: elephas/utils/rdd_utils.py:10-85). The checks are on VALUES and
+on round trips, with features that differ from row to row, so a converter that dropped, reordered or mis-encoded rows
+would be caught (the reference's own tests use all-ones features and mostly check shapes)."""
 import numpy as np
+import pytest
 
 from elephas.utils import rdd_utils
 
 
-def test_to_simple_rdd(spark_context):
-    features, labels = np.ones((5, 10)), np.ones((5,))
-    rdd = rdd_utils.to_simple_rdd(spark_context, features, labels)
-    assert rdd.count() == 5
-    first = rdd.first()
-    assert first[0].shape == (10,) and first[1] == 1.0
+def _data(rows=7, cols=5, classes=4, seed=0):
+    rng = np.random.default_rng(seed)
+    features = rng.normal(size=(rows, cols))
+    classes_of = rng.integers(0, classes, rows)
+    classes_of[0] = classes - 1  # the highest class is present, so nb_classes can be inferred
+    return features, classes_of, np.eye(classes)[classes_of]
 
 
-def test_to_labeled_rdd_categorical(spark_context):
-    features = np.ones((2, 10))
-    labels = np.asarray([[0, 0, 1.0], [0, 1.0, 0]])
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, labels, True)
-    assert lp_rdd.count() == 2
-    first = lp_rdd.first()
-    assert first.features.toArray().shape == (10,) and first.label == 2.0
+def test_to_simple_rdd_keeps_rows_and_order(spark_context):
+    features, classes_of, _ = _data()
+    rdd = rdd_utils.to_simple_rdd(spark_context, features, classes_of.astype(float))
+    rows = rdd.collect()
+    assert rdd.count() == len(rows) == 7
+    assert np.array_equal(np.stack([r[0] for r in rows]), features)
+    assert [float(r[1]) for r in rows] == [float(c) for c in classes_of]
 
 
-def test_to_labeled_rdd_not_categorical(spark_context):
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, np.ones((2, 10)), np.asarray([[2.0], [1.0]]), False)
-    assert lp_rdd.first().label == 2.0
+@pytest.mark.parametrize('categorical', [True, False])
+def test_labeled_points_round_trip(spark_context, categorical):
+    features, classes_of, one_hot = _data(seed=1)
+    labels = one_hot if categorical else classes_of.astype(float)
+    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, labels, categorical)
+    points = lp_rdd.collect()
+    assert [p.label for p in points] == [float(c) for c in classes_of]  # one-hot rows became class indices
+    assert np.array_equal(np.stack([p.features.toArray() for p in points]), features)
+    x, y = rdd_utils.from_labeled_point(lp_rdd, categorical, 4 if categorical else None)
+    assert np.array_equal(x, features)
+    assert np.array_equal(y, labels)
 
 
-def test_from_labeled_rdd(spark_context):
-    features, labels = np.ones((2, 10)), np.asarray([[2.0], [1.0]]).reshape((2,))
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, labels, False)
-    x, y = rdd_utils.from_labeled_point(lp_rdd, False, None)
-    assert x.shape == features.shape and y.shape == labels.shape
+def test_encode_label_is_a_unit_vector():
+    v = rdd_utils.encode_label(3, 10)
+    assert v.shape == (10,) and v[3] == 1.0 and v.sum() == 1.0
+    with pytest.raises(IndexError):
+        rdd_utils.encode_label(10, 10)
 
 
-def test_from_labeled_rdd_categorical(spark_context):
-    features = np.ones((2, 10))
-    labels = np.asarray([[0, 0, 1.0], [0, 1.0, 0]])
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, labels, True)
-    x, y = rdd_utils.from_labeled_point(lp_rdd, True, 3)
-    assert x.shape == features.shape and np.array_equal(y, labels)
-
-
-def test_encode_label():
-    assert np.array_equal(rdd_utils.encode_label(3, 10), np.eye(10)[3])
-
-
-def test_lp_to_simple_rdd_categorical(spark_context):
-    features = np.ones((2, 10))
-    labels = np.asarray([[0, 0, 1.0], [0, 1.0, 0]])
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, labels, True)
-    rdd = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=True, nb_classes=3)
-    assert rdd.first()[0].shape == (10,) and rdd.first()[1].shape == (3,)
-
-
-def test_lp_to_simple_rdd_not_categorical(spark_context):
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, np.ones((2, 10)), np.asarray([[2.0], [1.0]]).reshape((2,)), False)
-    rdd = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=False, nb_classes=3)
-    assert rdd.first()[0].shape == (10,) and rdd.first()[1] == 2.0
-
-
-def test_lp_to_simple_rdd_infers_nb_classes(spark_context):
-    labels = np.eye(5)[[0, 4, 2]]
-    lp_rdd = rdd_utils.to_labeled_point(spark_context, np.ones((3, 4)), labels, True)
-    rdd = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=True)
-    assert rdd.first()[1].shape == (5,)
+def test_lp_to_simple_rdd_one_hot_regression_and_inferred_width(spark_context):
+    features, classes_of, one_hot = _data(seed=2)
+    lp_rdd = rdd_utils.to_labeled_point(spark_context, features, one_hot, True)
+    rows = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=True, nb_classes=6).collect()
+    assert all(r[1].shape == (6,) and r[1].sum() == 1.0 and int(np.argmax(r[1])) == c for r, c in zip(rows, classes_of))
+    assert np.array_equal(np.stack([r[0] for r in rows]), features)
+    # nb_classes omitted: max label + 1 (rdd_utils.py:80)
+    inferred = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=True).collect()
+    assert all(r[1].shape == (4,) for r in inferred)
+    # regression: the label passes through as a scalar
+    plain = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=False).collect()
+    assert [float(r[1]) for r in plain] == [float(c) for c in classes_of]

@@ -89,3 +89,24 @@ def test_not_hdf5(tmp_path):
     p.write_bytes(b'nope' * 100)
     with pytest.raises(ValueError):
         hdf5.read_file(str(p))
+
+
+def test_reads_a_classic_libhdf5_layout_built_from_the_spec():
+    """The committed fixture is a version-0 superblock file with symbol-table groups (TREE / HEAP / SNOD) and version-1
+    object headers, assembled byte by byte from the HDF5 specification by ``make_v0_fixture.py`` - NOT by this
+    package's writer (which emits the version-2 layout). It is the layout libhdf5 / h5py / Keras write by default."""
+    import os
+    from tests.io import make_v0_fixture
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'fixtures', 'classic_v0.h5')
+    with open(path, 'rb') as fh:
+        blob = fh.read()
+    assert blob == make_v0_fixture.build()          # the committed bytes are what the generator states
+    assert blob[8] == 0 and b'TREE' in blob and b'SNOD' in blob and b'HEAP' in blob and b'OHDR' not in blob
+    root = hdf5.read_file(path)
+    assert sorted(root.keys()) == ['g', 'w']
+    assert root.attrs['note'] == b'built by hand' and int(root.attrs['answer']) == 42
+    w = np.asarray(root['w'])
+    assert w.dtype == np.float32 and np.array_equal(w, (np.arange(6, dtype=np.float32) * 0.5).reshape(2, 3))
+    b = root['g']['b']
+    assert np.array_equal(np.asarray(b), np.array([7, -1, 0, 2 ** 20], dtype=np.int32))
+    assert float(b.attrs['scale']) == 0.25

@@ -524,7 +524,9 @@ def run_torch(args, rt):
         load(i % n_w)
         step()
     torch.cuda.synchronize()
-    if os.environ.get('BENCH_TORCH_GRAPH', '1') != '0':
+    # whole-step capture only on one GPU: DDP's bucket hooks and an NCCL all-reduce issued from Python do not survive a
+    # capture here (the attempt fails and leaves the dropout generator in capture mode), so N > 1 runs eagerly
+    if N == 1 and os.environ.get('BENCH_TORCH_GRAPH', '1') != '0':
         try:
             g = torch.cuda.CUDAGraph()
             side = torch.cuda.Stream()

@@ -210,6 +210,23 @@ class ElephasTransformer(Model, HasKerasModelConfig, HasLabelCol, HasOutputCol, 
 
         regression = getattr(self, 'model_type', None) == ModelType.REGRESSION
 
+        if hasattr(df, 'column_block') and output_col not in df.columns:
+            # Local DataFrames: columns travel between pipeline stages as dense blocks. The features of ALL rows are one
+            # matrix (free when the previous stage - e.g. StandardScaler - produced the column as a block), the model
+            # predicts on it in one go (or in inference_batch_size pieces: bit-identical, tests/test_ml_model.py), and
+            # the predictions are appended as a block again; Row objects are only built if a later consumer asks for
+            # rows. The reference converts every row to a NumPy array and back (elephas/ml_model.py:222-250).
+            feats = np.ascontiguousarray(df.column_block(features_col), dtype=np.float32)
+            if feats.ndim == 2 and feats.shape[0] > 0:
+                if inference_batch_size is not None and inference_batch_size > 0:
+                    preds = np.vstack([model.predict(feats[i:i + inference_batch_size])
+                                       for i in range(0, len(feats), inference_batch_size)])
+                else:
+                    preds = model.predict(feats)
+                block = np.asarray(preds, dtype=np.float64).reshape(len(feats), -1)
+                return df.with_block_column(output_col, block[:, 0] if regression else block,
+                                            DoubleType() if regression else ArrayType(DoubleType()))
+
         def predict_rows(rows):
             # one predict per partition, then the output column is attached row by row: ndarray.tolist() converts the
             # whole block to Python floats at C speed (reference: one np.asarray + float() per row, ml_model.py:222-227)

@@ -383,6 +383,14 @@ class StringIndexerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadable
 
     def _transform(self, dataset):
         index = {l: float(i) for i, l in enumerate(self.labels)}
+        if hasattr(dataset, 'with_block_column') and self.getOutputCol() not in dataset.columns:
+            # one pass over the label column, the indices appended as a block (rows are only rebuilt on demand)
+            from .sql import DoubleType as _DoubleType
+            i, get = dataset.columns.index(self.getInputCol()), tuple.__getitem__
+            rows = dataset.rdd.collect()
+            if rows and isinstance(rows[0], tuple):
+                block = np.fromiter((index[str(get(r, i))] for r in rows), dtype=np.float64, count=len(rows))
+                return dataset.with_block_column(self.getOutputCol(), block, _DoubleType())
         return dataset.withColumn(self.getOutputCol(), Column(self.getInputCol(), fn=lambda v: index[str(v)]))
 
 
@@ -417,6 +425,15 @@ class StandardScalerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadabl
             arr = v.toArray() if isinstance(v, Vector) else np.asarray(v, dtype=np.float64)
             return DenseVector((arr - mean) * scale)
 
+        if hasattr(dataset, 'column_block') and self.getOutputCol() not in dataset.columns:
+            try:
+                block = dataset.column_block(self.getInputCol())
+            except (TypeError, ValueError):
+                block = None
+            if block is not None and block.ndim == 2:
+                # the whole column as one matrix in, one matrix out: later stages read the block, rows are built lazily
+                from .sql import VectorUDT as _VectorUDT
+                return dataset.with_block_column(self.getOutputCol(), (block - mean) * scale, _VectorUDT())
         blocked = self._transform_blocks(dataset, mean, scale)
         if blocked is not None:
             return blocked

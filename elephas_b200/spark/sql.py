@@ -223,31 +223,97 @@ class functions:
 
 # ----------------------------------------------------------------- DataFrame
 class DataFrame:
-    def __init__(self, rdd, schema, session):
-        self._rdd = rdd
+    def __init__(self, rdd, schema, session, base=None, blocks=None):
+        self._rdd = rdd  # None: rows are derived lazily from ``base``'s rows + the appended column blocks
         self.schema = schema
         self.sparkSession = session
         self.sql_ctx = session
+        self._base, self._blocks = base, dict(blocks or {})
+        self._block_cache = {}
 
     @property
     def rdd(self):
+        if self._rdd is None:
+            self._rdd = self._materialize_rows()
         return self._rdd
+
+    # ----------------------------------------------------------------- column blocks
+    # Pipeline stages that compute on whole columns (StandardScaler, ElephasTransformer) exchange dense matrices instead
+    # of Python row objects: a stage appends its output as a *block* (one ndarray for all rows), the next stage reads
+    # that block directly, and Row objects are only built if somebody asks for rows (collect / rdd / select). The
+    # reference pays per row at every stage (np.asarray + Vectors.dense + Row per element, elephas/ml_model.py:222-250).
+    def with_block_column(self, name, block, data_type):
+        """New DataFrame = this one + column ``name`` whose values are the rows of ``block`` (``[rows]`` or
+        ``[rows, width]``); ``data_type``: DoubleType (scalars), ArrayType(DoubleType()) (lists) or VectorUDT (vectors)."""
+        block = np.asarray(block)
+        if name in self.columns:
+            raise ValueError("column %r already exists" % (name,))
+        if block.shape[0] != self.count():
+            raise ValueError("block has %d rows, the frame %d" % (block.shape[0], self.count()))
+        schema = copy.deepcopy(self.schema)
+        schema.add(StructField(name, data_type, True))
+        return DataFrame(None, schema, self.sparkSession, base=self, blocks={name: block})
+
+    def column_block(self, name):
+        """The column as ONE float64 ndarray in row order (``[rows]`` for scalars, ``[rows, width]`` for vector / array
+        columns). Free when the column was appended as a block; otherwise built from the rows once and cached."""
+        if name in self._blocks:
+            return self._blocks[name]
+        if self._rdd is None and self._base is not None and name in self._base.columns:
+            return self._base.column_block(name)
+        cached = self._block_cache.get(name)
+        if cached is None:
+            i = self._col_index(name)
+            get = tuple.__getitem__
+            rows = self.rdd.collect()
+            vals = [get(r, i) for r in rows] if rows and isinstance(rows[0], tuple) else [r[i] for r in rows]
+            if vals and hasattr(vals[0], 'toArray'):
+                width = len(vals[0].toArray())
+                cached = np.empty((len(vals), width), dtype=np.float64)
+                for k, v in enumerate(vals):
+                    cached[k] = v.toArray()  # (row-wise copy into one matrix: no intermediate list of arrays)
+            else:
+                cached = np.asarray(vals, dtype=np.float64)
+            self._block_cache[name] = cached
+        return cached
+
+    def _materialize_rows(self):
+        from .linalg import DenseVector
+        base_rdd = self._base.rdd
+        names = self.columns
+        row_cls, new = _row_class(names), tuple.__new__
+        cols = []
+        for f in self.schema.fields[len(self._base.columns):]:
+            block = self._blocks[f.name]
+            if isinstance(f.dataType, VectorUDT):
+                cols.append([DenseVector(v) for v in np.asarray(block, dtype=np.float64)])
+            else:
+                cols.append(np.asarray(block, dtype=np.float64).tolist())  # whole block -> Python floats at C speed
+        parts, start = [], 0
+        for p in base_rdd.partitions():
+            rows = p if isinstance(p, list) else list(p)
+            extra = [c[start:start + len(rows)] for c in cols]
+            parts.append([new(row_cls, tuple(r) + tail) for r, tail in zip(rows, zip(*extra))] if rows else [])
+            start += len(rows)
+        return RDD(parts, base_rdd.context)
 
     @property
     def columns(self):
         return self.schema.names
 
     def count(self):
-        return self._rdd.count()
+        if self._rdd is None and self._base is not None:
+            return self._base.count()
+        return self.rdd.count()
 
     def collect(self):
-        return self._rdd.collect()
+        return self.rdd.collect()
 
     def take(self, n):
-        return self._rdd.take(n)
+        return self.rdd.take(n)
 
     def first(self):
-        return self._rdd.first()
+        return self.rdd.first()
 
     def head(self, n=None):
         return self.first() if n is None else self.take(n)
@@ -266,7 +332,7 @@ class DataFrame:
         names = [c.out_name for c in cols]
         fns = [c.fn for c in cols]
         fields = []
-        first = self._rdd.take(1)
+        first = self.rdd.take(1)
         for c, i, fn in zip(cols, idx, fns):
             base = self.schema.fields[i]
             dtype = base.dataType if fn is None else _infer_type(fn(first[0][i])) if first else base.dataType
@@ -275,12 +341,12 @@ class DataFrame:
         def project(row):
             return Row._make(names, [row[i] if fn is None else fn(row[i]) for i, fn in zip(idx, fns)])
 
-        return DataFrame(self._rdd.map(project), StructType(fields), self.sparkSession)
+        return DataFrame(self.rdd.map(project), StructType(fields), self.sparkSession)
 
     def withColumnRenamed(self, existing, new):
         names = [new if n == existing else n for n in self.columns]
         fields = [StructField(n, f.dataType, f.nullable) for n, f in zip(names, self.schema.fields)]
-        return DataFrame(self._rdd.map(lambda r: Row._make(names, list(r))), StructType(fields), self.sparkSession)
+        return DataFrame(self.rdd.map(lambda r: Row._make(names, list(r))), StructType(fields), self.sparkSession)
 
     def withColumn(self, name, col):
         if not isinstance(col, Column):
@@ -291,7 +357,7 @@ class DataFrame:
         replace = names.index(name) if name in names else None
         if replace is None:
             names.append(name)
-        first = self._rdd.take(1)
+        first = self.rdd.take(1)
         dtype = _infer_type(fn(first[0][src])) if first else DoubleType()
         fields = list(self.schema.fields)
         if replace is None:
@@ -308,7 +374,7 @@ class DataFrame:
             vals[replace] = fn(get(row, src))
             return new(row_cls, vals)
 
-        return DataFrame(self._rdd.map(extend), StructType(fields), self.sparkSession)
+        return DataFrame(self.rdd.map(extend), StructType(fields), self.sparkSession)
 
     def drop(self, *cols):
         keep = [c for c in self.columns if c not in cols]
@@ -321,13 +387,13 @@ class DataFrame:
             if key not in seen:
                 seen.add(key)
                 rows.append(r)
-        return DataFrame(RDD([rows], self._rdd.context), self.schema, self.sparkSession)
+        return DataFrame(RDD([rows], self.rdd.context), self.schema, self.sparkSession)
 
     def repartition(self, n):
-        return DataFrame(self._rdd.repartition(n), self.schema, self.sparkSession)
+        return DataFrame(self.rdd.repartition(n), self.schema, self.sparkSession)
 
     def limit(self, n):
-        return DataFrame(RDD([self.take(int(n))], self._rdd.context), self.schema, self.sparkSession)
+        return DataFrame(RDD([self.take(int(n))], self.rdd.context), self.schema, self.sparkSession)
 
     def randomSplit(self, weights, seed=None):
         """Random split by normalised ``weights`` (every row lands in exactly one part)."""
@@ -345,7 +411,7 @@ class DataFrame:
                 if u < b or i == len(bounds) - 1:
                     parts[i].append(row)
                     break
-        return [DataFrame(RDD([rows], self._rdd.context), self.schema, self.sparkSession) for rows in parts]
+        return [DataFrame(RDD([rows], self.rdd.context), self.schema, self.sparkSession) for rows in parts]
 
     def cache(self):
         return self

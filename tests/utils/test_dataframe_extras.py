@@ -88,3 +88,43 @@ def test_repartition_of_a_single_block_shares_memory():
     assert [len(p) for p in parts] == [4, 3, 3]
     assert np.shares_memory(np.asarray(parts[1].x), np.asarray(one.partitions()[0].x))
     assert np.array_equal(np.concatenate([np.asarray(p.x) for p in parts]), x)
+
+
+def test_pipeline_stages_exchange_column_blocks_and_build_rows_lazily():
+    """StringIndexer -> StandardScaler -> ElephasTransformer pass whole columns as ndarrays ("blocks"); Row objects for
+    the appended columns only come into being when a consumer asks for rows, and then hold exactly the block values."""
+    import numpy as np
+    from elephas.ml_model import ElephasTransformer
+    from elephas_b200.models import Dense, Sequential
+    from elephas_b200.spark import PipelineModel, SparkSession, StandardScaler, StringIndexer, Vectors
+    from elephas_b200.utils.model_utils import ModelType
+    rng = np.random.default_rng(5)
+    feats = rng.normal(size=(257, 6))
+    cats = ['c%d' % (i % 3) for i in range(257)]
+    spark = SparkSession.builder.getOrCreate()
+    df = spark.createDataFrame([(Vectors.dense(f), c) for f, c in zip(feats, cats)], ['features', 'category'])
+    model = Sequential([Dense(5, input_dim=6, activation='relu'), Dense(3, activation='softmax')])
+    stages = [StringIndexer(inputCol='category', outputCol='idx').fit(df),
+              StandardScaler(inputCol='features', outputCol='scaled', withMean=True, withStd=True).fit(df),
+              ElephasTransformer(keras_model_config=model.to_json(), weights=model.get_weights(), featuresCol='scaled',
+                                 labelCol='idx', outputCol='prediction', model_type=ModelType.CLASSIFICATION)]
+    out = PipelineModel(stages).transform(df)
+    assert out.columns == ['features', 'category', 'idx', 'scaled', 'prediction'] and out.count() == 257
+    assert out._rdd is None  # nothing has been turned into rows yet
+    scaled = (feats - feats.mean(0)) / feats.std(0, ddof=1)
+    assert np.allclose(out.column_block('scaled'), scaled)
+    expect = model.predict(scaled.astype(np.float32))
+    assert np.allclose(out.column_block('prediction'), expect, atol=1e-6)
+    labels = sorted(set(cats), key=lambda c: (-cats.count(c), c))
+    assert np.array_equal(out.column_block('idx'), np.array([float(labels.index(c)) for c in cats]))
+    rows = out.collect()  # now the rows exist, in the original order, with plain Python values
+    assert len(rows) == 257 and rows[7].category == cats[7] and isinstance(rows[7].prediction, list)
+    assert np.allclose(rows[7].prediction, expect[7], atol=1e-6) and np.allclose(rows[7].scaled.toArray(), scaled[7])
+    assert rows[7].idx == float(labels.index(cats[7]))
+    # a row-level consumer downstream still works on the lazily built frame
+    assert out.select('prediction').count() == 257
+    import pytest
+    with pytest.raises(ValueError):
+        out.with_block_column('prediction', np.zeros((257, 3)), None)
+    with pytest.raises(ValueError):
+        out.with_block_column('other', np.zeros((5, 3)), None)

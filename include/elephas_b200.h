@@ -327,6 +327,72 @@ int eb_head_fwd(const EbHeadArgs* args, void* stream);
 int eb_head_wgrad(const EbHeadArgs* args, void* stream);
 int eb_head_dgrad(const EbHeadArgs* args, void* stream);
 
+/* ------------------------------------------------------------ K9: convolutions as implicit GEMMs on tcgen05
+ * Channels-last bf16 activations [N][H][W][C], kernels [Cout][R][S][Cin] (OHWI, bf16 copies of the fp32 master), fp32
+ * accumulation in TMEM. No im2col matrix is ever built: the A operand of the GEMM is fetched patch by patch by TMA from
+ * a 4-D tensor map over the activation (a box of pn x ph x pw output pixels x 64 channels per filter tap, shifted by the
+ * tap offset, element strides = convolution stride, out-of-bounds = zero padding), straight into the 128B-swizzled
+ * layout tcgen05.mma reads. The reference reaches these ops through Keras' model.fit on any Keras model
+ * (elephas/worker.py:42,108); BASELINE.json names a ResNet-50-shaped CNN.
+ *
+ *   eb_conv_igemm   out[n][p*os][q*os][k] = bias[k] + sum_{r,s,c} in[n][p*stride - pad_h + r][q*stride - pad_w + s][c]
+ *                                                                  * w[k][tap(r,s)][c]
+ *       forward:        in = x, out = y, weights K-major ([Cout][R*S][Cin] = the OHWI kernel itself)
+ *       input gradient: in = dy, out = dx, stride 1, pad = R-1-pad, flip_taps = 1, w_mn = 1: the SAME kernel array is read
+ *                       "N-major" (Cout becomes the reduction dimension), so no transposed copy of the weights exists;
+ *                       for a strided 1x1 convolution os = stride scatters the result (the caller zeroes dx first)
+ *   eb_conv_wgrad   dw[k][tap][c] += sum_{n,p,q} dy[n][p][q][k] * x[n][p*stride - pad_h + r][q*stride - pad_w + s][c]
+ *                   (fp32, accumulated with red.add: the pixel reduction is split over CTAs; zero dw before the call)
+ * Requirements: Cin and Cout multiples of 8, 16-byte aligned tensors; pw * stride <= 256. */
+typedef struct {
+  const void* in;  int32_t N, H, W, C;       /* bf16 [N][H][W][C]: the tensor the patches are cut from */
+  const void* w;   int32_t K, R, S;          /* bf16 kernel [K][R][S][Cw]; forward: Cw = C, K = output channels;
+                                                input gradient (w_mn): the forward kernel [C][R][S][K], i.e. its first
+                                                dimension is the reduction and its last the output channels */
+  int32_t w_mn, flip_taps;
+  int32_t stride, pad_h, pad_w;
+  int32_t P, Q;                              /* patch-origin grid (= output pixels of the GEMM) */
+  int32_t pn, ph, pw;                        /* output pixels per tile: pn*ph*pw <= 128 */
+  void* out;       int32_t OH, OW, os;       /* bf16 [N][OH][OW][Kout]; GEMM pixel (n,p,q) lands at (n, p*os, q*os) */
+  const float* bias;                         /* [Kout] or NULL */
+  int32_t block_n;                           /* 0 = auto, else 64 / 128 */
+} EbConvArgs;
+int eb_conv_igemm(const EbConvArgs* args, void* stream);
+
+typedef struct {
+  const void* x;   int32_t N, H, W, C;       /* bf16 forward input */
+  const void* dy;  int32_t P, Q, K;          /* bf16 output gradient [N][P][Q][K] */
+  int32_t R, S, stride, pad_h, pad_w;
+  int32_t pn, ph, pw;                        /* pixels per reduction block: pn*ph*pw <= 64 */
+  float* dw;                                 /* fp32 [K][R][S][C], accumulated */
+  int32_t splits;                            /* 0 = auto: CTAs that share one output tile's pixel reduction */
+} EbConvWgradArgs;
+int eb_conv_wgrad(const EbConvWgradArgs* args, void* stream);
+
+/* Patch matrix of the first layer (3 input channels do not fill a TMA row): out[n*P*Q + p*Q + q][(r*S + s)*C + c] =
+ * x[n][p*stride - pad + r][q*stride - pad + s][c], zero padded to `ld` columns; x is fp32 or bf16 (x_is_f32). */
+int eb_conv_im2col(const void* x, int32_t x_is_f32, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
+                   int32_t stride, int32_t pad, int32_t P, int32_t Q, void* out_bf16, int32_t ld, void* stream);
+
+/* BatchNormalization over channels-last bf16 [M][C] (C multiple of 8), statistics in fp32.
+ *   eb_bn_stats       sums[0][c] += sum_m x, sums[1][c] += sum_m x^2                     (zero sums first)
+ *   eb_bn_finalize    mean, rstd = 1/sqrt(var + eps) from sums; running statistics updated with `momentum` (Keras:
+ *                     running = running * momentum + batch * (1 - momentum); unbiased batch variance), sums re-zeroed
+ *   eb_bn_apply       y = act((x - mean) * rstd * gamma + beta [+ residual]),  act = ReLU when relu != 0
+ *   eb_bn_bwd_reduce  dz = dy * (y > 0 if relu);  sums[0][c] += sum dz, sums[1][c] += sum dz * xhat
+ *   eb_bn_bwd_apply   dx = gamma * rstd * (dz - sums[0]/M - xhat * sums[1]/M); dres = dz when requested
+ * Reference: Keras BatchNormalization / Activation / Add layers inside model.fit (elephas/worker.py:42). */
+int eb_bn_stats(const void* x, int64_t M, int32_t C, float* sums, void* stream);
+int eb_bn_finalize(float* sums, int64_t M, int32_t C, float eps, float momentum, float* mean, float* rstd,
+                   float* running_mean, float* running_var, void* stream);
+int eb_bn_apply(const void* x, int64_t M, int32_t C, const float* mean, const float* rstd, const float* gamma,
+                const float* beta, const void* residual, int32_t relu, void* y, void* stream);
+int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
+                     const float* rstd, int32_t relu, float* sums, void* stream);
+int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
+                    const float* rstd, const float* gamma, const float* sums, int32_t relu, void* dx, void* dres,
+                    void* stream);
+
 /* ------------------------------------------------------------ host side of the input pipeline
  * dst[r][0..cols) = bf16(src[r][0..cols)) (round to nearest even, bit-identical to the device cast), padding columns
  * [cols, ld_dst) zeroed; runs on `threads` CPU threads (persistent pool) and returns when the batch is converted.

@@ -9,7 +9,7 @@ with Keras' config schema, weight order and weight *layouts* at the API boundary
 
 Internally weights live in the layout the B200 kernels want: a Dense kernel is stored
 ``[out, in]`` (K-major for the tcgen05 GEMM ``Y = X W^T``) and exposed as Keras' ``(in, out)``
-through ``get_weights`` / ``set_weights``; Conv2D is stored OIHW and exposed HWIO.
+through ``get_weights`` / ``set_weights``; Conv2D is stored OHWI (channels-last, the implicit-GEMM layout) and exposed HWIO.
 """
 import math
 import re
@@ -265,6 +265,10 @@ class Dense(Layer):
         return tuple(input_shape[:-1]) + (self.units,)
 
     def call(self, x, training=False):
+        if x.is_cuda and x.dim() == 2 and self.use_bias:
+            from ..ops import cnn as _cnn
+            if _cnn.usable(x) and _cnn.linear_supported(self.kernel):
+                return self.activation(_cnn.linear(x, self.kernel, self.bias))  # bf16 compute: tcgen05 GEMM (K1)
         return self.activation(F.linear(x, self.kernel, self.bias))
 
     def _extra_config(self):
@@ -396,7 +400,8 @@ def _same_pad(x, k, stride, dilation=(1, 1)):
 
 
 class Conv2D(Layer):
-    """channels_last convolution. Kernel exposed as Keras HWIO, stored OIHW (channels_last memory format)."""
+    """channels_last convolution. Kernel exposed as Keras HWIO, stored OHWI ``[filters, kh, kw, cin]``: the K-major weight
+    operand of the implicit-GEMM kernels (``ops/cnn.py``) as it is, and a channels-last OIHW view for the torch ops."""
 
     def __init__(self, filters, kernel_size, strides=(1, 1), padding='valid', data_format=None,
                  dilation_rate=(1, 1), groups=1, activation=None, use_bias=True,
@@ -423,7 +428,7 @@ class Conv2D(Layer):
         cin = int(input_shape[-1])
         kh, kw = self.kernel_size
         fan_in, fan_out = kh * kw * cin // self.groups, kh * kw * self.filters
-        w = torch.empty(self.filters, cin // self.groups, kh, kw)
+        w = torch.empty(self.filters, kh, kw, cin // self.groups)
         self.kernel = self.add_weight('kernel', _initialize(w, self.kernel_initializer, fan_in, fan_out))
         if self.use_bias:
             self.bias = self.add_weight('bias', _initialize(torch.empty(self.filters), self.bias_initializer, fan_in,
@@ -431,10 +436,10 @@ class Conv2D(Layer):
         self.built = True
 
     def to_keras_layout(self, index, tensor):
-        return tensor.permute(2, 3, 1, 0) if index == 0 else tensor
+        return tensor.permute(1, 2, 3, 0) if index == 0 else tensor
 
     def from_keras_layout(self, index, array):
-        return np.transpose(array, (3, 2, 0, 1)) if index == 0 else array
+        return np.transpose(array, (3, 0, 1, 2)) if index == 0 else array
 
     def compute_output_shape(self, input_shape):
         n, h, w, _ = input_shape
@@ -442,17 +447,17 @@ class Conv2D(Layer):
                 _conv_out(w, self.kernel_size[1], self.strides[1], self.padding, self.dilation_rate[1]), self.filters)
 
     def call(self, x, training=False):
+        pads = (0, 0, 0, 0)
         if self.padding == 'same':
-            pads = _same_pad(x, self.kernel_size, self.strides, self.dilation_rate)
-            if any(pads):
-                x = F.pad(x, (0, 0) + tuple(pads))
-        if x.is_cuda and torch.is_autocast_enabled('cuda'):
-            from ..ops import conv1x1 as _c1
-            # bf16 compute on a GPU: 1x1 / stride-1 convolutions can run on the tcgen05 GEMM (opt-in, ops/conv1x1.py)
-            if _c1.enabled() and _c1.eligible(x, self.kernel, self.strides, self.dilation_rate, self.groups,
-                                              self.padding == 'same' and self.kernel_size != (1, 1)):
-                return self.activation(_c1.conv1x1(x, self.kernel, self.bias))
-        y = F.conv2d(x.permute(0, 3, 1, 2), self.kernel, self.bias, stride=self.strides,
+            pads = tuple(_same_pad(x, self.kernel_size, self.strides, self.dilation_rate))  # (left, right, top, bottom)
+        from ..ops import cnn as _cnn
+        if _cnn.usable(x) and _cnn.conv2d_supported(x, self.kernel, self.strides, self.dilation_rate, self.groups, pads):
+            # bf16 compute on a B200: implicit GEMM on tcgen05; 'same' padding is the TMA's out-of-bounds zero fill
+            y = _cnn.conv2d(x, self.kernel, self.bias, self.strides[0], (pads[2], pads[3], pads[0], pads[1]))
+            return self.activation(y)
+        if any(pads):
+            x = F.pad(x, (0, 0) + pads)
+        y = F.conv2d(x.permute(0, 3, 1, 2), self.kernel.permute(0, 3, 1, 2), self.bias, stride=self.strides,
                      dilation=self.dilation_rate, groups=self.groups)
         return self.activation(y.permute(0, 2, 3, 1))
 
@@ -494,13 +499,23 @@ class BatchNormalization(Layer):
         self.moving_variance = self.add_weight('moving_variance', torch.ones(c), trainable=False)
         self.built = True
 
-    def call(self, x, training=False):
+    def call(self, x, training=False, residual=None, fuse_relu=False):
+        """``residual`` / ``fuse_relu``: the model's executor hands a following ``Add`` / ``Activation('relu')`` to this
+        layer when nothing else reads the intermediate values (one kernel instead of three passes over the tensor)."""
         nd = x.dim()
         axis = self.axis % nd
+        if axis == nd - 1 and x.is_cuda and x.shape[-1] % 8 == 0 and (training or not torch.is_grad_enabled()):
+            from ..ops import cnn as _cnn
+            if _cnn.usable(x):
+                return _cnn.batch_norm(x, self.gamma, self.beta, self.moving_mean, self.moving_variance, self.epsilon,
+                                       self.momentum, training, residual=residual, relu=fuse_relu)
         xc = x.movedim(axis, 1) if axis != 1 else x
         y = F.batch_norm(xc, self.moving_mean, self.moving_variance, self.gamma, self.beta, training=training,
                          momentum=1.0 - self.momentum, eps=self.epsilon)
-        return y.movedim(1, axis) if axis != 1 else y
+        y = y.movedim(1, axis) if axis != 1 else y
+        if residual is not None:
+            y = y + residual
+        return torch.relu(y) if fuse_relu else y
 
     def _extra_config(self):
         return {'axis': [self.axis], 'momentum': self.momentum, 'epsilon': self.epsilon, 'center': self.center,

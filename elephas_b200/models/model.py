@@ -14,6 +14,7 @@ every workload the reference ships) trains and predicts through the native sm_10
 every other model, and every model on the CPU, runs through torch autograd.
 """
 import json
+import os
 
 import numpy as np
 import torch
@@ -96,20 +97,79 @@ class Model:
         for o in self._outputs:
             visit(o)
         self._node_order = order
+        self._fusion_cache = None
         self.layers = []
         for t in order:
             if t.layer not in self.layers:
                 self.layers.append(t.layer)
 
+    def _fusion_plan(self):
+        """Which nodes collapse into their BatchNormalization producer (computed once per graph):
+
+        * BN -> Activation('relu'), the BN output read by nothing else:                  the BN applies the ReLU
+        * BN -> Add([other, BN]) -> Activation('relu'), intermediates read by nothing else: the BN adds ``other`` and
+          applies the ReLU (the tail of a residual block); ``other`` must be computed before the BN in node order.
+
+        Returns ``{bn node key: (relu, residual key or None)}, {absorbed node key: node key it aliases}``. The fused
+        call computes exactly what the separate layers compute; on B200 in bf16 it is one kernel (``ops/cnn.py``)."""
+        plan = getattr(self, '_fusion_cache', None)
+        if plan is not None:
+            return plan
+        key_of = lambda t: (id(t.layer), t.node_index)  # noqa: E731
+        order = {key_of(t): i for i, t in enumerate(self._node_order)}
+        consumers = {}
+        for t in self._node_order:
+            for s in t.layer.inbound[t.node_index]:
+                consumers.setdefault(key_of(s), []).append(t)
+        outputs = {key_of(o) for o in self._outputs}
+
+        def only_consumer(k):
+            c = consumers.get(k, [])
+            return c[0] if len(c) == 1 and k not in outputs else None
+
+        is_relu = lambda t: isinstance(t.layer, L.Activation) and t.layer.activation_name == 'relu'  # noqa: E731
+        fused, alias = {}, {}
+        for t in self._node_order:
+            if not isinstance(t.layer, L.BatchNormalization):
+                continue
+            k = key_of(t)
+            nxt = only_consumer(k)
+            if nxt is None:
+                continue
+            if is_relu(nxt):
+                fused[k] = (True, None)
+                alias[key_of(nxt)] = k
+            elif isinstance(nxt.layer, L.Add) and len(nxt.layer.inbound[nxt.node_index]) == 2:
+                srcs = [key_of(s) for s in nxt.layer.inbound[nxt.node_index]]
+                other = srcs[0] if srcs[1] == k else srcs[1]
+                after = only_consumer(key_of(nxt))
+                # this BN must be the later of the two Add inputs, and not the same tensor twice
+                if after is not None and is_relu(after) and other != k and order.get(other, -1) < order[k] \
+                        and other not in alias:
+                    fused[k] = (True, other)
+                    alias[key_of(nxt)] = k
+                    alias[key_of(after)] = k
+        self._fusion_cache = (fused, alias)
+        return self._fusion_cache
+
     def _forward(self, xs, training):
         values = {}
         for t, x in zip(self._inputs, xs):
             values[(id(t.layer), t.node_index)] = x
+        fused, alias = self._fusion_plan() if os.environ.get('ELEPHAS_B200_FUSE_BN', '1') != '0' else ({}, {})
         for t in self._node_order:
             key = (id(t.layer), t.node_index)
             if key in values:
                 continue
+            if key in alias:
+                values[key] = values[alias[key]]  # absorbed into the BatchNormalization that produced its input
+                continue
             ins = [values[(id(s.layer), s.node_index)] for s in t.layer.inbound[t.node_index]]
+            if key in fused:
+                relu, other = fused[key]
+                values[key] = t.layer.call(ins[0], training=training, fuse_relu=relu,
+                                           residual=values[other] if other is not None else None)
+                continue
             values[key] = t.layer.call(ins[0] if len(ins) == 1 else ins, training=training)
         outs = [values[(id(o.layer), o.node_index)] for o in self._outputs]
         return outs[0] if len(outs) == 1 else outs

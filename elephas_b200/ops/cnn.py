@@ -1,0 +1,230 @@
+"""Native convolutional layers (K9): autograd functions around the sm_100a kernels of ``csrc/conv_sm100.cu`` /
+``csrc/conv_aux.cu``.
+
+The reference trains CNNs through ``keras.Model.fit`` on the workers (``elephas/worker.py:42,108``). Here, for a model
+that computes in bf16 on a B200, every Conv2D / BatchNormalization / ReLU / residual Add / Dense of the forward and
+backward pass is one of this repository's kernels:
+
+* ``conv2d``      implicit GEMM on tcgen05: forward, input gradient (the same OHWI kernel array read N-major, no
+                  transposed copy) and split-K weight gradient; the 3-channel input layer goes through a small patch
+                  matrix (``eb_conv_im2col``) and then the same GEMM kernels
+* ``batch_norm``  statistics -> normalise (+ residual) (+ ReLU) in one pass; backward = one reduction pass + one apply
+                  pass that also emits the gradient of the residual branch
+* ``linear``      the tcgen05 GEMM of the Dense engine (K1)
+
+torch autograd only orders the calls (and the whole step is replayed from a CUDA graph by ``ops/torch_step.py``);
+activations travel channels-last in bf16, master weights stay fp32. ``ELEPHAS_B200_NATIVE_CONV=0`` switches the layers
+back to the torch / cuDNN ops (the A/B arm of the benchmark).
+"""
+import os
+
+import torch
+
+from . import native
+
+
+def enabled():
+    return os.environ.get('ELEPHAS_B200_NATIVE_CONV', '1') != '0' and native.available()
+
+
+def usable(x):
+    """bf16 compute on a CUDA device requested (autocast region of ``Model.set_compute_dtype('bfloat16')``)."""
+    return x.is_cuda and torch.is_autocast_enabled('cuda') and torch.get_autocast_dtype('cuda') == torch.bfloat16 and enabled()
+
+
+def _bf16(t):
+    t = t if t.dtype == torch.bfloat16 else t.to(torch.bfloat16)
+    return t if t.is_contiguous() else t.contiguous()
+
+
+def _out_size(size, k, stride, pad_lo, pad_hi):
+    return (size + pad_lo + pad_hi - k) // stride + 1
+
+
+class _Conv2d(torch.autograd.Function):
+    """``x`` NHWC, ``kernel`` fp32 OHWI ``[K, R, S, C]``; ``pads`` = (top, bottom, left, right) zeros (handled by the TMA
+    out-of-bounds fill: no padded copy of the activation is made)."""
+
+    @staticmethod
+    def forward(ctx, x, kernel, bias, stride, pads):
+        wb = kernel.detach().to(torch.bfloat16)
+        N, H, W, C = x.shape
+        K, R, S, _ = wb.shape
+        xb = _bf16(x) if C % 8 == 0 or not (x.dtype == torch.float32 and x.is_contiguous()) else None
+        pt, pb, pl, pr = pads
+        P, Q = _out_size(H, R, stride, pt, pb), _out_size(W, S, stride, pl, pr)
+        y = torch.empty(N, P, Q, K, dtype=torch.bfloat16, device=x.device)
+        b32 = bias.detach().float() if bias is not None else None
+        small_c = C % 8 != 0
+        cols = None
+        if small_c:
+            # input layer (3 channels): explicit patch matrix, then a 1x1 convolution over it
+            ld = (R * S * C + 31) // 32 * 32
+            cols = torch.empty(N, P, Q, ld, dtype=torch.bfloat16, device=x.device)
+            src = x if (x.dtype == torch.float32 and x.is_contiguous()) else xb  # the kernel casts while it gathers
+            native.conv_im2col(src, R, S, stride, pt, P, Q, cols, ld)
+            wpad = torch.zeros(K, 1, 1, ld, dtype=torch.bfloat16, device=x.device)
+            wpad.view(K, ld)[:, :R * S * C] = wb.view(K, R * S * C)
+            native.conv_igemm(cols, wpad, y, P, Q, 1, 1, bias=b32)
+            ctx.save_for_backward(cols, wpad)
+        else:
+            native.conv_igemm(xb, wb, y, P, Q, R, S, stride=stride, pad_h=pt, pad_w=pl, bias=b32)
+            ctx.save_for_backward(xb, wb)
+        ctx.geom = (x.shape, x.dtype, tuple(kernel.shape), stride, pads, P, Q, small_c, bias is not None)
+        ctx.kernel_param = kernel
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        saved_x, wb = ctx.saved_tensors
+        x_shape, x_dtype, k_shape, stride, pads, P, Q, small_c, has_bias = ctx.geom
+        kernel = ctx.kernel_param
+        K, R, S, C = k_shape
+        N, H, W, _ = x_shape
+        pt, pb, pl, pr = pads
+        g = _bf16(gy)
+        torch.cuda.set_device(g.device)  # autograd's worker thread: the TMA descriptor encoder needs the context
+        dx = dw = db = None
+        if ctx.needs_input_grad[0] and not small_c:
+            if stride == 1:
+                dxb = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=g.device)
+                # dx[h] = sum_r dy[h + pad - r] w[r]: a stride-1 convolution of dy with the flipped taps, padding R-1-pad
+                native.conv_igemm(g, wb, dxb, H, W, R, S, stride=1, pad_h=R - 1 - pt, pad_w=S - 1 - pl, w_mn=True,
+                                  flip_taps=True)
+            elif R == 1 and S == 1:
+                dxb = torch.zeros(N, H, W, C, dtype=torch.bfloat16, device=g.device)
+                native.conv_igemm(g, wb, dxb, P, Q, 1, 1, stride=1, os=stride, w_mn=True)  # scatter to the sampled pixels
+            else:
+                raise NotImplementedError("input gradient of a strided %dx%d convolution" % (R, S))
+            dx = dxb if x_dtype == torch.bfloat16 else dxb.to(x_dtype)
+        if ctx.needs_input_grad[1]:
+            target = kernel.grad if (kernel.grad is not None and kernel.grad.is_contiguous() and not small_c
+                                     and kernel.grad.dtype == torch.float32) else None
+            if small_c:
+                ld = saved_x.shape[3]
+                dwp = torch.zeros(K, 1, 1, ld, dtype=torch.float32, device=g.device)
+                native.conv_wgrad(saved_x, g, dwp, 1, 1)
+                dw = dwp.view(K, ld)[:, :R * S * C].reshape(K, R, S, C)
+            elif target is not None:
+                # accumulate straight into the (pre-zeroed) flat gradient buffer: no temporary, no add kernel
+                native.conv_wgrad(saved_x, g, target, R, S, stride=stride, pad_h=pt, pad_w=pl)
+            else:
+                dw = torch.zeros(K, R, S, C, dtype=torch.float32, device=g.device)
+                native.conv_wgrad(saved_x, g, dw, R, S, stride=stride, pad_h=pt, pad_w=pl)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(K, dtype=torch.float32, device=g.device)
+            native.colsum_bf16(g.view(-1, K), N * P * Q, K, db)
+        return dx, dw, db, None, None
+
+
+def conv2d(x, kernel, bias, stride, pads):
+    return _Conv2d.apply(x, kernel, bias, int(stride), tuple(int(v) for v in pads))
+
+
+def conv2d_supported(x, kernel, strides, dilation, groups, pads=(0, 0, 0, 0)):
+    K, R, S, C = kernel.shape
+    if x.dim() != 4 or tuple(dilation) != (1, 1) or groups != 1 or strides[0] != strides[1] or K % 8:
+        return False
+    if C % 8:
+        # the input layer: goes through the patch matrix (one symmetric padding value), never needs an input gradient
+        return C * R * S <= 512 and len(set(pads)) == 1 and not x.requires_grad
+    return strides[0] == 1 or (R == 1 and S == 1)
+
+
+class _BatchNorm(torch.autograd.Function):
+    """Training-mode BatchNormalization over the last axis (+ residual) (+ ReLU) of a channels-last bf16 tensor."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, residual, relu, eps, momentum, training):
+        xb = _bf16(x)
+        C = xb.shape[-1]
+        M = xb.numel() // C
+        dev = x.device
+        res = _bf16(residual) if residual is not None else None
+        y = torch.empty_like(xb)
+        g32 = gamma.detach().float() if gamma is not None else None
+        b32 = beta.detach().float() if beta is not None else None
+        if training:
+            sums = torch.zeros(2, C, dtype=torch.float32, device=dev)
+            mean = torch.empty(C, dtype=torch.float32, device=dev)
+            rstd = torch.empty(C, dtype=torch.float32, device=dev)
+            native.bn_stats(xb, M, C, sums)
+            native.bn_finalize(sums, M, C, eps, momentum, mean, rstd, running_mean, running_var)
+        else:
+            sums = None
+            mean = running_mean.detach().float()
+            rstd = torch.rsqrt(running_var.detach().float() + eps)
+        native.bn_apply(xb, M, C, mean, rstd, g32, b32, res, relu, y)
+        ctx.save_for_backward(xb, y if relu else None, mean, rstd, g32, sums)
+        ctx.meta = (x.dtype, relu, residual is not None, M, C, gamma is not None, beta is not None, training)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xb, y, mean, rstd, g32, sums = ctx.saved_tensors
+        x_dtype, relu, has_res, M, C, has_gamma, has_beta, training = ctx.meta
+        g = _bf16(gy)
+        torch.cuda.set_device(g.device)
+        if sums is None:
+            sums = torch.zeros(2, C, dtype=torch.float32, device=g.device)  # (finalize leaves the forward's buffer zeroed)
+        native.bn_bwd_reduce(g, y, xb, M, C, mean, rstd, relu, sums)
+        dx = torch.empty_like(xb)
+        dres = torch.empty_like(xb) if has_res else None
+        if not training:
+            raise NotImplementedError("gradient through inference-mode BatchNormalization")
+        native.bn_bwd_apply(g, y, xb, M, C, mean, rstd, g32, sums, relu, dx, dres)
+        dgamma = sums[1].clone() if has_gamma else None
+        dbeta = sums[0].clone() if has_beta else None
+        return (dx if x_dtype == torch.bfloat16 else dx.to(x_dtype)), dgamma, dbeta, None, None, dres, None, None, None, None
+
+
+def batch_norm(x, gamma, beta, running_mean, running_var, eps, momentum, training, residual=None, relu=False):
+    return _BatchNorm.apply(x, gamma, beta, running_mean, running_var, residual, bool(relu), float(eps), float(momentum),
+                            bool(training))
+
+
+class _Linear(torch.autograd.Function):
+    """``y = x W^T + b`` on the tcgen05 GEMM: ``x`` ``[..., in]``, ``weight`` fp32 ``[out, in]`` (the Dense layer's own layout)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        out_dim, in_dim = weight.shape
+        x2 = _bf16(x.reshape(-1, in_dim))
+        wb = weight.detach().to(torch.bfloat16)
+        m = x2.shape[0]
+        ldo = (out_dim + 7) // 8 * 8
+        y = torch.empty(m, ldo, dtype=torch.bfloat16, device=x.device)
+        native.gemm(x2, wb, m, out_dim, in_dim, out_bf16=y, ldo=ldo, bias=bias.detach().float() if bias is not None else None)
+        ctx.save_for_backward(x2, wb)
+        ctx.meta = (x.shape, x.dtype, bias is not None, ldo)
+        return y[:, :out_dim].reshape(*x.shape[:-1], out_dim)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x2, wb = ctx.saved_tensors
+        x_shape, x_dtype, has_bias, ldo = ctx.meta
+        out_dim, in_dim = wb.shape
+        m = x2.shape[0]
+        torch.cuda.set_device(gy.device)
+        g = torch.zeros(m, ldo, dtype=torch.bfloat16, device=gy.device)
+        g[:, :out_dim] = gy.reshape(m, out_dim)
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dxb = torch.empty(m, in_dim, dtype=torch.bfloat16, device=gy.device)
+            native.gemm(g, wb, m, in_dim, out_dim, b_mn=True, lda=ldo, out_bf16=dxb)
+            dx = dxb.reshape(x_shape).to(x_dtype)
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(out_dim, in_dim, dtype=torch.float32, device=gy.device)
+            native.gemm(g, x2, out_dim, in_dim, m, a_mn=True, b_mn=True, lda=ldo, out_f32=dw)
+        if has_bias and ctx.needs_input_grad[2]:
+            db = torch.empty(out_dim, dtype=torch.float32, device=gy.device)
+            native.colsum_bf16(g, m, out_dim, db, ld=ldo)
+        return dx, dw, db
+
+
+def linear(x, weight, bias):
+    return _Linear.apply(x, weight, bias)
+
+
+def linear_supported(weight):
+    return weight.shape[1] % 8 == 0

@@ -25,15 +25,15 @@ def enabled():
 
 def eligible(x, kernel, strides, dilation, groups, padding_applied):
     """CUDA tensor, bf16 compute requested by the caller, 1x1 / stride 1 / dense, channel counts multiples of 8."""
-    return (x.is_cuda and kernel.shape[2] == 1 and kernel.shape[3] == 1 and tuple(strides) == (1, 1)
+    return (x.is_cuda and kernel.shape[1] == 1 and kernel.shape[2] == 1 and tuple(strides) == (1, 1)
             and tuple(dilation) == (1, 1) and groups == 1 and not padding_applied
-            and kernel.shape[0] % 8 == 0 and kernel.shape[1] % 8 == 0 and native.available())
+            and kernel.shape[0] % 8 == 0 and kernel.shape[3] % 8 == 0 and native.available())
 
 
 class _Conv1x1(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, kernel, bias):
-        cout, cin = kernel.shape[0], kernel.shape[1]
+        cout, cin = kernel.shape[0], kernel.shape[3]
         x2 = x.reshape(-1, cin)
         xb = x2 if x2.dtype == torch.bfloat16 else x2.to(torch.bfloat16)
         xb = xb.contiguous()

@@ -98,6 +98,22 @@ class PsStore(ctypes.Structure):
                 ('world', c_int32), ('rank', c_int32), ('nspans', c_int32), ('spans', PsSpan * PS_MAX_SPANS)]
 
 
+class ConvArgs(ctypes.Structure):
+    _fields_ = [('inp', c_void_p), ('N', c_int32), ('H', c_int32), ('W', c_int32), ('C', c_int32),
+                ('w', c_void_p), ('K', c_int32), ('R', c_int32), ('S', c_int32),
+                ('w_mn', c_int32), ('flip_taps', c_int32), ('stride', c_int32), ('pad_h', c_int32), ('pad_w', c_int32),
+                ('P', c_int32), ('Q', c_int32), ('pn', c_int32), ('ph', c_int32), ('pw', c_int32),
+                ('out', c_void_p), ('OH', c_int32), ('OW', c_int32), ('os', c_int32), ('bias', c_void_p),
+                ('block_n', c_int32)]
+
+
+class ConvWgradArgs(ctypes.Structure):
+    _fields_ = [('x', c_void_p), ('N', c_int32), ('H', c_int32), ('W', c_int32), ('C', c_int32),
+                ('dy', c_void_p), ('P', c_int32), ('Q', c_int32), ('K', c_int32),
+                ('R', c_int32), ('S', c_int32), ('stride', c_int32), ('pad_h', c_int32), ('pad_w', c_int32),
+                ('pn', c_int32), ('ph', c_int32), ('pw', c_int32), ('dw', c_void_p), ('splits', c_int32)]
+
+
 _lib = None
 _lib_lock = threading.Lock()
 
@@ -142,6 +158,18 @@ def load():
         lib.eb_ps_striped_pull.argtypes = [c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_int64, c_int64, c_int32, c_void_p]
         lib.eb_ps_striped_push.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_void_p]
         lib.eb_ps_striped_optimizer_push.argtypes = [c_void_p, c_void_p, c_int32, c_void_p]
+        lib.eb_conv_igemm.argtypes = [c_void_p, c_void_p]
+        lib.eb_conv_wgrad.argtypes = [c_void_p, c_void_p]
+        lib.eb_conv_im2col.argtypes = [c_void_p, c_int32] + [c_int32] * 10 + [c_void_p, c_int32, c_void_p]
+        lib.eb_bn_stats.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p]
+        lib.eb_bn_finalize.argtypes = [c_void_p, c_int64, c_int32, c_float, c_float, c_void_p, c_void_p, c_void_p,
+                                       c_void_p, c_void_p]
+        lib.eb_bn_apply.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_int32, c_void_p, c_void_p]
+        lib.eb_bn_bwd_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32,
+                                         c_void_p, c_void_p]
+        lib.eb_bn_bwd_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p,
+                                        c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
@@ -502,6 +530,86 @@ def ps_striped_optimizer_push(store, kind, n, g32, step, slots=(None, None, None
     a = _optim_args(kind, n, g32, step, slots=slots, apply=False, advance=advance, **hyper)
     _check(require().eb_ps_striped_optimizer_push(ctypes.byref(store), ctypes.byref(a), int(bool(locked)), _stream(g32.device)),
            'eb_ps_striped_optimizer_push')
+
+
+# ------------------------------------------------------------------ convolutions (K9)
+def conv_patch(n, p, q, limit, stride=1):
+    """Output pixels per tile ``(pn, ph, pw)`` with ``pn * ph * pw <= limit`` (and every TMA box edge <= 256 input
+    elements) that wastes the fewest tile rows; among equals the widest rows (longest contiguous TMA runs)."""
+    edge = max(1, 256 // int(stride))
+    best = None
+    for pw in range(min(q, limit, edge), 0, -1):
+        for ph in range(min(p, limit // pw, edge), 0, -1):
+            pn = min(n, limit // (pw * ph), 256)
+            tiles = -(-n // pn) * -(-p // ph) * -(-q // pw)
+            eff = (n * p * q) / float(tiles * limit)
+            if best is None or eff > best[0] + 0.02:
+                best = (eff, pn, ph, pw)
+    return best[1:]
+
+
+def conv_igemm(inp, w, out, P, Q, R, S, stride=1, pad_h=0, pad_w=0, os=1, bias=None, w_mn=False, flip_taps=False,
+               patch=None, block_n=0):
+    """``eb_conv_igemm`` (see ``EbConvArgs``): ``inp`` bf16 ``[N,H,W,C]``, ``out`` bf16 ``[N,OH,OW,K]``; ``w`` is the OHWI
+    kernel ``[K,R,S,C]`` (forward) or, with ``w_mn``, the forward kernel ``[C,R,S,K]`` read N-major (input gradient)."""
+    a = ConvArgs()
+    N, H, W, C = inp.shape
+    K = out.shape[3]
+    a.inp, a.N, a.H, a.W, a.C = inp.data_ptr(), N, H, W, C
+    a.w, a.K, a.R, a.S = w.data_ptr(), K, int(R), int(S)
+    a.w_mn, a.flip_taps, a.stride, a.pad_h, a.pad_w = int(bool(w_mn)), int(bool(flip_taps)), int(stride), int(pad_h), int(pad_w)
+    a.P, a.Q = int(P), int(Q)
+    a.pn, a.ph, a.pw = patch if patch is not None else conv_patch(N, int(P), int(Q), 128, stride)
+    a.out, a.OH, a.OW, a.os = out.data_ptr(), out.shape[1], out.shape[2], int(os)
+    a.bias = bias.data_ptr() if bias is not None else None
+    a.block_n = int(block_n)
+    _check(require().eb_conv_igemm(ctypes.byref(a), _stream(inp.device)), 'eb_conv_igemm')
+
+
+def conv_wgrad(x, dy, dw, R, S, stride=1, pad_h=0, pad_w=0, patch=None, splits=0):
+    """``dw[K,R,S,C] (fp32) += sum over pixels dy[..., K] (x) x[shifted, C]`` - zero ``dw`` first (``EbConvWgradArgs``)."""
+    a = ConvWgradArgs()
+    N, H, W, C = x.shape
+    _, P, Q, K = dy.shape
+    a.x, a.N, a.H, a.W, a.C = x.data_ptr(), N, H, W, C
+    a.dy, a.P, a.Q, a.K = dy.data_ptr(), P, Q, K
+    a.R, a.S, a.stride, a.pad_h, a.pad_w = int(R), int(S), int(stride), int(pad_h), int(pad_w)
+    a.pn, a.ph, a.pw = patch if patch is not None else conv_patch(N, P, Q, 64, stride)
+    a.dw, a.splits = dw.data_ptr(), int(splits)
+    _check(require().eb_conv_wgrad(ctypes.byref(a), _stream(x.device)), 'eb_conv_wgrad')
+
+
+def conv_im2col(x, R, S, stride, pad, P, Q, out, ld):
+    N, H, W, C = x.shape
+    _check(require().eb_conv_im2col(x.data_ptr(), int(x.dtype == torch.float32), N, H, W, C, int(R), int(S), int(stride),
+                                    int(pad), int(P), int(Q), out.data_ptr(), int(ld), _stream(x.device)), 'eb_conv_im2col')
+
+
+def bn_stats(x, M, C, sums):
+    _check(require().eb_bn_stats(x.data_ptr(), int(M), int(C), sums.data_ptr(), _stream(x.device)), 'eb_bn_stats')
+
+
+def bn_finalize(sums, M, C, eps, momentum, mean, rstd, running_mean=None, running_var=None):
+    _check(require().eb_bn_finalize(sums.data_ptr(), int(M), int(C), float(eps), float(momentum), mean.data_ptr(),
+                                    rstd.data_ptr(), _ptr(running_mean), _ptr(running_var), _stream(sums.device)),
+           'eb_bn_finalize')
+
+
+def bn_apply(x, M, C, mean, rstd, gamma, beta, residual, relu, y):
+    _check(require().eb_bn_apply(x.data_ptr(), int(M), int(C), mean.data_ptr(), rstd.data_ptr(), _ptr(gamma), _ptr(beta),
+                                 _ptr(residual), int(bool(relu)), y.data_ptr(), _stream(x.device)), 'eb_bn_apply')
+
+
+def bn_bwd_reduce(dy, y, x, M, C, mean, rstd, relu, sums):
+    _check(require().eb_bn_bwd_reduce(dy.data_ptr(), _ptr(y), x.data_ptr(), int(M), int(C), mean.data_ptr(),
+                                      rstd.data_ptr(), int(bool(relu)), sums.data_ptr(), _stream(x.device)),
+           'eb_bn_bwd_reduce')
+
+
+def bn_bwd_apply(dy, y, x, M, C, mean, rstd, gamma, sums, relu, dx, dres=None):
+    _check(require().eb_bn_bwd_apply(dy.data_ptr(), _ptr(y), x.data_ptr(), int(M), int(C), mean.data_ptr(), rstd.data_ptr(),
+                                     _ptr(gamma), sums.data_ptr(), int(bool(relu)), dx.data_ptr(), _ptr(dres),
+                                     _stream(x.device)), 'eb_bn_bwd_apply')
 
 
 # ------------------------------------------------------------------ host staging

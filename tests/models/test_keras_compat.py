@@ -193,3 +193,38 @@ def test_resnet50_shape():
     out = m.predict(np.random.rand(2, 64, 64, 3).astype(np.float32))
     assert out.shape == (2, 10) and np.allclose(out.sum(1), 1, atol=1e-4)
     assert zoo.resnet50().count_params() == 25636712  # keras.applications.ResNet50
+
+
+def test_batchnorm_fusion_plan_computes_what_the_separate_layers_compute(monkeypatch):
+    """The executor folds ``BN -> ReLU`` and ``BN -> Add -> ReLU`` (the tail of a residual block) into the
+    BatchNormalization call when nothing else reads the intermediates. Same numbers as layer by layer, in training
+    and in inference mode; a BN whose output IS read elsewhere stays unfused."""
+    import torch
+    from elephas_b200.models import Model
+    from elephas_b200.models.layers import Activation, Add, BatchNormalization, Conv2D, GlobalAveragePooling2D, Input
+    torch.manual_seed(4)
+    inp = Input(shape=(8, 8, 8))
+    short = BatchNormalization(name='bn0')(Conv2D(16, 1, name='c0')(inp))          # read by the Add only: plain BN
+    y = Activation('relu', name='r1')(BatchNormalization(name='bn1')(Conv2D(16, 3, padding='same', name='c1')(inp)))
+    y = BatchNormalization(name='bn2')(Conv2D(16, 1, name='c2')(y))
+    out = Activation('relu', name='r2')(Add(name='add')([short, y]))
+    side = BatchNormalization(name='bn3')(Conv2D(16, 1, name='c3')(out))            # read twice: must not be fused
+    both = Add(name='add2')([Activation('relu', name='r3')(side), side])
+    model = Model(inputs=inp, outputs=Dense(3, name='head')(GlobalAveragePooling2D()(both)))
+    fused, alias = model._fusion_plan()
+    names = {id(l): l.name for l in model.layers}
+    assert {names[k[0]]: v[0] for k, v in fused.items()} == {'bn1': True, 'bn2': True}
+    assert {names[k[0]] for k in alias} == {'r1', 'add', 'r2'}
+    assert [names[v[1][0]] for k, v in fused.items() if names[k[0]] == 'bn2'] == ['bn0']
+    x = torch.randn(5, 8, 8, 8)
+    results = {}
+    for flag in ('1', '0'):
+        monkeypatch.setenv('ELEPHAS_B200_FUSE_BN', flag)
+        state = [w.detach().clone() for w in model.weights]
+        results[flag] = (model(x, training=True).detach().clone(), [w.detach().clone() for w in model.weights])
+        results[flag + 'eval'] = model(x, training=False).detach().clone()
+        for w, s in zip(model.weights, state):
+            w.data.copy_(s)  # the training pass moved the running statistics
+    assert torch.allclose(results['1'][0], results['0'][0], atol=1e-6)
+    assert all(torch.allclose(a, b, atol=1e-6) for a, b in zip(results['1'][1], results['0'][1]))
+    assert torch.allclose(results['1eval'], results['0eval'], atol=1e-6)

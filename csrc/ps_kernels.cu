@@ -5,8 +5,8 @@
 // both from elephas/utils/rwlock.py ("several threads can hold this type of lock" for reading, one for writing).
 // Here the master (fp32) and a bf16 mirror of it are cut into one stripe per rank (EbPsStore, include/elephas_b200.h);
 // a worker's push is ONE kernel whose blocks each take one chunk of one stripe: FIFO ticket -> sequence word odd ->
-// red.global.add.f32 of the negated delta straight into the owner's memory over NVLink -> mirror refresh -> sequence
-// word even -> ticket passed on. A pull takes no lock at all: it copies a chunk between two reads of the chunk's
+// red.global.add.f32 of the negated delta straight into the owner's memory over NVLink -> sequence word even (which
+// also serves the next ticket). A pull takes no lock at all: it copies a chunk between two reads of the chunk's
 // sequence word and repeats the copy when the word was odd or moved (seqlock), so any number of workers read at once
 // and none of them ever holds up a writer. Locks live and die inside a kernel: the holder of a ticket is always a
 // block that is running right now, never a kernel queued behind the one that waits for it.
@@ -106,13 +106,15 @@ __device__ __forceinline__ void for_each_group(const Dev& p, const Work& w, F f)
   }
 }
 
-// FIFO ticket lock of one chunk (thread 0 of the block). Returns the ticket; a waiter that is still not served after
-// kLockTimeoutNs records that in the chunk's status word and goes ahead (the host reports it; nothing hangs).
+// One word per chunk is both the FIFO turn and the sequence lock: S = 2k while k operations have completed and nobody is
+// inside, S = 2t + 1 while the holder of ticket t is inside. Ticket t (atomic increment of the word next to it) waits for
+// S == 2t, stores 2t + 1, works, stores 2t + 2. A waiter that is still not served after kLockTimeoutNs records that in
+// the chunk's status word and goes ahead (the host reports it; nothing hangs). Thread 0 of the block calls these.
 __device__ __forceinline__ uint32_t lock_chunk(uint32_t* lk) {
   const uint32_t ticket = atomicAdd_system(lk + 1, 1u);
   unsigned long long t0 = 0;
   uint32_t spins = 0;
-  while (ld_acquire_sys(lk + 2) != ticket) {
+  while (ld_acquire_sys(lk) != 2u * ticket) {
     if ((++spins & 0x3FFu) == 0) {
       const unsigned long long now = now_ns();
       if (t0 == 0) t0 = now;
@@ -122,29 +124,25 @@ __device__ __forceinline__ uint32_t lock_chunk(uint32_t* lk) {
       }
     }
   }
+  st_relaxed_sys(lk, 2u * ticket + 1u);  // odd: a pull that overlaps from here on will retry
   return ticket;
 }
 
-__device__ __forceinline__ void unlock_chunk(uint32_t* lk, uint32_t ticket) { st_release_sys(lk + 2, ticket + 1u); }
+__device__ __forceinline__ void unlock_chunk(uint32_t* lk, uint32_t ticket) { st_release_sys(lk, 2u * ticket + 2u); }
 
-// Writer side of the chunk's sequence lock, executed by the whole block around its reductions.
+// Writer side, executed by the whole block around its reductions.
 __device__ __forceinline__ void writer_enter(uint32_t* lk, uint32_t (&state)[2]) {
   if (threadIdx.x == 0) {
     state[0] = lock_chunk(lk);
-    state[1] = ld_relaxed_sys(lk);      // only the ticket holder writes this word
-    st_relaxed_sys(lk, state[1] + 1u);  // odd: a pull that overlaps from here on will retry
-    __threadfence_system();             // ... and the word is odd before any reduction of this block lands
+    __threadfence_system();  // the word is odd before any reduction of this block lands
   }
   __syncthreads();
 }
 
 __device__ __forceinline__ void writer_leave(uint32_t* lk, const uint32_t (&state)[2]) {
-  __threadfence_system();  // every thread: my reductions and mirror stores are performed before ...
+  __threadfence_system();  // every thread: my reductions (and mirror stores) are performed before ...
   __syncthreads();
-  if (threadIdx.x == 0) {
-    st_release_sys(lk, state[1] + 2u);  // ... the word becomes even again
-    unlock_chunk(lk, state[0]);
-  }
+  if (threadIdx.x == 0) unlock_chunk(lk, state[0]);  // ... the word becomes even again and the next ticket is served
 }
 
 enum { SRC_F32 = 0, SRC_BF16 = 1, SRC_DIFF = 2 };
@@ -158,6 +156,7 @@ struct PushSrc {
 
 // master[g..g+8) -= d, then the bf16 mirror of the same elements is rewritten from the values read back (same thread,
 // same address: the load observes at least this thread's own reduction). All-zero groups are skipped.
+template <bool MIRROR>
 __device__ __forceinline__ void apply_group(const Dev& p, int owner, long long g, const float (&d)[8]) {
   bool any = false;
 #pragma unroll
@@ -166,6 +165,7 @@ __device__ __forceinline__ void apply_group(const Dev& p, int owner, long long g
   float* m = p.master[owner] + g;
   red_add_v4(m, -d[0], -d[1], -d[2], -d[3]);
   red_add_v4(m + 4, -d[4], -d[5], -d[6], -d[7]);
+  if (!MIRROR) return;
   const uint4 a = ld_sys_v4(m), b = ld_sys_v4(m + 4);
   uint4 o;
   o.x = pack_bf16x2(__uint_as_float(a.x), __uint_as_float(a.y));
@@ -196,7 +196,7 @@ __global__ void __launch_bounds__(kThreads) ps_push_kernel(const Dev p, const Pu
       d[0] = b0.x - a0.x; d[1] = b0.y - a0.y; d[2] = b0.z - a0.z; d[3] = b0.w - a0.w;
       d[4] = b1.x - a1.x; d[5] = b1.y - a1.y; d[6] = b1.z - a1.z; d[7] = b1.w - a1.w;
     }
-    apply_group(p, w.owner, g, d);
+    apply_group<!LOCKED>(p, w.owner, g, d);
   });
   if (LOCKED) writer_leave(w.lock, state);
 }
@@ -222,7 +222,7 @@ __global__ void __launch_bounds__(kThreads) ps_optimizer_push_kernel(const Dev p
       step_quad<KIND>(o, f / 4 + 1, ld4(o.g32, f / 4 + 1), lr_t, lr_adam, st);
       d[4] = st[0]; d[5] = st[1]; d[6] = st[2]; d[7] = st[3];
     }
-    apply_group(p, w.owner, g, d);
+    apply_group<!LOCKED>(p, w.owner, g, d);
   });
   if (LOCKED) writer_leave(w.lock, state);
 }
@@ -234,17 +234,32 @@ struct PullDst {
   long long b16_lo, b16_hi;
 };
 
+// FROM_MASTER: the bf16 destination is converted from the fp32 master (stores whose pushes run under the chunk locks
+// do not maintain the mirror: the read-back it needs would double the time a lock is held); otherwise it is copied from
+// the bf16 mirror (half the NVLink bytes; hogwild stores keep it current for the pull-fused GEMM).
+template <bool FROM_MASTER>
 __device__ __forceinline__ void copy_chunk(const Dev& p, const Work& w, const PullDst& d) {
   for_each_group(p, w, [&](long long f, long long g) {
     // (ranges are multiples of 8 elements: a group is wholly inside or outside)
-    if (d.f32 != nullptr && f >= d.f32_lo && f < d.f32_hi) {
+    const bool want32 = d.f32 != nullptr && f >= d.f32_lo && f < d.f32_hi;
+    const bool want16 = d.b16 != nullptr && f >= d.b16_lo && f < d.b16_hi;
+    if (want32 || (want16 && FROM_MASTER)) {
       const float* m = p.master[w.owner] + g;
       const uint4 a = ld_sys_v4(m), b = ld_sys_v4(m + 4);
-      *reinterpret_cast<uint4*>(d.f32 + f) = a;
-      *reinterpret_cast<uint4*>(d.f32 + f + 4) = b;
+      if (want32) {
+        *reinterpret_cast<uint4*>(d.f32 + f) = a;
+        *reinterpret_cast<uint4*>(d.f32 + f + 4) = b;
+      }
+      if (want16 && FROM_MASTER) {
+        uint4 o;
+        o.x = pack_bf16x2(__uint_as_float(a.x), __uint_as_float(a.y));
+        o.y = pack_bf16x2(__uint_as_float(a.z), __uint_as_float(a.w));
+        o.z = pack_bf16x2(__uint_as_float(b.x), __uint_as_float(b.y));
+        o.w = pack_bf16x2(__uint_as_float(b.z), __uint_as_float(b.w));
+        *reinterpret_cast<uint4*>(d.b16 + f) = o;
+      }
     }
-    if (d.b16 != nullptr && f >= d.b16_lo && f < d.b16_hi)
-      *reinterpret_cast<uint4*>(d.b16 + f) = ld_sys_v4(p.mirror[w.owner] + g);
+    if (want16 && !FROM_MASTER) *reinterpret_cast<uint4*>(d.b16 + f) = ld_sys_v4(p.mirror[w.owner] + g);
   });
 }
 
@@ -256,7 +271,7 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
   Work w;
   if (!block_work(p, w)) return;
   if constexpr (!SEQLOCK) {
-    copy_chunk(p, w, d);
+    copy_chunk<false>(p, w, d);
   } else {
   __shared__ uint32_t sh_seq, sh_again;
   for (int attempt = 0;; ++attempt) {
@@ -264,7 +279,7 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
       __shared__ uint32_t sh_ticket;
       if (threadIdx.x == 0) sh_ticket = lock_chunk(w.lock);
       __syncthreads();
-      copy_chunk(p, w, d);
+      copy_chunk<true>(p, w, d);
       fence_acq_rel_sys();
       __syncthreads();
       if (threadIdx.x == 0) unlock_chunk(w.lock, sh_ticket);
@@ -288,7 +303,7 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
       sh_seq = s0;
     }
     __syncthreads();
-    copy_chunk(p, w, d);
+    copy_chunk<true>(p, w, d);
     fence_acq_rel_sys();  // the data loads above are performed before the sequence word is read again
     __syncthreads();
     if (threadIdx.x == 0) {

@@ -241,16 +241,19 @@ int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, 
  * [flat_off, flat_off + n) and lives at elements [owner_off, owner_off + n) of rank `owner`'s stripe (all three multiples
  * of 64; a Dense kernel is normally one span, so that the pull-fused GEMM, K2, can read it through one tensor map).
  * Every stripe is divided into `chunks` chunks of `chunk_len` elements, each guarded by its own lock record in the owner's
- * `ctrl` array (8 words per chunk: [0] sequence word, [1] next ticket, [2] now serving, [3] watchdog status):
- *   push, locked   (mode='asynchronous'): the block that pushes a chunk takes the chunk's FIFO ticket, makes the sequence
- *                  word odd, applies master -= delta with red.global.add.f32 into the owner's memory, refreshes the bf16
- *                  mirror, makes the sequence word even again and passes the ticket on - all inside one kernel, so a
- *                  lock is only ever held by a running block (elephas/parameter/server.py:117-132,201-210: write lock);
- *   pull, seqlock  (mode='asynchronous'): readers take NO lock: read the sequence word, copy the chunk, read the word again,
- *                  retry when it was odd or has changed (after EB_PS_SEQ_RETRIES failed attempts: take the ticket like a
- *                  writer). Any number of readers proceed at once and never delay a writer - the reference's "several
- *                  threads can hold this type of lock" for reads (elephas/utils/rwlock.py:24-33, server.py:107-115);
- *   unlocked       (mode='hogwild'): neither (server.py:109,120): relaxed red.add / plain loads.
+ * `ctrl` array (8 words per chunk: [0] sequence word S, [1] next ticket, [3] watchdog status). S = 2k when k operations
+ * have completed and nobody is inside, 2t + 1 while the holder of ticket t is inside:
+ *   push, locked   (mode='asynchronous'): the block that pushes a chunk takes a ticket t (FIFO), waits for S == 2t, stores
+ *                  2t + 1, applies master -= delta with red.global.add.f32 into the owner's memory, stores 2t + 2 - all
+ *                  inside one kernel, so a lock is only ever held by a running block, for two NVLink round trips
+ *                  (elephas/parameter/server.py:117-132,201-210: write lock). The bf16 mirror is NOT maintained by
+ *                  locked pushes (its read-back would double the hold time); locked pulls convert from the master;
+ *   pull, seqlock  (mode='asynchronous'): readers take NO lock: read S, copy the chunk, read S again, retry when it was
+ *                  odd or has changed (after EB_PS_SEQ_RETRIES failed attempts: take a ticket like a writer). Any
+ *                  number of readers proceed at once and never delay a writer - the reference's "several threads can
+ *                  hold this type of lock" for reads (elephas/utils/rwlock.py:24-33, server.py:107-115);
+ *   unlocked       (mode='hogwild'): neither (server.py:109,120): relaxed red.add / plain loads; pushes refresh the
+ *                  bf16 mirror of every element they touch, pulls and the pull-fused GEMM (K2) read it.
  * The unit of consistency is the chunk: a seqlock pull never observes a half-applied push inside a chunk. */
 #define EB_PS_MAX_RANKS 8
 #define EB_PS_MAX_SPANS 48
@@ -271,12 +274,14 @@ typedef struct {
   int32_t world, rank, nspans;
   EbPsSpan spans[EB_PS_MAX_SPANS];
 } EbPsStore;
-/* dst_f32[i] = master[i] for flat i in [f32_lo, f32_hi), dst_bf16[i] = mirror[i] for flat i in [b16_lo, b16_hi)
- * (destinations are indexed by FLAT element; either may be NULL). seqlock != 0: validated reads as described above. */
+/* dst_f32[i] = master[i] for flat i in [f32_lo, f32_hi), dst_bf16[i] = bf16 of it for flat i in [b16_lo, b16_hi)
+ * (destinations are indexed by FLAT element; either may be NULL). seqlock != 0: validated reads as described above, bf16
+ * converted from the master; seqlock == 0: bf16 copied from the mirror. */
 int eb_ps_striped_pull(const EbPsStore* store, float* dst_f32, int64_t f32_lo, int64_t f32_hi, void* dst_bf16,
                        int64_t b16_lo, int64_t b16_hi, int32_t seqlock, void* stream);
 /* master -= delta over the whole flat range; exactly one of delta_f32 / delta_bf16 / (before, after) describes the
- * delta (flat indexed). The bf16 mirror of every touched element is refreshed. locked != 0: per-chunk ticket + sequence. */
+ * delta (flat indexed). locked != 0: per-chunk ticket + sequence word; locked == 0: the bf16 mirror of every touched
+ * element is refreshed. */
 int eb_ps_striped_push(const EbPsStore* store, const float* delta_f32, const void* delta_bf16, const float* before,
                        const float* after, int32_t locked, void* stream);
 /* The optimizer step (K10: slots updated from the flat gradient opt->g32, Keras formulas) fused with the push: the step

@@ -32,7 +32,7 @@ static Shape shape_of(long long M, int C) {
 
 static int grid_for(const Shape& s) {
   long long blocks = (s.M + s.slots * 8 - 1) / (s.slots * 8);  // >= 8 pixels per thread before another block pays off
-  const long long cap = static_cast<long long>(num_sms()) * 4;
+  const long long cap = static_cast<long long>(num_sms()) * 8;  // 8 x 256 threads: every SM fully occupied
   if (blocks > cap) blocks = cap;
   return blocks < 1 ? 1 : static_cast<int>(blocks);
 }
@@ -52,10 +52,30 @@ __device__ __forceinline__ void load8(const float* p, float (&f)[8]) {
   f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
 }
 
+// Rows of this thread, kUnroll at a time: `load(m, k)` issues the loads of row m into register set k, `use(k)` consumes
+// them. All loads of a batch are issued before the first use: the kernels are latency-bound otherwise (a thread owns
+// ~40 rows of 16 bytes, one dependent load at a time hides nothing).
+constexpr int kUnroll = 4;
+template <typename Load, typename Use>
+__device__ __forceinline__ void walk_rows(const Shape& s, int slot, Load load, Use use) {
+  const long long stride = static_cast<long long>(gridDim.x) * s.slots;
+  long long m = static_cast<long long>(blockIdx.x) * s.slots + slot;
+  for (; m + (kUnroll - 1) * stride < s.M; m += kUnroll * stride) {
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) load(m + k * stride, k);
+#pragma unroll
+    for (int k = 0; k < kUnroll; ++k) use(m + k * stride, k);
+  }
+  for (; m < s.M; m += stride) {
+    load(m, 0);
+    use(m, 0);
+  }
+}
+
 // Combine the per-thread partial sums (two quantities x 8 channels) of all pixel slots of a channel group, then one
 // atomic per channel: out[0][c] += a, out[1][c] += b.
 __device__ __forceinline__ void block_reduce_pair(const Shape& s, int lane, int slot, int g, float (&a)[8], float (&b)[8],
-                                                  float* out) {
+                                                  float* out_a, float* out_b) {
   __shared__ float sh[kThreads][17];
   __syncthreads();
 #pragma unroll
@@ -72,8 +92,8 @@ __device__ __forceinline__ void block_reduce_pair(const Shape& s, int lane, int 
         ta += sh[k * s.lanes + lane][j];
         tb += sh[k * s.lanes + lane][8 + j];
       }
-      atomicAdd(out + g * 8 + j, ta);
-      atomicAdd(out + s.C + g * 8 + j, tb);
+      atomicAdd(out_a + g * 8 + j, ta);
+      atomicAdd(out_b + g * 8 + j, tb);
     }
   }
 }
@@ -84,14 +104,16 @@ __global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __
     const int g = g0 + lane;
     float a[8] = {0, 0, 0, 0, 0, 0, 0, 0}, b[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (slot < s.slots && g < s.groups) {
-      for (long long m = static_cast<long long>(blockIdx.x) * s.slots + slot; m < s.M; m += static_cast<long long>(gridDim.x) * s.slots) {
-        float f[8];
-        unpack8(ld_nc_u4(x + m * s.C + g * 8), f);
+      uint4 raw[kUnroll];
+      walk_rows(s, slot, [&](long long m, int k) { raw[k] = ld_nc_u4(x + m * s.C + g * 8); },
+                [&](long long, int k) {
+                  float f[8];
+                  unpack8(raw[k], f);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { a[j] += f[j]; b[j] += f[j] * f[j]; }
-      }
+                  for (int j = 0; j < 8; ++j) { a[j] += f[j]; b[j] += f[j] * f[j]; }
+                });
     }
-    block_reduce_pair(s, lane, slot, g, a, b, sums);
+    block_reduce_pair(s, lane, slot, g, a, b, sums, sums + s.C);
   }
 }
 
@@ -131,31 +153,38 @@ apply_kernel(const __nv_bfloat16* __restrict__ x, const Shape s, const float* __
       scale[j] = rs[j] * (gamma ? ga[j] : 1.f);
       shift[j] = (beta ? be[j] : 0.f) - mu[j] * scale[j];
     }
-    for (long long m = static_cast<long long>(blockIdx.x) * s.slots + slot; m < s.M; m += static_cast<long long>(gridDim.x) * s.slots) {
-      const long long off = m * s.C + g * 8;
-      float f[8];
-      unpack8(ld_nc_u4(x + off), f);
+    uint4 rx[kUnroll], rr[kUnroll];
+    walk_rows(s, slot,
+              [&](long long m, int k) {
+                const long long off = m * s.C + g * 8;
+                rx[k] = ld_nc_u4(x + off);
+                if (res != nullptr) rr[k] = ld_nc_u4(res + off);
+              },
+              [&](long long m, int k) {
+                float f[8];
+                unpack8(rx[k], f);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
-      if (res != nullptr) {
-        float r[8];
-        unpack8(ld_nc_u4(res + off), r);
+                for (int j = 0; j < 8; ++j) f[j] = f[j] * scale[j] + shift[j];
+                if (res != nullptr) {
+                  float r[8];
+                  unpack8(rr[k], r);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] += r[j];
-      }
-      if (relu) {
+                  for (int j = 0; j < 8; ++j) f[j] += r[j];
+                }
+                if (relu) {
 #pragma unroll
-        for (int j = 0; j < 8; ++j) f[j] = f[j] > 0.f ? f[j] : 0.f;
-      }
-      st_v4(y + off, pack8(f));
-    }
+                  for (int j = 0; j < 8; ++j) f[j] = f[j] > 0.f ? f[j] : 0.f;
+                }
+                st_v4(y + m * s.C + g * 8, pack8(f));
+              });
   }
 }
 
 // dz = dy * (y > 0) [ReLU]; sums[0][c] += sum dz, sums[1][c] += sum dz * xhat
 __global__ void __launch_bounds__(kThreads)
 bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
-                  const Shape s, const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* sums) {
+                  const Shape s, const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* sum_dz,
+                  float* sum_dzx) {
   const int lane = threadIdx.x % s.lanes, slot = threadIdx.x / s.lanes;
   for (int g0 = 0; g0 < s.groups; g0 += s.lanes) {
     const int g = g0 + lane;
@@ -164,32 +193,40 @@ bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
       float mu[8], rs[8];
       load8(mean + g * 8, mu);
       load8(rstd + g * 8, rs);
-      for (long long m = static_cast<long long>(blockIdx.x) * s.slots + slot; m < s.M; m += static_cast<long long>(gridDim.x) * s.slots) {
-        const long long off = m * s.C + g * 8;
-        float d[8], xv[8];
-        unpack8(ld_nc_u4(dy + off), d);
-        unpack8(ld_nc_u4(x + off), xv);
-        if (relu) {
-          float yv[8];
-          unpack8(ld_nc_u4(y + off), yv);
+      uint4 rd[kUnroll], rx[kUnroll], ry[kUnroll];
+      walk_rows(s, slot,
+                [&](long long m, int k) {
+                  const long long off = m * s.C + g * 8;
+                  rd[k] = ld_nc_u4(dy + off);
+                  rx[k] = ld_nc_u4(x + off);
+                  if (relu) ry[k] = ld_nc_u4(y + off);
+                },
+                [&](long long, int k) {
+                  float d[8], xv[8];
+                  unpack8(rd[k], d);
+                  unpack8(rx[k], xv);
+                  if (relu) {
+                    float yv[8];
+                    unpack8(ry[k], yv);
 #pragma unroll
-          for (int j = 0; j < 8; ++j) d[j] = yv[j] > 0.f ? d[j] : 0.f;
-        }
+                    for (int j = 0; j < 8; ++j) d[j] = yv[j] > 0.f ? d[j] : 0.f;
+                  }
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          a[j] += d[j];
-          b[j] += d[j] * (xv[j] - mu[j]) * rs[j];
-        }
-      }
+                  for (int j = 0; j < 8; ++j) {
+                    a[j] += d[j];
+                    b[j] += d[j] * (xv[j] - mu[j]) * rs[j];
+                  }
+                });
     }
-    block_reduce_pair(s, lane, slot, g, a, b, sums);
+    block_reduce_pair(s, lane, slot, g, a, b, sum_dz, sum_dzx);
   }
 }
 
 __global__ void __launch_bounds__(kThreads)
 bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
                  const Shape s, const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
-                 const float* __restrict__ sums, int relu, __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres) {
+                 const float* __restrict__ sum_dz, const float* __restrict__ sum_dzx, int relu, __nv_bfloat16* __restrict__ dx,
+                 __nv_bfloat16* __restrict__ dres) {
   const int lane = threadIdx.x % s.lanes, slot = threadIdx.x / s.lanes;
   if (slot >= s.slots) return;
   const float inv = 1.f / static_cast<float>(s.M);
@@ -198,52 +235,67 @@ bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __re
     load8(mean + g * 8, mu);
     load8(rstd + g * 8, rs);
     if (gamma) load8(gamma + g * 8, ga);
-    load8(sums + g * 8, sa);
-    load8(sums + s.C + g * 8, sb);
+    load8(sum_dz + g * 8, sa);
+    load8(sum_dzx + g * 8, sb);
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       sa[j] *= inv;
       sb[j] *= inv;
       ga[j] = rs[j] * (gamma ? ga[j] : 1.f);
     }
-    for (long long m = static_cast<long long>(blockIdx.x) * s.slots + slot; m < s.M; m += static_cast<long long>(gridDim.x) * s.slots) {
-      const long long off = m * s.C + g * 8;
-      float d[8], xv[8];
-      unpack8(ld_nc_u4(dy + off), d);
-      unpack8(ld_nc_u4(x + off), xv);
-      if (relu) {
-        float yv[8];
-        unpack8(ld_nc_u4(y + off), yv);
+    uint4 rd[kUnroll], rx[kUnroll], ry[kUnroll];
+    walk_rows(s, slot,
+              [&](long long m, int k) {
+                const long long off = m * s.C + g * 8;
+                rd[k] = ld_nc_u4(dy + off);
+                rx[k] = ld_nc_u4(x + off);
+                if (relu) ry[k] = ld_nc_u4(y + off);
+              },
+              [&](long long m, int k) {
+                const long long off = m * s.C + g * 8;
+                float d[8], xv[8];
+                unpack8(rd[k], d);
+                unpack8(rx[k], xv);
+                if (relu) {
+                  float yv[8];
+                  unpack8(ry[k], yv);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) d[j] = yv[j] > 0.f ? d[j] : 0.f;
-      }
-      if (dres != nullptr) st_v4(dres + off, pack8(d));
-      float o[8];
+                  for (int j = 0; j < 8; ++j) d[j] = yv[j] > 0.f ? d[j] : 0.f;
+                }
+                if (dres != nullptr) st_v4(dres + off, pack8(d));
+                float o[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) o[j] = ga[j] * (d[j] - sa[j] - (xv[j] - mu[j]) * rs[j] * sb[j]);
-      st_v4(dx + off, pack8(o));
-    }
+                for (int j = 0; j < 8; ++j) o[j] = ga[j] * (d[j] - sa[j] - (xv[j] - mu[j]) * rs[j] * sb[j]);
+                st_v4(dx + off, pack8(o));
+              });
   }
 }
 
-// patch matrix of the input layer: one thread per output element pair is plenty (the matrix is small)
+// patch matrix of the input layer: a thread builds 8 consecutive columns of one pixel's row (one 16-byte store)
 template <typename T>
 __global__ void __launch_bounds__(256)
 im2col_kernel(const T* __restrict__ x, int N, int H, int W, int C, int R, int S, int stride, int pad, int P, int Q,
               __nv_bfloat16* __restrict__ out, int ld) {
-  const long long total = static_cast<long long>(N) * P * Q * ld;
-  const int kvalid = R * S * C;
+  const int groups = ld / 8, kvalid = R * S * C;
+  const long long total = static_cast<long long>(N) * P * Q * groups;
   for (long long i = blockIdx.x * 256ll + threadIdx.x; i < total; i += static_cast<long long>(gridDim.x) * 256) {
-    const int col = static_cast<int>(i % ld);
-    const long long pix = i / ld;
-    float v = 0.f;
-    if (col < kvalid) {
-      const int c = col % C, tap = col / C, s = tap % S, r = tap / S;
-      const int q = static_cast<int>(pix % Q), p = static_cast<int>((pix / Q) % P), n = static_cast<int>(pix / (static_cast<long long>(Q) * P));
-      const int h = p * stride - pad + r, w = q * stride - pad + s;
-      if (h >= 0 && h < H && w >= 0 && w < W) v = static_cast<float>(x[((static_cast<long long>(n) * H + h) * W + w) * C + c]);
+    const int grp = static_cast<int>(i % groups);
+    const long long pix = i / groups;
+    const int q = static_cast<int>(pix % Q), p = static_cast<int>((pix / Q) % P), n = static_cast<int>(pix / (static_cast<long long>(Q) * P));
+    const T* img = x + static_cast<long long>(n) * H * W * C;
+    float v[8];
+    int col = grp * 8, tap = col / C, c = col - tap * C;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      v[j] = 0.f;
+      if (col + j < kvalid) {
+        const int r = tap / S, sx = tap - r * S;
+        const int h = p * stride - pad + r, w = q * stride - pad + sx;
+        if (h >= 0 && h < H && w >= 0 && w < W) v[j] = static_cast<float>(img[(static_cast<long long>(h) * W + w) * C + c]);
+      }
+      if (++c == C) { c = 0; ++tap; }
     }
-    out[i] = __float2bfloat16_rn(v);
+    st_v4(out + pix * ld + grp * 8, pack8(v));
   }
 }
 
@@ -289,26 +341,26 @@ extern "C" int eb_bn_apply(const void* x, int64_t M, int32_t C, const float* mea
 }
 
 extern "C" int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                                const float* rstd, int32_t relu, float* sums, void* stream) {
+                                const float* rstd, int32_t relu, float* sum_dz, float* sum_dzx, void* stream) {
   if (bn::check("eb_bn_bwd_reduce", x, M, C)) return 1;
   if (relu && y == nullptr) return fail("eb_bn_bwd_reduce: the ReLU mask needs the forward output");
   const bn::Shape s = bn::shape_of(M, C);
   bn::bwd_reduce_kernel<<<bn::grid_for(s), bn::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(x), s, mean,
-      rstd, relu, sums);
+      rstd, relu, sum_dz, sum_dzx);
   EB_LAUNCH_OK("bn_bwd_reduce_kernel");
   return 0;
 }
 
 extern "C" int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                               const float* rstd, const float* gamma, const float* sums, int32_t relu, void* dx, void* dres,
-                               void* stream) {
+                               const float* rstd, const float* gamma, const float* sum_dz, const float* sum_dzx, int32_t relu,
+                               void* dx, void* dres, void* stream) {
   if (bn::check("eb_bn_bwd_apply", x, M, C)) return 1;
   if (relu && y == nullptr) return fail("eb_bn_bwd_apply: the ReLU mask needs the forward output");
   const bn::Shape s = bn::shape_of(M, C);
   bn::bwd_apply_kernel<<<bn::grid_for(s), bn::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(x), s, mean,
-      rstd, gamma, sums, relu, static_cast<__nv_bfloat16*>(dx), static_cast<__nv_bfloat16*>(dres));
+      rstd, gamma, sum_dz, sum_dzx, relu, static_cast<__nv_bfloat16*>(dx), static_cast<__nv_bfloat16*>(dres));
   EB_LAUNCH_OK("bn_bwd_apply_kernel");
   return 0;
 }
@@ -316,8 +368,8 @@ extern "C" int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int
 extern "C" int eb_conv_im2col(const void* x, int32_t x_is_f32, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R,
                               int32_t S, int32_t stride, int32_t pad, int32_t P, int32_t Q, void* out_bf16, int32_t ld,
                               void* stream) {
-  if (N <= 0 || P <= 0 || Q <= 0 || ld < R * S * C) return fail("eb_conv_im2col: bad geometry");
-  const long long total = static_cast<long long>(N) * P * Q * ld;
+  if (N <= 0 || P <= 0 || Q <= 0 || ld < R * S * C || (ld % 8)) return fail("eb_conv_im2col: bad geometry (ld must be a multiple of 8 and >= R*S*C)");
+  const long long total = static_cast<long long>(N) * P * Q * (ld / 8);
   long long blocks = (total + 255) / 256;
   const long long cap = static_cast<long long>(num_sms()) * 16;
   if (blocks > cap) blocks = cap;

@@ -67,11 +67,16 @@ class _Conv2d(torch.autograd.Function):
             wpad.view(K, ld)[:, :R * S * C] = wb.view(K, R * S * C)
             native.conv_igemm(cols, wpad, y, P, Q, 1, 1, bias=b32)
             ctx.save_for_backward(cols, wpad)
+        elif R == 1 and S == 1 and stride == 1 and not any(pads):
+            # a 1x1 / stride-1 convolution IS the GEMM [pixels, C] x [K, C]^T: the clustered CTA-pair kernel of the Dense
+            # engine (K1, B tiles multicast across the cluster) serves it without any patch logic
+            native.gemm(xb.view(-1, C), wb.view(K, C), N * H * W, K, C, out_bf16=y.view(-1, K), bias=b32)
+            ctx.save_for_backward(xb, wb)
         else:
             native.conv_igemm(xb, wb, y, P, Q, R, S, stride=stride, pad_h=pt, pad_w=pl, bias=b32)
             ctx.save_for_backward(xb, wb)
         ctx.geom = (x.shape, x.dtype, tuple(kernel.shape), stride, pads, P, Q, small_c, bias is not None)
-        ctx.kernel_param = kernel
+        ctx.kernel_param, ctx.bias_param = kernel, bias
         return y
 
     @staticmethod
@@ -86,7 +91,10 @@ class _Conv2d(torch.autograd.Function):
         torch.cuda.set_device(g.device)  # autograd's worker thread: the TMA descriptor encoder needs the context
         dx = dw = db = None
         if ctx.needs_input_grad[0] and not small_c:
-            if stride == 1:
+            if stride == 1 and R == 1 and S == 1 and not any(pads):
+                dxb = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=g.device)
+                native.gemm(g.view(-1, K), wb.view(K, C), N * H * W, C, K, b_mn=True, out_bf16=dxb.view(-1, C))
+            elif stride == 1:
                 dxb = torch.empty(N, H, W, C, dtype=torch.bfloat16, device=g.device)
                 # dx[h] = sum_r dy[h + pad - r] w[r]: a stride-1 convolution of dy with the flipped taps, padding R-1-pad
                 native.conv_igemm(g, wb, dxb, H, W, R, S, stride=1, pad_h=R - 1 - pt, pad_w=S - 1 - pl, w_mn=True,
@@ -98,8 +106,7 @@ class _Conv2d(torch.autograd.Function):
                 raise NotImplementedError("input gradient of a strided %dx%d convolution" % (R, S))
             dx = dxb if x_dtype == torch.bfloat16 else dxb.to(x_dtype)
         if ctx.needs_input_grad[1]:
-            target = kernel.grad if (kernel.grad is not None and kernel.grad.is_contiguous() and not small_c
-                                     and kernel.grad.dtype == torch.float32) else None
+            target = None if small_c else _flat_grad(kernel)
             if small_c:
                 ld = saved_x.shape[3]
                 dwp = torch.zeros(K, 1, 1, ld, dtype=torch.float32, device=g.device)
@@ -112,8 +119,12 @@ class _Conv2d(torch.autograd.Function):
                 dw = torch.zeros(K, R, S, C, dtype=torch.float32, device=g.device)
                 native.conv_wgrad(saved_x, g, dw, R, S, stride=stride, pad_h=pt, pad_w=pl)
         if has_bias and ctx.needs_input_grad[2]:
-            db = torch.empty(K, dtype=torch.float32, device=g.device)
-            native.colsum_bf16(g.view(-1, K), N * P * Q, K, db)
+            into = _flat_grad(ctx.bias_param)
+            if into is not None:
+                native.colsum_bf16(g.view(-1, K), N * P * Q, K, into, accumulate=True)
+            else:
+                db = torch.empty(K, dtype=torch.float32, device=g.device)
+                native.colsum_bf16(g.view(-1, K), N * P * Q, K, db)
         return dx, dw, db, None, None
 
 
@@ -131,6 +142,26 @@ def conv2d_supported(x, kernel, strides, dilation, groups, pads=(0, 0, 0, 0)):
     return strides[0] == 1 or (R == 1 and S == 1)
 
 
+_ZERO_SCRATCH = {}
+
+
+def _zeroed_sums(device, C):
+    """``[2, C]`` fp32 scratch for the statistics pass, per device and width. It is all zeros between uses: the finalize
+    kernel clears it after reading, and everything on it is ordered by the stream (one step at a time per device)."""
+    key = (device.index, C, torch.cuda.current_stream(device).cuda_stream)
+    buf = _ZERO_SCRATCH.get(key)
+    if buf is None:
+        buf = _ZERO_SCRATCH[key] = torch.zeros(2, C, dtype=torch.float32, device=device)
+    return buf
+
+
+def _flat_grad(p):
+    """The pre-zeroed slice of the training engine's flat gradient buffer that belongs to ``p`` (``ops/torch_step.py``
+    marks the parameters it manages), or None: then gradients are returned to autograd as tensors."""
+    g = p.grad if p is not None and getattr(p, '_eb_flat_grad', False) else None
+    return g if (g is not None and g.dtype == torch.float32 and g.is_contiguous()) else None
+
+
 class _BatchNorm(torch.autograd.Function):
     """Training-mode BatchNormalization over the last axis (+ residual) (+ ReLU) of a channels-last bf16 tensor."""
 
@@ -142,39 +173,47 @@ class _BatchNorm(torch.autograd.Function):
         dev = x.device
         res = _bf16(residual) if residual is not None else None
         y = torch.empty_like(xb)
-        g32 = gamma.detach().float() if gamma is not None else None
-        b32 = beta.detach().float() if beta is not None else None
+        g32 = gamma.detach() if gamma is not None else None
+        b32 = beta.detach() if beta is not None else None
         if training:
-            sums = torch.zeros(2, C, dtype=torch.float32, device=dev)
+            sums = _zeroed_sums(dev, C)
             mean = torch.empty(C, dtype=torch.float32, device=dev)
             rstd = torch.empty(C, dtype=torch.float32, device=dev)
             native.bn_stats(xb, M, C, sums)
             native.bn_finalize(sums, M, C, eps, momentum, mean, rstd, running_mean, running_var)
         else:
-            sums = None
             mean = running_mean.detach().float()
             rstd = torch.rsqrt(running_var.detach().float() + eps)
         native.bn_apply(xb, M, C, mean, rstd, g32, b32, res, relu, y)
-        ctx.save_for_backward(xb, y if relu else None, mean, rstd, g32, sums)
-        ctx.meta = (x.dtype, relu, residual is not None, M, C, gamma is not None, beta is not None, training)
+        ctx.save_for_backward(xb, y if relu else None, mean, rstd, g32)
+        ctx.meta = (x.dtype, relu, residual is not None, M, C, training)
+        ctx.params = (gamma, beta)
         return y
 
     @staticmethod
     def backward(ctx, gy):
-        xb, y, mean, rstd, g32, sums = ctx.saved_tensors
-        x_dtype, relu, has_res, M, C, has_gamma, has_beta, training = ctx.meta
-        g = _bf16(gy)
-        torch.cuda.set_device(g.device)
-        if sums is None:
-            sums = torch.zeros(2, C, dtype=torch.float32, device=g.device)  # (finalize leaves the forward's buffer zeroed)
-        native.bn_bwd_reduce(g, y, xb, M, C, mean, rstd, relu, sums)
-        dx = torch.empty_like(xb)
-        dres = torch.empty_like(xb) if has_res else None
+        xb, y, mean, rstd, g32 = ctx.saved_tensors
+        x_dtype, relu, has_res, M, C, training = ctx.meta
+        gamma, beta = ctx.params
         if not training:
             raise NotImplementedError("gradient through inference-mode BatchNormalization")
-        native.bn_bwd_apply(g, y, xb, M, C, mean, rstd, g32, sums, relu, dx, dres)
-        dgamma = sums[1].clone() if has_gamma else None
-        dbeta = sums[0].clone() if has_beta else None
+        g = _bf16(gy)
+        torch.cuda.set_device(g.device)
+        # d beta = sum dz and d gamma = sum dz * xhat are exactly the two reductions the input gradient needs: when the
+        # training engine owns the (zeroed) gradient buffers they are accumulated there directly and read back from there
+        dgamma_buf, dbeta_buf = _flat_grad(gamma), _flat_grad(beta)
+        direct = dgamma_buf is not None and dbeta_buf is not None
+        if direct:
+            sum_dz, sum_dzx = dbeta_buf, dgamma_buf
+        else:
+            both = torch.zeros(2, C, dtype=torch.float32, device=g.device)
+            sum_dz, sum_dzx = both[0], both[1]
+        native.bn_bwd_reduce(g, y, xb, M, C, mean, rstd, relu, sum_dz, sum_dzx)
+        dx = torch.empty_like(xb)
+        dres = torch.empty_like(xb) if has_res else None
+        native.bn_bwd_apply(g, y, xb, M, C, mean, rstd, g32, sum_dz, sum_dzx, relu, dx, dres)
+        dgamma = None if (direct or gamma is None) else sum_dzx
+        dbeta = None if (direct or beta is None) else sum_dz
         return (dx if x_dtype == torch.bfloat16 else dx.to(x_dtype)), dgamma, dbeta, None, None, dres, None, None, None, None
 
 

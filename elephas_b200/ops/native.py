@@ -167,9 +167,9 @@ def load():
         lib.eb_bn_apply.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_int32, c_void_p, c_void_p]
         lib.eb_bn_bwd_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32,
-                                         c_void_p, c_void_p]
+                                         c_void_p, c_void_p, c_void_p]
         lib.eb_bn_bwd_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p,
-                                        c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
+                                        c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
@@ -600,16 +600,16 @@ def bn_apply(x, M, C, mean, rstd, gamma, beta, residual, relu, y):
                                  _ptr(residual), int(bool(relu)), y.data_ptr(), _stream(x.device)), 'eb_bn_apply')
 
 
-def bn_bwd_reduce(dy, y, x, M, C, mean, rstd, relu, sums):
+def bn_bwd_reduce(dy, y, x, M, C, mean, rstd, relu, sum_dz, sum_dzx):
     _check(require().eb_bn_bwd_reduce(dy.data_ptr(), _ptr(y), x.data_ptr(), int(M), int(C), mean.data_ptr(),
-                                      rstd.data_ptr(), int(bool(relu)), sums.data_ptr(), _stream(x.device)),
-           'eb_bn_bwd_reduce')
+                                      rstd.data_ptr(), int(bool(relu)), sum_dz.data_ptr(), sum_dzx.data_ptr(),
+                                      _stream(x.device)), 'eb_bn_bwd_reduce')
 
 
-def bn_bwd_apply(dy, y, x, M, C, mean, rstd, gamma, sums, relu, dx, dres=None):
+def bn_bwd_apply(dy, y, x, M, C, mean, rstd, gamma, sum_dz, sum_dzx, relu, dx, dres=None):
     _check(require().eb_bn_bwd_apply(dy.data_ptr(), _ptr(y), x.data_ptr(), int(M), int(C), mean.data_ptr(), rstd.data_ptr(),
-                                     _ptr(gamma), sums.data_ptr(), int(bool(relu)), dx.data_ptr(), _ptr(dres),
-                                     _stream(x.device)), 'eb_bn_bwd_apply')
+                                     _ptr(gamma), sum_dz.data_ptr(), sum_dzx.data_ptr(), int(bool(relu)), dx.data_ptr(),
+                                     _ptr(dres), _stream(x.device)), 'eb_bn_bwd_apply')
 
 
 # ------------------------------------------------------------------ host staging

@@ -56,6 +56,7 @@ class TorchStepEngine:
                 view.copy_(p)
                 p.data = view                                   # the model now trains inside the flat buffer
                 p.grad = self.g32[off:off + p.numel()].view(p.shape)   # autograd accumulates in place
+                p._eb_flat_grad = True  # native ops may add their parameter gradients straight into this (zeroed) view
         self.step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.stats = torch.zeros(8, dtype=torch.float64, device=dev)   # [0] loss sum, [1..4] metric sums, [7] rows
         self.slots = [None, None, None]

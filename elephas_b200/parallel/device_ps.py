@@ -11,17 +11,22 @@ the vector tail; with N ranks the pushes and pulls of N workers therefore land o
 sets of NVLink ports.
 
 * **push** (``client.update_parameters``, ``server.py:117-132,201-210``): ONE kernel; the block that
-  serves a chunk takes the chunk's FIFO ticket, marks the chunk's sequence word odd, applies
-  ``master -= delta`` with ``red.global.add.f32`` straight into the owner's memory, refreshes the bf16
-  mirror, marks the word even and passes the ticket on. The delta can be given (fp32 / bf16), formed as
-  ``before - after`` on the fly, or - ``optimizer_push`` - be the optimizer step itself, computed from
-  gradient and slots in registers and never written to memory.
+  serves a chunk takes a FIFO ticket *t*, waits until the chunk's sequence word reads ``2t``, stores
+  ``2t + 1`` (odd = a writer is inside), applies ``master -= delta`` with ``red.global.add.f32`` straight into
+  the owner's memory and stores ``2t + 2`` - which both ends the write and serves the next ticket. A lock is
+  held for two NVLink round trips. The delta can be given (fp32 / bf16), formed as ``before - after`` on
+  the fly, or - ``optimizer_push`` - be the optimizer step itself, computed from gradient and slots in
+  registers and never written to memory.
 * **pull** (``client.get_parameters``, ``server.py:107-115,212-218``): readers take **no lock**. In
   ``mode='asynchronous'`` a chunk is copied between two reads of its sequence word and copied again when
-  the word was odd or moved (seqlock; after a few failed attempts the reader queues for the ticket like a
+  the word was odd or moved (seqlock; after a few failed attempts the reader queues for a ticket like a
   writer, which bounds its wait). Any number of workers read at once and never delay a writer - the
-  device-side form of the reference's reader/writer lock (``utils/rwlock.py:24-48``).
-* ``mode='hogwild'`` skips ticket and sequence word (``server.py:109,120``): relaxed ``red.add``, plain loads.
+  device-side form of the reference's reader/writer lock (``utils/rwlock.py:24-48``). bf16 destinations
+  are converted from the fp32 master on the fly.
+* ``mode='hogwild'`` skips ticket and sequence word (``server.py:109,120``): relaxed ``red.add``, plain
+  loads. Only here do pushes also refresh the bf16 mirror (read back, round, store), because only here is
+  it read: by bf16 pulls and by the pull-fused GEMM (K2), whose TMA loads fetch weight tiles from the
+  owner's mirror. Under the locks that read-back would double the time a lock is held.
 
 Consistency unit: the **chunk** (at least 8192 elements, at most 64 chunks per stripe). A seqlock pull
 never sees a half-applied push inside a chunk, and pushes are element-wise atomic in every mode, so no
@@ -228,7 +233,8 @@ class DeviceStore:
 
     # ---------------------------------------------------------- flat, on device
     def pull_into(self, dst_flat, dst_bf16=None, f32_range=None, b16_range=None):
-        """``dst_flat <- master`` and / or ``dst_bf16 <- bf16 mirror`` (flat indexed; ranges default to everything)."""
+        """``dst_flat <- master`` and / or ``dst_bf16 <- bf16(master)`` (flat indexed; ranges default to everything;
+        hogwild stores serve the bf16 copy from their mirror)."""
         if self.mem is not None:
             from ..ops import native
             native.ps_striped_pull(self.args, dst_flat, f32_range, dst_bf16, b16_range, seqlock=self.locked,

@@ -384,8 +384,9 @@ int eb_conv_im2col(const void* x, int32_t x_is_f32, int32_t N, int32_t H, int32_
  *   eb_bn_finalize    mean, rstd = 1/sqrt(var + eps) from sums; running statistics updated with `momentum` (Keras:
  *                     running = running * momentum + batch * (1 - momentum); unbiased batch variance), sums re-zeroed
  *   eb_bn_apply       y = act((x - mean) * rstd * gamma + beta [+ residual]),  act = ReLU when relu != 0
- *   eb_bn_bwd_reduce  dz = dy * (y > 0 if relu);  sums[0][c] += sum dz, sums[1][c] += sum dz * xhat
- *   eb_bn_bwd_apply   dx = gamma * rstd * (dz - sums[0]/M - xhat * sums[1]/M); dres = dz when requested
+ *   eb_bn_bwd_reduce  dz = dy * (y > 0 if relu);  sum_dz[c] += sum dz (= d beta), sum_dzx[c] += sum dz * xhat (= d gamma):
+ *                     the two vectors may be the gradient buffers of beta and gamma themselves (zeroed for the step)
+ *   eb_bn_bwd_apply   dx = gamma * rstd * (dz - sum_dz/M - xhat * sum_dzx/M); dres = dz when requested
  * Reference: Keras BatchNormalization / Activation / Add layers inside model.fit (elephas/worker.py:42). */
 int eb_bn_stats(const void* x, int64_t M, int32_t C, float* sums, void* stream);
 int eb_bn_finalize(float* sums, int64_t M, int32_t C, float eps, float momentum, float* mean, float* rstd,
@@ -393,10 +394,10 @@ int eb_bn_finalize(float* sums, int64_t M, int32_t C, float eps, float momentum,
 int eb_bn_apply(const void* x, int64_t M, int32_t C, const float* mean, const float* rstd, const float* gamma,
                 const float* beta, const void* residual, int32_t relu, void* y, void* stream);
 int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                     const float* rstd, int32_t relu, float* sums, void* stream);
+                     const float* rstd, int32_t relu, float* sum_dz, float* sum_dzx, void* stream);
 int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                    const float* rstd, const float* gamma, const float* sums, int32_t relu, void* dx, void* dres,
-                    void* stream);
+                    const float* rstd, const float* gamma, const float* sum_dz, const float* sum_dzx, int32_t relu,
+                    void* dx, void* dres, void* stream);
 
 /* ------------------------------------------------------------ host side of the input pipeline
  * dst[r][0..cols) = bf16(src[r][0..cols)) (round to nearest even, bit-identical to the device cast), padding columns

@@ -61,6 +61,7 @@ def test_weight_gradient_accumulates_into_an_existing_grad_buffer():
     x = _rounded(2, 10, 10, 32, seed=5)
     w = _rounded(64, 3, 3, 32, scale=0.1, seed=6).requires_grad_(True)
     w.grad = torch.full_like(w, 0.5)
+    w._eb_flat_grad = True  # what ops/torch_step.py sets on the parameters whose gradient views it owns
     with torch.autocast('cuda', dtype=torch.bfloat16):
         y = cnn.conv2d(x, w, None, 1, (1, 1, 1, 1))
     g = _rounded(*y.shape, seed=7)

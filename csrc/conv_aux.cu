@@ -30,9 +30,10 @@ static Shape shape_of(long long M, int C) {
   return s;
 }
 
-static int grid_for(const Shape& s) {
+static int grid_for(const Shape& s, long long max_blocks = 0) {
   long long blocks = (s.M + s.slots * 8 - 1) / (s.slots * 8);  // >= 8 pixels per thread before another block pays off
-  const long long cap = static_cast<long long>(num_sms()) * 8;  // 8 x 256 threads: every SM fully occupied
+  long long cap = static_cast<long long>(num_sms()) * 8;  // 8 x 256 threads: every SM fully occupied
+  if (max_blocks > 0 && max_blocks < cap) cap = max_blocks;  // (reductions: one row of partial sums per block)
   if (blocks > cap) blocks = cap;
   return blocks < 1 ? 1 : static_cast<int>(blocks);
 }
@@ -72,10 +73,12 @@ __device__ __forceinline__ void walk_rows(const Shape& s, int slot, Load load, U
   }
 }
 
-// Combine the per-thread partial sums (two quantities x 8 channels) of all pixel slots of a channel group, then one
-// atomic per channel: out[0][c] += a, out[1][c] += b.
+// Combine the per-thread partial sums (two quantities x 8 channels) of all pixel slots of a channel group and store the
+// block's totals as row `blockIdx.x` of `partials` ([blocks][2][C]): no atomics (a thousand blocks adding into the same
+// few hundred addresses serialise in the L2), no zeroing, and a fixed summation order - a second, tiny kernel adds the
+// rows up.
 __device__ __forceinline__ void block_reduce_pair(const Shape& s, int lane, int slot, int g, float (&a)[8], float (&b)[8],
-                                                  float* out_a, float* out_b) {
+                                                  float* partials) {
   __shared__ float sh[kThreads][17];
   __syncthreads();
 #pragma unroll
@@ -85,20 +88,43 @@ __device__ __forceinline__ void block_reduce_pair(const Shape& s, int lane, int 
   }
   __syncthreads();
   if (slot == 0 && g < s.groups) {
+    float ta[8], tb[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float ta = 0.f, tb = 0.f;
+      ta[j] = 0.f;
+      tb[j] = 0.f;
       for (int k = 0; k < s.slots; ++k) {
-        ta += sh[k * s.lanes + lane][j];
-        tb += sh[k * s.lanes + lane][8 + j];
+        ta[j] += sh[k * s.lanes + lane][j];
+        tb[j] += sh[k * s.lanes + lane][8 + j];
       }
-      atomicAdd(out_a + g * 8 + j, ta);
-      atomicAdd(out_b + g * 8 + j, tb);
     }
+    float* row = partials + static_cast<long long>(blockIdx.x) * 2 * s.C + g * 8;
+    *reinterpret_cast<float4*>(row) = make_float4(ta[0], ta[1], ta[2], ta[3]);
+    *reinterpret_cast<float4*>(row + 4) = make_float4(ta[4], ta[5], ta[6], ta[7]);
+    *reinterpret_cast<float4*>(row + s.C) = make_float4(tb[0], tb[1], tb[2], tb[3]);
+    *reinterpret_cast<float4*>(row + s.C + 4) = make_float4(tb[4], tb[5], tb[6], tb[7]);
   }
 }
 
-__global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __restrict__ x, const Shape s, float* sums) {
+// totals of column c over the rows of `partials`: a[c] = sum_b partials[b][0][c], b[c] = sum_b partials[b][1][c]
+__device__ __forceinline__ void sum_partials(const float* __restrict__ partials, int nblocks, int C, int c, float& a, float& b) {
+  float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+  int r = 0;
+  for (; r + 1 < nblocks; r += 2) {
+    a0 += partials[(2ll * r) * C + c];
+    b0 += partials[(2ll * r + 1) * C + c];
+    a1 += partials[(2ll * r + 2) * C + c];
+    b1 += partials[(2ll * r + 3) * C + c];
+  }
+  if (r < nblocks) {
+    a0 += partials[(2ll * r) * C + c];
+    b0 += partials[(2ll * r + 1) * C + c];
+  }
+  a = a0 + a1;
+  b = b0 + b1;
+}
+
+__global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __restrict__ x, const Shape s, float* partials) {
   const int lane = threadIdx.x % s.lanes, slot = threadIdx.x / s.lanes;
   for (int g0 = 0; g0 < s.groups; g0 += s.lanes) {  // (one pass unless C > 2048; uniform trip count: barriers inside)
     const int g = g0 + lane;
@@ -113,17 +139,19 @@ __global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __
                   for (int j = 0; j < 8; ++j) { a[j] += f[j]; b[j] += f[j] * f[j]; }
                 });
     }
-    block_reduce_pair(s, lane, slot, g, a, b, sums, sums + s.C);
+    block_reduce_pair(s, lane, slot, g, a, b, partials);
   }
 }
 
-__global__ void finalize_kernel(float* sums, long long M, int C, float eps, float momentum, float* mean, float* rstd,
-                                float* running_mean, float* running_var) {
+__global__ void finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C, float eps, float momentum,
+                                float* mean, float* rstd, float* running_mean, float* running_var) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
+  float sum, sumsq;
+  sum_partials(partials, nblocks, C, c, sum, sumsq);
   const float inv = 1.f / static_cast<float>(M);
-  const float mu = sums[c] * inv;
-  float var = sums[C + c] * inv - mu * mu;
+  const float mu = sum * inv;
+  float var = sumsq * inv - mu * mu;
   var = var > 0.f ? var : 0.f;
   mean[c] = mu;
   rstd[c] = rsqrtf(var + eps);
@@ -132,8 +160,17 @@ __global__ void finalize_kernel(float* sums, long long M, int C, float eps, floa
     const float unbiased = M > 1 ? var * static_cast<float>(M) / static_cast<float>(M - 1) : var;
     running_var[c] = running_var[c] * momentum + unbiased * (1.f - momentum);
   }
-  sums[c] = 0.f;  // ready for the next use without a memset
-  sums[C + c] = 0.f;
+}
+
+// sum_dz[c] (+)= sum over blocks, sum_dzx[c] (+)= ...: one writer per channel (the destinations may be gradient buffers)
+__global__ void bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, float* sum_dz, float* sum_dzx,
+                                    int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a, b;
+  sum_partials(partials, nblocks, C, c, a, b);
+  sum_dz[c] = accumulate ? sum_dz[c] + a : a;
+  sum_dzx[c] = accumulate ? sum_dzx[c] + b : b;
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -183,8 +220,7 @@ apply_kernel(const __nv_bfloat16* __restrict__ x, const Shape s, const float* __
 // dz = dy * (y > 0) [ReLU]; sums[0][c] += sum dz, sums[1][c] += sum dz * xhat
 __global__ void __launch_bounds__(kThreads)
 bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
-                  const Shape s, const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* sum_dz,
-                  float* sum_dzx) {
+                  const Shape s, const float* __restrict__ mean, const float* __restrict__ rstd, int relu, float* partials) {
   const int lane = threadIdx.x % s.lanes, slot = threadIdx.x / s.lanes;
   for (int g0 = 0; g0 < s.groups; g0 += s.lanes) {
     const int g = g0 + lane;
@@ -218,7 +254,7 @@ bwd_reduce_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __r
                   }
                 });
     }
-    block_reduce_pair(s, lane, slot, g, a, b, sum_dz, sum_dzx);
+    block_reduce_pair(s, lane, slot, g, a, b, partials);
   }
 }
 
@@ -311,20 +347,16 @@ static int check(const char* who, const void* x, long long M, int C) {
 
 using namespace eb;
 
-extern "C" int eb_bn_stats(const void* x, int64_t M, int32_t C, float* sums, void* stream) {
+extern "C" int eb_bn_stats(const void* x, int64_t M, int32_t C, float* partials, int32_t max_blocks, float eps,
+                           float momentum, float* mean, float* rstd, float* running_mean, float* running_var, void* stream) {
   if (bn::check("eb_bn_stats", x, M, C)) return 1;
+  if (partials == nullptr || max_blocks < 1) return fail("eb_bn_stats: scratch for the per-block partial sums is required");
   const bn::Shape s = bn::shape_of(M, C);
-  bn::stats_kernel<<<bn::grid_for(s), bn::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-      static_cast<const __nv_bfloat16*>(x), s, sums);
+  const int grid = bn::grid_for(s, max_blocks);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  bn::stats_kernel<<<grid, bn::kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), s, partials);
   EB_LAUNCH_OK("bn_stats_kernel");
-  return 0;
-}
-
-extern "C" int eb_bn_finalize(float* sums, int64_t M, int32_t C, float eps, float momentum, float* mean, float* rstd,
-                              float* running_mean, float* running_var, void* stream) {
-  if (M <= 0 || C <= 0) return fail("eb_bn_finalize: empty tensor");
-  bn::finalize_kernel<<<(C + 127) / 128, 128, 0, static_cast<cudaStream_t>(stream)>>>(sums, M, C, eps, momentum, mean, rstd,
-                                                                                      running_mean, running_var);
+  bn::finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partials, grid, M, C, eps, momentum, mean, rstd, running_mean, running_var);
   EB_LAUNCH_OK("bn_finalize_kernel");
   return 0;
 }
@@ -341,14 +373,20 @@ extern "C" int eb_bn_apply(const void* x, int64_t M, int32_t C, const float* mea
 }
 
 extern "C" int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                                const float* rstd, int32_t relu, float* sum_dz, float* sum_dzx, void* stream) {
+                                const float* rstd, int32_t relu, float* partials, int32_t max_blocks, float* sum_dz,
+                                float* sum_dzx, int32_t accumulate, void* stream) {
   if (bn::check("eb_bn_bwd_reduce", x, M, C)) return 1;
   if (relu && y == nullptr) return fail("eb_bn_bwd_reduce: the ReLU mask needs the forward output");
+  if (partials == nullptr || max_blocks < 1) return fail("eb_bn_bwd_reduce: scratch for the per-block partial sums is required");
   const bn::Shape s = bn::shape_of(M, C);
-  bn::bwd_reduce_kernel<<<bn::grid_for(s), bn::kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+  const int grid = bn::grid_for(s, max_blocks);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  bn::bwd_reduce_kernel<<<grid, bn::kThreads, 0, st>>>(
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(x), s, mean,
-      rstd, relu, sum_dz, sum_dzx);
+      rstd, relu, partials);
   EB_LAUNCH_OK("bn_bwd_reduce_kernel");
+  bn::bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partials, grid, C, sum_dz, sum_dzx, accumulate);
+  EB_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }
 

@@ -142,16 +142,17 @@ def conv2d_supported(x, kernel, strides, dilation, groups, pads=(0, 0, 0, 0)):
     return strides[0] == 1 or (R == 1 and S == 1)
 
 
-_ZERO_SCRATCH = {}
+_PARTIALS = {}
 
 
-def _zeroed_sums(device, C):
-    """``[2, C]`` fp32 scratch for the statistics pass, per device and width. It is all zeros between uses: the finalize
-    kernel clears it after reading, and everything on it is ordered by the stream (one step at a time per device)."""
+def _partials(device, M, C):
+    """fp32 scratch for the per-block partial sums of the two BatchNormalization reductions, per device / stream / width
+    (everything on it is ordered by the stream: one layer at a time). Never needs clearing."""
+    rows = max(1, min(native.BN_MAX_BLOCKS, -(-int(M) // 8)))
     key = (device.index, C, torch.cuda.current_stream(device).cuda_stream)
-    buf = _ZERO_SCRATCH.get(key)
-    if buf is None:
-        buf = _ZERO_SCRATCH[key] = torch.zeros(2, C, dtype=torch.float32, device=device)
+    buf = _PARTIALS.get(key)
+    if buf is None or buf.numel() < rows * 2 * C:
+        buf = _PARTIALS[key] = torch.empty(rows * 2 * C, dtype=torch.float32, device=device)
     return buf
 
 
@@ -176,11 +177,9 @@ class _BatchNorm(torch.autograd.Function):
         g32 = gamma.detach() if gamma is not None else None
         b32 = beta.detach() if beta is not None else None
         if training:
-            sums = _zeroed_sums(dev, C)
             mean = torch.empty(C, dtype=torch.float32, device=dev)
             rstd = torch.empty(C, dtype=torch.float32, device=dev)
-            native.bn_stats(xb, M, C, sums)
-            native.bn_finalize(sums, M, C, eps, momentum, mean, rstd, running_mean, running_var)
+            native.bn_stats(xb, M, C, _partials(dev, M, C), eps, momentum, mean, rstd, running_mean, running_var)
         else:
             mean = running_mean.detach().float()
             rstd = torch.rsqrt(running_var.detach().float() + eps)
@@ -206,9 +205,9 @@ class _BatchNorm(torch.autograd.Function):
         if direct:
             sum_dz, sum_dzx = dbeta_buf, dgamma_buf
         else:
-            both = torch.zeros(2, C, dtype=torch.float32, device=g.device)
+            both = torch.empty(2, C, dtype=torch.float32, device=g.device)
             sum_dz, sum_dzx = both[0], both[1]
-        native.bn_bwd_reduce(g, y, xb, M, C, mean, rstd, relu, sum_dz, sum_dzx)
+        native.bn_bwd_reduce(g, y, xb, M, C, mean, rstd, relu, _partials(g.device, M, C), sum_dz, sum_dzx, accumulate=direct)
         dx = torch.empty_like(xb)
         dres = torch.empty_like(xb) if has_res else None
         native.bn_bwd_apply(g, y, xb, M, C, mean, rstd, g32, sum_dz, sum_dzx, relu, dx, dres)

@@ -161,13 +161,12 @@ def load():
         lib.eb_conv_igemm.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_wgrad.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_im2col.argtypes = [c_void_p, c_int32] + [c_int32] * 10 + [c_void_p, c_int32, c_void_p]
-        lib.eb_bn_stats.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p]
-        lib.eb_bn_finalize.argtypes = [c_void_p, c_int64, c_int32, c_float, c_float, c_void_p, c_void_p, c_void_p,
-                                       c_void_p, c_void_p]
+        lib.eb_bn_stats.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_int32, c_float, c_float, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p]
         lib.eb_bn_apply.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                     c_int32, c_void_p, c_void_p]
         lib.eb_bn_bwd_reduce.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_int32,
-                                         c_void_p, c_void_p, c_void_p]
+                                         c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
         lib.eb_bn_bwd_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
@@ -585,14 +584,14 @@ def conv_im2col(x, R, S, stride, pad, P, Q, out, ld):
                                     int(pad), int(P), int(Q), out.data_ptr(), int(ld), _stream(x.device)), 'eb_conv_im2col')
 
 
-def bn_stats(x, M, C, sums):
-    _check(require().eb_bn_stats(x.data_ptr(), int(M), int(C), sums.data_ptr(), _stream(x.device)), 'eb_bn_stats')
+BN_MAX_BLOCKS = 1184  # rows of the partial-sum scratch: 8 blocks per SM
 
 
-def bn_finalize(sums, M, C, eps, momentum, mean, rstd, running_mean=None, running_var=None):
-    _check(require().eb_bn_finalize(sums.data_ptr(), int(M), int(C), float(eps), float(momentum), mean.data_ptr(),
-                                    rstd.data_ptr(), _ptr(running_mean), _ptr(running_var), _stream(sums.device)),
-           'eb_bn_finalize')
+def bn_stats(x, M, C, partials, eps, momentum, mean, rstd, running_mean=None, running_var=None):
+    """Batch statistics of ``x`` ``[M, C]`` (two kernels: per-block partial sums into ``partials``, then their total)."""
+    _check(require().eb_bn_stats(x.data_ptr(), int(M), int(C), partials.data_ptr(), int(partials.numel() // (2 * C)),
+                                 float(eps), float(momentum), mean.data_ptr(), rstd.data_ptr(), _ptr(running_mean),
+                                 _ptr(running_var), _stream(x.device)), 'eb_bn_stats')
 
 
 def bn_apply(x, M, C, mean, rstd, gamma, beta, residual, relu, y):
@@ -600,10 +599,11 @@ def bn_apply(x, M, C, mean, rstd, gamma, beta, residual, relu, y):
                                  _ptr(residual), int(bool(relu)), y.data_ptr(), _stream(x.device)), 'eb_bn_apply')
 
 
-def bn_bwd_reduce(dy, y, x, M, C, mean, rstd, relu, sum_dz, sum_dzx):
+def bn_bwd_reduce(dy, y, x, M, C, mean, rstd, relu, partials, sum_dz, sum_dzx, accumulate=False):
     _check(require().eb_bn_bwd_reduce(dy.data_ptr(), _ptr(y), x.data_ptr(), int(M), int(C), mean.data_ptr(),
-                                      rstd.data_ptr(), int(bool(relu)), sum_dz.data_ptr(), sum_dzx.data_ptr(),
-                                      _stream(x.device)), 'eb_bn_bwd_reduce')
+                                      rstd.data_ptr(), int(bool(relu)), partials.data_ptr(),
+                                      int(partials.numel() // (2 * C)), sum_dz.data_ptr(), sum_dzx.data_ptr(),
+                                      int(bool(accumulate)), _stream(x.device)), 'eb_bn_bwd_reduce')
 
 
 def bn_bwd_apply(dy, y, x, M, C, mean, rstd, gamma, sum_dz, sum_dzx, relu, dx, dres=None):

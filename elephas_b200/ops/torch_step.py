@@ -60,10 +60,16 @@ class TorchStepEngine:
         self.step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.stats = torch.zeros(8, dtype=torch.float64, device=dev)   # [0] loss sum, [1..4] metric sums, [7] rows
         self.slots = [None, None, None]
+        self._in_warmup = False
         self._alloc_slots()
         self.import_optimizer_state()
         self.graphs = {}
         self.failed = False
+        # synchronous data parallel, frequency='batch' (parallel/sync_torch.py): an object with ``delta(flip)`` (bf16 flat
+        # buffer in peer-mapped memory the optimizer writes its step into) and ``reduce(flip)`` (fused all-reduce + update
+        # of w32); both double buffered, ``flip`` alternates every step and is part of the graph key
+        self.sync = None
+        self.flip = 0
 
     # ------------------------------------------------------------- optimizer state
     def _alloc_slots(self):
@@ -136,8 +142,16 @@ class TorchStepEngine:
         out = out.float()
         per_sample = model._loss_fn(y, out)
         per_sample.mean().backward()
-        native.optimizer_step(self.kind, self.numel, self.g32, self.step, w32=self.w32, slots=self.slots,
-                              apply=True, advance=True, **self._opt_kwargs())
+        if self.sync is None:
+            native.optimizer_step(self.kind, self.numel, self.g32, self.step, w32=self.w32, slots=self.slots,
+                                  apply=True, advance=True, **self._opt_kwargs())
+        else:
+            # the step of this replica goes out as a bf16 delta; ONE fused kernel averages the deltas of all ranks over
+            # NVLink and applies the mean to the fp32 weights (the reference's collect + average, per batch)
+            native.optimizer_step(self.kind, self.numel, self.g32, self.step, slots=self.slots, apply=False,
+                                  delta_bf16=self.sync.delta(self.flip), advance=True, **self._opt_kwargs())
+            if not self._in_warmup:
+                self.sync.reduce(self.flip)
         with torch.no_grad():
             self.stats[0] += per_sample.detach().double().sum()
             for i, (_, fn) in enumerate(model._metric_fns[:4]):
@@ -153,9 +167,13 @@ class TorchStepEngine:
         # warm-up outside of capture (cuDNN algorithm selection, lazy module loads) on saved state
         saved = (self.w32.clone(), [s.clone() if s is not None else None for s in self.slots], self.step.clone(),
                  self.stats.clone(), self._buffers_snapshot())
-        with torch.cuda.stream(stream):
-            for _ in range(2):
-                self._body(sx, sy)
+        self._in_warmup = True  # (collectives run exactly once per step on every rank: never in the warm-up passes)
+        try:
+            with torch.cuda.stream(stream):
+                for _ in range(2):
+                    self._body(sx, sy)
+        finally:
+            self._in_warmup = False
         torch.cuda.current_stream(self.device).wait_stream(stream)
         stream.synchronize()
         self._restore(saved)
@@ -193,7 +211,7 @@ class TorchStepEngine:
 
     def train_step(self, x, y):
         """One captured step on device tensors ``x`` / ``y`` (running sums go to ``self.stats``)."""
-        key = (tuple(x.shape), tuple(y.shape), x.dtype, y.dtype)
+        key = (tuple(x.shape), tuple(y.shape), x.dtype, y.dtype, self.flip if self.sync is not None else -1)
         entry = self.graphs.get(key)
         if entry is None:
             with _CAPTURE_LOCK:
@@ -203,6 +221,8 @@ class TorchStepEngine:
         sy.copy_(y)
         graph.replay()
         native.count_replay(launches)
+        if self.sync is not None:
+            self.flip ^= 1
 
     def read_stats(self, reset=True):
         """``([loss, metrics...], rows)`` means of the running sums since the last reset (ONE device->host read)."""

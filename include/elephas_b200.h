@@ -379,22 +379,24 @@ int eb_conv_wgrad(const EbConvWgradArgs* args, void* stream);
 int eb_conv_im2col(const void* x, int32_t x_is_f32, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
                    int32_t stride, int32_t pad, int32_t P, int32_t Q, void* out_bf16, int32_t ld, void* stream);
 
-/* BatchNormalization over channels-last bf16 [M][C] (C multiple of 8), statistics in fp32.
- *   eb_bn_stats       sums[0][c] += sum_m x, sums[1][c] += sum_m x^2                     (zero sums first)
- *   eb_bn_finalize    mean, rstd = 1/sqrt(var + eps) from sums; running statistics updated with `momentum` (Keras:
- *                     running = running * momentum + batch * (1 - momentum); unbiased batch variance), sums re-zeroed
+/* BatchNormalization over channels-last bf16 [M][C] (C multiple of 8), statistics in fp32. The two reductions write one
+ * row of partial sums per thread block into `partials` (fp32, room for max_blocks * 2 * C values, no need to clear it)
+ * and a second small kernel adds the rows: no atomics, fixed summation order.
+ *   eb_bn_stats       mean, rstd = 1/sqrt(var + eps) of x; running statistics updated with `momentum` (Keras:
+ *                     running = running * momentum + batch * (1 - momentum); unbiased batch variance) when given
  *   eb_bn_apply       y = act((x - mean) * rstd * gamma + beta [+ residual]),  act = ReLU when relu != 0
- *   eb_bn_bwd_reduce  dz = dy * (y > 0 if relu);  sum_dz[c] += sum dz (= d beta), sum_dzx[c] += sum dz * xhat (= d gamma):
- *                     the two vectors may be the gradient buffers of beta and gamma themselves (zeroed for the step)
+ *   eb_bn_bwd_reduce  dz = dy * (y > 0 if relu);  sum_dz[c] (+)= sum dz (= d beta), sum_dzx[c] (+)= sum dz * xhat
+ *                     (= d gamma); with accumulate != 0 the totals are ADDED to the two vectors, which may then be the
+ *                     gradient buffers of beta and gamma themselves (zeroed at the start of the step)
  *   eb_bn_bwd_apply   dx = gamma * rstd * (dz - sum_dz/M - xhat * sum_dzx/M); dres = dz when requested
  * Reference: Keras BatchNormalization / Activation / Add layers inside model.fit (elephas/worker.py:42). */
-int eb_bn_stats(const void* x, int64_t M, int32_t C, float* sums, void* stream);
-int eb_bn_finalize(float* sums, int64_t M, int32_t C, float eps, float momentum, float* mean, float* rstd,
-                   float* running_mean, float* running_var, void* stream);
+int eb_bn_stats(const void* x, int64_t M, int32_t C, float* partials, int32_t max_blocks, float eps, float momentum,
+                float* mean, float* rstd, float* running_mean, float* running_var, void* stream);
 int eb_bn_apply(const void* x, int64_t M, int32_t C, const float* mean, const float* rstd, const float* gamma,
                 const float* beta, const void* residual, int32_t relu, void* y, void* stream);
 int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
-                     const float* rstd, int32_t relu, float* sum_dz, float* sum_dzx, void* stream);
+                     const float* rstd, int32_t relu, float* partials, int32_t max_blocks, float* sum_dz, float* sum_dzx,
+                     int32_t accumulate, void* stream);
 int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int64_t M, int32_t C, const float* mean,
                     const float* rstd, const float* gamma, const float* sum_dz, const float* sum_dzx, int32_t relu,
                     void* dx, void* dres, void* stream);

@@ -570,42 +570,3 @@ def test_fused_mlp_predict_and_evaluate_match_the_gemm_chain(monkeypatch):
 def native_launches():
     from elephas_b200.ops import native
     return native.launch_count()
-
-
-def test_native_conv1x1_matches_cudnn(monkeypatch):
-    """First piece of K9: 1x1 / stride-1 convolutions on the tcgen05 GEMM, forward and all three gradients."""
-    from elephas_b200.ops import conv1x1
-    torch.manual_seed(17)
-    n, h, w, cin, cout = 4, 14, 14, 64, 256
-    x = torch.randn(n, h, w, cin, device='cuda', requires_grad=True)
-    k = (torch.randn(cout, cin, 1, 1, device='cuda') / 8).requires_grad_(True)
-    b = torch.randn(cout, device='cuda', requires_grad=True)
-    assert conv1x1.eligible(x, k, (1, 1), (1, 1), 1, False)
-    assert not conv1x1.eligible(x, torch.zeros(cout, cin, 3, 3, device='cuda'), (1, 1), (1, 1), 1, False)
-    y = conv1x1.conv1x1(x, k, b)
-    gy = torch.randn_like(y)
-    y.backward(gy)
-    got = (y.float(), x.grad.clone(), k.grad.clone(), b.grad.clone())
-    x.grad = k.grad = b.grad = None
-    xb, kb = x.detach().to(torch.bfloat16).float().requires_grad_(True), k.detach().to(torch.bfloat16).float().requires_grad_(True)
-    ref = torch.nn.functional.conv2d(xb.permute(0, 3, 1, 2), kb, b).permute(0, 2, 3, 1)
-    ref.backward(gy.float())
-    assert torch.allclose(got[0], ref, atol=3e-2, rtol=3e-2)
-    assert torch.allclose(got[1], xb.grad, atol=5e-2, rtol=5e-2)
-    assert torch.allclose(got[2], kb.grad, atol=0.3, rtol=3e-2)   # sums over 784 positions of bf16 products
-    assert torch.allclose(got[3], b.grad, atol=0.1, rtol=2e-2)
-    # inside a model: the captured step trains with the native path switched on
-    monkeypatch.setenv('ELEPHAS_B200_NATIVE_CONV1X1', '1')
-    from elephas_b200.models.layers import BatchNormalization, Conv2D, Flatten
-    m = Sequential([Conv2D(16, 3, padding='same', activation='relu', input_shape=(8, 8, 8)), Conv2D(32, 1), BatchNormalization(),
-                    Conv2D(16, 1, activation='relu'), Flatten(), Dense(10, activation='softmax')])
-    m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
-    m.set_compute_dtype('bfloat16')
-    m.to('cuda')
-    rng = np.random.default_rng(2)
-    xs = rng.normal(size=(128, 8, 8, 8)).astype(np.float32)
-    ys = np.eye(10, dtype=np.float32)[(xs.mean(axis=(1, 2, 3)) > 0).astype(int)]
-    launches = native_launches()
-    hist = m.fit(xs, ys, batch_size=32, epochs=6)
-    assert native_launches() > launches + 6 * 4 * 6   # the 1x1 layers ran on the native GEMM (3 launches each way)
-    assert hist.history['loss'][-1] < hist.history['loss'][0]

@@ -172,6 +172,42 @@ sm.fit(to_simple_rdd(sc, x, y), epochs=2, batch_size=64)
 same_on_all_ranks(sm.master_network.get_weights(), tol=1e-6)
 log("generic torch path with custom activation ok: acc %.3f" % sm.evaluate(xt, yt)[1])
 
+# ---- 5b. CNN, synchronous, frequency='batch' in bf16: native conv / BN kernels, fused all-reduce inside the step graph ---
+from elephas_b200.models import Model  # noqa: E402
+from elephas_b200.models.layers import (Activation, Add, BatchNormalization, Conv2D, GlobalAveragePooling2D, Input)  # noqa: E402
+from elephas_b200 import worker as _worker_mod  # noqa: E402,F401
+
+
+def small_cnn():
+    inp = Input(shape=(16, 16, 8))
+    h = Activation('relu')(BatchNormalization()(Conv2D(16, 3, padding='same')(inp)))
+    s_ = BatchNormalization()(Conv2D(32, 1, strides=2)(h))
+    t = Activation('relu')(BatchNormalization()(Conv2D(16, 1, strides=2)(h)))
+    t = BatchNormalization()(Conv2D(32, 3, padding='same')(t))
+    h = Activation('relu')(Add()([s_, t]))
+    return Model(inputs=inp, outputs=Dense(4, activation='softmax')(GlobalAveragePooling2D()(h)))
+
+
+rng = np.random.default_rng(11)
+n_img = 64 * 3 * W
+xc = rng.normal(size=(n_img, 16, 16, 8)).astype(np.float32)
+lab = (xc[:, :8].mean(axis=(1, 2, 3)) > 0).astype(int) + 2 * (xc[:, :, :8].mean(axis=(1, 2, 3)) > 0).astype(int)
+yc = np.eye(4, dtype=np.float32)[lab]
+torch.manual_seed(100 + R)
+cnn_model = small_cnn()
+cnn_model.compile(SGD(lr=0.05, momentum=0.9), 'categorical_crossentropy', ['acc'])
+cnn_model.set_compute_dtype('bfloat16')
+sm = SparkModel(cnn_model, mode='synchronous', frequency='batch', num_workers=W)
+before_eval = sm.evaluate(xc, yc)
+launched = native.launch_count()
+sm.fit(to_simple_rdd(sc, xc, yc), epochs=4, batch_size=64, verbose=0)
+assert native.launch_count() - launched > 4 * 3 * 20, "native conv kernels did not run"
+same_on_all_ranks(sm.master_network.get_weights(), tol=0.0)  # averaged every step: replicas are bit-identical
+after_eval = sm.evaluate(xc, yc)
+assert after_eval[0] < before_eval[0] and after_eval[1] > 0.5, (before_eval, after_eval)
+assert len(sm.training_histories) == W
+log("CNN synchronous/batch bf16 on native conv kernels ok: loss %.4f -> %.4f acc %.3f" % (before_eval[0], after_eval[0], after_eval[1]))
+
 # ---- 6. race test across ranks: every rank pushes integer deltas into ALL stripes of the striped store over NVLink ---
 from elephas_b200.parallel.device_ps import create_store, destroy_store  # noqa: E402
 

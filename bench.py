@@ -404,7 +404,7 @@ def run_config_script(args, rt):
     sys.path.insert(0, os.path.join(ROOT, 'benchmarks'))
     import configs as _configs
     ns = argparse.Namespace(config=3 if args.config == 'otto_pipeline' else 5, gpus=rt.world_size, epochs=None,
-                            samples=None, batch_size=args.batch_per_gpu, cpu=False)
+                            samples=None, batch_size=args.batch_per_gpu, cpu=False, frequency=args.frequency)
     res = _configs.config_otto(ns, rt) if ns.config == 3 else _configs.config_resnet(ns, rt)
     out = {'metric': 'samples/sec (wall clock around the public API call, max over ranks)', 'unit': 'samples/sec',
            'n_gpus': rt.world_size, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'impl': 'ours',

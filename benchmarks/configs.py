@@ -134,33 +134,41 @@ def config_otto(args, rt):
 
 
 def config_resnet(args, rt):
-    """Config 5: ResNet-50-shaped CNN, SparkModel synchronous, bf16 autocast (torch/cuDNN convolutions - there is no
-    native conv kernel yet, see DESIGN.md - with this framework's fused P2P all-reduce for the weight deltas)."""
+    """Config 5: ResNet-50-shaped CNN, SparkModel synchronous (frequency='batch': replicas averaged every step), bf16.
+    Convolutions, BatchNormalization (+ residual + ReLU) and the classifier run on this repository's tcgen05 / sm_100a
+    kernels (``ops/cnn.py``; ``ELEPHAS_B200_NATIVE_CONV=0`` = the cuDNN arm), the step is replayed from a CUDA graph, the
+    weight deltas go through the fused NVLink all-reduce inside that graph. Every rank generates only its own shard."""
     import numpy as np
     from elephas.spark_model import SparkModel
-    from elephas.utils.rdd_utils import to_simple_rdd
     from elephas_b200.models import SGD, zoo
+    from elephas_b200.ops import cnn
     from elephas_b200.spark import SparkContext
+    from elephas_b200.utils.rdd_utils import to_sharded_rdd
     bs = args.batch_size or 64
-    steps = 10
-    epochs = args.epochs or 4
+    steps = 20
+    epochs = args.epochs or 3
     side, classes = 224, 1000
-    n_rank = bs * steps
     rng = np.random.default_rng(7 + rt.rank)
-    n = n_rank * max(rt.world_size, 1)
-    x = rng.standard_normal((n, side, side, 3), dtype=np.float32)
-    y = np.eye(classes, dtype=np.float32)[rng.integers(0, classes, n)]
+    n_rank = bs * steps
+    x = rng.standard_normal((n_rank, side, side, 3), dtype=np.float32)
+    y = np.eye(classes, dtype=np.float32)[rng.integers(0, classes, n_rank)]
     model = zoo.resnet50(input_shape=(side, side, 3), classes=classes)
     model.compile(SGD(learning_rate=0.01, momentum=0.9), 'categorical_crossentropy', ['acc'])
     model.set_compute_dtype('bfloat16')
-    sm = SparkModel(model, mode='synchronous', frequency='epoch', num_workers=max(rt.world_size, 1))
+    frequency = getattr(args, 'frequency', None) or 'batch'
+    sm = SparkModel(model, mode='synchronous', frequency=frequency, num_workers=None)
     sc = SparkContext.getOrCreate()
-    rdd = to_simple_rdd(sc, x, y)
-    sm.fit(rdd, epochs=1, batch_size=bs, verbose=0, keep_context=True)  # warm-up (cuDNN autotune, graph capture)
+    rdd = to_sharded_rdd(sc, x, y)
+    sm.fit(rdd, epochs=1, batch_size=bs, verbose=0, keep_context=True)  # warm-up (graph capture, both delta buffers)
     dt, _ = timed(rt, lambda: sm.fit(rdd, epochs=epochs, batch_size=bs, verbose=0, keep_context=True))
+    hist = sm.training_histories[-1] or {}
     sm.release_context()
-    return dict(value=round(n * epochs / dt, 1), seconds=round(dt, 4), epochs=epochs, batch_size=bs, train_samples=n,
-                image=side, frequency='epoch', conv_backend='cuDNN (library), step replayed from a CUDA graph, native flat optimizer', dtype='bf16 autocast')
+    n = n_rank * max(rt.world_size, 1)
+    return dict(value=round(n * epochs / dt, 1), seconds=round(dt, 4), ms_per_step=round(dt * 1e3 / (epochs * steps), 3),
+                epochs=epochs, steps_per_epoch=steps, batch_size=bs, train_samples=n, image=side, frequency=frequency,
+                final_loss=round(float(hist.get('loss', [float('nan')])[-1]), 4),
+                conv_backend='native tcgen05 implicit GEMM + sm_100a BatchNorm kernels' if cnn.enabled()
+                else 'cuDNN (library)', dtype='bf16 (fp32 master weights)')
 
 
 def main():

@@ -106,22 +106,37 @@ __device__ __forceinline__ void block_reduce_pair(const Shape& s, int lane, int 
   }
 }
 
-// totals of column c over the rows of `partials`: a[c] = sum_b partials[b][0][c], b[c] = sum_b partials[b][1][c]
-__device__ __forceinline__ void sum_partials(const float* __restrict__ partials, int nblocks, int C, int c, float& a, float& b) {
+// Totals of 32 columns over the rows of `partials` by a block of 32 x 32 threads: thread (x, y) adds rows y, y + 32, ...
+// of column c = blockIdx.x * 32 + x (coalesced 128-byte reads, four independent loads in flight), then the 32 row
+// groups are combined through shared memory. The result is valid in the threads with threadIdx.y == 0.
+__device__ __forceinline__ void sum_partials(const float* __restrict__ partials, int nblocks, int C, float& a, float& b) {
+  __shared__ float sh[2][32][33];
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
-  int r = 0;
-  for (; r + 1 < nblocks; r += 2) {
-    a0 += partials[(2ll * r) * C + c];
-    b0 += partials[(2ll * r + 1) * C + c];
-    a1 += partials[(2ll * r + 2) * C + c];
-    b1 += partials[(2ll * r + 3) * C + c];
+  if (c < C) {
+    int r = threadIdx.y;
+    for (; r + 32 < nblocks; r += 64) {
+      a0 += partials[(2ll * r) * C + c];
+      b0 += partials[(2ll * r + 1) * C + c];
+      a1 += partials[(2ll * (r + 32)) * C + c];
+      b1 += partials[(2ll * (r + 32) + 1) * C + c];
+    }
+    if (r < nblocks) {
+      a0 += partials[(2ll * r) * C + c];
+      b0 += partials[(2ll * r + 1) * C + c];
+    }
   }
-  if (r < nblocks) {
-    a0 += partials[(2ll * r) * C + c];
-    b0 += partials[(2ll * r + 1) * C + c];
+  sh[0][threadIdx.y][threadIdx.x] = a0 + a1;
+  sh[1][threadIdx.y][threadIdx.x] = b0 + b1;
+  __syncthreads();
+  a = b = 0.f;
+  if (threadIdx.y == 0) {
+#pragma unroll 8
+    for (int k = 0; k < 32; ++k) {
+      a += sh[0][k][threadIdx.x];
+      b += sh[1][k][threadIdx.x];
+    }
   }
-  a = a0 + a1;
-  b = b0 + b1;
 }
 
 __global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __restrict__ x, const Shape s, float* partials) {
@@ -145,10 +160,10 @@ __global__ void __launch_bounds__(kThreads) stats_kernel(const __nv_bfloat16* __
 
 __global__ void finalize_kernel(const float* __restrict__ partials, int nblocks, long long M, int C, float eps, float momentum,
                                 float* mean, float* rstd, float* running_mean, float* running_var) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float sum, sumsq;
-  sum_partials(partials, nblocks, C, c, sum, sumsq);
+  sum_partials(partials, nblocks, C, sum, sumsq);
+  if (c >= C || threadIdx.y != 0) return;
   const float inv = 1.f / static_cast<float>(M);
   const float mu = sum * inv;
   float var = sumsq * inv - mu * mu;
@@ -165,10 +180,10 @@ __global__ void finalize_kernel(const float* __restrict__ partials, int nblocks,
 // sum_dz[c] (+)= sum over blocks, sum_dzx[c] (+)= ...: one writer per channel (the destinations may be gradient buffers)
 __global__ void bwd_finalize_kernel(const float* __restrict__ partials, int nblocks, int C, float* sum_dz, float* sum_dzx,
                                     int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+  const int c = blockIdx.x * 32 + threadIdx.x;
   float a, b;
-  sum_partials(partials, nblocks, C, c, a, b);
+  sum_partials(partials, nblocks, C, a, b);
+  if (c >= C || threadIdx.y != 0) return;
   sum_dz[c] = accumulate ? sum_dz[c] + a : a;
   sum_dzx[c] = accumulate ? sum_dzx[c] + b : b;
 }
@@ -356,7 +371,7 @@ extern "C" int eb_bn_stats(const void* x, int64_t M, int32_t C, float* partials,
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   bn::stats_kernel<<<grid, bn::kThreads, 0, st>>>(static_cast<const __nv_bfloat16*>(x), s, partials);
   EB_LAUNCH_OK("bn_stats_kernel");
-  bn::finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partials, grid, M, C, eps, momentum, mean, rstd, running_mean, running_var);
+  bn::finalize_kernel<<<(C + 31) / 32, dim3(32, 32), 0, st>>>(partials, grid, M, C, eps, momentum, mean, rstd, running_mean, running_var);
   EB_LAUNCH_OK("bn_finalize_kernel");
   return 0;
 }
@@ -385,7 +400,7 @@ extern "C" int eb_bn_bwd_reduce(const void* dy, const void* y, const void* x, in
       static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), static_cast<const __nv_bfloat16*>(x), s, mean,
       rstd, relu, partials);
   EB_LAUNCH_OK("bn_bwd_reduce_kernel");
-  bn::bwd_finalize_kernel<<<(C + 127) / 128, 128, 0, st>>>(partials, grid, C, sum_dz, sum_dzx, accumulate);
+  bn::bwd_finalize_kernel<<<(C + 31) / 32, dim3(32, 32), 0, st>>>(partials, grid, C, sum_dz, sum_dzx, accumulate);
   EB_LAUNCH_OK("bn_bwd_finalize_kernel");
   return 0;
 }

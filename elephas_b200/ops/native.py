@@ -584,7 +584,7 @@ def conv_im2col(x, R, S, stride, pad, P, Q, out, ld):
                                     int(pad), int(P), int(Q), out.data_ptr(), int(ld), _stream(x.device)), 'eb_conv_im2col')
 
 
-BN_MAX_BLOCKS = 1184  # rows of the partial-sum scratch: 8 blocks per SM
+BN_MAX_BLOCKS = 592  # rows of the partial-sum scratch: 4 blocks of 256 threads per SM
 
 
 def bn_stats(x, M, C, partials, eps, momentum, mean, rstd, running_mean=None, running_var=None):

@@ -354,6 +354,81 @@ __global__ void __launch_bounds__(512) allreduce_shard_update_kernel(const CommD
   }
 }
 
+// NVLS variant of the sharded-master kernel: the deltas of ALL ranks are added inside the NVSwitch
+// (multimem.ld_reduce on the multicast address of the delta buffers: one reduced stream arrives instead of N-1), rank r
+// updates slice r of its fp32 master, and ONE multimem.st per vector replicates the refreshed bf16 weights into every
+// rank's compute copy. Per rank and direction about S bytes cross NVLink instead of 2 (N-1)/N S, and the SMs issue 1/N
+// of the loads. p.delta[0] / p.avg[0] are the MULTICAST addresses of the delta and bf16 weight buffers (cuMulticast*
+// objects, csrc/vmm.cu); the flag pads are ordinary peer mappings.
+__device__ __forceinline__ uint4 multimem_ld_reduce_bf16x8(const void* mc) {
+  uint4 r;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(mc)
+               : "memory");
+  return r;
+}
+__device__ __forceinline__ void multimem_st_bf16x8(void* mc, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+
+template <int U>
+__global__ void __launch_bounds__(512) allreduce_nvls_update_kernel(const CommDev p) {
+  const uint32_t e = p.local[0] + 1;
+  if (blockIdx.x == 0) publish_flags(p, 0, e);
+  wait_flags(p, 0, e);
+  const long n8 = p.n / 8;
+  const long per = (n8 + p.world - 1) / p.world;
+  const long lo = per * p.rank, hi = min(n8, lo + per);
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  const __nv_bfloat16* mc_delta = static_cast<const __nv_bfloat16*>(p.delta[0]);
+  __nv_bfloat16* mc_w16 = static_cast<__nv_bfloat16*>(p.avg[0]);
+  for (long g0 = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g0 < hi; g0 += stride * U) {
+    uint4 raw[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long g = g0 + u * stride;
+      if (g < hi) raw[u] = multimem_ld_reduce_bf16x8(mc_delta + g * 8);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long g = g0 + u * stride;
+      if (g < hi) {
+        const uint4 v = raw[u];
+        float4 w0 = *reinterpret_cast<float4*>(p.w32 + g * 8), w1 = *reinterpret_cast<float4*>(p.w32 + g * 8 + 4);
+        w0.x -= bf16_lo(v.x) * p.scale; w0.y -= bf16_hi(v.x) * p.scale; w0.z -= bf16_lo(v.y) * p.scale; w0.w -= bf16_hi(v.y) * p.scale;
+        w1.x -= bf16_lo(v.z) * p.scale; w1.y -= bf16_hi(v.z) * p.scale; w1.z -= bf16_lo(v.w) * p.scale; w1.w -= bf16_hi(v.w) * p.scale;
+        *reinterpret_cast<float4*>(p.w32 + g * 8) = w0;
+        *reinterpret_cast<float4*>(p.w32 + g * 8 + 4) = w1;
+        uint4 o;
+        o.x = pack_bf16x2(w0.x, w0.y); o.y = pack_bf16x2(w0.z, w0.w);
+        o.z = pack_bf16x2(w1.x, w1.y); o.w = pack_bf16x2(w1.z, w1.w);
+        multimem_st_bf16x8(mc_w16 + g * 8, o);
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    if (atomicAdd(p.local + 2, 1u) == gridDim.x - 1) {
+      p.local[2] = 0;
+      __threadfence_system();
+      for (int k = 0; k < p.world; ++k) st_release_sys(p.pad[k] + 8 + p.rank, e);
+    }
+  }
+  wait_flags(p, 8, e);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(p.local + 1, 1u) == gridDim.x - 1) {
+      p.local[1] = 0;
+      p.local[0] = e;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ parameter server
 __global__ void ps_lock_kernel(uint32_t* ctrl) {
   // ctrl[1]: next ticket, ctrl[2]: now serving, ctrl[0]: sequence word (odd while a writer is inside),
@@ -541,6 +616,37 @@ extern "C" int eb_allreduce_shard_update(const EbCommArgs* a, void* stream) {
     else allreduce_shard_update_kernel<float, 8, 1><<<blocks, 512, 0, s>>>(p);
   }
   EB_LAUNCH_OK("allreduce_shard_update_kernel");
+  return 0;
+}
+
+extern "C" int eb_allreduce_nvls_update(const EbCommArgs* a, void* stream) {
+  if (a == nullptr) return fail("eb_allreduce_nvls_update: null args");
+  if (a->n <= 0) return 0;
+  if (a->world < 2 || a->world > kMaxRanks) return fail("eb_allreduce_nvls_update: world size %d outside [2, %d]", a->world, kMaxRanks);
+  if (a->rank < 0 || a->rank >= a->world) return fail("eb_allreduce_nvls_update: bad rank %d", a->rank);
+  if (a->n % 8) return fail("eb_allreduce_nvls_update: element count must be a multiple of 8");
+  if (!a->dtype_bf16) return fail("eb_allreduce_nvls_update: bf16 deltas only");
+  if (a->delta[0] == nullptr || a->avg[0] == nullptr || a->w32 == nullptr || a->local == nullptr)
+    return fail("eb_allreduce_nvls_update: multicast delta / weight addresses, fp32 weights and local scratch are required");
+  if ((reinterpret_cast<uintptr_t>(a->delta[0]) & 15) || (reinterpret_cast<uintptr_t>(a->avg[0]) & 15))
+    return fail("eb_allreduce_nvls_update: multicast addresses must be 16-byte aligned");
+  CommDev p;
+  for (int i = 0; i < kMaxRanks; ++i) {
+    p.delta[i] = nullptr; p.avg[i] = nullptr;
+    p.pad[i] = i < a->world ? static_cast<uint32_t*>(a->pad[i]) : nullptr;
+    if (i < a->world && p.pad[i] == nullptr) return fail("eb_allreduce_nvls_update: missing signal pad %d", i);
+  }
+  p.delta[0] = a->delta[0]; p.avg[0] = a->avg[0];
+  p.local = static_cast<uint32_t*>(a->local);
+  p.w32 = a->w32; p.w16 = nullptr; p.out32 = nullptr;
+  p.n = a->n; p.rank = a->rank; p.world = a->world; p.scale = a->scale;
+  int blocks = a->blocks > 0 ? a->blocks : 32;
+  if (blocks > num_sms()) blocks = num_sms();  // co-resident grid: the kernel contains a grid-wide barrier
+  const long work = (a->n / 8 / a->world + 512L * 4 - 1) / (512L * 4);
+  if (blocks > work) blocks = static_cast<int>(work);
+  if (blocks < 1) blocks = 1;
+  allreduce_nvls_update_kernel<4><<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(p);
+  EB_LAUNCH_OK("allreduce_nvls_update_kernel");
   return 0;
 }
 

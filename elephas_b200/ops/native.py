@@ -170,6 +170,17 @@ def load():
         lib.eb_bn_bwd_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
+        lib.eb_allreduce_nvls_update.argtypes = [c_void_p, c_void_p]
+        lib.eb_vmm_supported.argtypes = [ctypes.POINTER(c_int32), ctypes.POINTER(c_int32)]
+        lib.eb_vmm_create.argtypes = [c_int64, c_int32, ctypes.POINTER(c_uint64), ctypes.POINTER(c_int64)]
+        lib.eb_vmm_export_fd.argtypes = [c_uint64, ctypes.POINTER(c_int32)]
+        lib.eb_vmm_import_fd.argtypes = [c_int32, ctypes.POINTER(c_uint64)]
+        lib.eb_vmm_map.argtypes = [c_uint64, c_int64, ctypes.POINTER(c_void_p)]
+        lib.eb_vmm_unmap.argtypes = [c_void_p, c_int64]
+        lib.eb_vmm_release.argtypes = [c_uint64]
+        lib.eb_mc_create.argtypes = [c_int32, c_int64, ctypes.POINTER(c_uint64)]
+        lib.eb_mc_add_device.argtypes = [c_uint64]
+        lib.eb_mc_bind.argtypes = [c_uint64, c_uint64, c_int64]
         lib.eb_device_malloc.argtypes = [ctypes.POINTER(c_void_p), c_int64]
         lib.eb_device_free.argtypes = [c_void_p]
         lib.eb_ipc_export.argtypes = [c_void_p, c_void_p]
@@ -430,6 +441,14 @@ def allreduce_shard_update(delta_ptrs, pad_ptrs, local, n, rank, world, scale, d
     _check(require().eb_allreduce_shard_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_shard_update')
 
 
+def allreduce_nvls_update(mc_delta, mc_w16, pad_ptrs, local, n, rank, world, scale, w32, blocks=0, device=None):
+    """NVLS fused all-reduce + update: ``mc_delta`` / ``mc_w16`` are MULTICAST addresses (``symm.VmmSymmetricMemory``)."""
+    a = _comm_args([mc_delta] + [None] * 7, pad_ptrs, local, n, rank, world, scale, True, [mc_w16] + [None] * 7, w32, None,
+                   None, 0, blocks)
+    a.delta[0], a.avg[0] = mc_delta, mc_w16
+    _check(require().eb_allreduce_nvls_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_nvls_update')
+
+
 def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32, scale=1.0, blocks=0, device=None):
     a = _comm_args(delta_ptrs, pad_ptrs, local, n, rank, world, scale, dtype_bf16, None, None, None, out32, 1, blocks)
     _check(require().eb_allreduce_sum(ctypes.byref(a), _stream(device)), 'eb_allreduce_sum')
@@ -622,6 +641,70 @@ def host_f32_to_bf16(src, dst, rows=None, cols=None, threads=4):
         raise NativeError("host_f32_to_bf16 needs a host fp32 source and a host 16-bit destination")
     _check(load().eb_host_f32_to_bf16(src.data_ptr(), src.stride(0), dst.data_ptr(), dst.stride(0), rows, cols,
                                       int(threads)), 'eb_host_f32_to_bf16')
+
+
+# ------------------------------------------------- VMM allocations and multicast objects
+def vmm_supported():
+    """``(fd-exportable VMM allocations supported, NVSwitch multicast supported)`` on the current device."""
+    v, m = c_int32(0), c_int32(0)
+    _check(require().eb_vmm_supported(ctypes.byref(v), ctypes.byref(m)), 'eb_vmm_supported')
+    return bool(v.value), bool(m.value)
+
+
+def vmm_create(nbytes, multicast_ranks=0):
+    h, size = c_uint64(0), c_int64(0)
+    _check(require().eb_vmm_create(int(nbytes), int(multicast_ranks), ctypes.byref(h), ctypes.byref(size)), 'eb_vmm_create')
+    return h.value, size.value
+
+
+def vmm_export_fd(handle) -> int:
+    fd = c_int32(-1)
+    _check(require().eb_vmm_export_fd(c_uint64(handle), ctypes.byref(fd)), 'eb_vmm_export_fd')
+    return fd.value
+
+
+def vmm_import_fd(fd) -> int:
+    h = c_uint64(0)
+    _check(require().eb_vmm_import_fd(int(fd), ctypes.byref(h)), 'eb_vmm_import_fd')
+    return h.value
+
+
+def vmm_map(handle, size) -> int:
+    p = c_void_p()
+    _check(require().eb_vmm_map(c_uint64(handle), int(size), ctypes.byref(p)), 'eb_vmm_map')
+    return p.value
+
+
+def vmm_unmap(ptr, size):
+    _check(require().eb_vmm_unmap(c_void_p(ptr), int(size)), 'eb_vmm_unmap')
+
+
+def vmm_release(handle):
+    _check(require().eb_vmm_release(c_uint64(handle)), 'eb_vmm_release')
+
+
+def mc_create(ranks, size) -> int:
+    h = c_uint64(0)
+    _check(require().eb_mc_create(int(ranks), int(size), ctypes.byref(h)), 'eb_mc_create')
+    return h.value
+
+
+def mc_add_device(mc_handle):
+    _check(require().eb_mc_add_device(c_uint64(mc_handle)), 'eb_mc_add_device')
+
+
+def mc_bind(mc_handle, mem_handle, size):
+    _check(require().eb_mc_bind(c_uint64(mc_handle), c_uint64(mem_handle), int(size)), 'eb_mc_bind')
+
+
+def tensor_from_ptr(ptr, dtype, numel, device):
+    """A torch tensor over raw device memory owned by somebody else (VMM mappings, library allocations)."""
+    typestr = {torch.float32: '<f4', torch.bfloat16: '<u2', torch.int32: '<i4', torch.uint8: '|u1', torch.int64: '<i8',
+               torch.float64: '<f8'}[dtype]
+    iface = {'shape': (int(numel),), 'typestr': typestr, 'data': (int(ptr), False), 'version': 3}
+    holder = type('_CudaArray', (), {'__cuda_array_interface__': iface})()
+    t = torch.as_tensor(holder, device=device)
+    return t.view(torch.bfloat16) if dtype == torch.bfloat16 else t
 
 
 # --------------------------------------------------------------- memory / IPC

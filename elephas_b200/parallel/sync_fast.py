@@ -32,7 +32,7 @@ from ..ops import engine as _engine
 from ..ops import native
 from ..utils import tracing
 from ..worker import partition_to_arrays
-from .symm import SymmetricMemory
+from .symm import SymmetricMemory, VmmSymmetricMemory
 
 IN_PLACE = object()  # returned instead of a weight list: the master network already holds the result
 
@@ -297,6 +297,7 @@ class SyncContext:
         self.sharded = False
         self.w32_partial = False
         self._private_w16 = None
+        self.nvls = False
 
     # ---------------------------------------------------------------- comm setup
     def _setup_comm(self, dtype_bf16):
@@ -313,7 +314,26 @@ class SyncContext:
         # modes keep whole replicas and need the averaged-delta staging buffer of the two-shot kernel instead
         self.sharded = bool(dtype_bf16) and os.environ.get('ELEPHAS_B200_SHARDED_MASTER', '1') != '0'
         spec['w16' if self.sharded else 'avg'] = n * item
-        self.mem = SymmetricMemory(self.rt, spec)
+        # NVLS (ELEPHAS_B200_NVLS=1): the buffers come from the VMM allocator and are bound into an NVSwitch multicast
+        # object, the sharded kernel then lets the switch add the deltas and replicate the refreshed weights
+        self.nvls = False
+        want_nvls = self.sharded and os.environ.get('ELEPHAS_B200_NVLS', '0') == '1' and self.rt.distributed
+        if want_nvls:
+            try:
+                mem = VmmSymmetricMemory(self.rt, spec, multicast=True)
+                err = None
+            except native.NativeError as exc:
+                mem, err = None, str(exc)
+            ok = self.rt.all_gather_object(mem is not None and mem.multicast)
+            if all(ok):
+                self.mem, self.nvls = mem, True
+            else:
+                if mem is not None:
+                    mem.close()
+                if self.rt.is_driver:
+                    print(">>> NVLS not available on this node (%s): peer-to-peer kernels" % (err or 'no multicast support',))
+        if not self.nvls:
+            self.mem = SymmetricMemory(self.rt, spec)
         self.comm_local = torch.zeros(16, dtype=torch.int32, device=self.rt.device)
         self.dtype_bf16 = dtype_bf16
         tdt = torch.bfloat16 if dtype_bf16 else torch.float32
@@ -332,7 +352,11 @@ class SyncContext:
         self.rt.barrier()
         common = (self.mem.ptrs('delta0'), self.mem.ptrs('pad'), self.comm_local, 1024, self.rt.rank,
                   self.rt.world_size, 1.0 / self.n_sub, dtype_bf16, eng.w32)
-        if self.sharded:
+        if self.nvls:
+            native.allreduce_nvls_update(self.mem.mc_ptr('delta0'), self.mem.mc_ptr('w16'), self.mem.ptrs('pad'),
+                                         self.comm_local, 1024, self.rt.rank, self.rt.world_size, 1.0 / self.n_sub, eng.w32,
+                                         blocks=2, device=self.rt.device)
+        elif self.sharded:
             native.allreduce_shard_update(*common, self.mem.ptrs('w16'), blocks=2, device=self.rt.device)
         else:
             for algo in (1, 2):
@@ -386,7 +410,11 @@ class SyncContext:
         item = 2 if self.dtype_bf16 else 4
         common = (self.mem.ptrs(name, lo * item), self.mem.ptrs('pad'), self.comm_local, n, self.rt.rank,
                   self.rt.world_size, 1.0 / self.n_sub, self.dtype_bf16, eng.w32[lo:])
-        if self.sharded:
+        if self.nvls:
+            native.allreduce_nvls_update(self.mem.mc_ptr(name, lo * 2), self.mem.mc_ptr('w16', lo * 2), self.mem.ptrs('pad'),
+                                         self.comm_local, n, self.rt.rank, self.rt.world_size, 1.0 / self.n_sub,
+                                         eng.w32[lo:], blocks=blocks, device=self.rt.device)
+        elif self.sharded:
             native.allreduce_shard_update(*common, self.mem.ptrs('w16', lo * 2), blocks=blocks,
                                           device=self.rt.device)
         else:

@@ -188,6 +188,11 @@ int eb_allreduce_sum(const EbCommArgs* args, void* stream);
  * refreshed bf16 weights of that slice into every rank's compute copy, whose peer-mapped addresses are passed
  * in avg[]. The fp32 master of the other slices is NOT maintained on this rank (gather the slices afterwards). */
 int eb_allreduce_shard_update(const EbCommArgs* args, void* stream);
+/* NVLS form of eb_allreduce_shard_update (bf16 deltas): delta[0] and avg[0] are the MULTICAST addresses (cuMulticast*
+ * objects over all ranks' buffers, see eb_mc_*) of the delta buffers and of the bf16 weight copies; the sum over ranks is
+ * formed inside the NVSwitch by multimem.ld_reduce, the refreshed weights reach every rank with one multimem.st. pad[]
+ * are ordinary peer mappings. About half the NVLink bytes of the peer-to-peer kernel, 1/N of its load instructions. */
+int eb_allreduce_nvls_update(const EbCommArgs* args, void* stream);
 
 /* Allocation-free form of eb_allreduce_update for ONE rank (world = 1). This entry point has no
  * counterpart in the reference; it exists for hosts that are not allowed to allocate device memory at the
@@ -408,6 +413,24 @@ int eb_bn_bwd_apply(const void* dy, const void* y, const void* x, int64_t M, int
  * reference. */
 int eb_host_f32_to_bf16(const float* src, int64_t ld_src, void* dst, int64_t ld_dst, int64_t rows, int32_t cols,
                         int32_t threads);
+
+/* ------------------------------------------------------------ symmetric memory on the VMM API + multicast objects
+ * eb_vmm_*: physical allocations (cuMemCreate) exportable as POSIX file descriptors, import + map of a peer's allocation
+ * (NVLink peer access without cudaIpc*), eb_mc_*: an NVSwitch multicast object over the same allocation of all ranks -
+ * mapping ITS handle yields the address multimem.ld_reduce / multimem.st use. Protocol: every rank eb_vmm_create +
+ * eb_vmm_map + export; one rank eb_mc_create + export; every rank imports, eb_mc_add_device, (barrier), eb_mc_bind of its
+ * own allocation, (barrier), eb_vmm_map of the multicast handle. File descriptors travel over a Unix socket
+ * (parallel/symm.py). No counterpart in the reference (Spark broadcast / collect, elephas/spark_model.py:206-227). */
+int eb_vmm_supported(int32_t* vmm_out, int32_t* multicast_out);
+int eb_vmm_create(int64_t bytes, int32_t multicast_ranks, uint64_t* handle_out, int64_t* size_out);
+int eb_vmm_export_fd(uint64_t handle, int32_t* fd_out);
+int eb_vmm_import_fd(int32_t fd, uint64_t* handle_out);
+int eb_vmm_map(uint64_t handle, int64_t size, void** ptr_out);
+int eb_vmm_unmap(void* ptr, int64_t size);
+int eb_vmm_release(uint64_t handle);
+int eb_mc_create(int32_t ranks, int64_t size, uint64_t* handle_out);
+int eb_mc_add_device(uint64_t mc_handle);
+int eb_mc_bind(uint64_t mc_handle, uint64_t mem_handle, int64_t size);
 
 /* ------------------------------------------------------------ memory / IPC plumbing */
 int eb_device_malloc(void** ptr, int64_t bytes);   /* cudaMalloc + zero fill (IPC-exportable) */

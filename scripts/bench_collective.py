@@ -18,7 +18,7 @@ import torch  # noqa: E402
 
 from elephas_b200.ops import native  # noqa: E402
 from elephas_b200.parallel import get_runtime  # noqa: E402
-from elephas_b200.parallel.symm import SymmetricMemory  # noqa: E402
+from elephas_b200.parallel.symm import SymmetricMemory, VmmSymmetricMemory  # noqa: E402
 
 N_ELEMS = int(os.environ.get('COLL_ELEMS', 134254592))
 STEPS, WARM = int(os.environ.get('COLL_STEPS', 20)), 3
@@ -35,10 +35,32 @@ def main():
     for name in ('delta0', 'delta1'):
         mem.local(name, torch.bfloat16, n).normal_()
     variants = [('shard_update', blocks) for blocks in (16, 32, 74, 148)] + [('twoshot_update', 148)]
+    vm = None
+    if os.environ.get('COLL_NVLS', '1') != '0' and W > 1:
+        try:
+            vm = VmmSymmetricMemory(rt, {'delta0': n * 2, 'delta1': n * 2, 'w16': n * 2, 'pad': 256}, multicast=True)
+            if not vm.multicast:
+                vm.close()
+                vm = None
+        except native.NativeError as exc:
+            if rt.is_driver:
+                print('no NVLS arm: %s' % exc, file=sys.stderr)
+        if not all(rt.all_gather_object(vm is not None)):
+            if vm is not None:
+                vm.close()
+            vm = None
+    if vm is not None:
+        for name in ('delta0', 'delta1'):
+            vm.local(name, torch.bfloat16, n).normal_()
+        vlocal = torch.zeros(16, dtype=torch.int32, device=rt.device)
+        variants += [('nvls_update', blocks) for blocks in (8, 16, 32, 74)]
     for kind, blocks in variants:
         def call(flip):
             common = (mem.ptrs('delta%d' % flip), mem.ptrs('pad'), local, n, R, W, 1.0 / W, True, w32)
-            if kind == 'shard_update':
+            if kind == 'nvls_update':
+                native.allreduce_nvls_update(vm.mc_ptr('delta%d' % flip), vm.mc_ptr('w16'), vm.ptrs('pad'), vlocal, n, R, W,
+                                             1.0 / W, w32, blocks=blocks, device=rt.device)
+            elif kind == 'shard_update':
                 native.allreduce_shard_update(*common, mem.ptrs('w16'), blocks=blocks, device=rt.device)
             else:
                 native.allreduce_update(*common, w16=mem.local('w16', torch.bfloat16, n), avg_ptrs=mem.ptrs('avg'), algo=2,
@@ -70,6 +92,8 @@ def main():
                   flush=True)
     status = int(local[8].item())
     assert status == 0, "watchdog fired: peer %d" % (status - 1)
+    if vm is not None:
+        vm.close()
     mem.close()
     rt.shutdown()
 

@@ -108,6 +108,53 @@ for n in (1 << 12, (1 << 22) + 64):
     mem.close()
     log("allreduce_shard_update n=%d ok (max err %.2e)" % (n, err))
 
+# ---- 1c. NVLS variant: VMM allocations + multicast object, the switch adds the deltas (skipped without multicast) ----
+from elephas_b200.parallel.symm import VmmSymmetricMemory  # noqa: E402
+
+vmm_ok, mc_ok = native.vmm_supported()
+if all(rt.all_gather_object(vmm_ok)):
+    n = 1 << 21
+    vm = VmmSymmetricMemory(rt, {'delta0': n * 2, 'delta1': n * 2, 'w16': n * 2, 'pad': 256}, multicast=True)
+    # peer mappings through imported file descriptors: every rank reads what every other rank wrote
+    vm.local('delta0', torch.bfloat16, n).fill_(float(R + 1))
+    torch.cuda.synchronize()
+    rt.barrier()
+    for r in range(W):
+        peer = native.tensor_from_ptr(vm.ptrs('delta0')[r], torch.bfloat16, 8, rt.device)
+        assert float(peer[0]) == float(r + 1), (r, peer[:4])
+    rt.barrier()
+    if vm.multicast:
+        local = torch.zeros(16, dtype=torch.int32, device=rt.device)
+        w32 = torch.ones(n, device=rt.device)
+        expect = torch.ones(n, device=rt.device)
+        for it in range(4):
+            name = 'delta%d' % (it % 2)
+            d = torch.randn(n, generator=torch.Generator().manual_seed(300 * it + R)).to(torch.bfloat16)
+            vm.local(name, torch.bfloat16, n).copy_(d.to(rt.device))
+            parts = [torch.randn(n, generator=torch.Generator().manual_seed(300 * it + r)).to(torch.bfloat16).float()
+                     for r in range(W)]
+            expect -= (sum(parts) / W).to(rt.device)
+            native.allreduce_nvls_update(vm.mc_ptr(name), vm.mc_ptr('w16'), vm.ptrs('pad'), local, n, R, W, 1.0 / W, w32,
+                                         blocks=8, device=rt.device)
+        torch.cuda.synchronize()
+        rt.barrier()
+        n8 = n // 8
+        per = -(-n8 // W)
+        a, b = per * R * 8, min(n8, per * (R + 1)) * 8
+        # the switch returns the sum rounded to bf16 (fp32 accumulation inside): one extra bf16 rounding per step
+        err = (w32[a:b] - expect[a:b]).abs().max().item()
+        assert err < 4 * 0.02, err
+        w16 = vm.local('w16', torch.bfloat16, n)
+        assert torch.equal(w16[a:b], w32[a:b].to(torch.bfloat16))  # my slice, written through the multicast store
+        same_on_all_ranks([w16.float().cpu().numpy()])              # ... and everybody else's arrived here too
+        assert int(local[8].item()) == 0
+        log("allreduce_nvls_update n=%d ok (max err %.2e): multimem.ld_reduce / multimem.st over %d GPUs" % (n, err, W))
+    else:
+        log("VMM symmetric memory ok; no multicast support on this node: NVLS kernel skipped")
+    vm.close()
+else:
+    log("VMM file-descriptor export not supported here: skipped")
+
 # ---- 2. P2P sum all-reduce used by the generic path --------------------------------------------------
 flat = torch.full((1000,), float(R + 1), device=rt.device)
 out = all_reduce_sum(rt, flat)

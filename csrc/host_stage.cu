@@ -22,22 +22,9 @@
 
 namespace eb {
 
-// Round-to-nearest-even fp32 -> bf16, NaN -> 0x7FFF: what __float2bfloat16_rn produces on the device.
-__attribute__((target_clones("avx512f", "avx2", "default")))
-static void convert_rows(const float* src, int64_t ld_src, uint16_t* dst, int64_t ld_dst, int64_t r0, int64_t r1,
-                         int32_t cols) {
-  for (int64_t r = r0; r < r1; ++r) {
-    const uint32_t* s = reinterpret_cast<const uint32_t*>(src + r * ld_src);
-    uint16_t* d = dst + r * ld_dst;
-    for (int32_t c = 0; c < cols; ++c) {
-      uint32_t u = s[c];
-      const uint32_t rounded = u + 0x7FFFu + ((u >> 16) & 1u);
-      const bool nan = (u & 0x7FFFFFFFu) > 0x7F800000u;
-      d[c] = nan ? static_cast<uint16_t>(0x7FFFu) : static_cast<uint16_t>(rounded >> 16);
-    }
-    for (int64_t c = cols; c < ld_dst; ++c) d[c] = 0;  // padding columns the GEMM's TMA boxes may touch
-  }
-}
+// Row conversion with explicit AVX-512 / AVX2 intrinsics and non-temporal stores: host_cast.cpp
+void convert_rows(const float* src, int64_t ld_src, uint16_t* dst, int64_t ld_dst, int64_t r0, int64_t r1, int32_t cols);
+const char* host_cast_isa();
 
 // Persistent worker pool: run(fn, n) executes fn(i) for i in [0, n) on the workers plus the calling thread.
 class HostPool {
@@ -107,10 +94,17 @@ class HostPool {
 static HostPool* g_pool = nullptr;
 static std::mutex g_pool_mutex;
 
-static HostPool* pool_for(int threads) {
-  std::lock_guard<std::mutex> g(g_pool_mutex);
-  // created once, sized by the first caller (later calls share it, whatever thread count they ask for)
-  if (g_pool == nullptr) g_pool = new HostPool(threads > 1 ? threads - 1 : 0);
+// One pool per process, grown when a caller asks for more threads than it has. Jobs are serialised by g_pool_mutex
+// (one batch at a time anyway), so a pool is never replaced while a job runs on it.
+static HostPool* pool_for_locked(int threads) {  // caller holds g_pool_mutex (also while it runs its job on the pool)
+  const int workers = threads > 1 ? threads - 1 : 0;
+  if (g_pool == nullptr) {
+    g_pool = new HostPool(workers);
+  } else if (g_pool->workers() < workers) {
+    HostPool* old = g_pool;
+    g_pool = new HostPool(workers);
+    delete old;  // idle: joins its workers
+  }
   return g_pool;
 }
 
@@ -135,6 +129,9 @@ extern "C" int eb_host_f32_to_bf16(const float* src, int64_t ld_src, void* dst, 
     const int64_t r0 = i * chunk, r1 = r0 + chunk < rows ? r0 + chunk : rows;
     convert_rows(src, ld_src, out, ld_dst, r0, r1, cols);
   };
-  pool_for(threads)->run(fn, items);
+  std::lock_guard<std::mutex> g(g_pool_mutex);
+  pool_for_locked(threads)->run(fn, items);
   return 0;
 }
+
+extern "C" const char* eb_host_cast_isa() { return eb::host_cast_isa(); }

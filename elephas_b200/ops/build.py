@@ -21,7 +21,7 @@ LIB_PATH = os.path.join(LIB_DIR, 'libelephas_b200.so')
 OBJ_DIR = os.path.join(ROOT, 'build', 'obj')
 
 SOURCES = ['core.cu', 'gemm_sm100.cu', 'elementwise.cu', 'loss_kernels.cu', 'optim_kernels.cu', 'comm_kernels.cu', 'ps_kernels.cu', 'conv_sm100.cu', 'conv_aux.cu', 'vmm.cu',
-           'host_stage.cu', 'narrow_head.cu', 'mlp_fused.cu']
+           'host_stage.cu', 'host_cast.cpp', 'narrow_head.cu', 'mlp_fused.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-Xcompiler', '-fPIC',
               '-DNDEBUG']
 
@@ -52,12 +52,16 @@ def _digest(path):
 
 def _compile_one(src, verbose):
     path = os.path.join(CSRC, src)
-    obj = os.path.join(OBJ_DIR, src.replace('.cu', '.o'))
+    obj = os.path.join(OBJ_DIR, src.replace('.cu', '.o').replace('.cpp', '.o'))
     stamp = obj + '.sha'
     digest = _digest(path)
     if os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == digest:
         return obj, False
-    cmd = [_nvcc()] + NVCC_FLAGS + ['-I', INCLUDE, '-c', path, '-o', obj]
+    if src.endswith('.cpp'):
+        # plain host code (explicit SIMD with per-function target attributes): the host compiler alone
+        cmd = [shutil.which('g++') or 'g++', '-O3', '-std=c++17', '-fPIC', '-DNDEBUG', '-I', INCLUDE, '-c', path, '-o', obj]
+    else:
+        cmd = [_nvcc()] + NVCC_FLAGS + ['-I', INCLUDE, '-c', path, '-o', obj]
     if verbose:
         print(' '.join(cmd), flush=True)
     subprocess.run(cmd, check=True)

@@ -169,6 +169,7 @@ def load():
                                          c_void_p, c_int32, c_void_p, c_void_p, c_int32, c_void_p]
         lib.eb_bn_bwd_apply.argtypes = [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p,
                                         c_void_p, c_void_p, c_int32, c_void_p, c_void_p, c_void_p]
+        lib.eb_host_cast_isa.restype = ctypes.c_char_p
         lib.eb_host_f32_to_bf16.argtypes = [c_void_p, c_int64, c_void_p, c_int64, c_int64, c_int32, c_int32]
         lib.eb_allreduce_nvls_update.argtypes = [c_void_p, c_void_p]
         lib.eb_vmm_supported.argtypes = [ctypes.POINTER(c_int32), ctypes.POINTER(c_int32)]

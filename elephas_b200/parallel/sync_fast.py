@@ -90,8 +90,12 @@ class _InputFeeder:
     on the copy stream, record an event the compute stream waits on.
     """
 
-    def __init__(self, eng, x, y, batch_size, mode, shuffle):
+    def __init__(self, eng, x, y, batch_size, mode, shuffle, x16=None):
         self.eng, self.bs, self.shuffle = eng, batch_size, shuffle
+        # features already staged as bf16 in pinned memory by the caller (to_sharded_rdd(feature_dtype='bfloat16')): they
+        # are streamed as they are - half the PCIe bytes of the fp32 stream, no per-step CPU work
+        self.staged16 = x16 if (x16 is not None and x16.dtype == torch.bfloat16 and len(x16) == len(x)
+                                and x16.shape[1] == eng.ops[0].ld_in) else None
         dev = eng.device
         n = len(x)
         self.n = n
@@ -113,8 +117,16 @@ class _InputFeeder:
             self.copy_stream = torch.cuda.Stream(dev)
             cols, ycols = self.x_host.shape[1], self.y_host.shape[1]
             self.threads = _host_threads()
-            self.host_bf16 = self._choose_host_bf16(eng, batch_size)
-            if self.host_bf16:
+            self.host_bf16 = self.staged16 is None and self._choose_host_bf16(eng, batch_size)
+            if self.staged16 is not None:
+                if not self.staged16.is_pinned():
+                    self.staged16 = self.staged16.pin_memory()
+                ld = eng.ops[0].ld_in
+                self.stage = [(torch.empty(batch_size, ld, dtype=torch.bfloat16, device=dev),
+                               torch.empty(batch_size, ycols, dtype=torch.float32, device=dev),
+                               torch.cuda.Event()) for _ in range(2)]
+                self.h2d_bytes_per_step = batch_size * (ld * 2 + ycols * 4)
+            elif self.host_bf16:
                 ld = eng.ops[0].ld_in
                 self.pinned = [torch.empty(batch_size, ld, dtype=torch.bfloat16).pin_memory() for _ in range(3)]
                 self.pinned_free = [None, None, None]  # event: the slot's last H2D copy has finished
@@ -197,10 +209,11 @@ class _InputFeeder:
                 self._prefetch(0, 0)
 
     def _host_batch(self, start, rows):
+        xsrc = self.staged16 if self.staged16 is not None else self.x_host
         if self.order is None:
-            return self.x_host[start:start + rows], self.y_host[start:start + rows]
+            return xsrc[start:start + rows], self.y_host[start:start + rows]
         idx = self.order[start:start + rows]
-        return self.x_host.index_select(0, idx).pin_memory(), self.y_host.index_select(0, idx).pin_memory()
+        return xsrc.index_select(0, idx).pin_memory(), self.y_host.index_select(0, idx).pin_memory()
 
     # -- fp32 streaming (ELEPHAS_B200_HOST_BF16=0) ---------------------------------------------------------
     def _prefetch(self, step, start):
@@ -268,6 +281,9 @@ class _InputFeeder:
         cur = torch.cuda.current_stream(self.eng.device)
         if self.host_bf16:
             self.jobs.pop(step).result()  # converted and enqueued (normally long done: it ran during step - 2)
+            cur.wait_event(ev)
+            buf.x16.copy_(xs[:rows])
+        elif self.staged16 is not None:
             cur.wait_event(ev)
             buf.x16.copy_(xs[:rows])
         else:
@@ -512,6 +528,7 @@ class SyncContext:
         cfg = dict(train_config)
         with tracing.span('sync/partition_to_arrays'):
             x, y = partition_to_arrays(partition)
+        x16 = getattr(partition, 'x16', None)
         bs = self.bs = int(cfg.get('batch_size') or 32)
         epochs = int(cfg.get('epochs', 1))
         split = float(cfg.get('validation_split') or 0.0)
@@ -520,6 +537,7 @@ class SyncContext:
         if 0.0 < split < 1.0:
             at = int(len(x) * (1.0 - split))
             x, x_val, y, y_val = x[:at], x[at:], y[:at], y[at:]
+            x16 = x16[:at] if x16 is not None else None
         trainable = n_all > bs and len(x) > 0  # reference guard (worker.py:41)
         log_batch_loss = bool(cfg.get('log_batch_loss', False))
         batch_losses = []
@@ -542,9 +560,10 @@ class SyncContext:
             if distributed:
                 steps = int(rt.all_reduce_max_(torch.tensor([steps_local], device=rt.device))[0])
             with tracing.span('sync/input_feeder'):
-                feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True))) \
+                feeder = _InputFeeder(eng, x, y, bs, cfg.get('input_mode'), bool(cfg.get('shuffle', True)), x16=x16) \
                     if trainable else None
-            eng.input_bf16 = bool(feeder is not None and feeder.host_bf16)
+            eng.input_bf16 = bool(feeder is not None and feeder.mode == 'stream'
+                                  and (feeder.host_bf16 or feeder.staged16 is not None))
             names = self.model.metrics_names
             pinned = [torch.zeros(8, dtype=torch.float64).pin_memory() for _ in range(2)]
             events = [torch.cuda.Event() for _ in range(2)]

@@ -23,10 +23,13 @@ import numpy as np
 class PairBlock:
     """A partition of ``(x_i, y_i)`` rows held as two arrays with equal leading dimension."""
 
-    def __init__(self, x, y):
+    def __init__(self, x, y, x16=None):
         if len(x) != len(y):
             raise ValueError("features and labels differ in length: %d vs %d" % (len(x), len(y)))
         self.x, self.y = x, y
+        # optional: the same features already cast to bf16 in pinned host memory ([rows, round_up(cols, 8)] torch tensor,
+        # see rdd_utils.to_sharded_rdd(feature_dtype='bfloat16')): bf16 models stream these - half the PCIe bytes
+        self.x16 = x16
 
     def __len__(self):
         return len(self.x)
@@ -36,7 +39,7 @@ class PairBlock:
 
     def __getitem__(self, item):
         if isinstance(item, slice):
-            return PairBlock(self.x[item], self.y[item])
+            return PairBlock(self.x[item], self.y[item], self.x16[item] if self.x16 is not None else None)
         return (self.x[item], self.y[item])
 
 

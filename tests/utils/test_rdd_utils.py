@@ -56,3 +56,25 @@ def test_lp_to_simple_rdd_one_hot_regression_and_inferred_width(spark_context):
     # regression: the label passes through as a scalar
     plain = rdd_utils.lp_to_simple_rdd(lp_rdd, categorical=False).collect()
     assert [float(r[1]) for r in plain] == [float(c) for c in classes_of]
+
+
+def test_sharded_rdd_can_stage_features_as_bf16(spark_context):
+    """``to_sharded_rdd(feature_dtype='bfloat16')`` keeps, next to the fp32 rows, a bf16 copy of the shard (round to
+    nearest even, rows padded to a multiple of 8 columns with zeros) that bf16 models stream to the GPU as it is."""
+    import torch
+    from elephas_b200.ops import native
+    if not native.available():
+        pytest.skip("native library not built")
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(50, 93)).astype(np.float32)
+    x[0, 0], x[1, 1] = np.inf, -0.0
+    y = rng.normal(size=(50, 2)).astype(np.float32)
+    rdd = rdd_utils.to_sharded_rdd(spark_context, x, y, rank=0, world_size=2, feature_dtype='bfloat16')
+    mine, other = rdd.partitions()
+    assert len(other) == 0 and len(mine) == 50 and np.array_equal(mine.x, x)
+    assert mine.x16.dtype == torch.bfloat16 and tuple(mine.x16.shape) == (50, 96)
+    assert torch.equal(mine.x16[:, :93], torch.from_numpy(x).to(torch.bfloat16)) and bool((mine.x16[:, 93:] == 0).all())
+    part = mine[10:20]
+    assert len(part) == 10 and torch.equal(part.x16, mine.x16[10:20])
+    with pytest.raises(ValueError):
+        rdd_utils.to_sharded_rdd(spark_context, x, y, rank=0, world_size=2, feature_dtype='float16')

@@ -302,6 +302,8 @@ def _emulated_ranks(n, world, dtype, seed):
     deltas = [torch.randn(n, device='cuda').to(dtype) for _ in range(world)]
     # flags far in the future: no launch ever waits for another one (ranks emulated on one GPU run one after another)
     pads = [torch.full((64,), 1 << 30, dtype=torch.int32, device='cuda') for _ in range(world)]
+    for r, pad in enumerate(pads):
+        pad[8 + r] = 0  # ... except a rank's own phase flag: its blocks really wait for one another's stores
     mean = sum(d.float() for d in deltas) / world
     return deltas, pads, mean
 

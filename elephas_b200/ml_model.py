@@ -193,7 +193,6 @@ class ElephasTransformer(Model, HasKerasModelConfig, HasLabelCol, HasOutputCol, 
         output_col = self.getOutputCol()
         features_col = self.getFeaturesCol()
         new_schema = copy.deepcopy(df.schema)
-        rdd = df.rdd
         model = self._model_for_predict()
         inference_batch_size = self.get_inference_batch_size()
 
@@ -238,7 +237,7 @@ class ElephasTransformer(Model, HasKerasModelConfig, HasLabelCol, HasOutputCol, 
             values = block[:, 0].tolist() if regression else block.tolist()
             return [tuple(r) + (v,) for r, v in zip(rows, values)]
 
-        results_rdd = rdd.mapPartitions(predict_rows)
+        results_rdd = df.rdd.mapPartitions(predict_rows)  # (rows are only materialised on this path)
         output_field = StructField(output_col, DoubleType() if regression else ArrayType(DoubleType()), True)
         new_schema.add(output_field)
         return SparkSession.builder.getOrCreate().createDataFrame(results_rdd, new_schema)

@@ -158,7 +158,13 @@ class TorchSyncContext:
                         self._unpack(packed, bufs)
                 self._setup_comm()
             with tracing.span('sync_torch/h2d'):
-                xt = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(rt.device) if trainable else None
+                x16 = getattr(partition, 'x16', None)  # pinned bf16 copy staged once by to_sharded_rdd(feature_dtype=...)
+                if (trainable and torch.is_tensor(x16) and x16.dtype == torch.bfloat16 and len(x16) == len(x)
+                        and x16.shape[1] == int(np.prod(x.shape[1:])) and rt.device.type == 'cuda'
+                        and getattr(model, '_compute_dtype', 'float32') == 'bfloat16'):
+                    xt = x16.to(rt.device, non_blocking=True).view(x.shape)  # half the bytes, no pageable bounce
+                else:
+                    xt = torch.as_tensor(np.ascontiguousarray(x, dtype=np.float32)).to(rt.device) if trainable else None
                 yt = torch.as_tensor(np.ascontiguousarray(y, dtype=np.float32)).to(rt.device) if trainable else None
             per_batch = distributed and self.sm.frequency == 'batch' and sync_rounds != 'fit'
             if per_batch:

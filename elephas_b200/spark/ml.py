@@ -386,6 +386,12 @@ class StringIndexerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadable
         if hasattr(dataset, 'with_block_column') and self.getOutputCol() not in dataset.columns:
             # one pass over the label column, the indices appended as a block (rows are only rebuilt on demand)
             from .sql import DoubleType as _DoubleType
+            factor = dataset.column_factor(self.getInputCol()) if hasattr(dataset, 'column_factor') else None
+            if factor is not None:
+                # the column factorised once per frame (cached there): one table lookup per DISTINCT label, then a gather
+                uniques, inverse = factor
+                table = np.asarray([index[str(u)] for u in uniques.tolist()], dtype=np.float64)
+                return dataset.with_block_column(self.getOutputCol(), table[inverse], _DoubleType())
             i, get = dataset.columns.index(self.getInputCol()), tuple.__getitem__
             rows = dataset.rdd.collect()
             if rows and isinstance(rows[0], tuple):
@@ -405,8 +411,13 @@ class StringIndexer(Estimator, HasInputCol, HasOutputCol, DefaultParamsReadable,
     def _fit(self, dataset):
         i = dataset.columns.index(self.getInputCol())
         counts = {}
-        for r in dataset.collect():
-            counts[str(r[i])] = counts.get(str(r[i]), 0) + 1
+        factor = dataset.column_factor(self.getInputCol()) if hasattr(dataset, 'column_factor') else None
+        if factor is not None:
+            for u, c in zip(factor[0].tolist(), np.bincount(factor[1], minlength=len(factor[0])).tolist()):
+                counts[str(u)] = counts.get(str(u), 0) + c
+        else:
+            for r in dataset.collect():
+                counts[str(r[i])] = counts.get(str(r[i]), 0) + 1
         labels = [k for k, _ in sorted(counts.items(), key=lambda kv: (-kv[1], kv[0]))]
         return StringIndexerModel(labels, self.getInputCol(), self.getOutputCol())
 
@@ -433,7 +444,9 @@ class StandardScalerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadabl
             if block is not None and block.ndim == 2:
                 # the whole column as one matrix in, one matrix out: later stages read the block, rows are built lazily
                 from .sql import VectorUDT as _VectorUDT
-                return dataset.with_block_column(self.getOutputCol(), (block - mean) * scale, _VectorUDT())
+                out = np.subtract(block, mean, dtype=np.float64)  # one temporary, scaled in place
+                out *= scale
+                return dataset.with_block_column(self.getOutputCol(), out, _VectorUDT())
         blocked = self._transform_blocks(dataset, mean, scale)
         if blocked is not None:
             return blocked

@@ -277,6 +277,25 @@ class DataFrame:
             self._block_cache[name] = cached
         return cached
 
+    def column_factor(self, name):
+        """``(uniques, inverse)`` of a scalar column (``np.unique(..., return_inverse=True)``), built from the rows once and
+        cached: what a label indexer needs, without a Python-level lookup per row on later passes. None when the values do
+        not sort (mixed types)."""
+        key = ('factor', name)
+        if key not in self._block_cache:
+            if self._rdd is None and self._base is not None and name in self._base.columns and name not in self._blocks:
+                return self._base.column_factor(name)
+            i, get = self._col_index(name), tuple.__getitem__
+            rows = self.rdd.collect()
+            vals = [get(r, i) for r in rows] if rows and isinstance(rows[0], tuple) else [r[i] for r in rows]
+            try:
+                arr = np.asarray(vals)
+                self._block_cache[key] = np.unique(arr, return_inverse=True) if arr.ndim == 1 and arr.dtype != object \
+                    else None
+            except TypeError:
+                self._block_cache[key] = None
+        return self._block_cache[key]
+
     def _materialize_rows(self):
         from .linalg import DenseVector
         base_rdd = self._base.rdd

@@ -289,17 +289,19 @@ def run_sync(args, rt):
             rt.barrier()
             wall_ms = (time.perf_counter() - t0) * 1e3
             dev_ms = spark_model._last_sync_run.get('device_ms', wall_ms)
+            if tracing.enabled() and rt.is_driver:
+                print('--- phases of the timed fit, host features %s (wall %.3f ms, device %.3f ms)\n%s'
+                      % (feature_dtype or 'float32', wall_ms, dev_ms, tracing.report()), file=sys.stderr)
             ms = max_over_ranks(rt, max(wall_ms, dev_ms))
             hist = spark_model.training_histories[-1]
             assert len(hist['batch_loss']) == Ke, "one loss read-back per step expected"
             return {'value': round(N * B * Ke / (ms / 1e3), 2), 'unit': 'samples/sec', 'ms_per_step': round(ms / Ke, 4),
                     'steps': Ke, 'h2d_bytes_per_step': int(spark_model._last_sync_run['h2d_bytes_per_step']),
                     'd2h_bytes_per_step': 64, 'host_features': feature_dtype or 'float32',
+                    'device_ms_per_step_inside_fit': round(max_over_ranks(rt, dev_ms) / Ke, 4),
                     'timing': 'wall clock around SparkModel.fit incl. setup, max over ranks'}
 
         e2e_fp32 = timed_fit(None)
-        if tracing.enabled() and rt.is_driver:
-            print(tracing.report(), file=sys.stderr)
         e2e = timed_fit('bfloat16') if os.environ.get('BENCH_E2E_BF16', '1') != '0' else e2e_fp32
     ms_total = max_over_ranks(rt, ms_kernel)
     value = N * B * K / (ms_total / 1e3)
@@ -314,6 +316,9 @@ def run_sync(args, rt):
                    if args.config == 'wide_mlp' else args.config,
                    'global_batch': N * B, 'seq_len': None, 'parallelism': 'dp%d' % N,
                    'mode': 'synchronous', 'frequency': 'batch', 'optimizer': 'SGD',
+                   'collective': ('none (one GPU)' if N == 1 else
+                                  'fused all-reduce + update kernel, ' + ('NVLS multimem' if getattr(ctx, 'nvls', False)
+                                                                         else 'peer-to-peer loads / stores')),
                    'l2': 'working set (weights+grads+activations, >1 GB) exceeds the 126 MB L2; no flush needed'},
         'clocks': clocks, 'e2e': e2e, 'e2e_fp32_host_features': e2e_fp32, 'gpu_launches': int(launches),
         'tflops_per_gpu': round(flops_step / (ms_total / K / 1e3) / 1e12, 1),

@@ -586,6 +586,94 @@ def run_torch(args, rt):
                                  'final_loss': round(final_loss, 6), 'replicas_identical': bool(identical)}))
 
 
+def run_torch_resnet(args, rt):
+    """Library baseline for config 5: torchvision's ResNet-50 (the same architecture, 25.6 M parameters), channels-last,
+    bf16 autocast with fp32 master weights, fused SGD with momentum, cuDNN convolutions, DistributedDataParallel over NCCL
+    at N > 1 (gradient buckets overlapped with backward), the step replayed from a CUDA graph on one GPU. Batch 64 per
+    GPU, 224 x 224, a fresh device-resident batch every step; device-timed with CUDA events, max over ranks."""
+    import torch
+    import torch.nn as nn
+    from torchvision.models import resnet50
+    N, dev = rt.world_size, rt.device
+    B = args.batch_per_gpu or 64
+    K, W = args.steps, max(args.warmup, 3)
+    torch.manual_seed(5)
+    net = resnet50(num_classes=1000).to(dev).to(memory_format=torch.channels_last)
+    if N > 1:
+        import torch.distributed as dist
+        for t in list(net.parameters()) + list(net.buffers()):
+            dist.broadcast(t.data, src=0)
+    wrapped = nn.parallel.DistributedDataParallel(net, device_ids=[dev.index], gradient_as_bucket_view=True) \
+        if N > 1 else net
+    opt = torch.optim.SGD(net.parameters(), lr=0.01, momentum=0.9, fused=True)
+    loss_fn = nn.CrossEntropyLoss()
+    gen = torch.Generator(device=dev).manual_seed(7 + rt.rank)
+    DISTINCT = 8
+    xs = torch.randn(DISTINCT * B, 3, 224, 224, device=dev, generator=gen).to(memory_format=torch.channels_last)
+    ys = torch.randint(0, 1000, (DISTINCT * B,), device=dev, generator=gen)
+    xb, yb = torch.empty_like(xs[:B]), torch.empty_like(ys[:B])
+    loss_box = torch.zeros((), device=dev)
+
+    def step():
+        opt.zero_grad(set_to_none=False)
+        with torch.autocast('cuda', dtype=torch.bfloat16):
+            out = wrapped(xb)
+        loss = loss_fn(out.float(), yb)
+        loss.backward()
+        opt.step()
+        loss_box.copy_(loss.detach())
+
+    def load(i):
+        lo = (i % DISTINCT) * B
+        xb.copy_(xs[lo:lo + B])
+        yb.copy_(ys[lo:lo + B])
+
+    for i in range(max(W, 11)):
+        load(i)
+        step()
+    torch.cuda.synchronize()
+    graph = None
+    if N == 1 and os.environ.get('BENCH_TORCH_GRAPH', '1') != '0':
+        try:
+            g, side = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                with torch.cuda.graph(g, stream=side):
+                    step()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = g
+        except Exception as exc:
+            print('torch ResNet arm: CUDA-graph capture failed (%s); running eagerly' % (str(exc).splitlines()[0],),
+                  file=sys.stderr)
+            torch.cuda.synchronize()
+    rt.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(rt.local_rank)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(K):
+        load(i)
+        if graph is not None:
+            graph.replay()
+        else:
+            step()
+    e1.record()
+    torch.cuda.synchronize()
+    sampler.stop_flag.set()
+    rt.barrier()
+    ms = max_over_ranks(rt, e0.elapsed_time(e1))
+    if rt.is_driver:
+        print_result(json.dumps({'metric': METRIC, 'value': round(N * B * K / (ms / 1e3), 2), 'unit': 'samples/sec',
+                                 'n_gpus': N, 'steps': K, 'warmup': W, 'ms_per_step': round(ms / K, 4),
+                                 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16',
+                                 'data': 'synthetic', 'impl': args.impl,
+                                 'config': {'model': 'resnet50 (torchvision, channels-last, cuDNN)', 'global_batch': N * B,
+                                            'parallelism': 'dp%d' % N, 'cuda_graph': graph is not None,
+                                            'optimizer': 'SGD momentum fused'},
+                                 'clocks': sampler.summary(), 'gpu_launches': 0, 'final_loss': round(float(loss_box), 4)}))
+
+
 def main():
     args = parse()
     sys.stdout.flush()
@@ -607,7 +695,9 @@ def main():
         print("warning: --gpus %d but WORLD_SIZE=%d; launch with torch.distributed.run" % (args.gpus, rt.world_size),
               file=sys.stderr)
     mode = args.mode or {'mnist_mlp': 'asynchronous'}.get(args.config, 'synchronous')
-    if args.impl in ('ddp', 'localsgd'):
+    if args.impl == 'ddp' and args.config == 'resnet50':
+        run_torch_resnet(args, rt)
+    elif args.impl in ('ddp', 'localsgd'):
         run_torch(args, rt)
     elif args.config in ('otto_pipeline', 'resnet50'):
         run_config_script(args, rt)

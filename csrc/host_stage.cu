@@ -27,6 +27,9 @@ void convert_rows(const float* src, int64_t ld_src, uint16_t* dst, int64_t ld_ds
 const char* host_cast_isa();
 
 // Persistent worker pool: run(fn, n) executes fn(i) for i in [0, n) on the workers plus the calling thread.
+// All job state (fn_, total_, next_) is written under m_ while no worker is inside drain(): a worker enters drain() only
+// after it has seen a live job under m_ (active_ counts the workers inside), and run() returns only when every item is
+// done AND active_ is back to zero. (Checked with ThreadSanitizer: tests/native/tsan_host_pool.cpp.)
 class HostPool {
  public:
   explicit HostPool(int workers) {
@@ -47,16 +50,16 @@ class HostPool {
     {
       std::lock_guard<std::mutex> g(m_);
       fn_ = &fn;
-      next_.store(0);
       total_ = n;
       pending_ = n;
+      next_.store(0);
       ++generation_;
     }
     cv_.notify_all();
     drain();
     std::unique_lock<std::mutex> g(m_);
-    done_cv_.wait(g, [this] { return pending_ == 0; });
-    fn_ = nullptr;
+    done_cv_.wait(g, [this] { return pending_ == 0 && active_ == 0; });
+    fn_ = nullptr;  // a worker that wakes up late finds no job
   }
 
  private:
@@ -66,7 +69,7 @@ class HostPool {
       if (i >= total_) return;
       (*fn_)(i);
       std::lock_guard<std::mutex> g(m_);
-      if (--pending_ == 0) done_cv_.notify_all();
+      if (--pending_ == 0 && active_ == 0) done_cv_.notify_all();
     }
   }
   void loop() {
@@ -77,8 +80,12 @@ class HostPool {
         cv_.wait(g, [&] { return stop_ || generation_ != seen; });
         if (stop_) return;
         seen = generation_;
+        if (fn_ == nullptr) continue;  // that job is over already
+        ++active_;
       }
       drain();
+      std::lock_guard<std::mutex> g(m_);
+      if (--active_ == 0 && pending_ == 0) done_cv_.notify_all();
     }
   }
   std::vector<std::thread> threads_;
@@ -86,7 +93,7 @@ class HostPool {
   std::condition_variable cv_, done_cv_;
   const std::function<void(int)>* fn_ = nullptr;
   std::atomic<int> next_{0};
-  int total_ = 0, pending_ = 0;
+  int total_ = 0, pending_ = 0, active_ = 0;
   uint64_t generation_ = 0;
   bool stop_ = false;
 };

@@ -159,6 +159,11 @@ class TorchStepEngine:
             self.stats[7] += float(x.shape[0])
 
     def _record(self, key, x, y):
+        from ..utils import tracing
+        with tracing.span('torch_step/capture'):
+            return self._record_inner(key, x, y)
+
+    def _record_inner(self, key, x, y):
         sx, sy = torch.empty_like(x), torch.empty_like(y)
         sx.copy_(x)
         sy.copy_(y)

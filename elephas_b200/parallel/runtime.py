@@ -117,6 +117,25 @@ class Runtime:
         self._dist.all_gather_object(out, obj)
         return out
 
+    def all_true(self, flag):
+        """``all(flag over ranks)`` with one small all-reduce (no pickling, one device->host read)."""
+        if not self.distributed:
+            return bool(flag)
+        import torch
+        t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=self.device)
+        self._dist.all_reduce(t, op=self._dist.ReduceOp.MIN)
+        return bool(int(t.item()))
+
+    def all_gather_rows(self, row):
+        """``row`` (1-D tensor of the same length on every rank) from all ranks as ``[world, len]`` on the host."""
+        import torch
+        if not self.distributed:
+            return row.detach().cpu().unsqueeze(0)
+        src = row.to(self.device)
+        out = torch.empty((self.world_size,) + tuple(src.shape), dtype=src.dtype, device=self.device)
+        self._dist.all_gather_into_tensor(out, src)
+        return out.cpu()
+
     def broadcast_object(self, obj, src=0):
         if not self.distributed:
             return obj

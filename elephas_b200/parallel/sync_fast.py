@@ -37,6 +37,36 @@ from .symm import SymmetricMemory, VmmSymmetricMemory
 IN_PLACE = object()  # returned instead of a weight list: the master network already holds the result
 
 
+def _gather_histories(rt, hist, keys, width):
+    """Every rank's history dict (or None), in rank order, on every rank. The values travel as ONE float64 row per rank
+    (``[trainable, then per key: count, values...]``, one all-gather) instead of pickled objects: ``keys`` lists every
+    name a history of this fit can hold, in the order the dict has them; no list is longer than ``width``."""
+    row = torch.zeros(1 + len(keys) * (1 + width), dtype=torch.float64)
+    if hist is not None:
+        unknown = [k for k in hist if k not in keys]
+        assert not unknown and all(len(v) <= width for v in hist.values()), (unknown, width)
+        row[0] = 1.0
+        for i, k in enumerate(keys):
+            vals = hist.get(k)
+            if vals is not None:
+                at = 1 + i * (1 + width)
+                row[at] = len(vals) + 1  # 0: key absent, n + 1: a list of n values
+                if len(vals):
+                    row[at + 1:at + 1 + len(vals)] = torch.as_tensor([float(v) for v in vals], dtype=torch.float64)
+    out = []
+    for r in rt.all_gather_rows(row).tolist():
+        if r[0] == 0.0:
+            out.append(None)
+            continue
+        h = {}
+        for i, k in enumerate(keys):
+            at = 1 + i * (1 + width)
+            if r[at] > 0:
+                h[k] = r[at + 1:at + int(r[at])]
+        out.append(h)
+    return out
+
+
 def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
     if rt.device.type != 'cuda' or not _engine.native_enabled():
         return None
@@ -48,7 +78,7 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
     with tracing.span('sync/engine'):
         eng = master._native_engine()
     with tracing.span('sync/agree'):
-        if not all(rt.all_gather_object(eng is not None)):
+        if not rt.all_true(eng is not None):
             return None
     ctx = getattr(spark_model, '_sync_context', None)
     if ctx is None or ctx.eng is not eng:
@@ -648,8 +678,8 @@ class SyncContext:
         self.sm._last_sync_run = {'h2d_bytes_per_step': feeder.h2d_bytes_per_step if feeder else 0,
                                   'steps_per_epoch': steps, 'device_ms': t0.elapsed_time(t1)}
         with tracing.span('sync/gather_histories'):
-            gathered = rt.all_gather_object((rt.rank, hist))
-        return [h for _, h in sorted(gathered, key=lambda t: t[0])]
+            keys = list(names) + ['val_' + k for k in names] + ['batch_loss']
+            return _gather_histories(rt, hist, keys, max(epochs, epochs * steps if log_batch_loss else 0, 1))
 
     # ------------------------------------------------------------- kernel timing
     def timed_steps(self, x, y, steps, input_mode='device', on_start=None, on_stop=None):

@@ -178,6 +178,8 @@ class TorchSyncContext:
                 # buffers they address live as long as the context does
                 te.sync, te.flip = _StepSync(self), 1
             before = torch.empty_like(te.w32) if (distributed and not per_batch) else None
+            t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            t0.record()
             for epoch in range(epochs):
                 if before is not None and (epoch == 0 or sync_rounds != 'fit'):
                     before.copy_(te.w32)
@@ -197,9 +199,12 @@ class TorchSyncContext:
                         rt.all_reduce_sum_(packed)
                         packed /= rt.world_size
                         self._unpack(packed, bufs)
+            t1.record()
             if per_batch:
                 te.sync = None  # (steps outside of this context run the plain optimizer again; other graph keys)
             torch.cuda.synchronize(rt.device)
+            self.sm._last_sync_run = {'device_ms': t0.elapsed_time(t1), 'h2d_bytes_per_step': 0,
+                                      'steps_per_epoch': -(-len(x) // bs) if trainable else 0}
             if self.mem is not None:
                 status = int(self.comm_local[8].item()) or int(self.comm_local16[8].item())
                 if status:

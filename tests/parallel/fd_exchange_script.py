@@ -22,8 +22,8 @@ for rnd in range(2):  # two exchanges in a row: the socket names must not collid
     for r in range(rt.world_size):
         assert len(got[r]) == 2
         for k, fd in enumerate(got[r]):
-            os.lseek(fd, 0, os.SEEK_SET)
-            assert os.read(fd, 64) == ('rank %d file %d' % (r, k)).encode(), (r, k)
+            # (pread: duplicates in other processes share the file OFFSET with this one, a seek + read pair would race)
+            assert os.pread(fd, 64, 0) == ('rank %d file %d' % (r, k)).encode(), (r, k)
             if r != rt.rank:
                 os.close(fd)
 print('FD EXCHANGE OK rank %d' % rt.rank, flush=True)

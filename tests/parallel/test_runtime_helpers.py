@@ -1,0 +1,27 @@
+"""Host-side helpers of the synchronous fast path that can be checked without a GPU."""
+import torch
+
+from elephas_b200.parallel import sync_fast
+
+
+class _TwoRanks:
+    """Stands in for the runtime: collects the rows 'sent' by two emulated ranks, then answers with all of them."""
+
+    def __init__(self):
+        self.rows = []
+
+    def all_gather_rows(self, row):
+        self.rows.append(row.clone())
+        return torch.stack(self.rows)
+
+
+def test_histories_travel_as_one_row_per_rank():
+    keys = ['loss', 'acc', 'val_loss', 'val_acc', 'batch_loss']
+    h0 = {'loss': [0.5, 0.25], 'acc': [0.1, 0.2], 'batch_loss': [1.0, 0.75, 0.5, 0.3]}
+    rt = _TwoRanks()
+    first = sync_fast._gather_histories(rt, None, keys, 4)          # rank 0 had nothing to train on
+    assert first == [None]
+    both = sync_fast._gather_histories(rt, h0, keys, 4)
+    assert both[0] is None and both[1] == h0 and list(both[1]) == list(h0)
+    h2 = {'loss': [1e-30, 3.0], 'acc': [], 'val_loss': [2.0, 1.0]}   # an empty list is not an absent key
+    assert sync_fast._gather_histories(_TwoRanks(), h2, keys, 4) == [h2]

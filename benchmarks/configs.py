@@ -170,8 +170,8 @@ def config_resnet(args, rt):
         tracing.enable(True)
         out = timed(rt, lambda: sm.fit(rdd, epochs=epochs, batch_size=bs, verbose=0, keep_context=True))
         tracing.enable(False)
-        top = sorted(tracing.summary()['host'].items(), key=lambda kv: -kv[1]['total_ms'])[:8]
-        return out[0], {k: round(v['total_ms'], 1) for k, v in top}
+        top = sorted(tracing.summary()['host'].items(), key=lambda kv: -kv[1]['total_ms'])[:10]
+        return out[0], {k: '%d x, %.1f ms' % (v['calls'], v['total_ms']) for k, v in top}
 
     dt, phases = traced_fit()
     hist = sm.training_histories[-1] or {}

@@ -387,7 +387,9 @@ class Model:
         new_opt = _optimizers.get(optimizer)
         metrics = list(metrics) if metrics else []
         signature = (json.dumps(_optimizers.serialize(new_opt), sort_keys=True, default=str),
-                     _losses.canonical_name(loss), tuple(str(m) for m in metrics), str(self._device))
+                     _losses.canonical_name(loss), tuple(str(m) for m in metrics))
+        # (the device is not part of the signature: ``to()`` drops the engines itself, and a model that was compiled on
+        # the host and moved to the GPU by its first fit would otherwise rebuild engine and graphs in its second fit)
         unchanged = self._compiled and getattr(self, '_compile_signature', None) == signature
         same = unchanged and self._engine is not None
         te = getattr(self, '_torch_step', None)

@@ -35,7 +35,9 @@ def maybe_create(model):
     params = model.trainable_weights
     if kind is None or not params or any(p.dtype != torch.float32 for p in params) or len(model._metric_fns) > 4:
         return None
-    return TorchStepEngine(model, kind)
+    from ..utils import tracing
+    with tracing.span('torch_step/create'):
+        return TorchStepEngine(model, kind)
 
 
 class TorchStepEngine:

@@ -319,6 +319,9 @@ def test_emulated_eight_rank_twoshot_reduction(native, dtype):
         mean = mean.to(torch.bfloat16).float()  # the averaged slice travels in the delta's own type
     for target in (0, 3, 7):
         avgs = [torch.full((n,), float('nan'), dtype=dtype, device='cuda') for _ in range(world)]
+        for r, pad in enumerate(pads):  # fresh flags for this round (the previous one left every own flag published)
+            pad.fill_(1 << 30)
+            pad[8 + r] = 0
         order = [r for r in range(world) if r != target] + [target]
         for r in order:
             w32 = torch.ones(n, device='cuda')

@@ -544,7 +544,23 @@ class _Pool2D(Layer):
 
 
 class MaxPooling2D(_Pool2D):
-    def call(self, x, training=False):
+    def call(self, x, training=False, zero_pads=None):
+        """``zero_pads`` = ((top, bottom), (left, right)) of a ZeroPadding2D folded into this layer (``Model._fusion_plan``)."""
+        from ..ops import cnn as _cnn
+        if x.dim() == 4 and _cnn.usable(x) and (zero_pads is None or self.padding == 'valid'):
+            # native kernel (csrc/pool_kernels.cu): padding handled inside the window walk, no padded copy
+            if zero_pads is not None:
+                pads = (zero_pads[0][0], zero_pads[0][1], zero_pads[1][0], zero_pads[1][1])
+            elif self.padding == 'same':
+                l, r, t, b = _same_pad(x, self.pool_size, self.strides)
+                pads = (t, b, l, r)
+            else:
+                pads = (0, 0, 0, 0)
+            if _cnn.max_pool_supported(x, self.pool_size, self.strides, pads):
+                return _cnn.max_pool2d(x, self.pool_size, self.strides[0], pads, pad_is_zero=zero_pads is not None)
+        if zero_pads is not None:
+            (t, b), (l, r) = zero_pads
+            x = F.pad(x, (0, 0, l, r, t, b))
         if self.padding == 'same':
             pads = _same_pad(x, self.pool_size, self.strides)
             if any(pads):
@@ -566,6 +582,9 @@ class GlobalAveragePooling2D(Layer):
         return (input_shape[0], input_shape[-1])
 
     def call(self, x, training=False):
+        from ..ops import cnn as _cnn
+        if x.dim() == 4 and x.shape[-1] % 8 == 0 and _cnn.usable(x):
+            return _cnn.global_avg_pool(x)  # native kernel, fp32 accumulation (csrc/pool_kernels.cu)
         return x.mean(dim=(1, 2))
 
     def _extra_config(self):

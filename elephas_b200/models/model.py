@@ -98,6 +98,7 @@ class Model:
             visit(o)
         self._node_order = order
         self._fusion_cache = None
+        self._pool_pad_cache = None
         self.layers = []
         for t in order:
             if t.layer not in self.layers:
@@ -152,14 +153,45 @@ class Model:
         self._fusion_cache = (fused, alias)
         return self._fusion_cache
 
+    def _pool_pad_plan(self):
+        """ZeroPadding2D -> MaxPooling2D(padding='valid'), the padded tensor read by nothing else: the pool takes the
+        padding as an argument (zeros that take part in the maximum, exactly like the padded copy would) and the copy is
+        never made. Returns ``{pool node key: (padding, key of the pad's input)}, {pad node keys that are skipped}``."""
+        plan = getattr(self, '_pool_pad_cache', None)
+        if plan is not None:
+            return plan
+        key_of = lambda t: (id(t.layer), t.node_index)  # noqa: E731
+        consumers = {}
+        for t in self._node_order:
+            for s in t.layer.inbound[t.node_index]:
+                consumers.setdefault(key_of(s), []).append(t)
+        outputs = {key_of(o) for o in self._outputs}
+        pools, skipped = {}, set()
+        for t in self._node_order:
+            ins = t.layer.inbound[t.node_index]
+            if not isinstance(t.layer, L.ZeroPadding2D) or len(ins) != 1 or key_of(t) in outputs:
+                continue
+            users = consumers.get(key_of(t), [])
+            if len(users) == 1 and isinstance(users[0].layer, L.MaxPooling2D) and users[0].layer.padding == 'valid':
+                pools[key_of(users[0])] = (t.layer.padding, key_of(ins[0]))
+                skipped.add(key_of(t))
+        self._pool_pad_cache = (pools, skipped)
+        return self._pool_pad_cache
+
     def _forward(self, xs, training):
         values = {}
         for t, x in zip(self._inputs, xs):
             values[(id(t.layer), t.node_index)] = x
-        fused, alias = self._fusion_plan() if os.environ.get('ELEPHAS_B200_FUSE_BN', '1') != '0' else ({}, {})
+        fuse = os.environ.get('ELEPHAS_B200_FUSE_BN', '1') != '0'
+        fused, alias = self._fusion_plan() if fuse else ({}, {})
+        pools, skipped = self._pool_pad_plan() if fuse else ({}, set())
         for t in self._node_order:
             key = (id(t.layer), t.node_index)
-            if key in values:
+            if key in values or key in skipped:
+                continue
+            if key in pools:
+                pads, src = pools[key]
+                values[key] = t.layer.call(values[src], training=training, zero_pads=pads)
                 continue
             if key in alias:
                 values[key] = values[alias[key]]  # absorbed into the BatchNormalization that produced its input

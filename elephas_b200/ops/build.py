@@ -20,7 +20,7 @@ LIB_DIR = os.path.join(ROOT, 'elephas_b200', '_lib')
 LIB_PATH = os.path.join(LIB_DIR, 'libelephas_b200.so')
 OBJ_DIR = os.path.join(ROOT, 'build', 'obj')
 
-SOURCES = ['core.cu', 'gemm_sm100.cu', 'elementwise.cu', 'loss_kernels.cu', 'optim_kernels.cu', 'comm_kernels.cu', 'ps_kernels.cu', 'conv_sm100.cu', 'conv_aux.cu', 'vmm.cu',
+SOURCES = ['core.cu', 'gemm_sm100.cu', 'elementwise.cu', 'loss_kernels.cu', 'optim_kernels.cu', 'comm_kernels.cu', 'ps_kernels.cu', 'conv_sm100.cu', 'conv_aux.cu', 'pool_kernels.cu', 'vmm.cu',
            'host_stage.cu', 'host_cast.cpp', 'narrow_head.cu', 'mlp_fused.cu']
 NVCC_FLAGS = ['-gencode', 'arch=compute_100a,code=sm_100a', '-lineinfo', '-O3', '-std=c++17', '-Xcompiler', '-fPIC',
               '-DNDEBUG']

@@ -11,6 +11,8 @@ backward pass is one of this repository's kernels:
 * ``batch_norm``  statistics -> normalise (+ residual) (+ ReLU) in one pass; backward = one reduction pass + one apply
                   pass that also emits the gradient of the residual branch
 * ``linear``      the tcgen05 GEMM of the Dense engine (K1)
+* ``max_pool2d`` / ``global_avg_pool``  ``csrc/pool_kernels.cu``: the forward keeps a byte map of the winning taps, the
+                  backward gathers per input pixel (no atomics); a ZeroPadding2D in front of a pool is folded into it
 
 torch autograd only orders the calls (and the whole step is replayed from a CUDA graph by ``ops/torch_step.py``);
 activations travel channels-last in bf16, master weights stay fp32. ``ELEPHAS_B200_NATIVE_CONV=0`` switches the layers
@@ -266,3 +268,63 @@ def linear(x, weight, bias):
 
 def linear_supported(weight):
     return weight.shape[1] % 8 == 0
+
+
+class _MaxPool2d(torch.autograd.Function):
+    """``x`` NHWC bf16; ``pads`` = (top, bottom, left, right); elements outside the image count as zeros
+    (``pad_is_zero``: a ZeroPadding2D folded into the pool) or as -inf (Keras ``padding='same'``)."""
+
+    @staticmethod
+    def forward(ctx, x, window, stride, pads, pad_is_zero):
+        xb = _bf16(x)
+        N, H, W, C = xb.shape
+        R, S = window
+        pt, pb, pl, pr = pads
+        P, Q = _out_size(H, R, stride, pt, pb), _out_size(W, S, stride, pl, pr)
+        y = torch.empty(N, P, Q, C, dtype=torch.bfloat16, device=x.device)
+        idx = torch.empty(N, P, Q, C, dtype=torch.uint8, device=x.device)
+        native.pool_max_fwd(xb, R, S, stride, pt, pl, P, Q, pad_is_zero, y, idx)
+        ctx.save_for_backward(idx)
+        ctx.geo = (tuple(xb.shape), R, S, stride, pt, pl, x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (idx,) = ctx.saved_tensors
+        shape, R, S, stride, pt, pl, dtype = ctx.geo
+        dx = torch.empty(shape, dtype=torch.bfloat16, device=gy.device)
+        native.pool_max_bwd(_bf16(gy), idx, shape, R, S, stride, pt, pl, dx)
+        return (dx if dtype == torch.bfloat16 else dx.to(dtype)), None, None, None, None
+
+
+def max_pool2d(x, window, stride, pads=(0, 0, 0, 0), pad_is_zero=False):
+    return _MaxPool2d.apply(x, tuple(window), int(stride), tuple(pads), bool(pad_is_zero))
+
+
+def max_pool_supported(x, window, strides, pads=(0, 0, 0, 0)):
+    R, S = window
+    pt, pb, pl, pr = pads
+    return (x.dim() == 4 and x.shape[-1] % 8 == 0 and strides[0] == strides[1] and R * S < 255
+            and max(pt, pb) < R and max(pl, pr) < S
+            and _out_size(x.shape[1], R, strides[0], pt, pb) >= 1 and _out_size(x.shape[2], S, strides[0], pl, pr) >= 1)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        xb = _bf16(x)
+        y = torch.empty(xb.shape[0], xb.shape[-1], dtype=torch.bfloat16, device=x.device)
+        native.pool_gap_fwd(xb, y)
+        ctx.geo = (tuple(xb.shape), x.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        shape, dtype = ctx.geo
+        dx = torch.empty(shape, dtype=torch.bfloat16, device=gy.device)
+        native.pool_gap_bwd(_bf16(gy), dx)
+        return dx if dtype == torch.bfloat16 else dx.to(dtype)
+
+
+def global_avg_pool(x):
+    return _GlobalAvgPool.apply(x)

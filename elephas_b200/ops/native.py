@@ -161,6 +161,10 @@ def load():
         lib.eb_conv_igemm.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_wgrad.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_im2col.argtypes = [c_void_p, c_int32] + [c_int32] * 10 + [c_void_p, c_int32, c_void_p]
+        lib.eb_pool_max_fwd.argtypes = [c_void_p] + [c_int32] * 12 + [c_void_p, c_void_p, c_void_p]
+        lib.eb_pool_max_bwd.argtypes = [c_void_p, c_void_p] + [c_int32] * 11 + [c_void_p, c_void_p]
+        lib.eb_pool_gap_fwd.argtypes = [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]
+        lib.eb_pool_gap_bwd.argtypes = [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]
         lib.eb_bn_stats.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_int32, c_float, c_float, c_void_p, c_void_p,
                                     c_void_p, c_void_p, c_void_p]
         lib.eb_bn_apply.argtypes = [c_void_p, c_int64, c_int32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -602,6 +606,34 @@ def conv_im2col(x, R, S, stride, pad, P, Q, out, ld):
     N, H, W, C = x.shape
     _check(require().eb_conv_im2col(x.data_ptr(), int(x.dtype == torch.float32), N, H, W, C, int(R), int(S), int(stride),
                                     int(pad), int(P), int(Q), out.data_ptr(), int(ld), _stream(x.device)), 'eb_conv_im2col')
+
+
+def pool_max_fwd(x, R, S, stride, pad_t, pad_l, P, Q, pad_is_zero, y, idx):
+    """Max pooling of channels-last bf16 ``x`` [N, H, W, C] into ``y`` [N, P, Q, C]; ``idx`` (uint8, shape of y) = winning tap."""
+    N, H, W, C = x.shape
+    _check(require().eb_pool_max_fwd(x.data_ptr(), N, H, W, C, int(R), int(S), int(stride), int(pad_t), int(pad_l), int(P),
+                                     int(Q), int(bool(pad_is_zero)), y.data_ptr(), idx.data_ptr(), _stream(x.device)),
+           'eb_pool_max_fwd')
+
+
+def pool_max_bwd(dy, idx, x_shape, R, S, stride, pad_t, pad_l, dx):
+    N, H, W, C = x_shape
+    P, Q = dy.shape[1], dy.shape[2]
+    _check(require().eb_pool_max_bwd(dy.data_ptr(), idx.data_ptr(), N, H, W, C, int(R), int(S), int(stride), int(pad_t),
+                                     int(pad_l), P, Q, dx.data_ptr(), _stream(dy.device)), 'eb_pool_max_bwd')
+
+
+def pool_gap_fwd(x, y):
+    """Global average pooling of channels-last bf16 ``x`` [N, ..., C] into ``y`` [N, C]."""
+    N, C = x.shape[0], x.shape[-1]
+    _check(require().eb_pool_gap_fwd(x.data_ptr(), N, x.numel() // (N * C), C, y.data_ptr(), _stream(x.device)),
+           'eb_pool_gap_fwd')
+
+
+def pool_gap_bwd(dy, dx):
+    N, C = dx.shape[0], dx.shape[-1]
+    _check(require().eb_pool_gap_bwd(dy.data_ptr(), N, dx.numel() // (N * C), C, dx.data_ptr(), _stream(dy.device)),
+           'eb_pool_gap_bwd')
 
 
 BN_MAX_BLOCKS = 592  # rows of the partial-sum scratch: 4 blocks of 256 threads per SM

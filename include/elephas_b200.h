@@ -384,6 +384,22 @@ int eb_conv_wgrad(const EbConvWgradArgs* args, void* stream);
 int eb_conv_im2col(const void* x, int32_t x_is_f32, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
                    int32_t stride, int32_t pad, int32_t P, int32_t Q, void* out_bf16, int32_t ld, void* stream);
 
+/* Pooling over channels-last bf16 [N][H][W][C] (C multiple of 8).
+ *   eb_pool_max_fwd   y[n][p][q][c] = max over the R x S window at (p*stride - pad_t, q*stride - pad_l); elements outside
+ *                     the image count as -inf (pad_is_zero = 0, Keras padding='same') or as zeros (pad_is_zero = 1, a
+ *                     ZeroPadding2D folded into the pool). idx (bytes, same shape as y) receives the winning tap
+ *                     r*S + s (255: the padding won); the first maximum in row-major tap order wins.
+ *   eb_pool_max_bwd   dx[n][h][w][c] = sum of dy over the windows that contain (h, w) and were won by it (a gather over the
+ *                     input pixels: no atomics)
+ *   eb_pool_gap_fwd   y[n][c] = mean over the HW pixels (global average pooling), fp32 accumulation
+ *   eb_pool_gap_bwd   dx[n][m][c] = dy[n][c] / HW */
+int eb_pool_max_fwd(const void* x, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S, int32_t stride,
+                    int32_t pad_t, int32_t pad_l, int32_t P, int32_t Q, int32_t pad_is_zero, void* y, void* idx, void* stream);
+int eb_pool_max_bwd(const void* dy, const void* idx, int32_t N, int32_t H, int32_t W, int32_t C, int32_t R, int32_t S,
+                    int32_t stride, int32_t pad_t, int32_t pad_l, int32_t P, int32_t Q, void* dx, void* stream);
+int eb_pool_gap_fwd(const void* x, int32_t N, int32_t HW, int32_t C, void* y, void* stream);
+int eb_pool_gap_bwd(const void* dy, int32_t N, int32_t HW, int32_t C, void* dx, void* stream);
+
 /* BatchNormalization over channels-last bf16 [M][C] (C multiple of 8), statistics in fp32. The two reductions write one
  * row of partial sums per thread block into `partials` (fp32, room for max_blocks * 2 * C values, no need to clear it)
  * and a second small kernel adds the rows: no atomics, fixed summation order.

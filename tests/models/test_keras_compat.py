@@ -228,3 +228,31 @@ def test_batchnorm_fusion_plan_computes_what_the_separate_layers_compute(monkeyp
     assert torch.allclose(results['1'][0], results['0'][0], atol=1e-6)
     assert all(torch.allclose(a, b, atol=1e-6) for a, b in zip(results['1'][1], results['0'][1]))
     assert torch.allclose(results['1eval'], results['0eval'], atol=1e-6)
+
+
+def test_zero_padding_in_front_of_a_max_pool_is_folded_into_the_pool(monkeypatch):
+    """``ZeroPadding2D -> MaxPooling2D('valid')`` (ResNet's pool1): the executor hands the padding to the pool and skips
+    the padded copy when nothing else reads it - same numbers and gradients; a padded tensor that IS read elsewhere, or a
+    pool with padding='same', stays as written."""
+    import torch
+    from elephas_b200.models import Model
+    from elephas_b200.models.layers import Add, GlobalAveragePooling2D, Input, MaxPooling2D, ZeroPadding2D
+    inp = Input(shape=(9, 7, 8))
+    a = MaxPooling2D(3, strides=2, name='pool_a')(ZeroPadding2D(1, name='pad_a')(inp))          # folded
+    padded = ZeroPadding2D(((0, 2), (1, 1)), name='pad_b')(inp)                                  # read twice: kept
+    b = MaxPooling2D(3, strides=2, name='pool_b')(padded)
+    c = MaxPooling2D(3, strides=2, name='pool_c')(padded)
+    d = MaxPooling2D(3, strides=2, padding='same', name='pool_d')(ZeroPadding2D(1, name='pad_d')(inp))  # 'same': kept
+    model = Model(inputs=inp, outputs=[GlobalAveragePooling2D()(Add()([a, b, c])), GlobalAveragePooling2D()(d)])
+    pools, skipped = model._pool_pad_plan()
+    names = {id(l): l.name for l in model.layers}
+    assert {names[k[0]] for k in pools} == {'pool_a'} and {names[k[0]] for k in skipped} == {'pad_a'}
+    x = (torch.randn(3, 9, 7, 8) - 0.5).requires_grad_(True)
+    outs = {}
+    for flag in ('1', '0'):
+        monkeypatch.setenv('ELEPHAS_B200_FUSE_BN', flag)
+        y1, y2 = model(x, training=True)
+        (g,) = torch.autograd.grad(y1.sum() + 2 * y2.sum(), x)
+        outs[flag] = (y1.detach(), y2.detach(), g)
+    for u, v in zip(outs['1'], outs['0']):
+        assert torch.equal(u, v)

@@ -130,6 +130,50 @@ def test_batch_norm_matches_pytorch(M, C, relu, residual):
     _close(yi, torch.relu(ri) if relu else ri, rel=1e-2)
 
 
+POOL_CASES = [
+    # N, H, W, C, window, stride, pads (top, bottom, left, right), zero padding?
+    (2, 112, 112, 64, 3, 2, (1, 1, 1, 1), True),    # ResNet pool1 with its ZeroPadding2D folded in
+    (3, 13, 9, 24, 3, 2, (0, 1, 0, 1), False),      # Keras padding='same' on odd sizes (-inf outside)
+    (2, 8, 8, 16, 2, 2, (0, 0, 0, 0), False),       # plain 2x2
+    (1, 11, 7, 40, 3, 1, (1, 1, 1, 1), True),       # overlapping windows, stride 1
+    (2, 10, 10, 8, 5, 3, (2, 2, 2, 2), False),      # wide window, stride 3
+]
+
+
+@pytest.mark.parametrize('N,H,W,C,k,stride,pads,zero', POOL_CASES)
+def test_max_pool_matches_pytorch(N, H, W, C, k, stride, pads, zero):
+    """Forward values and the routing of the gradient (bf16 inputs have many exact ties: the first maximum in scan order
+    must win, as in the library kernel; a zero of the padding takes part like an element)."""
+    x = _rounded(N, H, W, C, seed=11)
+    if zero:
+        x = x - 1.0  # mostly negative: the padding zeros win many border windows
+    x = x.to(torch.bfloat16).float().requires_grad_(True)
+    pt, pb, pl, pr = pads
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        y = cnn.max_pool2d(x, (k, k), stride, pads, pad_is_zero=zero)
+    xp = F.pad(x.permute(0, 3, 1, 2), (pl, pr, pt, pb), value=0.0 if zero else float('-inf'))
+    ref = F.max_pool2d(xp, k, stride).permute(0, 2, 3, 1)
+    assert y.dtype == torch.bfloat16 and tuple(y.shape) == tuple(ref.shape)
+    assert torch.equal(y.float(), ref.detach())  # a maximum is one of the inputs: exact
+    g = _rounded(*ref.shape, seed=12)
+    (dx,) = torch.autograd.grad(y, x, g.to(torch.bfloat16))
+    (rx,) = torch.autograd.grad(ref, x, g)
+    _close(dx, rx, rel=1e-2)  # sums of up to four bf16 gradients, rounded once
+
+
+def test_global_average_pool_matches_pytorch():
+    x = _rounded(5, 7, 7, 136, seed=13).requires_grad_(True)
+    with torch.autocast('cuda', dtype=torch.bfloat16):
+        y = cnn.global_avg_pool(x)
+    ref = x.mean(dim=(1, 2))
+    assert y.dtype == torch.bfloat16 and tuple(y.shape) == (5, 136)
+    _close(y, ref.detach(), rel=1e-2)
+    g = _rounded(5, 136, seed=14)
+    (dx,) = torch.autograd.grad(y, x, g.to(torch.bfloat16))
+    (rx,) = torch.autograd.grad(ref, x, g)
+    _close(dx, rx, rel=1e-2)
+
+
 def test_linear_matches_pytorch():
     x = _rounded(70, 2048, seed=17).requires_grad_(True)
     w = _rounded(1000, 2048, scale=0.02, seed=18).requires_grad_(True)

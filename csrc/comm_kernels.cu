@@ -650,6 +650,40 @@ extern "C" int eb_allreduce_nvls_update(const EbCommArgs* a, void* stream) {
   return 0;
 }
 
+// Replicate a local buffer into every rank's memory through the multicast address of a symmetric buffer: one
+// multimem.st per 16 bytes, the NVSwitch fans the data out (the sender's link carries the payload once, not N-1 times).
+// Used for the weight broadcast at the start of a fit and for the gather of the sharded fp32 master at its end
+// (reference: Spark broadcast of the driver's weights, elephas/spark_model.py:206-207). Completion is ordered by the
+// caller (stream synchronize + barrier) - the kernel itself is a pure store stream.
+namespace eb {
+__global__ void __launch_bounds__(512) nvls_store_kernel(const uint4* __restrict__ src, uint4* mc_dst, long n16) {
+  const long stride = static_cast<long>(gridDim.x) * blockDim.x;
+  long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x;
+  for (; i + 3 * stride < n16; i += 4 * stride) {  // four loads in flight per thread
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_nc_u4(src + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) multimem_st_bf16x8(mc_dst + i + u * stride, v[u]);
+  }
+  for (; i < n16; i += stride) multimem_st_bf16x8(mc_dst + i, ld_nc_u4(src + i));
+}
+}  // namespace eb
+
+extern "C" int eb_nvls_store(const void* src, void* mc_dst, int64_t nbytes, int32_t blocks, void* stream) {
+  if (nbytes <= 0) return 0;
+  if (src == nullptr || mc_dst == nullptr) return fail("eb_nvls_store: null pointer");
+  if ((nbytes & 15) || (reinterpret_cast<uintptr_t>(src) & 15) || (reinterpret_cast<uintptr_t>(mc_dst) & 15))
+    return fail("eb_nvls_store: source, multicast destination and size must be multiples of 16 bytes");
+  const long n16 = static_cast<long>(nbytes / 16);
+  int grid = blocks > 0 ? blocks : 64;
+  if (grid > (n16 + 511) / 512) grid = static_cast<int>((n16 + 511) / 512);
+  nvls_store_kernel<<<grid, 512, 0, static_cast<cudaStream_t>(stream)>>>(static_cast<const uint4*>(src),
+                                                                        static_cast<uint4*>(mc_dst), n16);
+  EB_LAUNCH_OK("nvls_store_kernel");
+  return 0;
+}
+
 extern "C" int eb_allreduce_sum(const EbCommArgs* a, void* stream) {
   if (a == nullptr) return fail("eb_allreduce_sum: null args");
   if (a->n <= 0) return 0;

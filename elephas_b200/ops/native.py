@@ -161,6 +161,7 @@ def load():
         lib.eb_conv_igemm.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_wgrad.argtypes = [c_void_p, c_void_p]
         lib.eb_conv_im2col.argtypes = [c_void_p, c_int32] + [c_int32] * 10 + [c_void_p, c_int32, c_void_p]
+        lib.eb_nvls_store.argtypes = [c_void_p, c_void_p, c_int64, c_int32, c_void_p]
         lib.eb_pool_max_fwd.argtypes = [c_void_p] + [c_int32] * 12 + [c_void_p, c_void_p, c_void_p]
         lib.eb_pool_max_bwd.argtypes = [c_void_p, c_void_p] + [c_int32] * 11 + [c_void_p, c_void_p]
         lib.eb_pool_gap_fwd.argtypes = [c_void_p, c_int32, c_int32, c_int32, c_void_p, c_void_p]
@@ -452,6 +453,13 @@ def allreduce_nvls_update(mc_delta, mc_w16, pad_ptrs, local, n, rank, world, sca
                    None, 0, blocks)
     a.delta[0], a.avg[0] = mc_delta, mc_w16
     _check(require().eb_allreduce_nvls_update(ctypes.byref(a), _stream(device)), 'eb_allreduce_nvls_update')
+
+
+def nvls_store(src, mc_dst, nbytes=None, blocks=0, device=None):
+    """Replicate ``src`` (tensor) into every rank's symmetric buffer through its multicast address ``mc_dst`` (int)."""
+    nbytes = src.numel() * src.element_size() if nbytes is None else int(nbytes)
+    _check(require().eb_nvls_store(src.data_ptr(), mc_dst, nbytes, int(blocks), _stream(device if device is not None else src.device)),
+           'eb_nvls_store')
 
 
 def allreduce_sum(delta_ptrs, pad_ptrs, local, n, rank, world, dtype_bf16, out32, scale=1.0, blocks=0, device=None):

@@ -368,7 +368,8 @@ class SyncContext:
         want_nvls = self.sharded and nvls_env != '0' and self.rt.distributed
         if want_nvls:
             try:
-                mem = VmmSymmetricMemory(self.rt, spec, multicast=True)
+                # 'stage32': room for the fp32 master, the target of the multimem.st weight broadcast / master gather
+                mem = VmmSymmetricMemory(self.rt, dict(spec, stage32=n * 4), multicast=True)
                 err = None
             except native.NativeError as exc:
                 mem, err = None, str(exc)
@@ -436,17 +437,30 @@ class SyncContext:
                 out.append((lo + a * 8, lo + b * 8))
         return out
 
+    def _ranges_cover_master(self):
+        """True when the buckets tile the whole flat buffer (then the owned ranges of all ranks do, too): the staging
+        buffer of the NVLS gather holds no element nobody wrote."""
+        at = 0
+        for lo, n in sorted(self.eng.bucket_ranges()):
+            if lo != at or n % 8:
+                return False
+            at = lo + n
+        return at == self.eng.w32.numel()
+
     def _gather_master(self):
         """Sharded mode leaves every rank with an up-to-date fp32 master only for the slices it owns: rebuild
         the full replica (once per fit, not per step) so that ``get_weights`` / ``save`` see exact values."""
         if not self.w32_partial:
             return
         eng = self.eng
-        full = torch.zeros_like(eng.w32)
-        for a, b in self._owned_ranges():
-            full[a:b].copy_(eng.w32[a:b])
-        self.rt.all_reduce_sum_(full)
-        eng.w32.copy_(full)
+        if self.nvls and self.mem is not None and self._ranges_cover_master():
+            self._nvls_replicate(self._owned_ranges())
+        else:
+            full = torch.zeros_like(eng.w32)
+            for a, b in self._owned_ranges():
+                full[a:b].copy_(eng.w32[a:b])
+            self.rt.all_reduce_sum_(full)
+            eng.w32.copy_(full)
         self.w32_partial = False
         eng._weights_dirty_in_model = True
 
@@ -550,9 +564,28 @@ class SyncContext:
         eng, rt = self.eng, self.rt
         eng.reset_optimizer()
         if rt.distributed:
-            rt.broadcast_(eng.w32, src=0)
+            if self.nvls and self.mem is not None:
+                # rank 0 writes its fp32 master once to the multicast address of the staging buffer; the switch replicates
+                # it into every rank's memory (elephas/spark_model.py:206-207: Spark broadcast of the driver's weights)
+                self._nvls_replicate([(0, eng.w32.numel())] if rt.rank == 0 else [])
+            else:
+                rt.broadcast_(eng.w32, src=0)
             eng.refresh_bf16()
             eng._weights_dirty_in_model = True
+
+    def _nvls_replicate(self, ranges):
+        """Every rank stores the flat element ``ranges`` of its fp32 master through the multicast address of 'stage32'
+        (``multimem.st``: each payload byte leaves the sender once), then all ranks copy the staging buffer - now the
+        union of everybody's ranges - over their master. The ranges of different ranks must not overlap and must cover
+        the buffer. No barrier is needed BEFORE the stores: the previous reader of 'stage32' on every rank finished
+        before a collective every rank has since completed (the agreement all-reduce of ``try_fit`` / the flag barriers
+        of the training steps)."""
+        eng, rt = self.eng, self.rt
+        for a, b in ranges:
+            native.nvls_store(eng.w32[a:b], self.mem.mc_ptr('stage32', 4 * a), device=rt.device)
+        torch.cuda.synchronize(rt.device)
+        rt.barrier()  # every rank's stores have left its GPU and landed
+        eng.w32.copy_(self.mem.local('stage32', torch.float32, eng.w32.numel()))
 
     # ----------------------------------------------------------------------- fit
     def run(self, partition, train_config, sync_rounds):
@@ -578,11 +611,11 @@ class SyncContext:
         with torch.cuda.device(rt.device):
             distributed = rt.distributed
             per_batch = distributed and frequency == 'batch' and sync_rounds != 'fit'
-            with tracing.span('sync/broadcast_start'):
-                self._sync_start()
             if distributed:
                 with tracing.span('sync/setup_comm'):
                     self._setup_comm(dtype_bf16=per_batch)
+            with tracing.span('sync/broadcast_start'):
+                self._sync_start()
             if per_batch:
                 self._install_hooks()
             else:

@@ -194,6 +194,11 @@ int eb_allreduce_shard_update(const EbCommArgs* args, void* stream);
  * are ordinary peer mappings. About half the NVLink bytes of the peer-to-peer kernel, 1/N of its load instructions. */
 int eb_allreduce_nvls_update(const EbCommArgs* args, void* stream);
 
+/* Replicate nbytes (multiple of 16) of local memory `src` into every rank's copy of a symmetric buffer through its
+ * MULTICAST address `mc_dst` (multimem.st: the sender's NVLink carries the payload once). The kernel is a pure store
+ * stream; the caller orders completion (stream synchronize + barrier) before any rank reads its local copy. */
+int eb_nvls_store(const void* src, void* mc_dst, int64_t nbytes, int32_t blocks, void* stream);
+
 /* Allocation-free form of eb_allreduce_update for ONE rank (world = 1). This entry point has no
  * counterpart in the reference; it exists for hosts that are not allowed to allocate device memory at the
  * time they need the update: a serving or training process that has already handed all of the GPU's

@@ -4,12 +4,13 @@
 // get_parameters (server.py:107-115, 212-218), a write lock around `weights -= delta` (server.py:117-132, 201-210),
 // both from elephas/utils/rwlock.py ("several threads can hold this type of lock" for reading, one for writing).
 // Here the master (fp32) and a bf16 mirror of it are cut into one stripe per rank (EbPsStore, include/elephas_b200.h);
-// a worker's push is ONE kernel whose blocks each take one chunk of one stripe: FIFO ticket -> sequence word odd ->
-// red.global.add.f32 of the negated delta straight into the owner's memory over NVLink -> sequence word even (which
-// also serves the next ticket). A pull takes no lock at all: it copies a chunk between two reads of the chunk's
-// sequence word and repeats the copy when the word was odd or moved (seqlock), so any number of workers read at once
-// and none of them ever holds up a writer. Locks live and die inside a kernel: the holder of a ticket is always a
-// block that is running right now, never a kernel queued behind the one that waits for it.
+// a worker's push is ONE kernel whose blocks each take one chunk of one stripe: count the writer in -> red.global.add.f32
+// of the negated delta straight into the owner's memory over NVLink -> count it out. Additions are atomic per element,
+// so writers do not exclude each other; a pull copies a chunk between two reads of the chunk's counters and repeats the
+// copy when a writer was inside or arrived (seqlock), so any number of workers read at once and none of them holds up a
+// writer - unless a reader keeps losing: it then raises the chunk's gate for one copy, which writers respect. All of it
+// lives inside a kernel: whoever is waited for is a block that is running right now, never a kernel queued behind the
+// one that waits.
 //
 // The optimizer step can ride in the push kernel (ps_optimizer_push): the update of an element is computed from the
 // gradient and the optimizer slots in registers and leaves the SM as a red.add into peer memory - the per-batch loop of
@@ -106,43 +107,86 @@ __device__ __forceinline__ void for_each_group(const Dev& p, const Work& w, F f)
   }
 }
 
-// One word per chunk is both the FIFO turn and the sequence lock: S = 2k while k operations have completed and nobody is
-// inside, S = 2t + 1 while the holder of ticket t is inside. Ticket t (atomic increment of the word next to it) waits for
-// S == 2t, stores 2t + 1, works, stores 2t + 2. A waiter that is still not served after kLockTimeoutNs records that in
-// the chunk's status word and goes ahead (the host reports it; nothing hangs). Thread 0 of the block calls these.
-__device__ __forceinline__ uint32_t lock_chunk(uint32_t* lk) {
-  const uint32_t ticket = atomicAdd_system(lk + 1, 1u);
+// Lock record of a chunk (8 words in the owner's memory): [0] gate, [1] started - ONE 64-bit word, gate in the low half -
+// [2] finished, [3] watchdog status. Pushes are element-wise atomic additions, so writers need no exclusion among
+// themselves (any interleaving equals some serial order of the same updates); what a chunk's record provides is the
+// READER's guarantee of elephas/utils/rwlock.py: a pull never observes a half-applied push.
+//   writer   started += 1 (one 64-bit atomic that also returns the gate), red.adds, fence, finished += 1. Wait-free
+//            unless the gate is up: then it steps back out (finished += 1 without having written) and waits for the gate.
+//   reader   optimistic: read finished, then {gate, started}; equal counters = nobody inside; copy; re-read started;
+//            retry when it moved. After EB_PS_SEQ_RETRIES failed attempts it raises the gate (gate += 1 in the same word
+//            the writers increment, so every writer is ordered before or after it), waits until finished == started,
+//            copies - no writer can be inside - and lowers the gate. That bounds a reader's wait under any write load.
+// Counters wrap modulo 2^32 together (started sits in the HIGH half: its carry falls off the word, never into the gate).
+// A waiter that is still not served after kLockTimeoutNs records that in the status word and goes ahead (the host
+// reports it; nothing hangs). Thread 0 of the block calls these.
+__device__ __forceinline__ unsigned long long ld_acquire_sys_u64(const void* p) {
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t gate_of(unsigned long long w) { return static_cast<uint32_t>(w); }
+__device__ __forceinline__ uint32_t started_of(unsigned long long w) { return static_cast<uint32_t>(w >> 32); }
+
+struct Watchdog {
   unsigned long long t0 = 0;
   uint32_t spins = 0;
-  while (ld_acquire_sys(lk) != 2u * ticket) {
-    if ((++spins & 0x3FFu) == 0) {
-      const unsigned long long now = now_ns();
-      if (t0 == 0) t0 = now;
-      else if (now - t0 > kLockTimeoutNs) {
-        atomicExch_system(lk + 3, 1u);
-        break;
-      }
+  __device__ __forceinline__ bool expired(uint32_t* lk, uint32_t code) {
+    if ((++spins & 0x3FFu) != 0) return false;
+    const unsigned long long now = now_ns();
+    if (t0 == 0) { t0 = now; return false; }
+    if (now - t0 <= kLockTimeoutNs) return false;
+    atomicExch_system(lk + 3, code);
+    return true;
+  }
+};
+
+__device__ __forceinline__ void writer_begin(uint32_t* lk) {
+  unsigned long long* word = reinterpret_cast<unsigned long long*>(lk);
+  Watchdog dog;
+  for (;;) {
+    const unsigned long long old = atomicAdd_system(word, 1ull << 32);  // started += 1; the same atomic reads the gate
+    if (gate_of(old) == 0) return;
+    atomicAdd_system(lk + 2, 1u);  // a reader insists on a quiet chunk: step back out ...
+    bool give_up = false;
+    while (gate_of(ld_acquire_sys_u64(word)) != 0 && !give_up) give_up = dog.expired(lk, 1u);  // ... until it is done
+    if (give_up) {
+      atomicAdd_system(word, 1ull << 32);
+      return;
     }
   }
-  st_relaxed_sys(lk, 2u * ticket + 1u);  // odd: a pull that overlaps from here on will retry
-  return ticket;
 }
 
-__device__ __forceinline__ void unlock_chunk(uint32_t* lk, uint32_t ticket) { st_release_sys(lk, 2u * ticket + 2u); }
+__device__ __forceinline__ void writer_end(uint32_t* lk) { atomicAdd_system(lk + 2, 1u); }
+
+// Reader that has run out of optimistic attempts: raise the gate, wait for the writers inside to leave.
+__device__ __forceinline__ void reader_gate_up(uint32_t* lk) {
+  unsigned long long* word = reinterpret_cast<unsigned long long*>(lk);
+  atomicAdd_system(word, 1ull);
+  Watchdog dog;
+  for (;;) {
+    const uint32_t finished = ld_acquire_sys(lk + 2);
+    if (started_of(ld_acquire_sys_u64(word)) == finished) return;
+    if (dog.expired(lk, 2u)) return;
+  }
+}
+__device__ __forceinline__ void reader_gate_down(uint32_t* lk) {
+  atomicAdd_system(reinterpret_cast<unsigned long long*>(lk), ~0ull);  // gate -= 1 (never below zero: no borrow)
+}
 
 // Writer side, executed by the whole block around its reductions.
-__device__ __forceinline__ void writer_enter(uint32_t* lk, uint32_t (&state)[2]) {
+__device__ __forceinline__ void writer_enter(uint32_t* lk) {
   if (threadIdx.x == 0) {
-    state[0] = lock_chunk(lk);
-    __threadfence_system();  // the word is odd before any reduction of this block lands
+    writer_begin(lk);
+    __threadfence_system();  // the counter has moved before any reduction of this block lands
   }
   __syncthreads();
 }
 
-__device__ __forceinline__ void writer_leave(uint32_t* lk, const uint32_t (&state)[2]) {
-  __threadfence_system();  // every thread: my reductions (and mirror stores) are performed before ...
+__device__ __forceinline__ void writer_leave(uint32_t* lk) {
+  __threadfence_system();  // every thread: my reductions are performed before ...
   __syncthreads();
-  if (threadIdx.x == 0) unlock_chunk(lk, state[0]);  // ... the word becomes even again and the next ticket is served
+  if (threadIdx.x == 0) writer_end(lk);  // ... the chunk counts this writer as finished
 }
 
 enum { SRC_F32 = 0, SRC_BF16 = 1, SRC_DIFF = 2 };
@@ -179,8 +223,7 @@ template <int SRC, bool LOCKED>
 __global__ void __launch_bounds__(kThreads) ps_push_kernel(const Dev p, const PushSrc src) {
   Work w;
   if (!block_work(p, w)) return;
-  __shared__ uint32_t state[2];
-  if (LOCKED) writer_enter(w.lock, state);
+  if (LOCKED) writer_enter(w.lock);
   for_each_group(p, w, [&](long long f, long long g) {
     float d[8];
     if (SRC == SRC_F32) {
@@ -198,7 +241,7 @@ __global__ void __launch_bounds__(kThreads) ps_push_kernel(const Dev p, const Pu
     }
     apply_group<!LOCKED>(p, w.owner, g, d);
   });
-  if (LOCKED) writer_leave(w.lock, state);
+  if (LOCKED) writer_leave(w.lock);
 }
 
 // Optimizer step fused with the push: slots are updated in place from the flat gradient, the step of every element goes
@@ -207,10 +250,9 @@ template <int KIND, bool LOCKED>
 __global__ void __launch_bounds__(kThreads) ps_optimizer_push_kernel(const Dev p, const OptimDev o) {
   Work w;
   if (!block_work(p, w)) return;
-  __shared__ uint32_t state[2];
   __shared__ float sh_lr[2];
   if (threadIdx.x == 32) step_rates<KIND>(o, sh_lr[0], sh_lr[1]);
-  if (LOCKED) writer_enter(w.lock, state);
+  if (LOCKED) writer_enter(w.lock);
   else __syncthreads();
   const float lr_t = sh_lr[0], lr_adam = sh_lr[1];
   for_each_group(p, w, [&](long long f, long long g) {
@@ -224,7 +266,7 @@ __global__ void __launch_bounds__(kThreads) ps_optimizer_push_kernel(const Dev p
     }
     apply_group<!LOCKED>(p, w.owner, g, d);
   });
-  if (LOCKED) writer_leave(w.lock, state);
+  if (LOCKED) writer_leave(w.lock);
 }
 
 struct PullDst {
@@ -263,9 +305,9 @@ __device__ __forceinline__ void copy_chunk(const Dev& p, const Work& w, const Pu
   });
 }
 
-// Seqlock reader: [wait until the sequence word is even] copy [re-read the word: same value?]. Readers never write the
-// lock record, so they neither exclude each other nor slow a writer down. A chunk that keeps changing under the reader
-// (EB_PS_SEQ_RETRIES failed attempts) is copied under the writers' ticket instead, which bounds the wait.
+// Reader (see the lock record above): optimistic attempts between two reads of the counters; readers never exclude each
+// other and never make a writer wait. A chunk that keeps changing under the reader (EB_PS_SEQ_RETRIES failed attempts) is
+// copied behind the gate instead, which bounds the wait.
 template <bool SEQLOCK>
 __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const PullDst d) {
   Work w;
@@ -274,42 +316,34 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
     copy_chunk<false>(p, w, d);
   } else {
   __shared__ uint32_t sh_seq, sh_again;
+  const unsigned long long* word = reinterpret_cast<const unsigned long long*>(w.lock);
   for (int attempt = 0;; ++attempt) {
     if (attempt >= EB_PS_SEQ_RETRIES) {
-      __shared__ uint32_t sh_ticket;
-      if (threadIdx.x == 0) sh_ticket = lock_chunk(w.lock);
+      if (threadIdx.x == 0) reader_gate_up(w.lock);
       __syncthreads();
       copy_chunk<true>(p, w, d);
       fence_acq_rel_sys();
       __syncthreads();
-      if (threadIdx.x == 0) unlock_chunk(w.lock, sh_ticket);
+      if (threadIdx.x == 0) reader_gate_down(w.lock);
       return;
     }
     if (threadIdx.x == 0) {
-      uint32_t s0 = ld_acquire_sys(w.lock);
-      unsigned long long t0 = 0;
-      uint32_t spins = 0;
-      while (s0 & 1u) {  // a writer is inside: its block is running, this ends within microseconds
-        if ((++spins & 0x3FFu) == 0) {
-          const unsigned long long now = now_ns();
-          if (t0 == 0) t0 = now;
-          else if (now - t0 > kLockTimeoutNs) {
-            atomicExch_system(w.lock + 3, 2u);
-            break;
-          }
-        }
-        s0 = ld_acquire_sys(w.lock);
+      // finished FIRST, then started: equal values mean that nobody was inside when `started` was read
+      Watchdog dog;
+      uint32_t finished = ld_acquire_sys(w.lock + 2);
+      uint32_t started = started_of(ld_acquire_sys_u64(word));
+      while (started != finished) {  // a writer is inside: its block is running, this ends within microseconds
+        if (dog.expired(w.lock, 2u)) break;
+        finished = ld_acquire_sys(w.lock + 2);
+        started = started_of(ld_acquire_sys_u64(word));
       }
-      sh_seq = s0;
+      sh_seq = started;
     }
     __syncthreads();
     copy_chunk<true>(p, w, d);
-    fence_acq_rel_sys();  // the data loads above are performed before the sequence word is read again
+    fence_acq_rel_sys();  // the data loads above are performed before the counter is read again
     __syncthreads();
-    if (threadIdx.x == 0) {
-      const uint32_t s1 = ld_acquire_sys(w.lock);  // the version re-read
-      sh_again = (s1 != sh_seq) && !(sh_seq & 1u);
-    }
+    if (threadIdx.x == 0) sh_again = started_of(ld_acquire_sys_u64(word)) != sh_seq;  // the version re-read
     __syncthreads();
     if (!sh_again) return;
   }

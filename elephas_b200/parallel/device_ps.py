@@ -10,23 +10,24 @@ least loaded rank, so the pull-fused GEMM can read a layer through one tensor ma
 the vector tail; with N ranks the pushes and pulls of N workers therefore land on N memories, N L2s and N
 sets of NVLink ports.
 
-* **push** (``client.update_parameters``, ``server.py:117-132,201-210``): ONE kernel; the block that
-  serves a chunk takes a FIFO ticket *t*, waits until the chunk's sequence word reads ``2t``, stores
-  ``2t + 1`` (odd = a writer is inside), applies ``master -= delta`` with ``red.global.add.f32`` straight into
-  the owner's memory and stores ``2t + 2`` - which both ends the write and serves the next ticket. A lock is
-  held for two NVLink round trips. The delta can be given (fp32 / bf16), formed as ``before - after`` on
-  the fly, or - ``optimizer_push`` - be the optimizer step itself, computed from gradient and slots in
-  registers and never written to memory.
+* **push** (``client.update_parameters``, ``server.py:117-132,201-210``): ONE kernel; the block that serves a
+  chunk counts itself in (``started += 1``, one 64-bit atomic that also returns the chunk's gate), applies
+  ``master -= delta`` with ``red.global.add.f32`` straight into the owner's memory, and counts itself out
+  (``finished += 1``). Element-wise atomic additions commute, so writers need no exclusion among themselves:
+  every interleaving equals a serial order of the same updates, and no writer ever queues behind another.
+  The delta can be given (fp32 / bf16), formed as ``before - after`` on the fly, or - ``optimizer_push`` - be
+  the optimizer step itself, computed from gradient and slots in registers and never written to memory.
 * **pull** (``client.get_parameters``, ``server.py:107-115,212-218``): readers take **no lock**. In
-  ``mode='asynchronous'`` a chunk is copied between two reads of its sequence word and copied again when
-  the word was odd or moved (seqlock; after a few failed attempts the reader queues for a ticket like a
-  writer, which bounds its wait). Any number of workers read at once and never delay a writer - the
-  device-side form of the reference's reader/writer lock (``utils/rwlock.py:24-48``). bf16 destinations
-  are converted from the fp32 master on the fly.
-* ``mode='hogwild'`` skips ticket and sequence word (``server.py:109,120``): relaxed ``red.add``, plain
+  ``mode='asynchronous'`` a chunk is copied between two reads of its counters (``finished == started``:
+  nobody inside) and copied again when ``started`` moved (seqlock). A reader that keeps losing (8 attempts)
+  raises the chunk's gate - writers that see it step back out and wait - copies the quiet chunk and lowers
+  the gate, which bounds its wait. Any number of workers read at once - the device-side form of the
+  reference's reader/writer lock (``utils/rwlock.py:24-48``) - and none of them ever sees a half-applied push
+  inside a chunk. bf16 destinations are converted from the fp32 master on the fly.
+* ``mode='hogwild'`` skips the counters (``server.py:109,120``): relaxed ``red.add``, plain
   loads. Only here do pushes also refresh the bf16 mirror (read back, round, store), because only here is
   it read: by bf16 pulls and by the pull-fused GEMM (K2), whose TMA loads fetch weight tiles from the
-  owner's mirror. Under the locks that read-back would double the time a lock is held.
+  owner's mirror. In the locked mode that read-back would only lengthen the window in which readers have to retry.
 
 Consistency unit: the **chunk** (at least 8192 elements, at most 64 chunks per stripe). A seqlock pull
 never sees a half-applied push inside a chunk, and pushes are element-wise atomic in every mode, so no

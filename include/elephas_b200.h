@@ -251,17 +251,19 @@ int eb_ps_push_mirror(float* master, void* mirror_bf16, const float* delta_f32, 
  * [flat_off, flat_off + n) and lives at elements [owner_off, owner_off + n) of rank `owner`'s stripe (all three multiples
  * of 64; a Dense kernel is normally one span, so that the pull-fused GEMM, K2, can read it through one tensor map).
  * Every stripe is divided into `chunks` chunks of `chunk_len` elements, each guarded by its own lock record in the owner's
- * `ctrl` array (8 words per chunk: [0] sequence word S, [1] next ticket, [3] watchdog status). S = 2k when k operations
- * have completed and nobody is inside, 2t + 1 while the holder of ticket t is inside:
- *   push, locked   (mode='asynchronous'): the block that pushes a chunk takes a ticket t (FIFO), waits for S == 2t, stores
- *                  2t + 1, applies master -= delta with red.global.add.f32 into the owner's memory, stores 2t + 2 - all
- *                  inside one kernel, so a lock is only ever held by a running block, for two NVLink round trips
- *                  (elephas/parameter/server.py:117-132,201-210: write lock). The bf16 mirror is NOT maintained by
- *                  locked pushes (its read-back would double the hold time); locked pulls convert from the master;
- *   pull, seqlock  (mode='asynchronous'): readers take NO lock: read S, copy the chunk, read S again, retry when it was
- *                  odd or has changed (after EB_PS_SEQ_RETRIES failed attempts: take a ticket like a writer). Any
- *                  number of readers proceed at once and never delay a writer - the reference's "several threads can
- *                  hold this type of lock" for reads (elephas/utils/rwlock.py:24-33, server.py:107-115);
+ * `ctrl` array (8 words per chunk: [0] gate and [1] started - one 64-bit word - [2] finished, [3] watchdog status):
+ *   push, locked   (mode='asynchronous'): the block that pushes a chunk adds 1 to `started` (the same 64-bit atomic returns
+ *                  the gate), applies master -= delta with red.global.add.f32 into the owner's memory, fences and adds 1 to
+ *                  `finished` - inside one kernel. Additions are atomic per element, so concurrent writers need no
+ *                  exclusion among themselves: every interleaving equals a serial order of the same updates
+ *                  (elephas/parameter/server.py:117-132,201-210 serialises them with the write lock). The bf16 mirror is
+ *                  NOT maintained by locked pushes; locked pulls convert from the master;
+ *   pull, seqlock  (mode='asynchronous'): readers take NO lock: read `finished`, then `started` (equal: nobody inside), copy
+ *                  the chunk, read `started` again, retry when it moved. After EB_PS_SEQ_RETRIES failed attempts the reader
+ *                  raises the gate (writers that see it step back out and wait), waits for finished == started, copies and
+ *                  lowers the gate: its wait is bounded under any write load. Any number of readers proceed at once - the
+ *                  reference's "several threads can hold this type of lock" for reads (elephas/utils/rwlock.py:24-33,
+ *                  server.py:107-115) - and a pull never observes a half-applied push inside a chunk;
  *   unlocked       (mode='hogwild'): neither (server.py:109,120): relaxed red.add / plain loads; pushes refresh the
  *                  bf16 mirror of every element they touch, pulls and the pull-fused GEMM (K2) read it.
  * The unit of consistency is the chunk: a seqlock pull never observes a half-applied push inside a chunk. */

@@ -445,11 +445,12 @@ def test_striped_store_push_pull_match_pytorch(world, locked):
     assert torch.equal(part32[lo:], got32[lo:]) and bool((part32[:lo] == 7.0).all())
     assert torch.equal(part16[:lo], got16[:lo]) and bool((part16[lo:] == 3.0).all())
     assert all(int(c.view(-1, native.PS_LOCK_WORDS)[:, 3].max()) == 0 for c in ctrl)
-    if locked:  # every chunk's word counts completed operations twice (even = nobody inside) and agrees with the tickets
+    if locked:  # every chunk: as many writers counted out as counted in (three pushes), the readers' gate is down
         for r in range(world):
             words = ctrl[r].view(-1, native.PS_LOCK_WORDS)
             used = -(-plan.stripe_len[r] // plan.chunk_len)
-            assert bool((words[:used, 0] == 2 * words[:used, 1]).all()) and bool((words[:used, 1] >= 3).all())
+            assert bool((words[:used, 1] == words[:used, 2]).all()) and bool((words[:used, 1] >= 3).all())
+            assert bool((words[:used, 0] == 0).all())
 
 
 @pytest.mark.parametrize('opt', ['sgd', 'momentum', 'adam', 'rmsprop'])

@@ -4,7 +4,8 @@
 
 Payload = the wide MLP's 134,254,592 parameters as bf16 deltas (268.5 MB). Per call every rank reduces its 1/N slice
 of all peers' deltas over NVLink, updates its fp32 master slice and stores the refreshed bf16 weights into every
-peer's compute copy (``allreduce_shard_update``, K6b) - nothing else runs on the GPU. CUDA events around K calls, max
+peer's compute copy (``allreduce_shard_update``, K6b; ``nvls_update`` = the multimem variant K6c) - nothing else runs on the
+GPU. ``nccl_all_reduce_only`` times torch.distributed's all-reduce of the same payload (no master update, no bf16 refresh). CUDA events around K calls, max
 over ranks. Bytes that must cross NVLink per rank: (N-1)/N x payload inbound (delta loads) and the same outbound (bf16
 weight stores); the two directions are independent links. Reported against the measured peer-copy rate of this pool
 (770 GB/s per direction per GPU, B200_PROFILING.md) and the nominal 900 GB/s. Prints one JSON line per variant."""
@@ -35,6 +36,9 @@ def main():
     for name in ('delta0', 'delta1'):
         mem.local(name, torch.bfloat16, n).normal_()
     variants = [('shard_update', blocks) for blocks in (16, 32, 74, 148)] + [('twoshot_update', 148)]
+    if W > 1:
+        variants.append(('nccl_all_reduce_only', 0))  # the library's all-reduce of the same bf16 payload, WITHOUT the update
+        nccl_buf = torch.randn(n, device=rt.device).to(torch.bfloat16)
     vm = None
     if os.environ.get('COLL_NVLS', '1') != '0' and W > 1:
         try:
@@ -57,7 +61,9 @@ def main():
     for kind, blocks in variants:
         def call(flip):
             common = (mem.ptrs('delta%d' % flip), mem.ptrs('pad'), local, n, R, W, 1.0 / W, True, w32)
-            if kind == 'nvls_update':
+            if kind == 'nccl_all_reduce_only':
+                rt._dist.all_reduce(nccl_buf)
+            elif kind == 'nvls_update':
                 native.allreduce_nvls_update(vm.mc_ptr('delta%d' % flip), vm.mc_ptr('w16'), vm.ptrs('pad'), vlocal, n, R, W,
                                              1.0 / W, w32, blocks=blocks, device=rt.device)
             elif kind == 'shard_update':

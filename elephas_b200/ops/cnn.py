@@ -19,10 +19,35 @@ activations travel channels-last in bf16, master weights stay fp32. ``ELEPHAS_B2
 back to the torch / cuDNN ops (the A/B arm of the benchmark).
 """
 import os
+import threading
 
 import torch
 
 from . import native
+
+
+_scope = threading.local()  # .fresh: inside a training step whose engine has just refreshed the flat bf16 weight copy
+
+
+def weights_bf16(p):
+    """bf16 values of parameter ``p``: a view of the engine's flat bf16 copy inside a captured training step (ONE cast
+    kernel per step over all weights, ``TorchStepEngine._body``), a fresh cast everywhere else."""
+    w16 = getattr(p, '_eb_w16', None)
+    if w16 is not None and getattr(_scope, 'fresh', False) and w16.shape == p.shape:
+        return w16
+    return p.detach().to(torch.bfloat16)
+
+
+class fresh_weight_copy:
+    """Context of ``TorchStepEngine._body``: the flat bf16 copy matches the fp32 weights for the duration of the forward
+    pass (per thread: worker threads of one process train replicas side by side)."""
+
+    def __enter__(self):
+        self.prev = getattr(_scope, 'fresh', False)
+        _scope.fresh = True
+
+    def __exit__(self, *exc):
+        _scope.fresh = self.prev
 
 
 def enabled():
@@ -49,7 +74,7 @@ class _Conv2d(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, x, kernel, bias, stride, pads):
-        wb = kernel.detach().to(torch.bfloat16)
+        wb = weights_bf16(kernel)
         N, H, W, C = x.shape
         K, R, S, _ = wb.shape
         xb = _bf16(x) if C % 8 == 0 or not (x.dtype == torch.float32 and x.is_contiguous()) else None
@@ -230,7 +255,7 @@ class _Linear(torch.autograd.Function):
     def forward(ctx, x, weight, bias):
         out_dim, in_dim = weight.shape
         x2 = _bf16(x.reshape(-1, in_dim))
-        wb = weight.detach().to(torch.bfloat16)
+        wb = weights_bf16(weight)
         m = x2.shape[0]
         ldo = (out_dim + 7) // 8 * 8
         y = torch.empty(m, ldo, dtype=torch.bfloat16, device=x.device)

@@ -1,5 +1,6 @@
 """Graph-captured training step for models the native Dense engine does not cover (CNNs, custom activations,
-functional graphs): torch autograd + cuDNN compute, everything around it B200-style.
+functional graphs): torch autograd as the tape - the convolution / BatchNorm / pooling / Dense ops on it are the native
+sm_100a kernels of ``ops/cnn.py`` when the model computes in bf16 - everything around it B200-style.
 
 * all trainable weights live in ONE flat fp32 buffer (the model's tensors become views of it), gradients accumulate
   into a second flat buffer through pre-assigned ``.grad`` views, and the optimizer is ONE launch of the native
@@ -12,11 +13,13 @@ functional graphs): torch autograd + cuDNN compute, everything around it B200-st
 
 The reference trains these models through ``keras.Model.fit`` / ``train_on_batch`` (``elephas/worker.py:42,123``).
 """
+import contextlib
 import gc
 import os
 
 import torch
 
+from . import cnn as _cnn
 from . import native
 from .engine import _CAPTURE_LOCK, _optimizer_spec, native_enabled
 
@@ -59,6 +62,11 @@ class TorchStepEngine:
                 p.data = view                                   # the model now trains inside the flat buffer
                 p.grad = self.g32[off:off + p.numel()].view(p.shape)   # autograd accumulates in place
                 p._eb_flat_grad = True  # native ops may add their parameter gradients straight into this (zeroed) view
+        # bf16 copy of all weights for the native conv / linear ops: refreshed by ONE cast kernel at the start of a step
+        # (instead of one cast per layer), the layers read views of it (ops/cnn.py: weights_bf16)
+        self.w16 = torch.zeros(total, dtype=torch.bfloat16, device=dev)
+        for p, off in zip(self.params, offs):
+            p._eb_w16 = self.w16[off:off + p.numel()].view(p.shape)
         self.step = torch.zeros(1, dtype=torch.int64, device=dev)
         self.stats = torch.zeros(8, dtype=torch.float64, device=dev)   # [0] loss sum, [1..4] metric sums, [7] rows
         self.slots = [None, None, None]
@@ -139,7 +147,10 @@ class TorchStepEngine:
     def _body(self, x, y):
         model = self.model
         self.g32.zero_()
-        with model._autocast(x):
+        use16 = self._bf16_compute()
+        if use16:
+            native.cast_f32_to_bf16(self.w32, self.w16)
+        with model._autocast(x), (_cnn.fresh_weight_copy() if use16 else contextlib.nullcontext()):
             out = model(x, training=True)
         out = out.float()
         per_sample = model._loss_fn(y, out)
@@ -159,6 +170,9 @@ class TorchStepEngine:
             for i, (_, fn) in enumerate(model._metric_fns[:4]):
                 self.stats[1 + i] += fn(y, out.detach()).double().sum()
             self.stats[7] += float(x.shape[0])
+
+    def _bf16_compute(self):
+        return getattr(self.model, '_compute_dtype', 'float32') == 'bfloat16' and _cnn.enabled()
 
     def _record(self, key, x, y):
         from ..utils import tracing

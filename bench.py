@@ -210,7 +210,8 @@ def reference_arm():
     except Exception as exc:
         why = ("reference (elephas 4.1.0) not installable in this image: %s; it also needs tensorflow<=2.10, "
                "pyspark<=3.3, flask, h5py and python<3.11, none of which are available offline" % exc)
-    print_result(json.dumps({'impl': 'reference', 'unavailable': why or 'reference stack import failed'}))
+    if os.environ.get('RANK', '0') == '0':  # one line per job, also under torchrun
+        print_result(json.dumps({'impl': 'reference', 'unavailable': why or 'reference stack import failed'}))
 
 
 def run_sync(args, rt):

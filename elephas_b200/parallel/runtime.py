@@ -131,10 +131,10 @@ class Runtime:
         import torch
         if not self.distributed:
             return row.detach().cpu().unsqueeze(0)
-        src = row.to(self.device)
-        out = torch.empty((self.world_size,) + tuple(src.shape), dtype=src.dtype, device=self.device)
+        src = row.to(self.device).contiguous().view(-1)
+        out = torch.empty(self.world_size * src.numel(), dtype=src.dtype, device=self.device)  # (flat: every backend takes it)
         self._dist.all_gather_into_tensor(out, src)
-        return out.cpu()
+        return out.view(self.world_size, -1).cpu()
 
     def broadcast_object(self, obj, src=0):
         if not self.distributed:

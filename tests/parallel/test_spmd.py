@@ -57,3 +57,13 @@ def test_ranks_exchange_file_descriptors_over_unix_sockets():
            os.path.join(HERE, 'fd_exchange_script.py')]
     res = subprocess.run(cmd, env=dict(os.environ, OMP_NUM_THREADS='1'), capture_output=True, text=True, timeout=300)
     assert res.returncode == 0 and res.stdout.count('FD EXCHANGE OK') == 3, res.stdout[-2000:] + res.stderr[-3000:]
+
+
+def test_small_tensor_collectives_of_the_runtime():
+    """``Runtime.all_true`` / ``all_gather_rows`` (the agreement flag and the packed histories of the synchronous fast
+    path) over gloo with two CPU ranks."""
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
+           '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
+           os.path.join(HERE, 'runtime_helpers_script.py')]
+    res = subprocess.run(cmd, env=dict(os.environ, OMP_NUM_THREADS='1'), capture_output=True, text=True, timeout=300)
+    assert res.returncode == 0 and res.stdout.count('RT HELPERS OK') == 2, res.stdout[-2000:] + res.stderr[-3000:]

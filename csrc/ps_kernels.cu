@@ -186,7 +186,10 @@ __device__ __forceinline__ void writer_enter(uint32_t* lk) {
 __device__ __forceinline__ void writer_leave(uint32_t* lk) {
   __threadfence_system();  // every thread: my reductions are performed before ...
   __syncthreads();
-  if (threadIdx.x == 0) writer_end(lk);  // ... the chunk counts this writer as finished
+  if (threadIdx.x == 0) {
+    __threadfence_system();  // (release side of the counter: cumulative over the whole block's reductions)
+    writer_end(lk);          // ... the chunk counts this writer as finished
+  }
 }
 
 enum { SRC_F32 = 0, SRC_BF16 = 1, SRC_DIFF = 2 };

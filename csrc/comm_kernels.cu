@@ -386,27 +386,17 @@ __global__ void __launch_bounds__(512) allreduce_nvls_update_kernel(const CommDe
   __nv_bfloat16* mc_w16 = static_cast<__nv_bfloat16*>(p.avg[0]);
   for (long g0 = lo + blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; g0 < hi; g0 += stride * U) {
     uint4 raw[U];
-    float4 m0[U], m1[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long g = g0 + u * stride;
       if (g < hi) raw[u] = multimem_ld_reduce_bf16x8(mc_delta + g * 8);
-    }
-    // the master slice is local and independent of the reduced deltas: its loads travel with the switch's round trip
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const long g = g0 + u * stride;
-      if (g < hi) {
-        m0[u] = *reinterpret_cast<const float4*>(p.w32 + g * 8);
-        m1[u] = *reinterpret_cast<const float4*>(p.w32 + g * 8 + 4);
-      }
     }
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long g = g0 + u * stride;
       if (g < hi) {
         const uint4 v = raw[u];
-        float4 w0 = m0[u], w1 = m1[u];
+        float4 w0 = *reinterpret_cast<float4*>(p.w32 + g * 8), w1 = *reinterpret_cast<float4*>(p.w32 + g * 8 + 4);
         w0.x -= bf16_lo(v.x) * p.scale; w0.y -= bf16_hi(v.x) * p.scale; w0.z -= bf16_lo(v.y) * p.scale; w0.w -= bf16_hi(v.y) * p.scale;
         w1.x -= bf16_lo(v.z) * p.scale; w1.y -= bf16_hi(v.z) * p.scale; w1.z -= bf16_lo(v.w) * p.scale; w1.w -= bf16_hi(v.w) * p.scale;
         *reinterpret_cast<float4*>(p.w32 + g * 8) = w0;

@@ -9,8 +9,9 @@
 //   last layer   fp32 pre-activations go to global memory; the output activation (softmax / elementwise), loss and
 //                metrics are the existing K4 kernel
 //
-// Limits: 2-4 layers, hidden widths multiples of 16 up to 128, at most 128 output units, input width a multiple of 8.
-// Everything else runs the K1 GEMM chain. Reference call sites: model.predict / evaluate in the workers
+// Limits: 2-4 layers, hidden widths multiples of 16, input width a multiple of 8; up to 128 units per layer in this kernel,
+// up to 512 (and an input width up to 512) in the streamed-weights variant further down. Everything else runs the K1 GEMM
+// chain. Reference call sites: model.predict / evaluate in the workers
 // (elephas/spark_model.py:244-255,284-308; elephas/ml_model.py:199-233).
 #include <cuda.h>
 #include <cuda_bf16.h>
@@ -236,9 +237,282 @@ mlp_forward_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_const
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Wide variant (hidden widths up to 512, e.g. the Otto model 93-512-512-512-9): the weights no longer fit in shared
+// memory, so they STREAM - every layer's weights pass through the TMA ring in 128 x 64 tiles (they come out of L2: the
+// whole model is a megabyte) - while the activations stay resident: the input tile is loaded by TMA into the same
+// swizzled K-major buffer the epilogue writes the hidden activations into (8 chunks of 128 rows x 64 columns = 128 KB),
+// and the accumulator of a layer occupies up to all 512 TMEM columns (N chunks of 128 columns, one burst of MMAs each).
+// Same roles and barriers as above, plus in_full / in_free for the input tile.
+constexpr int kWideTmemCols = 512;
+constexpr int kWideActChunks = 8;
+constexpr int kWideTileN = 128;
+constexpr int kWideStageBytes = kWideTileN * 128;  // one weight tile: 128 units x 64 inputs (bf16)
+
+struct MlpWideDev {
+  int rows, layers;
+  int dims[EB_MLP_MAX_LAYERS + 1];
+  int npad[EB_MLP_MAX_LAYERS];
+  const float* bias[EB_MLP_MAX_LAYERS];
+  int act[EB_MLP_MAX_LAYERS];
+  float* z;
+  long ldz;
+  int stages, act_off, ring_off, bar_off, tiles;
+};
+
+__global__ void __launch_bounds__(kMlpThreads, 1)
+mlp_forward_wide_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w0,
+                        const __grid_constant__ CUtensorMap map_w1, const __grid_constant__ CUtensorMap map_w2,
+                        const __grid_constant__ CUtensorMap map_w3, const MlpWideDev p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* act_sm = smem + p.act_off;
+  uint8_t* ring = smem + p.ring_off;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + p.bar_off);
+  uint64_t* empty_bar = full_bar + 8;
+  uint64_t* acc_full = empty_bar + 8;    // MMA -> epilogue: the accumulator of the current layer is complete
+  uint64_t* act_ready = acc_full + 1;    // epilogue -> MMA: TMEM drained (and, for hidden layers, A operand written)
+  uint64_t* in_full = act_ready + 1;     // TMA -> MMA: the input tile has landed in the activation buffer
+  uint64_t* in_free = in_full + 1;       // MMA -> TMA: the last layer's MMAs have read the activation buffer
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(in_free + 1);
+
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
+  const int lane = threadIdx.x & 31;
+  const CUtensorMap* map_w[EB_MLP_MAX_LAYERS] = {&map_w0, &map_w1, &map_w2, &map_w3};
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_x);
+    for (int l = 0; l < p.layers; ++l) tma_prefetch_desc(map_w[l]);
+    for (int i = 0; i < 8; ++i) {
+      mbar_init(&full_bar[i], 1);
+      mbar_init(&empty_bar[i], 1);
+    }
+    mbar_init(acc_full, 1);
+    mbar_init(act_ready, 4);  // one arrival per epilogue warp
+    mbar_init(in_full, 1);
+    mbar_init(in_free, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) {
+    tmem_alloc<1>(tmem_slot, kWideTmemCols);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0);
+
+  if (warp == 0) {
+    // ------------------------------------------------------------------ TMA producer
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0, free_phase = 0;
+      bool first_tile = true;
+      const int in_chunks = (p.dims[0] + kMlpKBlock - 1) / kMlpKBlock;
+      for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+        if (!first_tile) {
+          mlp_wait(in_free, free_phase);  // the previous tile's last layer no longer reads the activation buffer
+          free_phase ^= 1;
+        }
+        first_tile = false;
+        mbar_arrive_expect_tx(in_full, in_chunks * kMlpChunkBytesA);
+        for (int c = 0; c < in_chunks; ++c)
+          tma_load_2d<1>(&map_x, in_full, act_sm + c * kMlpChunkBytesA, c * kMlpKBlock, t * kMlpTileM);
+        for (int l = 0; l < p.layers; ++l) {
+          const int kcs = (p.dims[l] + kMlpKBlock - 1) / kMlpKBlock;
+          const int ncs = (p.npad[l] + kWideTileN - 1) / kWideTileN;
+          for (int nc = 0; nc < ncs; ++nc)
+            for (int kb = 0; kb < kcs; ++kb) {
+              mlp_wait(&empty_bar[stage], phase ^ 1);
+              mbar_arrive_expect_tx(&full_bar[stage], kWideStageBytes);
+              tma_load_2d<1>(map_w[l], &full_bar[stage], ring + stage * kWideStageBytes, kb * kMlpKBlock, nc * kWideTileN);
+              if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // -------------------------------------------------------------------- MMA issuer
+    int stage = 0;
+    uint32_t phase = 0, act_phase = 0, in_phase = 0;
+    bool first_tile = true;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+      mlp_wait(in_full, in_phase);
+      in_phase ^= 1;
+      if (!first_tile) {
+        mlp_wait(act_ready, act_phase);  // the previous tile's last epilogue has drained the accumulator
+        act_phase ^= 1;
+      }
+      first_tile = false;
+      tc_fence_after();
+      for (int l = 0; l < p.layers; ++l) {
+        if (l > 0) {
+          mlp_wait(act_ready, act_phase);  // layer l-1's output is in the activation buffer, TMEM is free again
+          act_phase ^= 1;
+          tc_fence_after();
+        }
+        const int kcs = (p.dims[l] + kMlpKBlock - 1) / kMlpKBlock;
+        const int ncs = (p.npad[l] + kWideTileN - 1) / kWideTileN;
+        const bool last = l == p.layers - 1;
+        for (int nc = 0; nc < ncs; ++nc) {
+          const int ncols = min(kWideTileN, p.npad[l] - nc * kWideTileN);
+          const uint32_t idesc = make_idesc_bf16(kMlpTileM, ncols, 0, 0);
+          for (int kb = 0; kb < kcs; ++kb) {
+            mlp_wait(&full_bar[stage], phase);
+            tc_fence_after();
+            if (elect_one()) {
+              const uint64_t da = make_smem_desc_sw128(smem_u32(act_sm + kb * kMlpChunkBytesA), 16, 1024);
+              const uint64_t db = make_smem_desc_sw128(smem_u32(ring + stage * kWideStageBytes), 16, 1024);
+#pragma unroll
+              for (int k = 0; k < kMlpKBlock / kMlpUmmaK; ++k)
+                umma_bf16<1>(tmem_base + nc * kWideTileN, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_commit<1>(&empty_bar[stage]);
+              if (nc == ncs - 1 && kb == kcs - 1) {
+                umma_commit<1>(acc_full);
+                if (last) umma_commit<1>(in_free);
+              }
+            }
+            __syncwarp();
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------------- epilogue
+    const int quarter = warp & 3;
+    const int row = quarter * 32 + lane;
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quarter * 32) << 16);
+    uint32_t acc_phase = 0;
+    for (int t = blockIdx.x; t < p.tiles; t += gridDim.x) {
+      const long grow = static_cast<long>(t) * kMlpTileM + row;
+      for (int l = 0; l < p.layers; ++l) {
+        mlp_wait(acc_full, acc_phase);
+        acc_phase ^= 1;
+        tc_fence_after();
+        const bool last = l == p.layers - 1;
+        const int n_units = p.dims[l + 1];
+        const float* bias = p.bias[l];
+        for (int n0 = 0; n0 < p.npad[l]; n0 += 16) {
+          uint32_t v[32];
+          tmem_ld_32x16(taddr + n0, v);
+          tmem_ld_wait();
+          float x[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int n = n0 + j;
+            x[j] = __uint_as_float(v[j]) + ((bias != nullptr && n < n_units) ? bias[n] : 0.f);
+          }
+          if (last) {
+            if (grow < p.rows) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (n0 + j < n_units) p.z[grow * p.ldz + n0 + j] = x[j];
+            }
+          } else {
+            act_apply_chunk<16>(p.act[l], x);
+            const int chunk = n0 >> 6, g0 = (n0 & 63) >> 3;
+            uint8_t* base = act_sm + chunk * kMlpChunkBytesA + row * 128;
+            uint4 o0, o1;
+            o0.x = pack_bf16x2(x[0], x[1]); o0.y = pack_bf16x2(x[2], x[3]);
+            o0.z = pack_bf16x2(x[4], x[5]); o0.w = pack_bf16x2(x[6], x[7]);
+            o1.x = pack_bf16x2(x[8], x[9]); o1.y = pack_bf16x2(x[10], x[11]);
+            o1.z = pack_bf16x2(x[12], x[13]); o1.w = pack_bf16x2(x[14], x[15]);
+            *reinterpret_cast<uint4*>(base + ((g0 ^ (row & 7)) << 4)) = o0;
+            *reinterpret_cast<uint4*>(base + (((g0 + 1) ^ (row & 7)) << 4)) = o1;
+          }
+        }
+        if (!last) {
+          // the rest of the last 64-wide chunk is read by the next layer's MMAs (against zero weights): no stale NaNs there
+          const int upto = (p.npad[l] + 63) / 64 * 64;
+          for (int n0 = p.npad[l]; n0 < upto; n0 += 8) {
+            uint8_t* base = act_sm + (n0 >> 6) * kMlpChunkBytesA + row * 128;
+            *reinterpret_cast<uint4*>(base + ((((n0 & 63) >> 3) ^ (row & 7)) << 4)) = make_uint4(0u, 0u, 0u, 0u);
+          }
+        }
+        tc_fence_before();
+        if (!last) fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(act_ready);
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, kWideTmemCols);
+  }
+}
+
 }  // namespace eb
 
 using namespace eb;
+
+// Layers wider than 128 units: the streamed-weights kernel (input width and every layer up to 512).
+static int mlp_forward_wide(const EbMlpArgs* a, void* stream) {
+  if (a->dims[0] > kWideActChunks * kMlpKBlock)
+    return fail("eb_mlp_forward: input width %d exceeds %d (wide layers keep the input tile on chip)", a->dims[0],
+                kWideActChunks * kMlpKBlock);
+  MlpWideDev p;
+  p.rows = a->rows;
+  p.layers = a->layers;
+  p.dims[0] = a->dims[0];
+  for (int l = 0; l < a->layers; ++l) {
+    const int units = a->dims[l + 1];
+    const bool last = l == a->layers - 1;
+    if (units <= 0 || units > kWideTmemCols) return fail("eb_mlp_forward: layer %d has %d units (1..%d supported)", l, units, kWideTmemCols);
+    if (!last && (units % 16)) return fail("eb_mlp_forward: hidden width %d is not a multiple of 16", units);
+    if (a->w[l] == nullptr || (a->ldw[l] % 8) || (reinterpret_cast<uintptr_t>(a->w[l]) & 15) || a->ldw[l] < a->dims[l])
+      return fail("eb_mlp_forward: weights of layer %d must be 16-byte aligned with ldw %% 8 == 0 and ldw >= width", l);
+    p.dims[l + 1] = units;
+    p.npad[l] = (units + 15) / 16 * 16;
+    p.bias[l] = a->bias[l];
+    p.act[l] = a->act[l];
+  }
+  for (int l = a->layers; l < EB_MLP_MAX_LAYERS; ++l) {
+    p.dims[l + 1] = 0; p.npad[l] = 16; p.bias[l] = nullptr; p.act[l] = 0;
+  }
+  p.z = a->z;
+  p.ldz = a->ldz;
+  p.tiles = (a->rows + kMlpTileM - 1) / kMlpTileM;
+  // shared-memory plan: [activation buffer: 8 chunks of 128 rows x 128 B][weight ring][barriers]
+  p.act_off = 0;
+  p.ring_off = kWideActChunks * kMlpChunkBytesA;
+  p.stages = (227 * 1024 - 1024 - 256 - p.ring_off) / kWideStageBytes;
+  if (p.stages > 6) p.stages = 6;
+  p.bar_off = p.ring_off + p.stages * kWideStageBytes;
+  const int smem_bytes = p.bar_off + 256 + 1024;
+
+  CUtensorMap mx, mw[EB_MLP_MAX_LAYERS];
+  if (make_map(&mx, a->x, a->rows, a->dims[0], a->ldx, kMlpTileM, kMlpKBlock)) return 1;
+  for (int l = 0; l < EB_MLP_MAX_LAYERS; ++l) {
+    if (l < a->layers) {
+      if (make_map(&mw[l], a->w[l], p.dims[l + 1], p.dims[l], a->ldw[l], kWideTileN, kMlpKBlock)) return 1;
+    } else {
+      mw[l] = mw[0];
+    }
+  }
+  {
+    static std::mutex init_mutex;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    EB_CUDA_OK(cudaGetDevice(&dev));
+    std::lock_guard<std::mutex> guard(init_mutex);
+    if (!attr_set[dev & 63]) {
+      EB_CUDA_OK(cudaFuncSetAttribute(mlp_forward_wide_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      attr_set[dev & 63] = true;
+    }
+  }
+  int grid = num_sms();
+  if (grid > p.tiles) grid = p.tiles;
+  mlp_forward_wide_kernel<<<grid, kMlpThreads, smem_bytes, static_cast<cudaStream_t>(stream)>>>(mx, mw[0], mw[1], mw[2],
+                                                                                                mw[3], p);
+  EB_LAUNCH_OK("mlp_forward_wide_kernel");
+  return 0;
+}
 
 extern "C" int eb_mlp_forward(const EbMlpArgs* a, void* stream) {
   if (a == nullptr) return fail("eb_mlp_forward: null args");
@@ -248,6 +522,9 @@ extern "C" int eb_mlp_forward(const EbMlpArgs* a, void* stream) {
   if (a->x == nullptr || a->z == nullptr) return fail("eb_mlp_forward: input / output missing");
   if (a->dims[0] <= 0 || (a->dims[0] % 8) || (a->ldx % 8) || (reinterpret_cast<uintptr_t>(a->x) & 15))
     return fail("eb_mlp_forward: input width and ldx must be multiples of 8, x 16-byte aligned");
+  bool wide = false;
+  for (int l = 0; l < a->layers; ++l) wide |= a->dims[l + 1] > 128;
+  if (wide) return mlp_forward_wide(a, stream);
   MlpDev p;
   p.rows = a->rows;
   p.layers = a->layers;

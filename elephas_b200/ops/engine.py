@@ -395,7 +395,12 @@ class MLPEngine:
         """Inference forward through ``eb_mlp_forward`` (K8)? Small Dense chains only (see its limits)."""
         ok = getattr(self, '_fused_mlp', None)
         if ok is None:
-            ok = _FUSED_MLP and native.mlp_forward_supported(self.ops[0].ld_in, [op.out_dim for op in self.ops])
+            units = [op.out_dim for op in self.ops]
+            ok = _FUSED_MLP and native.mlp_forward_supported(self.ops[0].ld_in, units)
+            if ok and max(units) > 128:
+                # streamed-weights variant (layers up to 512 wide): the better choice for small row counts; on big blocks the
+                # chain of K1 GEMMs overlaps MMA and epilogue of a layer, which one CTA per row tile cannot
+                ok = os.environ.get('ELEPHAS_B200_FUSED_MLP_WIDE', '0') == '1'
             self._fused_mlp = ok
         return ok
 

@@ -270,11 +270,16 @@ def gemm(A, B, M, N, K, a_mn=False, b_mn=False, lda=None, ldb=None, out_bf16=Non
 
 # ------------------------------------------------------------- fused MLP forward (K8)
 def mlp_forward_supported(in_dim, units):
-    """Can ``eb_mlp_forward`` run a Dense chain with these widths? (2-4 layers, hidden widths multiples of 16 up to
-    128, at most 128 output units, 8-aligned input width.)"""
+    """Can ``eb_mlp_forward`` run a Dense chain with these widths? 2-4 layers, hidden widths multiples of 16, 8-aligned
+    input width; every layer up to 128 units (weights resident in shared memory), or up to 512 units with an input width
+    of at most 512 (weights streamed through the TMA ring, activations resident)."""
     units = list(units)
-    return (2 <= len(units) <= MLP_MAX_LAYERS and in_dim % 8 == 0 and all(u % 16 == 0 and 0 < u <= 128 for u in units[:-1])
-            and 0 < units[-1] <= 128)
+    if not (2 <= len(units) <= MLP_MAX_LAYERS and in_dim % 8 == 0 and all(u % 16 == 0 and u > 0 for u in units[:-1])
+            and units[-1] > 0):
+        return False
+    if max(units) <= 128:
+        return True
+    return max(units) <= 512 and in_dim <= 512
 
 
 def mlp_forward(x16, rows, in_dim, layers, z, ldx=None):

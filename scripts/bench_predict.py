@@ -1,9 +1,12 @@
-"""Forward pass of the reference's MNIST MLP (784-128-128-10): the one-kernel K8 forward against the per-layer K1 GEMM
-chain, device time (CUDA events, best of 10) for a block of rows already on the device, plus Model.predict end to end."""
+"""Forward pass of the reference's MNIST MLP (784-128-128-10; MODEL=otto: the Otto MLP 93-512-512-512-9 on the streamed-
+weights variant): the one-kernel K8 forward against the per-layer K1 GEMM chain, device time (CUDA events, best of 10) for a
+block of rows already on the device, plus Model.predict end to end."""
 import json
 import os
 import sys
 import time
+
+os.environ.setdefault('ELEPHAS_B200_FUSED_MLP_WIDE', '1')
 
 import numpy as np
 import torch
@@ -15,11 +18,13 @@ from elephas_b200.ops import native  # noqa: E402
 
 rows = int(os.environ.get('ROWS', 65536))
 torch.manual_seed(0)
-m = zoo.mnist_mlp()
+which = os.environ.get('MODEL', 'mnist')
+m = zoo.otto_mlp() if which == 'otto' else zoo.mnist_mlp()
+in_dim = 93 if which == 'otto' else 784
 m.compile(SGD(learning_rate=0.05), 'categorical_crossentropy', ['acc'])
 m.to('cuda')
 eng = m._native_engine()
-x = np.random.default_rng(0).random((rows, 784), dtype=np.float32)
+x = np.random.default_rng(0).random((rows, in_dim), dtype=np.float32)
 res = {}
 flush = torch.zeros(64 << 20, device='cuda')
 for fused in (True, False):
@@ -48,6 +53,7 @@ for fused in (True, False):
     res['fused' if fused else 'gemm_chain'] = {'forward_us_per_%d_rows' % buf.B: round(best * 1e3, 1),
                                                'predict_rows_per_s': round(rows / dt)}
     res.setdefault('check', []).append(float(out.sum()))
+res['model'] = which
 print(json.dumps(res))
 os.makedirs('gpurun_out', exist_ok=True)
-json.dump(res, open('gpurun_out/bench_predict.json', 'w'))
+json.dump(res, open('gpurun_out/bench_predict_%s.json' % which, 'w'))

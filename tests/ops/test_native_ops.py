@@ -489,6 +489,9 @@ def test_narrow_head_kernels_match_torch(native, rows, K, out):
     (1000, (200, 32, 48, 128, 3), ('relu', 'sigmoid', 'elu')),
     (20000, (784, 128, 128, 10), ('relu', 'relu')),      # several tiles per CTA
     (77, (96, 16, 1), ('linear',)),
+    (700, (96, 512, 512, 512, 9), ('relu', 'relu', 'relu')),   # the Otto MLP: weights streamed, activations resident
+    (129, (200, 144, 320, 48), ('tanh', 'relu')),              # widths that are no multiples of 64 / 128
+    (5000, (512, 512, 512), ('relu',)),                        # full-width input, several tiles per CTA
 ])
 def test_fused_mlp_forward_matches_layer_by_layer(native, rows, dims, acts):
     """K8: one persistent kernel carries a row tile through every layer (activations stay on chip)."""
@@ -517,7 +520,8 @@ def test_fused_mlp_forward_matches_layer_by_layer(native, rows, dims, acts):
     torch.cuda.synchronize()
     assert torch.allclose(z[:, :dims[-1]], ref, atol=3e-2, rtol=3e-2), (z[:, :dims[-1]] - ref).abs().max()
     assert torch.all(z[:, dims[-1]:] == 9.0)
-    assert not native.mlp_forward_supported(in_dim, (512, 10)) and not native.mlp_forward_supported(in_dim, (10,))
+    assert not native.mlp_forward_supported(in_dim, (1024, 10)) and not native.mlp_forward_supported(in_dim, (10,))
+    assert not native.mlp_forward_supported(784, (512, 10))  # wide layers need the input tile on chip (<= 512 columns)
 
 
 def test_launch_counter_moves(native):

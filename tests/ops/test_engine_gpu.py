@@ -568,6 +568,28 @@ def test_fused_mlp_predict_and_evaluate_match_the_gemm_chain(monkeypatch):
     assert la < lb                     # one forward kernel instead of three GEMMs per block of rows
 
 
+def test_wide_fused_mlp_predict_matches_the_gemm_chain(monkeypatch):
+    """K8, streamed-weights variant, on the Otto MLP (93-512-512-512-9): opt-in, same predictions as the GEMM chain."""
+    rng = np.random.default_rng(5)
+    xt = rng.random((3000, 93), dtype=np.float32)
+    torch.manual_seed(13)
+    m = zoo.otto_mlp()
+    m.compile(SGD(lr=0.05), 'categorical_crossentropy', ['acc'])
+    m.to('cuda')
+    outs = {}
+    for wide in ('1', '0'):
+        monkeypatch.setenv('ELEPHAS_B200_FUSED_MLP_WIDE', wide)
+        eng = m._native_engine()
+        eng._fused_mlp = None
+        eng.invalidate_graphs()
+        launches = native_launches()
+        outs[wide] = (m.predict(xt), native_launches() - launches)
+        assert eng._fused_mlp_ok() is (wide == '1')
+    (pa, la), (pb, lb) = outs['1'], outs['0']
+    assert np.allclose(pa, pb, atol=2e-2) and (pa.argmax(1) == pb.argmax(1)).mean() > 0.99
+    assert la < lb
+
+
 def native_launches():
     from elephas_b200.ops import native
     return native.launch_count()

@@ -25,3 +25,30 @@ def test_histories_travel_as_one_row_per_rank():
     assert both[0] is None and both[1] == h0 and list(both[1]) == list(h0)
     h2 = {'loss': [1e-30, 3.0], 'acc': [], 'val_loss': [2.0, 1.0]}   # an empty list is not an absent key
     assert sync_fast._gather_histories(_TwoRanks(), h2, keys, 4) == [h2]
+
+
+def test_nvls_master_gather_only_when_the_buckets_tile_the_buffer():
+    """The multimem.st gather of the sharded fp32 master copies the whole staging buffer over the master: only valid when
+    every element belongs to exactly one bucket (then the ranks' owned slices cover the buffer)."""
+    class _Eng:
+        def __init__(self, ranges, numel):
+            self._ranges, self.w32 = ranges, torch.zeros(numel)
+
+        def bucket_ranges(self):
+            return self._ranges
+
+    class _Rt:
+        rank, world_size = 1, 4
+
+    def ctx(ranges, numel):
+        c = sync_fast.SyncContext.__new__(sync_fast.SyncContext)
+        c.eng, c.rt = _Eng(ranges, numel), _Rt()
+        return c
+
+    tiled = ctx([(128, 64), (0, 128), (192, 64)], 256)            # emitted last layer first, vectors last: any order
+    assert tiled._ranges_cover_master()
+    owned = tiled._owned_ranges()
+    assert owned == [(128 + 16, 128 + 32), (32, 64), (192 + 16, 192 + 32)]      # slice 1 of 4 of every bucket
+    assert not ctx([(0, 128), (192, 64)], 256)._ranges_cover_master()          # a gap
+    assert not ctx([(0, 128), (128, 64)], 256)._ranges_cover_master()          # the tail is nobody's
+    assert not ctx([(0, 132), (132, 124)], 256)._ranges_cover_master()         # slices must be groups of 8 elements

@@ -120,6 +120,8 @@ class _InputFeeder:
     on the copy stream, record an event the compute stream waits on.
     """
 
+    SLOTS = 3  # device staging slots of the streamed modes (the host-cast mode keeps two, its helper thread runs ahead)
+
     def __init__(self, eng, x, y, batch_size, mode, shuffle, x16=None):
         self.eng, self.bs, self.shuffle = eng, batch_size, shuffle
         # features already staged as bf16 in pinned memory by the caller (to_sharded_rdd(feature_dtype='bfloat16')): they
@@ -154,7 +156,7 @@ class _InputFeeder:
                 ld = eng.ops[0].ld_in
                 self.stage = [(torch.empty(batch_size, ld, dtype=torch.bfloat16, device=dev),
                                torch.empty(batch_size, ycols, dtype=torch.float32, device=dev),
-                               torch.cuda.Event()) for _ in range(2)]
+                               torch.cuda.Event()) for _ in range(self.SLOTS)]
                 self.h2d_bytes_per_step = batch_size * (ld * 2 + ycols * 4)
             elif self.host_bf16:
                 ld = eng.ops[0].ld_in
@@ -170,9 +172,9 @@ class _InputFeeder:
             else:
                 self.stage = [(torch.empty(batch_size, cols, dtype=torch.float32, device=dev),
                                torch.empty(batch_size, ycols, dtype=torch.float32, device=dev),
-                               torch.cuda.Event()) for _ in range(2)]
+                               torch.cuda.Event()) for _ in range(self.SLOTS)]
                 self.h2d_bytes_per_step = batch_size * (cols + ycols) * 4
-            self.consumed = [None, None]
+            self.consumed = [None] * self.SLOTS
         self.order = None
 
     def _choose_host_bf16(self, eng, batch_size):
@@ -236,7 +238,8 @@ class _InputFeeder:
                 self._submit(0, 0)
                 self._submit(1, self.bs)
             else:
-                self._prefetch(0, 0)
+                for ahead in range(self.SLOTS - 1):  # copies run SLOTS - 1 batches ahead of the step that consumes them
+                    self._prefetch(ahead, ahead * self.bs)
 
     def _host_batch(self, start, rows):
         xsrc = self.staged16 if self.staged16 is not None else self.x_host
@@ -250,7 +253,7 @@ class _InputFeeder:
         rows = min(self.bs, self.n - start)
         if rows <= 0:
             return
-        slot = step % 2
+        slot = step % self.SLOTS
         xs, ys, ev = self.stage[slot]
         xh, yh = self._host_batch(start, rows)
         if self.consumed[slot] is not None:
@@ -306,7 +309,7 @@ class _InputFeeder:
                 buf.x32.copy_(self.xd[start:start + rows])
                 buf.y32.copy_(self.yd[start:start + rows])
             return rows
-        slot = step % 2
+        slot = step % (2 if self.host_bf16 else self.SLOTS)
         xs, ys, ev = self.stage[slot]
         cur = torch.cuda.current_stream(self.eng.device)
         if self.host_bf16:
@@ -326,8 +329,9 @@ class _InputFeeder:
         if self.host_bf16:
             self._submit(step + 2, start + rows + self.bs)
         else:
-            # the next batch goes into the other slot: its H2D copy overlaps this step's compute
-            self._prefetch(step + 1, start + rows)
+            # the batch SLOTS - 1 steps ahead goes into the slot that was consumed longest ago: two copies are in flight
+            # behind the running step, so one slow copy (eight GPUs share the host's PCIe switches) does not stall it
+            self._prefetch(step + self.SLOTS - 1, start + rows + (self.SLOTS - 2) * self.bs)
         return rows
 
 

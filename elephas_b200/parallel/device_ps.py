@@ -211,8 +211,8 @@ class DeviceStore:
         return self.mem is not None
 
     def configure(self, local_workers=1, distributed=False):
-        """Kept for callers of the first design (one owner GPU, lock kernels on a dedicated stream): ticket and sequence
-        word are now taken and released inside the push / pull kernels themselves, so the same code is correct for
+        """Kept for callers of the first design (one owner GPU, lock kernels on a dedicated stream): the chunk counters are
+        now read and moved inside the push / pull kernels themselves, so the same code is correct for
         worker threads of one process and for one worker per rank. Nothing to choose any more."""
 
     def matrix_source(self, flat_off):

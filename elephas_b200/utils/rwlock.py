@@ -4,7 +4,8 @@ Reference: ``elephas/utils/rwlock.py:1-67`` (same public methods: ``acquire_read
 ``acquire_write``, ``release``). Any number of readers may hold the lock at once, or exactly one
 writer. A waiting writer blocks *new* readers so a stream of pulls cannot starve pushes. This host
 lock guards the HTTP / socket parameter servers; the NVLink parameter server implements the same
-policy on the device with a ticket/sequence lock (``csrc/ps_kernels.cu``).
+policy on the device per chunk: writers count themselves in and out, readers validate their copy against the
+counters and can raise a gate when they keep losing (``csrc/ps_kernels.cu``).
 """
 import threading
 from contextlib import contextmanager

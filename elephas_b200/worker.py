@@ -264,7 +264,7 @@ class AsynchronousSparkWorker(_WorkerBase):
                lock and retry a chunk that a writer touched meanwhile.
         train  forward / loss / backward on the native engine; the gradient stays in the flat fp32 buffer
         push   the optimizer kernel IS the push: the step of every element goes from registers into its owner's master
-               (``red.add``, under the chunk's ticket in asynchronous mode); the delta is never materialised
+               (``red.add``; counted in and out of the chunk in asynchronous mode); the delta is never materialised
 
         Reference loop: ``get_parameters`` / ``set_weights`` / ``train_on_batch`` / ``subtract_params`` /
         ``update_parameters`` per batch (``elephas/worker.py:116-127``). Options (``train_config``): ``input_mode``

@@ -31,6 +31,7 @@ PAGES = [
     ('runtime/symmetric-memory.md', 'elephas_b200.parallel.symm', None),
     ('runtime/sync-torch-path.md', 'elephas_b200.parallel.sync_torch', None),
     ('runtime/torch-step.md', 'elephas_b200.ops.torch_step', None),
+    ('runtime/native-cnn-ops.md', 'elephas_b200.ops.cnn', None),
     ('utils/tracing.md', 'elephas_b200.utils.tracing', None),
     ('runtime/engine.md', 'elephas_b200.ops.engine', None),
     ('runtime/native-bindings.md', 'elephas_b200.ops.native', None),

@@ -1,9 +1,11 @@
 """Small CNN through SparkModel in synchronous mode: a model the native Dense engine does not cover.
 
-On a GPU the training step (torch autograd + cuDNN) is captured into a CUDA graph over flat weights with the native
-optimizer kernel, `set_compute_dtype('bfloat16')` runs it under bf16 autocast, and the per-epoch weight deltas are
-averaged by the fused P2P all-reduce; on a CPU the same script runs the eager path. BASELINE.json config 5 is the same
-flow with `zoo.resnet50()` (`benchmarks/configs.py --config 5`).
+On a GPU `set_compute_dtype('bfloat16')` puts every convolution, BatchNormalization (+ ReLU), pooling and Dense layer on
+this repository's sm_100a kernels (implicit-GEMM convolutions on tcgen05, `ops/cnn.py`), the whole training step is
+captured into a CUDA graph over flat weights with the native optimizer kernel, and the weight deltas are averaged by the
+fused all-reduce + update kernel over NVLink (per batch with `frequency='batch'`: inside the captured step); on a CPU the
+same script runs the eager torch path. BASELINE.json config 5 is the same flow with `zoo.resnet50()`
+(`python bench.py --config resnet50`).
 
     python examples/cnn_sync.py
     python -m torch.distributed.run --nproc-per-node 4 --master-addr 127.0.0.1 examples/cnn_sync.py

@@ -56,6 +56,14 @@ __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, 
   asm volatile("red.relaxed.sys.global.add.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 __device__ __forceinline__ void fence_acq_rel_sys() { asm volatile("fence.acq_rel.sys;" ::: "memory"); }
+// The fence of the ONE thread that moves a chunk's counters; the block's other threads are ordered with it by bar.sync
+// (barrier + release pattern of a single thread is cumulative over what the block did before the barrier). A store whose
+// stripes all live on this GPU has no observer outside of it: device scope is enough there, and several times cheaper
+// (ncu of the one-GPU loop: the system-scope fences of all 512 threads were 60 % of both kernels' stall cycles).
+__device__ __forceinline__ void fence_counters(bool sys) {
+  if (sys) asm volatile("fence.acq_rel.sys;" ::: "memory");
+  else asm volatile("fence.acq_rel.gpu;" ::: "memory");
+}
 __device__ __forceinline__ unsigned long long now_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -175,20 +183,19 @@ __device__ __forceinline__ void reader_gate_down(uint32_t* lk) {
 }
 
 // Writer side, executed by the whole block around its reductions.
-__device__ __forceinline__ void writer_enter(uint32_t* lk) {
+__device__ __forceinline__ void writer_enter(uint32_t* lk, bool sys) {
   if (threadIdx.x == 0) {
     writer_begin(lk);
-    __threadfence_system();  // the counter has moved before any reduction of this block lands
+    fence_counters(sys);  // the counter has moved before any reduction of this block lands
   }
   __syncthreads();
 }
 
-__device__ __forceinline__ void writer_leave(uint32_t* lk) {
-  __threadfence_system();  // every thread: my reductions are performed before ...
-  __syncthreads();
+__device__ __forceinline__ void writer_leave(uint32_t* lk, bool sys) {
+  __syncthreads();  // every thread's reductions are issued ...
   if (threadIdx.x == 0) {
-    __threadfence_system();  // (release side of the counter: cumulative over the whole block's reductions)
-    writer_end(lk);          // ... the chunk counts this writer as finished
+    fence_counters(sys);  // ... and performed (release side of the counter, cumulative over the block) before ...
+    writer_end(lk);       // ... the chunk counts this writer as finished
   }
 }
 
@@ -226,7 +233,7 @@ template <int SRC, bool LOCKED>
 __global__ void __launch_bounds__(kThreads) ps_push_kernel(const Dev p, const PushSrc src) {
   Work w;
   if (!block_work(p, w)) return;
-  if (LOCKED) writer_enter(w.lock);
+  if (LOCKED) writer_enter(w.lock, p.world > 1);
   for_each_group(p, w, [&](long long f, long long g) {
     float d[8];
     if (SRC == SRC_F32) {
@@ -244,7 +251,7 @@ __global__ void __launch_bounds__(kThreads) ps_push_kernel(const Dev p, const Pu
     }
     apply_group<!LOCKED>(p, w.owner, g, d);
   });
-  if (LOCKED) writer_leave(w.lock);
+  if (LOCKED) writer_leave(w.lock, p.world > 1);
 }
 
 // Optimizer step fused with the push: slots are updated in place from the flat gradient, the step of every element goes
@@ -255,7 +262,7 @@ __global__ void __launch_bounds__(kThreads) ps_optimizer_push_kernel(const Dev p
   if (!block_work(p, w)) return;
   __shared__ float sh_lr[2];
   if (threadIdx.x == 32) step_rates<KIND>(o, sh_lr[0], sh_lr[1]);
-  if (LOCKED) writer_enter(w.lock);
+  if (LOCKED) writer_enter(w.lock, p.world > 1);
   else __syncthreads();
   const float lr_t = sh_lr[0], lr_adam = sh_lr[1];
   for_each_group(p, w, [&](long long f, long long g) {
@@ -269,7 +276,7 @@ __global__ void __launch_bounds__(kThreads) ps_optimizer_push_kernel(const Dev p
     }
     apply_group<!LOCKED>(p, w.owner, g, d);
   });
-  if (LOCKED) writer_leave(w.lock);
+  if (LOCKED) writer_leave(w.lock, p.world > 1);
 }
 
 struct PullDst {
@@ -325,9 +332,11 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
       if (threadIdx.x == 0) reader_gate_up(w.lock);
       __syncthreads();
       copy_chunk<true>(p, w, d);
-      fence_acq_rel_sys();
       __syncthreads();
-      if (threadIdx.x == 0) reader_gate_down(w.lock);
+      if (threadIdx.x == 0) {
+        fence_counters(p.world > 1);
+        reader_gate_down(w.lock);
+      }
       return;
     }
     if (threadIdx.x == 0) {
@@ -344,9 +353,11 @@ __global__ void __launch_bounds__(kThreads) ps_pull_kernel(const Dev p, const Pu
     }
     __syncthreads();
     copy_chunk<true>(p, w, d);
-    fence_acq_rel_sys();  // the data loads above are performed before the counter is read again
-    __syncthreads();
-    if (threadIdx.x == 0) sh_again = started_of(ld_acquire_sys_u64(word)) != sh_seq;  // the version re-read
+    __syncthreads();  // every thread's loads have returned (their values were stored) ...
+    if (threadIdx.x == 0) {
+      fence_counters(p.world > 1);  // ... before the counter is read again
+      sh_again = started_of(ld_acquire_sys_u64(word)) != sh_seq;  // the version re-read
+    }
     __syncthreads();
     if (!sh_again) return;
   }

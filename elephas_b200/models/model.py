@@ -497,6 +497,13 @@ class Model:
                 stats.append(float(fn(yb, out.detach()).mean()))
         return stats
 
+    def _tune_cpu_threads(self, rows):
+        """CPU only: intra-op thread count fitted to this model's layer sizes (``utils/cpu_threads.py``: the small layers of
+        the reference's workloads run many times faster on one thread than on a pool of all cores)."""
+        if self._device.type == 'cpu':
+            from ..utils import cpu_threads
+            cpu_threads.tune_for(self, rows)
+
     def train_on_batch(self, x, y, **kwargs):
         self._require_compiled()
         eng = self._native_engine()
@@ -507,6 +514,7 @@ class Model:
             yb = _as_tensor(y, self._device)
             if xb.dim() == 1:
                 xb = xb.unsqueeze(-1)
+            self._tune_cpu_threads(len(xb))
             te = self._torch_engine()
             if te is not None:
                 te.stats.zero_()
@@ -538,6 +546,7 @@ class Model:
         if eng is not None:
             eng.fit(x, y, batch_size, epochs, shuffle, history, x_val, y_val, verbose, initial_epoch)
             return history
+        self._tune_cpu_threads(batch_size)
         xt = _as_tensor(x, self._device)
         yt = _as_tensor(y, self._device)
         if xt.dim() == 1:
@@ -594,6 +603,7 @@ class Model:
         xt = _as_tensor(x, self._device)
         if xt.dim() == 1:
             xt = xt.unsqueeze(-1)
+        self._tune_cpu_threads(_PREDICT_BLOCK)
         outs = []
         # Fixed-size row blocks (the last one zero-padded): every GEMM the library sees has the same
         # shape, so a row's result does not depend on how the caller batched the rows - the
@@ -630,6 +640,7 @@ class Model:
         n = xt.shape[0]
         sums = [0.0] * len(self.metrics_names)
         step = max(batch_size, 8192)
+        self._tune_cpu_threads(min(step, max(n, 1)))
         for start in range(0, n, step):
             xb, yb = xt[start:start + step], yt[start:start + step]
             with self._autocast(xb):

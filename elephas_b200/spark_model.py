@@ -343,26 +343,40 @@ class SparkModel:
         current = init
         zero = get_neutral(init)
 
+        pool = None
+        if rt.device.type == 'cpu' and len(workers) > 1 and os.environ.get('ELEPHAS_B200_CPU_PARALLEL_WORKERS', '1') != '0':
+            # the replicas of one process train side by side in threads (torch drops the GIL inside its operators) - what
+            # Spark's ``local[N]`` does with N executor threads
+            from concurrent.futures import ThreadPoolExecutor
+            pool = ThreadPoolExecutor(max_workers=len(workers), thread_name_prefix='elephas-sync-worker')
+
+        def rounds(fn):
+            return list(pool.map(fn, workers)) if pool is not None else [fn(w) for w in workers]
+
         def averaged_round(deltas):
             local = zero
             for d in deltas:
                 local = add_params(local, d)
             return subtract_params(current, self._reduce_deltas(rt, local, n_sub))
 
-        if sync_rounds == 'fit' or (self.frequency == 'epoch' and epochs <= 1):
-            current = averaged_round([w.train_round(current, epochs=epochs)[0] for w in workers])
-        elif self.frequency == 'epoch':
-            for epoch in range(epochs):
-                current = averaged_round([w.train_round(current, epochs=1, initial_epoch=epoch)[0] for w in workers])
-        else:  # 'batch': every worker takes one step from the same weights, then the replicas are averaged
-            steps = max([w.num_batches() for w in workers] + [0])
-            steps = int(rt.all_reduce_max_(torch.tensor([steps], device=rt.device if rt.device.type == 'cuda'
-                                                        else 'cpu'))[0])
-            for _ in range(epochs):
-                for b in range(steps):
-                    current = averaged_round([w.train_batch(current, b) for w in workers])
-                for w in workers:
-                    w.end_batch_epoch()
+        try:
+            if sync_rounds == 'fit' or (self.frequency == 'epoch' and epochs <= 1):
+                current = averaged_round(rounds(lambda w: w.train_round(current, epochs=epochs)[0]))
+            elif self.frequency == 'epoch':
+                for epoch in range(epochs):
+                    current = averaged_round(rounds(lambda w, e=epoch: w.train_round(current, epochs=1, initial_epoch=e)[0]))
+            else:  # 'batch': every worker takes one step from the same weights, then the replicas are averaged
+                steps = max([w.num_batches() for w in workers] + [0])
+                steps = int(rt.all_reduce_max_(torch.tensor([steps], device=rt.device if rt.device.type == 'cuda'
+                                                            else 'cpu'))[0])
+                for _ in range(epochs):
+                    for b in range(steps):
+                        current = averaged_round(rounds(lambda w, i=b: w.train_batch(current, i)))
+                    for w in workers:
+                        w.end_batch_epoch()
+        finally:
+            if pool is not None:
+                pool.shutdown(wait=True)
         local_hist = [(i, (w.history if w.trainable else None)) for w, (i, _) in zip(workers, mine)]
         gathered = [h for chunk in rt.all_gather_object(local_hist) for h in chunk]
         self._training_histories.extend(h for _, h in sorted(gathered, key=lambda t: t[0]))

@@ -50,7 +50,7 @@ def _weights_of(parameters):
 
 
 # counters for tests / diagnostics: which device paths actually ran in this process
-STATS = {'fused_pull_steps': 0, 'device_ps_steps': 0}
+STATS = {'fused_pull_steps': 0, 'device_ps_steps': 0, 'host_store_rounds': 0}
 
 class _WorkerBase:
     def __init__(self, json, parameters, train_config, master_optimizer, master_loss, master_metrics,
@@ -200,6 +200,10 @@ class AsynchronousSparkWorker(_WorkerBase):
             self._train_against_device_ps(model, eng, x_train, y_train, epochs, batch_size, trainable)
             yield []
             return
+        if isinstance(self.client, DeviceClient) and model.device.type == 'cpu' and not self.client._store().on_device:
+            self._train_against_host_store(model, self.client._store(), x_train, y_train, epochs, batch_size, trainable)
+            yield []
+            return
 
         if self.frequency == 'epoch':
             cfg = dict(self.train_config)
@@ -225,6 +229,47 @@ class AsynchronousSparkWorker(_WorkerBase):
                     model.train_on_batch(x_train[lo:hi], y_train[lo:hi])
                     self.client.update_parameters(subtract_params(before, model.get_weights()))
         yield []
+
+    def _train_against_host_store(self, model, store, x_train, y_train, epochs, batch_size, trainable):
+        """CPU form of the device path (``parameter_server_mode='nvlink'`` on a machine without a GPU: the store is a flat
+        tensor in this process behind the host RWLock). The same pull -> train -> push loop as the reference's
+        (``elephas/worker.py:102-127``), but the weights travel as ONE flat tensor in the model's own layout: no list of
+        NumPy arrays, no Keras-layout transposes, no pickling - two copies and one subtraction per round."""
+        import torch
+        layout = store.layout
+        flat = torch.empty(layout.numel, dtype=torch.float32)
+        before = torch.empty_like(flat)
+        n = x_train.shape[0]
+
+        def pull():
+            store.pull_into(flat)
+            before.copy_(flat)
+            layout.unpack_to_model(flat, model)
+
+        def push():
+            layout.pack_model(model, out=flat)
+            store.push_delta(before=before, after=flat)
+            STATS['host_store_rounds'] += 1
+
+        if self.frequency == 'epoch':
+            cfg = dict(self.train_config)
+            for epoch in range(epochs):
+                pull()
+                if trainable:
+                    cfg['epochs'] = epoch + 1
+                    cfg['initial_epoch'] = epoch
+                    h = model.fit(x_train, y_train, **cfg)
+                    for k, v in h.history.items():
+                        self.history.setdefault(k, []).extend(v)
+                push()
+        elif trainable:
+            nb_batch = -(-n // batch_size)
+            for _ in range(epochs):
+                for b in range(nb_batch):
+                    pull()
+                    lo, hi = b * batch_size, min(n, (b + 1) * batch_size)
+                    model.train_on_batch(x_train[lo:hi], y_train[lo:hi])
+                    push()
 
     def _train_against_device_ps(self, model, eng, x_train, y_train, epochs, batch_size, trainable):
         """B200 path of the pull -> train -> push loop: the replica's weights never leave the device.

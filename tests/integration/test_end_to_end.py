@@ -133,3 +133,30 @@ def test_unknown_mode(spark_context, classification_model, mnist_data):
 def test_uncompiled_model_is_rejected(classification_model):
     with pytest.raises(Exception):
         SparkModel(classification_model)
+
+
+@pytest.mark.parametrize('mode,frequency', [('asynchronous', 'batch'), ('hogwild', 'epoch')])
+def test_cpu_workers_move_flat_tensors_against_the_in_process_store(spark_context, mode, frequency):
+    """``parameter_server_mode='nvlink'`` without a GPU: the store is a flat tensor in this process and the workers pull /
+    push flat tensors in the model's own layout (no list of arrays, no pickling) - same training result as the socket
+    server within the tolerance of asynchronous updates, and every round goes through the fast path."""
+    import numpy as np
+    from elephas_b200 import worker as worker_mod
+    from elephas_b200.models import SGD, Dense, Sequential
+    from elephas_b200.parallel import get_runtime
+    if get_runtime().device.type != 'cpu':
+        pytest.skip('CPU form of the device path')
+    rng = np.random.default_rng(3)
+    x = rng.normal(size=(512, 20)).astype('float32')
+    labels = (x[:, :4].sum(1) > 0).astype(int)
+    y = np.eye(2, dtype='float32')[labels]
+    model = Sequential([Dense(19, input_dim=20, activation='relu'), Dense(2, activation='softmax')])   # 19: padded rows
+    model.compile(SGD(learning_rate=0.2), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode=mode, frequency=frequency, parameter_server_mode='nvlink', num_workers=2)
+    before = sm.evaluate(x, y)
+    rounds = worker_mod.STATS['host_store_rounds']
+    sm.fit(to_simple_rdd(spark_context, x, y), epochs=4, batch_size=32, verbose=0)
+    after = sm.evaluate(x, y)
+    expected = 2 * 4 * (8 if frequency == 'batch' else 1)   # workers x epochs x (batches of a 256-row partition | 1)
+    assert worker_mod.STATS['host_store_rounds'] - rounds == expected
+    assert after[0] < before[0] and after[1] > 0.85

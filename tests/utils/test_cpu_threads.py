@@ -20,7 +20,8 @@ def test_small_layers_run_on_one_thread_and_the_choice_is_adjustable(monkeypatch
         wide = zoo.wide_mlp(input_dim=512, hidden=512, depth=2, out_dim=1)   # 2 * 4096 * 512 * 512 = 2 GFLOP: timed
         wide.compile(SGD(learning_rate=0.01), 'mse')
         chosen = cpu_threads.tune_for(wide, 4096)
-        assert 1 <= chosen <= max(start, 1) and torch.get_num_threads() == chosen
+        upper = cpu_threads.tune_for._upper   # the count torch had when this process first asked (other tests may have run)
+        assert 1 <= chosen <= upper and torch.get_num_threads() == chosen
         assert cpu_threads.tune_for(wide, 4096) == chosen                    # cached per shape
     finally:
         torch.set_num_threads(start)

@@ -1,54 +1,53 @@
-"""Client/server factories (reference: ``elephas/parameter/factory.py:6-41``), plus ``'nvlink'``."""
-from abc import ABC, abstractmethod
+"""Factories that pair a parameter client with its server: ``'http'``, ``'socket'`` and the device store ``'nvlink'``.
 
+Same public surface as the reference (``elephas/parameter/factory.py:6-41``: ``ClientServerFactory.get_factory(name)``,
+``create_client`` / ``create_server``, one subclass per transport), built the other way round: a transport is ONE line
+that names its two classes, the base class does the rest, and ``get_factory`` looks the name up in a registry that the
+subclasses fill in as they are defined (so a user-defined transport registers itself by subclassing, too).
+"""
 from .client import DeviceClient, HttpClient, SocketClient
 from .server import DeviceServer, HttpServer, SocketServer
 
 
-class ClientServerFactory(ABC):
+class ClientServerFactory:
+    """``get_factory('socket').create_server(model, port, mode)`` / ``.create_client(port)``."""
+
     _type = 'base'
+    client_class = server_class = None
+    _registry = {}
+
+    def __init_subclass__(cls, **kwargs):
+        super().__init_subclass__(**kwargs)
+        if cls._type != 'base':
+            ClientServerFactory._registry[cls._type] = cls
 
     @classmethod
     def get_factory(cls, _type):
-        for klass in cls.__subclasses__():
-            if klass._type == _type:
-                return klass()
-        raise ValueError("Unknown factory type {}".format(_type))
+        factory = cls._registry.get(_type)
+        if factory is None:
+            raise ValueError("Unknown factory type {}".format(_type))
+        return factory()
 
-    @abstractmethod
+    def _build(self, which, args, kwargs):
+        target = getattr(self, which)
+        if target is None:
+            raise NotImplementedError("%s does not name its %s" % (type(self).__name__, which.replace('_', ' ')))
+        return target(*args, **kwargs)
+
     def create_client(self, *args, **kwargs):
-        pass
+        return self._build('client_class', args, kwargs)
 
-    @abstractmethod
     def create_server(self, *args, **kwargs):
-        pass
+        return self._build('server_class', args, kwargs)
 
 
 class HttpFactory(ClientServerFactory):
-    _type = 'http'
-
-    def create_client(self, *args, **kwargs):
-        return HttpClient(*args, **kwargs)
-
-    def create_server(self, *args, **kwargs):
-        return HttpServer(*args, **kwargs)
+    _type, client_class, server_class = 'http', HttpClient, HttpServer
 
 
 class SocketFactory(ClientServerFactory):
-    _type = 'socket'
-
-    def create_client(self, *args, **kwargs):
-        return SocketClient(*args, **kwargs)
-
-    def create_server(self, *args, **kwargs):
-        return SocketServer(*args, **kwargs)
+    _type, client_class, server_class = 'socket', SocketClient, SocketServer
 
 
 class DeviceFactory(ClientServerFactory):
-    _type = 'nvlink'
-
-    def create_client(self, *args, **kwargs):
-        return DeviceClient(*args, **kwargs)
-
-    def create_server(self, *args, **kwargs):
-        return DeviceServer(*args, **kwargs)
+    _type, client_class, server_class = 'nvlink', DeviceClient, DeviceServer

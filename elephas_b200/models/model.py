@@ -468,9 +468,10 @@ class Model:
         return ends_softmax and self._loss_name == 'categorical_crossentropy'
 
     def set_compute_dtype(self, dtype):
-        """Compute precision of the generic (torch autograd / cuDNN) path on CUDA devices: ``'bfloat16'`` runs the
-        forward/backward under bf16 autocast with fp32 master weights and an fp32 loss (what the native Dense
-        engine always does); ``'float32'`` (default) switches it off. No counterpart in the reference."""
+        """Compute precision of models outside the native Dense engine (convolutional models, functional graphs) on CUDA
+        devices: ``'bfloat16'`` runs forward / backward in bf16 with fp32 master weights and an fp32 loss (what the Dense
+        engine always does) - and puts every Conv2D / BatchNormalization / pooling / Dense layer on the native sm_100a
+        kernels of ``ops/cnn.py``; ``'float32'`` (default) keeps the plain torch ops. No counterpart in the reference."""
         if dtype not in ('float32', 'bfloat16'):
             raise ValueError("compute dtype must be 'float32' or 'bfloat16', got %r" % (dtype,))
         self._compute_dtype = dtype

@@ -480,7 +480,21 @@ class Model:
         on = getattr(self, '_compute_dtype', 'float32') == 'bfloat16' and xb.is_cuda
         return torch.autocast('cuda', dtype=torch.bfloat16, enabled=on)
 
+    def _cpu_step(self):
+        """Hand-written forward / backward of Dense chains on the CPU (``ops/cpu_mlp.py``), or None (autograd tape)."""
+        if self._device.type != 'cpu':
+            return None
+        key = (id(self.optimizer), getattr(self, '_compile_signature', None), len(self.layers))
+        cached = getattr(self, '_cpu_step_cache', None)
+        if cached is None or cached[0] != key:
+            from ..ops import cpu_mlp
+            cached = self._cpu_step_cache = (key, cpu_mlp.maybe_create(self))
+        return cached[1]
+
     def _torch_train_step(self, xb, yb):
+        step = self._cpu_step()
+        if step is not None:
+            return step(xb, yb)
         params = self.trainable_weights
         for p in params:
             p.grad = None

@@ -125,6 +125,7 @@ def exchange_fds(rt, fds, tag):
     server = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
     server.bind(base + str(rank))
     server.listen(world)
+    server.settimeout(120.0)  # a peer that died before it connected must not leave this rank in accept() for ever
     rt.barrier()  # every listener is up
     try:
         for peer in range(world):

@@ -32,6 +32,8 @@ PAGES = [
     ('runtime/sync-torch-path.md', 'elephas_b200.parallel.sync_torch', None),
     ('runtime/torch-step.md', 'elephas_b200.ops.torch_step', None),
     ('runtime/native-cnn-ops.md', 'elephas_b200.ops.cnn', None),
+    ('runtime/cpu-mlp-step.md', 'elephas_b200.ops.cpu_mlp', None),
+    ('utils/cpu_threads.md', 'elephas_b200.utils.cpu_threads', None),
     ('utils/tracing.md', 'elephas_b200.utils.tracing', None),
     ('runtime/engine.md', 'elephas_b200.ops.engine', None),
     ('runtime/native-bindings.md', 'elephas_b200.ops.native', None),

@@ -52,3 +52,27 @@ def test_nvls_master_gather_only_when_the_buckets_tile_the_buffer():
     assert not ctx([(0, 128), (192, 64)], 256)._ranges_cover_master()          # a gap
     assert not ctx([(0, 128), (128, 64)], 256)._ranges_cover_master()          # the tail is nobody's
     assert not ctx([(0, 132), (132, 124)], 256)._ranges_cover_master()         # slices must be groups of 8 elements
+
+
+def test_packed_histories_round_trip_for_arbitrary_shapes():
+    """Property: whatever subset of the keys a rank's history holds and however long its lists are (up to the width), every
+    rank gets back exactly what was sent, None included, keys in canonical order."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+
+    keys = ['loss', 'acc', 'val_loss', 'val_acc', 'batch_loss']
+    values = st.floats(allow_nan=False, allow_infinity=False, width=64)
+    history = st.one_of(st.none(), st.dictionaries(st.sampled_from(keys), st.lists(values, max_size=6), max_size=5))
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.lists(history, min_size=1, max_size=4))
+    def check(per_rank):
+        rt = _TwoRanks()
+        result = None
+        for hist in per_rank:   # rank after rank "sends" its row; the last call sees all of them
+            ordered = None if hist is None else {k: hist[k] for k in keys if k in hist}
+            result = sync_fast._gather_histories(rt, ordered, keys, 6)
+        expected = [None if h is None else {k: h[k] for k in keys if k in h} for h in per_rank]
+        assert result == expected
+
+    check()

@@ -142,6 +142,42 @@ def test_stripe_plan_covers_the_flat_buffer_exactly_once():
             assert (covered == 1).all()
 
 
+def test_stripe_plan_invariants_hold_for_arbitrary_dense_chains():
+    """Property: for any chain of Dense layers (odd widths included) and any world size the plan puts every flat element
+    in exactly one span, keeps stripe-local ranges disjoint and sizes the chunks within the lock-record budget."""
+    import numpy as np
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+    from elephas_b200.models import Dense, Sequential
+    from elephas_b200.parallel.device_ps import MAX_CHUNKS, MIN_CHUNK, MAX_SPANS, StripePlan
+    from elephas_b200.parallel.flat import FlatLayout
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.lists(st.integers(min_value=1, max_value=300), min_size=2, max_size=7), st.integers(min_value=1, max_value=8))
+    def check(widths, world):
+        model = Sequential([Dense(widths[1], input_dim=widths[0])] + [Dense(w) for w in widths[2:]])
+        layout = FlatLayout(model)
+        plan = StripePlan(layout, world)
+        assert 1 <= len(plan.spans) <= MAX_SPANS
+        seen = np.zeros(layout.numel, dtype=np.int32)
+        used = [np.zeros(plan.capacity, dtype=np.int32) for _ in range(world)]
+        for flat_off, n, owner, owner_off in plan.spans:
+            assert n > 0 and n % 64 == 0 and flat_off % 64 == 0 and owner_off % 64 == 0 and 0 <= owner < world
+            seen[flat_off:flat_off + n] += 1
+            used[owner][owner_off:owner_off + n] += 1
+        assert (seen == 1).all()
+        for r in range(world):
+            assert used[r].max() <= 1 and used[r].sum() == plan.stripe_len[r]
+        assert plan.chunk_len % 64 == 0 and plan.chunk_len >= MIN_CHUNK and 1 <= plan.chunks <= MAX_CHUNKS
+        assert plan.chunks * plan.chunk_len >= max(plan.stripe_len)
+        covered = np.zeros(layout.numel, dtype=np.int32)
+        for lo, hi in plan.chunk_ranges_flat():
+            covered[lo:hi] += 1
+        assert (covered == 1).all()
+
+    check()
+
+
 def test_reference_method_names_of_the_servers_work_as_blocking_services():
     """``HttpServer.start_flask_service`` and ``SocketServer.start_server`` / ``stop_server`` (the reference's entry
     points, run there as process / thread targets) serve in the calling thread until stopped."""

@@ -28,3 +28,25 @@ def test_pool_geometry_guard():
     assert not cnn.max_pool_supported(torch.zeros(2, 9, 7, 12), (3, 3), (2, 2))     # channels not a multiple of 8
     assert not cnn.max_pool_supported(x, (3, 3), (2, 1))                            # anisotropic stride
     assert not cnn.max_pool_supported(x, (2, 2), (2, 2), (2, 0, 0, 0))              # padding as large as the window
+
+
+def test_conv_tile_patch_respects_the_tma_limits_for_arbitrary_geometries():
+    """Property: the output-pixel patch of a convolution tile never exceeds the tile (128 rows), never asks a TMA box for
+    more than 256 input elements along an edge, never exceeds the tensor, and wastes at most half of the tile rows unless
+    the whole output is smaller than a tile."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+    from elephas_b200.ops import native
+
+    @settings(max_examples=200, deadline=None)
+    @given(st.integers(1, 300), st.integers(1, 230), st.integers(1, 230), st.sampled_from([1, 2, 3, 4]))
+    def check(n, p, q, stride):
+        pn, ph, pw = native.conv_patch(n, p, q, 128, stride)
+        assert 1 <= pn <= n and 1 <= ph <= p and 1 <= pw <= q
+        assert pn * ph * pw <= 128 and pn <= 256
+        assert (ph - 1) * stride + 1 <= 256 + stride and (pw - 1) * stride + 1 <= 256 + stride
+        tiles = -(-n // pn) * -(-p // ph) * -(-q // pw)
+        if n * p * q >= 128:
+            assert n * p * q / (tiles * 128.0) > 0.4
+
+    check()

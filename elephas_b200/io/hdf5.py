@@ -214,7 +214,8 @@ class _Writer:
         return addr
 
     def write_dataset(self, ds: Dataset) -> int:
-        arr = _normalise_attr(ds.data) if ds.data.dtype.kind in 'SUO' else np.ascontiguousarray(ds.data)
+        # (np.asarray(..., order='C'), not ascontiguousarray: the latter turns a scalar dataset into shape (1,))
+        arr = _normalise_attr(ds.data) if ds.data.dtype.kind in 'SUO' else np.asarray(ds.data, order='C')
         if arr.dtype.byteorder == '>':
             arr = arr.astype(arr.dtype.newbyteorder('<'))
         if arr.dtype.kind == 'f' and arr.dtype.itemsize == 2:

@@ -110,3 +110,40 @@ def test_reads_a_classic_libhdf5_layout_built_from_the_spec():
     b = root['g']['b']
     assert np.array_equal(np.asarray(b), np.array([7, -1, 0, 2 ** 20], dtype=np.int32))
     assert float(b.attrs['scale']) == 0.25
+
+
+def test_random_trees_round_trip(tmp_path):
+    """Property: groups nested at random depths with datasets of random dtypes / shapes (scalars, empty and odd-sized
+    arrays) and attributes come back exactly as written."""
+    from hypothesis import given, settings
+    from hypothesis import strategies as st
+    from hypothesis.extra import numpy as hnp
+
+    names = st.text(alphabet='abcdefgh_:0123456789', min_size=1, max_size=12)
+    dtypes = st.sampled_from([np.float32, np.float64, np.int32, np.int64])
+    arrays = dtypes.flatmap(lambda dt: hnp.arrays(dt, hnp.array_shapes(min_dims=0, max_dims=3, min_side=0, max_side=5),
+                                                   elements=st.integers(-1000, 1000) if np.issubdtype(dt, np.integer)
+                                                   else st.floats(-1e6, 1e6, width=32)))
+    counter = [0]
+
+    @settings(max_examples=25, deadline=None)
+    @given(st.dictionaries(st.lists(names, min_size=1, max_size=3).map('/'.join), arrays, min_size=1, max_size=6),
+           st.dictionaries(names, arrays, max_size=3))
+    def check(datasets, attrs):
+        # a path can be a dataset or a group, not both: drop paths that are a prefix of another one
+        paths = [p for p in datasets if not any(o != p and o.startswith(p + '/') for o in datasets)]
+        root = hdf5.Group(dict(attrs))
+        for p in paths:
+            parent, _, leaf = p.rpartition('/')
+            (root.create_group(parent) if parent else root).create_dataset(leaf, datasets[p])
+        counter[0] += 1
+        path = str(tmp_path / ('r%d.h5' % counter[0]))
+        hdf5.write_file(path, root)
+        back = hdf5.read_file(path)
+        for p in paths:
+            got = back[p].data
+            assert got.dtype == datasets[p].dtype and got.shape == datasets[p].shape and np.array_equal(got, datasets[p])
+        for k, v in attrs.items():
+            assert np.array_equal(np.asarray(back.attrs[k]), v) and np.asarray(back.attrs[k]).dtype == v.dtype
+
+    check()

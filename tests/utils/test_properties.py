@@ -73,3 +73,37 @@ def test_socket_frames_of_any_size(arrays, blob):
     b.close()
     assert got['blob'] == blob and len(got['delta']) == len(arrays)
     assert all(np.array_equal(x, y) and x.dtype == y.dtype for x, y in zip(got['delta'], arrays))
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.integers(1, 40), st.integers(1, 12), st.integers(2, 7), st.integers(0, 2 ** 31 - 1))
+def test_labeled_point_and_data_frame_adapters_round_trip(rows, features, classes, seed):
+    """features / labels -> LabeledPoint RDD / DataFrame -> back (``utils/rdd_utils.py``, ``ml/adapter.py``,
+    ``mllib/adapter.py``), categorical and plain, for any sizes."""
+    from elephas_b200.ml import adapter as ml_adapter
+    from elephas_b200.mllib import adapter as mllib_adapter
+    from elephas_b200.spark import SparkContext
+    from elephas_b200.utils import rdd_utils
+    sc = SparkContext.getOrCreate()
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(rows, features))
+    labels = rng.integers(0, classes, rows)
+    labels[0] = classes - 1  # (lp_to_simple_rdd infers the class count from the largest label)
+    onehot = np.eye(classes)[labels]
+    lp = rdd_utils.to_labeled_point(sc, x, onehot, categorical=True)
+    fx, fy = rdd_utils.from_labeled_point(lp, categorical=True, nb_classes=classes)
+    assert np.allclose(fx, x) and np.array_equal(fy, onehot)
+    pairs = rdd_utils.lp_to_simple_rdd(lp, categorical=True, nb_classes=classes).collect()
+    assert len(pairs) == rows and all(np.allclose(p[0], x[i]) and np.array_equal(p[1], onehot[i]) for i, p in enumerate(pairs))
+    # plain labels come back as integers: the reference reads them with int(lp.label) (elephas/utils/rdd_utils.py:47)
+    fx2, fy2 = rdd_utils.from_labeled_point(rdd_utils.to_labeled_point(sc, x, labels.astype(float), categorical=False))
+    assert np.allclose(fx2, x) and np.array_equal(np.asarray(fy2).reshape(-1), labels)
+    df = ml_adapter.to_data_frame(sc, x, onehot, categorical=True)
+    dx, dy = ml_adapter.from_data_frame(df, categorical=True, nb_classes=classes)
+    assert np.allclose(dx, x) and np.array_equal(dy, onehot)
+    simple = ml_adapter.df_to_simple_rdd(df, categorical=True, nb_classes=classes).collect()
+    assert len(simple) == rows and all(np.allclose(s[0], x[i]) and np.array_equal(s[1], onehot[i]) for i, s in enumerate(simple))
+    m = rng.normal(size=(rows, features))
+    assert np.array_equal(mllib_adapter.from_matrix(mllib_adapter.to_matrix(m)), m)      # D6: values land where they were
+    v = rng.normal(size=features)
+    assert np.array_equal(mllib_adapter.from_vector(mllib_adapter.to_vector(v)), v)

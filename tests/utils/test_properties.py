@@ -107,3 +107,38 @@ def test_labeled_point_and_data_frame_adapters_round_trip(rows, features, classe
     assert np.array_equal(mllib_adapter.from_matrix(mllib_adapter.to_matrix(m)), m)      # D6: values land where they were
     v = rng.normal(size=features)
     assert np.array_equal(mllib_adapter.from_vector(mllib_adapter.to_vector(v)), v)
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.lists(st.tuples(st.integers(1, 33), st.sampled_from([None, 'relu', 'tanh', 'sigmoid', 'softmax', 'elu']),
+                          st.sampled_from([0.0, 0.0, 0.25, 0.5]), st.booleans()), min_size=1, max_size=4),
+       st.integers(1, 17), st.integers(0, 2 ** 31 - 1))
+def test_model_json_and_weights_round_trip(layers, in_dim, seed):
+    """A random Dense / Activation / Dropout / BatchNormalization stack -> to_json + get_weights -> model_from_json +
+    set_weights predicts the same values (the closure the reference ships to its workers, elephas/worker.py:27-34,
+    elephas/utils/serialization.py)."""
+    from elephas_b200.models import Activation, BatchNormalization, Dropout, model_from_json
+    from elephas_b200.utils.serialization import dict_to_model, model_to_dict
+    torch.manual_seed(seed % 1000)
+    stack = []
+    for i, (units, act, drop, norm) in enumerate(layers):
+        kwargs = {'input_dim': in_dim} if i == 0 else {}
+        if act in (None, 'elu'):
+            stack.append(Dense(units, activation=act, **kwargs))
+        else:
+            stack += [Dense(units, **kwargs), Activation(act)]
+        if norm:
+            stack.append(BatchNormalization())
+        if drop:
+            stack.append(Dropout(drop))
+    model = Sequential(stack)
+    x = np.random.default_rng(seed).normal(size=(5, in_dim)).astype(np.float32)
+    want = model.predict(x)
+    twin = model_from_json(model.to_json())
+    assert [type(l).__name__ for l in twin.layers] == [type(l).__name__ for l in model.layers]
+    assert [w.shape for w in twin.get_weights()] == [w.shape for w in model.get_weights()]
+    twin.set_weights(model.get_weights())
+    assert np.allclose(twin.predict(x), want, atol=1e-6)
+    third = dict_to_model(model_to_dict(model))
+    assert np.allclose(third.predict(x), want, atol=1e-6)
+    assert twin.to_json() == model_from_json(twin.to_json()).to_json()   # the JSON is a fixed point

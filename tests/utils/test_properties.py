@@ -142,3 +142,32 @@ def test_model_json_and_weights_round_trip(layers, in_dim, seed):
     third = dict_to_model(model_to_dict(model))
     assert np.allclose(third.predict(x), want, atol=1e-6)
     assert twin.to_json() == model_from_json(twin.to_json()).to_json()   # the JSON is a fixed point
+
+
+@settings(max_examples=15, deadline=None)
+@given(st.integers(2, 60), st.integers(1, 9), st.integers(2, 5), st.integers(0, 2 ** 31 - 1))
+def test_block_columns_equal_the_row_path(rows, features, classes, seed):
+    """DataFrame stages that compute on whole columns (StringIndexer, StandardScaler) give the rows the row-wise
+    definitions give: the lazily appended block columns materialise to the same values, in the same order."""
+    from elephas_b200.spark import SparkSession, StandardScaler, StringIndexer, Vectors
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(rows, features))
+    cats = ['class_%d' % c for c in rng.integers(0, classes, rows)]
+    spark = SparkSession.builder.getOrCreate()
+    df = spark.createDataFrame([(Vectors.dense(f), c) for f, c in zip(x, cats)], ['features', 'category'])
+    indexed = StringIndexer(inputCol='category', outputCol='idx').fit(df).transform(df)
+    scaler = StandardScaler(inputCol='features', outputCol='scaled', withMean=True, withStd=True).fit(indexed)
+    scaled = scaler.transform(indexed)
+    out = scaled.collect()
+    assert len(out) == rows and scaled.columns == ['features', 'category', 'idx', 'scaled']
+    # label indices: descending frequency, ties alphabetical (Spark's default)
+    counts = {}
+    for c in cats:
+        counts[c] = counts.get(c, 0) + 1
+    order = [k for k, _ in sorted(counts.items(), key=lambda kv: (-kv[1], kv[0]))]
+    assert [r['idx'] for r in out] == [float(order.index(c)) for c in cats]
+    mean, std = x.mean(axis=0), x.std(axis=0, ddof=1) if rows > 1 else np.ones(features)
+    want = (x - mean) / np.where(std > 0, std, 1.0) * (std > 0)
+    got = np.stack([np.asarray(r['scaled'].toArray()) for r in out])
+    assert np.allclose(got, want, atol=1e-9)
+    assert [r['category'] for r in out] == cats and np.allclose(np.stack([r['features'].toArray() for r in out]), x)

@@ -171,3 +171,34 @@ def test_block_columns_equal_the_row_path(rows, features, classes, seed):
     got = np.stack([np.asarray(r['scaled'].toArray()) for r in out])
     assert np.allclose(got, want, atol=1e-9)
     assert [r['category'] for r in out] == cats and np.allclose(np.stack([r['features'].toArray() for r in out]), x)
+
+
+@settings(max_examples=12, deadline=None)
+@given(widths, st.sampled_from(['sgd', 'momentum', 'adam', 'rmsprop', 'adagrad']), st.integers(0, 2 ** 31 - 1))
+def test_checkpoints_resume_exactly(ws, opt_name, seed):
+    """save -> load_model -> one more step == one more step without the detour: weights, optimizer slots (stored in Keras
+    layout) and the iteration counter all survive the file (elephas/spark_model.py:92-134 relies on Keras for this)."""
+    import os
+    import tempfile
+    from elephas_b200.models import SGD, Adagrad, Adam, RMSprop, load_model
+    make = {'sgd': lambda: SGD(learning_rate=0.05), 'momentum': lambda: SGD(learning_rate=0.05, momentum=0.9, nesterov=True),
+            'adam': lambda: Adam(learning_rate=0.01), 'rmsprop': lambda: RMSprop(learning_rate=0.01),
+            'adagrad': lambda: Adagrad(learning_rate=0.05)}[opt_name]
+    torch.manual_seed(seed % 997)
+    model = _chain(ws)
+    model.compile(make(), 'mse', ['mae'])
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(24, ws[0])).astype(np.float32)
+    y = rng.normal(size=(24, ws[-1])).astype(np.float32)
+    for i in (0, 8):
+        model.train_on_batch(x[i:i + 8], y[i:i + 8])
+    with tempfile.TemporaryDirectory() as tmp:
+        path = os.path.join(tmp, 'm.h5')
+        model.save(path)
+        resumed = load_model(path)
+    assert resumed.optimizer.iterations == model.optimizer.iterations == 2
+    a = model.train_on_batch(x[16:], y[16:])
+    b = resumed.train_on_batch(x[16:], y[16:])
+    assert np.allclose(a, b, atol=1e-6, rtol=1e-5)
+    for u, v in zip(model.get_weights(), resumed.get_weights()):
+        assert np.allclose(u, v, atol=1e-6, rtol=1e-5), np.abs(u - v).max()

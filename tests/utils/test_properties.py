@@ -202,3 +202,27 @@ def test_checkpoints_resume_exactly(ws, opt_name, seed):
     assert np.allclose(a, b, atol=1e-6, rtol=1e-5)
     for u, v in zip(model.get_weights(), resumed.get_weights()):
         assert np.allclose(u, v, atol=1e-6, rtol=1e-5), np.abs(u - v).max()
+
+
+@settings(max_examples=10, deadline=None)
+@given(st.integers(1, 97), st.integers(1, 6), st.integers(0, 2 ** 31 - 1))
+def test_distributed_predict_and_evaluate_equal_the_local_ones(rows, workers, seed):
+    """SparkModel.predict keeps the row order and SparkModel.evaluate the sample-weighted mean for ANY number of rows and
+    partitions - empty and one-row partitions included (elephas/spark_model.py:235-308 does this with zipWithIndex /
+    sortBy and a weighted reduce)."""
+    from elephas.spark_model import SparkModel
+    from elephas_b200.models import SGD, Activation
+    from elephas_b200.spark import SparkContext
+    torch.manual_seed(seed % 991)
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(rows, 7)).astype(np.float32)
+    y = np.eye(3, dtype=np.float32)[rng.integers(0, 3, rows)]
+    model = Sequential([Dense(9, input_dim=7, activation='relu'), Dense(3), Activation('softmax')])
+    model.compile(SGD(learning_rate=0.1), 'categorical_crossentropy', ['acc'])
+    sm = SparkModel(model, mode='synchronous', num_workers=workers)
+    sc = SparkContext.getOrCreate()
+    local_pred = model.predict(x)
+    assert np.allclose(sm.predict(x), local_pred, atol=1e-6)
+    assert np.allclose(np.asarray(sm.predict(sc.parallelize(list(x), workers))), local_pred, atol=1e-6)
+    local_eval = model.evaluate(x, y)
+    assert np.allclose(sm.evaluate(x, y), local_eval, atol=1e-5)

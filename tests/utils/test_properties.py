@@ -226,3 +226,43 @@ def test_distributed_predict_and_evaluate_equal_the_local_ones(rows, workers, se
     assert np.allclose(np.asarray(sm.predict(sc.parallelize(list(x), workers))), local_pred, atol=1e-6)
     local_eval = model.evaluate(x, y)
     assert np.allclose(sm.evaluate(x, y), local_eval, atol=1e-5)
+
+
+@settings(max_examples=8, deadline=None)
+@given(st.integers(20, 90), st.integers(2, 4), st.sampled_from([4, 8, 16]), st.integers(0, 2 ** 31 - 1))
+def test_synchronous_mode_is_the_mean_of_the_replicas(rows, workers, batch, seed):
+    """The defining identity of the reference's synchronous mode (elephas/spark_model.py:217-231): after one round the
+    master equals the mean of the replicas trained alone on their partitions from the same start - for any row count,
+    worker count and batch size (partitions not larger than a batch contribute a zero delta, worker.py:41)."""
+    import copy
+    from elephas.spark_model import SparkModel
+    from elephas_b200.models import SGD
+    from elephas_b200.spark import SparkContext
+    from elephas.utils.rdd_utils import to_simple_rdd
+    torch.manual_seed(seed % 983)
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(rows, 5)).astype(np.float32)
+    y = rng.normal(size=(rows, 2)).astype(np.float32)
+    model = Sequential([Dense(6, input_dim=5, activation='tanh'), Dense(2)])
+    model.compile(SGD(learning_rate=0.05), 'mse')
+    start = [w.copy() for w in model.get_weights()]
+    sm = SparkModel(model, mode='synchronous', num_workers=workers, sync_rounds='fit')
+    rdd = to_simple_rdd(SparkContext.getOrCreate(), x, y)
+    parts = [p for p in rdd.repartition(workers).partitions()]
+    sm.fit(rdd, epochs=2, batch_size=batch, verbose=0, shuffle=False)
+    got = sm.master_network.get_weights()
+    # replicas trained alone
+    ends = []
+    for part in parts:
+        rows_p = list(part)
+        replica = Sequential([Dense(6, input_dim=5, activation='tanh'), Dense(2)])
+        replica.compile(SGD(learning_rate=0.05), 'mse')
+        replica.set_weights(copy.deepcopy(start))
+        if len(rows_p) > batch:
+            px = np.stack([np.asarray(r[0]) for r in rows_p]).astype(np.float32)
+            py = np.stack([np.asarray(r[1]) for r in rows_p]).astype(np.float32)
+            replica.fit(px, py, batch_size=batch, epochs=2, shuffle=False, verbose=0)
+        ends.append(replica.get_weights())
+    for i, g in enumerate(got):
+        want = np.mean([e[i] for e in ends], axis=0)
+        assert np.allclose(g, want, atol=2e-6), np.abs(g - want).max()

@@ -266,3 +266,31 @@ def test_synchronous_mode_is_the_mean_of_the_replicas(rows, workers, batch, seed
     for i, g in enumerate(got):
         want = np.mean([e[i] for e in ends], axis=0)
         assert np.allclose(g, want, atol=2e-6), np.abs(g - want).max()
+
+
+@settings(max_examples=40, deadline=None)
+@given(st.lists(st.integers(-50, 50), max_size=60), st.integers(1, 7), st.integers(1, 7))
+def test_rdd_stand_in_behaves_like_the_list_it_holds(items, slices, repart):
+    """The local RDD (elephas_b200/spark/context.py) against plain Python on the same data: order-preserving
+    transformations, partition bookkeeping, actions - for any contents and partition counts, empty partitions included."""
+    from elephas_b200.spark import SparkContext
+    rdd = SparkContext.getOrCreate().parallelize(items, slices)
+    assert rdd.getNumPartitions() == slices and rdd.collect() == items and rdd.count() == len(items)
+    assert sum(len(list(p)) for p in rdd.partitions()) == len(items)
+    assert rdd.map(lambda v: v * 2).collect() == [v * 2 for v in items]
+    assert rdd.filter(lambda v: v % 3 == 0).collect() == [v for v in items if v % 3 == 0]
+    assert rdd.flatMap(lambda v: [v, -v]).collect() == [w for v in items for w in (v, -v)]
+    assert rdd.zipWithIndex().collect() == [(v, i) for i, v in enumerate(items)]
+    assert rdd.mapPartitions(lambda it: [sum(it)]).collect() == [sum(p) for p in rdd.glom().collect()]
+    again = rdd.repartition(repart)
+    assert again.getNumPartitions() == repart and again.collect() == items   # (the stand-in keeps the order)
+    assert rdd.sortBy(lambda v: v).collect() == sorted(items)
+    assert rdd.sortBy(lambda v: v, ascending=False).collect() == sorted(items, reverse=True)
+    assert sorted(rdd.distinct().collect()) == sorted(set(items))
+    assert rdd.zip(rdd.map(lambda v: v + 1)).collect() == [(v, v + 1) for v in items]
+    assert rdd.union(rdd).collect() == items + items
+    assert rdd.isEmpty() == (not items) and rdd.take(3) == items[:3]
+    if items:
+        assert rdd.reduce(lambda a, b: a + b) == sum(items) and rdd.sum() == sum(items)
+        assert rdd.max() == max(items) and rdd.min() == min(items) and rdd.first() == items[0]
+        assert np.isclose(rdd.mean(), np.mean(items))

@@ -294,3 +294,35 @@ def test_rdd_stand_in_behaves_like_the_list_it_holds(items, slices, repart):
         assert rdd.reduce(lambda a, b: a + b) == sum(items) and rdd.sum() == sum(items)
         assert rdd.max() == max(items) and rdd.min() == min(items) and rdd.first() == items[0]
         assert np.isclose(rdd.mean(), np.mean(items))
+
+
+@settings(max_examples=25, deadline=None)
+@given(st.integers(1, 30), st.integers(0, 35), st.integers(0, 2 ** 31 - 1))
+def test_data_frame_operations_on_frames_with_block_columns(rows, limit, seed):
+    """select / drop / limit / rename / withColumn / SQL on a frame whose newest columns exist only as blocks (appended by
+    StringIndexer / StandardScaler): the lazily built rows equal what the eager definitions give."""
+    from elephas_b200.spark import DoubleType, SparkSession, StandardScaler, StringIndexer, Vectors, functions
+    rng = np.random.default_rng(seed)
+    x = rng.normal(size=(rows, 3))
+    cats = ['c%d' % c for c in rng.integers(0, 3, rows)]
+    spark = SparkSession.builder.getOrCreate()
+    df = spark.createDataFrame([(Vectors.dense(f), c, int(i)) for i, (f, c) in enumerate(zip(x, cats))],
+                               ['features', 'category', 'row'])
+    df = StringIndexer(inputCol='category', outputCol='idx').fit(df).transform(df)
+    df = StandardScaler(inputCol='features', outputCol='scaled', withMean=True, withStd=False).fit(df).transform(df)
+    idx = [r['idx'] for r in df.collect()]
+    centred = x - x.mean(axis=0)
+    sel = df.select('row', 'idx').collect()
+    assert [(r['row'], r['idx']) for r in sel] == list(zip(range(rows), idx))
+    assert df.drop('features', 'category').columns == ['row', 'idx', 'scaled']
+    lim = df.limit(limit)
+    assert lim.count() == min(limit, rows) and [r['row'] for r in lim.collect()] == list(range(min(limit, rows)))
+    assert np.allclose(np.stack([r['scaled'].toArray() for r in lim.collect()]) if lim.count() else np.zeros((0, 3)),
+                       centred[:limit])
+    ren = df.withColumnRenamed('idx', 'label')
+    assert ren.columns == ['features', 'category', 'row', 'label', 'scaled'] and [r['label'] for r in ren.collect()] == idx
+    plus = df.withColumn('twice', functions.col('idx').astype(DoubleType()))
+    assert [r['twice'] for r in plus.collect()] == idx
+    df.createOrReplaceTempView('frame_under_test')
+    out = spark.sql('SELECT scaled AS features, idx as label from frame_under_test').collect()
+    assert [r['label'] for r in out] == idx and np.allclose(np.stack([r['features'].toArray() for r in out]), centred)

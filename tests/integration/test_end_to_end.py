@@ -146,6 +146,8 @@ def test_cpu_workers_move_flat_tensors_against_the_in_process_store(spark_contex
     from elephas_b200.parallel import get_runtime
     if get_runtime().device.type != 'cpu':
         pytest.skip('CPU form of the device path')
+    import torch
+    torch.manual_seed(17)  # reproducible initial weights
     rng = np.random.default_rng(3)
     x = rng.normal(size=(512, 20)).astype('float32')
     labels = (x[:, :4].sum(1) > 0).astype(int)

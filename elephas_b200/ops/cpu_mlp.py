@@ -9,7 +9,8 @@ The optimizer is the model's own (``Optimizer.apply_gradients``), the loss value
 functions as on the tape path, so both paths report and apply the same numbers (``tests/models/test_cpu_mlp.py``).
 
 Covered: hidden activations relu / linear / sigmoid / tanh, Dropout after a hidden layer, outputs softmax +
-categorical cross-entropy or linear / sigmoid / tanh / relu + mean squared error. Anything else stays on the tape.
+categorical cross-entropy, sigmoid + binary cross-entropy, or linear / sigmoid / tanh / relu + mean squared / absolute
+error. Anything else stays on the tape.
 ``ELEPHAS_B200_CPU_ENGINE=0`` switches the module off.
 
 Reference call sites: ``model.fit`` / ``train_on_batch`` inside the workers (``elephas/worker.py:42,108,123``).
@@ -20,6 +21,7 @@ import numpy as np
 import torch
 
 _HIDDEN = ('relu', 'linear', 'sigmoid', 'tanh')
+_EPS = 1e-7  # Keras' clipping constant of the cross-entropies (models/losses.py)
 
 
 def enabled():
@@ -94,8 +96,13 @@ class CpuMlpStep:
         # dL/dz of the output layer for the mean-over-batch loss
         if self.loss_name == 'categorical_crossentropy':
             dz = (out - yb).div_(rows)
-        else:  # mean_squared_error: mean over the outputs, then over the batch
-            dz = (out - yb).mul_(2.0 / (rows * out.shape[-1]))
+        elif self.loss_name == 'binary_crossentropy':  # sigmoid outputs; Keras clips p to [eps, 1 - eps]: no gradient there
+            dz = (out - yb).div_(rows * out.shape[-1]).mul_((out > _EPS) & (out < 1.0 - _EPS))
+        else:  # mean squared / absolute error: mean over the outputs, then over the batch
+            if self.loss_name == 'mean_squared_error':
+                dz = (out - yb).mul_(2.0 / (rows * out.shape[-1]))
+            else:
+                dz = torch.sign(out - yb).div_(rows * out.shape[-1])
             _times_derivative_(dz, out, self.out_act)
         grads = [None] * (2 * len(ops))
         for i in range(len(ops) - 1, -1, -1):
@@ -137,7 +144,10 @@ def maybe_create(model):
     if loss_name == 'categorical_crossentropy':
         if out_act != 'softmax':
             return None
-    elif loss_name == 'mean_squared_error':
+    elif loss_name == 'binary_crossentropy':
+        if out_act != 'sigmoid':
+            return None
+    elif loss_name in ('mean_squared_error', 'mean_absolute_error'):
         if out_act not in _HIDDEN:
             return None
     else:

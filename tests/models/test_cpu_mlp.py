@@ -13,10 +13,13 @@ def _model(kind, optimizer):
         m = Sequential([Dense(24, input_dim=13), Activation('relu'), Dense(17, activation='tanh'), Dense(5),
                         Activation('softmax')])
         m.compile(optimizer, 'categorical_crossentropy', ['acc'])
+    elif kind == 'multilabel':
+        m = Sequential([Dense(16, input_dim=13, activation='relu'), Dense(2, activation='sigmoid')])
+        m.compile(optimizer, 'binary_crossentropy', ['binary_accuracy'])
     else:
         m = Sequential([Dense(16, input_dim=13, activation='sigmoid'), Dense(8, activation='relu'),
-                        Dense(2, activation='linear' if kind == 'regressor' else 'sigmoid')])
-        m.compile(optimizer, 'mse', ['mae'])
+                        Dense(2, activation='linear' if kind != 'bounded_regressor' else 'sigmoid')])
+        m.compile(optimizer, 'mae' if kind == 'robust_regressor' else 'mse', ['mae'])
     return m
 
 
@@ -25,12 +28,14 @@ def _data(kind):
     x = rng.normal(size=(96, 13)).astype('float32')
     if kind == 'classifier':
         y = np.eye(5, dtype='float32')[rng.integers(0, 5, 96)]
+    elif kind == 'multilabel':
+        y = rng.integers(0, 2, (96, 2)).astype('float32')
     else:
         y = rng.random((96, 2)).astype('float32')
     return x, y
 
 
-@pytest.mark.parametrize('kind', ['classifier', 'regressor', 'bounded_regressor'])
+@pytest.mark.parametrize('kind', ['classifier', 'regressor', 'bounded_regressor', 'robust_regressor', 'multilabel'])
 @pytest.mark.parametrize('make_opt', [lambda: SGD(learning_rate=0.1, momentum=0.9), lambda: Adam(learning_rate=0.01),
                                       lambda: RMSprop(learning_rate=0.01)])
 def test_hand_written_step_equals_the_autograd_step(monkeypatch, kind, make_opt):
@@ -63,9 +68,9 @@ def test_dropout_chain_trains_and_other_models_stay_on_the_tape():
     other = Sequential([Dense(4, input_dim=20, activation='elu'), Dense(1)])
     other.compile(SGD(learning_rate=0.1), 'mse')
     assert other._cpu_step() is None
-    mae = Sequential([Dense(4, input_dim=20, activation='relu'), Dense(1)])
-    mae.compile(SGD(learning_rate=0.1), 'mae')
-    assert mae._cpu_step() is None
+    mape = Sequential([Dense(4, input_dim=20, activation='relu'), Dense(1)])
+    mape.compile(SGD(learning_rate=0.1), 'mean_absolute_percentage_error')
+    assert mape._cpu_step() is None
     clipped = Sequential([Dense(4, input_dim=20, activation='relu'), Dense(1)])
     clipped.compile(SGD(learning_rate=0.1, clipnorm=1.0), 'mse')
     assert clipped._cpu_step() is None

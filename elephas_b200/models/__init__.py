@@ -7,6 +7,9 @@ from . import activations, losses, metrics, optimizers  # noqa: F401
 from .layers import (Activation, Add, AveragePooling2D, BatchNormalization, Concatenate, Conv2D, Dense,  # noqa: F401
                      Dropout, Flatten, GlobalAveragePooling2D, Input, InputLayer, Layer, MaxPooling2D, ReLU,
                      Reshape, Softmax, ZeroPadding2D)
+from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Conv1D, Embedding, GlobalAveragePooling1D,  # noqa: F401
+                           GlobalMaxPooling1D, GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Maximum, MaxPooling1D,
+                           Minimum, Multiply, SimpleRNN, Subtract)
 from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
                     to_categorical)
 from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, Nadam, RMSprop  # noqa: F401

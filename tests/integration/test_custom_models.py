@@ -63,3 +63,27 @@ def test_custom_activation_trains_and_predicts_on_every_worker(mode, workers, sp
     assert abs(loss - by_hand_loss) < 1e-4 and 0.0 <= acc <= 1.0
     if mode == 'synchronous':  # (a parameter server ADDS the workers' deltas: no monotonicity promise after one fit)
         assert loss < loss_before
+
+
+@pytest.mark.parametrize('mode,ps', [('synchronous', None), ('asynchronous', 'socket'), ('hogwild', 'nvlink')])
+def test_recurrent_model_trains_through_every_mode(spark_context, mode, ps):
+    """A sequence model (Embedding -> LSTM -> Dense) travels to the workers as JSON like any Keras model the reference
+    accepts (elephas/worker.py:27-34), trains in all three modes and predicts the same through SparkModel and locally."""
+    import numpy as np
+    import torch
+    from elephas.spark_model import SparkModel
+    from elephas.utils.rdd_utils import to_simple_rdd
+    from elephas_b200.models import LSTM, Activation, Adam, Dense, Embedding, Sequential
+    torch.manual_seed(11)
+    rng = np.random.default_rng(11)
+    tokens = rng.integers(1, 12, (192, 8))
+    y = np.eye(2, dtype='float32')[(tokens[:, 0] > 6).astype(int)]      # the first token decides the class
+    model = Sequential([Embedding(12, 6, input_length=8), LSTM(8, go_backwards=True), Dense(2), Activation('softmax')])
+    model.compile(Adam(learning_rate=0.02), 'categorical_crossentropy', ['acc'])
+    kwargs = {'parameter_server_mode': ps, 'port': 4000 + int(rng.integers(100, 900))} if ps else {}
+    sm = SparkModel(model, mode=mode, frequency='epoch', num_workers=2, **kwargs)
+    before = sm.evaluate(tokens, y)
+    sm.fit(to_simple_rdd(spark_context, tokens, y), epochs=10, batch_size=16, verbose=0)
+    after = sm.evaluate(tokens, y)
+    assert after[0] < before[0] and after[1] > 0.8
+    assert np.allclose(sm.predict(tokens[:10]), sm.master_network.predict(tokens[:10]), atol=1e-6)

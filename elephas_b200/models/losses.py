@@ -77,7 +77,54 @@ def cosine_proximity(y_true, y_pred):
     return -(a * b).sum(dim=-1)
 
 
+def _mean_last(v):
+    return v.flatten(1).mean(dim=1) if v.dim() > 1 else v
+
+
+def hinge(y_true, y_pred):
+    """Labels in {-1, 1} (0 / 1 labels are converted, as Keras does): mean(max(1 - y * p, 0))."""
+    y_true = _match(y_true, y_pred)
+    if bool(((y_true == 0) | (y_true == 1)).all()):
+        y_true = 2.0 * y_true - 1.0
+    return _mean_last(torch.clamp(1.0 - y_true * y_pred, min=0.0))
+
+
+def squared_hinge(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    if bool(((y_true == 0) | (y_true == 1)).all()):
+        y_true = 2.0 * y_true - 1.0
+    return _mean_last(torch.clamp(1.0 - y_true * y_pred, min=0.0) ** 2)
+
+
+def categorical_hinge(y_true, y_pred):
+    y_true = y_true.to(y_pred.dtype)
+    pos = (y_true * y_pred).sum(dim=-1)
+    neg = ((1.0 - y_true) * y_pred).max(dim=-1).values
+    return torch.clamp(neg - pos + 1.0, min=0.0)
+
+
+def kl_divergence(y_true, y_pred):
+    y_true = torch.clamp(y_true.to(y_pred.dtype), EPS, 1.0)
+    y_pred = torch.clamp(y_pred, EPS, 1.0)
+    return (y_true * torch.log(y_true / y_pred)).sum(dim=-1)
+
+
+def poisson(y_true, y_pred):
+    y_true = _match(y_true, y_pred)
+    return _mean_last(y_pred - y_true * torch.log(y_pred + EPS))
+
+
+def huber(y_true, y_pred, delta=1.0):
+    y_true = _match(y_true, y_pred)
+    err = (y_pred - y_true).abs()
+    quad = torch.clamp(err, max=delta)
+    return _mean_last(0.5 * quad ** 2 + delta * (err - quad))
+
+
 _BUILTIN = {
+    'hinge': hinge, 'squared_hinge': squared_hinge, 'categorical_hinge': categorical_hinge,
+    'kl_divergence': kl_divergence, 'kld': kl_divergence, 'kullback_leibler_divergence': kl_divergence,
+    'poisson': poisson, 'huber': huber, 'huber_loss': huber,
     'mean_squared_error': mean_squared_error, 'mse': mean_squared_error, 'MSE': mean_squared_error,
     'mean_absolute_error': mean_absolute_error, 'mae': mean_absolute_error, 'MAE': mean_absolute_error,
     'mean_absolute_percentage_error': mean_absolute_percentage_error, 'mape': mean_absolute_percentage_error,
@@ -93,6 +140,7 @@ CANONICAL = {
     'mse': 'mean_squared_error', 'MSE': 'mean_squared_error', 'mae': 'mean_absolute_error',
     'MAE': 'mean_absolute_error', 'mape': 'mean_absolute_percentage_error',
     'msle': 'mean_squared_logarithmic_error', 'log_cosh': 'logcosh', 'cosine_similarity': 'cosine_proximity',
+    'kld': 'kl_divergence', 'kullback_leibler_divergence': 'kl_divergence', 'huber_loss': 'huber',
 }
 
 

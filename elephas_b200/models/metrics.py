@@ -24,9 +24,23 @@ def sparse_categorical_accuracy(y_true, y_pred):
     return (idx == y_pred.argmax(dim=-1)).to(y_pred.dtype)
 
 
+def top_k_categorical_accuracy(y_true, y_pred, k=5):
+    k = min(int(k), y_pred.shape[-1])
+    top = y_pred.topk(k, dim=-1).indices
+    return (top == y_true.argmax(dim=-1, keepdim=True)).any(dim=-1).to(y_pred.dtype)
+
+
+def sparse_top_k_categorical_accuracy(y_true, y_pred, k=5):
+    k = min(int(k), y_pred.shape[-1])
+    idx = y_true.reshape(y_pred.shape[0], -1)[:, :1].long()
+    return (y_pred.topk(k, dim=-1).indices == idx).any(dim=-1).to(y_pred.dtype)
+
+
 _BUILTIN = {
     'binary_accuracy': binary_accuracy, 'categorical_accuracy': categorical_accuracy,
     'sparse_categorical_accuracy': sparse_categorical_accuracy,
+    'top_k_categorical_accuracy': top_k_categorical_accuracy,
+    'sparse_top_k_categorical_accuracy': sparse_top_k_categorical_accuracy,
 }
 
 

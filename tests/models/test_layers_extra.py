@@ -160,3 +160,40 @@ def test_sequence_models_train_and_survive_json_and_hdf5(tmp_path):
     first = seq.evaluate(xs, ys)
     seq.fit(xs, ys, batch_size=16, epochs=15, verbose=0)
     assert seq.evaluate(xs, ys) < first
+
+
+def test_more_keras_losses_and_metrics_match_their_definitions():
+    from elephas_b200.models import losses, metrics
+    rng = np.random.default_rng(4)
+    p = rng.random((6, 4)).astype(np.float32)
+    p /= p.sum(1, keepdims=True)
+    y = np.eye(4, dtype=np.float32)[rng.integers(0, 4, 6)]
+    t = lambda a: torch.from_numpy(np.asarray(a, dtype=np.float32))  # noqa: E731
+    signed = 2 * y - 1
+    assert np.allclose(losses.hinge(t(y), t(p)).numpy(), np.maximum(1 - signed * p, 0).mean(1), atol=1e-6)
+    assert np.allclose(losses.hinge(t(signed), t(p)).numpy(), np.maximum(1 - signed * p, 0).mean(1), atol=1e-6)
+    assert np.allclose(losses.squared_hinge(t(y), t(p)).numpy(), (np.maximum(1 - signed * p, 0) ** 2).mean(1), atol=1e-6)
+    pos, neg = (y * p).sum(1), ((1 - y) * p).max(1)
+    assert np.allclose(losses.categorical_hinge(t(y), t(p)).numpy(), np.maximum(neg - pos + 1, 0), atol=1e-6)
+    q = rng.random((6, 4)).astype(np.float32)
+    q /= q.sum(1, keepdims=True)
+    assert np.allclose(losses.kl_divergence(t(q), t(p)).numpy(), (q * np.log(q / p)).sum(1), atol=1e-5)
+    counts = rng.poisson(3.0, (6, 4)).astype(np.float32)
+    rate = rng.random((6, 4)).astype(np.float32) * 4 + 0.1
+    assert np.allclose(losses.poisson(t(counts), t(rate)).numpy(), (rate - counts * np.log(rate + 1e-7)).mean(1), atol=1e-5)
+    err = rng.normal(size=(6, 4)).astype(np.float32) * 2
+    want = np.where(np.abs(err) <= 1, 0.5 * err ** 2, np.abs(err) - 0.5).mean(1)
+    assert np.allclose(losses.huber(t(np.zeros_like(err)), t(err)).numpy(), want, atol=1e-6)
+    assert losses.get('kld') is losses.kl_divergence and losses.canonical_name('huber_loss') == 'huber'
+    top2 = metrics.top_k_categorical_accuracy(t(y), t(p), k=2).numpy()
+    assert np.array_equal(top2, [float(y[i].argmax() in np.argsort(-p[i])[:2]) for i in range(6)])
+    sparse = metrics.sparse_top_k_categorical_accuracy(t(y.argmax(1)), t(p), k=2).numpy()
+    assert np.array_equal(sparse, top2)
+    # they compile and train like any built-in loss
+    model = Sequential([Dense(8, input_dim=5, activation='relu'), Dense(1)])
+    model.compile(Adam(learning_rate=0.02), 'huber', ['mae'])
+    xs = rng.normal(size=(64, 5)).astype(np.float32)
+    ys = xs[:, :1] * 2
+    first = model.evaluate(xs, ys)[0]
+    model.fit(xs, ys, batch_size=16, epochs=20, verbose=0)
+    assert model.evaluate(xs, ys)[0] < first

@@ -7,9 +7,11 @@ from . import activations, losses, metrics, optimizers  # noqa: F401
 from .layers import (Activation, Add, AveragePooling2D, BatchNormalization, Concatenate, Conv2D, Dense,  # noqa: F401
                      Dropout, Flatten, GlobalAveragePooling2D, Input, InputLayer, Layer, MaxPooling2D, ReLU,
                      Reshape, Softmax, ZeroPadding2D)
-from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Conv1D, Embedding, GlobalAveragePooling1D,  # noqa: F401
-                           GlobalMaxPooling1D, GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Maximum, MaxPooling1D,
-                           Minimum, Multiply, SimpleRNN, Subtract)
+from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Bidirectional, Conv1D, Conv2DTranspose,  # noqa: F401
+                           DepthwiseConv2D, Dot, Embedding, GaussianNoise, GlobalAveragePooling1D, GlobalMaxPooling1D,
+                           GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Maximum, MaxPooling1D, Minimum, Multiply,
+                           Permute, RepeatVector, SeparableConv2D, SimpleRNN, SpatialDropout1D, SpatialDropout2D,
+                           Subtract, TimeDistributed, UpSampling2D)
 from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
                     to_categorical)
 from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, Nadam, RMSprop  # noqa: F401

@@ -1,5 +1,6 @@
 """More of the Keras layer vocabulary: advanced activations, merge layers, 1-D convolution / pooling, normalisation over
-features, embeddings and recurrent layers.
+features, embeddings, recurrent layers and their wrappers (Bidirectional, TimeDistributed), depthwise / separable /
+transposed convolutions, up-sampling, shape and noise layers.
 
 The reference hands an arbitrary compiled Keras model to its workers (``elephas/worker.py:27-42``: ``model_from_json`` +
 ``model.fit``), so the layer set decides which user models can be trained at all. These layers follow the Keras 2.10
@@ -284,6 +285,16 @@ class Conv1D(Layer):
 
 
 # --------------------------------------------------------------------------------------------------------- recurrent
+def _from_config_with_custom_objects(cls, config, custom_objects=None):
+    cfg = dict(config)
+    if cfg.get('batch_input_shape') is not None:
+        cfg['batch_input_shape'] = tuple(cfg['batch_input_shape'])
+    return cls(custom_objects=custom_objects, **cfg)
+
+
+Conv1D.from_config = classmethod(_from_config_with_custom_objects)
+
+
 class _Recurrent(Layer):
     """Shared part of SimpleRNN / LSTM / GRU: weights in the Keras layouts (``kernel [in, g*units]``,
     ``recurrent_kernel [units, g*units]``, ``bias``), named below the cell like Keras 2.10 does
@@ -353,6 +364,8 @@ class _Recurrent(Layer):
             if self.return_sequences:
                 outputs.append(h)
         return torch.stack(outputs, dim=1) if self.return_sequences else h
+
+    from_config = classmethod(_from_config_with_custom_objects)
 
     def _extra_config(self):
         return {'units': self.units, 'activation': self.activation_name, 'use_bias': self.use_bias,
@@ -460,7 +473,445 @@ class GRU(_Recurrent):
         return cfg
 
 
+# ------------------------------------------------------------------------------- more convolutions and resampling
+def _tf_same_pads(size, k, stride, dilation=1):
+    eff = (k - 1) * dilation + 1
+    total = max((-(-size // stride) - 1) * stride + eff - size, 0)
+    return total // 2, total - total // 2
+
+
+class DepthwiseConv2D(Layer):
+    """One filter stack per input channel. Weight ``depthwise_kernel`` in Keras is ``(kh, kw, channels, multiplier)``; it is
+    kept as the grouped-convolution weight ``[channels * multiplier, 1, kh, kw]`` (same output channel order)."""
+
+    def __init__(self, kernel_size, strides=(1, 1), padding='valid', depth_multiplier=1, data_format=None,
+                 dilation_rate=(1, 1), activation=None, use_bias=True, depthwise_initializer='glorot_uniform',
+                 bias_initializer='zeros', custom_objects=None, **kwargs):
+        for key in ('depthwise_regularizer', 'bias_regularizer', 'activity_regularizer', 'depthwise_constraint',
+                    'bias_constraint', 'groups'):
+            kwargs.pop(key, None)
+        super().__init__(**kwargs)
+        pair = lambda v: (int(v), int(v)) if isinstance(v, int) else tuple(int(i) for i in v)  # noqa: E731
+        self.kernel_size, self.strides, self.dilation_rate = pair(kernel_size), pair(strides), pair(dilation_rate)
+        self.padding, self.depth_multiplier, self.use_bias = padding, int(depth_multiplier), bool(use_bias)
+        self.activation_name, self.activation = _act.get(activation, custom_objects)
+        self.depthwise_initializer = _init_config(depthwise_initializer, 'glorot_uniform')
+        self.depthwise_kernel = self.bias = None
+
+    def build(self, input_shape):
+        self.channels = cin = int(input_shape[-1])
+        kh, kw = self.kernel_size
+        w = torch.empty(cin * self.depth_multiplier, 1, kh, kw)
+        self.depthwise_kernel = self.add_weight('depthwise_kernel', _initialize(w, self.depthwise_initializer, kh * kw,
+                                                                                kh * kw * self.depth_multiplier))
+        if self.use_bias:
+            self.bias = self.add_weight('bias', torch.zeros(cin * self.depth_multiplier))
+        self.built = True
+
+    def to_keras_layout(self, index, tensor):
+        if index != 0:
+            return tensor
+        kh, kw = self.kernel_size
+        return tensor.reshape(self.channels, self.depth_multiplier, kh, kw).permute(2, 3, 0, 1)
+
+    def from_keras_layout(self, index, array):
+        if index != 0:
+            return array
+        kh, kw, c, m = array.shape
+        return np.transpose(array, (2, 3, 0, 1)).reshape(c * m, 1, kh, kw)
+
+    def compute_output_shape(self, input_shape):
+        n, h, w, c = input_shape
+        return (n, _conv_out(h, self.kernel_size[0], self.strides[0], self.padding, self.dilation_rate[0]),
+                _conv_out(w, self.kernel_size[1], self.strides[1], self.padding, self.dilation_rate[1]),
+                c * self.depth_multiplier)
+
+    def _depthwise(self, x):
+        if self.padding == 'same':
+            t, b = _tf_same_pads(x.shape[1], self.kernel_size[0], self.strides[0], self.dilation_rate[0])
+            l, r = _tf_same_pads(x.shape[2], self.kernel_size[1], self.strides[1], self.dilation_rate[1])
+            if t or b or l or r:
+                x = F.pad(x, (0, 0, l, r, t, b))
+        return F.conv2d(x.permute(0, 3, 1, 2), self.depthwise_kernel, None, stride=self.strides,
+                        dilation=self.dilation_rate, groups=x.shape[-1])
+
+    def call(self, x, training=False):
+        y = self._depthwise(x)
+        if self.bias is not None:
+            y = y + self.bias.view(1, -1, 1, 1)
+        return self.activation(y.permute(0, 2, 3, 1))
+
+    def _extra_config(self):
+        return {'kernel_size': list(self.kernel_size), 'strides': list(self.strides), 'padding': self.padding,
+                'data_format': 'channels_last', 'dilation_rate': list(self.dilation_rate), 'groups': 1,
+                'activation': self.activation_name, 'use_bias': self.use_bias, 'depth_multiplier': self.depth_multiplier,
+                'depthwise_initializer': self.depthwise_initializer, 'bias_initializer': _init_config('zeros', 'zeros'),
+                'depthwise_regularizer': None, 'bias_regularizer': None, 'activity_regularizer': None,
+                'depthwise_constraint': None, 'bias_constraint': None}
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        cfg = dict(config)
+        if cfg.get('batch_input_shape') is not None:
+            cfg['batch_input_shape'] = tuple(cfg['batch_input_shape'])
+        return cls(custom_objects=custom_objects, **cfg)
+
+
+class SeparableConv2D(DepthwiseConv2D):
+    """Depthwise convolution followed by a 1 x 1 convolution (``pointwise_kernel`` ``(1, 1, channels * multiplier,
+    filters)`` in Keras, kept as ``[filters, channels * multiplier]``)."""
+
+    def __init__(self, filters, kernel_size, pointwise_initializer='glorot_uniform', **kwargs):
+        for key in ('pointwise_regularizer', 'pointwise_constraint'):
+            kwargs.pop(key, None)
+        super().__init__(kernel_size, **kwargs)
+        self.filters = int(filters)
+        self.pointwise_initializer = _init_config(pointwise_initializer, 'glorot_uniform')
+        self.pointwise_kernel = None
+
+    def build(self, input_shape):
+        self.channels = cin = int(input_shape[-1])
+        kh, kw = self.kernel_size
+        mid = cin * self.depth_multiplier
+        self.depthwise_kernel = self.add_weight('depthwise_kernel', _initialize(
+            torch.empty(mid, 1, kh, kw), self.depthwise_initializer, kh * kw, kh * kw * self.depth_multiplier))
+        self.pointwise_kernel = self.add_weight('pointwise_kernel', _initialize(
+            torch.empty(self.filters, mid), self.pointwise_initializer, mid, self.filters))
+        if self.use_bias:
+            self.bias = self.add_weight('bias', torch.zeros(self.filters))
+        self.built = True
+
+    def to_keras_layout(self, index, tensor):
+        if index == 1:
+            return tensor.t().reshape(1, 1, tensor.shape[1], tensor.shape[0])
+        return super().to_keras_layout(index, tensor)
+
+    def from_keras_layout(self, index, array):
+        if index == 1:
+            return np.ascontiguousarray(array.reshape(array.shape[2], array.shape[3]).T)
+        return super().from_keras_layout(index, array)
+
+    def compute_output_shape(self, input_shape):
+        return tuple(super().compute_output_shape(input_shape)[:3]) + (self.filters,)
+
+    def call(self, x, training=False):
+        y = self._depthwise(x).permute(0, 2, 3, 1)
+        return self.activation(F.linear(y, self.pointwise_kernel, self.bias))
+
+    def _extra_config(self):
+        cfg = super()._extra_config()
+        cfg.update({'filters': self.filters, 'pointwise_initializer': self.pointwise_initializer,
+                    'pointwise_regularizer': None, 'pointwise_constraint': None})
+        return cfg
+
+
+class Conv2DTranspose(Layer):
+    """Transposed convolution with TensorFlow's output geometry ('valid': ``in * s + max(k - s, 0)``, 'same':
+    ``in * s``). Keras kernel ``(kh, kw, filters, channels)``, kept as torch's ``[channels, filters, kh, kw]``."""
+
+    def __init__(self, filters, kernel_size, strides=(1, 1), padding='valid', output_padding=None, data_format=None,
+                 dilation_rate=(1, 1), activation=None, use_bias=True, kernel_initializer='glorot_uniform',
+                 bias_initializer='zeros', custom_objects=None, **kwargs):
+        for key in ('kernel_regularizer', 'bias_regularizer', 'activity_regularizer', 'kernel_constraint',
+                    'bias_constraint', 'groups'):
+            kwargs.pop(key, None)
+        super().__init__(**kwargs)
+        if output_padding is not None or tuple(np.atleast_1d(dilation_rate)) not in ((1,), (1, 1)):
+            raise ValueError("Conv2DTranspose: output_padding / dilation are not supported")
+        pair = lambda v: (int(v), int(v)) if isinstance(v, int) else tuple(int(i) for i in v)  # noqa: E731
+        self.filters, self.kernel_size, self.strides, self.padding = int(filters), pair(kernel_size), pair(strides), padding
+        self.activation_name, self.activation = _act.get(activation, custom_objects)
+        self.use_bias = bool(use_bias)
+        self.kernel_initializer = _init_config(kernel_initializer, 'glorot_uniform')
+        self.kernel = self.bias = None
+
+    def build(self, input_shape):
+        cin = int(input_shape[-1])
+        kh, kw = self.kernel_size
+        self.kernel = self.add_weight('kernel', _initialize(torch.empty(cin, self.filters, kh, kw), self.kernel_initializer,
+                                                            kh * kw * cin, kh * kw * self.filters))
+        if self.use_bias:
+            self.bias = self.add_weight('bias', torch.zeros(self.filters))
+        self.built = True
+
+    def to_keras_layout(self, index, tensor):
+        return tensor.permute(2, 3, 1, 0) if index == 0 else tensor
+
+    def from_keras_layout(self, index, array):
+        return np.transpose(array, (3, 2, 0, 1)) if index == 0 else array
+
+    def _out(self, size, k, s):
+        if size is None:
+            return None
+        return size * s if self.padding == 'same' else size * s + max(k - s, 0)
+
+    def compute_output_shape(self, input_shape):
+        n, h, w, _ = input_shape
+        return (n, self._out(h, self.kernel_size[0], self.strides[0]), self._out(w, self.kernel_size[1], self.strides[1]),
+                self.filters)
+
+    def call(self, x, training=False):
+        full = F.conv_transpose2d(x.permute(0, 3, 1, 2), self.kernel, self.bias, stride=self.strides)
+        out = []
+        for dim, (size, k, s) in enumerate(zip(x.shape[1:3], self.kernel_size, self.strides)):
+            want = self._out(size, k, s)
+            start = max(k - s, 0) // 2 if self.padding == 'same' else 0
+            out.append((start, want))
+        (h0, hh), (w0, ww) = out
+        full = full[:, :, h0:h0 + hh, w0:w0 + ww]
+        pad_h, pad_w = hh - full.shape[2], ww - full.shape[3]
+        if pad_h > 0 or pad_w > 0:  # stride larger than the kernel: the tail of the output sees no input
+            full = F.pad(full, (0, max(pad_w, 0), 0, max(pad_h, 0)))
+            if self.bias is not None:  # ... but still the bias
+                if pad_h > 0:
+                    full[:, :, -pad_h:, :] = self.bias.view(1, -1, 1, 1)
+                if pad_w > 0:
+                    full[:, :, :, -pad_w:] = self.bias.view(1, -1, 1, 1)
+        return self.activation(full.permute(0, 2, 3, 1))
+
+    def _extra_config(self):
+        return {'filters': self.filters, 'kernel_size': list(self.kernel_size), 'strides': list(self.strides),
+                'padding': self.padding, 'data_format': 'channels_last', 'dilation_rate': [1, 1], 'groups': 1,
+                'activation': self.activation_name, 'use_bias': self.use_bias, 'kernel_initializer': self.kernel_initializer,
+                'bias_initializer': _init_config('zeros', 'zeros'), 'kernel_regularizer': None, 'bias_regularizer': None,
+                'activity_regularizer': None, 'kernel_constraint': None, 'bias_constraint': None, 'output_padding': None}
+
+    from_config = classmethod(DepthwiseConv2D.from_config.__func__)
+
+
+class UpSampling2D(Layer):
+    def __init__(self, size=(2, 2), data_format=None, interpolation='nearest', **kwargs):
+        super().__init__(**kwargs)
+        self.size = (int(size), int(size)) if isinstance(size, int) else tuple(int(v) for v in size)
+        if interpolation not in ('nearest', 'bilinear'):
+            raise ValueError("UpSampling2D: interpolation must be 'nearest' or 'bilinear'")
+        self.interpolation = interpolation
+
+    def compute_output_shape(self, input_shape):
+        n, h, w, c = input_shape
+        return (n, None if h is None else h * self.size[0], None if w is None else w * self.size[1], c)
+
+    def call(self, x, training=False):
+        if self.interpolation == 'nearest':
+            return x.repeat_interleave(self.size[0], dim=1).repeat_interleave(self.size[1], dim=2)
+        y = F.interpolate(x.permute(0, 3, 1, 2), scale_factor=tuple(float(v) for v in self.size), mode='bilinear',
+                          align_corners=False)
+        return y.permute(0, 2, 3, 1)
+
+    def _extra_config(self):
+        return {'size': list(self.size), 'data_format': 'channels_last', 'interpolation': self.interpolation}
+
+
+# ------------------------------------------------------------------------------------------ shape and noise layers
+class Permute(Layer):
+    def __init__(self, dims, **kwargs):
+        super().__init__(**kwargs)
+        self.dims = tuple(int(d) for d in dims)
+
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0],) + tuple(input_shape[d] for d in self.dims)
+
+    def call(self, x, training=False):
+        return x.permute((0,) + self.dims)
+
+    def _extra_config(self):
+        return {'dims': list(self.dims)}
+
+
+class RepeatVector(Layer):
+    def __init__(self, n, **kwargs):
+        super().__init__(**kwargs)
+        self.n = int(n)
+
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0], self.n, input_shape[1])
+
+    def call(self, x, training=False):
+        return x.unsqueeze(1).expand(-1, self.n, -1)
+
+    def _extra_config(self):
+        return {'n': self.n}
+
+
+class _ChannelDropout(Layer):
+    """Drops whole feature maps (one decision per sample and channel), scaled like Dropout."""
+
+    def __init__(self, rate, data_format=None, noise_shape=None, seed=None, **kwargs):
+        super().__init__(**kwargs)
+        self.rate = float(rate)
+
+    def call(self, x, training=False):
+        if not training or self.rate <= 0.0:
+            return x
+        shape = (x.shape[0],) + (1,) * (x.dim() - 2) + (x.shape[-1],)
+        return x * F.dropout(torch.ones(shape, dtype=x.dtype, device=x.device), self.rate, True)
+
+    def _extra_config(self):
+        return {'rate': self.rate, 'noise_shape': None, 'seed': None}
+
+
+class SpatialDropout1D(_ChannelDropout):
+    pass
+
+
+class SpatialDropout2D(_ChannelDropout):
+    def _extra_config(self):
+        return dict(super()._extra_config(), data_format='channels_last')
+
+
+class GaussianNoise(Layer):
+    def __init__(self, stddev, seed=None, **kwargs):
+        super().__init__(**kwargs)
+        self.stddev = float(stddev)
+
+    def call(self, x, training=False):
+        return x + torch.randn_like(x) * self.stddev if training else x
+
+    def _extra_config(self):
+        return {'stddev': self.stddev, 'seed': None}
+
+
+class Dot(Layer):
+    """Batch-wise dot product of two ``[batch, features]`` inputs (``axes=1`` / ``-1``), optionally L2-normalised."""
+
+    def __init__(self, axes=-1, normalize=False, **kwargs):
+        super().__init__(**kwargs)
+        self.axes, self.normalize = axes, bool(normalize)
+
+    def compute_output_shape(self, input_shape):
+        return (input_shape[0][0], 1)
+
+    def call(self, xs, training=False):
+        a, b = xs
+        if a.dim() != 2 or b.dim() != 2:
+            raise ValueError("Dot is implemented for 2-D inputs")
+        if self.normalize:
+            a, b = F.normalize(a, dim=-1), F.normalize(b, dim=-1)
+        return (a * b).sum(dim=-1, keepdim=True)
+
+    def _extra_config(self):
+        return {'axes': self.axes, 'normalize': self.normalize}
+
+
+# ------------------------------------------------------------------------------------------------------- wrappers
+class _Wrapper(Layer):
+    """A layer that owns other layers: their weights are listed under this layer's name, as Keras does."""
+
+    def _adopt(self, inner, prefix=''):
+        for name, tensor, trainable in inner._weights:
+            self._weights.append((prefix + name, tensor, trainable))
+
+    @staticmethod
+    def _inner_from(spec, custom_objects=None):
+        from .layers import deserialize_layer
+        return spec if isinstance(spec, Layer) else deserialize_layer(spec, custom_objects)
+
+    @staticmethod
+    def _spec(inner):
+        return {'class_name': type(inner).__name__, 'config': inner.get_config()}
+
+
+class TimeDistributed(_Wrapper):
+    """Applies ``layer`` to every time step of ``[batch, time, ...]`` (one call on the flattened batch)."""
+
+    def __init__(self, layer, custom_objects=None, **kwargs):
+        super().__init__(**kwargs)
+        self.layer = self._inner_from(layer, custom_objects)
+
+    def build(self, input_shape):
+        inner_shape = (input_shape[0],) + tuple(input_shape[2:])
+        if not self.layer.built:
+            self.layer.build(inner_shape)
+            self.layer.built = True
+        self._adopt(self.layer)
+        self.built = True
+
+    def to_keras_layout(self, index, tensor):
+        return self.layer.to_keras_layout(index, tensor)
+
+    def from_keras_layout(self, index, array):
+        return self.layer.from_keras_layout(index, array)
+
+    def compute_output_shape(self, input_shape):
+        inner = self.layer.compute_output_shape((input_shape[0],) + tuple(input_shape[2:]))
+        return (input_shape[0], input_shape[1]) + tuple(inner[1:])
+
+    def call(self, x, training=False):
+        b, t = x.shape[0], x.shape[1]
+        y = self.layer.call(x.reshape((b * t,) + tuple(x.shape[2:])), training=training)
+        return y.reshape((b, t) + tuple(y.shape[1:]))
+
+    def _extra_config(self):
+        return {'layer': self._spec(self.layer)}
+
+    @classmethod
+    def from_config(cls, config, custom_objects=None):
+        cfg = dict(config)
+        if cfg.get('batch_input_shape') is not None:
+            cfg['batch_input_shape'] = tuple(cfg['batch_input_shape'])
+        return cls(custom_objects=custom_objects, **cfg)
+
+
+class Bidirectional(_Wrapper):
+    """Runs a recurrent layer forwards and a copy of it backwards and merges the two (``concat`` / ``sum`` / ``mul`` /
+    ``ave``); with ``return_sequences`` the backward outputs are put back into forward time order first."""
+
+    def __init__(self, layer, merge_mode='concat', weights=None, backward_layer=None, custom_objects=None, **kwargs):
+        super().__init__(**kwargs)
+        if merge_mode not in ('concat', 'sum', 'mul', 'ave'):
+            raise ValueError("Bidirectional: merge_mode must be one of concat / sum / mul / ave")
+        self.merge_mode = merge_mode
+        self.forward = self._inner_from(layer, custom_objects)
+        if not isinstance(self.forward, _Recurrent):
+            raise ValueError("Bidirectional wraps SimpleRNN / LSTM / GRU layers")
+        if backward_layer is not None:
+            self.backward = self._inner_from(backward_layer, custom_objects)
+        else:
+            cfg = self.forward.get_config()
+            cfg['go_backwards'] = not self.forward.go_backwards
+            cfg['name'] = 'backward_' + self.forward.name
+            self.backward = type(self.forward).from_config(cfg, custom_objects=custom_objects)
+        if not self.forward.name.startswith('forward_'):
+            self.forward.name = 'forward_' + self.forward.name
+
+    def build(self, input_shape):
+        for inner in (self.forward, self.backward):
+            if not inner.built:
+                inner.build(input_shape)
+                inner.built = True
+            self._adopt(inner, prefix=inner.name + '/')
+        self.built = True
+
+    def compute_output_shape(self, input_shape):
+        shape = list(self.forward.compute_output_shape(input_shape))
+        if self.merge_mode == 'concat':
+            shape[-1] *= 2
+        return tuple(shape)
+
+    def call(self, x, training=False):
+        a = self.forward.call(x, training=training)
+        b = self.backward.call(x, training=training)
+        if self.forward.return_sequences:
+            b = b.flip(1)
+        if self.merge_mode == 'concat':
+            return torch.cat([a, b], dim=-1)
+        if self.merge_mode == 'sum':
+            return a + b
+        if self.merge_mode == 'mul':
+            return a * b
+        return (a + b) / 2.0
+
+    def _extra_config(self):
+        fwd = self._spec(self.forward)
+        fwd['config']['name'] = self.forward.name[len('forward_'):] if self.forward.name.startswith('forward_') \
+            else self.forward.name
+        return {'layer': fwd, 'merge_mode': self.merge_mode}
+
+    from_config = classmethod(TimeDistributed.from_config.__func__)
+
+
 EXTRA_LAYERS = (LeakyReLU, ELU, Multiply, Subtract, Maximum, Minimum, Average, GlobalMaxPooling2D, GlobalAveragePooling1D,
                 GlobalMaxPooling1D, MaxPooling1D, AveragePooling1D, LayerNormalization, Embedding, Conv1D, SimpleRNN, LSTM,
-                GRU)
+                GRU, DepthwiseConv2D, SeparableConv2D, Conv2DTranspose, UpSampling2D, Permute, RepeatVector,
+                SpatialDropout1D, SpatialDropout2D, GaussianNoise, Dot, TimeDistributed, Bidirectional)
 LAYER_CLASSES.update({c.__name__: c for c in EXTRA_LAYERS})

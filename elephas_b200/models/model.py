@@ -271,15 +271,23 @@ class Model:
         if device == self._device:
             return self
         self._sync_from_engine()
-        for layer in self.layers:
-            moved = []
-            for n, w, t in layer._weights:
-                nw = w.detach().to(device).requires_grad_(w.requires_grad)
-                moved.append((n, nw, t))
-                for attr in ('kernel', 'bias', 'gamma', 'beta', 'moving_mean', 'moving_variance'):
-                    if getattr(layer, attr, None) is w:
-                        setattr(layer, attr, nw)
-            layer._weights = moved
+        # every weight tensor once (wrappers list the tensors of the layers they own under their own name), then every
+        # reference to it: the weight lists and whatever attribute a layer keeps it under (kernel, recurrent_kernel, ...)
+        everyone, todo = [], list(self.layers)
+        while todo:
+            layer = todo.pop()
+            everyone.append(layer)
+            todo.extend(v for v in vars(layer).values() if isinstance(v, L.Layer))
+        moved = {}
+        for layer in everyone:
+            for _, w, _ in layer._weights:
+                if id(w) not in moved:
+                    moved[id(w)] = (w, w.detach().to(device).requires_grad_(w.requires_grad))
+        for layer in everyone:
+            layer._weights = [(n, moved[id(w)][1], t) for n, w, t in layer._weights]
+            for attr, value in list(vars(layer).items()):
+                if isinstance(value, torch.Tensor) and id(value) in moved:
+                    setattr(layer, attr, moved[id(value)][1])
         if self.optimizer is not None:
             self.optimizer._slots = {k: v.to(device) for k, v in self.optimizer._slots.items()}
         self._device = device

@@ -197,3 +197,110 @@ def test_more_keras_losses_and_metrics_match_their_definitions():
     first = model.evaluate(xs, ys)[0]
     model.fit(xs, ys, batch_size=16, epochs=20, verbose=0)
     assert model.evaluate(xs, ys)[0] < first
+
+
+def test_second_batch_of_layers_and_device_moves(tmp_path):
+    from elephas_b200.models import BatchNormalization, Conv2D
+    from elephas_b200.models.layers_extra import (Bidirectional, Conv2DTranspose, DepthwiseConv2D, Dot, GaussianNoise,
+                                                  Permute, RepeatVector, SeparableConv2D, SpatialDropout1D,
+                                                  SpatialDropout2D, TimeDistributed, UpSampling2D)
+    rng = np.random.default_rng(6)
+    img = rng.normal(size=(2, 7, 6, 3)).astype(np.float32)
+    # depthwise: per-channel correlation, Keras kernel (kh, kw, channels, multiplier), output channel c * m + j
+    dw = DepthwiseConv2D(3, depth_multiplier=2, padding='same', strides=2)
+    got = _run(dw, img)
+    k = dw.to_keras_layout(0, dw.depthwise_kernel.detach()).numpy()
+    b = dw.bias.detach().numpy()
+    assert k.shape == (3, 3, 3, 2) and got.shape == (2, 4, 3, 6) == tuple(dw.compute_output_shape((2, 7, 6, 3)))
+    xp = np.pad(img, ((0, 0), (1, 1), (0, 1), (0, 0)))          # TF 'same' for 7 -> 4 (stride 2): 1 + 1; for 6 -> 3: 0 + 1
+    want = np.zeros((2, 4, 3, 6), np.float32)
+    for p in range(4):
+        for q in range(3):
+            patch = xp[:, 2 * p:2 * p + 3, 2 * q:2 * q + 3, :]   # [n, 3, 3, c]
+            want[:, p, q, :] = np.einsum('nhwc,hwcm->ncm', patch, k).reshape(2, 6) + b
+    assert np.allclose(got, want, atol=1e-5)
+    assert np.array_equal(dw.from_keras_layout(0, k), dw.depthwise_kernel.detach().numpy())
+    sep = SeparableConv2D(5, 3, padding='valid')
+    got = _run(sep, img)
+    kd = sep.to_keras_layout(0, sep.depthwise_kernel.detach()).numpy()
+    kp = sep.to_keras_layout(1, sep.pointwise_kernel.detach()).numpy()
+    assert kp.shape == (1, 1, 3, 5) and got.shape == (2, 5, 4, 5)
+    mid = np.zeros((2, 5, 4, 3), np.float32)
+    for p in range(5):
+        for q in range(4):
+            mid[:, p, q, :] = np.einsum('nhwc,hwcm->ncm', img[:, p:p + 3, q:q + 3, :], kd).reshape(2, 3)
+    assert np.allclose(got, mid @ kp[0, 0] + sep.bias.detach().numpy(), atol=1e-5)
+    assert np.array_equal(sep.from_keras_layout(1, kp), sep.pointwise_kernel.detach().numpy())
+    # transposed convolution: the adjoint of the forward convolution with the same kernel (TF output sizes)
+    for padding, k_, s_ in (('valid', 3, 2), ('same', 3, 2), ('same', 4, 2), ('valid', 2, 3), ('same', 3, 1)):
+        up = Conv2DTranspose(4, k_, strides=s_, padding=padding, use_bias=False)
+        small = rng.normal(size=(2, 4, 5, 3)).astype(np.float32)
+        y = _run(up, small)
+        out_shape = tuple(up.compute_output_shape((2, 4, 5, 3)))
+        assert y.shape == out_shape
+        if k_ >= s_:
+            # <conv_T(x), z> == <x, conv(z)> with conv = Conv2D over the transposed-kernel roles
+            z = rng.normal(size=y.shape).astype(np.float32)
+            kern = up.to_keras_layout(0, up.kernel.detach()).numpy()                 # (kh, kw, filters, cin)
+            fwd = Conv2D(3, k_, strides=s_, padding=padding, use_bias=False)
+            fwd.build(z.shape)
+            fwd.kernel.data.copy_(torch.from_numpy(np.transpose(kern, (3, 0, 1, 2))))  # OHWI with O = cin, I = filters
+            back = _run(fwd, z)
+            assert back.shape == small.shape
+            assert np.isclose((y * z).sum(), (small * back).sum(), rtol=1e-4)
+    assert np.array_equal(_run(UpSampling2D((2, 3)), img), img.repeat(2, axis=1).repeat(3, axis=2))
+    assert _run(UpSampling2D(2, interpolation='bilinear'), img).shape == (2, 14, 12, 3)
+    seq = rng.normal(size=(3, 5, 4)).astype(np.float32)
+    assert np.array_equal(_run(Permute((2, 1)), seq), seq.transpose(0, 2, 1))
+    assert np.array_equal(_run(RepeatVector(3), seq[:, 0]), np.repeat(seq[:, :1], 3, axis=1))
+    a, b2 = torch.from_numpy(seq[:, 0]), torch.from_numpy(seq[:, 1])
+    assert np.allclose(Dot()([a, b2]).numpy()[:, 0], (seq[:, 0] * seq[:, 1]).sum(-1), atol=1e-6)
+    cos = Dot(normalize=True)([a, b2]).numpy()[:, 0]
+    assert np.allclose(cos, (seq[:, 0] * seq[:, 1]).sum(-1) / np.linalg.norm(seq[:, 0], axis=1) / np.linalg.norm(seq[:, 1], axis=1),
+                       atol=1e-6)
+    torch.manual_seed(0)
+    dropped = SpatialDropout1D(0.5)(torch.ones(4, 6, 8), training=True).numpy()
+    assert set(np.unique(dropped)) <= {0.0, 2.0} and all(len(np.unique(dropped[n, :, c])) == 1 for n in range(4) for c in range(8))
+    assert np.array_equal(SpatialDropout2D(0.5)(torch.ones(2, 3, 3, 4), training=False).numpy(), np.ones((2, 3, 3, 4)))
+    assert np.array_equal(GaussianNoise(0.5)(torch.ones(2, 3), training=False).numpy(), np.ones((2, 3)))
+    assert not np.array_equal(GaussianNoise(0.5)(torch.ones(2, 3), training=True).numpy(), np.ones((2, 3)))
+    # wrappers: TimeDistributed(Dense) == Dense on every step; Bidirectional = forward | backward halves
+    td = TimeDistributed(Dense(3))
+    got = _run(td, seq)
+    kern, bias = [w.detach().numpy() for w in td.weights]
+    assert np.allclose(got, seq @ kern.T + bias, atol=1e-6)
+    bi = Bidirectional(LSTM(4, return_sequences=True))
+    got = _run(bi, seq)
+    assert got.shape == (3, 5, 8) and len(bi.weights) == 6
+    assert np.allclose(got[..., :4], _run(bi.forward, seq), atol=1e-6)
+    assert np.allclose(got[..., 4:], _run(bi.backward, seq)[:, ::-1], atol=1e-6)
+    assert bi.backward.go_backwards and not bi.forward.go_backwards
+    assert bi.weight_names()[0].endswith('forward_' + bi.forward.name[len('forward_'):] + '/lstm_cell/kernel:0')
+    # a model with wrappers: JSON / HDF5 round trip, training, and a device move that re-binds every weight reference
+    torch.manual_seed(2)
+    model = Sequential([Bidirectional(GRU(5, return_sequences=True), merge_mode='sum', input_shape=(5, 4)),
+                        TimeDistributed(Dense(3, activation='relu')), GlobalMaxPooling1D(), Dense(2), Activation('softmax')])
+    model.compile(Adam(learning_rate=0.02), 'categorical_crossentropy', ['acc'])
+    xs = rng.normal(size=(96, 5, 4)).astype(np.float32)
+    ys = np.eye(2, dtype=np.float32)[(xs[:, :, 0].sum(1) > 0).astype(int)]
+    first = model.evaluate(xs, ys)[0]
+    model.fit(xs, ys, batch_size=16, epochs=10, verbose=0)
+    assert model.evaluate(xs, ys)[0] < first
+    want = model.predict(xs[:8])
+    twin = model_from_json(model.to_json())
+    twin.set_weights(model.get_weights())
+    assert np.allclose(twin.predict(xs[:8]), want, atol=1e-6)
+    path = str(tmp_path / 'wrapped.h5')
+    model.save(path)
+    assert np.allclose(load_model(path).predict(xs[:8]), want, atol=1e-6)
+    cnn = Sequential([SeparableConv2D(4, 3, padding='same', input_shape=(7, 6, 3)), BatchNormalization(),
+                      Conv2DTranspose(2, 2, strides=2), DepthwiseConv2D(3), GlobalMaxPooling2D(), Dense(2)])
+    assert cnn.predict(img).shape == (2, 2)
+    for m in (model, cnn):
+        m.to('meta')    # no data, but every reference must follow: the weight lists AND the attributes the layers use
+        stack = list(m.layers)
+        while stack:
+            layer = stack.pop()
+            stack.extend(v for v in vars(layer).values() if hasattr(v, '_weights') and v is not layer)
+            assert all(w.device.type == 'meta' for w in layer.weights)
+            assert all(v.device.type == 'meta' for v in vars(layer).values() if isinstance(v, torch.Tensor))

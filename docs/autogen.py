@@ -21,6 +21,7 @@ PAGES = [
     ('models/keras-layer.md', 'elephas_b200.models.model', ['Model', 'Sequential', 'model_from_json', 'load_model']),
     ('models/layers.md', 'elephas_b200.models.layers', None),
     ('models/layers-extra.md', 'elephas_b200.models.layers_extra', None),
+    ('models/callbacks.md', 'elephas_b200.models.callbacks', None),
     ('models/optimizers.md', 'elephas_b200.models.optimizers', None),
     ('models/zoo.md', 'elephas_b200.models.zoo', None),
     ('parameter/server.md', 'elephas_b200.parameter.server', None),

@@ -12,6 +12,7 @@ from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Bidirectio
                            GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Maximum, MaxPooling1D, Minimum, Multiply,
                            Permute, RepeatVector, SeparableConv2D, SimpleRNN, SpatialDropout1D, SpatialDropout2D,
                            Subtract, TimeDistributed, UpSampling2D)
+from . import callbacks  # noqa: F401
 from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
                     to_categorical)
 from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, Nadam, RMSprop  # noqa: F401

@@ -565,9 +565,29 @@ class Model:
             x, x_val = x[:split_at], x[split_at:]
             y, y_val = y[:split_at], y[split_at:]
         history = History()
+        from .callbacks import CallbackList
+        cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': len(x), 'verbose': verbose})
+        self.stop_training = False
         eng = self._native_engine()
-        if eng is not None:
+        if eng is not None and not cbs:
             eng.fit(x, y, batch_size, epochs, shuffle, history, x_val, y_val, verbose, initial_epoch)
+            return history
+        cbs.on_train_begin()
+        if eng is not None:  # callbacks see every epoch: one engine call per epoch, graphs re-recorded on an lr change
+            for epoch in range(initial_epoch, epochs):
+                cbs.on_epoch_begin(epoch)
+                self._sync_hyper_parameters()
+                eng.fit(x, y, batch_size, epoch + 1, shuffle, history, x_val, y_val, verbose, epoch)
+                logs = {k: v[-1] for k, v in history.history.items()}
+                cbs.on_epoch_end(epoch, logs)
+                for k, v in logs.items():  # what a callback adds to the logs ('lr') goes into the history too
+                    if k not in history.history:
+                        history.history[k] = [v]
+                    elif len(history.history[k]) < len(history.epoch):
+                        history.history[k].append(v)
+                if self.stop_training:
+                    break
+            cbs.on_train_end()
             return history
         self._tune_cpu_threads(batch_size)
         xt = _as_tensor(x, self._device)
@@ -577,6 +597,8 @@ class Model:
         n = xt.shape[0]
         names = self.metrics_names
         for epoch in range(initial_epoch, epochs):
+            cbs.on_epoch_begin(epoch)
+            self._sync_hyper_parameters()
             order = torch.randperm(n, device=self._device) if shuffle else torch.arange(n, device=self._device)
             sums = [0.0] * len(names)
             te = self._torch_engine()
@@ -603,15 +625,25 @@ class Model:
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
                 val = val if isinstance(val, list) else [val]
                 logs.update({'val_' + k: v for k, v in zip(names, val)})
+            cbs.on_epoch_end(epoch, logs)
             history._append(epoch, logs)
             if verbose:
                 print("Epoch %d/%d - " % (epoch + 1, epochs) + " - ".join("%s: %.4f" % kv for kv in logs.items()))
-            for cb in callbacks or []:
-                if hasattr(cb, 'on_epoch_end'):
-                    cb.on_epoch_end(epoch, logs)
             if self.stop_training:
                 break
+        cbs.on_train_end()
         return history
+
+    def _sync_hyper_parameters(self):
+        """Captured steps bake the optimizer's hyper-parameters into their kernels' arguments: when one was assigned
+        since the graphs were recorded (a learning-rate callback), drop the graphs; the next step records new ones."""
+        version = getattr(self.optimizer, '_hyper_version', 0)
+        if version == getattr(self, '_hyper_seen', 0):
+            return
+        self._hyper_seen = version
+        for holder in (self._engine, getattr(self, '_torch_step', None)):
+            if holder is not None:
+                holder.invalidate_graphs()
 
     # ------------------------------------------------------------- inference
     @torch.no_grad()

@@ -37,6 +37,7 @@ class Optimizer:
         self._config = cfg
         self.iterations = 0
         self._slots = {}
+        self._hyper_version = 0  # bumped when a hyper-parameter is assigned: captured CUDA graphs bake them in
 
     # ------------------------------------------------------------------ config
     def __getattr__(self, item):
@@ -46,8 +47,17 @@ class Optimizer:
         raise AttributeError(item)
 
     @property
-    def lr(self):
+    def learning_rate(self):
         return self._config['learning_rate']
+
+    @learning_rate.setter
+    def learning_rate(self, value):
+        value = float(value)
+        if value != self._config['learning_rate']:
+            self._config['learning_rate'] = value
+            self._hyper_version = self.__dict__.get('_hyper_version', 0) + 1
+
+    lr = learning_rate
 
     def get_config(self):
         cfg = {'name': self._config['name']}

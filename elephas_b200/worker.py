@@ -195,7 +195,9 @@ class AsynchronousSparkWorker(_WorkerBase):
         trainable = n > batch_size
 
         from .parameter.client import DeviceClient
-        eng = model._native_engine() if model.device.type == 'cuda' else None
+        # callbacks run inside Model.fit: with them the worker takes the generic pull -> fit -> push loop below
+        plain = not self.train_config.get('callbacks')
+        eng = model._native_engine() if model.device.type == 'cuda' and plain else None
         if eng is not None and isinstance(self.client, DeviceClient):
             self._train_against_device_ps(model, eng, x_train, y_train, epochs, batch_size, trainable)
             yield []

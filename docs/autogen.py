@@ -22,6 +22,8 @@ PAGES = [
     ('models/layers.md', 'elephas_b200.models.layers', None),
     ('models/layers-extra.md', 'elephas_b200.models.layers_extra', None),
     ('models/callbacks.md', 'elephas_b200.models.callbacks', None),
+    ('models/regularizers.md', 'elephas_b200.models.regularizers', None),
+    ('models/constraints.md', 'elephas_b200.models.constraints', None),
     ('models/optimizers.md', 'elephas_b200.models.optimizers', None),
     ('models/zoo.md', 'elephas_b200.models.zoo', None),
     ('parameter/server.md', 'elephas_b200.parameter.server', None),

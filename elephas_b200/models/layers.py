@@ -92,6 +92,9 @@ def _initialize(tensor, init_cfg, fan_in, fan_out):
     return tensor
 
 
+_OPTION_SUFFIXES = ('_regularizer', '_constraint')
+
+
 class KerasTensor:
     """Symbolic tensor of the functional API: produced by ``Input`` or by calling a layer."""
 
@@ -110,6 +113,9 @@ class Layer:
 
     def __init__(self, name=None, trainable=True, dtype='float32', input_shape=None, input_dim=None,
                  batch_input_shape=None, **kwargs):
+        # `<weight>_regularizer`, `<weight>_constraint`, `activity_regularizer`: every layer takes them the same way
+        self._weight_options = {}
+        self._take_weight_options(**{k: kwargs.pop(k) for k in list(kwargs) if k.endswith(_OPTION_SUFFIXES)})
         if kwargs:
             raise TypeError("%s got unexpected keyword argument(s) %s" % (type(self).__name__, sorted(kwargs)))
         self.name = name or unique_name(_to_snake(type(self).__name__))
@@ -124,6 +130,35 @@ class Layer:
         self._weights = []  # list of (keras_name, tensor, trainable) in Keras order
         self.inbound = []  # functional API: list (per call) of lists of KerasTensor
         self.outputs = []  # functional API: KerasTensor per call
+
+    # -- regularizers / constraints -------------------------------------------
+    def _take_weight_options(self, custom_objects=None, **options):
+        from . import constraints, regularizers
+        for key, value in options.items():
+            module = regularizers if key.endswith('_regularizer') else constraints
+            obj = module.get(value, custom_objects)
+            if obj is not None:
+                self._weight_options[key] = obj
+            else:
+                self._weight_options.pop(key, None)
+
+    @property
+    def activity_regularizer(self):
+        return self._weight_options.get('activity_regularizer')
+
+    def weight_options(self):
+        """``[(kind, option, index, tensor)]``: the regularizers ('regularizer') and constraints ('constraint') of this
+        layer's own weights, resolved to positions in ``_weights`` (``recurrent_regularizer`` -> ``recurrent_kernel``)."""
+        out = []
+        for key, obj in self._weight_options.items():
+            target, kind = key.rsplit('_', 1)
+            if target == 'activity':
+                continue
+            names = {target, target + '_kernel'}
+            for idx, (name, tensor, _) in enumerate(self._weights):
+                if name.rsplit('/', 1)[-1] in names:
+                    out.append((kind, obj, idx, tensor))
+        return out
 
     # -- weights -------------------------------------------------------------
     def add_weight(self, name, tensor, trainable=True):
@@ -167,6 +202,10 @@ class Layer:
             cfg['batch_input_shape'] = list(self.batch_input_shape)
         cfg['dtype'] = self.dtype
         cfg.update(self._extra_config())
+        from . import constraints, regularizers
+        for key, obj in self._weight_options.items():
+            module = regularizers if key.endswith('_regularizer') else constraints
+            cfg[key] = module.serialize(obj) if hasattr(obj, 'get_config') else obj
         return cfg
 
     @classmethod
@@ -238,6 +277,9 @@ class Dense(Layer):
                  activity_regularizer=None, kernel_constraint=None, bias_constraint=None, custom_objects=None,
                  **kwargs):
         super().__init__(**kwargs)
+        self._take_weight_options(custom_objects, kernel_regularizer=kernel_regularizer, bias_regularizer=bias_regularizer,
+                                  activity_regularizer=activity_regularizer, kernel_constraint=kernel_constraint,
+                                  bias_constraint=bias_constraint)
         self.units = int(units)
         self.activation_name, self.activation = _act.get(activation, custom_objects)
         self.use_bias = use_bias
@@ -409,6 +451,9 @@ class Conv2D(Layer):
                  bias_regularizer=None, activity_regularizer=None, kernel_constraint=None, bias_constraint=None,
                  custom_objects=None, **kwargs):
         super().__init__(**kwargs)
+        self._take_weight_options(custom_objects, kernel_regularizer=kernel_regularizer, bias_regularizer=bias_regularizer,
+                                  activity_regularizer=activity_regularizer, kernel_constraint=kernel_constraint,
+                                  bias_constraint=bias_constraint)
         if (data_format or 'channels_last') != 'channels_last':
             raise ValueError("only data_format='channels_last' is supported")
         self.filters = int(filters)
@@ -485,6 +530,8 @@ class BatchNormalization(Layer):
                  moving_variance_initializer='ones', beta_regularizer=None, gamma_regularizer=None,
                  beta_constraint=None, gamma_constraint=None, **kwargs):
         super().__init__(**kwargs)
+        self._take_weight_options(beta_regularizer=beta_regularizer, gamma_regularizer=gamma_regularizer,
+                                  beta_constraint=beta_constraint, gamma_constraint=gamma_constraint)
         self.axis = axis[0] if isinstance(axis, (list, tuple)) else axis
         self.momentum, self.epsilon, self.center, self.scale = momentum, epsilon, center, scale
         self.gamma = self.beta = self.moving_mean = self.moving_variance = None

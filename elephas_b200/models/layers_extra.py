@@ -166,6 +166,8 @@ class LayerNormalization(Layer):
                  gamma_initializer='ones', beta_regularizer=None, gamma_regularizer=None, beta_constraint=None,
                  gamma_constraint=None, **kwargs):
         super().__init__(**kwargs)
+        self._take_weight_options(beta_regularizer=beta_regularizer, gamma_regularizer=gamma_regularizer,
+                                  beta_constraint=beta_constraint, gamma_constraint=gamma_constraint)
         axis = axis[0] if isinstance(axis, (list, tuple)) else axis
         self.axis, self.epsilon, self.center, self.scale = int(axis), float(epsilon), bool(center), bool(scale)
         self.gamma = self.beta = None
@@ -198,6 +200,8 @@ class Embedding(Layer):
         if input_length is not None and 'input_shape' not in kwargs and 'batch_input_shape' not in kwargs:
             kwargs['input_shape'] = (int(input_length),)
         super().__init__(**kwargs)
+        self._take_weight_options(embeddings_regularizer=embeddings_regularizer, activity_regularizer=activity_regularizer,
+                                  embeddings_constraint=embeddings_constraint)
         self.input_dim, self.output_dim = int(input_dim), int(output_dim)
         self.mask_zero, self.input_length = bool(mask_zero), input_length
         self.embeddings = None
@@ -231,6 +235,9 @@ class Conv1D(Layer):
                  kernel_regularizer=None, bias_regularizer=None, activity_regularizer=None, kernel_constraint=None,
                  bias_constraint=None, custom_objects=None, **kwargs):
         super().__init__(**kwargs)
+        self._take_weight_options(custom_objects, kernel_regularizer=kernel_regularizer, bias_regularizer=bias_regularizer,
+                                  activity_regularizer=activity_regularizer, kernel_constraint=kernel_constraint,
+                                  bias_constraint=bias_constraint)
         first = lambda v: int(v[0] if isinstance(v, (list, tuple)) else v)  # noqa: E731
         self.filters, self.kernel_size, self.strides = int(filters), first(kernel_size), first(strides)
         self.dilation_rate, self.groups, self.padding = first(dilation_rate), int(groups), padding
@@ -307,8 +314,7 @@ class _Recurrent(Layer):
                  kernel_initializer='glorot_uniform', recurrent_initializer='orthogonal', bias_initializer='zeros',
                  return_sequences=False, return_state=False, go_backwards=False, stateful=False, unroll=False,
                  dropout=0.0, recurrent_dropout=0.0, custom_objects=None, **kwargs):
-        for key in ('kernel_regularizer', 'recurrent_regularizer', 'bias_regularizer', 'activity_regularizer',
-                    'kernel_constraint', 'recurrent_constraint', 'bias_constraint', 'time_major', 'implementation'):
+        for key in ('time_major', 'implementation'):
             kwargs.pop(key, None)
         super().__init__(**kwargs)
         if return_state or stateful:
@@ -487,9 +493,7 @@ class DepthwiseConv2D(Layer):
     def __init__(self, kernel_size, strides=(1, 1), padding='valid', depth_multiplier=1, data_format=None,
                  dilation_rate=(1, 1), activation=None, use_bias=True, depthwise_initializer='glorot_uniform',
                  bias_initializer='zeros', custom_objects=None, **kwargs):
-        for key in ('depthwise_regularizer', 'bias_regularizer', 'activity_regularizer', 'depthwise_constraint',
-                    'bias_constraint', 'groups'):
-            kwargs.pop(key, None)
+        kwargs.pop('groups', None)
         super().__init__(**kwargs)
         pair = lambda v: (int(v), int(v)) if isinstance(v, int) else tuple(int(i) for i in v)  # noqa: E731
         self.kernel_size, self.strides, self.dilation_rate = pair(kernel_size), pair(strides), pair(dilation_rate)
@@ -562,8 +566,6 @@ class SeparableConv2D(DepthwiseConv2D):
     filters)`` in Keras, kept as ``[filters, channels * multiplier]``)."""
 
     def __init__(self, filters, kernel_size, pointwise_initializer='glorot_uniform', **kwargs):
-        for key in ('pointwise_regularizer', 'pointwise_constraint'):
-            kwargs.pop(key, None)
         super().__init__(kernel_size, **kwargs)
         self.filters = int(filters)
         self.pointwise_initializer = _init_config(pointwise_initializer, 'glorot_uniform')
@@ -612,9 +614,7 @@ class Conv2DTranspose(Layer):
     def __init__(self, filters, kernel_size, strides=(1, 1), padding='valid', output_padding=None, data_format=None,
                  dilation_rate=(1, 1), activation=None, use_bias=True, kernel_initializer='glorot_uniform',
                  bias_initializer='zeros', custom_objects=None, **kwargs):
-        for key in ('kernel_regularizer', 'bias_regularizer', 'activity_regularizer', 'kernel_constraint',
-                    'bias_constraint', 'groups'):
-            kwargs.pop(key, None)
+        kwargs.pop('groups', None)
         super().__init__(**kwargs)
         if output_padding is not None or tuple(np.atleast_1d(dilation_rate)) not in ((1,), (1, 1)):
             raise ValueError("Conv2DTranspose: output_padding / dilation are not supported")

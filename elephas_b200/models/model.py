@@ -185,6 +185,7 @@ class Model:
         fuse = os.environ.get('ELEPHAS_B200_FUSE_BN', '1') != '0'
         fused, alias = self._fusion_plan() if fuse else ({}, {})
         pools, skipped = self._pool_pad_plan() if fuse else ({}, set())
+        self._activity_terms = []
         for t in self._node_order:
             key = (id(t.layer), t.node_index)
             if key in values or key in skipped:
@@ -203,6 +204,9 @@ class Model:
                                            residual=values[other] if other is not None else None)
                 continue
             values[key] = t.layer.call(ins[0] if len(ins) == 1 else ins, training=training)
+            if training and t.layer.activity_regularizer is not None:
+                out = values[key]
+                self._activity_terms.append(t.layer.activity_regularizer(out) / out.shape[0])
         outs = [values[(id(o.layer), o.node_index)] for o in self._outputs]
         return outs[0] if len(outs) == 1 else outs
 
@@ -243,6 +247,64 @@ class Model:
 
     def count_params(self):
         return int(sum(w.numel() for w in self.weights))
+
+    # --------------------------------------------- regularizers / constraints
+    def _all_layers(self):
+        """The layers of the graph and the layers they own (TimeDistributed / Bidirectional)."""
+        seen, todo = [], list(self.layers)
+        while todo:
+            layer = todo.pop()
+            if any(layer is s for s in seen):
+                continue
+            seen.append(layer)
+            todo.extend(v for v in vars(layer).values() if isinstance(v, L.Layer))
+        return seen
+
+    def _weight_options(self):
+        """``(penalties, constraints, activity)``: ``[(tensor, regularizer)]``, ``[(layer, index, tensor, constraint)]`` and
+        whether any layer regularises its output. The walk over the layers is cached (``compile`` drops it); the tensors
+        are read from the layers at every use, so ``to()`` needs no invalidation."""
+        cached = getattr(self, '_wopt_cache', None)
+        if cached is None:
+            entries, activity = [], False
+            for layer in self._all_layers():
+                activity = activity or layer.activity_regularizer is not None
+                entries.extend((layer, kind, obj, idx) for kind, obj, idx, _ in layer.weight_options())
+            cached = self._wopt_cache = (entries, activity)
+        penalties, cons = [], []
+        for layer, kind, obj, idx in cached[0]:
+            tensor = layer._weights[idx][1]
+            if kind == 'regularizer':
+                if tensor.requires_grad:
+                    penalties.append((tensor, obj))
+            else:
+                cons.append((layer, idx, tensor, obj))
+        return penalties, cons, cached[1]
+
+    def has_weight_options(self):
+        """True when a layer carries a regularizer or a constraint: the fused native engines do not apply them, such
+        models train on the tape path (eagerly on the CPU, as a captured torch step on the GPU)."""
+        penalties, cons, activity = self._weight_options()
+        return bool(penalties or cons or activity)
+
+    def _regularization_loss(self):
+        """Sum of the weight penalties and of the activity penalties noted by the last training forward, or None."""
+        penalties, _, _ = self._weight_options()
+        terms = [reg(w) for w, reg in penalties] + list(getattr(self, '_activity_terms', ()))
+        self._activity_terms = []
+        if not terms:
+            return None
+        total = terms[0]
+        for t in terms[1:]:
+            total = total + t
+        return total
+
+    @torch.no_grad()
+    def _apply_constraints(self):
+        _, cons, _ = self._weight_options()
+        for layer, idx, tensor, con in cons:
+            view = layer.to_keras_layout(idx, tensor)   # a view of the weight in the layout `axis` refers to
+            view.copy_(con(view))
 
     def get_weights(self):
         """List of NumPy arrays in Keras order and Keras layouts (Dense kernels are ``(in, out)``)."""
@@ -442,6 +504,7 @@ class Model:
                 te.export_optimizer_state()  # the captured step's slots belong to the outgoing optimizer
                 self._torch_step = None
         self._torch_engine_failed = False
+        self._wopt_cache = None
         self.optimizer = new_opt
         self.loss = loss
         self._loss_name = _losses.canonical_name(loss)
@@ -511,9 +574,13 @@ class Model:
         out = out.float()
         per_sample = self._loss_fn(yb, out)
         loss = per_sample.mean()
+        penalty = self._regularization_loss()
+        if penalty is not None:
+            loss = loss + penalty
         loss.backward()
         grads = [p.grad if p.grad is not None else torch.zeros_like(p) for p in params]
         self.optimizer.apply_gradients(params, grads)
+        self._apply_constraints()
         with torch.no_grad():
             stats = [float(loss.detach())]
             for _, fn in self._metric_fns:

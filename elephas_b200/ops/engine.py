@@ -158,6 +158,8 @@ def maybe_create(model):
     """An :class:`MLPEngine` for a compiled model on a CUDA device, or None (torch path)."""
     if not native_enabled() or model.device.type != 'cuda':
         return None
+    if model.has_weight_options():
+        return None  # weight / activity penalties and constraints: the captured torch step applies them
     plan = _plan(model)
     if plan is None:
         return None

@@ -154,7 +154,11 @@ class TorchStepEngine:
             out = model(x, training=True)
         out = out.float()
         per_sample = model._loss_fn(y, out)
-        per_sample.mean().backward()
+        penalty = model._regularization_loss()  # None unless a layer carries a regularizer
+        if penalty is None:
+            per_sample.mean().backward()
+        else:
+            (per_sample.mean() + penalty).backward()
         if self.sync is None:
             native.optimizer_step(self.kind, self.numel, self.g32, self.step, w32=self.w32, slots=self.slots,
                                   apply=True, advance=True, **self._opt_kwargs())
@@ -165,8 +169,11 @@ class TorchStepEngine:
                                   delta_bf16=self.sync.delta(self.flip), advance=True, **self._opt_kwargs())
             if not self._in_warmup:
                 self.sync.reduce(self.flip)
+        model._apply_constraints()
         with torch.no_grad():
             self.stats[0] += per_sample.detach().double().sum()
+            if penalty is not None:
+                self.stats[0] += penalty.detach().double() * float(x.shape[0])
             for i, (_, fn) in enumerate(model._metric_fns[:4]):
                 self.stats[1 + i] += fn(y, out.detach()).double().sum()
             self.stats[7] += float(x.shape[0])

@@ -24,6 +24,7 @@ PAGES = [
     ('models/callbacks.md', 'elephas_b200.models.callbacks', None),
     ('models/regularizers.md', 'elephas_b200.models.regularizers', None),
     ('models/constraints.md', 'elephas_b200.models.constraints', None),
+    ('models/schedules.md', 'elephas_b200.models.schedules', None),
     ('models/optimizers.md', 'elephas_b200.models.optimizers', None),
     ('models/zoo.md', 'elephas_b200.models.zoo', None),
     ('parameter/server.md', 'elephas_b200.parameter.server', None),

@@ -61,7 +61,20 @@ def build_tree(model, include_optimizer=True, extra_root_attrs=None):
     compiled = getattr(model, '_compiled', False)
     if compiled:
         root.attrs['training_config'] = json.dumps(_training_config(model)).encode('utf8')
-    mw = root.create_group('model_weights')
+    _write_weights(model, root.create_group('model_weights'))
+    if include_optimizer and compiled and model.optimizer is not None:
+        ow = root.create_group('optimizer_weights')
+        names, values = _optimizer_weight_entries(model)
+        ow.attrs['weight_names'] = np.array([n.encode('utf8') for n in names])
+        for n, v in zip(names, values):
+            ow.create_dataset(n, v)
+    for k, v in (extra_root_attrs or {}).items():
+        root.attrs[k] = v
+    return root
+
+
+def _write_weights(model, mw):
+    """The weight groups of ``model`` below ``mw`` (``model_weights`` of a full file, the root of a weights-only file)."""
     layers = [l for l in model.layers]
     mw.attrs['layer_names'] = np.array([l.name.encode('utf8') for l in layers]) if layers else np.zeros((0,))
     mw.attrs['backend'] = _model_mod.BACKEND.encode('utf8')
@@ -74,15 +87,55 @@ def build_tree(model, include_optimizer=True, extra_root_attrs=None):
         for idx, (name, (_, w, _t)) in enumerate(zip(names, layer._weights)):
             value = layer.to_keras_layout(idx, w.detach()).cpu().numpy()
             g.create_dataset(name, np.ascontiguousarray(value, dtype=np.float32))
-    if include_optimizer and compiled and model.optimizer is not None:
-        ow = root.create_group('optimizer_weights')
-        names, values = _optimizer_weight_entries(model)
-        ow.attrs['weight_names'] = np.array([n.encode('utf8') for n in names])
-        for n, v in zip(names, values):
-            ow.create_dataset(n, v)
-    for k, v in (extra_root_attrs or {}).items():
-        root.attrs[k] = v
-    return root
+
+
+def save_weights(model, filepath, overwrite=True):
+    filepath = str(filepath)
+    if os.path.exists(filepath) and not overwrite:
+        raise IOError("%s already exists" % filepath)
+    root = hdf5.Group()
+    _write_weights(model, root)
+    hdf5.save_tree(filepath, root)
+
+
+def load_weights(model, filepath, by_name=False, skip_mismatch=False):
+    root = hdf5.load_tree(str(filepath))
+    mw = root['model_weights'] if 'model_weights' in root else root
+    saved = []
+    for lname in _names(mw.attrs.get('layer_names')):
+        g = mw[lname]
+        saved.append((lname, [np.asarray(g[wn].data) for wn in _names(g.attrs.get('weight_names'))]))
+    current = model.get_weights()
+    slots, at = {}, 0
+    for layer in model.layers:
+        slots[id(layer)] = (at, len(layer._weights))
+        at += len(layer._weights)
+
+    def assign(layer, values, origin):
+        lo, count = slots[id(layer)]
+        bad = len(values) != count or any(tuple(v.shape) != tuple(c.shape) for v, c in zip(values, current[lo:lo + count]))
+        if bad:
+            if skip_mismatch and by_name:
+                return
+            raise ValueError("layer %r expects weights of shapes %s, %s has %s"
+                             % (layer.name, [tuple(c.shape) for c in current[lo:lo + count]], origin,
+                                [tuple(v.shape) for v in values]))
+        current[lo:lo + count] = values
+
+    if by_name:
+        table = dict(saved)
+        for layer in model.layers:
+            if layer.name in table and (table[layer.name] or layer._weights):
+                assign(layer, table[layer.name], 'the file')
+    else:
+        with_weights = [(n, v) for n, v in saved if v]
+        mine = [l for l in model.layers if l._weights]
+        if len(with_weights) != len(mine):
+            raise ValueError("the file holds weights of %d layers, the model has %d layers with weights"
+                             % (len(with_weights), len(mine)))
+        for layer, (lname, values) in zip(mine, with_weights):
+            assign(layer, values, 'file layer %r' % lname)
+    model.set_weights(current)
 
 
 def save_model(model, filepath, overwrite=True, include_optimizer=True, extra_root_attrs=None):

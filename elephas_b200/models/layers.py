@@ -53,14 +53,20 @@ def _init_config(identifier, default):
         'glorot_uniform': 'GlorotUniform', 'glorot_normal': 'GlorotNormal', 'he_normal': 'HeNormal',
         'he_uniform': 'HeUniform', 'zeros': 'Zeros', 'ones': 'Ones', 'lecun_normal': 'LecunNormal',
         'lecun_uniform': 'LecunUniform', 'random_normal': 'RandomNormal', 'random_uniform': 'RandomUniform',
+        'normal': 'RandomNormal', 'uniform': 'RandomUniform', 'truncated_normal': 'TruncatedNormal',
+        'variance_scaling': 'VarianceScaling', 'orthogonal': 'Orthogonal', 'identity': 'Identity',
+        'constant': 'Constant', 'zero': 'Zeros', 'one': 'Ones',
     }
     cls = table.get(identifier, identifier)
-    cfg = {} if cls in ('Zeros', 'Ones') else {'seed': None}
-    if cls == 'RandomNormal':
-        cfg = {'mean': 0.0, 'stddev': 0.05, 'seed': None}
-    if cls == 'RandomUniform':
-        cfg = {'minval': -0.05, 'maxval': 0.05, 'seed': None}
-    return {'class_name': cls, 'config': cfg}
+    defaults = {
+        'Zeros': {}, 'Ones': {}, 'Constant': {'value': 0},
+        'RandomNormal': {'mean': 0.0, 'stddev': 0.05, 'seed': None},
+        'TruncatedNormal': {'mean': 0.0, 'stddev': 0.05, 'seed': None},
+        'RandomUniform': {'minval': -0.05, 'maxval': 0.05, 'seed': None},
+        'VarianceScaling': {'scale': 1.0, 'mode': 'fan_in', 'distribution': 'truncated_normal', 'seed': None},
+        'Orthogonal': {'gain': 1.0, 'seed': None}, 'Identity': {'gain': 1.0},
+    }
+    return {'class_name': cls, 'config': dict(defaults.get(cls, {'seed': None}))}
 
 
 def _initialize(tensor, init_cfg, fan_in, fan_out):
@@ -87,6 +93,44 @@ def _initialize(tensor, init_cfg, fan_in, fan_out):
             tensor.normal_(cfg.get('mean', 0.0), cfg.get('stddev', 0.05), generator=gen)
         elif cls == 'RandomUniform':
             tensor.uniform_(cfg.get('minval', -0.05), cfg.get('maxval', 0.05), generator=gen)
+        elif cls == 'TruncatedNormal':
+            mean, std = float(cfg.get('mean', 0.0)), float(cfg.get('stddev', 0.05))
+            torch.nn.init.trunc_normal_(tensor, mean=mean, std=std, a=mean - 2 * std, b=mean + 2 * std, generator=gen)
+        elif cls == 'Constant':
+            value = cfg.get('value', 0)
+            if isinstance(value, (int, float)):
+                tensor.fill_(float(value))
+            else:  # a Keras-layout array: the caller's layouts differ, only shapes that match as they are can be taken
+                value = torch.as_tensor(value, dtype=tensor.dtype)
+                if tuple(value.shape) != tuple(tensor.shape):
+                    raise ValueError("Constant initializer: value of shape %s for a weight stored as %s"
+                                     % (tuple(value.shape), tuple(tensor.shape)))
+                tensor.copy_(value)
+        elif cls == 'VarianceScaling':
+            fan = {'fan_in': fan_in, 'fan_out': fan_out, 'fan_avg': (fan_in + fan_out) / 2.0}[cfg.get('mode', 'fan_in')]
+            var = float(cfg.get('scale', 1.0)) / max(1.0, fan)
+            dist = cfg.get('distribution', 'truncated_normal')
+            if dist in ('truncated_normal', 'normal'):  # ('normal' is the Keras 2.2 spelling of the truncated form)
+                std = math.sqrt(var) / 0.87962566103423978
+                torch.nn.init.trunc_normal_(tensor, mean=0.0, std=std, a=-2 * std, b=2 * std, generator=gen)
+            elif dist == 'untruncated_normal':
+                tensor.normal_(0.0, math.sqrt(var), generator=gen)
+            elif dist == 'uniform':
+                limit = math.sqrt(3.0 * var)
+                tensor.uniform_(-limit, limit, generator=gen)
+            else:
+                raise ValueError("VarianceScaling: unknown distribution %r" % (dist,))
+        elif cls == 'Orthogonal':
+            if tensor.dim() < 2:
+                raise ValueError("Orthogonal initializer needs a weight of rank >= 2")
+            flat = torch.empty(tensor.shape[0], tensor.numel() // tensor.shape[0]).normal_(0.0, 1.0, generator=gen)
+            q, r = torch.linalg.qr(flat if flat.shape[0] >= flat.shape[1] else flat.t())
+            q = q * torch.sign(torch.diagonal(r))
+            tensor.copy_((q if flat.shape[0] >= flat.shape[1] else q.t()).reshape(tensor.shape) * float(cfg.get('gain', 1.0)))
+        elif cls == 'Identity':
+            if tensor.dim() != 2:
+                raise ValueError("Identity initializer needs a rank-2 weight")
+            tensor.copy_(torch.eye(tensor.shape[0], tensor.shape[1]) * float(cfg.get('gain', 1.0)))
         else:
             raise ValueError("Unsupported initializer %r" % (cls,))
     return tensor

@@ -29,6 +29,30 @@ KERAS_VERSION = '2.10.0'
 BACKEND = 'tensorflow'
 
 
+def _row_weights(y, sample_weight, class_weight):
+    """One weight per row from ``sample_weight`` and / or ``class_weight`` (``{class index: weight}``; the class of a row is
+    its integer label or the arg-max of its one-hot row), or None."""
+    if sample_weight is None and not class_weight:
+        return None
+    rows = len(y)
+    w = np.ones(rows, dtype=np.float32)
+    if sample_weight is not None:
+        sample_weight = np.asarray(sample_weight, dtype=np.float32).reshape(-1)
+        if len(sample_weight) != rows:
+            raise ValueError("sample_weight has %d entries for %d rows" % (len(sample_weight), rows))
+        w *= sample_weight
+    if class_weight:
+        labels = y.detach().cpu().numpy() if isinstance(y, torch.Tensor) else np.asarray(y)
+        if labels.ndim > 1 and labels.shape[-1] > 1:
+            labels = labels.reshape(rows, -1).argmax(axis=1)
+        labels = labels.reshape(rows).astype(np.int64)
+        table = np.ones(int(max(labels.max(initial=0), max(class_weight))) + 1, dtype=np.float32)
+        for k, v in class_weight.items():
+            table[int(k)] = float(v)
+        w *= table[labels]
+    return w
+
+
 class History:
     """``History.history`` maps metric name -> list of per-epoch values (Keras semantics)."""
 
@@ -562,8 +586,8 @@ class Model:
             cached = self._cpu_step_cache = (key, cpu_mlp.maybe_create(self))
         return cached[1]
 
-    def _torch_train_step(self, xb, yb):
-        step = self._cpu_step()
+    def _torch_train_step(self, xb, yb, wb=None):
+        step = self._cpu_step() if wb is None else None
         if step is not None:
             return step(xb, yb)
         params = self.trainable_weights
@@ -573,6 +597,8 @@ class Model:
             out = self(xb, training=True)
         out = out.float()
         per_sample = self._loss_fn(yb, out)
+        if wb is not None:  # Keras' sum-over-batch-size reduction: sum(w * loss) / rows
+            per_sample = per_sample * wb.reshape(per_sample.shape[0], *([1] * (per_sample.dim() - 1)))
         loss = per_sample.mean()
         penalty = self._regularization_loss()
         if penalty is not None:
@@ -594,9 +620,10 @@ class Model:
             from ..utils import cpu_threads
             cpu_threads.tune_for(self, rows)
 
-    def train_on_batch(self, x, y, **kwargs):
+    def train_on_batch(self, x, y, sample_weight=None, class_weight=None, return_dict=False, **kwargs):
         self._require_compiled()
-        eng = self._native_engine()
+        row_weight = _row_weights(y, sample_weight, class_weight)
+        eng = self._native_engine() if row_weight is None else None
         if eng is not None:
             stats = eng.train_on_batch(x, y)
         else:
@@ -605,18 +632,39 @@ class Model:
             if xb.dim() == 1:
                 xb = xb.unsqueeze(-1)
             self._tune_cpu_threads(len(xb))
-            te = self._torch_engine()
+            te = self._torch_engine() if row_weight is None else None
             if te is not None:
                 te.stats.zero_()
             if te is not None and self._graphed_step(xb, yb):
                 stats, _ = te.read_stats()
                 self.optimizer.iterations = int(te.step.item())
             else:
-                stats = self._torch_train_step(xb, yb)
+                wb = torch.as_tensor(row_weight, device=self._device) if row_weight is not None else None
+                stats = self._torch_train_step(xb, yb, wb)
+        if return_dict:
+            return dict(zip(self.metrics_names, stats))
         return stats if len(stats) > 1 else stats[0]
 
+    def test_on_batch(self, x, y, return_dict=False, **kwargs):
+        """Loss and metrics of one batch, no update."""
+        return self.evaluate(x, y, batch_size=max(len(x), 1), return_dict=return_dict)
+
+    def predict_on_batch(self, x):
+        return self.predict(x, batch_size=max(len(x), 1))
+
+    def get_layer(self, name=None, index=None):
+        if index is not None:
+            layers = self.layers
+            if not -len(layers) <= index < len(layers):
+                raise ValueError("Was asked to retrieve layer at index %d but model only has %d layers" % (index, len(layers)))
+            return layers[index]
+        for layer in self.layers:
+            if layer.name == name:
+                return layer
+        raise ValueError("No such layer: %s" % (name,))
+
     def fit(self, x=None, y=None, batch_size=None, epochs=1, verbose=0, callbacks=None, validation_split=0.0,
-            validation_data=None, shuffle=True, initial_epoch=0, **kwargs):
+            validation_data=None, shuffle=True, class_weight=None, sample_weight=None, initial_epoch=0, **kwargs):
         self._require_compiled()
         if 'nb_epoch' in kwargs:
             epochs = kwargs.pop('nb_epoch')
@@ -624,6 +672,7 @@ class Model:
         x = np.asarray(x) if not isinstance(x, torch.Tensor) else x
         y = np.asarray(y) if not isinstance(y, torch.Tensor) else y
         n_total = len(x)
+        row_weight = _row_weights(y, sample_weight, class_weight)
         x_val = y_val = None
         if validation_data is not None:
             x_val, y_val = validation_data[0], validation_data[1]
@@ -631,11 +680,13 @@ class Model:
             split_at = int(n_total * (1.0 - validation_split))
             x, x_val = x[:split_at], x[split_at:]
             y, y_val = y[:split_at], y[split_at:]
+            row_weight = row_weight[:split_at] if row_weight is not None else None
         history = History()
         from .callbacks import CallbackList
         cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': len(x), 'verbose': verbose})
         self.stop_training = False
-        eng = self._native_engine()
+        # weighted rows: the loss of the fused engines has no weight operand, the autograd step takes them
+        eng = self._native_engine() if row_weight is None else None
         if eng is not None and not cbs:
             eng.fit(x, y, batch_size, epochs, shuffle, history, x_val, y_val, verbose, initial_epoch)
             return history
@@ -662,13 +713,14 @@ class Model:
         if xt.dim() == 1:
             xt = xt.unsqueeze(-1)
         n = xt.shape[0]
+        wt = torch.as_tensor(row_weight, dtype=torch.float32, device=self._device) if row_weight is not None else None
         names = self.metrics_names
         for epoch in range(initial_epoch, epochs):
             cbs.on_epoch_begin(epoch)
             self._sync_hyper_parameters()
             order = torch.randperm(n, device=self._device) if shuffle else torch.arange(n, device=self._device)
             sums = [0.0] * len(names)
-            te = self._torch_engine()
+            te = self._torch_engine() if wt is None else None
             if te is not None:
                 te.stats.zero_()
             graphed_rows = 0
@@ -678,7 +730,7 @@ class Model:
                     graphed_rows += len(idx)  # loss / metric sums stay on the device until the epoch ends
                     continue
                 te = None
-                stats = self._torch_train_step(xt[idx], yt[idx])
+                stats = self._torch_train_step(xt[idx], yt[idx], wt[idx] if wt is not None else None)
                 for i, s in enumerate(stats):
                     sums[i] += s * len(idx)
             if graphed_rows:
@@ -748,7 +800,14 @@ class Model:
         return torch.cat(outs, dim=0).cpu().numpy()
 
     @torch.no_grad()
-    def evaluate(self, x=None, y=None, batch_size=None, verbose=0, **kwargs):
+    def evaluate(self, x=None, y=None, batch_size=None, verbose=0, return_dict=False, **kwargs):
+        stats = self._evaluate(x, y, batch_size)
+        if return_dict:
+            stats = stats if isinstance(stats, list) else [stats]
+            return dict(zip(self.metrics_names, stats))
+        return stats
+
+    def _evaluate(self, x, y, batch_size):
         self._require_compiled()
         batch_size = int(batch_size or 32)
         eng = self._native_engine()
@@ -779,9 +838,16 @@ class Model:
         from ..io.keras_h5 import save_model
         save_model(self, filepath, overwrite=overwrite, include_optimizer=include_optimizer)
 
-    def save_weights(self, filepath):
-        from ..io.keras_h5 import save_model
-        save_model(self, filepath, overwrite=True, include_optimizer=False)
+    def save_weights(self, filepath, overwrite=True):
+        """Weights only, in the layout of ``keras.Model.save_weights`` (one group per layer at the root of the file)."""
+        from ..io.keras_h5 import save_weights
+        save_weights(self, filepath, overwrite=overwrite)
+
+    def load_weights(self, filepath, by_name=False, skip_mismatch=False):
+        """Weights from a file written by ``save_weights`` or ``save`` (ours or Keras'): by position in the layer list, or
+        ``by_name`` (only layers whose names match are loaded - the transfer-learning form)."""
+        from ..io.keras_h5 import load_weights
+        load_weights(self, filepath, by_name=by_name, skip_mismatch=skip_mismatch)
 
     def summary(self, print_fn=print):
         print_fn('Model: "%s"' % self.name)
@@ -827,6 +893,17 @@ class Sequential(Model):
         self._tail = layer(self._tail)
         self._stack.append(layer)
         self._init_graph([self._stack[0].outputs[0]], [self._tail])
+
+    def pop(self):
+        """Removes the last layer (``keras.Sequential.pop``): the usual first step of re-heading a trained stack."""
+        if not self.layers_without_input:
+            raise TypeError("There are no layers in the model.")
+        layer = self._stack.pop()
+        self._tail = layer.inbound.pop()[0]
+        layer.outputs.pop()
+        self._init_graph([self._stack[0].outputs[0]], [self._tail])
+        self._engine = self._infer_engine = self._torch_step = self._wopt_cache = None
+        return layer
 
     @property
     def layers_without_input(self):

@@ -22,7 +22,9 @@ class Optimizer:
     _class_name = 'Optimizer'
     _defaults = {}
 
-    def __init__(self, **kwargs):
+    def __init__(self, learning_rate=None, **kwargs):
+        if learning_rate is not None:  # Keras takes the rate as the first positional argument: Adam(1e-3)
+            kwargs['learning_rate'] = learning_rate
         if 'lr' in kwargs:  # legacy Keras spelling, used by the reference tests (SGD(lr=0.1))
             kwargs['learning_rate'] = kwargs.pop('lr')
         self.clipnorm = kwargs.pop('clipnorm', None)
@@ -34,6 +36,9 @@ class Optimizer:
             raise TypeError("Unexpected keyword argument(s) for %s: %s" % (self._class_name, sorted(unknown)))
         cfg.update(kwargs)
         cfg.setdefault('name', self._class_name)
+        if isinstance(cfg['learning_rate'], dict):  # a serialised schedule ({"class_name": "ExponentialDecay", ...})
+            from . import schedules
+            cfg['learning_rate'] = schedules.deserialize(cfg['learning_rate'])
         self._config = cfg
         self.iterations = 0
         self._slots = {}
@@ -52,7 +57,7 @@ class Optimizer:
 
     @learning_rate.setter
     def learning_rate(self, value):
-        value = float(value)
+        value = value if callable(value) else float(value)
         if value != self._config['learning_rate']:
             self._config['learning_rate'] = value
             self._hyper_version = self.__dict__.get('_hyper_version', 0) + 1
@@ -62,6 +67,9 @@ class Optimizer:
     def get_config(self):
         cfg = {'name': self._config['name']}
         cfg.update({k: v for k, v in self._config.items() if k != 'name'})
+        if self.schedule is not None:
+            from . import schedules
+            cfg['learning_rate'] = schedules.serialize(self.schedule)
         for k in ('clipnorm', 'clipvalue', 'global_clipnorm'):
             if getattr(self, k) is not None:
                 cfg[k] = getattr(self, k)
@@ -72,9 +80,19 @@ class Optimizer:
         return cls(**copy.deepcopy(config))
 
     # ------------------------------------------------------------------- state
+    @property
+    def schedule(self):
+        """The learning-rate schedule (``models/schedules.py``), or None for a plain number."""
+        lr = self._config['learning_rate']
+        return lr if callable(lr) else None
+
+    def _base_lr(self):
+        lr = self._config['learning_rate']
+        return float(lr(self.iterations)) if callable(lr) else float(lr)
+
     def _lr_t(self):
         decay = self._config.get('decay', 0.0) or 0.0
-        lr = float(self._config['learning_rate'])
+        lr = self._base_lr()
         return lr / (1.0 + decay * self.iterations) if decay else lr
 
     def _slot(self, idx, name, like, init=0.0):
@@ -224,8 +242,8 @@ class Nadam(Optimizer):
     _class_name = 'Nadam'
     _defaults = {'learning_rate': 0.001, 'decay': 0.004, 'beta_1': 0.9, 'beta_2': 0.999, 'epsilon': 1e-07}
 
-    def __init__(self, **kwargs):
-        super().__init__(**kwargs)
+    def __init__(self, *args, **kwargs):
+        super().__init__(*args, **kwargs)
         self._m_schedule = 1.0
 
     def reset_state(self):
@@ -233,7 +251,7 @@ class Nadam(Optimizer):
         self._m_schedule = 1.0
 
     def _lr_t(self):  # Nadam's `decay` is the momentum-schedule decay, not an lr decay
-        return float(self._config['learning_rate'])
+        return self._base_lr()
 
     def _apply(self, params, grads):
         t = self.iterations + 1

@@ -72,8 +72,8 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
         return None
     if len(partitions) != rt.world_size or len(mine) != 1:
         return None
-    if train_config.get('callbacks'):
-        return None  # callbacks run inside Model.fit: the generic worker path calls it with them
+    if any(train_config.get(k) is not None and train_config.get(k) != [] for k in ('callbacks', 'class_weight', 'sample_weight')):
+        return None  # callbacks and row weights belong to Model.fit: the generic worker path calls it with them
     master = spark_model.master_network
     if master.device != rt.device:
         master.to(rt.device)

@@ -34,8 +34,8 @@ def try_fit(spark_model, rt, partitions, mine, train_config, sync_rounds):
         return None
     if len(partitions) != rt.world_size or len(mine) != 1:
         return None
-    if train_config.get('callbacks'):
-        return None  # callbacks run inside Model.fit: the generic worker path calls it with them
+    if any(train_config.get(k) is not None and train_config.get(k) != [] for k in ('callbacks', 'class_weight', 'sample_weight')):
+        return None  # callbacks and row weights belong to Model.fit: the generic worker path calls it with them
     per_batch = rt.distributed and spark_model.frequency == 'batch' and sync_rounds != 'fit'
     if per_batch:
         bs = int(train_config.get('batch_size') or 32)

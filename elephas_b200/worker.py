@@ -196,7 +196,7 @@ class AsynchronousSparkWorker(_WorkerBase):
 
         from .parameter.client import DeviceClient
         # callbacks run inside Model.fit: with them the worker takes the generic pull -> fit -> push loop below
-        plain = not self.train_config.get('callbacks')
+        plain = not any(self.train_config.get(k) for k in ('callbacks', 'class_weight'))
         eng = model._native_engine() if model.device.type == 'cuda' and plain else None
         if eng is not None and isinstance(self.client, DeviceClient):
             self._train_against_device_ps(model, eng, x_train, y_train, epochs, batch_size, trainable)

@@ -1,0 +1,138 @@
+"""The smaller corners of the ``keras.Model`` surface: row weights, ``*_on_batch``, ``get_layer``, ``pop``, weight files."""
+import numpy as np
+import pytest
+import torch
+
+from elephas_b200.models import Dense, Sequential, load_model
+from elephas_b200.models.optimizers import SGD
+
+
+def _xy(n=96, seed=0):
+    rng = np.random.default_rng(seed)
+    x = rng.standard_normal((n, 6)).astype(np.float32)
+    y = np.eye(3, dtype=np.float32)[rng.integers(0, 3, n)]
+    return x, y
+
+
+def _model(lr=0.1, names=('a', 'b')):
+    m = Sequential([Dense(8, activation='relu', input_shape=(6,), name=names[0]), Dense(3, activation='softmax', name=names[1])])
+    m.compile(SGD(learning_rate=lr), 'categorical_crossentropy', ['acc'])
+    return m
+
+
+def _oracle_step(weights, x, y, w, lr):
+    ws = [torch.tensor(v, requires_grad=True) for v in weights]
+    h = torch.relu(torch.tensor(x) @ ws[0] + ws[1])
+    p = torch.softmax(h @ ws[2] + ws[3], dim=1)
+    per_row = -(torch.tensor(y) * torch.log(p)).sum(1)
+    loss = (per_row * torch.tensor(w)).sum() / len(x)
+    loss.backward()
+    return float(loss.detach()), [(v - lr * v.grad).detach().numpy() for v in ws]
+
+
+def test_sample_and_class_weights_scale_the_rows():
+    x, y = _xy()
+    rng = np.random.default_rng(1)
+    sw = rng.uniform(0.0, 2.0, len(x)).astype(np.float32)
+    cw = {0: 1.0, 1: 3.0, 2: 0.5}
+    m = _model()
+    w0 = m.get_weights()
+    rows = sw * np.array([cw[int(k)] for k in y.argmax(1)], dtype=np.float32)
+    loss, after = _oracle_step(w0, x, y, rows, 0.1)
+    got = m.train_on_batch(x, y, sample_weight=sw, class_weight=cw, return_dict=True)
+    assert got['loss'] == pytest.approx(loss, rel=1e-5) and 0.0 <= got['acc'] <= 1.0
+    for a, b in zip(m.get_weights(), after):
+        np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-6)
+    # through fit: one batch covering every row, no shuffling, is the same step
+    m2 = _model()
+    m2.set_weights(w0)
+    h = m2.fit(x, y, batch_size=len(x), epochs=1, shuffle=False, sample_weight=sw, class_weight=cw)
+    assert h.history['loss'][0] == pytest.approx(loss, rel=1e-5)
+    for a, b in zip(m2.get_weights(), after):
+        np.testing.assert_allclose(a, b, rtol=1e-4, atol=1e-6)
+    # zero weights: nothing moves; integer labels are read as class indices
+    m3 = _model()
+    m3.set_weights(w0)
+    m3.fit(x, y, batch_size=32, epochs=1, sample_weight=np.zeros(len(x)))
+    for a, b in zip(m3.get_weights(), w0):
+        np.testing.assert_array_equal(a, b)
+    with pytest.raises(ValueError):
+        m3.fit(x, y, sample_weight=np.ones(3))
+
+
+def test_class_weight_with_integer_labels_and_validation_split():
+    from elephas_b200.models.model import _row_weights
+    w = _row_weights(np.array([0, 2, 1, 2]), None, {2: 4.0})
+    np.testing.assert_array_equal(w, [1.0, 4.0, 1.0, 4.0])
+    assert _row_weights(np.zeros(3), None, None) is None
+    x, y = _xy()
+    h = _model().fit(x, y, batch_size=16, epochs=2, validation_split=0.25, class_weight={0: 2.0})
+    assert len(h.history['val_loss']) == 2
+
+
+def test_on_batch_calls_and_return_dict():
+    x, y = _xy(32)
+    m = _model()
+    before = m.get_weights()
+    t = m.test_on_batch(x, y, return_dict=True)
+    assert set(t) == {'loss', 'acc'}
+    for a, b in zip(m.get_weights(), before):
+        np.testing.assert_array_equal(a, b)
+    e = m.evaluate(x, y, batch_size=8, return_dict=True)
+    assert e['loss'] == pytest.approx(t['loss'], rel=1e-5)
+    np.testing.assert_allclose(m.predict_on_batch(x), m.predict(x), rtol=1e-6)
+
+
+def test_get_layer_and_pop():
+    m = _model()
+    assert m.get_layer('a').units == 8 and m.get_layer(index=-1).name == 'b'
+    with pytest.raises(ValueError):
+        m.get_layer('c')
+    with pytest.raises(ValueError):
+        m.get_layer(index=9)
+    x, _ = _xy(8)
+    hidden = m.get_layer('a')
+    last = m.pop()
+    assert last.name == 'b' and m.output_shape == (None, 8)
+    np.testing.assert_allclose(m.predict(x), np.maximum(x @ m.get_weights()[0] + m.get_weights()[1], 0), rtol=1e-5, atol=1e-6)
+    m.add(Dense(2, activation='softmax', name='new_head'))
+    m.compile(SGD(learning_rate=0.1), 'categorical_crossentropy')
+    assert m.output_shape == (None, 2) and m.get_layer('a') is hidden
+    assert m.predict(x).shape == (8, 2)
+    m.pop(), m.pop()
+    with pytest.raises(TypeError):
+        m.pop()
+
+
+def test_weight_files_by_position_and_by_name(tmp_path):
+    x, _ = _xy(8)
+    m = _model()
+    path = str(tmp_path / 'w.h5')
+    m.save_weights(path)
+    from elephas_b200.io import hdf5
+    root = hdf5.load_tree(path)
+    assert 'model_weights' not in root and 'a' in root     # the layout of keras.Model.save_weights
+    other = _model(names=('p', 'q'))
+    other.load_weights(path)                               # by position: the names differ
+    np.testing.assert_allclose(other.predict(x), m.predict(x), rtol=1e-6)
+    # by name: only 'a' exists in both
+    third = Sequential([Dense(8, activation='relu', input_shape=(6,), name='a'), Dense(5, name='head')])
+    head = [w.copy() for w in third.get_weights()[2:]]
+    third.load_weights(path, by_name=True)
+    np.testing.assert_array_equal(third.get_weights()[0], m.get_weights()[0])
+    np.testing.assert_array_equal(third.get_weights()[2], head[0])
+    # a full model file works as a weight file too
+    full = str(tmp_path / 'full.h5')
+    m.save(full)
+    fourth = _model(names=('r', 's'))
+    fourth.load_weights(full)
+    np.testing.assert_allclose(fourth.predict(x), load_model(full).predict(x), rtol=1e-6)
+    # shape mismatches are errors unless asked to skip them by name
+    clash = Sequential([Dense(4, input_shape=(6,), name='a')])
+    with pytest.raises(ValueError):
+        clash.load_weights(path, by_name=True)
+    clash.load_weights(path, by_name=True, skip_mismatch=True)
+    with pytest.raises(ValueError):
+        clash.load_weights(path)
+    with pytest.raises(IOError):
+        m.save_weights(path, overwrite=False)

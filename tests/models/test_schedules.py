@@ -1,0 +1,68 @@
+"""Learning-rate schedules (``models/schedules.py``): values against the closed forms of ``tf.keras.optimizers.schedules``,
+the optimizer config round trip, and the rate an optimizer really applies."""
+import json
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from elephas_b200.models import Dense, Sequential, optimizers, schedules
+
+
+def test_values_match_the_closed_forms():
+    e = schedules.ExponentialDecay(0.1, decay_steps=10, decay_rate=0.5)
+    assert e(0) == pytest.approx(0.1) and e(10) == pytest.approx(0.05) and e(5) == pytest.approx(0.1 * 0.5 ** 0.5)
+    s = schedules.ExponentialDecay(0.1, 10, 0.5, staircase=True)
+    assert s(9) == pytest.approx(0.1) and s(19) == pytest.approx(0.05)
+    i = schedules.InverseTimeDecay(0.1, 10, 0.5)
+    assert i(20) == pytest.approx(0.1 / 2.0)
+    p = schedules.PiecewiseConstantDecay([100, 200], [1.0, 0.5, 0.1])
+    assert [p(0), p(100), p(101), p(200), p(201)] == [1.0, 1.0, 0.5, 0.5, 0.1]
+    with pytest.raises(ValueError):
+        schedules.PiecewiseConstantDecay([1], [1.0])
+    poly = schedules.PolynomialDecay(0.1, 100, end_learning_rate=0.01, power=2.0)
+    assert poly(50) == pytest.approx(0.09 * 0.25 + 0.01) and poly(1000) == pytest.approx(0.01)
+    cyc = schedules.PolynomialDecay(0.1, 100, end_learning_rate=0.01, cycle=True)
+    assert cyc(150) == pytest.approx(0.09 * (1 - 150 / 200) + 0.01)
+    c = schedules.CosineDecay(0.1, 100, alpha=0.1)
+    assert c(0) == pytest.approx(0.1) and c(100) == pytest.approx(0.01) and c(50) == pytest.approx(0.1 * (0.9 * 0.5 + 0.1))
+    r = schedules.CosineDecayRestarts(0.1, 10, t_mul=2.0, m_mul=0.5)
+    assert r(0) == pytest.approx(0.1) and r(10) == pytest.approx(0.05) and r(30) == pytest.approx(0.025)
+    assert r(20) == pytest.approx(0.05 * 0.5 * (1 + math.cos(math.pi * 0.5)))
+    flat = schedules.CosineDecayRestarts(0.1, 10, t_mul=1.0)
+    assert flat(25) == pytest.approx(0.1 * 0.5 * (1 + math.cos(math.pi * 0.5)))
+
+
+def test_optimizer_config_round_trip_and_applied_rate():
+    sched = schedules.ExponentialDecay(0.5, decay_steps=1, decay_rate=0.5)
+    opt = optimizers.SGD(learning_rate=sched)
+    cfg = optimizers.serialize(opt)
+    assert cfg['config']['learning_rate'] == {'class_name': 'ExponentialDecay', 'config': sched.get_config()}
+    json.dumps(cfg)                                           # what travels to the workers is plain JSON
+    back = optimizers.deserialize(cfg)
+    assert isinstance(back.schedule, schedules.ExponentialDecay) and back.schedule.get_config() == sched.get_config()
+    w = torch.zeros(1, requires_grad=True)
+    for expected in (0.5, 0.25, 0.125):                        # gradient 1: the step IS the rate
+        before = float(w.detach())
+        back.apply_gradients([w], [torch.ones(1)])
+        assert before - float(w.detach()) == pytest.approx(expected)
+    with pytest.raises(ValueError):
+        optimizers.SGD(learning_rate={'class_name': 'Sideways', 'config': {}})
+
+
+def test_a_model_with_a_schedule_trains_and_keeps_it_through_json():
+    from elephas_b200.models import model_from_json
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((128, 5)).astype(np.float32)
+    y = (x @ rng.standard_normal((5, 1))).astype(np.float32)
+    m = Sequential([Dense(8, activation='tanh', input_shape=(5,)), Dense(1)])
+    m.compile(optimizers.Adam(learning_rate=schedules.CosineDecay(0.05, 200)), 'mse')
+    h = m.fit(x, y, batch_size=16, epochs=8)
+    assert h.history['loss'][-1] < 0.5 * h.history['loss'][0]
+    assert m.optimizer.iterations == 64
+    from elephas_b200.ops.engine import _optimizer_spec
+    assert _optimizer_spec(m.optimizer) is None and _optimizer_spec(optimizers.Adam(0.01)) is not None
+    clone = model_from_json(m.to_json())
+    clone.compile(optimizers.deserialize(optimizers.serialize(m.optimizer)), 'mse')
+    assert clone.optimizer.schedule(100) == pytest.approx(0.025)

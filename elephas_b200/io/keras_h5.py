@@ -19,11 +19,12 @@ import numpy as np
 
 from . import hdf5
 from ..models import model as _model_mod
+from ..models import losses as _losses
 from ..models import optimizers as _optimizers
 
 
 def _training_config(model):
-    loss = model.loss if isinstance(model.loss, str) else getattr(model.loss, '__name__', None)
+    loss = _losses.serialize(model.loss)
     metrics = [m if isinstance(m, str) else getattr(m, '__name__', str(m))
                for m in (model.compiled_metrics._metrics or [])]
     return {'loss': loss, 'metrics': metrics, 'weighted_metrics': None, 'loss_weights': None,
@@ -186,7 +187,10 @@ def load_model(filepath, custom_objects=None, compile=True):
         tc = json.loads(_text(root.attrs['training_config']))
         loss = tc.get('loss')
         if isinstance(loss, dict):
-            loss = loss.get('config', {}).get('name', loss.get('class_name'))
+            if 'class_name' in loss:
+                loss = _losses.deserialize(loss, custom_objects)
+            else:  # one entry per output name: single-output models only
+                loss = next(iter(loss.values()))
         model.compile(optimizer=_optimizers.deserialize(tc['optimizer_config'], custom_objects), loss=loss,
                       metrics=tc.get('metrics') or None)
         if 'optimizer_weights' in root:

@@ -18,7 +18,9 @@ Read support: everything this module writes, plus the classic layout ``h5py`` pr
 B-tree v1 / local heap, contiguous or compact datasets, fixed- and variable-length string
 attributes through the global heap) - i.e. uncompressed Keras ``.h5`` files written elsewhere.
 """
+import os
 import struct
+import threading
 
 import numpy as np
 
@@ -555,7 +557,20 @@ def have_h5py() -> bool:
 
 
 def save_tree(path, root: Group):
-    """Write ``root`` with h5py when available, otherwise with the built-in writer."""
+    """Write ``root`` with h5py when available, otherwise with the built-in writer. The file appears under its name in one
+    step (written next to it, then renamed): a reader, or a second writer of the same checkpoint path - the workers of one
+    process all run the same ``ModelCheckpoint`` - never sees a half-written file."""
+    path = str(path)
+    tmp = "%s.tmp-%d-%d" % (path, os.getpid(), threading.get_ident())
+    try:
+        _save_tree(tmp, root)
+        os.replace(tmp, path)
+    finally:
+        if os.path.exists(tmp):
+            os.remove(tmp)
+
+
+def _save_tree(path, root: Group):
     if have_h5py():  # pragma: no cover - h5py is absent from the B200 image
         import h5py
 

@@ -105,6 +105,7 @@ class Model:
 
     # ---------------------------------------------------------------- graph
     def _init_graph(self, inputs, outputs):
+        self._wopt_cache = None
         self._inputs = list(inputs) if isinstance(inputs, (list, tuple)) else [inputs]
         self._outputs = list(outputs) if isinstance(outputs, (list, tuple)) else [outputs]
         order, seen = [], set()

@@ -147,3 +147,32 @@ def test_random_trees_round_trip(tmp_path):
             assert np.array_equal(np.asarray(back.attrs[k]), v) and np.asarray(back.attrs[k]).dtype == v.dtype
 
     check()
+
+
+def test_concurrent_writers_of_one_path_leave_a_whole_file(tmp_path):
+    """Several workers checkpointing to one name: every reader finds a complete file, no temporary files stay behind."""
+    import threading
+    path = str(tmp_path / 'shared.h5')
+    trees = []
+    for i in range(4):
+        root = hdf5.Group()
+        root.attrs['writer'] = np.int64(i)
+        root.create_dataset('payload', np.full((256, 64), float(i), dtype=np.float32))
+        trees.append(root)
+    errors = []
+
+    def writer(tree):
+        try:
+            for _ in range(10):
+                hdf5.save_tree(path, tree)
+                back = hdf5.load_tree(path)
+                who = int(np.asarray(back.attrs['writer']))
+                assert np.all(np.asarray(back['payload'].data) == float(who))
+        except Exception as exc:  # noqa: BLE001 - collected for the main thread
+            errors.append(exc)
+
+    threads = [threading.Thread(target=writer, args=(t,)) for t in trees]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+    assert not errors, errors[:1]
+    assert sorted(p.name for p in tmp_path.iterdir()) == ['shared.h5']

@@ -19,7 +19,8 @@ def test_autogen_writes_pages(tmp_path, monkeypatch):
     assert 'eb_gemm_bf16' in (tmp_path / 'c-api.md').read_text()
 
 
-@pytest.mark.parametrize('script', ['mnist_mlp_spark_synchronous.py', 'ml_mlp_regression.py', 'wide_mlp_sync.py', 'cnn_sync.py'])
+@pytest.mark.parametrize('script', ['mnist_mlp_spark_synchronous.py', 'ml_mlp_regression.py', 'wide_mlp_sync.py', 'cnn_sync.py',
+                                    'lstm_callbacks.py'])
 def test_example_runs(script):
     env = dict(os.environ, ELEPHAS_B200_DEVICE='cpu', SPARK_LOCAL_IP='127.0.0.1')
     res = subprocess.run([sys.executable, script], cwd=os.path.join(ROOT, 'examples'), env=env, capture_output=True,

@@ -9,7 +9,7 @@ from .layers import (Activation, Add, AveragePooling2D, BatchNormalization, Conc
                      Reshape, Softmax, ZeroPadding2D)
 from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Bidirectional, Conv1D, Conv2DTranspose,  # noqa: F401
                            DepthwiseConv2D, Dot, Embedding, GaussianNoise, GlobalAveragePooling1D, GlobalMaxPooling1D,
-                           GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Maximum, MaxPooling1D, Minimum, Multiply,
+                           GlobalMaxPooling2D, LayerNormalization, LeakyReLU, Masking, Maximum, MaxPooling1D, Minimum, Multiply,
                            Permute, RepeatVector, SeparableConv2D, SimpleRNN, SpatialDropout1D, SpatialDropout2D,
                            Subtract, TimeDistributed, UpSampling2D)
 from . import callbacks  # noqa: F401

@@ -104,10 +104,18 @@ class GlobalAveragePooling1D(Layer):
         self.keepdims = keepdims
 
     def compute_output_shape(self, input_shape):
-        return (input_shape[0], input_shape[-1])
+        return (input_shape[0], 1, input_shape[-1]) if self.keepdims else (input_shape[0], input_shape[-1])
 
-    def call(self, x, training=False):
-        return x.mean(dim=1)
+    accepts_mask = True
+
+    def compute_mask(self, x, mask):
+        return None
+
+    def call(self, x, training=False, mask=None):
+        if mask is None:
+            return x.mean(dim=1, keepdim=bool(self.keepdims))
+        m = mask.to(x.dtype).unsqueeze(-1)   # mean over the steps that are not masked
+        return (x * m).sum(dim=1, keepdim=bool(self.keepdims)) / m.sum(dim=1, keepdim=bool(self.keepdims)).clamp(min=1.0)
 
     def _extra_config(self):
         return {'data_format': 'channels_last', 'keepdims': self.keepdims}
@@ -216,6 +224,9 @@ class Embedding(Layer):
 
     def call(self, x, training=False):
         return F.embedding(x.long(), self.embeddings)
+
+    def compute_mask(self, x, mask):
+        return (x != 0) if self.mask_zero else None
 
     def _extra_config(self):
         return {'input_dim': self.input_dim, 'output_dim': self.output_dim,
@@ -359,14 +370,36 @@ class _Recurrent(Layer):
                                  self.recurrent_dropout, True)
         return mask_in, mask_rec
 
-    def call(self, x, training=False):
+    accepts_mask = True
+
+    def compute_mask(self, x, mask):
+        return mask if self.return_sequences else None
+
+    def _input_bias(self):
+        return self.bias
+
+    def call(self, x, training=False, mask=None):
+        """``mask`` (``[batch, time]``, from ``Embedding(mask_zero=True)`` / ``Masking``): a masked step leaves the state
+        untouched and repeats the previous output, as Keras does."""
         steps = range(x.shape[1] - 1, -1, -1) if self.go_backwards else range(x.shape[1])
         mask_in, mask_rec = self._masks(x, training)
+        # the input half of every step in ONE product over [batch * time, features]; the loop keeps the recurrent half
+        xz = (x if mask_in is None else x * mask_in.unsqueeze(1)) @ self.kernel
+        bias = self._input_bias()
+        if bias is not None:
+            xz = xz + bias
         state = self._initial_state(x)
+        h = x.new_zeros(x.shape[0], self.units)
         outputs = []
         for t in steps:
-            xt = x[:, t] if mask_in is None else x[:, t] * mask_in
-            h, state = self._step(xt, state, mask_rec)
+            h_new, state_new = self._step(xz[:, t], state, mask_rec)
+            if mask is None:
+                h, state = h_new, state_new
+            else:
+                keep = mask[:, t].reshape(-1, 1).to(torch.bool)
+                h = torch.where(keep, h_new, h)
+                state = tuple(torch.where(keep, n, o) for n, o in zip(state_new, state)) \
+                    if isinstance(state, tuple) else torch.where(keep, state_new, state)
             if self.return_sequences:
                 outputs.append(h)
         return torch.stack(outputs, dim=1) if self.return_sequences else h
@@ -392,11 +425,8 @@ class SimpleRNN(_Recurrent):
     def _initial_state(self, x):
         return x.new_zeros(x.shape[0], self.units)
 
-    def _step(self, xt, h, mask_rec):
-        z = xt @ self.kernel + (h if mask_rec is None else h * mask_rec) @ self.recurrent_kernel
-        if self.bias is not None:
-            z = z + self.bias
-        h = self.activation(z)
+    def _step(self, xz, h, mask_rec):
+        h = self.activation(xz + (h if mask_rec is None else h * mask_rec) @ self.recurrent_kernel)
         return h, h
 
 
@@ -418,11 +448,9 @@ class LSTM(_Recurrent):
     def _initial_state(self, x):
         return (x.new_zeros(x.shape[0], self.units), x.new_zeros(x.shape[0], self.units))
 
-    def _step(self, xt, state, mask_rec):
+    def _step(self, xz, state, mask_rec):
         h, c = state
-        z = xt @ self.kernel + (h if mask_rec is None else h * mask_rec) @ self.recurrent_kernel
-        if self.bias is not None:
-            z = z + self.bias
+        z = xz + (h if mask_rec is None else h * mask_rec) @ self.recurrent_kernel
         i, f, g, o = z.chunk(4, dim=-1)
         i, f, o = self.recurrent_activation(i), self.recurrent_activation(f), self.recurrent_activation(o)
         c = f * c + i * self.activation(g)
@@ -452,20 +480,22 @@ class GRU(_Recurrent):
     def _initial_state(self, x):
         return x.new_zeros(x.shape[0], self.units)
 
-    def _step(self, xt, h, mask_rec):
+    def _input_bias(self):
+        if self.bias is None:
+            return None
+        return self.bias[0] if self.reset_after else self.bias
+
+    def _step(self, xz, h, mask_rec):
         u = self.units
         hm = h if mask_rec is None else h * mask_rec
-        xz = xt @ self.kernel
         if self.reset_after:
             hz = hm @ self.recurrent_kernel
             if self.bias is not None:
-                xz, hz = xz + self.bias[0], hz + self.bias[1]
+                hz = hz + self.bias[1]
             z = self.recurrent_activation(xz[:, :u] + hz[:, :u])
             r = self.recurrent_activation(xz[:, u:2 * u] + hz[:, u:2 * u])
             cand = self.activation(xz[:, 2 * u:] + r * hz[:, 2 * u:])
         else:
-            if self.bias is not None:
-                xz = xz + self.bias
             z = self.recurrent_activation(xz[:, :u] + hm @ self.recurrent_kernel[:, :u])
             r = self.recurrent_activation(xz[:, u:2 * u] + hm @ self.recurrent_kernel[:, u:2 * u])
             cand = self.activation(xz[:, 2 * u:] + (r * hm) @ self.recurrent_kernel[:, 2 * u:])
@@ -888,9 +918,14 @@ class Bidirectional(_Wrapper):
             shape[-1] *= 2
         return tuple(shape)
 
-    def call(self, x, training=False):
-        a = self.forward.call(x, training=training)
-        b = self.backward.call(x, training=training)
+    accepts_mask = True
+
+    def compute_mask(self, x, mask):
+        return mask if self.forward.return_sequences else None
+
+    def call(self, x, training=False, mask=None):
+        a = self.forward.call(x, training=training, mask=mask)
+        b = self.backward.call(x, training=training, mask=mask)
         if self.forward.return_sequences:
             b = b.flip(1)
         if self.merge_mode == 'concat':
@@ -910,7 +945,25 @@ class Bidirectional(_Wrapper):
     from_config = classmethod(TimeDistributed.from_config.__func__)
 
 
-EXTRA_LAYERS = (LeakyReLU, ELU, Multiply, Subtract, Maximum, Minimum, Average, GlobalMaxPooling2D, GlobalAveragePooling1D,
+class Masking(Layer):
+    """Marks the time steps whose features all equal ``mask_value``: they are zeroed here and skipped by the recurrent
+    layers downstream (``Model._forward`` carries the mask along)."""
+
+    def __init__(self, mask_value=0.0, **kwargs):
+        super().__init__(**kwargs)
+        self.mask_value = float(mask_value)
+
+    def compute_mask(self, x, mask):
+        return (x != self.mask_value).any(dim=-1)
+
+    def call(self, x, training=False):
+        return x * self.compute_mask(x, None).unsqueeze(-1).to(x.dtype)
+
+    def _extra_config(self):
+        return {'mask_value': self.mask_value}
+
+
+EXTRA_LAYERS = (Masking, LeakyReLU, ELU, Multiply, Subtract, Maximum, Minimum, Average, GlobalMaxPooling2D, GlobalAveragePooling1D,
                 GlobalMaxPooling1D, MaxPooling1D, AveragePooling1D, LayerNormalization, Embedding, Conv1D, SimpleRNN, LSTM,
                 GRU, DepthwiseConv2D, SeparableConv2D, Conv2DTranspose, UpSampling2D, Permute, RepeatVector,
                 SpatialDropout1D, SpatialDropout2D, GaussianNoise, Dot, TimeDistributed, Bidirectional)

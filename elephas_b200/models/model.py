@@ -25,6 +25,9 @@ from . import metrics as _metrics
 from . import optimizers as _optimizers
 
 _PREDICT_BLOCK = 256
+# layers that hand the mask of their input on unchanged (they keep the [batch, time] axes and look at no neighbours)
+_MASK_TRANSPARENT = frozenset(('Dropout', 'SpatialDropout1D', 'Activation', 'ReLU', 'LeakyReLU', 'ELU', 'Softmax', 'Dense',
+                               'TimeDistributed', 'LayerNormalization', 'BatchNormalization', 'GaussianNoise'))
 KERAS_VERSION = '2.10.0'
 BACKEND = 'tensorflow'
 
@@ -211,6 +214,7 @@ class Model:
         fused, alias = self._fusion_plan() if fuse else ({}, {})
         pools, skipped = self._pool_pad_plan() if fuse else ({}, set())
         self._activity_terms = []
+        masks = {}  # node key -> [batch, time] mask (Embedding(mask_zero=True) / Masking), carried to the recurrent layers
         for t in self._node_order:
             key = (id(t.layer), t.node_index)
             if key in values or key in skipped:
@@ -221,6 +225,8 @@ class Model:
                 continue
             if key in alias:
                 values[key] = values[alias[key]]  # absorbed into the BatchNormalization that produced its input
+                if alias[key] in masks:
+                    masks[key] = masks[alias[key]]
                 continue
             ins = [values[(id(s.layer), s.node_index)] for s in t.layer.inbound[t.node_index]]
             if key in fused:
@@ -228,7 +234,20 @@ class Model:
                 values[key] = t.layer.call(ins[0], training=training, fuse_relu=relu,
                                            residual=values[other] if other is not None else None)
                 continue
-            values[key] = t.layer.call(ins[0] if len(ins) == 1 else ins, training=training)
+            srcs = t.layer.inbound[t.node_index]
+            mask = masks.get((id(srcs[0].layer), srcs[0].node_index)) if len(srcs) == 1 else None
+            if mask is not None and getattr(t.layer, 'accepts_mask', False):
+                values[key] = t.layer.call(ins[0], training=training, mask=mask)
+            else:
+                values[key] = t.layer.call(ins[0] if len(ins) == 1 else ins, training=training)
+            if len(srcs) == 1:
+                compute = getattr(t.layer, 'compute_mask', None)
+                if compute is not None:
+                    mask = compute(ins[0], mask)
+                elif type(t.layer).__name__ not in _MASK_TRANSPARENT:
+                    mask = None
+                if mask is not None:
+                    masks[key] = mask
             if training and t.layer.activity_regularizer is not None:
                 out = values[key]
                 self._activity_terms.append(t.layer.activity_regularizer(out) / out.shape[0])

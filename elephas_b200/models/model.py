@@ -869,12 +869,33 @@ class Model:
         from ..io.keras_h5 import load_weights
         load_weights(self, filepath, by_name=by_name, skip_mismatch=skip_mismatch)
 
-    def summary(self, print_fn=print):
+    def summary(self, line_length=None, positions=None, print_fn=print):
+        """The table of ``keras.Model.summary``: layer (type), output shape, parameter count, totals."""
+        width = int(line_length or 65)
+        cols = [int(width * p) for p in (positions or (0.45, 0.85, 1.0))]
+        def row(cells):  # noqa: E306
+            line = ''
+            for text, end in zip(cells, cols):
+                line = (line + str(text))[:end - 1].ljust(end)
+            return line.rstrip()
         print_fn('Model: "%s"' % self.name)
+        print_fn('_' * width)
+        print_fn(row(('Layer (type)', 'Output Shape', 'Param #')))
+        print_fn('=' * width)
+        trainable = 0
         for layer in self.layers:
-            print_fn("  %-28s %-20s params=%d" % (layer.name, type(layer).__name__,
-                                                  sum(w.numel() for w in layer.weights)))
-        print_fn("Total params: %d" % self.count_params())
+            shape = layer.outputs[-1].shape if layer.outputs else getattr(layer, 'batch_input_shape', None)
+            if isinstance(layer, L.InputLayer):
+                shape = [tuple(shape)]
+            count = sum(w.numel() for w in layer.weights)
+            trainable += sum(w.numel() for w in layer.trainable_weights)
+            print_fn(row(('%s (%s)' % (layer.name, type(layer).__name__), shape, count)))
+        total = self.count_params()
+        print_fn('=' * width)
+        print_fn('Total params: {:,}'.format(total))
+        print_fn('Trainable params: {:,}'.format(trainable))
+        print_fn('Non-trainable params: {:,}'.format(total - trainable))
+        print_fn('_' * width)
 
 
 class Sequential(Model):

@@ -136,3 +136,14 @@ def test_weight_files_by_position_and_by_name(tmp_path):
         clash.load_weights(path)
     with pytest.raises(IOError):
         m.save_weights(path, overwrite=False)
+
+
+def test_summary_lists_shapes_and_parameter_totals():
+    from elephas_b200.models import BatchNormalization
+    m = Sequential([Dense(8, input_shape=(4,), name='d0'), BatchNormalization(name='bn'), Dense(2, name='d1')])
+    lines = []
+    m.summary(print_fn=lines.append)
+    text = '\n'.join(lines)
+    assert 'd0 (Dense)' in text and '(None, 8)' in text and 'bn (BatchNormalization)' in text
+    assert 'Total params: 90' in text and 'Trainable params: 74' in text and 'Non-trainable params: 16' in text
+    assert all(len(line) <= 65 for line in lines)

@@ -738,6 +738,7 @@ class Model:
         for epoch in range(initial_epoch, epochs):
             cbs.on_epoch_begin(epoch)
             self._sync_hyper_parameters()
+            self._reset_metrics()
             order = torch.randperm(n, device=self._device) if shuffle else torch.arange(n, device=self._device)
             sums = [0.0] * len(names)
             te = self._torch_engine() if wt is None else None
@@ -760,6 +761,7 @@ class Model:
                     sums[i] += v * rows
                 self.optimizer.iterations = int(te.step.item())
             logs = {k: (s / n if n else 0.0) for k, s in zip(names, sums)}
+            logs.update(self._stateful_results())
             if x_val is not None and len(x_val):
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
                 val = val if isinstance(val, list) else [val]
@@ -840,6 +842,7 @@ class Model:
             xt = xt.unsqueeze(-1)
         n = xt.shape[0]
         sums = [0.0] * len(self.metrics_names)
+        self._reset_metrics()
         step = max(batch_size, 8192)
         self._tune_cpu_threads(min(step, max(n, 1)))
         for start in range(0, n, step):
@@ -851,7 +854,18 @@ class Model:
             for i, v in enumerate(vals):
                 sums[i] += float(v.double().sum())
         stats = [s / n if n else 0.0 for s in sums]
+        final = self._stateful_results()
+        stats = [final.get(name, v) for name, v in zip(self.metrics_names, stats)]
         return stats if len(stats) > 1 else stats[0]
+
+    def _reset_metrics(self):
+        for _, fn in self._metric_fns:
+            if _metrics.is_stateful(fn):
+                fn.reset_state()
+
+    def _stateful_results(self):
+        """``{name: result}`` of the metrics that accumulate counts instead of averaging rows (``metrics.Metric``)."""
+        return {name: fn.result() for name, fn in self._metric_fns if _metrics.is_stateful(fn)}
 
     # ----------------------------------------------------------------- io
     def save(self, filepath, overwrite=True, include_optimizer=True):

@@ -130,8 +130,8 @@ def maybe_create(model):
     """A :class:`CpuMlpStep` for a compiled Dense chain on the CPU, or None (autograd path)."""
     if not enabled() or model.device.type != 'cpu' or not getattr(model, '_compiled', False):
         return None
-    if model.has_weight_options():
-        return None  # penalties and constraints live on the autograd path
+    if model.has_weight_options() or any(getattr(fn, 'stateful', False) for _, fn in model._metric_fns):
+        return None  # penalties, constraints and count-based metrics live on the autograd path
     from . import engine as _engine  # (only its pure-Python plan builder is used: no native library needed)
     try:
         plan = _engine._plan(model)

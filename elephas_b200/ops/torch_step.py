@@ -38,6 +38,8 @@ def maybe_create(model):
     params = model.trainable_weights
     if kind is None or not params or any(p.dtype != torch.float32 for p in params) or len(model._metric_fns) > 4:
         return None
+    if any(getattr(fn, 'stateful', False) for _, fn in model._metric_fns):
+        return None  # count-based metrics (precision, AUC, ...) keep their state on the host
     from ..utils import tracing
     with tracing.span('torch_step/create'):
         return TorchStepEngine(model, kind)

@@ -56,6 +56,18 @@ def _row_weights(y, sample_weight, class_weight):
     return w
 
 
+class _Multi(list):
+    """The arrays (or tensors) of a multi-input model: ``fit([xa, xb], y)``. Sliced and indexed together."""
+
+
+def _rows(x):
+    return len(x[0]) if isinstance(x, _Multi) else len(x)
+
+
+def _take(x, idx):
+    return _Multi(a[idx] for a in x) if isinstance(x, _Multi) else x[idx]
+
+
 class History:
     """``History.history`` maps metric name -> list of per-epoch values (Keras semantics)."""
 
@@ -423,6 +435,8 @@ class Model:
         """Graph-captured torch step (flat weights + native optimizer kernel) for models without a native engine."""
         if self._device.type != 'cuda' or not self._compiled or getattr(self, '_torch_engine_failed', False):
             return None
+        if len(self._inputs) != 1 or len(self._outputs) != 1:
+            return None
         te = getattr(self, '_torch_step', None)
         key = (self._device, id(self.optimizer))
         if te is not None and (getattr(self, '_torch_step_key', None) != key or not te.still_valid()):
@@ -592,6 +606,7 @@ class Model:
         self._compute_dtype = dtype
 
     def _autocast(self, xb):
+        xb = xb[0] if isinstance(xb, _Multi) else xb
         on = getattr(self, '_compute_dtype', 'float32') == 'bfloat16' and xb.is_cuda
         return torch.autocast('cuda', dtype=torch.bfloat16, enabled=on)
 
@@ -640,6 +655,29 @@ class Model:
             from ..utils import cpu_threads
             cpu_threads.tune_for(self, rows)
 
+    def _host_x(self, x):
+        """The ``x`` argument of fit / evaluate / predict: one array, or - for a model with several inputs - a list of
+        arrays (or a dict keyed by input-layer name) in the order of ``Model(inputs=[...])``."""
+        if len(self._inputs) == 1:
+            if isinstance(x, (list, tuple)) and len(x) == 1 and isinstance(x[0], (np.ndarray, torch.Tensor)) \
+                    and x[0].ndim == len(self._inputs[0].shape):
+                x = x[0]   # Keras also takes [array] for the single input
+            return x if isinstance(x, torch.Tensor) else np.asarray(x)
+        if isinstance(x, dict):
+            x = [x[t.layer.name] for t in self._inputs]
+        if not isinstance(x, (list, tuple)) or len(x) != len(self._inputs):
+            raise ValueError("this model has %d inputs: pass a list of %d arrays" % (len(self._inputs), len(self._inputs)))
+        arrays = _Multi(a if isinstance(a, torch.Tensor) else np.asarray(a) for a in x)
+        if len({len(a) for a in arrays}) != 1:
+            raise ValueError("the inputs have different numbers of rows: %s" % [len(a) for a in arrays])
+        return arrays
+
+    def _device_x(self, x):
+        if isinstance(x, _Multi):
+            return _Multi(_as_tensor(a, self._device) for a in x)
+        xt = _as_tensor(x, self._device)
+        return xt.unsqueeze(-1) if xt.dim() == 1 else xt
+
     def train_on_batch(self, x, y, sample_weight=None, class_weight=None, return_dict=False, **kwargs):
         self._require_compiled()
         row_weight = _row_weights(y, sample_weight, class_weight)
@@ -647,11 +685,9 @@ class Model:
         if eng is not None:
             stats = eng.train_on_batch(x, y)
         else:
-            xb = _as_tensor(x, self._device)
+            xb = self._device_x(self._host_x(x))
             yb = _as_tensor(y, self._device)
-            if xb.dim() == 1:
-                xb = xb.unsqueeze(-1)
-            self._tune_cpu_threads(len(xb))
+            self._tune_cpu_threads(_rows(xb))
             te = self._torch_engine() if row_weight is None else None
             if te is not None:
                 te.stats.zero_()
@@ -667,10 +703,10 @@ class Model:
 
     def test_on_batch(self, x, y, return_dict=False, **kwargs):
         """Loss and metrics of one batch, no update."""
-        return self.evaluate(x, y, batch_size=max(len(x), 1), return_dict=return_dict)
+        return self.evaluate(x, y, batch_size=max(len(y), 1), return_dict=return_dict)
 
     def predict_on_batch(self, x):
-        return self.predict(x, batch_size=max(len(x), 1))
+        return self.predict(x)
 
     def get_layer(self, name=None, index=None):
         if index is not None:
@@ -689,21 +725,21 @@ class Model:
         if 'nb_epoch' in kwargs:
             epochs = kwargs.pop('nb_epoch')
         batch_size = int(batch_size or 32)
-        x = np.asarray(x) if not isinstance(x, torch.Tensor) else x
+        x = self._host_x(x)
         y = np.asarray(y) if not isinstance(y, torch.Tensor) else y
-        n_total = len(x)
+        n_total = _rows(x)
         row_weight = _row_weights(y, sample_weight, class_weight)
         x_val = y_val = None
         if validation_data is not None:
             x_val, y_val = validation_data[0], validation_data[1]
         elif validation_split and 0.0 < validation_split < 1.0:
             split_at = int(n_total * (1.0 - validation_split))
-            x, x_val = x[:split_at], x[split_at:]
+            x, x_val = _take(x, slice(None, split_at)), _take(x, slice(split_at, None))
             y, y_val = y[:split_at], y[split_at:]
             row_weight = row_weight[:split_at] if row_weight is not None else None
         history = History()
         from .callbacks import CallbackList
-        cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': len(x), 'verbose': verbose})
+        cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': _rows(x), 'verbose': verbose})
         self.stop_training = False
         # weighted rows: the loss of the fused engines has no weight operand, the autograd step takes them
         eng = self._native_engine() if row_weight is None else None
@@ -728,11 +764,9 @@ class Model:
             cbs.on_train_end()
             return history
         self._tune_cpu_threads(batch_size)
-        xt = _as_tensor(x, self._device)
+        xt = self._device_x(x)
         yt = _as_tensor(y, self._device)
-        if xt.dim() == 1:
-            xt = xt.unsqueeze(-1)
-        n = xt.shape[0]
+        n = _rows(xt)
         wt = torch.as_tensor(row_weight, dtype=torch.float32, device=self._device) if row_weight is not None else None
         names = self.metrics_names
         for epoch in range(initial_epoch, epochs):
@@ -751,7 +785,7 @@ class Model:
                     graphed_rows += len(idx)  # loss / metric sums stay on the device until the epoch ends
                     continue
                 te = None
-                stats = self._torch_train_step(xt[idx], yt[idx], wt[idx] if wt is not None else None)
+                stats = self._torch_train_step(_take(xt, idx), yt[idx], wt[idx] if wt is not None else None)
                 for i, s in enumerate(stats):
                     sums[i] += s * len(idx)
             if graphed_rows:
@@ -762,7 +796,7 @@ class Model:
                 self.optimizer.iterations = int(te.step.item())
             logs = {k: (s / n if n else 0.0) for k, s in zip(names, sums)}
             logs.update(self._stateful_results())
-            if x_val is not None and len(x_val):
+            if x_val is not None and len(y_val):
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
                 val = val if isinstance(val, list) else [val]
                 logs.update({'val_' + k: v for k, v in zip(names, val)})
@@ -796,9 +830,9 @@ class Model:
             eng = _engine_mod.maybe_create_inference(self)
         if eng is not None:
             return eng.predict(x)
-        xt = _as_tensor(x, self._device)
-        if xt.dim() == 1:
-            xt = xt.unsqueeze(-1)
+        xt = self._device_x(self._host_x(x))
+        if isinstance(xt, _Multi):
+            return self._predict_multi(xt)
         self._tune_cpu_threads(_PREDICT_BLOCK)
         outs = []
         # Fixed-size row blocks (the last one zero-padded): every GEMM the library sees has the same
@@ -821,6 +855,21 @@ class Model:
             return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
         return torch.cat(outs, dim=0).cpu().numpy()
 
+    def _predict_multi(self, xt):
+        """Several inputs: the same fixed row blocks as above, every input cut and padded alike."""
+        outs, block, n = [], _PREDICT_BLOCK, _rows(xt)
+        for start in range(0, n, block):
+            xb = _take(xt, slice(start, start + block))
+            rows = _rows(xb)
+            if rows < block:
+                xb = _Multi(torch.cat([a, a.new_zeros((block - rows,) + tuple(a.shape[1:]))], dim=0) for a in xb)
+            with self._autocast(xb):
+                o = self(xb, training=False)
+            outs.append(o.float()[:rows])
+        if not outs:
+            return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
+        return torch.cat(outs, dim=0).cpu().numpy()
+
     @torch.no_grad()
     def evaluate(self, x=None, y=None, batch_size=None, verbose=0, return_dict=False, **kwargs):
         stats = self._evaluate(x, y, batch_size)
@@ -836,17 +885,15 @@ class Model:
         if eng is not None:
             stats = eng.evaluate(x, y)
             return stats if len(stats) > 1 else stats[0]
-        xt = _as_tensor(x, self._device)
+        xt = self._device_x(self._host_x(x))
         yt = _as_tensor(y, self._device)
-        if xt.dim() == 1:
-            xt = xt.unsqueeze(-1)
-        n = xt.shape[0]
+        n = _rows(xt)
         sums = [0.0] * len(self.metrics_names)
         self._reset_metrics()
         step = max(batch_size, 8192)
         self._tune_cpu_threads(min(step, max(n, 1)))
         for start in range(0, n, step):
-            xb, yb = xt[start:start + step], yt[start:start + step]
+            xb, yb = _take(xt, slice(start, start + step)), yt[start:start + step]
             with self._autocast(xb):
                 out = self(xb, training=False)
             out = out.float()

@@ -1,0 +1,109 @@
+"""Third batch of layers (``models/layers_more.py``): values against torch oracles, shapes, JSON round trips."""
+import json
+
+import numpy as np
+import pytest
+import torch
+
+from elephas_b200.models import (AlphaDropout, Attention, Cropping1D, Cropping2D, Dense, Flatten, GaussianDropout,
+                                 GlobalAveragePooling1D, Input, Lambda, LayerNormalization, Model, MultiHeadAttention,
+                                 PReLU, Rescaling, Sequential, ThresholdedReLU, UpSampling1D, ZeroPadding1D, Add,
+                                 model_from_json)
+from elephas_b200.models.optimizers import Adam
+
+
+def _double_plus(x, shift=0.0):
+    return 2.0 * x + shift
+
+
+def test_lambda_travels_by_name_through_custom_objects():
+    m = Sequential([Dense(3, input_shape=(4,)), Lambda(_double_plus, arguments={'shift': 1.0}), Dense(2)])
+    x = np.random.default_rng(0).standard_normal((5, 4)).astype(np.float32)
+    cfg = [l for l in json.loads(m.to_json())['config']['layers'] if l['class_name'] == 'Lambda'][0]['config']
+    assert cfg['function'] == '_double_plus' and cfg['arguments'] == {'shift': 1.0}
+    with pytest.raises(ValueError):
+        model_from_json(m.to_json())
+    back = model_from_json(m.to_json(), custom_objects={'_double_plus': _double_plus})
+    back.set_weights(m.get_weights())
+    np.testing.assert_allclose(back.predict(x), m.predict(x), rtol=1e-6)
+    w = m.get_weights()
+    np.testing.assert_allclose(m.predict(x), (2.0 * (x @ w[0] + w[1]) + 1.0) @ w[2] + w[3], rtol=1e-5, atol=1e-6)
+    # a function that changes the shape: the output shape is found by probing
+    s = Sequential([Lambda(lambda t: t.sum(dim=1, keepdim=True), input_shape=(4,)), Dense(1)])
+    assert s.output_shape == (None, 1) and s.layers[-1].kernel.shape == (1, 1)
+
+
+def test_activations_and_noise_layers():
+    x = torch.randn(64, 6)
+    p = PReLU(alpha_initializer={'class_name': 'Constant', 'config': {'value': 0.25}})
+    np.testing.assert_allclose(p(x).detach().numpy(), torch.nn.functional.prelu(x, torch.tensor(0.25)).numpy(), rtol=1e-6)
+    assert p.alpha.shape == (6,)
+    shared = PReLU(shared_axes=[1, 2])
+    shared(torch.randn(2, 5, 5, 3))
+    assert shared.alpha.shape == (1, 1, 3)
+    t = ThresholdedReLU(theta=0.5)(x)
+    np.testing.assert_array_equal(t.numpy(), np.where(x.numpy() > 0.5, x.numpy(), 0.0))
+    big = torch.nn.functional.selu(torch.randn(200000))
+    torch.manual_seed(0)
+    dropped = AlphaDropout(0.3).call(big, training=True)
+    assert float(dropped.mean()) == pytest.approx(float(big.mean()), abs=0.02)
+    assert float(dropped.std()) == pytest.approx(float(big.std()), rel=0.03)
+    assert AlphaDropout(0.3).call(big, training=False) is big
+    noisy = GaussianDropout(0.2).call(torch.ones(200000), training=True)
+    assert float(noisy.mean()) == pytest.approx(1.0, abs=0.01) and float(noisy.var()) == pytest.approx(0.25, rel=0.05)
+
+
+def test_shape_layers():
+    x = torch.arange(2 * 5 * 3, dtype=torch.float32).reshape(2, 5, 3)
+    assert ZeroPadding1D((1, 2))(x).shape == (2, 8, 3) and float(ZeroPadding1D(1)(x)[0, 0].abs().sum()) == 0.0
+    np.testing.assert_array_equal(Cropping1D((1, 2))(x).numpy(), x[:, 1:3].numpy())
+    np.testing.assert_array_equal(UpSampling1D(2)(x)[:, :4].numpy(), x[:, [0, 0, 1, 1]].numpy())
+    img = torch.randn(2, 8, 9, 3)
+    np.testing.assert_array_equal(Cropping2D(((1, 2), (3, 0)))(img).numpy(), img[:, 1:6, 3:].numpy())
+    assert Cropping2D(2).compute_output_shape((None, 8, 9, 3)) == (None, 4, 5, 3)
+    np.testing.assert_allclose(Rescaling(1 / 255.0, offset=-0.5)(img).numpy(), img.numpy() / 255.0 - 0.5, rtol=1e-6)
+
+
+def test_attention_layers_match_torch():
+    torch.manual_seed(1)
+    q, v, k = torch.randn(3, 4, 8), torch.randn(3, 6, 8), torch.randn(3, 6, 8)
+    out = Attention()([q, v, k])
+    ref = torch.softmax(q @ k.transpose(1, 2), dim=-1) @ v
+    np.testing.assert_allclose(out.numpy(), ref.numpy(), rtol=1e-5, atol=1e-6)
+    causal = Attention(causal=True, use_scale=True)([q[:, :4], v[:, :4]])
+    assert causal.shape == (3, 4, 8)
+    np.testing.assert_allclose(causal[:, 0].detach().numpy(), v[:, 0].numpy(), rtol=1e-5, atol=1e-6)   # step 0 sees only itself
+
+    heads, key_dim, dim = 2, 4, 8
+    mha = MultiHeadAttention(heads, key_dim)
+    got = mha(q, v)                                # query from q, keys and values from v
+    assert [tuple(w.shape) for w in mha.weights] == [(8, 2, 4), (2, 4), (8, 2, 4), (2, 4), (8, 2, 4), (2, 4), (2, 4, 8), (8,)]
+    ref = torch.nn.MultiheadAttention(dim, heads, batch_first=True)
+    with torch.no_grad():                          # the same weights in torch's packed layout
+        packed = torch.cat([w.reshape(dim, heads * key_dim).t() for w in (mha.wq, mha.wk, mha.wv)], dim=0)
+        ref.in_proj_weight.copy_(packed)
+        ref.in_proj_bias.copy_(torch.cat([b.reshape(-1) for b in (mha.bq, mha.bk, mha.bv)]))
+        ref.out_proj.weight.copy_(mha.wo.reshape(heads * key_dim, dim).t())
+        ref.out_proj.bias.copy_(mha.bo)
+    want, _ = ref(q, v, v)
+    np.testing.assert_allclose(got.detach().numpy(), want.detach().numpy(), rtol=1e-4, atol=1e-5)
+
+
+def test_a_small_transformer_block_trains_and_round_trips():
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((256, 6, 8)).astype(np.float32)
+    y = np.eye(2, dtype=np.float32)[(x[:, :, 0].max(axis=1) > 1.0).astype(int)]
+    torch.manual_seed(0)
+    inp = Input(shape=(6, 8))
+    att = MultiHeadAttention(2, 4, name='mha')([inp, inp])
+    h = LayerNormalization()(Add()([inp, att]))
+    out = Dense(2, activation='softmax')(GlobalAveragePooling1D()(Dense(16, activation='relu')(h)))
+    m = Model(inputs=inp, outputs=out)
+    m.compile(Adam(learning_rate=0.01), 'categorical_crossentropy', ['acc'])
+    hist = m.fit(x, y, batch_size=32, epochs=15)
+    assert hist.history['loss'][-1] < 0.8 * hist.history['loss'][0]
+    back = model_from_json(m.to_json())
+    back.set_weights(m.get_weights())
+    np.testing.assert_allclose(back.predict(x[:16]), m.predict(x[:16]), rtol=1e-5, atol=1e-6)
+    names = [n for n in back.get_layer('mha').weight_names()]
+    assert names[0] == 'mha/query/kernel:0' and names[-1] == 'mha/attention_output/bias:0'

@@ -160,6 +160,7 @@ class Layer:
         # `<weight>_regularizer`, `<weight>_constraint`, `activity_regularizer`: every layer takes them the same way
         self._weight_options = {}
         self._take_weight_options(**{k: kwargs.pop(k) for k in list(kwargs) if k.endswith(_OPTION_SUFFIXES)})
+        kwargs.pop('seed', None)  # (Keras 3 writes a seed into the config of every layer that draws random numbers)
         if kwargs:
             raise TypeError("%s got unexpected keyword argument(s) %s" % (type(self).__name__, sorted(kwargs)))
         self.name = name or unique_name(_to_snake(type(self).__name__))

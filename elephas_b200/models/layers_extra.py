@@ -325,7 +325,7 @@ class _Recurrent(Layer):
                  kernel_initializer='glorot_uniform', recurrent_initializer='orthogonal', bias_initializer='zeros',
                  return_sequences=False, return_state=False, go_backwards=False, stateful=False, unroll=False,
                  dropout=0.0, recurrent_dropout=0.0, custom_objects=None, **kwargs):
-        for key in ('time_major', 'implementation'):
+        for key in ('time_major', 'implementation', 'seed', 'zero_output_for_mask', 'use_cudnn'):
             kwargs.pop(key, None)
         super().__init__(**kwargs)
         if return_state or stateful:

@@ -1031,7 +1031,81 @@ def model_from_json(json_string, custom_objects=None):
     return model_from_config(spec, custom_objects)
 
 
+_KERAS3_ONLY_KEYS = frozenset(('lora_rank', 'lora_alpha', 'synchronized', 'optional', 'quantization_config'))
+
+
+def _keras3_tensors(node):
+    """The ``__keras_tensor__`` references inside one Keras 3 inbound node, in call order: positional arguments first
+    (nested lists flattened), then the keyword arguments a layer is called with (``value`` / ``key`` of attention)."""
+    found = []
+
+    def walk(item):
+        if isinstance(item, dict):
+            if item.get('class_name') == '__keras_tensor__':
+                name, node_index, tensor_index = item['config']['keras_history']
+                found.append([name, int(node_index), int(tensor_index), {}])
+            else:
+                for value in item.values():
+                    walk(value)
+        elif isinstance(item, (list, tuple)):
+            for value in item:
+                walk(value)
+
+    walk(node.get('args', []))
+    kwargs = node.get('kwargs', {}) or {}
+    for key in ('value', 'key'):
+        walk(kwargs.get(key))
+    return found
+
+
+def _from_keras3(spec):
+    """A model config in the Keras 3 dialect (``module`` / ``registered_name`` entries, ``DTypePolicy`` dictionaries,
+    ``batch_shape``, inbound nodes as ``{"args", "kwargs"}``) rewritten into the Keras 2.10 dialect this package reads."""
+    import copy
+    spec = copy.deepcopy(spec)
+
+    def clean(item):
+        if isinstance(item, dict):
+            item.pop('module', None), item.pop('registered_name', None)
+            for value in item.values():
+                clean(value)
+        elif isinstance(item, list):
+            for value in item:
+                clean(value)
+
+    clean(spec)
+    cfg = spec['config']
+    cfg.pop('dtype', None), cfg.pop('trainable', None), cfg.pop('build_input_shape', None)
+    for layer in cfg.get('layers', []):
+        lc = layer['config']
+        layer.pop('build_config', None)
+        layer.setdefault('name', lc.get('name'))
+        if isinstance(lc.get('dtype'), dict):
+            lc['dtype'] = lc['dtype'].get('config', {}).get('name', 'float32')
+        if 'batch_shape' in lc:
+            lc['batch_input_shape'] = lc.pop('batch_shape')
+        for key in _KERAS3_ONLY_KEYS & set(lc):
+            lc.pop(key)
+        for inner in ('layer', 'backward_layer'):   # wrappers carry a full layer spec
+            if isinstance(lc.get(inner), dict) and isinstance(lc[inner].get('config'), dict):
+                sub = {'config': {'layers': [lc[inner]]}}
+                lc[inner] = _from_keras3(sub)['config']['layers'][0]
+        nodes = layer.get('inbound_nodes')
+        if nodes and isinstance(nodes[0], dict):
+            layer['inbound_nodes'] = [_keras3_tensors(node) for node in nodes]
+    return spec
+
+
+def _is_keras3(spec):
+    if 'module' in spec or 'registered_name' in spec:
+        return True
+    layers = spec.get('config', {}).get('layers', []) if isinstance(spec.get('config'), dict) else []
+    return any('module' in l or isinstance(l.get('config', {}).get('dtype'), dict) for l in layers)
+
+
 def model_from_config(spec, custom_objects=None):
+    if _is_keras3(spec):
+        spec = _from_keras3(spec)
     cls_name = spec.get('class_name')
     if cls_name == 'Sequential':
         return Sequential.from_config(spec['config'], custom_objects)

@@ -21,6 +21,7 @@ import torch
 class Optimizer:
     _class_name = 'Optimizer'
     _defaults = {}
+    _default_weight_decay = None
 
     def __init__(self, learning_rate=None, **kwargs):
         if learning_rate is not None:  # Keras takes the rate as the first positional argument: Adam(1e-3)
@@ -30,6 +31,14 @@ class Optimizer:
         self.clipnorm = kwargs.pop('clipnorm', None)
         self.clipvalue = kwargs.pop('clipvalue', None)
         self.global_clipnorm = kwargs.pop('global_clipnorm', None)
+        # keys of the Keras 2.11+ / Keras 3 optimizer configs: decoupled weight decay is applied, the switches that have
+        # no meaning here are accepted when they are off
+        self.weight_decay = kwargs.pop('weight_decay', self._default_weight_decay) or None
+        for key in ('use_ema', 'gradient_accumulation_steps', 'loss_scale_factor'):
+            if kwargs.pop(key, None):
+                raise ValueError("%s: %s is not supported" % (self._class_name, key))
+        for key in ('ema_momentum', 'ema_overwrite_frequency', 'jit_compile', 'is_legacy_optimizer'):
+            kwargs.pop(key, None)
         cfg = dict(self._defaults)
         unknown = set(kwargs) - set(cfg) - {'name'}
         if unknown:
@@ -70,7 +79,7 @@ class Optimizer:
         if self.schedule is not None:
             from . import schedules
             cfg['learning_rate'] = schedules.serialize(self.schedule)
-        for k in ('clipnorm', 'clipvalue', 'global_clipnorm'):
+        for k in ('clipnorm', 'clipvalue', 'global_clipnorm', 'weight_decay'):
             if getattr(self, k) is not None:
                 cfg[k] = getattr(self, k)
         return cfg
@@ -122,7 +131,12 @@ class Optimizer:
     def apply_gradients(self, params, grads):
         """``params[i] -= step(grads[i])`` in place; advances ``iterations``."""
         grads = self._clip(list(grads))
-        self._apply(list(params), grads)
+        params = list(params)
+        if self.weight_decay:  # decoupled (AdamW-style): w <- w - lr * wd * w, before the gradient step
+            shrink = 1.0 - self._lr_t() * float(self.weight_decay)
+            for p in params:
+                p.mul_(shrink)
+        self._apply(params, grads)
         self.iterations += 1
 
     def _apply(self, params, grads):  # pragma: no cover - abstract
@@ -193,6 +207,12 @@ class Adam(Optimizer):
                 p.addcdiv_(m, vhat.sqrt() + eps, value=-lr)
             else:
                 p.addcdiv_(m, v.sqrt() + eps, value=-lr)
+
+
+class AdamW(Adam):
+    """Adam with decoupled weight decay (``keras.optimizers.AdamW``, default ``weight_decay=0.004``)."""
+    _class_name = 'AdamW'
+    _default_weight_decay = 0.004
 
 
 class Adagrad(Optimizer):
@@ -275,7 +295,7 @@ class Nadam(Optimizer):
             p.addcdiv_(m_bar, v_prime.sqrt() + eps, value=-lr)
 
 
-_CLASSES = {c._class_name.lower(): c for c in (SGD, RMSprop, Adam, Adagrad, Adadelta, Adamax, Nadam)}
+_CLASSES = {c._class_name.lower(): c for c in (SGD, RMSprop, Adam, AdamW, Adagrad, Adadelta, Adamax, Nadam)}
 
 
 def serialize(optimizer: Optimizer) -> dict:

@@ -66,3 +66,46 @@ def test_a_model_with_a_schedule_trains_and_keeps_it_through_json():
     clone = model_from_json(m.to_json())
     clone.compile(optimizers.deserialize(optimizers.serialize(m.optimizer)), 'mse')
     assert clone.optimizer.schedule(100) == pytest.approx(0.025)
+
+
+def test_adamw_and_the_newer_optimizer_config_keys(tmp_path):
+    from elephas_b200.models import load_model
+    w = torch.full((3,), 2.0, requires_grad=True)
+    ref = torch.full((3,), 2.0, requires_grad=True)
+    ours = optimizers.AdamW(learning_rate=0.1, weight_decay=0.05)
+    theirs = torch.optim.AdamW([ref], lr=0.1, weight_decay=0.05, eps=1e-7)
+    for step in range(5):
+        g = torch.tensor([0.5, -1.0, 2.0]) * (step + 1)
+        ours.apply_gradients([w], [g])
+        ref.grad = g.clone()
+        theirs.step()
+    np.testing.assert_allclose(w.detach().numpy(), ref.detach().numpy(), rtol=1e-5)
+    assert optimizers.AdamW().weight_decay == 0.004 and optimizers.Adam().weight_decay is None
+    assert 'weight_decay' not in optimizers.Adam().get_config()
+    # a Keras 2.11+ / Keras 3 optimizer config: new keys, no `decay`
+    cfg = {'class_name': 'Adam', 'config': {'name': 'Adam', 'weight_decay': None, 'clipnorm': None, 'global_clipnorm': None,
+                                            'clipvalue': None, 'use_ema': False, 'ema_momentum': 0.99,
+                                            'ema_overwrite_frequency': None, 'jit_compile': True, 'is_legacy_optimizer': False,
+                                            'learning_rate': 0.001, 'beta_1': 0.9, 'beta_2': 0.999, 'epsilon': 1e-07,
+                                            'amsgrad': False, 'loss_scale_factor': None, 'gradient_accumulation_steps': None}}
+    opt = optimizers.deserialize(cfg)
+    assert opt.learning_rate == 0.001 and opt.weight_decay is None
+    with pytest.raises(ValueError):
+        optimizers.deserialize({'class_name': 'SGD', 'config': {'use_ema': True}})
+    from elephas_b200.ops.engine import _optimizer_spec
+    assert _optimizer_spec(optimizers.SGD(0.1, weight_decay=1e-4)) is None
+    # through a model file
+    m = Sequential([Dense(4, activation='relu', input_shape=(5,)), Dense(1)])
+    m.compile(optimizers.AdamW(0.01), 'mse')
+    rng = np.random.default_rng(0)
+    x, y = rng.standard_normal((64, 5)).astype(np.float32), rng.standard_normal((64, 1)).astype(np.float32)
+    m.fit(x, y, batch_size=16, epochs=2)
+    path = str(tmp_path / 'adamw.h5')
+    m.save(path)
+    back = load_model(path)
+    assert type(back.optimizer).__name__ == 'AdamW' and back.optimizer.weight_decay == 0.004
+    assert back.optimizer.iterations == 8
+    a = m.train_on_batch(x[:16], y[:16])
+    b = back.train_on_batch(x[:16], y[:16])
+    assert a == pytest.approx(b, rel=1e-6)
+    np.testing.assert_allclose(back.get_weights()[0], m.get_weights()[0], rtol=1e-5, atol=1e-7)

@@ -18,4 +18,4 @@ from .layers_more import (AlphaDropout, Attention, Cropping1D, Cropping2D, Gauss
 from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
                     to_categorical)
 from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, AdamW, Nadam, RMSprop  # noqa: F401
-from . import zoo  # noqa: F401
+from . import utils, zoo  # noqa: F401

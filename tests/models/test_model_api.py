@@ -147,3 +147,19 @@ def test_summary_lists_shapes_and_parameter_totals():
     assert 'd0 (Dense)' in text and '(None, 8)' in text and 'bn (BatchNormalization)' in text
     assert 'Total params: 90' in text and 'Trainable params: 74' in text and 'Non-trainable params: 16' in text
     assert all(len(line) <= 65 for line in lines)
+
+
+def test_pad_sequences_and_normalize():
+    from elephas_b200.models.utils import normalize, pad_sequences, to_categorical
+    seqs = [[1, 2, 3], [4], [], [5, 6, 7, 8, 9]]
+    np.testing.assert_array_equal(pad_sequences(seqs, maxlen=4), [[0, 1, 2, 3], [0, 0, 0, 4], [0, 0, 0, 0], [6, 7, 8, 9]])
+    np.testing.assert_array_equal(pad_sequences(seqs, maxlen=4, padding='post', truncating='post', value=-1),
+                                  [[1, 2, 3, -1], [4, -1, -1, -1], [-1, -1, -1, -1], [5, 6, 7, 8]])
+    assert pad_sequences(seqs).shape == (4, 5) and pad_sequences(seqs).dtype == np.int32
+    vec = pad_sequences([np.ones((2, 3)), np.ones((1, 3))], dtype='float32')
+    assert vec.shape == (2, 2, 3) and vec[1, 0].sum() == 0 and vec[1, 1].sum() == 3
+    with pytest.raises(ValueError):
+        pad_sequences(seqs, padding='left')
+    n = normalize(np.array([[3.0, 4.0], [0.0, 0.0]]))
+    np.testing.assert_allclose(n, [[0.6, 0.8], [0.0, 0.0]])
+    assert to_categorical([0, 2]).tolist() == [[1, 0, 0], [0, 0, 1]]

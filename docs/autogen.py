@@ -55,6 +55,8 @@ PAGES = [
     ('io/hdf5.md', 'elephas_b200.io.hdf5', None),
     ('io/keras-h5.md', 'elephas_b200.io.keras_h5', None),
     ('spark/stand-ins.md', 'elephas_b200.spark.context', None),
+    ('spark/feature-stages.md', 'elephas_b200.spark.feature', None),
+    ('spark/evaluators.md', 'elephas_b200.spark.ml_evaluation', None),
 ]
 
 

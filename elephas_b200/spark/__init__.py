@@ -21,7 +21,10 @@ if HAVE_PYSPARK:  # pragma: no cover
     from pyspark import RDD, SparkConf, SparkContext, keyword_only  # noqa: F401
     from pyspark.broadcast import Broadcast  # noqa: F401
     from pyspark.ml import Estimator, Model, Pipeline, PipelineModel, Transformer  # noqa: F401
-    from pyspark.ml.feature import StandardScaler, StringIndexer  # noqa: F401
+    from pyspark.ml.feature import (IndexToString, MinMaxScaler, Normalizer, OneHotEncoder, StandardScaler,  # noqa: F401
+                                    StringIndexer, VectorAssembler)
+    from pyspark.ml.evaluation import (BinaryClassificationEvaluator, MulticlassClassificationEvaluator,  # noqa: F401
+                                       RegressionEvaluator)
     from pyspark.ml.linalg import Vector as MLVector, Vectors as MLVectors  # noqa: F401
     from pyspark.ml.param.shared import HasFeaturesCol, HasLabelCol, HasOutputCol, Param, Params  # noqa: F401
     from pyspark.ml.util import DefaultParamsReadable, DefaultParamsWritable  # noqa: F401
@@ -39,6 +42,9 @@ else:
     from .ml import (DefaultParamsReadable, DefaultParamsWritable, Estimator, HasFeaturesCol, HasLabelCol,  # noqa: F401
                      HasOutputCol, Model, Param, Params, Pipeline, PipelineModel, StandardScaler, StringIndexer,
                      Transformer, keyword_only)
+    from .feature import IndexToString, MinMaxScaler, Normalizer, OneHotEncoder, VectorAssembler  # noqa: F401
+    from .ml_evaluation import (BinaryClassificationEvaluator, MulticlassClassificationEvaluator,  # noqa: F401
+                                RegressionEvaluator)
     from .regression import LabeledPoint  # noqa: F401
     from .sql import (ArrayType, Column, DataFrame, DoubleType, Row, SparkSession, StructField, StructType,  # noqa: F401
                       functions)

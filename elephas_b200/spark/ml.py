@@ -375,7 +375,39 @@ class PipelineModel(Model, DefaultParamsReadable, DefaultParamsWritable):
 
 
 # ---------------------------------------------------------- feature stages
-class StringIndexerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadable, DefaultParamsWritable):
+class _WithData:
+    """Fitted stages keep their state in ``path/data/part-00000`` (JSON) next to Spark-style ``metadata``."""
+
+    _state = ()
+
+    def _save_impl(self, path):
+        super()._save_impl(path)
+        os.makedirs(os.path.join(path, 'data'))
+        state = {k: (getattr(self, k).tolist() if isinstance(getattr(self, k), np.ndarray) else getattr(self, k))
+                 for k in self._state}
+        with open(os.path.join(path, 'data', 'part-00000'), 'w') as fh:
+            json.dump(state, fh)
+
+    @classmethod
+    def _load_impl(cls, meta, path):
+        inst = cls()
+        inst.uid = meta['uid']
+        for k, v in meta.get('paramMap', {}).items():
+            if inst.hasParam(k):
+                inst._paramMap[inst.getParam(k)] = v
+        with open(os.path.join(path, 'data', 'part-00000')) as fh:
+            state = json.load(fh)
+        for k in cls._state:
+            v = state.get(k)
+            setattr(inst, k, np.asarray(v, dtype=np.float64) if isinstance(v, list) and k not in cls._lists else v)
+        return inst
+
+    _lists = ()
+
+
+class StringIndexerModel(_WithData, Model, HasInputCol, HasOutputCol, DefaultParamsReadable, DefaultParamsWritable):
+    _state = _lists = ('labels',)
+
     def __init__(self, labels=None, inputCol=None, outputCol=None):
         super().__init__()
         self.labels = list(labels or [])
@@ -422,7 +454,9 @@ class StringIndexer(Estimator, HasInputCol, HasOutputCol, DefaultParamsReadable,
         return StringIndexerModel(labels, self.getInputCol(), self.getOutputCol())
 
 
-class StandardScalerModel(Model, HasInputCol, HasOutputCol, DefaultParamsReadable, DefaultParamsWritable):
+class StandardScalerModel(_WithData, Model, HasInputCol, HasOutputCol, DefaultParamsReadable, DefaultParamsWritable):
+    _state = ('mean', 'std', 'withMean', 'withStd')
+
     def __init__(self, mean=None, std=None, withMean=False, withStd=True, inputCol=None, outputCol=None):
         super().__init__()
         self.mean, self.std, self.withMean, self.withStd = mean, std, withMean, withStd

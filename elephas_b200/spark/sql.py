@@ -207,6 +207,56 @@ class Column:
     def out_name(self):
         return self._alias or self.name
 
+    # comparisons and arithmetic against literals (``df.filter(df.label > 0.5)``, ``col('x') * 2``)
+    def _with(self, op):
+        prev = self.fn
+        return Column(self.name, (lambda v: op(prev(v))) if prev else op, self._alias)
+
+    def __gt__(self, other):
+        return self._with(lambda v: v > other)
+
+    def __ge__(self, other):
+        return self._with(lambda v: v >= other)
+
+    def __lt__(self, other):
+        return self._with(lambda v: v < other)
+
+    def __le__(self, other):
+        return self._with(lambda v: v <= other)
+
+    def __eq__(self, other):  # noqa: D105 - builds a condition, like pyspark's Column
+        return self._with(lambda v: v == other)
+
+    def __ne__(self, other):
+        return self._with(lambda v: v != other)
+
+    __hash__ = object.__hash__
+
+    def __add__(self, other):
+        return self._with(lambda v: v + other)
+
+    def __sub__(self, other):
+        return self._with(lambda v: v - other)
+
+    def __mul__(self, other):
+        return self._with(lambda v: v * other)
+
+    def __truediv__(self, other):
+        return self._with(lambda v: v / other)
+
+    def __invert__(self):
+        return self._with(lambda v: not v)
+
+    def isin(self, *values):
+        pool = set(values[0]) if len(values) == 1 and isinstance(values[0], (list, tuple, set)) else set(values)
+        return self._with(lambda v: v in pool)
+
+    def isNull(self):
+        return self._with(lambda v: v is None)
+
+    def isNotNull(self):
+        return self._with(lambda v: v is not None)
+
 
 class functions:
     """Tiny ``pyspark.sql.functions``: ``col`` and ``array_argmax`` (the reference's tests spell the
@@ -399,6 +449,53 @@ class DataFrame:
         keep = [c for c in self.columns if c not in cols]
         return self.select(*keep)
 
+    def __getitem__(self, name):
+        self._col_index(name)
+        return Column(name)
+
+    def __getattr__(self, name):  # df.label, as pyspark allows
+        if name.startswith('_') or name not in self.__dict__.get('schema', StructType([])).names:
+            raise AttributeError(name)
+        return Column(name)
+
+    def filter(self, condition):
+        """Rows for which ``condition`` holds: a Column compared with a literal (``df.x > 1``) or a function of the Row."""
+        if isinstance(condition, Column):
+            i, fn = self._col_index(condition.name), condition.fn or bool
+            keep = lambda row: bool(fn(row[i]))  # noqa: E731
+        elif callable(condition):
+            keep = condition
+        else:
+            raise TypeError("filter expects a Column condition or a function of the row")
+        return DataFrame(self.rdd.filter(keep), self.schema, self.sparkSession)
+
+    where = filter
+
+    def orderBy(self, *cols, ascending=True):
+        cols = [c.name if isinstance(c, Column) else c for c in (cols[0] if len(cols) == 1 and isinstance(cols[0], (list, tuple)) else cols)]
+        idx = [self._col_index(c) for c in cols]
+        flags = list(ascending) if isinstance(ascending, (list, tuple)) else [ascending] * len(idx)
+        rows = self.collect()
+        for i, asc in reversed(list(zip(idx, flags))):   # stable sorts, last key first
+            rows = sorted(rows, key=lambda r, i=i: r[i], reverse=not asc)
+        return DataFrame(RDD([rows], self.rdd.context), self.schema, self.sparkSession)
+
+    sort = orderBy
+
+    def dropna(self, how='any', subset=None):
+        idx = [self._col_index(c) for c in (subset or self.columns)]
+        test = any if how == 'any' else all
+
+        def missing(v):
+            return v is None or (isinstance(v, float) and v != v)
+
+        return self.filter(lambda row: not test(missing(row[i]) for i in idx))
+
+    def groupBy(self, *cols):
+        return GroupedData(self, [c.name if isinstance(c, Column) else c for c in cols])
+
+    groupby = groupBy
+
     def distinct(self):
         seen, rows = set(), []
         for r in self.collect():
@@ -458,6 +555,48 @@ class DataFrame:
 
     def __repr__(self):
         return "DataFrame[%s]" % ", ".join("%s: %s" % (f.name, f.dataType.simpleString()) for f in self.schema.fields)
+
+
+class GroupedData:
+    """``df.groupBy(cols)``: ``count()`` and the numeric aggregates ``avg / mean / sum / min / max`` of named columns."""
+
+    def __init__(self, frame, keys):
+        self.frame, self.keys = frame, keys
+        self._idx = [frame._col_index(k) for k in keys]
+
+    def _groups(self):
+        groups = {}
+        for row in self.frame.collect():
+            groups.setdefault(tuple(row[i] for i in self._idx), []).append(row)
+        return groups
+
+    def _result(self, names, types, rows):
+        fields = [self.frame.schema.fields[i] for i in self._idx] + [StructField(n, t) for n, t in zip(names, types)]
+        all_names = self.keys + names
+        data = [Row._make(all_names, list(r)) for r in rows]
+        return DataFrame(RDD([data], self.frame.rdd.context), StructType(fields), self.frame.sparkSession)
+
+    def count(self):
+        return self._result(['count'], [LongType()], [key + (len(rows),) for key, rows in self._groups().items()])
+
+    def _aggregate(self, label, fn, cols):
+        idx = [self.frame._col_index(c) for c in cols]
+        out = [key + tuple(float(fn([r[i] for r in rows])) for i in idx) for key, rows in self._groups().items()]
+        return self._result(['%s(%s)' % (label, c) for c in cols], [DoubleType()] * len(cols), out)
+
+    def avg(self, *cols):
+        return self._aggregate('avg', lambda v: sum(v) / len(v), cols)
+
+    mean = avg
+
+    def sum(self, *cols):
+        return self._aggregate('sum', sum, cols)
+
+    def min(self, *cols):
+        return self._aggregate('min', min, cols)
+
+    def max(self, *cols):
+        return self._aggregate('max', max, cols)
 
 
 # -------------------------------------------------------------- SparkSession

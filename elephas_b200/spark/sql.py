@@ -557,6 +557,81 @@ class DataFrame:
         return "DataFrame[%s]" % ", ".join("%s: %s" % (f.name, f.dataType.simpleString()) for f in self.schema.fields)
 
 
+class DataFrameReader:
+    """``spark.read``: CSV files (``header``, ``inferSchema``, ``sep``) and JSON-lines files into local DataFrames."""
+
+    def __init__(self, session):
+        self._session, self._format, self._options = session, 'csv', {}
+
+    def format(self, source):  # noqa: A003 - pyspark's name
+        if source not in ('csv', 'json', 'com.databricks.spark.csv'):
+            raise NotImplementedError("the local reader knows 'csv' and 'json', not %r" % (source,))
+        self._format = 'json' if source == 'json' else 'csv'
+        return self
+
+    def option(self, key, value):
+        self._options[key] = value
+        return self
+
+    def options(self, **kwargs):
+        self._options.update(kwargs)
+        return self
+
+    def load(self, path):
+        return self.json(path) if self._format == 'json' else self.csv(path)
+
+    @staticmethod
+    def _flag(value):
+        return str(value).lower() in ('true', '1', 'yes')
+
+    def csv(self, path, header=None, inferSchema=None, sep=None, schema=None):
+        import csv as _csv
+        opts = self._options
+        header = self._flag(opts.get('header', False) if header is None else header)
+        infer = self._flag(opts.get('inferSchema', opts.get('inferschema', False)) if inferSchema is None else inferSchema)
+        sep = sep or opts.get('sep') or opts.get('delimiter') or ','
+        with open(path, newline='') as fh:
+            records = [r for r in _csv.reader(fh, delimiter=sep) if r]
+        names = records.pop(0) if header and records else ['_c%d' % i for i in range(len(records[0]) if records else 0)]
+        if isinstance(schema, StructType):
+            names, casts = schema.names, [_caster_of(f.dataType) for f in schema.fields]
+        elif infer:
+            casts = [_infer_text_caster([r[i] for r in records]) for i in range(len(names))]
+        else:
+            casts = [str] * len(names)
+        rows = [tuple(None if v == '' and c is not str else c(v) for v, c in zip(r, casts)) for r in records]
+        return self._session.createDataFrame(rows, schema if isinstance(schema, StructType) else names)
+
+    def json(self, path):
+        import json as _json
+        with open(path) as fh:
+            records = [_json.loads(line) for line in fh if line.strip()]
+        names = sorted({k for r in records for k in r})
+        return self._session.createDataFrame([tuple(r.get(k) for k in names) for r in records], names)
+
+
+def _caster_of(data_type):
+    if isinstance(data_type, (DoubleType, FloatType)):
+        return float
+    if isinstance(data_type, (IntegerType, LongType)):
+        return int
+    if isinstance(data_type, BooleanType):
+        return lambda v: str(v).lower() == 'true'
+    return str
+
+
+def _infer_text_caster(values):
+    values = [v for v in values if v != '']
+    for cast in (int, float):
+        try:
+            for v in values:
+                cast(v)
+            return cast
+        except ValueError:
+            continue
+    return str
+
+
 class GroupedData:
     """``df.groupBy(cols)``: ``count()`` and the numeric aggregates ``avg / mean / sum / min / max`` of named columns."""
 
@@ -640,7 +715,14 @@ class SparkSession:
         self._views = {}
         SparkSession._active = self
 
+    @property
+    def read(self):
+        return DataFrameReader(self)
+
     def createDataFrame(self, data, schema=None):
+        if type(data).__module__.startswith('pandas') and hasattr(data, 'itertuples'):   # a pandas.DataFrame
+            schema = schema or [str(c) for c in data.columns]
+            data = [tuple(v.item() if hasattr(v, 'item') else v for v in row) for row in data.itertuples(index=False, name=None)]
         rdd = data if isinstance(data, RDD) else self.sparkContext.parallelize(list(data))
         first = rdd.take(1)
         if first and isinstance(first[0], LabeledPoint):

@@ -141,3 +141,27 @@ def test_a_pipeline_of_stand_ins_ends_in_the_estimator():
     scored = out.select(S.functions.array_argmax('prediction').alias('prediction'), 'label')
     scored = scored.withColumn('prediction', S.functions.col('prediction').cast(S.DoubleType()))
     assert S.MulticlassClassificationEvaluator(metricName='accuracy').evaluate(scored) > 0.9
+
+
+def test_reader_and_pandas_frames(tmp_path):
+    import pandas as pd
+    session = S.SparkSession.builder.getOrCreate()
+    path = tmp_path / 'data.csv'
+    path.write_text("id,score,name\n1,0.5,ann\n2,,bob\n3,2.25,cy\n")
+    df = session.read.csv(str(path), header=True, inferSchema=True)
+    assert df.columns == ['id', 'score', 'name']
+    rows = df.collect()
+    assert rows[0].id == 1 and rows[0].score == 0.5 and rows[1].score is None and rows[2].name == 'cy'
+    assert df.dropna().count() == 2
+    same = session.read.format('csv').option('header', 'true').option('inferSchema', 'true').load(str(path))
+    assert same.collect() == rows
+    text = session.read.csv(str(path))
+    assert text.columns == ['_c0', '_c1', '_c2'] and text.first()[0] == 'id'
+    lines = tmp_path / 'data.json'
+    lines.write_text('{"a": 1, "b": "x"}\n{"a": 2}\n')
+    js = session.read.json(str(lines))
+    assert js.columns == ['a', 'b'] and js.collect()[1].b is None
+    frame = pd.DataFrame({'u': [1.5, 2.5], 'w': ['p', 'q']})
+    back = session.createDataFrame(frame)
+    assert back.columns == ['u', 'w'] and back.collect()[1].w == 'q' and isinstance(back.first().u, float)
+    assert back.toPandas().equals(frame)

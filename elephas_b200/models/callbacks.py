@@ -182,6 +182,34 @@ class TerminateOnNaN(Callback):
             self.model.stop_training = True
 
 
+class CSVLogger(Callback):
+    """One line per epoch (``epoch`` and every entry of the logs) into ``filename``; ``append`` keeps an existing file."""
+
+    def __init__(self, filename, separator=',', append=False):
+        super().__init__()
+        self.filename, self.separator, self.append = str(filename), separator, bool(append)
+        self._keys = None
+
+    def on_train_begin(self, logs=None):
+        import os
+        keep = self.append and os.path.exists(self.filename) and os.path.getsize(self.filename) > 0
+        if keep and self._keys is None:
+            with open(self.filename) as fh:
+                self._keys = fh.readline().rstrip('\n').split(self.separator)[1:]
+        self._fh = open(self.filename, 'a' if keep else 'w')
+
+    def on_epoch_end(self, epoch, logs=None):
+        logs = logs or {}
+        if self._keys is None:
+            self._keys = sorted(logs)
+            self._fh.write(self.separator.join(['epoch'] + self._keys) + '\n')
+        self._fh.write(self.separator.join([str(epoch)] + [repr(float(logs[k])) if k in logs else 'NA' for k in self._keys]) + '\n')
+        self._fh.flush()
+
+    def on_train_end(self, logs=None):
+        self._fh.close()
+
+
 class CallbackList:
     """What ``Model.fit`` drives: plain objects that only define ``on_epoch_end`` (the reference's tests pass such
     objects) work as well as :class:`Callback` subclasses."""

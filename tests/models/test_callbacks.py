@@ -191,3 +191,16 @@ def test_callbacks_travel_through_spark_model_fit(mode, ps):
            callbacks=[C.LambdaCallback(on_epoch_end=lambda e, logs: seen.append((e, logs['loss'])))])
     assert sorted(e for e, _ in seen) == [0, 0, 1, 1]
     assert all(np.isfinite(v) for _, v in seen)
+
+
+def test_csv_logger_writes_one_line_per_epoch(tmp_path):
+    x, y = _data()
+    path = tmp_path / 'log.csv'
+    m = _model()
+    m.fit(x, y, epochs=2, validation_split=0.25, callbacks=[C.CSVLogger(path)])
+    lines = path.read_text().strip().split('\n')
+    assert lines[0] == 'epoch,acc,loss,val_acc,val_loss' and [l.split(',')[0] for l in lines[1:]] == ['0', '1']
+    assert all(len(l.split(',')) == 5 for l in lines[1:])
+    m.fit(x, y, epochs=3, initial_epoch=2, validation_split=0.25, callbacks=[C.CSVLogger(path, append=True)])
+    lines = path.read_text().strip().split('\n')
+    assert len(lines) == 4 and lines[-1].split(',')[0] == '2'

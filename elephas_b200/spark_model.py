@@ -314,7 +314,11 @@ class SparkModel:
         if self.frequency not in ('epoch', 'batch'):
             raise ValueError('frequency parameter can be `epoch` or `batch, got {}'.format(self.frequency))
         epochs = int(train_config.get('epochs', 1))
-        if rt.is_driver and epochs > 1 and 'sync_rounds' not in self.kwargs and not getattr(self, '_sync_notice_done', False):
+        if train_config.get('callbacks') and 'sync_rounds' not in self.kwargs:
+            # callbacks keep state from epoch to epoch (patience counters, best values): every worker runs ONE fit over all
+            # epochs, as under the reference, and the replicas are averaged at its end
+            sync_rounds = 'fit'
+        elif rt.is_driver and epochs > 1 and 'sync_rounds' not in self.kwargs and not getattr(self, '_sync_notice_done', False):
             # the one place where a ported script computes something else than under the reference: say so, once
             print(">>> note: synchronous mode averages the replicas after every %s here; the reference averages once per "
                   "fit (elephas/spark_model.py:217-231) - pass sync_rounds='fit' for that behaviour"

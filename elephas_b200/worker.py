@@ -58,6 +58,10 @@ class _WorkerBase:
         self.json = json
         self.parameters = parameters
         self.train_config = dict(train_config)
+        if self.train_config.get('callbacks'):
+            # every worker counts for itself (patience, best value, the model it is attached to), as the pickled copies
+            # on Spark executors do under the reference
+            self.train_config['callbacks'] = copy.deepcopy(list(self.train_config['callbacks']))
         self.master_optimizer = master_optimizer
         self.master_loss = master_loss
         self.master_metrics = master_metrics

@@ -204,3 +204,22 @@ def test_csv_logger_writes_one_line_per_epoch(tmp_path):
     m.fit(x, y, epochs=3, initial_epoch=2, validation_split=0.25, callbacks=[C.CSVLogger(path, append=True)])
     lines = path.read_text().strip().split('\n')
     assert len(lines) == 4 and lines[-1].split(',')[0] == '2'
+
+
+def test_early_stopping_keeps_its_patience_across_the_epochs_of_a_synchronous_fit():
+    """With callbacks every worker runs one fit over all epochs (the reference's scheme): patience accumulates."""
+    from elephas_b200.spark_model import SparkModel
+    from elephas_b200.spark import SparkContext
+    from elephas_b200.utils.rdd_utils import to_simple_rdd
+    x, y = _data(512)
+    rdd = to_simple_rdd(SparkContext.getOrCreate(), x, y).repartition(2)
+    seen = []
+
+    class Flat(C.Callback):   # the monitored value never improves after the first epoch
+        def on_epoch_end(self, epoch, logs=None):
+            logs['val_loss'] = 1.0
+            seen.append(epoch)
+
+    sm = SparkModel(_model(), mode='synchronous', num_workers=2)
+    sm.fit(rdd, epochs=10, batch_size=32, verbose=0, callbacks=[Flat(), C.EarlyStopping(patience=2)])
+    assert sorted(seen) == [0, 0, 1, 1, 2, 2]     # both workers stop after epoch 2 (epochs 1 and 2 did not improve)

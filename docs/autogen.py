@@ -21,6 +21,7 @@ PAGES = [
     ('models/keras-layer.md', 'elephas_b200.models.model', ['Model', 'Sequential', 'model_from_json', 'load_model']),
     ('models/layers.md', 'elephas_b200.models.layers', None),
     ('models/layers-extra.md', 'elephas_b200.models.layers_extra', None),
+    ('models/keras-namespace.md', 'elephas_b200.keras', None),
     ('models/layers-more.md', 'elephas_b200.models.layers_more', None),
     ('models/callbacks.md', 'elephas_b200.models.callbacks', None),
     ('models/regularizers.md', 'elephas_b200.models.regularizers', None),

@@ -1,0 +1,48 @@
+"""``elephas_b200.keras``: a Keras script with the import prefix changed and nothing else."""
+import numpy as np
+
+
+def test_a_keras_script_with_only_its_import_prefix_changed(tmp_path):
+    from elephas_b200.keras import callbacks, initializers, optimizers, regularizers
+    from elephas_b200.keras.layers import LSTM, Dense, Dropout, Embedding
+    from elephas_b200.keras.losses import CategoricalCrossentropy
+    from elephas_b200.keras.metrics import AUC
+    from elephas_b200.keras.models import Sequential, clone_model, load_model
+    from elephas_b200.keras.preprocessing.sequence import pad_sequences
+    from elephas_b200.keras.utils import to_categorical
+
+    rng = np.random.default_rng(0)
+    seqs = [rng.integers(1, 20, rng.integers(3, 9)).tolist() for _ in range(200)]
+    x = pad_sequences(seqs, maxlen=8)
+    y = to_categorical([int(np.mean(s) > 10) for s in seqs], 2)
+
+    model = Sequential()
+    model.add(Embedding(20, 8, mask_zero=True, input_length=8))
+    model.add(LSTM(12, kernel_initializer=initializers.GlorotUniform(seed=1), kernel_regularizer=regularizers.l2(1e-4)))
+    model.add(Dropout(0.1))
+    model.add(Dense(2, activation='softmax'))
+    model.compile(optimizer=optimizers.Adam(learning_rate=0.02), loss=CategoricalCrossentropy(label_smoothing=0.05),
+                  metrics=['accuracy', AUC(name='auc')])
+    best = str(tmp_path / 'best.h5')
+    history = model.fit(x, y, batch_size=20, epochs=10, validation_split=0.2, verbose=0,
+                        callbacks=[callbacks.EarlyStopping(monitor='val_loss', patience=5),
+                                   callbacks.ModelCheckpoint(best, save_best_only=True)])
+    assert history.history['accuracy'][-1] > 0.8 and history.history['auc'][-1] > 0.85
+    restored = load_model(best)
+    assert restored.predict(x[:4]).shape == (4, 2)
+    twin = clone_model(model)
+    assert twin.count_params() == model.count_params() and not np.array_equal(twin.get_weights()[-2], model.get_weights()[-2])
+
+
+def test_namespace_lists_every_layer_and_initializers_check_their_arguments():
+    import pytest
+
+    import elephas_b200.keras as keras
+    from elephas_b200.models.layers import LAYER_CLASSES
+    assert set(LAYER_CLASSES) <= set(keras.layers.__all__)
+    assert keras.layers.Conv2D is LAYER_CLASSES['Conv2D'] and keras.Sequential is keras.models.Sequential
+    assert keras.initializers.RandomNormal(stddev=0.1)['config']['stddev'] == 0.1
+    with pytest.raises(TypeError):
+        keras.initializers.Zeros(seed=1)
+    assert keras.optimizers.get('adamw').weight_decay == 0.004
+    assert keras.constraints.max_norm(3).max_value == 3.0

@@ -326,3 +326,81 @@ def test_data_frame_operations_on_frames_with_block_columns(rows, limit, seed):
     df.createOrReplaceTempView('frame_under_test')
     out = spark.sql('SELECT scaled AS features, idx as label from frame_under_test').collect()
     assert [r['label'] for r in out] == idx and np.allclose(np.stack([r['features'].toArray() for r in out]), centred)
+
+
+# ----------------------------------------------------------------------------- Keras-surface building blocks
+small_floats = st.floats(min_value=-4.0, max_value=4.0, allow_nan=False, width=32)
+matrices = hnp.arrays(np.float32, hnp.array_shapes(min_dims=2, max_dims=2, min_side=1, max_side=6), elements=small_floats)
+
+
+@settings(max_examples=60, deadline=None, derandomize=True)
+@given(matrices, st.sampled_from(['MaxNorm', 'UnitNorm', 'NonNeg', 'MinMaxNorm']), st.integers(0, 1))
+def test_constraints_are_projections(w, name, axis):
+    """Applying a constraint twice equals applying it once, and the constrained weight satisfies the bound."""
+    from elephas_b200.models import constraints
+    con = {'MaxNorm': constraints.MaxNorm(1.5, axis=axis), 'UnitNorm': constraints.UnitNorm(axis=axis),
+           'NonNeg': constraints.NonNeg(), 'MinMaxNorm': constraints.MinMaxNorm(0.5, 1.5, axis=axis)}[name]
+    w = np.where(np.abs(w) < 1e-2, 0.0, w).astype(np.float32)   # (norms of the order of Keras' epsilon 1e-7 take two steps)
+    once = con(torch.tensor(w))
+    twice = con(once)
+    np.testing.assert_allclose(twice.numpy(), once.numpy(), rtol=1e-4, atol=1e-5)
+    norms = once.norm(dim=axis)
+    if name == 'MaxNorm':
+        assert bool((norms <= 1.5 + 1e-4).all())
+    if name == 'NonNeg':
+        assert bool((once >= 0).all())
+    if name == 'UnitNorm':
+        nonzero = torch.tensor(w).norm(dim=axis) > 1e-3
+        np.testing.assert_allclose(norms[nonzero].numpy(), np.ones(int(nonzero.sum())), rtol=1e-3)
+
+
+@settings(max_examples=40, deadline=None, derandomize=True)
+@given(matrices, st.floats(0.001, 0.5), st.floats(0.0, 0.5))
+def test_regularizer_gradients_match_their_closed_form(w, l1, l2):
+    from elephas_b200.models import regularizers
+    t = torch.tensor(w, requires_grad=True)
+    regularizers.L1L2(l1, l2)(t).backward()
+    np.testing.assert_allclose(t.grad.numpy(), l1 * np.sign(w) + 2.0 * l2 * w, rtol=1e-5, atol=1e-6)
+
+
+@settings(max_examples=60, deadline=None, derandomize=True)
+@given(st.lists(st.lists(st.integers(1, 50), max_size=9), min_size=1, max_size=8), st.integers(1, 10),
+       st.sampled_from(['pre', 'post']), st.sampled_from(['pre', 'post']))
+def test_pad_sequences_keeps_the_right_end_of_every_sequence(seqs, maxlen, padding, truncating):
+    from elephas_b200.models.utils import pad_sequences
+    out = pad_sequences(seqs, maxlen=maxlen, padding=padding, truncating=truncating)
+    assert out.shape == (len(seqs), maxlen)
+    for row, seq in zip(out, seqs):
+        kept = seq[-maxlen:] if truncating == 'pre' else seq[:maxlen]
+        body = row[maxlen - len(kept):] if padding == 'pre' else row[:len(kept)]
+        rest = row[:maxlen - len(kept)] if padding == 'pre' else row[len(kept):]
+        assert body.tolist() == kept and not rest.any()
+
+
+@settings(max_examples=40, deadline=None, derandomize=True)
+@given(st.floats(1e-4, 1.0), st.integers(1, 500), st.floats(0.05, 0.99), st.integers(0, 2000), st.integers(0, 2000))
+def test_decaying_schedules_never_increase_and_never_go_negative(lr, steps, rate, a, b):
+    from elephas_b200.models import schedules
+    lo, hi = min(a, b), max(a, b)
+    for sched in (schedules.ExponentialDecay(lr, steps, rate), schedules.ExponentialDecay(lr, steps, rate, staircase=True),
+                  schedules.InverseTimeDecay(lr, steps, rate), schedules.CosineDecay(lr, steps, alpha=0.1),
+                  schedules.PolynomialDecay(lr, steps, end_learning_rate=lr * 0.01)):
+        assert 0.0 <= sched(hi) <= sched(lo) * (1 + 1e-9) <= lr * (1 + 1e-9)   # (0.5 ** 1074 underflows to zero)
+
+
+@settings(max_examples=25, deadline=None, derandomize=True)
+@given(st.integers(1, 6), st.integers(1, 5), st.integers(2, 7), st.integers(0, 2 ** 31 - 1))
+def test_masked_recurrent_rows_do_not_depend_on_their_padding(batch, features, steps, seed):
+    """Whatever follows the last unmasked step of a row - other rows' lengths, the padded values - the row's result is the
+    result of the bare sequence."""
+    from elephas_b200.models import GRU, Masking, Sequential as Seq
+    rng = np.random.default_rng(seed)
+    torch.manual_seed(seed % 1000)
+    m = Seq([Masking(0.0, input_shape=(steps, features)), GRU(3)])
+    lengths = rng.integers(1, steps + 1, batch)
+    x = np.zeros((batch, steps, features), dtype=np.float32)
+    for r, n in enumerate(lengths):
+        x[r, :n] = rng.uniform(0.5, 1.5, (n, features))
+    out = m.predict(x)
+    for r, n in enumerate(lengths):
+        np.testing.assert_allclose(out[r], m.predict(x[r:r + 1, :n])[0], rtol=1e-5, atol=1e-6)

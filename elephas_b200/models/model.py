@@ -25,6 +25,10 @@ from . import metrics as _metrics
 from . import optimizers as _optimizers
 
 _PREDICT_BLOCK = 256
+# fit() keywords that are accepted and have no effect here (data-loader knobs of Keras; options of this package's
+# distributed paths that travel in the same train_config dictionary)
+_FIT_ACCEPTED = frozenset(('workers', 'use_multiprocessing', 'max_queue_size', 'validation_steps', 'validation_batch_size',
+                           'compute_dtype', 'input_mode', 'log_batch_loss', 'keep_context', 'timed_from'))
 # layers that hand the mask of their input on unchanged (they keep the [batch, time] axes and look at no neighbours)
 _MASK_TRANSPARENT = frozenset(('Dropout', 'SpatialDropout1D', 'Activation', 'ReLU', 'LeakyReLU', 'ELU', 'Softmax', 'Dense',
                                'TimeDistributed', 'LayerNormalization', 'BatchNormalization', 'GaussianNoise'))
@@ -724,6 +728,11 @@ class Model:
         self._require_compiled()
         if 'nb_epoch' in kwargs:
             epochs = kwargs.pop('nb_epoch')
+        steps_per_epoch = kwargs.pop('steps_per_epoch', None)
+        validation_freq = kwargs.pop('validation_freq', 1)
+        unknown = set(kwargs) - _FIT_ACCEPTED
+        if unknown:
+            raise TypeError("fit() got unexpected keyword argument(s) %s" % sorted(unknown))
         batch_size = int(batch_size or 32)
         x = self._host_x(x)
         y = np.asarray(y) if not isinstance(y, torch.Tensor) else y
@@ -742,7 +751,7 @@ class Model:
         cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': _rows(x), 'verbose': verbose})
         self.stop_training = False
         # weighted rows: the loss of the fused engines has no weight operand, the autograd step takes them
-        eng = self._native_engine() if row_weight is None else None
+        eng = self._native_engine() if row_weight is None and steps_per_epoch is None and validation_freq == 1 else None
         if eng is not None and not cbs:
             eng.fit(x, y, batch_size, epochs, shuffle, history, x_val, y_val, verbose, initial_epoch)
             return history
@@ -779,7 +788,8 @@ class Model:
             if te is not None:
                 te.stats.zero_()
             graphed_rows = 0
-            for start in range(0, n, batch_size):
+            seen = n if steps_per_epoch is None else min(n, int(steps_per_epoch) * batch_size)
+            for start in range(0, seen, batch_size):
                 idx = order[start:start + batch_size]
                 if te is not None and self._graphed_step(xt[idx], yt[idx]):
                     graphed_rows += len(idx)  # loss / metric sums stay on the device until the epoch ends
@@ -794,9 +804,11 @@ class Model:
                 for i, v in enumerate(vals):
                     sums[i] += v * rows
                 self.optimizer.iterations = int(te.step.item())
-            logs = {k: (s / n if n else 0.0) for k, s in zip(names, sums)}
+            logs = {k: (s / seen if seen else 0.0) for k, s in zip(names, sums)}
             logs.update(self._stateful_results())
-            if x_val is not None and len(y_val):
+            validate = (epoch + 1) in validation_freq if isinstance(validation_freq, (list, tuple)) \
+                else (epoch + 1) % int(validation_freq) == 0
+            if x_val is not None and len(y_val) and validate:
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
                 val = val if isinstance(val, list) else [val]
                 logs.update({'val_' + k: v for k, v in zip(names, val)})

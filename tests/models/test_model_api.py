@@ -163,3 +163,15 @@ def test_pad_sequences_and_normalize():
     n = normalize(np.array([[3.0, 4.0], [0.0, 0.0]]))
     np.testing.assert_allclose(n, [[0.6, 0.8], [0.0, 0.0]])
     assert to_categorical([0, 2]).tolist() == [[1, 0, 0], [0, 0, 1]]
+
+
+def test_steps_per_epoch_validation_freq_and_unknown_keywords():
+    x, y = _xy(96)
+    m = _model()
+    h = m.fit(x, y, batch_size=16, epochs=4, steps_per_epoch=2, validation_data=(x[:32], y[:32]), validation_freq=2)
+    assert m.optimizer.iterations == 8                       # 2 steps in each of 4 epochs
+    assert len(h.history['loss']) == 4 and len(h.history['val_loss']) == 2
+    h = _model().fit(x, y, batch_size=16, epochs=3, validation_split=0.25, validation_freq=[1, 3], workers=4)
+    assert len(h.history['val_loss']) == 2
+    with pytest.raises(TypeError):
+        m.fit(x, y, batchsize=16)

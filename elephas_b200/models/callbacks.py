@@ -78,7 +78,7 @@ class EarlyStopping(Callback):
                 self.best_weights = self.model.get_weights()
             return
         self.wait += 1
-        if self.wait >= self.patience:
+        if self.wait >= self.patience and epoch > 0:
             self.stopped_epoch = epoch
             self.model.stop_training = True
             if self.restore_best_weights and self.best_weights is not None:
@@ -172,7 +172,7 @@ class ReduceLROnPlateau(Callback):
                     self.model.optimizer.learning_rate = max(old * self.factor, self.min_lr)
                     if self.verbose:
                         print("Epoch %d: reducing learning rate to %.6g" % (epoch + 1, self.model.optimizer.learning_rate))
-                self.cooldown_counter, self.wait = self.cooldown, 0
+                    self.cooldown_counter, self.wait = self.cooldown, 0
 
 
 class TerminateOnNaN(Callback):

@@ -38,10 +38,11 @@ class Lambda(Layer):
     def compute_output_shape(self, input_shape):
         if self.output_shape_arg is not None:
             return (input_shape[0],) + self.output_shape_arg
+        dims = lambda shape: tuple(1 if d is None else int(d) for d in shape[1:])  # noqa: E731 (free axes probed with length 1)
         if isinstance(input_shape, list):   # run the function on one zero row of every input to learn the shape
-            probe = [torch.zeros((1,) + tuple(int(d) for d in s[1:])) for s in input_shape]
+            probe = [torch.zeros((1,) + dims(s)) for s in input_shape]
         else:
-            probe = torch.zeros((1,) + tuple(int(d) for d in input_shape[1:]))
+            probe = torch.zeros((1,) + dims(input_shape))
         out = self.function(probe, **self.arguments)
         return (None,) + tuple(out.shape[1:])
 

@@ -24,11 +24,26 @@ from ..models import optimizers as _optimizers
 
 
 def _training_config(model):
-    loss = _losses.serialize(model.loss)
-    metrics = [m if isinstance(m, str) else getattr(m, '__name__', str(m))
-               for m in (model.compiled_metrics._metrics or [])]
-    return {'loss': loss, 'metrics': metrics, 'weighted_metrics': None, 'loss_weights': None,
-            'optimizer_config': _optimizers.serialize(model.optimizer)}
+    def one_metric(m):
+        return m if isinstance(m, str) else getattr(m, '__name__', str(m))
+
+    def metric_names(ms):
+        if isinstance(ms, dict):
+            return {k: metric_names(v) for k, v in ms.items()}
+        if isinstance(ms, (list, tuple)):
+            return [metric_names(m) if isinstance(m, (list, tuple)) else one_metric(m) for m in ms]
+        return one_metric(ms)
+
+    loss = model.loss
+    if isinstance(loss, (list, tuple)):
+        loss = [_losses.serialize(l) for l in loss]
+    elif isinstance(loss, dict) and 'class_name' not in loss:
+        loss = {k: _losses.serialize(v) for k, v in loss.items()}
+    else:
+        loss = _losses.serialize(loss)
+    metrics = model.compiled_metrics._metrics
+    return {'loss': loss, 'metrics': metric_names(metrics) if metrics else [], 'weighted_metrics': None,
+            'loss_weights': getattr(model, 'loss_weights', None), 'optimizer_config': _optimizers.serialize(model.optimizer)}
 
 
 def _optimizer_weight_entries(model):
@@ -185,14 +200,20 @@ def load_model(filepath, custom_objects=None, compile=True):
     model.set_weights(weights)
     if compile and 'training_config' in root.attrs:
         tc = json.loads(_text(root.attrs['training_config']))
+        def revive(entry):
+            return _losses.deserialize(entry, custom_objects) if isinstance(entry, dict) and 'class_name' in entry else entry
+
         loss = tc.get('loss')
-        if isinstance(loss, dict):
-            if 'class_name' in loss:
-                loss = _losses.deserialize(loss, custom_objects)
-            else:  # one entry per output name: single-output models only
+        if isinstance(loss, list):
+            loss = [revive(l) for l in loss]
+        elif isinstance(loss, dict) and 'class_name' not in loss:
+            loss = {k: revive(v) for k, v in loss.items()}
+            if len(model._outputs) == 1:   # Keras writes {output name: loss} for one output too
                 loss = next(iter(loss.values()))
+        else:
+            loss = revive(loss)
         model.compile(optimizer=_optimizers.deserialize(tc['optimizer_config'], custom_objects), loss=loss,
-                      metrics=tc.get('metrics') or None)
+                      metrics=tc.get('metrics') or None, loss_weights=tc.get('loss_weights'))
         if 'optimizer_weights' in root:
             _restore_optimizer(model, root['optimizer_weights'])
     return model

@@ -72,6 +72,43 @@ def _take(x, idx):
     return _Multi(a[idx] for a in x) if isinstance(x, _Multi) else x[idx]
 
 
+def _float(out):
+    return [o.float() for o in out] if isinstance(out, (list, tuple)) else out.float()
+
+
+def _head(out, rows):
+    return [o.float()[:rows] for o in out] if isinstance(out, (list, tuple)) else out.float()[:rows]
+
+
+def _join(blocks):
+    """Row blocks of predictions -> one array, or one array per output."""
+    if isinstance(blocks[0], (list, tuple)):
+        return [torch.cat([b[i] for b in blocks], dim=0).cpu().numpy() for i in range(len(blocks[0]))]
+    return torch.cat(blocks, dim=0).cpu().numpy()
+
+
+def _detach(out):
+    return [o.detach() for o in out] if isinstance(out, (list, tuple)) else out.detach()
+
+
+class _PerOutput:
+    """The loss or a metric of ONE output of a model with several outputs, as a function of all targets and all outputs -
+    the shape every training / evaluation loop of this module works with."""
+
+    def __init__(self, fn, index):
+        self.fn, self.index = fn, index
+        self.stateful = bool(getattr(fn, 'stateful', False))
+
+    def __call__(self, ys, outs):
+        return self.fn(ys[self.index], outs[self.index])
+
+    def reset_state(self):
+        self.fn.reset_state()
+
+    def result(self):
+        return self.fn.result()
+
+
 class History:
     """``History.history`` maps metric name -> list of per-epoch values (Keras semantics)."""
 
@@ -549,9 +586,13 @@ class Model:
     # --------------------------------------------------------------- compile
     def compile(self, optimizer='rmsprop', loss=None, metrics=None, **kwargs):
         new_opt = _optimizers.get(optimizer)
+        metrics_arg = metrics
         metrics = list(metrics) if metrics else []
         signature = (json.dumps(_optimizers.serialize(new_opt), sort_keys=True, default=str),
-                     _losses.canonical_name(loss), tuple(str(m) for m in metrics))
+                     _losses.canonical_name(loss) if not isinstance(loss, (list, tuple, dict)) or
+                     (isinstance(loss, dict) and 'class_name' in loss) else repr(loss),
+                     tuple(str(m) for m in metrics) if not isinstance(metrics_arg, dict) else repr(metrics_arg),
+                     repr(kwargs.get('loss_weights')))
         # (the device is not part of the signature: ``to()`` drops the engines itself, and a model that was compiled on
         # the host and moved to the GPU by its first fit would otherwise rebuild engine and graphs in its second fit)
         unchanged = self._compiled and getattr(self, '_compile_signature', None) == signature
@@ -569,12 +610,18 @@ class Model:
         self._wopt_cache = None
         self.optimizer = new_opt
         self.loss = loss
-        self._loss_name = _losses.canonical_name(loss)
-        self._loss_fn = _losses.get(loss, self.custom_objects)
-        self.compiled_metrics = _CompiledMetrics(list(metrics) if metrics else None)
-        out_shape = self.output_shape
-        out_dim = out_shape[-1] if out_shape and not isinstance(out_shape[0], (tuple, list)) else None
-        self._metric_fns = [_metrics.resolve(m, self._loss_name, out_dim, self.custom_objects) for m in metrics]
+        self.loss_weights = kwargs.get('loss_weights')
+        self.compiled_metrics = _CompiledMetrics((metrics_arg if isinstance(metrics_arg, dict) else list(metrics)) if metrics else None)
+        if len(self._outputs) > 1:
+            self._compile_outputs(loss, metrics_arg or [], self.loss_weights)
+        else:
+            if isinstance(loss, (list, tuple)) and len(loss) == 1:
+                loss = self.loss = loss[0]
+            self._loss_name = _losses.canonical_name(loss)
+            self._loss_fn = _losses.get(loss, self.custom_objects)
+            out_shape = self.output_shape
+            out_dim = out_shape[-1] if out_shape and not isinstance(out_shape[0], (tuple, list)) else None
+            self._metric_fns = [_metrics.resolve(m, self._loss_name, out_dim, self.custom_objects) for m in metrics]
         self.metrics_names = ['loss'] + [n for n, _ in self._metric_fns]
         self._compiled = True
         self._compile_signature = signature
@@ -586,6 +633,66 @@ class Model:
         self._sync_from_engine()
         self._engine = None
         self._infer_engine = None
+
+    def _compile_outputs(self, loss, metrics, loss_weights):
+        """Several outputs: one loss per output (one name for all, a list in output order, or a dict by output-layer name),
+        optional ``loss_weights``, metrics for all outputs or per output. The total loss is the weighted sum; the reported
+        names follow Keras: ``loss``, ``<output>_loss`` ..., ``<output>_<metric>`` ..."""
+        names = [t.layer.name for t in self._outputs]
+
+        def per_output(value, what, default=None):
+            if isinstance(value, dict) and 'class_name' not in value:
+                unknown = set(value) - set(names)
+                if unknown:
+                    raise ValueError("%s refers to unknown outputs %s (outputs: %s)" % (what, sorted(unknown), names))
+                return [value.get(n, default) for n in names]
+            if isinstance(value, (list, tuple)):
+                if len(value) != len(names):
+                    raise ValueError("%s has %d entries for %d outputs" % (what, len(value), len(names)))
+                return list(value)
+            return [value] * len(names)
+
+        losses = per_output(loss, 'loss')
+        if any(l is None for l in losses):
+            raise ValueError("every output needs a loss (outputs: %s)" % names)
+        weights = [1.0 if w is None else float(w) for w in per_output(loss_weights, 'loss_weights', 1.0)]
+        parts = [_PerOutput(_losses.get(l, self.custom_objects), i) for i, l in enumerate(losses)]
+
+        def total(ys, outs):
+            value = weights[0] * parts[0](ys, outs)
+            for w, part in zip(weights[1:], parts[1:]):
+                value = value + w * part(ys, outs)
+            return value
+
+        self._loss_fn, self._loss_name = total, 'weighted_sum(%s)' % ', '.join(_losses.canonical_name(l) for l in losses)
+        fns = [(n + '_loss', part) for n, part in zip(names, parts)]
+        if isinstance(metrics, dict) or (metrics and all(isinstance(m, (list, tuple)) for m in metrics)):
+            chosen = per_output(metrics, 'metrics', [])
+        else:
+            chosen = [list(metrics)] * len(names)
+        for i, (n, ms) in enumerate(zip(names, chosen)):
+            ms = [ms] if isinstance(ms, str) or callable(ms) else list(ms or [])
+            shape = self._outputs[i].shape
+            for m in ms:
+                label, fn = _metrics.resolve(m, _losses.canonical_name(losses[i]), shape[-1], self.custom_objects)
+                fns.append(('%s_%s' % (n, label), _PerOutput(fn, i)))
+        self._metric_fns = fns
+
+    def _host_y(self, y):
+        """Targets: one array, or for several outputs a list in output order / a dict by output-layer name."""
+        if len(self._outputs) == 1:
+            if isinstance(y, (list, tuple)) and len(y) == 1 and isinstance(y[0], (np.ndarray, torch.Tensor)) \
+                    and y[0].ndim == len(self._outputs[0].shape):
+                y = y[0]   # [array] for the single output (a list holding ONE ROW stays a batch of one row)
+            return y if isinstance(y, torch.Tensor) else np.asarray(y)
+        if isinstance(y, dict):
+            y = [y[t.layer.name] for t in self._outputs]
+        if not isinstance(y, (list, tuple)) or len(y) != len(self._outputs):
+            raise ValueError("this model has %d outputs: pass a list of %d target arrays" % (len(self._outputs), len(self._outputs)))
+        return _Multi(a if isinstance(a, torch.Tensor) else np.asarray(a) for a in y)
+
+    def _device_y(self, y):
+        return _Multi(_as_tensor(a, self._device) for a in y) if isinstance(y, _Multi) else _as_tensor(y, self._device)
 
     def _require_compiled(self):
         if not self._compiled:
@@ -634,7 +741,7 @@ class Model:
             p.grad = None
         with self._autocast(xb):
             out = self(xb, training=True)
-        out = out.float()
+        out = _float(out)
         per_sample = self._loss_fn(yb, out)
         if wb is not None:  # Keras' sum-over-batch-size reduction: sum(w * loss) / rows
             per_sample = per_sample * wb.reshape(per_sample.shape[0], *([1] * (per_sample.dim() - 1)))
@@ -649,7 +756,7 @@ class Model:
         with torch.no_grad():
             stats = [float(loss.detach())]
             for _, fn in self._metric_fns:
-                stats.append(float(fn(yb, out.detach()).mean()))
+                stats.append(float(fn(yb, _detach(out)).mean()))
         return stats
 
     def _tune_cpu_threads(self, rows):
@@ -690,7 +797,7 @@ class Model:
             stats = eng.train_on_batch(x, y)
         else:
             xb = self._device_x(self._host_x(x))
-            yb = _as_tensor(y, self._device)
+            yb = self._device_y(self._host_y(y))
             self._tune_cpu_threads(_rows(xb))
             te = self._torch_engine() if row_weight is None else None
             if te is not None:
@@ -735,16 +842,18 @@ class Model:
             raise TypeError("fit() got unexpected keyword argument(s) %s" % sorted(unknown))
         batch_size = int(batch_size or 32)
         x = self._host_x(x)
-        y = np.asarray(y) if not isinstance(y, torch.Tensor) else y
+        y = self._host_y(y)
         n_total = _rows(x)
-        row_weight = _row_weights(y, sample_weight, class_weight)
+        if class_weight and isinstance(y, _Multi):
+            raise ValueError("class_weight is only supported for models with one output")
+        row_weight = _row_weights(y[0] if isinstance(y, _Multi) else y, sample_weight, class_weight)
         x_val = y_val = None
         if validation_data is not None:
             x_val, y_val = validation_data[0], validation_data[1]
         elif validation_split and 0.0 < validation_split < 1.0:
             split_at = int(n_total * (1.0 - validation_split))
             x, x_val = _take(x, slice(None, split_at)), _take(x, slice(split_at, None))
-            y, y_val = y[:split_at], y[split_at:]
+            y, y_val = _take(y, slice(None, split_at)), _take(y, slice(split_at, None))
             row_weight = row_weight[:split_at] if row_weight is not None else None
         history = History()
         from .callbacks import CallbackList
@@ -774,7 +883,7 @@ class Model:
             return history
         self._tune_cpu_threads(batch_size)
         xt = self._device_x(x)
-        yt = _as_tensor(y, self._device)
+        yt = self._device_y(y)
         n = _rows(xt)
         wt = torch.as_tensor(row_weight, dtype=torch.float32, device=self._device) if row_weight is not None else None
         names = self.metrics_names
@@ -795,7 +904,7 @@ class Model:
                     graphed_rows += len(idx)  # loss / metric sums stay on the device until the epoch ends
                     continue
                 te = None
-                stats = self._torch_train_step(_take(xt, idx), yt[idx], wt[idx] if wt is not None else None)
+                stats = self._torch_train_step(_take(xt, idx), _take(yt, idx), wt[idx] if wt is not None else None)
                 for i, s in enumerate(stats):
                     sums[i] += s * len(idx)
             if graphed_rows:
@@ -808,7 +917,7 @@ class Model:
             logs.update(self._stateful_results())
             validate = (epoch + 1) in validation_freq if isinstance(validation_freq, (list, tuple)) \
                 else (epoch + 1) % int(validation_freq) == 0
-            if x_val is not None and len(y_val) and validate:
+            if x_val is not None and _rows(y_val) and validate:
                 val = self.evaluate(x_val, y_val, batch_size=batch_size, verbose=0)
                 val = val if isinstance(val, list) else [val]
                 logs.update({'val_' + k: v for k, v in zip(names, val)})
@@ -858,14 +967,14 @@ class Model:
                 pad = torch.zeros((block - xb.shape[0],) + tuple(xb.shape[1:]), dtype=xb.dtype, device=xb.device)
                 with self._autocast(xb):
                     o = self(torch.cat([xb, pad], dim=0), training=False)
-                outs.append(o.float()[:xb.shape[0]])
+                outs.append(_head(o, xb.shape[0]))
             else:
                 with self._autocast(xb):
                     o = self(xb, training=False)
-                outs.append(o.float())
+                outs.append(_float(o))
         if not outs:
             return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
-        return torch.cat(outs, dim=0).cpu().numpy()
+        return _join(outs)
 
     def _predict_multi(self, xt):
         """Several inputs: the same fixed row blocks as above, every input cut and padded alike."""
@@ -877,10 +986,10 @@ class Model:
                 xb = _Multi(torch.cat([a, a.new_zeros((block - rows,) + tuple(a.shape[1:]))], dim=0) for a in xb)
             with self._autocast(xb):
                 o = self(xb, training=False)
-            outs.append(o.float()[:rows])
+            outs.append(_head(o, rows))
         if not outs:
             return np.zeros((0,) + tuple(d for d in self.output_shape[1:]), dtype=np.float32)
-        return torch.cat(outs, dim=0).cpu().numpy()
+        return _join(outs)
 
     @torch.no_grad()
     def evaluate(self, x=None, y=None, batch_size=None, verbose=0, return_dict=False, **kwargs):
@@ -898,17 +1007,17 @@ class Model:
             stats = eng.evaluate(x, y)
             return stats if len(stats) > 1 else stats[0]
         xt = self._device_x(self._host_x(x))
-        yt = _as_tensor(y, self._device)
+        yt = self._device_y(self._host_y(y))
         n = _rows(xt)
         sums = [0.0] * len(self.metrics_names)
         self._reset_metrics()
         step = max(batch_size, 8192)
         self._tune_cpu_threads(min(step, max(n, 1)))
         for start in range(0, n, step):
-            xb, yb = _take(xt, slice(start, start + step)), yt[start:start + step]
+            xb, yb = _take(xt, slice(start, start + step)), _take(yt, slice(start, start + step))
             with self._autocast(xb):
                 out = self(xb, training=False)
-            out = out.float()
+            out = _float(out)
             vals = [self._loss_fn(yb, out)] + [fn(yb, out) for _, fn in self._metric_fns]
             for i, v in enumerate(vals):
                 sums[i] += float(v.double().sum())

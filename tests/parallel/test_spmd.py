@@ -16,10 +16,10 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _launch(tmp_path, mode, ps, freq):
+def _launch(tmp_path, mode, ps, freq, *extra):
     cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node=2',
            '--master-addr', '127.0.0.1', '--master-port', str(_free_port()),
-           os.path.join(HERE, 'spmd_script.py'), mode, ps, freq, str(_free_port()), str(tmp_path)]
+           os.path.join(HERE, 'spmd_script.py'), mode, ps, freq, str(_free_port()), str(tmp_path)] + list(extra)
     env = dict(os.environ, SPARK_LOCAL_IP='127.0.0.1', OMP_NUM_THREADS='2')
     res = subprocess.run(cmd, env=env, capture_output=True, text=True, timeout=300)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-4000:]
@@ -39,6 +39,17 @@ def test_two_ranks(tmp_path, mode, ps, freq):
     assert r0['eval'][0] < r0['before'][0]
     if mode == 'synchronous':
         assert r0['hist'] == 2
+
+
+@pytest.mark.parametrize('mode,ps', [('synchronous', 'none'), ('asynchronous', 'socket')])
+def test_two_ranks_with_penalties_constraints_callbacks_and_class_weights(tmp_path, mode, ps):
+    """The Keras features that the fused paths do not implement take the generic worker loop on every rank: the ranks
+    still agree on the result, each worker's callbacks saw its epochs, the constraint holds on the master weights."""
+    r0, r1 = _launch(tmp_path, mode, ps, 'epoch', 'features')
+    assert abs(r0['digest'] - r1['digest']) < 1e-3 * max(1.0, abs(r0['digest']))
+    assert r0['argmax'] == r1['argmax'] and r0['eval'][0] < r0['before'][0]
+    assert r0['epochs_seen'] == [0, 1] and r1['epochs_seen'] == [0, 1]   # one worker per rank, both epochs each
+    assert r0['max_col_norm'] <= 4.0 + 1e-3
 
 
 def test_cpulist_parser_and_numa_binding_is_harmless_without_a_gpu():

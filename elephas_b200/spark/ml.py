@@ -395,7 +395,10 @@ class _WithData:
         for k, v in meta.get('paramMap', {}).items():
             if inst.hasParam(k):
                 inst._paramMap[inst.getParam(k)] = v
-        with open(os.path.join(path, 'data', 'part-00000')) as fh:
+        data = os.path.join(path, 'data', 'part-00000')
+        if not os.path.exists(data):
+            raise IOError("%s holds no fitted state (%s is missing): it was not written by this version" % (path, data))
+        with open(data) as fh:
             state = json.load(fh)
         for k in cls._state:
             v = state.get(k)

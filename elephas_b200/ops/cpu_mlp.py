@@ -66,6 +66,8 @@ class CpuMlpStep:
     def __init__(self, model, ops, out_act, loss_name):
         self.model, self.ops, self.out_act, self.loss_name = model, ops, out_act, loss_name
         self.rng = np.random.default_rng(int(torch.randint(0, 2 ** 31 - 1, (1,))))  # dropout masks (see _dropout_mask)
+        penalties, constraints, _ = model._weight_options()
+        self.regularized, self.constrained = bool(penalties), bool(constraints)
 
     @torch.no_grad()
     def __call__(self, xb, yb):
@@ -119,8 +121,20 @@ class CpuMlpStep:
         params = []
         for op in ops:
             params += [op.layer.kernel, op.layer.bias]
+        penalty = 0.0
+        if self.regularized:  # L1 / L2 penalties of the layer configs: closed-form gradient, value added to the loss
+            where = {id(p): k for k, p in enumerate(params)}
+            for w, reg in model._weight_options()[0]:
+                g = grads[where[id(w)]]
+                if reg.l2:
+                    g.add_(w, alpha=2.0 * reg.l2)
+                if reg.l1:
+                    g.add_(torch.sign(w), alpha=reg.l1)
+                penalty += float(reg(w))
         model.optimizer.apply_gradients(params, grads)
-        stats = [float(model._loss_fn(yb, out).mean())]
+        if self.constrained:
+            model._apply_constraints()
+        stats = [float(model._loss_fn(yb, out).mean()) + penalty]
         for _, fn in model._metric_fns:
             stats.append(float(fn(yb, out).mean()))
         return stats
@@ -130,8 +144,12 @@ def maybe_create(model):
     """A :class:`CpuMlpStep` for a compiled Dense chain on the CPU, or None (autograd path)."""
     if not enabled() or model.device.type != 'cpu' or not getattr(model, '_compiled', False):
         return None
-    if model.has_weight_options() or any(getattr(fn, 'stateful', False) for _, fn in model._metric_fns):
-        return None  # penalties, constraints and count-based metrics live on the autograd path
+    if any(getattr(fn, 'stateful', False) for _, fn in model._metric_fns):
+        return None  # count-based metrics live on the autograd path
+    from ..models.regularizers import L1L2
+    penalties, _, activity = model._weight_options()
+    if activity or any(not isinstance(reg, L1L2) for _, reg in penalties):
+        return None  # activity penalties and penalties without a closed-form gradient here: autograd
     from . import engine as _engine  # (only its pure-Python plan builder is used: no native library needed)
     try:
         plan = _engine._plan(model)

@@ -74,3 +74,36 @@ def test_dropout_chain_trains_and_other_models_stay_on_the_tape():
     clipped = Sequential([Dense(4, input_dim=20, activation='relu'), Dense(1)])
     clipped.compile(SGD(learning_rate=0.1, clipnorm=1.0), 'mse')
     assert clipped._cpu_step() is None
+
+
+def test_penalties_and_constraints_stay_on_the_cpu_step(monkeypatch):
+    """L1 / L2 penalties (closed-form gradient) and constraints do not cost a Dense chain its hand-written CPU step; the
+    result equals the autograd path. Activity penalties do go to autograd."""
+    import numpy as np
+    import torch
+    from elephas_b200.models import Dense, Sequential, constraints, regularizers
+    from elephas_b200.models.optimizers import Adam
+
+    def build(**first):
+        torch.manual_seed(1)
+        m = Sequential([Dense(16, activation='relu', input_shape=(8,), kernel_regularizer=regularizers.l1_l2(1e-3, 1e-2),
+                              bias_regularizer='l2', kernel_constraint=constraints.MaxNorm(0.8), **first),
+                        Dense(3, activation='softmax', kernel_regularizer='l2', bias_constraint='non_neg')])
+        m.compile(Adam(0.05), 'categorical_crossentropy', ['acc'])
+        return m
+
+    rng = np.random.default_rng(0)
+    x = rng.standard_normal((64, 8)).astype('float32')
+    y = np.eye(3, dtype='float32')[rng.integers(0, 3, 64)]
+    fast = build()
+    assert fast._cpu_step() is not None
+    assert build(activity_regularizer='l1')._cpu_step() is None
+    monkeypatch.setenv('ELEPHAS_B200_CPU_ENGINE', '0')
+    tape = build()
+    assert tape._cpu_step() is None
+    for _ in range(5):
+        a, b = fast.train_on_batch(x, y), tape.train_on_batch(x, y)
+        assert a[0] == pytest.approx(b[0], rel=1e-5) and a[1] == b[1]
+    for wa, wb in zip(fast.get_weights(), tape.get_weights()):
+        np.testing.assert_allclose(wa, wb, rtol=1e-4, atol=1e-6)
+    assert np.all(np.linalg.norm(fast.get_weights()[0], axis=0) <= 0.8 + 1e-5) and np.all(fast.get_weights()[3] >= 0)

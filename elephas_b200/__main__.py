@@ -10,7 +10,7 @@ import sys
 
 KNOBS = ('DEVICE', 'NATIVE', 'GRAPHS', 'TORCH_GRAPHS', 'NATIVE_CONV', 'FUSE_BN', 'FUSED_MLP', 'FUSED_MLP_WIDE', 'FUSED_PULL',
          'NVLS', 'SHARDED_MASTER', 'COMM_BLOCKS', 'COMM_TAIL_BLOCKS', 'SIDE_STREAM', 'HOST_BF16', 'HOST_THREADS', 'NUMA_BIND',
-         'CPU_ENGINE', 'CPU_THREADS', 'CPU_PARALLEL_WORKERS', 'FORCE_LOCAL_SPARK', 'TRACE')
+         'CPU_ENGINE', 'CPU_THREADS', 'CPU_PARALLEL_WORKERS', 'PS_TIMEOUT', 'FORCE_LOCAL_SPARK', 'TRACE')
 
 
 def info():

@@ -7,13 +7,42 @@ servers (``SocketClient(ack=False)``; the default adds an acknowledged update op
 are kernels that read and update master weights resident in (peer) HBM - no host round trip.
 """
 import abc
+import os
 import pickle
 import socket
+import time
+import urllib.error
 import urllib.request
 
 import numpy as np
 
 from ..utils.sockets import determine_master, receive, send
+
+
+def _timeout():
+    """Seconds a request may take before the worker gives up on the server (``ELEPHAS_B200_PS_TIMEOUT``, default 120):
+    a server that died must fail the fit, not hang it."""
+    return float(os.environ.get('ELEPHAS_B200_PS_TIMEOUT', '120'))
+
+
+def _refused(exc):
+    reason = getattr(exc, 'reason', exc)
+    return isinstance(reason, ConnectionRefusedError)
+
+
+def _when_listening(request, attempts=6, first_wait=0.05):
+    """Run ``request()``; a REFUSED connection (the server thread has not bound its port yet, or is restarting) is tried
+    again with doubling waits. Nothing has been sent in that case, so repeating is safe for pushes too; any other failure -
+    a reset in the middle of a request, a timeout - is raised: the server may have applied the update already."""
+    wait = first_wait
+    for attempt in range(attempts):
+        try:
+            return request()
+        except (ConnectionRefusedError, urllib.error.URLError) as exc:
+            if not _refused(exc) or attempt == attempts - 1:
+                raise
+            time.sleep(wait)
+            wait *= 2
 
 
 class BaseParameterClient(abc.ABC):
@@ -54,8 +83,12 @@ class HttpClient(BaseParameterClient):
 
     def _open(self, path, body=None):
         request = urllib.request.Request('http://%s/%s' % (self.master_url, path), data=body, headers=self.headers)
-        with urllib.request.urlopen(request) as response:
-            return response.read()
+
+        def once():
+            with urllib.request.urlopen(request, timeout=_timeout()) as response:
+                return response.read()
+
+        return _when_listening(once)
 
     def get_parameters(self):
         return pickle.loads(self._open('parameters'))
@@ -78,10 +111,18 @@ class SocketClient(BaseParameterClient):
 
     def _connect(self):
         host = determine_master(port=self.port).split(':')[0]
-        sock = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
-        sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
-        sock.connect((host, self.port))
-        return sock
+        def once():
+            sock = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+            sock.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)
+            sock.settimeout(_timeout())
+            try:
+                sock.connect((host, self.port))
+            except BaseException:
+                sock.close()
+                raise
+            return sock
+
+        return _when_listening(once)
 
     def get_parameters(self):
         with self._connect() as sock:

@@ -253,3 +253,48 @@ def test_socket_server_speaks_the_reference_frames_and_survives_half_a_frame():
         assert all(np.allclose(a, b - 1.5) for a, b in zip(acked.get_parameters(), w0))
     finally:
         server.stop()
+
+
+def test_clients_wait_for_a_server_that_is_not_listening_yet_and_give_up_on_a_dead_one(monkeypatch):
+    """A refused connection is retried (the server thread may not have bound its port yet); a server that never comes up,
+    or one that accepts and never answers, fails the request instead of hanging the worker."""
+    import socket
+    import threading
+    import time
+
+    from elephas_b200.parameter import client as C
+
+    with socket.socket() as probe:
+        probe.bind(('127.0.0.1', 0))
+        port = probe.getsockname()[1]
+    monkeypatch.setenv('SPARK_LOCAL_IP', '127.0.0.1')
+    started = time.time()
+    with pytest.raises(ConnectionRefusedError):
+        C.SocketClient(port).get_parameters()
+    assert time.time() - started >= 0.05 * (1 + 2 + 4 + 8 + 16) * 0.9      # it did wait between its attempts
+
+    calls = []
+
+    def flaky():
+        calls.append(1)
+        if len(calls) < 3:
+            raise ConnectionRefusedError()
+        return 'up'
+
+    assert C._when_listening(flaky) == 'up' and len(calls) == 3
+    with pytest.raises(ConnectionResetError):   # anything but "refused" is not repeated: the update may have been applied
+        C._when_listening(lambda: (_ for _ in ()).throw(ConnectionResetError()))
+
+    silent = socket.socket()
+    silent.bind(('127.0.0.1', 0))
+    silent.listen(1)
+    monkeypatch.setenv('ELEPHAS_B200_PS_TIMEOUT', '0.3')
+    holder = []
+    t = threading.Thread(target=lambda: holder.append(silent.accept()), daemon=True)
+    t.start()
+    with pytest.raises((socket.timeout, TimeoutError)):
+        C.SocketClient(silent.getsockname()[1]).get_parameters()
+    t.join(2)
+    for conn, _ in holder:
+        conn.close()
+    silent.close()

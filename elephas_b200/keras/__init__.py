@@ -10,5 +10,6 @@ The reference has no model code of its own: every script it runs builds a ``tens
 """
 from . import (callbacks, constraints, initializers, layers, losses, metrics, models, optimizers, preprocessing,  # noqa: F401
                regularizers, utils)
+from ..models import mixed_precision  # noqa: F401
 from .layers import Input  # noqa: F401
 from .models import Model, Sequential  # noqa: F401

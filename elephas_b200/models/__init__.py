@@ -3,7 +3,8 @@
 ``from elephas_b200.models import Sequential, Dense, ...`` plays the role that
 ``tensorflow.keras`` plays for the reference (which has no model code of its own).
 """
-from . import activations, constraints, losses, metrics, optimizers, regularizers, schedules  # noqa: F401
+from . import (activations, constraints, losses, metrics, mixed_precision, optimizers, regularizers,  # noqa: F401
+               schedules)
 from .layers import (Activation, Add, AveragePooling2D, BatchNormalization, Concatenate, Conv2D, Dense,  # noqa: F401
                      Dropout, Flatten, GlobalAveragePooling2D, Input, InputLayer, Layer, MaxPooling2D, ReLU,
                      Reshape, Softmax, ZeroPadding2D)

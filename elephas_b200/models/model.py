@@ -156,6 +156,8 @@ class Model:
         self._engine = None
         self._engine_key = None
         self.custom_objects = {}
+        from . import mixed_precision
+        self._compute_dtype = mixed_precision.compute_dtype()  # the global policy at construction time, as in Keras
         if inputs is not None:
             self._init_graph(inputs, outputs)
 

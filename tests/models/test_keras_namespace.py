@@ -46,3 +46,27 @@ def test_namespace_lists_every_layer_and_initializers_check_their_arguments():
         keras.initializers.Zeros(seed=1)
     assert keras.optimizers.get('adamw').weight_decay == 0.004
     assert keras.constraints.max_norm(3).max_value == 3.0
+
+
+def test_global_dtype_policy_sets_the_compute_dtype_of_new_models():
+    import pytest
+
+    from elephas_b200.keras import mixed_precision
+    from elephas_b200.keras.layers import Dense
+    from elephas_b200.keras.models import Sequential
+    assert mixed_precision.global_policy().name == 'float32'
+    before = Sequential([Dense(2, input_shape=(3,))])
+    try:
+        mixed_precision.set_global_policy('mixed_bfloat16')
+        policy = mixed_precision.global_policy()
+        assert policy.compute_dtype == 'bfloat16' and policy.variable_dtype == 'float32'
+        after = Sequential([Dense(2, input_shape=(3,))])
+        assert after._compute_dtype == 'bfloat16' and before._compute_dtype == 'float32'
+        assert after.get_weights()[0].dtype == np.float32            # master weights stay fp32
+        after.compile('sgd', 'mse')
+        after.fit(np.zeros((8, 3), np.float32), np.zeros((8, 2), np.float32), epochs=1, batch_size=4)   # on a CPU: plain fp32
+        with pytest.raises(ValueError):
+            mixed_precision.set_global_policy('mixed_float16')
+    finally:
+        mixed_precision.set_global_policy(mixed_precision.Policy('float32'))
+    assert Sequential([Dense(2, input_shape=(3,))])._compute_dtype == 'float32'

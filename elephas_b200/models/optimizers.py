@@ -34,7 +34,10 @@ class Optimizer:
         # keys of the Keras 2.11+ / Keras 3 optimizer configs: decoupled weight decay is applied, the switches that have
         # no meaning here are accepted when they are off
         self.weight_decay = kwargs.pop('weight_decay', self._default_weight_decay) or None
-        for key in ('use_ema', 'gradient_accumulation_steps', 'loss_scale_factor'):
+        self.gradient_accumulation_steps = int(kwargs.pop('gradient_accumulation_steps', None) or 0) or None
+        if self.gradient_accumulation_steps is not None and self.gradient_accumulation_steps < 2:
+            raise ValueError("gradient_accumulation_steps must be >= 2 (or None), got %r" % self.gradient_accumulation_steps)
+        for key in ('use_ema', 'loss_scale_factor'):
             if kwargs.pop(key, None):
                 raise ValueError("%s: %s is not supported" % (self._class_name, key))
         for key in ('ema_momentum', 'ema_overwrite_frequency', 'jit_compile', 'is_legacy_optimizer'):
@@ -79,7 +82,7 @@ class Optimizer:
         if self.schedule is not None:
             from . import schedules
             cfg['learning_rate'] = schedules.serialize(self.schedule)
-        for k in ('clipnorm', 'clipvalue', 'global_clipnorm', 'weight_decay'):
+        for k in ('clipnorm', 'clipvalue', 'global_clipnorm', 'weight_decay', 'gradient_accumulation_steps'):
             if getattr(self, k) is not None:
                 cfg[k] = getattr(self, k)
         return cfg
@@ -115,6 +118,7 @@ class Optimizer:
     def reset_state(self):
         self.iterations = 0
         self._slots = {}
+        self._held = None
 
     def _clip(self, grads):
         if self.clipvalue is not None:
@@ -130,8 +134,21 @@ class Optimizer:
     @torch.no_grad()
     def apply_gradients(self, params, grads):
         """``params[i] -= step(grads[i])`` in place; advances ``iterations``."""
-        grads = self._clip(list(grads))
-        params = list(params)
+        grads, params = list(grads), list(params)
+        if self.gradient_accumulation_steps:
+            # the gradients of k calls are averaged and applied on the k-th (an update every k batches, as Keras 3 does)
+            held = self.__dict__.setdefault('_held', None)
+            if held is None:
+                self._held, self._held_calls = [g.clone() for g in grads], 1
+            else:
+                for h, g in zip(held, grads):
+                    h.add_(g)
+                self._held_calls += 1
+            if self._held_calls < self.gradient_accumulation_steps:
+                return
+            grads = [h.div_(self._held_calls) for h in self._held]
+            self._held = None
+        grads = self._clip(grads)
         if self.weight_decay:  # decoupled (AdamW-style): w <- w - lr * wd * w, before the gradient step
             shrink = 1.0 - self._lr_t() * float(self.weight_decay)
             for p in params:

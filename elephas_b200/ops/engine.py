@@ -147,8 +147,8 @@ def _optimizer_spec(opt):
         return None
     if opt.clipnorm is not None or opt.clipvalue is not None or opt.global_clipnorm is not None:
         return None
-    if getattr(opt, 'weight_decay', None):
-        return None  # decoupled weight decay is not in the optimizer kernels
+    if getattr(opt, 'weight_decay', None) or getattr(opt, 'gradient_accumulation_steps', None):
+        return None  # decoupled weight decay / accumulation over several batches are not in the optimizer kernels
     if getattr(opt, 'schedule', None) is not None:
         return None  # the kernels take the rate as a launch argument that a captured graph freezes
     return native.OPT_IDS[opt._class_name]

@@ -109,3 +109,32 @@ def test_adamw_and_the_newer_optimizer_config_keys(tmp_path):
     b = back.train_on_batch(x[:16], y[:16])
     assert a == pytest.approx(b, rel=1e-6)
     np.testing.assert_allclose(back.get_weights()[0], m.get_weights()[0], rtol=1e-5, atol=1e-7)
+
+
+def test_gradient_accumulation_applies_the_mean_every_k_calls():
+    w = torch.zeros(2, requires_grad=True)
+    opt = optimizers.SGD(0.5, gradient_accumulation_steps=3)
+    grads = [torch.tensor([1.0, 2.0]), torch.tensor([3.0, 0.0]), torch.tensor([2.0, 4.0]), torch.tensor([1.0, 1.0])]
+    seen = []
+    for g in grads:
+        opt.apply_gradients([w], [g])
+        seen.append(w.detach().tolist())
+    assert seen == [[0.0, 0.0], [0.0, 0.0], [-1.0, -1.0], [-1.0, -1.0]] and opt.iterations == 1
+    back = optimizers.deserialize(optimizers.serialize(opt))
+    assert back.gradient_accumulation_steps == 3
+    with pytest.raises(ValueError):
+        optimizers.SGD(gradient_accumulation_steps=1)
+    from elephas_b200.ops.engine import _optimizer_spec
+    assert _optimizer_spec(opt) is None
+    # k batches of size b with accumulation == one batch of size k * b without (plain SGD, mean-reduced loss)
+    rng = np.random.default_rng(0)
+    x, y = rng.standard_normal((48, 5)).astype(np.float32), rng.standard_normal((48, 1)).astype(np.float32)
+    big = Sequential([Dense(4, activation='tanh', input_shape=(5,)), Dense(1)])
+    small = Sequential([Dense(4, activation='tanh', input_shape=(5,)), Dense(1)])
+    small.set_weights(big.get_weights())
+    big.compile(optimizers.SGD(0.1), 'mse')
+    small.compile(optimizers.SGD(0.1, gradient_accumulation_steps=3), 'mse')
+    big.fit(x, y, batch_size=48, epochs=1, shuffle=False)
+    small.fit(x, y, batch_size=16, epochs=1, shuffle=False)
+    for a, b in zip(big.get_weights(), small.get_weights()):
+        np.testing.assert_allclose(a, b, rtol=1e-5, atol=1e-6)

@@ -303,7 +303,7 @@ class Model:
                     mask = None
                 if mask is not None:
                     masks[key] = mask
-            if training and t.layer.activity_regularizer is not None:
+            if t.layer.activity_regularizer is not None:   # (noted in evaluation too: Keras reports the penalties there)
                 out = values[key]
                 self._activity_terms.append(t.layer.activity_regularizer(out) / out.shape[0])
         outs = [values[(id(o.layer), o.node_index)] for o in self._outputs]
@@ -1023,6 +1023,9 @@ class Model:
             vals = [self._loss_fn(yb, out)] + [fn(yb, out) for _, fn in self._metric_fns]
             for i, v in enumerate(vals):
                 sums[i] += float(v.double().sum())
+            penalty = self._regularization_loss()   # weight / activity penalties are part of the reported loss, as in Keras
+            if penalty is not None:
+                sums[0] += float(penalty) * _rows(xb)
         stats = [s / n if n else 0.0 for s in sums]
         final = self._stateful_results()
         stats = [final.get(name, v) for name, v in zip(self.metrics_names, stats)]

@@ -154,6 +154,16 @@ def canonical_name(identifier):
     return CANONICAL.get(identifier, identifier)
 
 
+def family_name(identifier):
+    """The named function a loss belongs to, whatever its options (``SparseCategoricalCrossentropy(from_logits=True)`` ->
+    ``'sparse_categorical_crossentropy'``): what ``'accuracy'`` is resolved against."""
+    if isinstance(identifier, dict) and 'class_name' in identifier:
+        identifier = deserialize(identifier)
+    if isinstance(identifier, Loss):
+        return identifier.function
+    return canonical_name(identifier)
+
+
 def get(identifier, custom_objects=None):
     if isinstance(identifier, dict):
         identifier = deserialize(identifier, custom_objects)

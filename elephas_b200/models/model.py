@@ -623,7 +623,8 @@ class Model:
             self._loss_fn = _losses.get(loss, self.custom_objects)
             out_shape = self.output_shape
             out_dim = out_shape[-1] if out_shape and not isinstance(out_shape[0], (tuple, list)) else None
-            self._metric_fns = [_metrics.resolve(m, self._loss_name, out_dim, self.custom_objects) for m in metrics]
+            family = _losses.family_name(loss)
+            self._metric_fns = [_metrics.resolve(m, family, out_dim, self.custom_objects) for m in metrics]
         self.metrics_names = ['loss'] + [n for n, _ in self._metric_fns]
         self._compiled = True
         self._compile_signature = signature
@@ -676,7 +677,7 @@ class Model:
             ms = [ms] if isinstance(ms, str) or callable(ms) else list(ms or [])
             shape = self._outputs[i].shape
             for m in ms:
-                label, fn = _metrics.resolve(m, _losses.canonical_name(losses[i]), shape[-1], self.custom_objects)
+                label, fn = _metrics.resolve(m, _losses.family_name(losses[i]), shape[-1], self.custom_objects)
                 fns.append(('%s_%s' % (n, label), _PerOutput(fn, i)))
         self._metric_fns = fns
 

@@ -66,3 +66,17 @@ def test_a_logits_model_trains_and_its_loss_object_survives_a_model_file(tmp_pat
     n = Sequential([Dense(3, activation='softmax', input_shape=(6,))])
     n.compile('sgd', losses.CategoricalCrossentropy())
     assert n._loss_name == 'categorical_crossentropy' and n._loss_fn is losses.categorical_crossentropy
+
+
+def test_accuracy_follows_the_family_of_a_loss_object():
+    from elephas_b200.models import metrics
+    sparse = Sequential([Dense(3, input_shape=(4,))])
+    sparse.compile('sgd', losses.SparseCategoricalCrossentropy(from_logits=True), ['accuracy'])
+    assert sparse._metric_fns[0][1] is metrics.sparse_categorical_accuracy
+    binary = Sequential([Dense(2, input_shape=(4,))])
+    binary.compile('sgd', losses.BinaryCrossentropy(from_logits=True), ['acc'])
+    assert binary._metric_fns[0][1] is metrics.binary_accuracy
+    rng = np.random.default_rng(0)
+    x, labels = rng.standard_normal((64, 4)).astype(np.float32), rng.integers(0, 3, 64)
+    loss, acc = sparse.evaluate(x, labels, batch_size=64)
+    assert acc == pytest.approx(float((sparse.predict(x).argmax(1) == labels).mean()))

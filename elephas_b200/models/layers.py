@@ -205,6 +205,20 @@ class Layer:
                     out.append((kind, obj, idx, tensor))
         return out
 
+    # -- symbolic ends (functional API: Model(inputs=base.input, outputs=base.get_layer('x').output)) --------------
+    @property
+    def output(self):
+        if not self.outputs:
+            raise AttributeError("layer %r has not been called on a symbolic input yet" % self.name)
+        return self.outputs[0]
+
+    @property
+    def input(self):  # noqa: A003 - the Keras name
+        if not self.inbound:
+            raise AttributeError("layer %r has not been called on a symbolic input yet" % self.name)
+        ins = self.inbound[0]
+        return ins[0] if len(ins) == 1 else list(ins)
+
     # -- weights -------------------------------------------------------------
     def add_weight(self, name, tensor, trainable=True):
         tensor.requires_grad_(bool(trainable and self.trainable))

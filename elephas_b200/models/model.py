@@ -115,6 +115,7 @@ class History:
     def __init__(self):
         self.history = {}
         self.epoch = []
+        self.params, self.model = {}, None
 
     def _append(self, epoch, logs):
         self.epoch.append(epoch)
@@ -316,6 +317,22 @@ class Model:
     @property
     def built(self):
         return all(l.built for l in self.layers)
+
+    @property
+    def inputs(self):
+        return list(self._inputs)
+
+    @property
+    def outputs(self):
+        return list(self._outputs)
+
+    @property
+    def input(self):  # noqa: A003 - the Keras name
+        return self._inputs[0] if len(self._inputs) == 1 else list(self._inputs)
+
+    @property
+    def output(self):
+        return self._outputs[0] if len(self._outputs) == 1 else list(self._outputs)
 
     def build(self, input_shape=None):
         return None
@@ -860,7 +877,10 @@ class Model:
             row_weight = row_weight[:split_at] if row_weight is not None else None
         history = History()
         from .callbacks import CallbackList
-        cbs = CallbackList(callbacks, self, {'epochs': epochs, 'batch_size': batch_size, 'samples': _rows(x), 'verbose': verbose})
+        params = {'epochs': epochs, 'batch_size': batch_size, 'samples': _rows(x), 'verbose': verbose,
+                  'steps': steps_per_epoch or -(-_rows(x) // batch_size)}
+        history.params, history.model = params, self
+        cbs = CallbackList(callbacks, self, params)
         self.stop_training = False
         # weighted rows: the loss of the fused engines has no weight operand, the autograd step takes them
         eng = self._native_engine() if row_weight is None and steps_per_epoch is None and validation_freq == 1 else None

@@ -175,3 +175,26 @@ def test_steps_per_epoch_validation_freq_and_unknown_keywords():
     assert len(h.history['val_loss']) == 2
     with pytest.raises(TypeError):
         m.fit(x, y, batchsize=16)
+
+
+def test_symbolic_ends_build_feature_extractors_and_new_heads_on_shared_layers():
+    from elephas_b200.models import Model
+    x, y = _xy(64)
+    base = _model(names=('h', 'o'))
+    base.fit(x, y, batch_size=16, epochs=1)
+    features = Model(inputs=base.input, outputs=base.get_layer('h').output)
+    w = base.get_weights()
+    np.testing.assert_allclose(features.predict(x), np.maximum(x @ w[0] + w[1], 0.0), rtol=1e-5, atol=1e-6)
+    assert base.inputs[0] is base.input and base.outputs[0] is base.output and base.get_layer('o').input is base.get_layer('h').output
+    # a new head on the frozen trunk: only the head moves, and the base model sees nothing of it
+    base.get_layer('h').trainable = False
+    head = Dense(2, activation='softmax', name='new_head')(base.get_layer('h').output)
+    tuned = Model(inputs=base.input, outputs=head)
+    tuned.compile(SGD(learning_rate=0.5), 'categorical_crossentropy')
+    assert len(tuned.trainable_weights) == 2
+    y2 = np.eye(2, dtype=np.float32)[(x[:, 0] > 0).astype(int)]
+    tuned.fit(x, y2, batch_size=16, epochs=2)
+    after = base.get_weights()
+    np.testing.assert_array_equal(after[0], w[0])
+    np.testing.assert_array_equal(after[2], w[2])
+    assert tuned.predict(x).shape == (64, 2) and base.predict(x).shape == (64, 3)

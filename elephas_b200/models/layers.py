@@ -205,6 +205,20 @@ class Layer:
                     out.append((kind, obj, idx, tensor))
         return out
 
+    # -- freezing ------------------------------------------------------------
+    @property
+    def trainable(self):
+        return self._trainable
+
+    @trainable.setter
+    def trainable(self, value):
+        """``layer.trainable = False`` freezes the layer: its weights leave ``trainable_weights`` and stop asking autograd
+        for gradients (recompile the model afterwards, as in Keras)."""
+        self._trainable = bool(value)
+        for _, w, t in self.__dict__.get('_weights', ()):
+            if w.is_leaf:
+                w.requires_grad_(bool(t and value))
+
     # -- symbolic ends (functional API: Model(inputs=base.input, outputs=base.get_layer('x').output)) --------------
     @property
     def output(self):

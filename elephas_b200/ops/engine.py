@@ -168,6 +168,8 @@ def maybe_create(model):
     if plan is None:
         return None
     ops, out_act = plan
+    if any(not op.layer.trainable for op in ops):
+        return None  # frozen layers: the fused step updates the whole flat buffer; the captured torch step skips them
     spec = _training_spec(model, out_act, ops[-1].out_dim)
     kind = _optimizer_spec(model.optimizer)
     if spec is None or kind is None:

@@ -95,3 +95,20 @@ def test_early_stopping_and_checkpoints_on_the_native_engine(tmp_path):
     assert len(h.history['loss']) == 3
     back = load_model(path)
     np.testing.assert_allclose(back.predict(x[:8]), m.predict(x[:8]), rtol=2e-2, atol=2e-3)
+
+
+def test_frozen_layers_stay_frozen_on_the_gpu():
+    x, y = _data()
+    torch.manual_seed(8)
+    m = Sequential([Dense(32, activation='relu', input_shape=(16,), name='trunk'), Dense(4, activation='softmax', name='head')])
+    m.get_layer('trunk').trainable = False
+    m.compile(SGD(learning_rate=0.2), 'categorical_crossentropy')
+    before = m.get_weights()
+    m.to('cuda')
+    assert m._native_engine() is None          # the fused step would update the whole flat buffer
+    m.fit(x, y, batch_size=64, epochs=2)
+    after = m.get_weights()
+    np.testing.assert_array_equal(after[0], before[0])
+    np.testing.assert_array_equal(after[1], before[1])
+    assert not np.array_equal(after[2], before[2])
+    assert m.predict(x).shape == (256, 4)

@@ -624,6 +624,7 @@ class BatchNormalization(Layer):
         layer when nothing else reads the intermediate values (one kernel instead of three passes over the tensor)."""
         nd = x.dim()
         axis = self.axis % nd
+        training = training and self.trainable   # a frozen BatchNormalization runs in inference mode (TF 2 semantics)
         if axis == nd - 1 and x.is_cuda and x.shape[-1] % 8 == 0 and (training or not torch.is_grad_enabled()):
             from ..ops import cnn as _cnn
             if _cnn.usable(x):

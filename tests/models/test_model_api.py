@@ -198,3 +198,19 @@ def test_symbolic_ends_build_feature_extractors_and_new_heads_on_shared_layers()
     np.testing.assert_array_equal(after[0], w[0])
     np.testing.assert_array_equal(after[2], w[2])
     assert tuned.predict(x).shape == (64, 2) and base.predict(x).shape == (64, 3)
+
+
+def test_a_frozen_batch_normalization_uses_its_moving_statistics_while_training():
+    from elephas_b200.models import BatchNormalization
+    rng = np.random.default_rng(0)
+    x = (3.0 + 2.0 * rng.standard_normal((64, 5))).astype(np.float32)
+    y = rng.standard_normal((64, 2)).astype(np.float32)
+    m = Sequential([BatchNormalization(input_shape=(5,), name='bn'), Dense(2, name='d')])
+    m.get_layer('bn').trainable = False
+    m.compile(SGD(learning_rate=0.1), 'mse')
+    before = m.get_weights()
+    m.fit(x, y, batch_size=16, epochs=2)
+    after = m.get_weights()
+    for a, b in zip(after[:4], before[:4]):       # gamma, beta AND the moving statistics stay as they were
+        np.testing.assert_array_equal(a, b)
+    assert not np.array_equal(after[4], before[4])

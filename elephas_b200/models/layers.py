@@ -247,6 +247,54 @@ class Layer:
     def trainable_weights(self):
         return [w for _, w, t in self._weights if t and self.trainable]
 
+    @property
+    def non_trainable_weights(self):
+        return [w for _, w, t in self._weights if not (t and self.trainable)]
+
+    def count_params(self):
+        return int(sum(w.numel() for w in self.weights))
+
+    def get_weights(self):
+        """This layer's weights as NumPy arrays in the Keras layouts (a Dense kernel is ``(in, out)``)."""
+        for model in self._live_owners():
+            model._sync_from_engine()   # a native engine may hold newer values than the layer's tensors
+        return [self.to_keras_layout(i, w.detach()).cpu().numpy().copy() for i, (_, w, _) in enumerate(self._weights)]
+
+    def __getstate__(self):
+        state = dict(self.__dict__)
+        state.pop('_owners', None)   # weak references: the model that owns a copy registers itself again
+        return state
+
+    def _live_owners(self):
+        """The models this layer is part of (weak references kept by ``Model._init_graph``)."""
+        return [m for m in (ref() for ref in self.__dict__.get('_owners', ())) if m is not None]
+
+    def set_weights(self, weights):
+        if len(weights) != len(self._weights):
+            raise ValueError("layer %r expects %d weight arrays, got %d" % (self.name, len(self._weights), len(weights)))
+        import numpy as _np
+        owners = self._live_owners()
+        for model in owners:
+            model._sync_from_engine()
+        with torch.no_grad():
+            for i, ((_, w, _), value) in enumerate(zip(self._weights, weights)):
+                value = _np.ascontiguousarray(self.from_keras_layout(i, _np.asarray(value, dtype=_np.float32)))
+                if tuple(value.shape) != tuple(w.shape):
+                    raise ValueError("layer %r: weight %d expects shape %s, got %s"
+                                     % (self.name, i, tuple(self.to_keras_layout(i, w).shape), tuple(weights[i].shape)))
+                w.copy_(torch.from_numpy(value))
+        for model in owners:
+            model._push_to_engine()
+
+    @property
+    def output_shape(self):
+        return self.output.shape
+
+    @property
+    def input_shape(self):
+        ins = self.input
+        return [t.shape for t in ins] if isinstance(ins, list) else ins.shape
+
     def weight_names(self):
         return ["%s/%s:0" % (self.name, n) for n, _, _ in self._weights]
 

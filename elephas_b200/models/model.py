@@ -187,6 +187,18 @@ class Model:
         for t in order:
             if t.layer not in self.layers:
                 self.layers.append(t.layer)
+        self._register_with_layers()
+
+    def _register_with_layers(self):
+        """Weak back references layer -> model: ``layer.get_weights`` / ``set_weights`` reach the engines through them."""
+        import weakref
+        for layer in self.layers:
+            owners = layer.__dict__.setdefault('_owners', [])
+            owners[:] = [ref for ref in owners if ref() is not None and ref() is not self] + [weakref.ref(self)]
+
+    def __setstate__(self, state):   # copies and unpickled models own their (copied) layers
+        self.__dict__.update(state)
+        self._register_with_layers()
 
     def _fusion_plan(self):
         """Which nodes collapse into their BatchNormalization producer (computed once per graph):
@@ -360,6 +372,20 @@ class Model:
     @property
     def trainable_weights(self):
         return [w for l in self.layers for w in l.trainable_weights]
+
+    @property
+    def non_trainable_weights(self):
+        return [w for l in self.layers for w in l.non_trainable_weights]
+
+    @property
+    def trainable(self):
+        return any(l.trainable for l in self.layers)
+
+    @trainable.setter
+    def trainable(self, value):
+        """``model.trainable = False`` freezes every layer (a trunk inside a larger graph); recompile afterwards."""
+        for layer in self._all_layers():
+            layer.trainable = value
 
     def count_params(self):
         return int(sum(w.numel() for w in self.weights))

@@ -214,3 +214,38 @@ def test_a_frozen_batch_normalization_uses_its_moving_statistics_while_training(
     for a, b in zip(after[:4], before[:4]):       # gamma, beta AND the moving statistics stay as they were
         np.testing.assert_array_equal(a, b)
     assert not np.array_equal(after[4], before[4])
+
+
+def test_layer_level_weights_and_freezing_a_whole_model():
+    m = _model(names=('h', 'o'))
+    h = m.get_layer('h')
+    k, b = h.get_weights()
+    assert k.shape == (6, 8) and b.shape == (8,) and h.count_params() == 56
+    assert h.input_shape == (None, 6) and h.output_shape == (None, 8)
+    h.set_weights([np.ones((6, 8), np.float32), np.zeros(8, np.float32)])
+    np.testing.assert_array_equal(m.get_weights()[0], np.ones((6, 8), np.float32))
+    x = np.ones((2, 6), np.float32)
+    np.testing.assert_allclose(np.maximum(x @ h.get_weights()[0], 0), 6.0)
+    assert h._live_owners() == [m]
+    with pytest.raises(ValueError):
+        h.set_weights([np.ones((8, 6), np.float32), np.zeros(8, np.float32)])
+    with pytest.raises(ValueError):
+        h.set_weights([np.ones((6, 8), np.float32)])
+    assert m.trainable and len(m.non_trainable_weights) == 0
+    m.trainable = False
+    assert not m.trainable and m.trainable_weights == [] and len(m.non_trainable_weights) == 4
+    assert all(not w.requires_grad for w in m.weights)
+    m.trainable = True
+    assert len(m.trainable_weights) == 4 and all(w.requires_grad for w in m.weights)
+
+
+def test_models_stay_picklable_and_copies_own_their_layers():
+    import copy
+    import pickle
+    m = _model()
+    twin, back = copy.deepcopy(m), pickle.loads(pickle.dumps(m))
+    x = np.ones((2, 6), np.float32)
+    for other in (twin, back):
+        assert other.layers[1]._live_owners() == [other]
+        np.testing.assert_allclose(other.predict(x), m.predict(x), rtol=1e-6)
+    assert m.layers[1]._live_owners() == [m]

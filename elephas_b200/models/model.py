@@ -1041,17 +1041,17 @@ class Model:
         return _join(outs)
 
     @torch.no_grad()
-    def evaluate(self, x=None, y=None, batch_size=None, verbose=0, return_dict=False, **kwargs):
-        stats = self._evaluate(x, y, batch_size)
+    def evaluate(self, x=None, y=None, batch_size=None, verbose=0, sample_weight=None, return_dict=False, **kwargs):
+        stats = self._evaluate(x, y, batch_size, sample_weight)
         if return_dict:
             stats = stats if isinstance(stats, list) else [stats]
             return dict(zip(self.metrics_names, stats))
         return stats
 
-    def _evaluate(self, x, y, batch_size):
+    def _evaluate(self, x, y, batch_size, sample_weight=None):
         self._require_compiled()
         batch_size = int(batch_size or 32)
-        eng = self._native_engine()
+        eng = self._native_engine() if sample_weight is None else None
         if eng is not None:
             stats = eng.evaluate(x, y)
             return stats if len(stats) > 1 else stats[0]
@@ -1060,6 +1060,10 @@ class Model:
         n = _rows(xt)
         sums = [0.0] * len(self.metrics_names)
         self._reset_metrics()
+        weights = None
+        if sample_weight is not None:
+            weights = torch.as_tensor(_row_weights(yt[0] if isinstance(yt, _Multi) else yt, sample_weight, None),
+                                      device=self._device)
         step = max(batch_size, 8192)
         self._tune_cpu_threads(min(step, max(n, 1)))
         for start in range(0, n, step):
@@ -1068,6 +1072,9 @@ class Model:
                 out = self(xb, training=False)
             out = _float(out)
             vals = [self._loss_fn(yb, out)] + [fn(yb, out) for _, fn in self._metric_fns]
+            if weights is not None:   # the loss only, as in fit: sum(w * loss) / rows
+                wb = weights[start:start + step]
+                vals[0] = vals[0] * wb.reshape(vals[0].shape[0], *([1] * (vals[0].dim() - 1)))
             for i, v in enumerate(vals):
                 sums[i] += float(v.double().sum())
             penalty = self._regularization_loss()   # weight / activity penalties are part of the reported loss, as in Keras

@@ -249,3 +249,16 @@ def test_models_stay_picklable_and_copies_own_their_layers():
         assert other.layers[1]._live_owners() == [other]
         np.testing.assert_allclose(other.predict(x), m.predict(x), rtol=1e-6)
     assert m.layers[1]._live_owners() == [m]
+
+
+def test_evaluate_takes_sample_weights():
+    x, y = _xy(40)
+    m = _model()
+    rng = np.random.default_rng(4)
+    w = rng.uniform(0, 2, 40).astype(np.float32)
+    p = np.clip(m.predict(x), 1e-7, 1.0)
+    per_row = -(y * np.log(p)).sum(1)
+    loss, acc = m.evaluate(x, y, batch_size=16, sample_weight=w)
+    assert loss == pytest.approx(float((per_row * w).mean()), rel=1e-5)
+    assert acc == pytest.approx(float((p.argmax(1) == y.argmax(1)).mean()))
+    assert m.evaluate(x, y, sample_weight=np.ones(40))[0] == pytest.approx(m.evaluate(x, y)[0], rel=1e-6)

@@ -8,6 +8,8 @@ large configurations named in BASELINE.json.
 * ``otto_mlp``      93-512-512-512-9 with Dropout(0.5) (``examples/ml_pipeline_otto.py:57-68``)
 * ``wide_mlp``      4096-wide x 8 layer regression MLP (BASELINE.json config 4)
 * ``resnet50``      ResNet-50-shaped CNN (BASELINE.json config 5)
+* ``lstm_classifier`` / ``transformer_classifier``  sequence models (what a Keras user brings besides MLPs and CNNs: the
+                    reference accepts any ``model_from_json``-able model, ``elephas/worker.py:30``)
 """
 from .layers import (Activation, Add, BatchNormalization, Conv2D, Dense, Dropout, GlobalAveragePooling2D, Input,
                      MaxPooling2D, ZeroPadding2D)
@@ -103,3 +105,32 @@ def resnet50(input_shape=(224, 224, 3), classes=1000):
     x = GlobalAveragePooling2D(name='avg_pool')(x)
     out = Dense(classes, activation='softmax', name='predictions')(x)
     return Model(inputs=inp, outputs=out, name='resnet50')
+
+
+def lstm_classifier(vocab=20000, maxlen=80, embed=128, units=128, classes=2, bidirectional=False, dropout=0.2):
+    """The Keras IMDB example's shape: ``Embedding(mask_zero) -> LSTM (optionally Bidirectional) -> Dense`` over padded
+    token sequences (``keras.utils.pad_sequences``; the padding steps are skipped through the mask)."""
+    from .layers_extra import LSTM, Bidirectional, Embedding
+    rnn = LSTM(units, dropout=dropout, recurrent_dropout=0.0)
+    return Sequential([Embedding(vocab, embed, mask_zero=True, input_length=maxlen),
+                       Bidirectional(rnn) if bidirectional else rnn,
+                       Dense(classes, activation='softmax' if classes > 1 else 'sigmoid')], name='lstm_classifier')
+
+
+def transformer_classifier(vocab=20000, maxlen=128, embed=64, heads=4, ff=128, blocks=2, classes=2, dropout=0.1):
+    """A small pre-softmax transformer encoder for sequence classification (the Keras "text classification with
+    Transformer" example): token embedding, ``blocks`` x (self-attention + feed-forward, each with residual and
+    LayerNormalization), average pooling, Dense head."""
+    from .layers_extra import Embedding, GlobalAveragePooling1D, LayerNormalization
+    from .layers_more import MultiHeadAttention
+    inp = Input(shape=(maxlen,), name='tokens')
+    x = Embedding(vocab, embed, name='token_embedding')(inp)
+    for b in range(blocks):
+        att = MultiHeadAttention(heads, embed // heads, dropout=dropout, name='block%d_attention' % b)([x, x])
+        x = LayerNormalization(epsilon=1e-6, name='block%d_norm1' % b)(Add(name='block%d_add1' % b)([x, att]))
+        f = Dense(ff, activation='relu', name='block%d_ff1' % b)(x)
+        f = Dropout(dropout, name='block%d_drop' % b)(Dense(embed, name='block%d_ff2' % b)(f))
+        x = LayerNormalization(epsilon=1e-6, name='block%d_norm2' % b)(Add(name='block%d_add2' % b)([x, f]))
+    x = GlobalAveragePooling1D(name='pool')(x)
+    out = Dense(classes, activation='softmax', name='predictions')(x)
+    return Model(inputs=inp, outputs=out, name='transformer_classifier')

@@ -107,3 +107,27 @@ def test_a_small_transformer_block_trains_and_round_trips():
     np.testing.assert_allclose(back.predict(x[:16]), m.predict(x[:16]), rtol=1e-5, atol=1e-6)
     names = [n for n in back.get_layer('mha').weight_names()]
     assert names[0] == 'mha/query/kernel:0' and names[-1] == 'mha/attention_output/bias:0'
+
+
+def test_zoo_sequence_models_train_through_spark_model():
+    from elephas_b200.models import zoo
+    from elephas_b200.spark import SparkContext
+    from elephas_b200.spark_model import SparkModel
+    from elephas_b200.utils.rdd_utils import to_simple_rdd
+    rng = np.random.default_rng(0)
+    tokens = rng.integers(1, 30, (192, 10)).astype(np.float32)
+    tokens[:, 7:] *= (rng.random((192, 3)) < 0.5)            # some trailing padding
+    y = np.eye(2, dtype=np.float32)[(np.sum(tokens < 10, axis=1) >= 3).astype(int)]
+    sc = SparkContext.getOrCreate()
+    for build in (lambda: zoo.lstm_classifier(vocab=30, maxlen=10, embed=8, units=12, bidirectional=True, dropout=0.0),
+                  lambda: zoo.transformer_classifier(vocab=30, maxlen=10, embed=16, heads=2, ff=32, blocks=1, dropout=0.0)):
+        torch.manual_seed(0)
+        model = build()
+        model.compile(Adam(learning_rate=0.02), 'categorical_crossentropy', ['acc'])
+        before = model.evaluate(tokens, y, batch_size=64)[0]
+        sm = SparkModel(model, mode='synchronous', num_workers=2)
+        sm.fit(to_simple_rdd(sc, tokens, y), epochs=6, batch_size=16, verbose=0)
+        after = sm.evaluate(tokens, y)
+        assert after[0] < before and len(sm.predict(tokens[:5])) == 5
+        again = model_from_json(model.to_json())
+        assert again.count_params() == model.count_params()

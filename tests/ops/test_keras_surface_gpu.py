@@ -112,3 +112,23 @@ def test_frozen_layers_stay_frozen_on_the_gpu():
     np.testing.assert_array_equal(after[1], before[1])
     assert not np.array_equal(after[2], before[2])
     assert m.predict(x).shape == (256, 4)
+
+
+@pytest.mark.parametrize('family', ['lstm', 'transformer'])
+def test_sequence_models_train_in_the_captured_step(family):
+    from elephas_b200.models import zoo
+    from elephas_b200.models.optimizers import Adam
+    rng = np.random.default_rng(0)
+    tokens = rng.integers(1, 30, (256, 12)).astype(np.float32)
+    tokens[:, 9:] *= (rng.random((256, 3)) < 0.5)
+    y = np.eye(2, dtype=np.float32)[(np.sum(tokens < 10, axis=1) >= 4).astype(int)]
+    torch.manual_seed(0)
+    m = zoo.lstm_classifier(vocab=30, maxlen=12, embed=16, units=16, bidirectional=True, dropout=0.0) if family == 'lstm' \
+        else zoo.transformer_classifier(vocab=30, maxlen=12, embed=16, heads=2, ff=32, blocks=1, dropout=0.0)
+    m.compile(Adam(learning_rate=0.02), 'categorical_crossentropy', ['acc'])
+    cpu_out = m.predict(tokens[:16])
+    m.to('cuda')
+    np.testing.assert_allclose(m.predict(tokens[:16]), cpu_out, rtol=1e-3, atol=1e-4)
+    h = m.fit(tokens, y, batch_size=64, epochs=8)
+    assert m._torch_step is not None                       # the step was captured, not run eagerly
+    assert h.history['loss'][-1] < 0.8 * h.history['loss'][0]

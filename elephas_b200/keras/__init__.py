@@ -8,7 +8,7 @@ of its imports and nothing else.
 The reference has no model code of its own: every script it runs builds a ``tensorflow.keras`` model first
 (``examples/mnist_mlp_spark.py:1-10``). These modules are thin re-exports; the implementation lives in ``models/``.
 """
-from . import (callbacks, constraints, initializers, layers, losses, metrics, models, optimizers, preprocessing,  # noqa: F401
+from . import (backend, callbacks, constraints, initializers, layers, losses, metrics, models, optimizers, preprocessing,  # noqa: F401
                regularizers, utils)
 from ..models import mixed_precision  # noqa: F401
 from .layers import Input  # noqa: F401

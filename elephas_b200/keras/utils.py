@@ -1,2 +1,2 @@
 """``keras.utils``."""
-from ..models.utils import normalize, pad_sequences, to_categorical  # noqa: F401
+from ..models.utils import normalize, pad_sequences, set_random_seed, to_categorical  # noqa: F401

@@ -38,3 +38,14 @@ def normalize(x, axis=-1, order=2):
     norms = np.atleast_1d(np.linalg.norm(x, order, axis))
     norms[norms == 0] = 1
     return x / np.expand_dims(norms, axis)
+
+
+def set_random_seed(seed):
+    """``keras.utils.set_random_seed``: seeds Python's, NumPy's and torch's generators (initial weights, shuffling and
+    dropout masks of this package draw from the torch one)."""
+    import random
+
+    import torch
+    random.seed(seed)
+    np.random.seed(seed)
+    torch.manual_seed(seed)

@@ -70,3 +70,20 @@ def test_global_dtype_policy_sets_the_compute_dtype_of_new_models():
     finally:
         mixed_precision.set_global_policy(mixed_precision.Policy('float32'))
     assert Sequential([Dense(2, input_shape=(3,))])._compute_dtype == 'float32'
+
+
+def test_backend_and_seed_helpers():
+    import elephas_b200.keras as keras
+    from elephas_b200.keras.layers import Dense
+    from elephas_b200.keras.models import Sequential
+    keras.backend.clear_session()
+    first = Sequential([Dense(2, input_shape=(3,)), Dense(1)])
+    assert [l.name for l in first.layers[1:]] == ['dense', 'dense_1']
+    keras.backend.clear_session()
+    assert Sequential([Dense(2, input_shape=(3,))]).layers[-1].name == 'dense'
+    keras.utils.set_random_seed(11)
+    a = Sequential([Dense(4, input_shape=(3,))]).get_weights()[0]
+    keras.utils.set_random_seed(11)
+    b = Sequential([Dense(4, input_shape=(3,))]).get_weights()[0]
+    np.testing.assert_array_equal(a, b)
+    assert keras.backend.epsilon() == 1e-7 and keras.backend.image_data_format() == 'channels_last'

@@ -67,7 +67,33 @@ def gelu(x):
     return F.gelu(x)
 
 
+def relu6(x):
+    return torch.clamp(x, 0.0, 6.0)
+
+
+def leaky_relu(x, negative_slope=0.2):   # (the Keras 3 activation of that name; the LeakyReLU layer defaults to 0.3)
+    return F.leaky_relu(x, negative_slope)
+
+
+def mish(x):
+    return x * torch.tanh(F.softplus(x))
+
+
+def hard_silu(x):
+    return x * torch.clamp(x / 6.0 + 0.5, 0.0, 1.0)
+
+
+def log_softmax(x, axis=-1):
+    return torch.log_softmax(x, dim=axis)
+
+
+def softmax_v2(x):
+    return softmax(x)
+
+
 _BUILTIN = {
+    'relu6': relu6, 'leaky_relu': leaky_relu, 'mish': mish, 'hard_silu': hard_silu, 'hard_swish': hard_silu,
+    'log_softmax': log_softmax, 'softmax_v2': softmax_v2,
     'linear': linear, 'relu': relu, 'sigmoid': sigmoid, 'tanh': tanh, 'softmax': softmax, 'softplus': softplus,
     'softsign': softsign, 'elu': elu, 'selu': selu, 'exponential': exponential, 'hard_sigmoid': hard_sigmoid,
     'swish': swish, 'silu': swish, 'gelu': gelu,

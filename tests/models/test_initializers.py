@@ -52,3 +52,21 @@ def test_structured_initializers():
         _kernel('sideways')
     with pytest.raises(ValueError):
         _kernel({'class_name': 'VarianceScaling', 'config': {'distribution': 'cauchy'}})
+
+
+def test_the_newer_activation_names():
+    import torch
+
+    from elephas_b200.models import activations
+    x = torch.linspace(-8, 8, 33)
+    for name, ref in (('relu6', torch.nn.functional.relu6), ('mish', torch.nn.functional.mish),
+                      ('hard_silu', torch.nn.functional.hardswish), ('hard_swish', torch.nn.functional.hardswish),
+                      ('leaky_relu', lambda t: torch.nn.functional.leaky_relu(t, 0.2)), ('silu', torch.nn.functional.silu)):
+        got_name, fn = activations.get(name)
+        assert got_name == name
+        np.testing.assert_allclose(fn(x).numpy(), ref(x).numpy(), rtol=1e-5, atol=1e-6)
+    m = Sequential([Dense(4, activation='mish', input_shape=(3,)), Dense(2, activation='log_softmax')])
+    back = model_from_json(m.to_json())
+    assert [l.activation_name for l in back.layers[1:]] == ['mish', 'log_softmax']
+    with pytest.raises(ValueError):
+        activations.get('squareplus')

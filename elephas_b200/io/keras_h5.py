@@ -102,7 +102,7 @@ def _write_weights(model, mw):
         g.attrs['weight_names'] = np.array([n.encode('utf8') for n in names]) if names else np.zeros((0,))
         for idx, (name, (_, w, _t)) in enumerate(zip(names, layer._weights)):
             value = layer.to_keras_layout(idx, w.detach()).cpu().numpy()
-            g.create_dataset(name, np.ascontiguousarray(value, dtype=np.float32))
+            g.create_dataset(name, np.asarray(value, dtype=np.float32, order='C'))  # (ascontiguousarray would turn () into (1,))
 
 
 def save_weights(model, filepath, overwrite=True):

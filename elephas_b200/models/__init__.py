@@ -15,7 +15,7 @@ from .layers_extra import (ELU, GRU, LSTM, Average, AveragePooling1D, Bidirectio
                            Subtract, TimeDistributed, UpSampling2D)
 from . import callbacks  # noqa: F401
 from .layers_more import (AlphaDropout, Attention, Cropping1D, Cropping2D, GaussianDropout, Lambda,  # noqa: F401
-                          MultiHeadAttention, PReLU, Rescaling, ThresholdedReLU, UpSampling1D, ZeroPadding1D)
+                          MultiHeadAttention, Normalization, PReLU, Rescaling, ThresholdedReLU, UpSampling1D, ZeroPadding1D)
 from .model import (History, Model, Sequential, load_model, model_from_config, model_from_json,  # noqa: F401
                     to_categorical)
 from .optimizers import SGD, Adadelta, Adagrad, Adam, Adamax, AdamW, Nadam, RMSprop  # noqa: F401

@@ -278,7 +278,7 @@ class Layer:
             model._sync_from_engine()
         with torch.no_grad():
             for i, ((_, w, _), value) in enumerate(zip(self._weights, weights)):
-                value = _np.ascontiguousarray(self.from_keras_layout(i, _np.asarray(value, dtype=_np.float32)))
+                value = _np.asarray(self.from_keras_layout(i, _np.asarray(value, dtype=_np.float32)), order='C')
                 if tuple(value.shape) != tuple(w.shape):
                     raise ValueError("layer %r: weight %d expects shape %s, got %s"
                                      % (self.name, i, tuple(self.to_keras_layout(i, w).shape), tuple(weights[i].shape)))

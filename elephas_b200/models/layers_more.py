@@ -228,6 +228,53 @@ class Rescaling(Layer):
         return {'scale': self.scale, 'offset': self.offset}
 
 
+class Normalization(Layer):
+    """``keras.layers.Normalization``: ``(x - mean) / sqrt(variance)`` over the feature axis, with the statistics either
+    given (``mean=`` / ``variance=``) or learned from data by ``adapt(data)`` before training. Weights (non-trainable, the
+    Keras order): ``mean``, ``variance``, ``count``."""
+
+    def __init__(self, axis=-1, mean=None, variance=None, invert=False, **kwargs):
+        super().__init__(**kwargs)
+        axis = axis[0] if isinstance(axis, (list, tuple)) else axis
+        if axis not in (-1, None):
+            raise ValueError("Normalization: only axis=-1 (per feature) or None (one scalar) is supported")
+        if (mean is None) != (variance is None):
+            raise ValueError("Normalization: pass both mean and variance, or neither (and call adapt)")
+        self.axis, self.invert = axis, bool(invert)
+        self._given = None if mean is None else (np.asarray(mean, dtype=np.float32), np.asarray(variance, dtype=np.float32))
+        self.mean = self.variance = self.count = None
+
+    def build(self, input_shape):
+        width = 1 if self.axis is None else int(input_shape[-1])
+        mean, var = (np.zeros(width, np.float32), np.ones(width, np.float32)) if self._given is None else \
+            (np.broadcast_to(self._given[0].reshape(-1), (width,)).copy(), np.broadcast_to(self._given[1].reshape(-1), (width,)).copy())
+        self.mean = self.add_weight('mean', torch.from_numpy(mean), trainable=False)
+        self.variance = self.add_weight('variance', torch.from_numpy(var), trainable=False)
+        self.count = self.add_weight('count', torch.zeros(()), trainable=False)
+        self.built = True
+
+    def adapt(self, data, batch_size=None, steps=None):
+        data = np.asarray(data, dtype=np.float64)
+        if not self.built:
+            self.build((None,) + tuple(data.shape[1:]))
+        flat = data.reshape(-1, 1) if self.axis is None else data.reshape(-1, data.shape[-1])
+        with torch.no_grad():
+            self.mean.copy_(torch.from_numpy(flat.mean(axis=0).astype(np.float32)))
+            self.variance.copy_(torch.from_numpy(flat.var(axis=0).astype(np.float32)))
+            self.count.fill_(float(flat.shape[0]))
+        for model in self._live_owners():
+            model._push_to_engine()
+
+    def call(self, x, training=False):
+        scale = torch.clamp(torch.sqrt(self.variance), min=1e-7)
+        return x * scale + self.mean if self.invert else (x - self.mean) / scale
+
+    def _extra_config(self):
+        given = self._given
+        return {'axis': None if self.axis is None else [self.axis], 'invert': self.invert,
+                'mean': None if given is None else given[0].tolist(), 'variance': None if given is None else given[1].tolist()}
+
+
 # --------------------------------------------------------------------------------------------------------- attention
 class Attention(Layer):
     """Dot-product (Luong) attention over ``[query, value]`` or ``[query, value, key]``; ``use_scale`` learns one scalar."""
@@ -331,6 +378,6 @@ class MultiHeadAttention(Layer):
                 'kernel_constraint': None, 'bias_constraint': None}
 
 
-MORE_LAYERS = (Lambda, PReLU, ThresholdedReLU, AlphaDropout, GaussianDropout, ZeroPadding1D, Cropping1D, Cropping2D,
+MORE_LAYERS = (Normalization, Lambda, PReLU, ThresholdedReLU, AlphaDropout, GaussianDropout, ZeroPadding1D, Cropping1D, Cropping2D,
                UpSampling1D, Rescaling, Attention, MultiHeadAttention)
 LAYER_CLASSES.update({c.__name__: c for c in MORE_LAYERS})

@@ -463,7 +463,7 @@ class Model:
                     src = layer.from_keras_layout(idx, value.detach().cpu().numpy())
                 else:
                     src = layer.from_keras_layout(idx, np.asarray(value))
-                src = torch.from_numpy(np.ascontiguousarray(src, dtype=np.float32))
+                src = torch.from_numpy(np.asarray(src, dtype=np.float32, order='C'))   # (keeps 0-d weights 0-d)
                 if tuple(src.shape) != tuple(w.shape):
                     raise ValueError("weight %s expects shape %s, got %s" % (layer.name, tuple(w.shape), tuple(src.shape)))
                 w.copy_(src)

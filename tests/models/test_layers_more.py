@@ -131,3 +131,30 @@ def test_zoo_sequence_models_train_through_spark_model():
         assert after[0] < before and len(sm.predict(tokens[:5])) == 5
         again = model_from_json(model.to_json())
         assert again.count_params() == model.count_params()
+
+
+def test_normalization_layer_adapts_and_round_trips(tmp_path):
+    from elephas_b200.models import Normalization, load_model
+    rng = np.random.default_rng(0)
+    x = (5.0 + 3.0 * rng.standard_normal((500, 4)) * [1, 2, 3, 4]).astype(np.float32)
+    norm = Normalization(input_shape=(4,))
+    m = Sequential([norm, Dense(1)])
+    norm.adapt(x)
+    z = (x - norm.get_weights()[0]) / np.sqrt(norm.get_weights()[1])
+    np.testing.assert_allclose(z.mean(0), 0.0, atol=1e-4), np.testing.assert_allclose(z.std(0), 1.0, rtol=1e-4)
+    assert [tuple(w.shape) for w in norm.get_weights()] == [(4,), (4,), ()] and norm.trainable_weights == []
+    w = m.get_weights()
+    np.testing.assert_allclose(m.predict(x[:8]), z[:8] @ w[3] + w[4], rtol=1e-4, atol=1e-5)
+    m.compile('sgd', 'mse')
+    before = [a.copy() for a in m.get_weights()[:3]]
+    m.fit(x, x[:, :1], batch_size=50, epochs=1)
+    for a, b in zip(m.get_weights()[:3], before):      # the statistics are not trained
+        np.testing.assert_array_equal(a, b)
+    path = str(tmp_path / 'n.h5')
+    m.save(path)
+    np.testing.assert_allclose(load_model(path).predict(x[:8]), m.predict(x[:8]), rtol=1e-6)
+    fixed = Sequential([Normalization(mean=[1.0, 2.0], variance=[4.0, 9.0], input_shape=(2,))])
+    np.testing.assert_allclose(fixed.predict(np.array([[3.0, 8.0]], np.float32)), [[1.0, 2.0]], rtol=1e-6)
+    assert model_from_json(fixed.to_json()).predict(np.array([[3.0, 8.0]], np.float32)).tolist() == [[1.0, 2.0]]
+    with pytest.raises(ValueError):
+        Normalization(mean=[0.0])
